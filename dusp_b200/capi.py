@@ -1,0 +1,195 @@
+"""ctypes binding of ``libdusp_b200.so`` (C ABI: ``include/dusp_b200.h``).
+
+The library is built in-tree by ``__graft_entry__.build()`` /
+``make -C dusp_b200/csrc``.  There is no fallback: if the shared object is
+missing ``load()`` raises, and without a CUDA device every session call fails.
+"""
+import ctypes
+import os
+
+from . import config
+from .graph import DuspError
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdusp_b200.so")
+_lib = None
+
+OUT_VOICES = 0
+OUT_MIX = 1
+E_UNSUPPORTED = -2
+
+# every symbol include/dusp_b200.h declares (tests check the .so exports them all)
+SYMBOLS = [
+    "dusp_abi_version", "dusp_last_error", "dusp_program_create", "dusp_program_destroy",
+    "dusp_program_num_channels", "dusp_program_num_units", "dusp_program_num_instructions",
+    "dusp_program_num_slots", "dusp_program_bytes_per_voice_sample", "dusp_program_num_params",
+    "dusp_program_param_name", "dusp_program_param_index", "dusp_program_param_default",
+    "dusp_program_disassemble", "dusp_session_create", "dusp_session_destroy", "dusp_session_num_voices",
+    "dusp_session_num_channels", "dusp_session_unit_count", "dusp_session_set_params", "dusp_session_reset",
+    "dusp_session_render", "dusp_session_launch_count", "dusp_session_launch_info", "dusp_rand53",
+]
+
+
+class UnsupportedCircuit(DuspError):
+    """The circuit uses a unit or configuration outside the accelerated path."""
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError("libdusp_b200.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "or `make -C dusp_b200/csrc`); there is no CPU fallback")
+    L = ctypes.CDLL(LIB_PATH)
+    c = ctypes
+    L.dusp_last_error.restype = c.c_char_p
+    L.dusp_program_create.argtypes = [c.c_char_p, c.c_size_t, c.POINTER(c.c_void_p)]
+    L.dusp_program_destroy.argtypes = [c.c_void_p]
+    L.dusp_program_destroy.restype = None
+    for nm in ("num_channels", "num_units", "num_instructions", "num_slots", "num_params"):
+        getattr(L, "dusp_program_" + nm).argtypes = [c.c_void_p]
+    L.dusp_program_bytes_per_voice_sample.argtypes = [c.c_void_p, c.c_int]
+    L.dusp_program_bytes_per_voice_sample.restype = c.c_double
+    L.dusp_program_param_name.argtypes = [c.c_void_p, c.c_int]
+    L.dusp_program_param_name.restype = c.c_char_p
+    L.dusp_program_param_index.argtypes = [c.c_void_p, c.c_char_p]
+    L.dusp_program_param_default.argtypes = [c.c_void_p, c.c_int]
+    L.dusp_program_param_default.restype = c.c_double
+    L.dusp_program_disassemble.argtypes = [c.c_void_p, c.c_char_p, c.c_size_t]
+    L.dusp_program_disassemble.restype = c.c_size_t
+    L.dusp_session_create.argtypes = [c.POINTER(c.c_void_p), c.POINTER(c.c_int), c.c_int, c.c_int, c.POINTER(c.c_void_p)]
+    L.dusp_session_destroy.argtypes = [c.c_void_p]
+    L.dusp_session_destroy.restype = None
+    L.dusp_session_num_voices.argtypes = [c.c_void_p]
+    L.dusp_session_num_channels.argtypes = [c.c_void_p]
+    L.dusp_session_unit_count.argtypes = [c.c_void_p]
+    L.dusp_session_unit_count.restype = c.c_longlong
+    L.dusp_session_set_params.argtypes = [c.c_void_p, c.c_int, c.POINTER(c.c_int), c.c_int, c.POINTER(c.c_double)]
+    L.dusp_session_reset.argtypes = [c.c_void_p]
+    L.dusp_session_render.argtypes = [c.c_void_p, c.c_longlong, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p]
+    L.dusp_session_launch_count.argtypes = [c.c_void_p]
+    L.dusp_session_launch_count.restype = c.c_longlong
+    L.dusp_session_launch_info.argtypes = [c.c_void_p, c.POINTER(c.c_int), c.POINTER(c.c_int), c.POINTER(c.c_int)]
+    L.dusp_rand53.argtypes = [c.c_uint64, c.c_uint64]
+    L.dusp_rand53.restype = c.c_double
+    if L.dusp_abi_version() != 1:
+        raise RuntimeError("libdusp_b200.so ABI version mismatch")
+    assert config.sampleRate == 44100 and config.standardChunkSize == 256  # compiled into the kernels
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc == 0:
+        return
+    msg = load().dusp_last_error().decode()
+    if rc == E_UNSUPPORTED:
+        raise UnsupportedCircuit(msg)
+    raise DuspError(msg)
+
+
+class Program:
+    """A circuit compiled to a flat op program (``dusp_program``)."""
+
+    def __init__(self, blob):
+        L = load()
+        self.blob = blob
+        h = ctypes.c_void_p()
+        data = blob.encode()
+        check(L.dusp_program_create(data, len(data), ctypes.byref(h)))
+        self._h = h
+        self.num_channels = L.dusp_program_num_channels(h)
+        self.num_units = L.dusp_program_num_units(h)
+        self.num_instructions = L.dusp_program_num_instructions(h)
+        self.num_slots = L.dusp_program_num_slots(h)
+
+    def __del__(self):
+        if getattr(self, "_h", None) and _lib is not None:
+            _lib.dusp_program_destroy(self._h)
+            self._h = None
+
+    def params(self):
+        L = load()
+        n = L.dusp_program_num_params(self._h)
+        return [(L.dusp_program_param_name(self._h, i).decode(), L.dusp_program_param_default(self._h, i))
+                for i in range(n)]
+
+    def param_index(self, name):
+        i = load().dusp_program_param_index(self._h, name.encode())
+        if i < 0:
+            raise DuspError("no such parameter: " + name)
+        return i
+
+    def bytes_per_voice_sample(self, out_mode=OUT_VOICES):
+        return load().dusp_program_bytes_per_voice_sample(self._h, out_mode)
+
+    def disassemble(self):
+        L = load()
+        n = L.dusp_program_disassemble(self._h, None, 0)
+        buf = ctypes.create_string_buffer(n)
+        L.dusp_program_disassemble(self._h, buf, n)
+        return buf.value.decode()
+
+
+class Session:
+    """n voices of one or more programs resident on one GPU (``dusp_session``)."""
+
+    def __init__(self, programs, voices, device=0):
+        L = load()
+        self.programs = list(programs)
+        n = len(self.programs)
+        ph = (ctypes.c_void_p * n)(*[p._h for p in self.programs])
+        vc = (ctypes.c_int * n)(*[int(v) for v in voices])
+        h = ctypes.c_void_p()
+        check(L.dusp_session_create(ph, vc, n, int(device), ctypes.byref(h)))
+        self._h = h
+        self.device = device
+        self.num_voices = L.dusp_session_num_voices(h)
+        self.num_channels = L.dusp_session_num_channels(h)
+        self.unit_count = L.dusp_session_unit_count(h)
+
+    def close(self):
+        if getattr(self, "_h", None) and _lib is not None:
+            _lib.dusp_session_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def set_params(self, program_index, names, values):
+        """values: array [n_voices_of_program][len(names)] of float64."""
+        import numpy as np
+        L = load()
+        prog = self.programs[program_index]
+        ids = (ctypes.c_int * len(names))(*[prog.param_index(n) if isinstance(n, str) else int(n) for n in names])
+        vals = np.ascontiguousarray(values, dtype=np.float64)
+        check(L.dusp_session_set_params(self._h, program_index, ids, len(names),
+                                        vals.ctypes.data_as(ctypes.POINTER(ctypes.c_double))))
+
+    def reset(self):
+        check(load().dusp_session_reset(self._h))
+
+    def render_host(self, n_samples, out_mode=OUT_VOICES):
+        """Render into a fresh host array: [voices][channels][n] or [2][n] (mix)."""
+        import numpy as np
+        shape = (self.num_voices, self.num_channels, n_samples) if out_mode == OUT_VOICES else (2, n_samples)
+        out = np.empty(shape, dtype=np.float32)
+        check(load().dusp_session_render(self._h, int(n_samples), out_mode, out.ctypes.data_as(ctypes.c_void_p), None, None))
+        return out
+
+    def render_into_host(self, out, n_samples, out_mode=OUT_VOICES):
+        check(load().dusp_session_render(self._h, int(n_samples), out_mode, ctypes.c_void_p(out), None, None))
+
+    def render_device(self, n_samples, device_ptr, out_mode=OUT_VOICES, stream=None):
+        """Enqueue a render into caller-owned device memory (no synchronisation)."""
+        check(load().dusp_session_render(self._h, int(n_samples), out_mode, None, ctypes.c_void_p(device_ptr),
+                                         ctypes.c_void_p(stream) if stream else None))
+
+    @property
+    def launch_count(self):
+        return load().dusp_session_launch_count(self._h)
+
+    def launch_info(self):
+        g, b, s = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        load().dusp_session_launch_info(self._h, ctypes.byref(g), ctypes.byref(b), ctypes.byref(s))
+        return {"grid": g.value, "block": b.value, "smem_bytes": s.value}

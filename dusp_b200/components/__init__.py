@@ -1,0 +1,713 @@
+"""Hot-path units as host-side graph nodes.
+
+Each class mirrors the reference constructor of the same name: same port
+names in the same declaration order, same defaults (``x || default``), same
+methods that edit state before rendering (``trigger``, ``stop``, ``waveform``,
+``setSeconds`` ...).  There is no ``_tick`` here -- the per-sample arithmetic of
+every unit lives in ``csrc/render_sm100.cu`` (and, for the tests, in the
+oracle).  ``blob_props`` serialises the state the device kernels start from.
+"""
+from .. import config
+from ..config import js_or
+from ..graph import Unit, DuspError
+
+SR = config.sampleRate
+
+WAVEFORMS = ["sin", "sine", "saw", "square", "triangle", "8bit"]  # waveTables.js:33-40
+SHAPES = ["decay", "attack", "semiSine", "decaySquared"]          # shapeTables.js:20-38
+
+
+def _js_round(x):
+    import math
+    return math.floor(x + 0.5)
+
+
+# ------------------------------------------------------------ oscillators
+class Osc(Unit):
+    """src/components/Osc/Osc.js:6-66"""
+    KIND = "Osc"
+
+    def __init__(self, f=None, waveform=None):
+        super().__init__()
+        self.addInlet("f", {"mono": True, "measuredIn": "Hz"})
+        self.addOutlet("out", {"mono": True, "type": "audio"})
+        self.F = js_or(f, 440)
+        self.phase = 0
+        self.waveform = js_or(waveform, "sin")
+
+    @property
+    def waveform(self):
+        return self._waveform
+
+    @waveform.setter
+    def waveform(self, waveform):  # Osc.js:52-62
+        if waveform == "random":
+            waveform = WAVEFORMS[int(config.host_random.random() * len(WAVEFORMS))]
+        if waveform not in WAVEFORMS:
+            raise DuspError("waveform doesn't exist: " + str(waveform))
+        object.__setattr__(self, "_waveform", waveform)
+
+    def randomPhaseFlip(self):  # Osc.js:63-66
+        if config.host_random.random() < 0.5:
+            self.phase += SR / 2
+
+    def blob_props(self):
+        return {"phase": self.phase}, {"waveform": self._waveform}
+
+
+class MultiChannelOsc(Osc):
+    """src/components/Osc/MultiChannelOsc.js:7-62 (multi-channel f/out, phase per channel)"""
+    KIND = "MultiChannelOsc"
+
+    def __init__(self, f=None, waveform=None):
+        Unit.__init__(self)
+        self.addInlet("f", {"measuredIn": "Hz"})
+        self.addOutlet("out", {"type": "audio"})
+        self.F = js_or(f, 440)
+        self.phase = []
+        self.waveform = js_or(waveform, "sin")
+
+    def resetPhase(self):
+        self.phase = [0 for _ in self.phase]
+
+    def randomPhaseFlip(self):  # :57-61 -- iterates an empty phase array before the first tick
+        if config.host_random.random() < 0.5:
+            self.phase = [p + SR / 2 for p in self.phase]
+
+    def blob_props(self):
+        return {}, {"waveform": self._waveform}
+
+
+# -------------------------------------------------------------- envelopes
+class Ramp(Unit):
+    """src/components/Ramp.js:3-40 (duration in SAMPLES; inert until trigger())"""
+    KIND = "Ramp"
+
+    def __init__(self, duration=None, y0=None, y1=None):
+        super().__init__()
+        self.addOutlet("out", {"mono": True, "type": "control"})
+        self.duration = js_or(duration, self.sampleRate)
+        self.y0 = js_or(y0, 1)
+        self.y1 = js_or(y1, 0)
+        self.t = 0
+        self.playing = False
+
+    def trigger(self):
+        self.playing = True
+        self.t = 0
+        return self
+
+    def blob_props(self):
+        return {"duration": self.duration, "y0": self.y0, "y1": self.y1, "t": self.t,
+                "playing": int(self.playing)}, {}
+
+
+class Shape(Unit):
+    """src/components/Shape/index.js:7-99"""
+    KIND = "Shape"
+
+    def __init__(self, shape=None, durationInSeconds=None, min=None, max=None):
+        super().__init__()
+        self.addInlet("duration", {"mono": True, "type": "time", "measuredIn": "s"})
+        self.addInlet("min", {"mono": True, "type": "scalar"})
+        self.addInlet("max", {"mono": True, "type": "scalar"})
+        self.addOutlet("out", {"mono": True, "type": "control", "min": 0, "max": 1})
+        self.t = 0
+        self.playing = False
+        self.leftEdge = 0
+        self.rightEdge = "shape"
+        self.shape = js_or(shape, "decay")
+        self.DURATION = js_or(durationInSeconds, 1)
+        self.MIN = js_or(min, 0)
+        self.MAX = js_or(max, 1)
+
+    def __setattr__(self, name, val):
+        if name == "shape":  # index.js:103-109
+            if val not in SHAPES:
+                raise DuspError(self.label + ":\n\tinvalid shape function: " + str(val))
+            object.__setattr__(self, "_shape", val)
+        else:
+            super().__setattr__(name, val)
+
+    @property
+    def shape(self):
+        return self._shape
+
+    dusp_flags = {"trigger": lambda self: self.trigger()}  # index.js:62-67
+
+    def trigger(self):
+        self.playing = True
+        self.t = 0
+        return self
+
+    def stop(self):
+        self.playing = False
+
+    def blob_props(self):
+        p = {"t": self.t, "playing": int(self.playing), "finished": int(self.finished)}
+        s = {"shape": self._shape}
+        for nm in ("leftEdge", "rightEdge"):
+            v = getattr(self, nm)
+            if isinstance(v, str):
+                s[nm] = v
+            else:
+                p[nm] = v
+        return p, s
+
+
+class AHD(Unit):
+    """src/components/AHD.js:6-76"""
+    KIND = "AHD"
+
+    def __init__(self, attack=None, hold=None, decay=None):
+        super().__init__()
+        self.addInlet("attack", {"mono": True, "type": "time", "measuredIn": "s"})
+        self.addInlet("hold", {"mono": True, "type": "time", "measuredIn": "s"})
+        self.addInlet("decay", {"mono": True, "type": "time", "measuredIn": "s"})
+        self.addOutlet("out", {"mono": True, "type": "control", "min": 0, "max": 1})
+        self.ATTACK = js_or(attack, 0)
+        self.HOLD = js_or(hold, 0)
+        self.DECAY = js_or(decay, 0)
+        self.state = 0
+        self.playing = False
+        self.t = 0
+
+    def trigger(self):
+        self.state = 1
+        self.playing = True
+        return self
+
+    def stop(self):
+        self.state = 0
+        self.playing = False
+        return self
+
+    def blob_props(self):
+        return {"state": self.state, "playing": int(self.playing), "t": self.t}, {}
+
+
+class Timer(Unit):
+    """src/components/Timer.js:25-46"""
+    KIND = "Timer"
+
+    def __init__(self):
+        super().__init__()
+        self.addOutlet("out", {"mono": True})
+        self.t = 0
+
+    def trigger(self):
+        self.t = 0
+
+    def blob_props(self):
+        return {"t": self.t}, {}
+
+
+class Noise(Unit):
+    """src/components/Noise.js:3-28.  ``Math.random`` is replaced by the
+    injected counter-based generator: the unit owns a 64-bit stream ``seed``;
+    draw 0 initialises ``y`` (ctor, :10), draws 1.. happen in ``_tick``."""
+    KIND = "Noise"
+
+    def __init__(self, f=None, seed=None):
+        super().__init__()
+        self.addInlet("f", {"measuredIn": "Hz"})
+        self.addOutlet("out", {"type": "audio"})
+        self.F = js_or(f, Unit.sampleRate)
+        self.phase = 0
+        self.seed = config.host_random.next_noise_seed() if seed is None else int(seed) & ((1 << 64) - 1)
+        self.draw = 1
+        self.y = config.rand53(self.seed, 0) * 2 - 1
+
+    def reseed(self, seed):
+        self.seed = int(seed) & ((1 << 64) - 1)
+        self.draw = 1
+        self.y = config.rand53(self.seed, 0) * 2 - 1
+        return self
+
+    def blob_props(self):
+        return {"phase": self.phase, "seed_lo": self.seed & 0xFFFFFFFF, "seed_hi": self.seed >> 32,
+                "draw": self.draw, "y": self.y}, {}
+
+
+# ---------------------------------------------------------------- filters
+class Filter(Unit):
+    """src/components/Filter.js:5-104 (2nd-order Butterworth, LP/HP)"""
+    KIND = "Filter"
+
+    def __init__(self, input=None, f=None, kind=None):
+        super().__init__()
+        self.addInlet("in", {"type": "audio"})
+        self.addInlet("f", {"mono": True, "measuredIn": "Hz"})
+        self.addOutlet("out", {"type": "audio"})
+        if js_or(input, None) is not None:
+            self.IN = input
+        if js_or(f, None) is not None:
+            self.F = f
+        self.kind = js_or(kind, "LP")
+
+    def __setattr__(self, name, val):
+        if name == "kind":  # Filter.js:56-64
+            if val not in ("LP", "HP", "BP", "BR"):
+                raise DuspError("invalid filter type: " + str(val))
+            object.__setattr__(self, "_kind", val)
+        else:
+            super().__setattr__(name, val)
+
+    @property
+    def kind(self):
+        return self._kind
+
+    def blob_props(self):
+        return {}, {"kind": self._kind}
+
+
+# ------------------------------------------------------------- arithmetic
+class _AB(Unit):
+    DEFAULT = 0
+
+    def __init__(self, a=None, b=None):
+        super().__init__()
+        self.addInlet("a")
+        self.addInlet("b")
+        self.addOutlet("out")
+        self.A = js_or(a, self.DEFAULT)
+        self.B = js_or(b, self.DEFAULT)
+
+
+class Multiply(_AB):
+    """src/components/Multiply.js:4-34"""
+    KIND = "Multiply"
+    DEFAULT = 1
+
+
+class Divide(_AB):
+    """src/components/Divide.js:3-27"""
+    KIND = "Divide"
+    DEFAULT = 1
+
+
+class SignalCombiner(_AB):
+    """src/components/SignalCombiner.js:3-33"""
+    KIND = "Sum"
+
+
+class Sum(SignalCombiner):
+    """src/components/Sum.js:5-44"""
+    KIND = "Sum"
+
+    @staticmethod
+    def many(inputs):  # Sum.js:18-29
+        if len(inputs) == 1:
+            return inputs[0]
+        sums = [Sum(inputs[0], inputs[1])]
+        for i in range(2, len(inputs)):
+            sums.append(Sum(sums[i - 2], inputs[i]))
+        return sums[-1]
+
+
+class Subtract(_AB):
+    """src/components/Subtract.js:4-29"""
+    KIND = "Subtract"
+
+
+class Pow(Unit):
+    """src/components/Pow.js:3-32 (no defaults: undefined operands throw)"""
+    KIND = "Pow"
+
+    def __init__(self, a=None, b=None):
+        super().__init__()
+        self.addInlet("a")
+        self.addInlet("b")
+        self.addOutlet("out")
+        self.A = a
+        self.B = b
+
+
+class ConcatChannels(_AB):
+    """src/components/ConcatChannels.js:3-30"""
+    KIND = "ConcatChannels"
+
+
+class _In(Unit):
+    DEFAULT = 0
+
+    def __init__(self, input=None):
+        super().__init__()
+        self.addInlet("in")
+        self.addOutlet("out")
+        self.IN = js_or(input, self.DEFAULT)
+
+
+class PolarityInvert(_In):
+    """src/components/PolarityInvert.js:3-22"""
+    KIND = "PolarityInvert"
+
+
+class Abs(_In):
+    """src/components/Abs.js:3-24"""
+    KIND = "Abs"
+
+
+class DecibelToScaler(Unit):
+    """src/components/DecibelToScaler.js:3-19"""
+    KIND = "DecibelToScaler"
+
+    def __init__(self, input=None):
+        super().__init__()
+        self.addInlet("in", {"measuredIn": "dB"})
+        self.addOutlet("out")
+        self.IN = js_or(input, 0)
+
+
+class SemitoneToRatio(_In):
+    """src/components/SemitoneToRatio.js:3-22"""
+    KIND = "SemitoneToRatio"
+    DEFAULT = 69
+
+
+class MidiToFrequency(Unit):
+    """src/components/MidiToFrequency.js:3-21"""
+    KIND = "MidiToFrequency"
+
+    def __init__(self, midi=None):
+        super().__init__()
+        self.addInlet("midi", {"type": "midi"})
+        self.addOutlet("frequency", {"measuredIn": "Hz"})
+        self.MIDI = js_or(midi, 69)
+
+
+class SecondsToSamples(Unit):
+    """src/components/SecondsToSamples.js:4-20"""
+    KIND = "SecondsToSamples"
+
+    def __init__(self):
+        super().__init__()
+        self.addInlet("in", {"measuredIn": "s"})
+        self.addOutlet("out", {"measuredIn": "samples"})
+
+
+class Repeater(Unit):
+    """src/components/Repeater.js:3-30"""
+    KIND = "Repeater"
+
+    def __init__(self, val=None, measuredIn=None):
+        super().__init__()
+        self.addInlet("in", {"measuredIn": measuredIn})
+        self.addOutlet("out", {"measuredIn": measuredIn})
+        self.measuredIn = measuredIn
+        self.IN = js_or(val, 0)
+
+
+class FixedMultiply(Unit):
+    """src/components/FixedMultiply.js:3-22"""
+    KIND = "FixedMultiply"
+
+    def __init__(self, sf=None, input=None):
+        super().__init__()
+        self.addInlet("in", {"mono": True})
+        self.addOutlet("out", {"mono": True})
+        self.sf = sf
+        self.IN = js_or(input, 0)
+
+    def blob_props(self):
+        return {"sf": float("nan") if self.sf is None else self.sf}, {}
+
+
+class Gain(Unit):
+    """src/components/Gain.js:3-28"""
+    KIND = "Gain"
+
+    def __init__(self, gain=None):
+        super().__init__()
+        self.addInlet("in")
+        self.addInlet("gain", {"mono": True, "measuredIn": "dB"})
+        self.addOutlet("out")
+        self.GAIN = js_or(gain, 0)
+
+
+class Clip(Unit):
+    """src/components/Clip.js:3-23 (THRESHOLD = undefined throws, as in the reference)"""
+    KIND = "Clip"
+
+    def __init__(self, threshold=None):
+        super().__init__()
+        self.addInlet("in")
+        self.addInlet("threshold")
+        self.addOutlet("out")
+        self.THRESHOLD = threshold
+
+
+class _InThreshold(Unit):
+    def __init__(self, input=None, threshold=None):
+        super().__init__()
+        self.addInlet("in")
+        self.addInlet("threshold")
+        self.addOutlet("out")
+        self.IN = js_or(input, 0)
+        self.THRESHOLD = js_or(threshold, 0)
+
+
+class HardClipAbove(_InThreshold):
+    """src/components/HardClipAbove.js:3-26"""
+    KIND = "HardClipAbove"
+
+
+class HardClipBelow(_InThreshold):
+    """src/components/HardClipBelow.js:3-26"""
+    KIND = "HardClipBelow"
+
+
+class Rescale(Unit):
+    """src/components/Rescale.js:3-37"""
+    KIND = "Rescale"
+
+    def __init__(self, inLower=None, inUpper=None, outLower=None, outUpper=None):
+        super().__init__()
+        for nm in ("in", "inLower", "inUpper", "outLower", "outUpper"):
+            self.addInlet(nm)
+        self.addOutlet("out")
+        self.IN = 0
+        self.INLOWER = js_or(inLower, -1)
+        self.INUPPER = js_or(inUpper, 1)
+        self.OUTLOWER = js_or(outLower, 0)
+        self.OUTUPPER = js_or(outUpper, 1)
+
+
+class CrossFader(Unit):
+    """src/components/CrossFader.js:3-29"""
+    KIND = "CrossFader"
+
+    def __init__(self, a=None, b=None, dial=None):
+        super().__init__()
+        self.addInlet("a", {"type": "audio"})
+        self.addInlet("b", {"type": "audio"})
+        self.addInlet("dial", {"mono": True, "min": 0, "max": 1, "zero": 0.5})
+        self.addOutlet("out", {"type": "audio"})
+        self.A = js_or(a, 0)
+        self.B = js_or(b, 0)
+        self.DIAL = js_or(dial, 0)
+
+
+class Pan(Unit):
+    """src/components/Pan.js:3-28"""
+    KIND = "Pan"
+
+    def __init__(self, input=None, pan=None):
+        super().__init__()
+        self.addInlet("in", {"mono": True, "type": "audio"})
+        self.addInlet("pan", {"mono": True, "min": -1, "max": 1})
+        self.addOutlet("out", {"numberOfChannels": 2, "type": "audio"})
+        self.PAN = js_or(pan, 0)
+        self.IN = js_or(input, 0)
+        self.compensationDB = 1.5
+
+    def blob_props(self):
+        return {"compensationDB": self.compensationDB}, {}
+
+
+class PickChannel(Unit):
+    """src/components/PickChannel.js:3-21"""
+    KIND = "PickChannel"
+
+    def __init__(self, input=None, c=None):
+        super().__init__()
+        self.addInlet("in")
+        self.addInlet("c", {"mono": True})
+        self.addOutlet("out", {"mono": True})
+        self.IN = js_or(input, 0)
+        self.C = js_or(c, 0)
+
+
+class VectorMagnitude(Unit):
+    """src/components/VectorMagnitude.js:5-28"""
+    KIND = "VectorMagnitude"
+
+    def __init__(self):
+        super().__init__()
+        self.addInlet("in")
+        self.addOutlet("out", {"mono": True})
+        self.IN = [0, 0]
+
+
+# ----------------------------------------------------------------- delays
+class Delay(Unit):
+    """src/components/Delay.js:6-43 (write-ahead interpolating delay, 5 s ring per channel)"""
+    KIND = "Delay"
+
+    def __init__(self, input=None, delay=None, maxDelay=None):
+        super().__init__()
+        self.addInlet("in")
+        self.addInlet("delay", {"measuredIn": "samples"})
+        self.addOutlet("out")
+        self.maxDelay = js_or(maxDelay, Unit.sampleRate * 5)
+        self.IN = js_or(input, 0)
+        self.DELAY = js_or(delay, 4410)
+
+    def blob_props(self):
+        return {"maxDelay": int(self.maxDelay)}, {}
+
+
+class MonoDelay(Unit):
+    """src/components/MonoDelay.js:3-30"""
+    KIND = "MonoDelay"
+
+    def __init__(self, input=None, delay=None):
+        super().__init__()
+        self.addInlet("in", {"mono": True, "type": "audio"})
+        self.addInlet("delay", {"mono": True, "measuredIn": "samples"})
+        self.addOutlet("out", {"mono": True, "type": "audio"})
+        self.maxDelay = Unit.sampleRate * 5
+        self.IN = js_or(input, 0)
+        self.DELAY = js_or(delay, 4410)
+
+
+class ReadBackDelay(Unit):
+    """src/components/ReadBackDelay.js:4-43"""
+    KIND = "ReadBackDelay"
+
+    def __init__(self, input=None, delay=None, bufferLength=None):
+        super().__init__()
+        self.addInlet("in")
+        self.addInlet("delay", {"measuredIn": "samples"})
+        self.addOutlet("out")
+        self.bufferLength = js_or(bufferLength, config.sampleRate)
+        self.tBuffer = 0
+        self.IN = js_or(input, 0)
+        self.DELAY = js_or(delay, 0)
+
+    def blob_props(self):
+        return {"bufferLength": int(self.bufferLength), "tBuffer": self.tBuffer}, {}
+
+
+class FixedDelay(Unit):
+    """src/components/FixedDelay.js:3-38"""
+    KIND = "FixedDelay"
+
+    def __init__(self, delayTime=None):
+        super().__init__()
+        self.addInlet("in", {"mono": True, "type": "audio"})
+        self.addOutlet("out", {"mono": True, "type": "audio"})
+        self.setSeconds(delayTime)
+        self.tBuffer = 0
+
+    def setDelayTime(self, tSamples):  # :22-28
+        if tSamples is None or not tSamples or tSamples != tSamples or tSamples < 0.5:
+            raise DuspError("Cannot have fixed delay of length 0 samples")
+        self.delayTimeInSamples = _js_round(tSamples)
+        self.delayTimeInSeconds = tSamples / self.sampleRate
+
+    def setSeconds(self, duration):
+        self.setDelayTime(None if duration is None else duration * self.sampleRate)
+
+    def setFrequency(self, f):
+        self.setSeconds(1 / f)
+
+    def blob_props(self):
+        return {"delayTimeInSamples": int(self.delayTimeInSamples), "tBuffer": self.tBuffer}, {}
+
+
+class CombFilter(FixedDelay):
+    """src/components/CombFilter.js:3-26"""
+    KIND = "CombFilter"
+
+    def __init__(self, delayTime=None, feedbackGain=None):
+        super().__init__(delayTime)
+        self.addInlet("feedbackGain", {"mono": True, "type": "scalar"})
+        self.FEEDBACKGAIN = js_or(feedbackGain, 0)
+
+
+class AllPass(CombFilter):
+    """src/components/AllPass.js:3-51"""
+    KIND = "AllPass"
+
+    @staticmethod
+    def random(maxDelayTime=None, maxFeedbackGain=None):  # :20-25
+        r = config.host_random.random
+        return AllPass(js_or(maxDelayTime, 1) * r(), js_or(maxFeedbackGain, 1) * r())
+
+    @staticmethod
+    def manyRandom(n, maxDelay, maxFeedback):  # :27-38 (the `delay` local is computed and unused)
+        r = config.host_random.random
+        out = []
+        for _ in range(n):
+            delay = 2 / SR + r() * (maxDelay - 2 / SR)  # `this.sampleRate` is undefined on the class: NaN, unused
+            while delay == 0:
+                delay = r() * maxDelay
+            out.append(AllPass(r() * maxDelay, r() * maxFeedback))
+        return out
+
+
+# ----------------------------------------------------- CircleBuffer taps
+class CircleBuffer:
+    """src/CircleBuffer.js:3-35 -- device-resident ring; host object only carries its shape."""
+
+    def __init__(self, numberOfChannels=None, lengthInSeconds=None):
+        import math
+        self.numberOfChannels = js_or(numberOfChannels, 1)
+        self.lengthInSeconds = lengthInSeconds
+        self.sampleRate = config.sampleRate
+        self.lengthInSamples = math.ceil(self.lengthInSeconds * self.sampleRate)
+
+
+class CircleBufferNode(Unit):
+    """src/components/CircleBufferNode.js:7-31"""
+
+    def __init__(self, buffer=None, offset=None):
+        super().__init__()
+        self.t = 0
+        self._buffer = None
+        if buffer is not None:
+            self.buffer = buffer
+        self.addInlet("offset", {"measuredIn": "s"})
+        self.OFFSET = js_or(offset, 0)
+
+    def __setattr__(self, name, val):
+        if name == "buffer":  # set buffer(): grow OUT to the buffer's channel count (:19-27)
+            out = self.__dict__.get("_sugar", {}).get("OUT")
+            if out is not None and out.isOutlet:
+                while len(out.chunk) < val.numberOfChannels:
+                    out.chunk.append(0.0)
+            object.__setattr__(self, "_buffer", val)
+        else:
+            super().__setattr__(name, val)
+
+    @property
+    def buffer(self):
+        return self._buffer
+
+
+class CircleBufferReader(CircleBufferNode):
+    """src/components/CircleBufferReader.js:3-27"""
+    KIND = "CircleBufferReader"
+
+    def __init__(self, buffer=None, offset=None):
+        super().__init__(None, offset)
+        self.addOutlet("out")
+        self.buffer = buffer
+        self.postWipe = False
+
+    def blob_props(self):
+        return {"t": self.t, "postWipe": int(bool(self.postWipe))}, {}
+
+
+class CircleBufferWriter(CircleBufferNode):
+    """src/components/CircleBufferWriter.js:3-27"""
+    KIND = "CircleBufferWriter"
+
+    def __init__(self, buffer=None, offset=None):
+        super().__init__(buffer, offset)
+        self.addInlet("in")
+        self.preWipe = False
+
+    def blob_props(self):
+        return {"t": self.t, "preWipe": int(bool(self.preWipe))}, {}
+
+
+__all__ = [
+    "AHD", "Abs", "AllPass", "CircleBuffer", "CircleBufferNode", "CircleBufferReader", "CircleBufferWriter",
+    "Clip", "CombFilter", "ConcatChannels", "CrossFader", "DecibelToScaler", "Delay", "Divide", "Filter",
+    "FixedDelay", "FixedMultiply", "Gain", "HardClipAbove", "HardClipBelow", "MidiToFrequency", "MonoDelay",
+    "Multiply", "Noise", "MultiChannelOsc", "Osc", "Pan", "PickChannel", "PolarityInvert", "Pow", "Ramp",
+    "ReadBackDelay", "Repeater", "Rescale", "SecondsToSamples", "SemitoneToRatio", "Shape", "SignalCombiner",
+    "Subtract", "Sum", "Timer", "VectorMagnitude",
+]

@@ -1,0 +1,320 @@
+// capi.cc -- the C ABI of libdusp_b200.so (include/dusp_b200.h): programs,
+// device-resident sessions and the render call.  No CPU rendering path exists
+// in this library: without a CUDA device every session call fails.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/dusp_b200.h"
+#include "compile.h"
+#include "graph.h"
+#include "launch.h"
+
+using namespace dusp;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+#define CUDA_TRY(x)                                                                                   \
+  do {                                                                                                \
+    cudaError_t e_ = (x);                                                                             \
+    if (e_ != cudaSuccess) return fail(DUSP_ECUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+struct dusp_program {
+  Program prog;
+  std::string listing;
+};
+
+namespace {
+
+// waveTables.js:5-40 and shapeTables.js:3-38: 44101-entry float32 tables, built
+// with the host libm exactly as the reference builds them with Math.sin.
+const std::vector<float> &host_tables() {
+  static std::vector<float> t;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    const int N = DUSP_TABLE_LEN, SR = DUSP_SR;
+    t.assign((size_t)TAB_COUNT * N, 0.f);
+    float *sine = &t[(size_t)TAB_SIN * N], *saw = &t[(size_t)TAB_SAW * N], *sq = &t[(size_t)TAB_SQUARE * N];
+    float *tri = &t[(size_t)TAB_TRIANGLE * N], *bit8 = &t[(size_t)TAB_8BIT * N];
+    const double PHI = 2 * M_PI;
+    for (int i = 0; i < N; i++) sine[i] = (float)std::sin(PHI * i / N);
+    for (int i = 0; i < SR; i++) saw[i] = (float)(-1 + i * 2.0 / N);
+    const int q = SR / 4;
+    for (int i = 0; i < q; i++) {
+      tri[i] = (float)((double)i / SR * 4);
+      tri[i + q] = (float)(1 - (double)tri[i]);
+      tri[i + 2 * q] = (float)(-(double)tri[i]);
+      tri[i + 3 * q] = (float)(-1 + (double)tri[i]);
+    }
+    tri[SR] = 0;
+    for (int i = 0; i < N; i++) sq[i] = i < SR / 2 ? 1.f : -1.f;
+    for (int i = 0; i < N; i++) bit8[i] = (float)(std::floor((double)sine[i] * 128.0 + 0.5) / 128.0);
+    float *dec = &t[(size_t)TAB_DECAY * N], *att = &t[(size_t)TAB_ATTACK * N];
+    float *semi = &t[(size_t)TAB_SEMISINE * N], *dsq = &t[(size_t)TAB_DECAYSQ * N];
+    for (int i = 0; i < N; i++) {
+      const double x = (double)i / SR;
+      dec[i] = (float)(1 - x);
+      att[i] = (float)x;
+      semi[i] = (float)std::sin(M_PI * x);
+      dsq[i] = (float)((1 - x) * (1 - x));
+    }
+  });
+  return t;
+}
+
+struct Group {
+  Program prog;
+  int n_voices = 0, voice0 = 0;
+  long long nv_pad = 0;
+  std::vector<double> h_words;  // [n_words][nv_pad] initial values (defaults + overrides)
+  DuspInstr *d_code = nullptr;
+  double *d_words = nullptr;
+  float *d_rings = nullptr;
+  DuspRing *d_ringtab = nullptr;
+  float *d_stale = nullptr;
+  bool dirty = true;  // device words/rings need (re)initialisation
+};
+
+}  // namespace
+
+struct dusp_session {
+  int device = 0;
+  std::vector<Group> groups;
+  int n_voices = 0, out_nch = 0;
+  long long unit_count = 0;
+  long long clock = 0;
+  float *d_tables = nullptr;
+  float *d_staging = nullptr;
+  size_t staging_floats = 0;
+  long long launches = 0;
+  int last_grid = 0, last_block = 0, last_smem = 0;
+  int sub_block = 8;
+};
+
+extern "C" {
+
+int dusp_abi_version(void) { return DUSP_ABI_VERSION; }
+const char *dusp_last_error(void) { return g_err.c_str(); }
+
+int dusp_program_create(const char *blob, size_t len, dusp_program **out) {
+  if (!blob || !out) return fail(DUSP_EINVAL, "renderAudioBuffer expects an outlet");
+  try {
+    Graph g = parse_graph(blob, len);
+    auto p = std::make_unique<dusp_program>();
+    p->prog = compile(g);
+    p->listing = p->prog.listing();
+    *out = p.release();
+    return DUSP_OK;
+  } catch (const Unsupported &e) {
+    return fail(DUSP_EUNSUPPORTED, e.what());
+  } catch (const std::exception &e) {
+    return fail(DUSP_EINVAL, e.what());
+  }
+}
+void dusp_program_destroy(dusp_program *p) { delete p; }
+int dusp_program_num_channels(const dusp_program *p) { return p->prog.out_nch; }
+int dusp_program_num_units(const dusp_program *p) { return p->prog.n_units; }
+int dusp_program_num_instructions(const dusp_program *p) { return (int)p->prog.code.size(); }
+int dusp_program_num_slots(const dusp_program *p) { return p->prog.n_slots; }
+double dusp_program_bytes_per_voice_sample(const dusp_program *p, int out_mode) {
+  return p->prog.ring_bytes_per_sample + (out_mode == DUSP_OUT_VOICES ? 4.0 * p->prog.out_nch : 0.0);
+}
+int dusp_program_num_params(const dusp_program *p) { return (int)p->prog.words.size(); }
+const char *dusp_program_param_name(const dusp_program *p, int i) {
+  return i >= 0 && i < (int)p->prog.words.size() ? p->prog.words[i].name.c_str() : nullptr;
+}
+int dusp_program_param_index(const dusp_program *p, const char *name) {
+  for (size_t i = 0; i < p->prog.words.size(); i++) if (p->prog.words[i].name == name) return (int)i;
+  return -1;
+}
+double dusp_program_param_default(const dusp_program *p, int i) {
+  return i >= 0 && i < (int)p->prog.words.size() ? p->prog.words[i].dflt : NAN;
+}
+size_t dusp_program_disassemble(const dusp_program *p, char *buf, size_t cap) {
+  if (buf && cap) { size_t n = std::min(cap - 1, p->listing.size()); memcpy(buf, p->listing.data(), n); buf[n] = 0; }
+  return p->listing.size() + 1;
+}
+
+static void free_group(Group &g) {
+  cudaFree(g.d_code); cudaFree(g.d_words); cudaFree(g.d_rings); cudaFree(g.d_ringtab); cudaFree(g.d_stale);
+  g.d_code = nullptr; g.d_words = nullptr; g.d_rings = nullptr; g.d_ringtab = nullptr; g.d_stale = nullptr;
+}
+
+void dusp_session_destroy(dusp_session *s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  for (auto &g : s->groups) free_group(g);
+  cudaFree(s->d_tables); cudaFree(s->d_staging);
+  delete s;
+}
+
+int dusp_session_create(const dusp_program *const *programs, const int *voices, int n_programs, int device,
+                        dusp_session **out) {
+  if (!programs || !voices || n_programs < 1 || !out) return fail(DUSP_EINVAL, "dusp_session_create: bad arguments");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
+    return fail(DUSP_ECUDA, "no CUDA device: libdusp_b200 has no CPU rendering path");
+  if (device < 0 || device >= ndev) return fail(DUSP_EINVAL, "dusp_session_create: no such CUDA device");
+  CUDA_TRY(cudaSetDevice(device));
+  std::unique_ptr<dusp_session, void (*)(dusp_session *)> s(new dusp_session, dusp_session_destroy);
+  s->device = device;
+  const auto &tabs = host_tables();
+  CUDA_TRY(cudaMalloc(&s->d_tables, tabs.size() * sizeof(float)));
+  CUDA_TRY(cudaMemcpy(s->d_tables, tabs.data(), tabs.size() * sizeof(float), cudaMemcpyHostToDevice));
+  int voice0 = 0;
+  for (int i = 0; i < n_programs; i++) {
+    if (!programs[i] || voices[i] < 1) return fail(DUSP_EINVAL, "dusp_session_create: empty program group");
+    s->groups.emplace_back();
+    Group &g = s->groups.back();
+    g.prog = programs[i]->prog;
+    g.n_voices = voices[i];
+    g.voice0 = voice0;
+    g.nv_pad = ((long long)voices[i] + 31) / 32 * 32;
+    voice0 += voices[i];
+    s->out_nch = std::max(s->out_nch, g.prog.out_nch);
+    s->unit_count += (long long)g.prog.n_units * voices[i];
+    const size_t nw = g.prog.words.size();
+    g.h_words.resize(std::max<size_t>(nw, 1) * g.nv_pad);
+    for (size_t w = 0; w < nw; w++) {
+      const Param &p = g.prog.words[w];
+      const double v = p.f32 ? (double)(float)p.dflt : p.dflt;
+      for (long long k = 0; k < g.nv_pad; k++) g.h_words[w * g.nv_pad + k] = v;
+    }
+    CUDA_TRY(cudaMalloc(&g.d_code, std::max<size_t>(g.prog.code.size(), 1) * sizeof(DuspInstr)));
+    CUDA_TRY(cudaMemcpy(g.d_code, g.prog.code.data(), g.prog.code.size() * sizeof(DuspInstr), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMalloc(&g.d_words, g.h_words.size() * sizeof(double)));
+    const size_t ring_bytes = (size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad * sizeof(float);
+    if (cudaMalloc(&g.d_rings, ring_bytes) != cudaSuccess) {
+      cudaGetLastError();
+      char m[160];
+      snprintf(m, sizeof m, "delay lines need %.1f GB of device memory for %d voices", ring_bytes / 1e9, g.n_voices);
+      return fail(DUSP_ENOMEM, m);
+    }
+    CUDA_TRY(cudaMalloc(&g.d_ringtab, std::max<size_t>(g.prog.rings.size(), 1) * sizeof(DuspRing)));
+    CUDA_TRY(cudaMemcpy(g.d_ringtab, g.prog.rings.data(), g.prog.rings.size() * sizeof(DuspRing), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMalloc(&g.d_stale, (size_t)std::max(g.prog.n_stale, 1) * DUSP_CHUNK * g.nv_pad * sizeof(float)));
+  }
+  s->n_voices = voice0;
+  *out = s.release();
+  return DUSP_OK;
+}
+
+int dusp_session_num_voices(const dusp_session *s) { return s->n_voices; }
+int dusp_session_num_channels(const dusp_session *s) { return s->out_nch; }
+long long dusp_session_unit_count(const dusp_session *s) { return s->unit_count; }
+long long dusp_session_launch_count(const dusp_session *s) { return s->launches; }
+int dusp_session_launch_info(const dusp_session *s, int *grid, int *block, int *smem) {
+  if (grid) *grid = s->last_grid;
+  if (block) *block = s->last_block;
+  if (smem) *smem = s->last_smem;
+  return DUSP_OK;
+}
+
+int dusp_session_set_params(dusp_session *s, int gi, const int *ids, int n_ids, const double *values) {
+  if (!s || gi < 0 || gi >= (int)s->groups.size() || !ids || !values || n_ids < 0)
+    return fail(DUSP_EINVAL, "dusp_session_set_params: bad arguments");
+  Group &g = s->groups[gi];
+  const int nw = (int)g.prog.words.size();
+  for (int k = 0; k < n_ids; k++)
+    if (ids[k] < 0 || ids[k] >= nw) return fail(DUSP_EINVAL, "dusp_session_set_params: no such parameter");
+  for (int v = 0; v < g.n_voices; v++)
+    for (int k = 0; k < n_ids; k++) {
+      const Param &p = g.prog.words[ids[k]];
+      const double x = values[(size_t)v * n_ids + k];
+      g.h_words[(size_t)ids[k] * g.nv_pad + v] = p.f32 ? (double)(float)x : x;
+    }
+  if (!g.prog.tap_pairs.empty()) {  // per-voice CircleBuffer offsets must keep the reordering proof (compile.cc)
+    std::vector<double> wv(nw);
+    for (int v = 0; v < g.n_voices; v++) {
+      for (int w = 0; w < nw; w++) wv[w] = g.h_words[(size_t)w * g.nv_pad + v];
+      std::string msg = g.prog.check_taps(wv.data());
+      if (!msg.empty()) return fail(DUSP_EUNSUPPORTED, "voice " + std::to_string(v) + ": " + msg);
+    }
+  }
+  g.dirty = true;
+  s->clock = 0;
+  return DUSP_OK;
+}
+
+int dusp_session_reset(dusp_session *s) {
+  if (!s) return fail(DUSP_EINVAL, "dusp_session_reset: null session");
+  for (auto &g : s->groups) g.dirty = true;
+  s->clock = 0;
+  return DUSP_OK;
+}
+
+int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, float *out_host, float *out_device,
+                        void *cuda_stream) {
+  if (!s || n_samples < 0 || (out_mode != DUSP_OUT_VOICES && out_mode != DUSP_OUT_MIX) || (!out_host == !out_device))
+    return fail(DUSP_EINVAL, "dusp_session_render: bad arguments");
+  if (s->clock % DUSP_CHUNK) return fail(DUSP_EINVAL, "dusp_session_render: a previous render ended inside a chunk");
+  CUDA_TRY(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  const size_t out_floats = (out_mode == DUSP_OUT_VOICES ? (size_t)s->n_voices * s->out_nch : 2) * (size_t)n_samples;
+  float *d_out = out_device;
+  if (out_host) {
+    if (s->staging_floats < out_floats) {
+      cudaFree(s->d_staging); s->d_staging = nullptr; s->staging_floats = 0;
+      if (cudaMalloc(&s->d_staging, std::max<size_t>(out_floats, 1) * sizeof(float)) != cudaSuccess) {
+        cudaGetLastError();
+        return fail(DUSP_ENOMEM, "output does not fit on the device: render in shorter time blocks");
+      }
+      s->staging_floats = out_floats;
+    }
+    d_out = s->d_staging;
+  }
+  if (n_samples == 0) return DUSP_OK;
+  // channels a group does not produce (and the mix accumulator) start at zero
+  bool need_zero = out_mode == DUSP_OUT_MIX;
+  for (auto &g : s->groups) if (g.prog.out_nch != s->out_nch) need_zero = true;
+  if (need_zero) CUDA_TRY(cudaMemsetAsync(d_out, 0, out_floats * sizeof(float), st));
+  for (auto &g : s->groups) {
+    if (g.dirty) {
+      CUDA_TRY(cudaMemcpyAsync(g.d_words, g.h_words.data(), g.h_words.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+      CUDA_TRY(cudaMemsetAsync(g.d_rings, 0, (size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad * sizeof(float), st));
+      CUDA_TRY(cudaMemsetAsync(g.d_stale, 0, (size_t)std::max(g.prog.n_stale, 1) * DUSP_CHUNK * g.nv_pad * sizeof(float), st));
+      g.dirty = false;
+    }
+    DuspKernelParams kp;
+    memset(&kp, 0, sizeof kp);
+    kp.prog = g.d_code; kp.n_instr = (int)g.prog.code.size(); kp.n_slots = g.prog.n_slots;
+    kp.n_voices = g.n_voices; kp.voice0 = g.voice0; kp.nv_stride = g.nv_pad;
+    kp.words = g.d_words; kp.rings = g.d_rings; kp.ring_stride = std::max<long long>(g.prog.ring_floats, 4);
+    kp.ring_tab = g.d_ringtab; kp.stale = g.d_stale; kp.n_stale = g.prog.n_stale; kp.tables = s->d_tables;
+    kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = g.prog.out_nch; kp.out_mode = out_mode;
+    kp.out_len = n_samples; kp.clock0 = s->clock; kp.n_samples = n_samples;
+    const int n_warps = (g.n_voices + 31) / 32;
+    int wpc = n_warps >= 148 * 16 ? 4 : 1;
+    const size_t per_warp = (size_t)g.prog.n_slots * s->sub_block * 32 * sizeof(float);
+    while (wpc > 1 && per_warp * wpc > 200 * 1024) wpc >>= 1;
+    if (per_warp > 220 * 1024) return fail(DUSP_EUNSUPPORTED, "circuit needs more live signal slots than shared memory holds");
+    int grid = 0, smem = 0;
+    int e = dusp_launch_render(&kp, s->sub_block, wpc, st, &grid, &smem);
+    if (e != 0) return fail(DUSP_ECUDA, std::string("render launch: ") + cudaGetErrorString((cudaError_t)e));
+    s->launches++;
+    s->last_grid = grid; s->last_block = wpc * 32; s->last_smem = smem;
+  }
+  s->clock += (n_samples + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;
+  if (out_host) {
+    CUDA_TRY(cudaMemcpyAsync(out_host, d_out, out_floats * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+  }
+  return DUSP_OK;
+}
+
+double dusp_rand53(uint64_t seed, uint64_t k) {
+  uint64_t z = seed + (k + 1) * 0x9E3779B97F4A7C15ULL;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  z ^= z >> 31;
+  return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+}
+
+}  // extern "C"

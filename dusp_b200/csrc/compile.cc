@@ -1,0 +1,614 @@
+// compile.cc -- the Circuit scheduler's tick list -> flat op program.
+//
+// What the reference does per 256-sample chunk (Circuit.js:34-37): call every
+// unit's _tick in `circuit.units` order, each reading its inlets' SignalChunks
+// and writing its outlets'.  Here that list is flattened once:
+//   * every (outlet, channel) becomes a VALUE; a connected inlet is an alias of
+//     the producer's value (Inlet.js:53), an unconnected inlet is a per-voice
+//     constant word (Inlet.js:76-93);
+//   * multi-channel units are expanded to one instruction per channel with the
+//     reference's channel-count growth rules evaluated statically;
+//   * a value consumed by a unit that ticks BEFORE its producer (cyclic graphs,
+//     Unit.js:171-181 breaks the cycle there) is read one chunk stale through a
+//     256-sample per-voice buffer -- exactly what the aliased SignalChunk holds
+//     in the reference at that moment;
+//   * values get shared-memory slots by linear-scan liveness.
+// The device interprets the program sub-block by sub-block (B samples at a time)
+// instead of chunk by chunk; that reordering is exact for everything except
+// CircleBuffer taps that touch each other's samples inside one chunk, which are
+// rejected below (DUSP_EUNSUPPORTED) rather than approximated.
+#include "compile.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <set>
+#include <tuple>
+
+namespace dusp {
+
+namespace {
+
+const char *OP_NAMES[OP_COUNT] = {
+    "nop", "copy", "neg", "abs", "s2s", "semi", "db2s", "midi2f", "fixmul", "mul", "div", "pow", "add", "sub",
+    "gain", "clip", "hca", "hcb", "rescale", "xfade", "pan", "vecmag", "osc", "mcosc", "ramp", "shape", "ahd",
+    "timer", "noise", "filter", "fixdelay", "comb", "allpass", "delay", "monodelay", "readback", "cbwrite",
+    "cbread", "ldstale", "ststale", "out"};
+
+struct Opnd {
+  int kind = 0;  // 0 none (reads 0), 1 value, 2 const word
+  int id = -1;
+};
+
+struct IR {
+  int op = OP_NOP;
+  Opnd in[5];
+  int outv[2] = {-1, -1};
+  int p = -1;
+  int aux[3] = {0, 0, 0};
+  int unit = -1, chan = 0;
+  bool root = false;  // has effects beyond its output values
+  int pos = 0;        // index of the owning unit in the tick order
+};
+
+struct Val {
+  int unit, outlet, chan;
+  int def = -1;  // producing IR index
+};
+
+struct Builder {
+  const Graph &g;
+  Program prog;
+  std::vector<IR> ir;
+  std::vector<Val> vals;
+  std::map<std::tuple<int, int, int>, int> valmap;
+  std::vector<std::vector<int>> nch;  // steady-state channel count per [unit][outlet]
+  std::vector<int> pos_of_unit;
+
+  explicit Builder(const Graph &gr) : g(gr) {}
+
+  int val(int u, int o, int c) {
+    auto key = std::make_tuple(u, o, c);
+    auto it = valmap.find(key);
+    if (it != valmap.end()) return it->second;
+    vals.push_back({u, o, c, -1});
+    return valmap[key] = (int)vals.size() - 1;
+  }
+  int word(const std::string &name, double dflt, bool f32) {
+    prog.words.push_back({name, dflt, f32});
+    return (int)prog.words.size() - 1;
+  }
+  int ring(long long len) {
+    if (len < 1) throw Unsupported("delay line of length < 1 sample");
+    prog.rings.push_back({prog.ring_floats, len});
+    prog.ring_floats += (len + 3) & ~3LL;  // keep every ring 16-byte aligned
+    return (int)prog.rings.size() - 1;
+  }
+  static std::string uname(int u) { return "u" + std::to_string(u); }
+
+  int in_nch(const std::vector<std::vector<int>> &n, int u, int i) const {
+    const GPort &p = g.units[u].in[i];
+    if (p.connected) return n[p.src_unit][p.src_outlet];
+    return (int)p.consts.size();
+  }
+  // operand for channel `c` of inlet `i` (caller has already applied the unit's
+  // own modulo / zero-fill rule, so c < channel count or the result is "none")
+  Opnd in_ref(int u, int i, int c) {
+    const GPort &p = g.units[u].in[i];
+    Opnd o;
+    if (p.connected) {
+      if (p.src_unit == u) throw Unsupported("unit " + g.units[u].label + " feeds its own inlet (sample-level self feedback)");
+      if (c >= nch[p.src_unit][p.src_outlet]) return o;
+      o.kind = 1;
+      o.id = val(p.src_unit, p.src_outlet, c);
+    } else {
+      if (c >= (int)p.consts.size()) return o;
+      o.kind = 2;
+      o.id = word(uname(u) + "." + p.name + "[" + std::to_string(c) + "]", p.consts[c], true);
+    }
+    return o;
+  }
+  IR &emit(int op, int u, int c) {
+    ir.emplace_back();
+    IR &r = ir.back();
+    r.op = op; r.unit = u; r.chan = c; r.pos = pos_of_unit[u];
+    return r;
+  }
+  void def(IR &r, int k, int u, int o, int c) {
+    int v = val(u, o, c);
+    r.outv[k] = v;
+    vals[v].def = (int)(&r - &ir[0]);
+  }
+};
+
+int find_inlet(const GUnit &u, const char *name) {
+  for (size_t i = 0; i < u.in.size(); i++) if (u.in[i].name == name) return (int)i;
+  throw std::runtime_error("unit " + u.kind + " lacks inlet " + name);
+}
+
+int table_id(const std::string &s, bool shape) {
+  if (!shape) {
+    if (s == "sin" || s == "sine") return TAB_SIN;
+    if (s == "saw") return TAB_SAW;
+    if (s == "square") return TAB_SQUARE;
+    if (s == "triangle") return TAB_TRIANGLE;
+    if (s == "8bit") return TAB_8BIT;
+    throw std::runtime_error("waveform doesn't exist: " + s);  // Osc.js:60-61
+  }
+  if (s == "decay") return TAB_DECAY;
+  if (s == "attack") return TAB_ATTACK;
+  if (s == "semiSine") return TAB_SEMISINE;
+  if (s == "decaySquared") return TAB_DECAYSQ;
+  throw std::runtime_error("invalid shape function: " + s);
+}
+
+// How many channels of outlet 0 a unit's _tick writes / grows to, given the
+// channel counts it sees (the `out[c] = out[c] || new Float32Array` lines).
+int written_channels(const Graph &g, const std::vector<std::vector<int>> &n, int ui, const Builder &b) {
+  const GUnit &u = g.units[ui];
+  const std::string &k = u.kind;
+  auto in = [&](int i) { return b.in_nch(n, ui, i); };
+  if (k == "MultiChannelOsc") return in(0);
+  if (k == "Filter" || k == "Gain" || k == "PolarityInvert" || k == "Abs" || k == "Repeater" ||
+      k == "SecondsToSamples" || k == "SemitoneToRatio" || k == "DecibelToScaler" || k == "Clip" ||
+      k == "HardClipAbove" || k == "HardClipBelow" || k == "Rescale")
+    return in(0);
+  if (k == "Multiply" || k == "Divide" || k == "Pow" || k == "Sum" || k == "Subtract" || k == "CrossFader" ||
+      k == "Delay" || k == "ReadBackDelay")
+    return std::max(in(0), in(1));
+  if (k == "ConcatChannels") return in(0) + in(1);
+  if (k == "Pan") return 2;
+  if (k == "CircleBufferReader") return g.cbs.at((size_t)u.num("buffer", -1)).nch;
+  return 0;  // mono-outlet units and MidiToFrequency never grow their outlet
+}
+
+}  // namespace
+
+const char *op_name(int op) { return op >= 0 && op < OP_COUNT ? OP_NAMES[op] : "?"; }
+
+Program compile(const Graph &g) {
+  Builder b(g);
+  const int NU = (int)g.units.size();
+  b.pos_of_unit.assign(NU, -1);
+  for (size_t i = 0; i < g.order.size(); i++) {
+    if (b.pos_of_unit[g.order[i]] >= 0) throw std::runtime_error("graph blob: unit listed twice in ORDER");
+    b.pos_of_unit[g.order[i]] = (int)i;
+  }
+  for (int u = 0; u < NU; u++)
+    if (b.pos_of_unit[u] < 0) b.pos_of_unit[u] = 1 << 28;  // not ticked: never produces
+  if (b.pos_of_unit[g.root_unit] >= (1 << 28)) throw std::runtime_error("rendered unit is not in the circuit");
+  b.prog.n_units = (int)g.order.size();
+
+  // ---- channel counts: steady state, then check tick 0 already sees it ----
+  std::vector<std::vector<int>> init(NU);
+  for (int u = 0; u < NU; u++) for (auto &o : g.units[u].out) init[u].push_back(std::max(1, o.nch));
+  auto simulate = [&](std::vector<std::vector<int>> n, std::vector<std::vector<int>> *seen) {
+    for (int ui : g.order) {
+      const GUnit &u = g.units[ui];
+      if (seen) { (*seen)[ui].clear(); for (size_t i = 0; i < u.in.size(); i++) (*seen)[ui].push_back(b.in_nch(n, ui, (int)i)); }
+      if (!u.out.empty()) n[ui][0] = std::max(n[ui][0], written_channels(g, n, ui, b));
+      if (u.kind == "Delay" && u.in[0].connected && b.in_nch(n, ui, 0) < b.in_nch(n, ui, 1))
+        throw Unsupported("Delay with more DELAY channels than IN channels aliases channels into its producer (Delay.js:23)");
+    }
+    return n;
+  };
+  std::vector<std::vector<int>> seen0(NU), seenS(NU);
+  auto n1 = simulate(init, &seen0);
+  auto ns = n1;
+  for (int it = 0; it < 16; it++) { auto nn = simulate(ns, nullptr); if (nn == ns) break; ns = nn; }
+  simulate(ns, &seenS);
+  if (seen0 != seenS || n1[g.root_unit][g.root_outlet] != ns[g.root_unit][g.root_outlet])
+    throw Unsupported("channel counts keep growing after the first chunk (multi-channel signal through a feedback edge)");
+  b.nch = ns;
+  for (auto &v : b.nch) for (int c : v) if (c > 16) throw Unsupported("more than 16 channels on one outlet");
+
+  // ---- emit one instruction per unit-channel, in tick order ----
+  std::map<std::pair<int, int>, int> cb_ring;  // (buffer, channel) -> ring id
+  for (size_t bi = 0; bi < g.cbs.size(); bi++)
+    for (int c = 0; c < g.cbs[bi].nch; c++) cb_ring[{(int)bi, c}] = b.ring(g.cbs[bi].len);
+  struct Tap { int unit; bool writer; Opnd off; };
+  std::map<int, std::vector<Tap>> taps;  // ring -> taps (for the reordering check)
+
+  for (int ui : g.order) {
+    const GUnit &u = g.units[ui];
+    const std::string &k = u.kind;
+    const std::string un = Builder::uname(ui);
+    auto inn = [&](int i) { return b.in_nch(b.nch, ui, i); };
+    auto need_in = [&](size_t n) { if (u.in.size() < n || u.out.empty()) throw std::runtime_error("unit " + k + " has too few ports in graph blob"); };
+    auto unary = [&](int op) { need_in(1); for (int c = 0; c < inn(0); c++) { IR &r = b.emit(op, ui, c); r.in[0] = b.in_ref(ui, 0, c); b.def(r, 0, ui, 0, c); } };
+    auto binary_mod = [&](int op) {
+      need_in(2);
+      int n = std::max(inn(0), inn(1));
+      for (int c = 0; c < n; c++) { IR &r = b.emit(op, ui, c); r.in[0] = b.in_ref(ui, 0, c % inn(0)); r.in[1] = b.in_ref(ui, 1, c % inn(1)); b.def(r, 0, ui, 0, c); }
+    };
+    if (k == "Osc") {
+      need_in(1);
+      IR &r = b.emit(OP_OSC, ui, 0); r.in[0] = b.in_ref(ui, 0, 0);
+      r.p = b.word(un + ".phase", u.num("phase", 0), false);
+      r.aux[0] = table_id(u.str("waveform", "sin"), false);
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "MultiChannelOsc") {
+      need_in(1);
+      for (int c = 0; c < inn(0); c++) {
+        IR &r = b.emit(OP_MCOSC, ui, c); r.in[0] = b.in_ref(ui, 0, c);
+        r.p = b.word(un + ".phase[" + std::to_string(c) + "]", 0, false);
+        r.aux[0] = table_id(u.str("waveform", "sin"), false);
+        b.def(r, 0, ui, 0, c);
+      }
+    } else if (k == "Ramp") {
+      IR &r = b.emit(OP_RAMP, ui, 0);
+      r.p = b.word(un + ".t", u.num("t", 0), false);
+      b.word(un + ".playing", u.num("playing", 0), false);
+      b.word(un + ".duration", u.num("duration", DUSP_SR), false);
+      b.word(un + ".y0", u.num("y0", 1), false);
+      b.word(un + ".y1", u.num("y1", 0), false);
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "Shape") {
+      need_in(3);
+      IR &r = b.emit(OP_SHAPE, ui, 0);
+      for (int i = 0; i < 3; i++) r.in[i] = b.in_ref(ui, i, 0);
+      r.p = b.word(un + ".t", u.num("t", 0), false);
+      b.word(un + ".playing", u.num("playing", 0), false);
+      b.word(un + ".leftEdge", u.num("leftEdge", 0), false);
+      b.word(un + ".rightEdge", u.num("rightEdge", 0), false);
+      r.aux[0] = table_id(u.str("shape", "decay"), true);
+      bool le_shape = u.str("leftEdge", "") == "shape";
+      bool re_shape = u.S.count("rightEdge") ? u.str("rightEdge", "") == "shape" : !u.has("rightEdge");
+      if ((u.S.count("leftEdge") && !le_shape) || (u.S.count("rightEdge") && !re_shape))
+        throw Unsupported("Shape edge must be \"shape\" or a number");
+      r.aux[1] = (le_shape ? 1 : 0) | (re_shape ? 2 : 0);
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "AHD") {
+      need_in(3);
+      IR &r = b.emit(OP_AHD, ui, 0);
+      for (int i = 0; i < 3; i++) r.in[i] = b.in_ref(ui, i, 0);
+      r.p = b.word(un + ".t", u.num("t", 0), false);
+      b.word(un + ".state", u.num("state", 0), false);
+      b.word(un + ".playing", u.num("playing", 0), false);
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "Timer") {
+      IR &r = b.emit(OP_TIMER, ui, 0);
+      r.p = b.word(un + ".t", u.num("t", 0), false);
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "Noise") {
+      need_in(1);
+      if (b.nch[ui][0] != 1) throw Unsupported("multi-channel Noise shares one phase across channels chunk by chunk (Noise.js:17-27)");
+      IR &r = b.emit(OP_NOISE, ui, 0); r.in[0] = b.in_ref(ui, 0, 0);
+      r.p = b.word(un + ".phase", u.num("phase", 0), false);
+      b.word(un + ".y", u.num("y", 0), false);
+      b.word(un + ".draw", u.num("draw", 1), false);
+      b.word(un + ".seed_lo", u.num("seed_lo", 0), false);
+      b.word(un + ".seed_hi", u.num("seed_hi", 0), false);
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "Filter") {
+      need_in(2);
+      std::string kind = u.str("kind", "LP");
+      if (kind != "LP" && kind != "HP") throw Unsupported("Filter kind " + kind + " (the reference's BP/BR coefficient functions are never passed a bandwidth)");
+      for (int c = 0; c < inn(0); c++) {
+        IR &r = b.emit(OP_FILTER, ui, c); r.in[0] = b.in_ref(ui, 0, c); r.in[1] = b.in_ref(ui, 1, 0);
+        std::string s = "[" + std::to_string(c) + "]";
+        const char *names[11] = {"a0", "a1", "a2", "b1", "b2", "lastF", "lastFdefined", "x1", "x2", "y1", "y2"};
+        for (int w = 0; w < 11; w++) {
+          int id = b.word(un + "." + names[w] + s, w < 5 ? NAN : 0.0, false);
+          if (w == 0) r.p = id;
+        }
+        r.aux[0] = kind == "HP";
+        b.def(r, 0, ui, 0, c);
+      }
+    } else if (k == "Multiply") binary_mod(OP_MUL);
+    else if (k == "Divide") binary_mod(OP_DIV);
+    else if (k == "Pow") binary_mod(OP_POW);
+    else if (k == "Sum") binary_mod(OP_ADD);
+    else if (k == "Subtract" || k == "CrossFader") {
+      need_in(k == "Subtract" ? 2 : 3);
+      int n = std::max(inn(0), inn(1));
+      for (int c = 0; c < n; c++) {
+        IR &r = b.emit(k == "Subtract" ? OP_SUB : OP_XFADE, ui, c);
+        r.in[0] = b.in_ref(ui, 0, c); r.in[1] = b.in_ref(ui, 1, c);  // zero-fill, not modulo (Subtract.js:23-24)
+        if (k == "CrossFader") r.in[2] = b.in_ref(ui, 2, 0);
+        b.def(r, 0, ui, 0, c);
+      }
+    } else if (k == "Gain") {
+      need_in(2);
+      for (int c = 0; c < inn(0); c++) { IR &r = b.emit(OP_GAIN, ui, c); r.in[0] = b.in_ref(ui, 0, c); r.in[1] = b.in_ref(ui, 1, 0); b.def(r, 0, ui, 0, c); }
+    } else if (k == "PolarityInvert") unary(OP_NEG);
+    else if (k == "Abs") unary(OP_ABS);
+    else if (k == "Repeater") unary(OP_COPY);
+    else if (k == "SecondsToSamples") unary(OP_S2S);
+    else if (k == "SemitoneToRatio") unary(OP_SEMI);
+    else if (k == "DecibelToScaler") unary(OP_DB2S);
+    else if (k == "MidiToFrequency") {
+      need_in(1);
+      for (int c = 0; c < std::min(inn(0), b.nch[ui][0]); c++) { IR &r = b.emit(OP_MIDI2F, ui, c); r.in[0] = b.in_ref(ui, 0, c); b.def(r, 0, ui, 0, c); }
+    } else if (k == "Clip" || k == "HardClipAbove" || k == "HardClipBelow") {
+      need_in(2);
+      int op = k == "Clip" ? OP_CLIP : k == "HardClipAbove" ? OP_HCA : OP_HCB;
+      for (int c = 0; c < inn(0); c++) { IR &r = b.emit(op, ui, c); r.in[0] = b.in_ref(ui, 0, c); r.in[1] = b.in_ref(ui, 1, c % inn(1)); b.def(r, 0, ui, 0, c); }
+    } else if (k == "Rescale") {
+      need_in(5);
+      for (int c = 0; c < inn(0); c++) {
+        IR &r = b.emit(OP_RESCALE, ui, c); r.in[0] = b.in_ref(ui, 0, c);
+        for (int i = 1; i < 5; i++) r.in[i] = b.in_ref(ui, i, c % inn(i));
+        b.def(r, 0, ui, 0, c);
+      }
+    } else if (k == "Pan") {
+      need_in(2);
+      IR &r = b.emit(OP_PAN, ui, 0); r.in[0] = b.in_ref(ui, 0, 0); r.in[1] = b.in_ref(ui, 1, 0);
+      r.p = b.word(un + ".compensationDB", u.num("compensationDB", 1.5), false);
+      b.def(r, 0, ui, 0, 0); b.def(r, 1, ui, 0, 1);
+    } else if (k == "FixedMultiply") {
+      need_in(1);
+      IR &r = b.emit(OP_FIXMUL, ui, 0); r.in[0] = b.in_ref(ui, 0, 0);
+      r.p = b.word(un + ".sf", u.num("sf", NAN), false);
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "ConcatChannels") {
+      need_in(2);
+      int na = inn(0), n = na + inn(1);
+      for (int c = 0; c < n; c++) { IR &r = b.emit(OP_COPY, ui, c); r.in[0] = c < na ? b.in_ref(ui, 0, c) : b.in_ref(ui, 1, c - na); b.def(r, 0, ui, 0, c); }
+    } else if (k == "PickChannel") {
+      need_in(2);
+      const GPort &cp = u.in[1];
+      if (cp.connected) throw Unsupported("PickChannel with a signal-rate channel index");
+      double idx = std::fmod((double)(float)cp.consts[0], (double)inn(0));  // PickChannel.js:19
+      IR &r = b.emit(OP_COPY, ui, 0);
+      if (idx == std::floor(idx) && idx >= 0 && idx < inn(0)) r.in[0] = b.in_ref(ui, 0, (int)idx);
+      else throw Unsupported("PickChannel index selects no channel (the reference throws a TypeError)");
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "VectorMagnitude") {
+      need_in(1);
+      if (inn(0) > 5) throw Unsupported("VectorMagnitude over more than 5 channels");
+      IR &r = b.emit(OP_VECMAG, ui, 0);
+      for (int c = 0; c < inn(0); c++) r.in[c] = b.in_ref(ui, 0, c);
+      r.aux[0] = inn(0);
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "Delay" || k == "ReadBackDelay") {
+      need_in(2);
+      int n = std::max(inn(0), inn(1));
+      for (int c = 0; c < n; c++) {
+        IR &r = b.emit(k == "Delay" ? OP_DELAY : OP_READBACK, ui, c);
+        // Delay.js:23 aliases in[c % length] while the array grows: every added channel is channel c % (original count)
+        r.in[0] = b.in_ref(ui, 0, c % inn(0)); r.in[1] = b.in_ref(ui, 1, c % inn(1));
+        if (k == "Delay") r.aux[0] = b.ring((long long)u.num("maxDelay", DUSP_SR * 5));
+        else {
+          r.aux[0] = b.ring((long long)u.num("bufferLength", DUSP_SR));
+          r.p = b.word(un + ".tBuffer[" + std::to_string(c) + "]", u.num("tBuffer", 0), false);
+        }
+        b.prog.ring_bytes_per_sample += k == "Delay" ? 24 : 8;
+        b.def(r, 0, ui, 0, c);
+      }
+    } else if (k == "MonoDelay") {
+      need_in(2);
+      IR &r = b.emit(OP_MONODELAY, ui, 0); r.in[0] = b.in_ref(ui, 0, 0); r.in[1] = b.in_ref(ui, 1, 0);
+      r.aux[0] = b.ring(DUSP_SR * 5);
+      b.prog.ring_bytes_per_sample += 24;
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "FixedDelay" || k == "CombFilter" || k == "AllPass") {
+      need_in(k == "FixedDelay" ? 1 : 2);
+      IR &r = b.emit(k == "FixedDelay" ? OP_FIXDELAY : k == "CombFilter" ? OP_COMB : OP_ALLPASS, ui, 0);
+      r.in[0] = b.in_ref(ui, 0, 0);
+      if (k != "FixedDelay") r.in[1] = b.in_ref(ui, 1, 0);
+      r.aux[0] = b.ring((long long)u.num("delayTimeInSamples", 0));
+      r.p = b.word(un + ".tBuffer", u.num("tBuffer", 0), false);
+      b.prog.ring_bytes_per_sample += 8;
+      b.def(r, 0, ui, 0, 0);
+    } else if (k == "CircleBufferWriter" || k == "CircleBufferReader") {
+      bool writer = k == "CircleBufferWriter";
+      int bi = (int)u.num("buffer", -1);
+      if (bi < 0 || bi >= (int)g.cbs.size()) throw std::runtime_error("CircleBuffer node without a buffer");
+      int io = find_inlet(u, "offset");
+      int ii = writer ? find_inlet(u, "in") : -1;
+      for (int c = 0; c < g.cbs[bi].nch; c++) {
+        IR &r = b.emit(writer ? OP_CBWRITE : OP_CBREAD, ui, c);
+        r.in[0] = b.in_ref(ui, io, c % inn(io));
+        if (writer) r.in[1] = b.in_ref(ui, ii, c);  // `if(this.in[c])`: absent channel -> no mix
+        r.p = b.word(un + ".t[" + std::to_string(c) + "]", u.num("t", 0), false);
+        r.aux[0] = cb_ring[{bi, c}];
+        r.aux[1] = (int)u.num(writer ? "preWipe" : "postWipe", 0);
+        r.root = writer || r.aux[1];
+        if (!writer) b.def(r, 0, ui, 0, c);
+        taps[r.aux[0]].push_back({ui, writer || r.aux[1] != 0, r.in[0]});
+        b.prog.ring_bytes_per_sample += writer ? (r.aux[1] ? 4 : 8) : (r.aux[1] ? 8 : 4);
+      }
+    } else {
+      throw Unsupported("unit kind " + k + " is outside the accelerated render path");
+    }
+  }
+
+  // ---- CircleBuffer taps: sub-block interleaving must not reorder accesses --
+  // Two different units touching one ring see the same samples in the same
+  // order as the reference (unit after unit per 256-chunk) iff their constant
+  // time shifts are equal or at least one chunk apart on the ring.
+  for (auto &kv : taps) {
+    auto &tv = kv.second;
+    long long len = b.prog.rings[kv.first].length;
+    if (len < 2 * DUSP_CHUNK && tv.size() > 1) throw Unsupported("shared CircleBuffer shorter than two chunks");
+    for (size_t i = 0; i < tv.size(); i++)
+      for (size_t j = i + 1; j < tv.size(); j++) {
+        if (tv[i].unit == tv[j].unit) continue;
+        if (!tv[i].writer && !tv[j].writer) continue;
+        if (tv[i].off.kind != 2 || tv[j].off.kind != 2)
+          throw Unsupported("CircleBuffer taps with signal-rate OFFSET sharing a buffer");
+        auto sign = [&](const Tap &t) { return g.units[t.unit].kind == "CircleBufferWriter" ? 1 : -1; };
+        b.prog.tap_pairs.push_back({tv[i].off.id, tv[j].off.id, sign(tv[i]), sign(tv[j]), len});
+      }
+  }
+  {
+    std::vector<double> dv;
+    for (auto &w : b.prog.words) dv.push_back(w.dflt);
+    std::string msg = b.prog.check_taps(dv.data());
+    if (!msg.empty()) throw Unsupported(msg);
+  }
+
+  // ---- rendered outlet -> OUT instructions ----
+  const int out_nch = b.nch[g.root_unit][g.root_outlet];
+  b.prog.out_nch = out_nch;
+  std::vector<IR> outs;
+  for (int c = 0; c < out_nch; c++) {
+    IR r; r.op = OP_OUT; r.unit = g.root_unit; r.chan = c; r.aux[0] = c; r.root = true;
+    auto it = b.valmap.find(std::make_tuple(g.root_unit, g.root_outlet, c));
+    if (it != b.valmap.end() && b.vals[it->second].def >= 0) { r.in[0].kind = 1; r.in[0].id = it->second; }
+    r.pos = 1 << 29;
+    outs.push_back(r);
+  }
+
+  // ---- dead-code elimination (keep OUT, CircleBuffer side effects, and their inputs) ----
+  std::vector<IR> &ir = b.ir;
+  for (auto &o : outs) ir.push_back(o);
+  // re-index defs (emit() may have reallocated; defs were recorded by index so they are valid)
+  std::vector<char> live(ir.size(), 0);
+  std::vector<int> stack;
+  for (size_t i = 0; i < ir.size(); i++) if (ir[i].root) { live[i] = 1; stack.push_back((int)i); }
+  while (!stack.empty()) {
+    int i = stack.back(); stack.pop_back();
+    for (auto &o : ir[i].in)
+      if (o.kind == 1) { int d = b.vals[o.id].def; if (d >= 0 && !live[d]) { live[d] = 1; stack.push_back(d); } }
+  }
+  // values without a producer read as silence (a channel the unit never writes stays zero-filled)
+  for (auto &r : ir) for (auto &o : r.in) if (o.kind == 1 && b.vals[o.id].def < 0) o = Opnd();
+
+  // ---- order + stale edges ----
+  struct Item { IR r; int orig; };
+  std::vector<IR> seq;
+  std::vector<int> newidx(ir.size(), -1);
+  for (size_t i = 0; i < ir.size(); i++) if (live[i]) { newidx[i] = (int)seq.size(); seq.push_back(ir[i]); }
+  for (auto &v : b.vals) v.def = v.def >= 0 ? newidx[v.def] : -1;
+  // place each OUT right after its producer (keeps the value's live range short)
+  {
+    std::vector<IR> body, tail;
+    for (auto &r : seq) (r.op == OP_OUT ? tail : body).push_back(r);
+    std::vector<IR> res;
+    std::map<int, std::vector<IR>> after;  // producer body index -> outs
+    std::vector<IR> front;
+    // recompute def index within `body`
+    std::map<int, int> defidx;
+    for (size_t i = 0; i < body.size(); i++) for (int k = 0; k < 2; k++) if (body[i].outv[k] >= 0) defidx[body[i].outv[k]] = (int)i;
+    for (auto &o : tail) {
+      if (o.in[0].kind == 1) after[defidx.at(o.in[0].id)].push_back(o);
+      else front.push_back(o);
+    }
+    for (auto &o : front) res.push_back(o);
+    for (size_t i = 0; i < body.size(); i++) { res.push_back(body[i]); for (auto &o : after[(int)i]) res.push_back(o); }
+    seq.swap(res);
+  }
+  auto recompute_defs = [&]() {
+    for (auto &v : b.vals) v.def = -1;
+    for (size_t i = 0; i < seq.size(); i++) for (int k = 0; k < 2; k++) if (seq[i].outv[k] >= 0) b.vals[seq[i].outv[k]].def = (int)i;
+  };
+  recompute_defs();
+  // stale reads: consumer scheduled at or before its producer
+  {
+    std::map<int, int> stale_id;   // value -> stale buffer
+    std::map<int, int> stale_tmp;  // value -> temp value holding the loaded previous chunk
+    std::vector<IR> res;
+    for (size_t i = 0; i < seq.size(); i++) {
+      IR r = seq[i];
+      for (auto &o : r.in) {
+        if (o.kind != 1) continue;
+        int d = b.vals[o.id].def;
+        if (d >= 0 && d >= (int)i) {
+          int v = o.id;
+          if (!stale_id.count(v)) {
+            stale_id[v] = b.prog.n_stale++;
+            b.vals.push_back({b.vals[v].unit, b.vals[v].outlet, b.vals[v].chan, -1});
+            stale_tmp[v] = (int)b.vals.size() - 1;
+            IR ld; ld.op = OP_LDSTALE; ld.unit = b.vals[v].unit; ld.chan = b.vals[v].chan;
+            ld.aux[0] = stale_id[v]; ld.outv[0] = stale_tmp[v];
+            res.push_back(ld);
+          }
+          o.id = stale_tmp[v];
+        }
+      }
+      res.push_back(r);
+      for (int k = 0; k < 2; k++)
+        if (r.outv[k] >= 0 && stale_id.count(r.outv[k])) {
+          IR st; st.op = OP_STSTALE; st.unit = r.unit; st.chan = r.chan; st.aux[0] = stale_id[r.outv[k]];
+          st.in[0].kind = 1; st.in[0].id = r.outv[k];
+          res.push_back(st);
+        }
+    }
+    // a producer may precede the discovery of its stale consumers only if the consumer comes later,
+    // which by definition is not stale; so every STSTALE was emitted above.
+    seq.swap(res);
+  }
+  recompute_defs();
+
+  // ---- slot allocation: linear scan, in-place reuse allowed (ops load all inputs before storing) ----
+  std::vector<int> last_use(b.vals.size(), -1);
+  for (size_t i = 0; i < seq.size(); i++) for (auto &o : seq[i].in) if (o.kind == 1) last_use[o.id] = (int)i;
+  std::vector<int> slot_of(b.vals.size(), -1);
+  std::vector<int> free_slots;
+  int n_slots = 0;
+  for (size_t i = 0; i < seq.size(); i++) {
+    IR &r = seq[i];
+    std::set<int> freed;
+    for (auto &o : r.in)
+      if (o.kind == 1 && last_use[o.id] == (int)i && !freed.count(o.id)) { freed.insert(o.id); free_slots.push_back(slot_of[o.id]); }
+    for (int k = 0; k < 2; k++) {
+      int v = r.outv[k];
+      if (v < 0) continue;
+      if (last_use[v] < 0) { r.outv[k] = -1; continue; }  // never read: op writes nowhere
+      int s;
+      if (!free_slots.empty()) { std::sort(free_slots.begin(), free_slots.end(), std::greater<int>()); s = free_slots.back(); free_slots.pop_back(); }
+      else s = n_slots++;
+      slot_of[v] = s;
+    }
+  }
+  b.prog.n_slots = std::max(n_slots, 1);
+
+  // ---- encode ----
+  for (auto &r : seq) {
+    DuspInstr di;
+    std::memset(&di, 0, sizeof di);
+    di.op = r.op;
+    for (int k = 0; k < 5; k++)
+      di.in[k] = r.in[k].kind == 1 ? slot_of[r.in[k].id] : r.in[k].kind == 2 ? ref_const(r.in[k].id) : REF_NONE;
+    for (int k = 0; k < 2; k++) di.out[k] = r.outv[k] >= 0 ? slot_of[r.outv[k]] : REF_NONE;
+    di.p = r.p;
+    for (int k = 0; k < 3; k++) di.aux[k] = r.aux[k];
+    di.unit = r.unit; di.chan = r.chan;
+    b.prog.code.push_back(di);
+  }
+  return b.prog;
+}
+
+std::string Program::check_taps(const double *wv) const {
+  for (auto &t : tap_pairs) {
+    double sa = t.sign_a * (double)DUSP_SR * (double)(float)wv[t.word_a];
+    double sb = t.sign_b * (double)DUSP_SR * (double)(float)wv[t.word_b];
+    double d = std::fabs(sa - sb);
+    if (!(d == d) || std::isinf(d)) return "CircleBuffer tap OFFSET is not finite";
+    d = std::fmod(d, (double)t.ring_len);
+    d = std::min(d, (double)t.ring_len - d);
+    if (d != 0 && d < DUSP_CHUNK)
+      return "CircleBuffer taps closer than one 256-sample chunk (intra-chunk ordering differs from the reference)";
+  }
+  return "";
+}
+
+std::string Program::listing() const {
+  std::string s;
+  char buf[256];
+  snprintf(buf, sizeof buf, "; %zu instr, %d slots, %d stale, %zu rings (%lld floats/voice), %zu words, %d ch out\n",
+           code.size(), n_slots, n_stale, rings.size(), ring_floats, words.size(), out_nch);
+  s += buf;
+  for (size_t i = 0; i < code.size(); i++) {
+    const DuspInstr &d = code[i];
+    snprintf(buf, sizeof buf, "%3zu %-9s u%d.%d ", i, op_name(d.op), d.unit, d.chan);
+    s += buf;
+    for (int k = 0; k < 5; k++) {
+      if (d.in[k] == REF_NONE) continue;
+      if (d.in[k] >= 0) snprintf(buf, sizeof buf, "s%d ", d.in[k]);
+      else snprintf(buf, sizeof buf, "$%s ", words[REF_CONST_BASE - d.in[k]].name.c_str());
+      s += buf;
+    }
+    s += "-> ";
+    for (int k = 0; k < 2; k++) if (d.out[k] >= 0) { snprintf(buf, sizeof buf, "s%d ", d.out[k]); s += buf; }
+    snprintf(buf, sizeof buf, "[p=%d aux=%d,%d,%d]\n", d.p, d.aux[0], d.aux[1], d.aux[2]);
+    s += buf;
+  }
+  return s;
+}
+
+}  // namespace dusp

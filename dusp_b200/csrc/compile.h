@@ -1,0 +1,50 @@
+// compile.h -- circuit description -> flat op program (host side).
+#pragma once
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "graph.h"
+#include "vm.h"
+
+namespace dusp {
+
+struct Unsupported : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+
+struct Param {
+  std::string name;  // "u<unit>.<inlet>[<ch>]" (inlet constant, f32-valued) or "u<unit>.<prop>"
+  double dflt;
+  bool f32;          // value is what a Float32Array chunk holds: rounded to binary32 on upload
+};
+
+// Two CircleBuffer taps of different units on one ring: their per-voice OFFSET
+// constants must keep them either on the same sample or >= one chunk apart
+// (see compile.cc); re-checked whenever a voice overrides an offset.
+struct TapPair {
+  int word_a, word_b;    // OFFSET constant words
+  int sign_a, sign_b;    // +1 writer (t + SR*off), -1 reader (t - SR*off)
+  long long ring_len;
+};
+
+struct Program {
+  std::vector<DuspInstr> code;
+  std::vector<Param> words;     // per-voice words: parameters and unit state, in instruction order
+  std::vector<DuspRing> rings;  // per-voice delay lines / CircleBuffer channels
+  long long ring_floats = 0;
+  int n_slots = 0;
+  int n_stale = 0;
+  int out_nch = 0;
+  int n_units = 0;              // units the reference ticks per chunk (metric: unit-samples)
+  double ring_bytes_per_sample = 0;  // SURVEY 8d accounting
+  std::vector<TapPair> tap_pairs;
+  // returns "" if the offsets (one value per word, as the voice will see them) are admissible
+  std::string check_taps(const double *word_values) const;
+  std::string listing() const;
+};
+
+Program compile(const Graph &g);
+const char *op_name(int op);
+
+}  // namespace dusp

@@ -1,0 +1,130 @@
+/*
+ * dusp_b200.h -- C ABI of the B200-native Dusp circuit renderer (libdusp_b200.so).
+ *
+ * This is the drop-in boundary for ONE path of the reference: rendering a
+ * circuit (or a batch of independent circuits / voices) to channel data,
+ *     /root/reference/src/renderChannelData.js:5-49
+ *       -> Circuit.tickUntil / tick            src/Circuit.js:19-47
+ *       -> every unit's _tick                  src/components/ *.js  
+ * The reference has no FFI for this path (it is plain JavaScript); the entry
+ * points below are what a Node.js N-API addon binds (bindings/node/, see
+ * INTEGRATION.md) and what the Python host mirror (dusp_b200/capi.py, ctypes)
+ * calls.  Plain pointers and sizes only; no C++/torch types cross this line.
+ *
+ * Error convention: every int-returning call returns 0 on success and a
+ * negative DUSP_E* code on failure; dusp_last_error() then returns the message
+ * (thread-local).  The reference throws *strings* (renderChannelData.js:13,17);
+ * host shims re-throw dusp_last_error() verbatim.
+ *
+ * There is no CPU fallback: without a CUDA device every session call fails
+ * with DUSP_ECUDA.
+ */
+#ifndef DUSP_B200_H
+#define DUSP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DUSP_ABI_VERSION 1
+#define DUSP_SAMPLE_RATE 44100 /* src/config.js:7 */
+#define DUSP_CHUNK 256         /* src/config.js:6 */
+
+enum {
+  DUSP_OK = 0,
+  DUSP_EINVAL = -1,      /* bad argument / malformed graph blob */
+  DUSP_EUNSUPPORTED = -2,/* graph uses a unit or configuration outside the accelerated path */
+  DUSP_ECUDA = -3,       /* CUDA runtime error, or no device */
+  DUSP_ENOMEM = -4
+};
+
+/* Where dusp_session_render puts the audio. */
+enum {
+  DUSP_OUT_VOICES = 0, /* per-voice channel data, layout [voice][channel][n_samples] f32
+                          == what renderChannelData returns for each circuit (renderChannelData.js:26-45) */
+  DUSP_OUT_MIX = 1     /* stereo mixdown only, layout [2][n_samples] f32:
+                          mix[c] = sum over voices of out_v[c % nch_v]  (Sum's modulo broadcast, Sum.js:33-44) */
+};
+
+typedef struct dusp_program dusp_program; /* a circuit compiled to a flat op program */
+typedef struct dusp_session dusp_session; /* n voices of one or more programs, resident on one GPU */
+
+int dusp_abi_version(void);
+const char *dusp_last_error(void);
+
+/* ---- compile -------------------------------------------------------------
+ * Replaces: `new Circuit(outlet.unit)` + the per-chunk unit dispatch loop
+ * (renderChannelData.js:20, Circuit.js:34-37, Unit.js:111-119).  `graph_blob`
+ * is the "DUSPGRAPH 1" text description of the circuit: units in tick order
+ * (circuit.units), their inlets' constants / connections, unit state, shared
+ * CircleBuffers and the rendered outlet (format: dusp_b200/graphblob.py).
+ * The tick list becomes a flat op program; SignalChunk buffers become slots. */
+int dusp_program_create(const char *graph_blob, size_t len, dusp_program **out);
+void dusp_program_destroy(dusp_program *p);
+
+int dusp_program_num_channels(const dusp_program *p); /* channels of the rendered outlet */
+int dusp_program_num_units(const dusp_program *p);    /* units the reference would tick per chunk */
+int dusp_program_num_instructions(const dusp_program *p);
+int dusp_program_num_slots(const dusp_program *p);
+/* bytes of compulsory HBM traffic per voice-sample in DUSP_OUT_VOICES mode
+ * (SURVEY.md 8d accounting: 4*C_out + ring traffic) and the ring part alone */
+double dusp_program_bytes_per_voice_sample(const dusp_program *p, int out_mode);
+
+/* Per-voice parameters: every inlet constant ("u<unit>.<inlet>[<ch>]") and every
+ * numeric unit property / initial state ("u<unit>.<prop>") can be overridden per
+ * voice, so one program renders many differently-tuned voices in one launch. */
+int dusp_program_num_params(const dusp_program *p);
+const char *dusp_program_param_name(const dusp_program *p, int index);
+int dusp_program_param_index(const dusp_program *p, const char *name); /* -1 if absent */
+double dusp_program_param_default(const dusp_program *p, int index);
+/* human-readable listing of the op program (debugging); returns bytes needed */
+size_t dusp_program_disassemble(const dusp_program *p, char *buf, size_t cap);
+
+/* ---- sessions ------------------------------------------------------------
+ * Replaces: the circuit objects' run-time state (SignalChunks, unit fields,
+ * CircleBuffer / delay rings) -- here device-resident arrays for n voices.
+ * `programs[i]` is instantiated `voices[i]` times; voices are numbered in that
+ * order.  `device` is the CUDA ordinal.  */
+int dusp_session_create(const dusp_program *const *programs, const int *voices, int n_programs,
+                        int device, dusp_session **out);
+void dusp_session_destroy(dusp_session *s);
+int dusp_session_num_voices(const dusp_session *s);
+int dusp_session_num_channels(const dusp_session *s); /* max over programs */
+long long dusp_session_unit_count(const dusp_session *s); /* sum over voices of units per voice */
+
+/* values[v * n_ids + k] overrides parameter param_ids[k] of voice v of program
+ * `program_index` (v counts within that program).  Call before the first render
+ * or after dusp_session_reset. */
+int dusp_session_set_params(dusp_session *s, int program_index, const int *param_ids, int n_ids,
+                            const double *values);
+int dusp_session_reset(dusp_session *s); /* back to clock 0 / initial unit state */
+
+/* Replaces: the `for t0 ... await circuit.tickUntil(t1)` loop and the copy-out
+ * (renderChannelData.js:29-45), for all voices at once.  Renders the next
+ * `n_samples` samples (the session clock advances by whole chunks, like
+ * Circuit.tick).  Exactly one of `out_host` / `out_device` is non-NULL:
+ *   out_host   -- caller-owned host buffer; the call returns when it is filled
+ *   out_device -- caller-owned device buffer on the session's GPU; the kernels
+ *                 are enqueued on `cuda_stream` (a cudaStream_t, may be NULL)
+ *                 and the call returns without synchronising
+ * Buffer size: DUSP_OUT_VOICES n_voices*n_channels*n_samples floats,
+ *              DUSP_OUT_MIX 2*n_samples floats.  NaN and -0 samples are stored
+ *              as +0 (`x || 0`, renderChannelData.js:44). */
+int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, float *out_host,
+                        float *out_device, void *cuda_stream);
+
+/* number of kernel launches issued by this session so far (bench accounting) */
+long long dusp_session_launch_count(const dusp_session *s);
+/* last launch geometry, for reporting: grid, block, dynamic smem bytes */
+int dusp_session_launch_info(const dusp_session *s, int *grid, int *block, int *smem_bytes);
+
+/* The injected PRNG (replaces Math.random in Noise.js:10,23): draw k of stream `seed`. */
+double dusp_rand53(uint64_t seed, uint64_t k);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DUSP_B200_H */

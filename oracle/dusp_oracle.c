@@ -1,0 +1,980 @@
+/*
+ * dusp_oracle.c -- CPU restatement of the Dusp reference render path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  This file is the parity oracle (and the timed CPU
+ * baseline "port").  Nothing in the product (dusp_b200/, libdusp_b200.so) may
+ * include, link or call it.  Only tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs load liboracle.
+ *
+ * PARITY STATUS: "parity unpinned by the reference's own tests" -- the
+ * reference (plain JavaScript, /root/reference) ships no golden vectors, no
+ * assertions and cannot run here (no node / JS engine in the image).  The
+ * oracle is pinned instead against closed-form known answers derived from the
+ * reference source (tests/test_oracle_kat.py).
+ *
+ * Every function cites the reference file:line it restates.  Rounding rules
+ * (SURVEY 8c): all arithmetic in double, a (float) cast exactly where the JS
+ * stores into a Float32Array, reads of f32 buffers widen to double, JS `%` is
+ * fmod, compile with -ffp-contract=off.  The scheduler (Circuit.add /
+ * computeProcessIndex / computeOrders) is restated verbatim so that cyclic
+ * graphs get the same one-chunk-stale edges as the reference.
+ *
+ * Input is the neutral "DUSPGRAPH 1" text blob written by
+ * dusp_b200/graphblob.py (format documented in DESIGN.md section 3).
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define SR 44100            /* src/config.js:7 */
+#define CHUNK 256           /* src/config.js:6 */
+#define MAXCH 16
+#define MAXPORTS 24
+
+/* ---------------------------------------------------------------- chunks */
+/* src/SignalChunk.js:1-11 -- channelData: Float32Array(chunkSize)[nChannels] */
+typedef struct Chunk {
+  int nch;
+  float *ch[MAXCH];
+} Chunk;
+
+static Chunk *chunk_new(int nch) {
+  Chunk *c = (Chunk *)calloc(1, sizeof(Chunk));
+  c->nch = nch;
+  for (int i = 0; i < nch; i++) c->ch[i] = (float *)calloc(CHUNK, sizeof(float));
+  return c;
+}
+static float *chunk_ensure(Chunk *c, int i) { /* `out[c] = out[c] || new Float32Array(chunkSize)` */
+  if (i >= MAXCH) { fprintf(stderr, "oracle: too many channels\n"); abort(); }
+  while (c->nch <= i) { c->ch[c->nch] = (float *)calloc(CHUNK, sizeof(float)); c->nch++; }
+  return c->ch[i];
+}
+static void chunk_free(Chunk *c) {
+  if (!c) return;
+  for (int i = 0; i < c->nch; i++) {
+    /* Delay.js:23 may alias one Float32Array under two indices */
+    int dup = 0;
+    for (int j = 0; j < i; j++) if (c->ch[j] == c->ch[i]) dup = 1;
+    if (!dup) free(c->ch[i]);
+  }
+  free(c);
+}
+
+/* src/CircleBuffer.js:3-35 */
+typedef struct CircleBuffer {
+  int nch;
+  long len;
+  float **ch;
+} CircleBuffer;
+
+/* JS typed-array element access with a double index: non-integer, negative or
+ * out-of-range reads give `undefined` (NaN once it meets arithmetic or a
+ * Float32Array store); such writes are silently dropped. */
+static int ta_valid(double idx, long len) { return idx == floor(idx) && idx >= 0 && idx < (double)len; }
+static double ta_read(const float *a, long len, double idx) { return ta_valid(idx, len) ? (double)a[(long)idx] : NAN; }
+static void ta_write(float *a, long len, double idx, double v) { if (ta_valid(idx, len)) a[(long)idx] = (float)v; }
+
+static double cb_index(const CircleBuffer *b, double t) { /* CircleBuffer.js:17-20 */
+  t = floor(fmod(t, (double)b->len));
+  while (t < 0) t += (double)b->len;
+  return t;
+}
+static double cb_read(const CircleBuffer *b, int c, double t) { return ta_read(b->ch[c], b->len, cb_index(b, t)); }
+static void cb_write(CircleBuffer *b, int c, double t, double y) { ta_write(b->ch[c], b->len, cb_index(b, t), y); }
+static void cb_mix(CircleBuffer *b, int c, double t, double y) { /* CircleBuffer.js:29-34 `+=` */
+  double i = cb_index(b, t);
+  if (ta_valid(i, b->len)) b->ch[c][(long)i] = (float)((double)b->ch[c][(long)i] + y);
+}
+
+/* ---------------------------------------------------------------- graph */
+enum Kind {
+  K_OSC, K_MCOSC, K_RAMP, K_SHAPE, K_AHD, K_TIMER, K_NOISE, K_FILTER,
+  K_MULTIPLY, K_SUM, K_SUBTRACT, K_DIVIDE, K_GAIN, K_POLARITYINVERT, K_ABS, K_CLIP,
+  K_HARDCLIPABOVE, K_HARDCLIPBELOW, K_POW, K_RESCALE, K_CROSSFADER, K_PAN, K_REPEATER,
+  K_FIXEDMULTIPLY, K_SEMITONETORATIO, K_MIDITOFREQUENCY, K_DECIBELTOSCALER, K_SECONDSTOSAMPLES,
+  K_CONCATCHANNELS, K_PICKCHANNEL, K_VECTORMAGNITUDE,
+  K_DELAY, K_MONODELAY, K_READBACKDELAY, K_FIXEDDELAY, K_COMBFILTER, K_ALLPASS,
+  K_CBWRITER, K_CBREADER, K_NKINDS
+};
+static const char *KIND_NAMES[K_NKINDS] = {
+  "Osc", "MultiChannelOsc", "Ramp", "Shape", "AHD", "Timer", "Noise", "Filter",
+  "Multiply", "Sum", "Subtract", "Divide", "Gain", "PolarityInvert", "Abs", "Clip",
+  "HardClipAbove", "HardClipBelow", "Pow", "Rescale", "CrossFader", "Pan", "Repeater",
+  "FixedMultiply", "SemitoneToRatio", "MidiToFrequency", "DecibelToScaler", "SecondsToSamples",
+  "ConcatChannels", "PickChannel", "VectorMagnitude",
+  "Delay", "MonoDelay", "ReadBackDelay", "FixedDelay", "CombFilter", "AllPass",
+  "CircleBufferWriter", "CircleBufferReader"};
+
+struct Unit;
+typedef struct Port {
+  char name[32];
+  int mono;          /* Piglet.js:13-17 exposeAsMono */
+  int nodata;        /* Unit.js:88-98 chain ports */
+  int connected;
+  int src_unit, src_outlet; /* inlets only */
+  Chunk *chunk;      /* owned by outlets and unconnected inlets; aliased by connected inlets (Inlet.js:53) */
+  int owns;
+  int nconn, conn_unit[64]; /* outlets: connections in push order (Outlet.js / Inlet.js:52) */
+} Port;
+
+typedef struct Unit {
+  int kind;
+  char label[48];
+  int nin, nout;
+  Port in[MAXPORTS], out[MAXPORTS];
+  int process_index; /* -1 = undefined (Unit.js:171-209) */
+  int in_circuit;
+  /* generic numeric / string properties */
+  int nprops;
+  char pname[24][24];
+  double pval[24];
+  int nsprops;
+  char sname[4][24];
+  char sval[4][32];
+  /* run-time state */
+  double phase, t, y, y0, y1, duration, left_edge, right_edge, sf, comp_db;
+  int playing, state, finished, right_edge_is_shape, left_edge_is_shape;
+  uint64_t seed, draw;
+  const float *table;        /* Osc wave table / Shape table */
+  double mc_phase[MAXCH]; int mc_phase_set[MAXCH];
+  /* Filter.js:17-20,27-51 */
+  int fkind; int lastf_defined; double lastf, a0, a1, a2, b1, b2;
+  double x1[MAXCH], x2[MAXCH], fy1[MAXCH], fy2[MAXCH]; int sdef[MAXCH][4];
+  /* delays */
+  long maxdelay; float *bufs[MAXCH]; long buflen; double tbuffer;
+  CircleBuffer *cb; int prewipe, postwipe;
+} Unit;
+
+typedef struct Oracle {
+  int nunits;
+  Unit *units;
+  int ncb;
+  CircleBuffer *cbs;
+  int norder, *order;
+  int has_order;
+  int root_unit, root_outlet;
+  double clock;
+  char err[256];
+} Oracle;
+
+/* ------------------------------------------------------------ wave tables */
+/* src/components/Osc/waveTables.js:5-40 -- 44101-entry float32 tables. */
+static float *T_SIN, *T_SAW, *T_TRI, *T_SQUARE, *T_8BIT;
+/* src/components/Shape/shapeTables.js:3-38 */
+static float *S_DECAY, *S_ATTACK, *S_SEMISINE, *S_DECAYSQ;
+static int tables_ready = 0;
+
+static void build_tables(void) {
+  if (tables_ready) return;
+  const int N = SR + 1;
+  const double PHI = 2 * M_PI;
+  T_SIN = (float *)calloc(N, 4); T_SAW = (float *)calloc(N, 4); T_TRI = (float *)calloc(N, 4);
+  T_SQUARE = (float *)calloc(N, 4); T_8BIT = (float *)calloc(N, 4);
+  for (int t = 0; t < N; t++) T_SIN[t] = (float)sin(PHI * t / N);          /* waveTables.js:6-8 */
+  for (int t = 0; t < SR; t++) T_SAW[t] = (float)(-1 + t * 2.0 / N);       /* :10-12 (last entry stays 0) */
+  { int q = SR / 4;                                                        /* :14-22 */
+    for (int t = 0; t < q; t++) {
+      T_TRI[t] = (float)((double)t / SR * 4);
+      T_TRI[t + q] = (float)(1 - (double)T_TRI[t]);
+      T_TRI[t + q * 2] = (float)(-(double)T_TRI[t]);
+      T_TRI[t + q * 3] = (float)(-1 + (double)T_TRI[t]);
+    }
+    T_TRI[SR] = 0; }
+  for (int t = 0; t < N; t++) T_SQUARE[t] = t < SR / 2 ? 1.f : -1.f;        /* :24-26 */
+  for (int t = 0; t < N; t++) {                                            /* :28-31 Math.round = floor(x+0.5) */
+    double s = (double)T_SIN[t] * 128.0;
+    T_8BIT[t] = (float)(floor(s + 0.5) / 128.0);
+  }
+  S_DECAY = (float *)calloc(N, 4); S_ATTACK = (float *)calloc(N, 4);
+  S_SEMISINE = (float *)calloc(N, 4); S_DECAYSQ = (float *)calloc(N, 4);
+  for (int x = 0; x < N; x++) {                                            /* shapeTables.js:3-9,20-37 */
+    double u = (double)x / SR;
+    S_DECAY[x] = (float)(1 - u);
+    S_ATTACK[x] = (float)u;
+    S_SEMISINE[x] = (float)sin(M_PI * u);
+    S_DECAYSQ[x] = (float)((1 - u) * (1 - u));
+  }
+  tables_ready = 1;
+}
+
+const float *oracle_wave_table(const char *name) {
+  build_tables();
+  if (!strcmp(name, "sin") || !strcmp(name, "sine")) return T_SIN;
+  if (!strcmp(name, "saw")) return T_SAW;
+  if (!strcmp(name, "square")) return T_SQUARE;
+  if (!strcmp(name, "triangle")) return T_TRI;
+  if (!strcmp(name, "8bit")) return T_8BIT;
+  return NULL;
+}
+const float *oracle_shape_table(const char *name) {
+  build_tables();
+  if (!strcmp(name, "decay")) return S_DECAY;
+  if (!strcmp(name, "attack")) return S_ATTACK;
+  if (!strcmp(name, "semiSine")) return S_SEMISINE;
+  if (!strcmp(name, "decaySquared")) return S_DECAYSQ;
+  return NULL;
+}
+
+/* Injected PRNG replacing Math.random (Noise.js:10,23): counter-based
+ * splitmix64 keyed by (unit seed, draw index) -> 53-bit uniform in [0,1). */
+double oracle_rand(uint64_t seed, uint64_t k) {
+  uint64_t z = seed + (k + 1) * 0x9E3779B97F4A7C15ULL;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  z ^= z >> 31;
+  return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+}
+
+/* ----------------------------------------------------------- blob parser */
+static double *prop(Unit *u, const char *name) {
+  for (int i = 0; i < u->nprops; i++) if (!strcmp(u->pname[i], name)) return &u->pval[i];
+  return NULL;
+}
+static double propd(Unit *u, const char *name, double dflt) { double *p = prop(u, name); return p ? *p : dflt; }
+static const char *sprop(Unit *u, const char *name, const char *dflt) {
+  for (int i = 0; i < u->nsprops; i++) if (!strcmp(u->sname[i], name)) return u->sval[i];
+  return dflt;
+}
+static Port *find_in(Unit *u, const char *name) {
+  for (int i = 0; i < u->nin; i++) if (!strcmp(u->in[i].name, name)) return &u->in[i];
+  return NULL;
+}
+static Port *find_out(Unit *u, const char *name) {
+  for (int i = 0; i < u->nout; i++) if (!strcmp(u->out[i].name, name)) return &u->out[i];
+  return NULL;
+}
+
+static int kind_from_name(const char *s) {
+  for (int i = 0; i < K_NKINDS; i++) if (!strcmp(KIND_NAMES[i], s)) return i;
+  return -1;
+}
+
+void oracle_free(Oracle *o);
+
+static int fail(Oracle *o, const char *msg) { snprintf(o->err, sizeof o->err, "%s", msg); return -1; }
+
+static int init_unit_state(Oracle *o, Unit *u) {
+  u->phase = propd(u, "phase", 0);
+  u->t = propd(u, "t", 0);
+  u->playing = (int)propd(u, "playing", 0);
+  switch (u->kind) {
+  case K_OSC: case K_MCOSC:
+    u->table = oracle_wave_table(sprop(u, "waveform", "sin"));
+    if (!u->table) return fail(o, "waveform doesn't exist"); /* Osc.js:60-61 */
+    break;
+  case K_RAMP: /* Ramp.js:3-14 */
+    u->duration = propd(u, "duration", SR); u->y0 = propd(u, "y0", 1); u->y1 = propd(u, "y1", 0);
+    break;
+  case K_SHAPE: { /* Shape/index.js:7-24 */
+    u->table = oracle_shape_table(sprop(u, "shape", "decay"));
+    if (!u->table) return fail(o, "invalid shape function");
+    const char *le = sprop(u, "leftEdge", NULL), *re = sprop(u, "rightEdge", NULL);
+    u->left_edge_is_shape = le && !strcmp(le, "shape");
+    u->right_edge_is_shape = re ? !strcmp(re, "shape") : (prop(u, "rightEdge") == NULL);
+    u->left_edge = propd(u, "leftEdge", 0);
+    u->right_edge = propd(u, "rightEdge", 0);
+    u->finished = (int)propd(u, "finished", 0);
+    break; }
+  case K_AHD: u->state = (int)propd(u, "state", 0); break; /* AHD.js:19-21 */
+  case K_NOISE: /* Noise.js:3-11 */
+    u->seed = (uint64_t)propd(u, "seed_lo", 0) | ((uint64_t)propd(u, "seed_hi", 0) << 32);
+    u->draw = (uint64_t)propd(u, "draw", 1);
+    u->y = propd(u, "y", 0);
+    break;
+  case K_FILTER: { /* Filter.js:56-64 */
+    const char *k = sprop(u, "kind", "LP");
+    if (!strcmp(k, "LP")) u->fkind = 0; else if (!strcmp(k, "HP")) u->fkind = 1;
+    else return fail(o, "invalid filter type (only LP/HP are callable in the reference)");
+    u->a0 = u->a1 = u->a2 = u->b1 = u->b2 = NAN; /* calculateCoefficients(undefined) */
+    u->lastf_defined = 0;
+    break; }
+  case K_PAN: u->comp_db = propd(u, "compensationDB", 1.5); break; /* Pan.js:12 */
+  case K_FIXEDMULTIPLY: u->sf = propd(u, "sf", NAN); break;
+  case K_DELAY: u->maxdelay = (long)propd(u, "maxDelay", SR * 5); break;            /* Delay.js:13-14 */
+  case K_MONODELAY: u->maxdelay = SR * 5; u->bufs[0] = (float *)calloc(u->maxdelay, 4); break; /* MonoDelay.js:9-10 */
+  case K_READBACKDELAY: u->buflen = (long)propd(u, "bufferLength", SR); u->tbuffer = propd(u, "tBuffer", 0); break;
+  case K_FIXEDDELAY: case K_COMBFILTER: case K_ALLPASS: /* FixedDelay.js:22-28 */
+    u->buflen = (long)propd(u, "delayTimeInSamples", 0);
+    if (u->buflen < 1) return fail(o, "Cannot have fixed delay of length 0 samples");
+    u->bufs[0] = (float *)calloc(u->buflen, 4);
+    u->tbuffer = propd(u, "tBuffer", 0);
+    break;
+  case K_CBWRITER: case K_CBREADER: { /* CircleBufferNode.js:7-31 */
+    int bi = (int)propd(u, "buffer", -1);
+    if (bi < 0 || bi >= o->ncb) return fail(o, "CircleBuffer node without buffer");
+    u->cb = &o->cbs[bi];
+    u->prewipe = (int)propd(u, "preWipe", 0);
+    u->postwipe = (int)propd(u, "postWipe", 0);
+    if (u->kind == K_CBREADER) /* set buffer(): grow out to buffer.numberOfChannels */
+      for (int c = 0; c < u->cb->nch; c++) chunk_ensure(u->out[0].chunk, c);
+    break; }
+  default: break;
+  }
+  return 0;
+}
+
+Oracle *oracle_load(const char *blob, char *err, int errlen) {
+  build_tables();
+  Oracle *o = (Oracle *)calloc(1, sizeof(Oracle));
+  int cap = 16;
+  o->units = (Unit *)calloc(cap, sizeof(Unit));
+  o->cbs = (CircleBuffer *)calloc(64, sizeof(CircleBuffer));
+  o->root_unit = -1;
+  const char *p = blob;
+  Unit *u = NULL;
+  int bad = 0;
+  char line[8192];
+  while (*p && !bad) {
+    const char *e = strchr(p, '\n');
+    size_t n = e ? (size_t)(e - p) : strlen(p);
+    if (n >= sizeof line) { bad = 1; break; }
+    memcpy(line, p, n); line[n] = 0;
+    p = e ? e + 1 : p + n;
+    char *save = NULL;
+    char *tok = strtok_r(line, " \t\r", &save);
+    if (!tok || tok[0] == '#') continue;
+    if (!strcmp(tok, "DUSPGRAPH")) continue;
+    if (!strcmp(tok, "END")) break;
+    if (!strcmp(tok, "CB")) {
+      CircleBuffer *b = &o->cbs[o->ncb++];
+      b->nch = atoi(strtok_r(NULL, " ", &save));
+      b->len = atol(strtok_r(NULL, " ", &save));
+      b->ch = (float **)calloc(b->nch, sizeof(float *));
+      for (int c = 0; c < b->nch; c++) b->ch[c] = (float *)calloc(b->len, 4);
+    } else if (!strcmp(tok, "U")) {
+      if (o->nunits == cap) { cap *= 2; o->units = (Unit *)realloc(o->units, cap * sizeof(Unit)); memset(o->units + o->nunits, 0, (cap - o->nunits) * sizeof(Unit)); }
+      u = &o->units[o->nunits++];
+      char *k = strtok_r(NULL, " ", &save), *l = strtok_r(NULL, " ", &save);
+      u->kind = k ? kind_from_name(k) : -1;
+      if (u->kind < 0) { snprintf(o->err, sizeof o->err, "unknown unit kind %s", k ? k : "?"); bad = 1; break; }
+      snprintf(u->label, sizeof u->label, "%s", l ? l : "");
+      u->process_index = -1;
+    } else if (!u) { bad = 1;
+    } else if (!strcmp(tok, "P")) {
+      char *nm = strtok_r(NULL, " ", &save), *v = strtok_r(NULL, " ", &save);
+      snprintf(u->pname[u->nprops], 24, "%s", nm); u->pval[u->nprops++] = strtod(v, NULL);
+    } else if (!strcmp(tok, "S")) {
+      char *nm = strtok_r(NULL, " ", &save), *v = strtok_r(NULL, " ", &save);
+      snprintf(u->sname[u->nsprops], 24, "%s", nm); snprintf(u->sval[u->nsprops++], 32, "%s", v);
+    } else if (!strcmp(tok, "I")) {
+      Port *pt = &u->in[u->nin++];
+      snprintf(pt->name, 32, "%s", strtok_r(NULL, " ", &save));
+      pt->mono = atoi(strtok_r(NULL, " ", &save));
+      char *mode = strtok_r(NULL, " ", &save);
+      if (mode[0] == 'C') { /* Inlet.setConstant, Inlet.js:76-93: chunk channels pre-filled */
+        int nc = atoi(strtok_r(NULL, " ", &save));
+        pt->chunk = chunk_new(nc); pt->owns = 1;
+        for (int c = 0; c < nc; c++) {
+          float v = (float)strtod(strtok_r(NULL, " ", &save), NULL);
+          for (int t = 0; t < CHUNK; t++) pt->chunk->ch[c][t] = v;
+        }
+      } else {
+        pt->connected = 1; pt->nodata = (mode[0] == 'N');
+        pt->src_unit = atoi(strtok_r(NULL, " ", &save));
+        pt->src_outlet = atoi(strtok_r(NULL, " ", &save));
+      }
+    } else if (!strcmp(tok, "O")) {
+      Port *pt = &u->out[u->nout++];
+      snprintf(pt->name, 32, "%s", strtok_r(NULL, " ", &save));
+      pt->mono = atoi(strtok_r(NULL, " ", &save));
+      pt->chunk = chunk_new(atoi(strtok_r(NULL, " ", &save))); pt->owns = 1;
+      char *cv; /* outlet.connections in connect order (Inlet.js:52) */
+      while ((cv = strtok_r(NULL, " ", &save)) && pt->nconn < 64) pt->conn_unit[pt->nconn++] = atoi(cv);
+    } else if (!strcmp(tok, "ORDER")) {
+      o->order = (int *)calloc(o->nunits + 1, sizeof(int));
+      char *v;
+      while ((v = strtok_r(NULL, " ", &save))) o->order[o->norder++] = atoi(v);
+      o->has_order = 1;
+    } else if (!strcmp(tok, "ROOT")) {
+      o->root_unit = atoi(strtok_r(NULL, " ", &save));
+      o->root_outlet = atoi(strtok_r(NULL, " ", &save));
+    } else { snprintf(o->err, sizeof o->err, "bad blob line tag %s", tok); bad = 1; }
+  }
+  /* resolve connections: Inlet.connect (Inlet.js:40-56) aliases the outlet's chunk */
+  for (int i = 0; i < o->nunits && !bad; i++) {
+    Unit *w = &o->units[i];
+    for (int j = 0; j < w->nin; j++) {
+      Port *pt = &w->in[j];
+      if (!pt->connected) continue;
+      if (pt->src_unit < 0 || pt->src_unit >= o->nunits || pt->src_outlet >= o->units[pt->src_unit].nout) { bad = 1; break; }
+      Port *src = &o->units[pt->src_unit].out[pt->src_outlet];
+      pt->chunk = src->chunk; pt->owns = 0;
+    }
+  }
+  for (int i = 0; i < o->nunits && !bad; i++) if (init_unit_state(o, &o->units[i])) bad = 1;
+  if (!bad && (o->root_unit < 0 || o->root_unit >= o->nunits)) { fail(o, "renderAudioBuffer expects an outlet"); bad = 1; }
+  if (bad) {
+    if (err) snprintf(err, errlen, "%s", o->err[0] ? o->err : "malformed graph blob");
+    oracle_free(o);
+    return NULL;
+  }
+  return o;
+}
+
+void oracle_free(Oracle *o) {
+  if (!o) return;
+  for (int i = 0; i < o->nunits; i++) {
+    Unit *u = &o->units[i];
+    for (int j = 0; j < u->nin; j++) if (u->in[j].owns) chunk_free(u->in[j].chunk);
+    for (int j = 0; j < u->nout; j++) if (u->out[j].owns) chunk_free(u->out[j].chunk);
+    for (int c = 0; c < MAXCH; c++) free(u->bufs[c]);
+  }
+  for (int i = 0; i < o->ncb; i++) { for (int c = 0; c < o->cbs[i].nch; c++) free(o->cbs[i].ch[c]); free(o->cbs[i].ch); }
+  free(o->cbs); free(o->units); free(o->order); free(o);
+}
+
+/* ------------------------------------------------------------- scheduler */
+/* Unit.js:121-132 inputUnits: connected inlets in declaration order, dedup. */
+static int input_units(Oracle *o, int ui, int *list) {
+  Unit *u = &o->units[ui]; int n = 0;
+  for (int j = 0; j < u->nin; j++) {
+    if (!u->in[j].connected) continue;
+    int s = u->in[j].src_unit, dup = 0;
+    for (int k = 0; k < n; k++) if (list[k] == s) dup = 1;
+    if (!dup) list[n++] = s;
+  }
+  return n;
+}
+/* Unit.js:133-143 outputUnits: per outlet, per connection, dedup. */
+static int output_units(Oracle *o, int ui, int *list) {
+  Unit *u = &o->units[ui]; int n = 0;
+  for (int j = 0; j < u->nout; j++)
+    for (int k = 0; k < u->out[j].nconn; k++) {
+      int s = u->out[j].conn_unit[k], dup = 0;
+      for (int m = 0; m < n; m++) if (list[m] == s) dup = 1;
+      if (!dup) list[n++] = s;
+    }
+  return n;
+}
+static int in_hist(const int *h, int nh, int x) { for (int i = 0; i < nh; i++) if (h[i] == x) return 1; return 0; }
+
+/* Unit.js:171-209 computeProcessIndex(history) */
+static int compute_process_index(Oracle *o, int ui, const int *hist, int nh) {
+  int *h = (int *)malloc((nh + 1) * sizeof(int));
+  memcpy(h, hist, nh * sizeof(int)); h[nh] = ui;
+  int *tmp = (int *)malloc(sizeof(int) * (o->nunits + 1));
+  int n = input_units(o, ui, tmp), max = -1;
+  for (int i = 0; i < n; i++) {
+    if (in_hist(h, nh + 1, tmp[i])) continue;
+    if (o->units[tmp[i]].process_index < 0) compute_process_index(o, tmp[i], h, nh + 1);
+    if (o->units[tmp[i]].process_index > max) max = o->units[tmp[i]].process_index;
+  }
+  o->units[ui].process_index = max + 1;
+  n = output_units(o, ui, tmp);
+  for (int i = 0; i < n; i++) {
+    if (in_hist(h, nh + 1, tmp[i])) continue;
+    int pi = o->units[tmp[i]].process_index;
+    if (pi < 0 || pi <= o->units[ui].process_index) compute_process_index(o, tmp[i], h, nh + 1);
+  }
+  free(tmp); free(h);
+  return o->units[ui].process_index;
+}
+/* Circuit.js:125-131 computeOrders: `units.sort((a,b) => a.processIndex - b.processIndex)`.
+ * Restated as V8's Array.prototype.sort (TimSort, third_party/v8/builtins/array-sort.tq;
+ * Node >= 11) for arrays below the 64-element min-run threshold: one CountAndMakeRun
+ * followed by a binary insertion sort.  The comparator returns NaN while a unit's
+ * processIndex is still undefined; `order < 0` and `order >= 0` are then both false,
+ * which this code reproduces.  With every key defined any stable sort agrees, so
+ * larger circuits take the same path. */
+static double cmp_pi(Oracle *o, int a, int b) {
+  int pa = o->units[a].process_index, pb = o->units[b].process_index;
+  if (pa < 0 || pb < 0) return NAN;
+  return (double)(pa - pb);
+}
+static void compute_orders(Oracle *o) {
+  int n = o->norder, *w = o->order;
+  if (n < 2) return;
+  /* CountAndMakeRun(0, n) */
+  int run = 2;
+  double order = cmp_pi(o, w[1], w[0]);
+  int desc = order < 0;
+  int prev = w[1];
+  for (int idx = 2; idx < n; idx++) {
+    order = cmp_pi(o, w[idx], prev);
+    if (desc) { if (order >= 0) break; } else { if (order < 0) break; }
+    prev = w[idx]; run++;
+  }
+  if (desc) for (int i = 0, j = run - 1; i < j; i++, j--) { int t = w[i]; w[i] = w[j]; w[j] = t; }
+  /* BinaryInsertionSort(0, run, n) */
+  for (int start = run; start < n; start++) {
+    int left = 0, right = start, pivot = w[start];
+    while (left < right) {
+      int mid = left + ((right - left) >> 1);
+      if (cmp_pi(o, pivot, w[mid]) < 0) right = mid; else left = mid + 1;
+    }
+    for (int p = start; p > left; p--) w[p] = w[p - 1];
+    w[left] = pivot;
+  }
+}
+/* Circuit.js:67-107 add(unit) */
+static void circuit_add(Oracle *o, int ui) {
+  if (o->units[ui].in_circuit) return;
+  o->order[o->norder++] = ui;
+  o->units[ui].in_circuit = 1;
+  int *tmp = (int *)malloc(sizeof(int) * (o->nunits + 1));
+  int n = input_units(o, ui, tmp);
+  for (int i = 0; i < n; i++) circuit_add(o, tmp[i]);
+  n = output_units(o, ui, tmp);
+  for (int i = 0; i < n; i++) circuit_add(o, tmp[i]);
+  free(tmp);
+  compute_process_index(o, ui, NULL, 0);
+  compute_orders(o);
+}
+/* `new Circuit(outlet.unit)` (renderChannelData.js:20).  Returns #units ticked. */
+int oracle_schedule(Oracle *o, int *order_out) {
+  free(o->order);
+  o->order = (int *)calloc(o->nunits + 1, sizeof(int)); o->norder = 0;
+  for (int i = 0; i < o->nunits; i++) { o->units[i].in_circuit = 0; o->units[i].process_index = -1; }
+  circuit_add(o, o->root_unit);
+  o->has_order = 1;
+  if (order_out) memcpy(order_out, o->order, o->norder * sizeof(int));
+  return o->norder;
+}
+
+/* ----------------------------------------------------------------- ticks */
+#define INCH(u, i) ((u)->in[i].chunk)
+#define OUTCH(u, i) ((u)->out[i].chunk)
+static const float ZERO_CHUNK[CHUNK];
+static double js_or0(double x) { return (x != x || x == 0) ? 0.0 : x; } /* `x || 0` */
+
+/* Osc.js:35-47 */
+static void tick_osc(Unit *u) {
+  const float *f = INCH(u, 0)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  for (int t = 0; t < CHUNK; t++) {
+    u->phase += (double)f[t];
+    u->phase = fmod(u->phase, (double)SR);
+    if (u->phase < 0) u->phase += SR;
+    double fr = fmod(u->phase, 1.0);
+    out[t] = (float)(ta_read(u->table, SR + 1, floor(u->phase)) * (1 - fr) + ta_read(u->table, SR + 1, ceil(u->phase)) * fr);
+  }
+}
+/* MultiChannelOsc.js:21-38 (no negative-phase fix) */
+static void tick_mcosc(Unit *u) {
+  Chunk *fc = INCH(u, 0), *oc = OUTCH(u, 0);
+  for (int c = 0; c < fc->nch; c++) {
+    if (!u->mc_phase_set[c] || u->mc_phase[c] == 0 || u->mc_phase[c] != u->mc_phase[c]) { u->mc_phase[c] = 0; u->mc_phase_set[c] = 1; } /* `phase[c] || 0` */
+    float *out = chunk_ensure(oc, c); const float *f = fc->ch[c];
+    for (int t = 0; t < CHUNK; t++) {
+      u->mc_phase[c] += (double)f[t];
+      u->mc_phase[c] = fmod(u->mc_phase[c], (double)SR);
+      double ph = u->mc_phase[c], fr = fmod(ph, 1.0);
+      out[t] = (float)(ta_read(u->table, SR + 1, floor(ph)) * (1 - fr) + ta_read(u->table, SR + 1, ceil(ph)) * fr);
+    }
+  }
+}
+/* Ramp.js:25-40 */
+static void tick_ramp(Unit *u) {
+  float *out = OUTCH(u, 0)->ch[0];
+  for (int i = 0; i < CHUNK; i++) {
+    if (u->playing) {
+      u->t++;
+      if (u->t > u->duration) { u->playing = 0; u->t = u->duration; }
+      if (u->t < 0) { u->playing = 0; u->t = 0; }
+    }
+    out[i] = (float)(u->y0 + (u->t / u->duration) * (u->y1 - u->y0));
+  }
+}
+/* Shape/index.js:28-59 */
+static void tick_shape(Unit *u) {
+  const float *dur = INCH(u, 0)->ch[0], *mn = INCH(u, 1)->ch[0], *mx = INCH(u, 2)->ch[0];
+  float *out = OUTCH(u, 0)->ch[0];
+  for (int t = 0; t < CHUNK; t++) {
+    if (u->playing) u->t += 1 / (double)dur[t];
+    double lo = mn[t], hi = mx[t];
+    if (u->t <= 0) {
+      if (u->left_edge_is_shape) out[t] = (float)((double)u->table[0] * (hi - lo) + lo);
+      else out[t] = (float)(u->left_edge * (hi - lo) + lo);
+    } else if (u->t > SR) {
+      if (!u->finished) u->finished = 1; /* finish(): UnitOrPatch.js:77-84 (onFinish graph edits out of scope) */
+      if (u->right_edge_is_shape) out[t] = (float)((double)u->table[SR] * (hi - lo) + lo);
+      else out[t] = (float)(u->right_edge * (hi - lo) + lo);
+    } else {
+      double fr = fmod(u->t, 1.0);
+      out[t] = (float)(lo + (hi - lo) * (ta_read(u->table, SR + 1, ceil(u->t)) * fr + ta_read(u->table, SR + 1, floor(u->t)) * (1 - fr)));
+    }
+    /* NaN t (duration NaN): all three comparisons false -> third branch; table[NaN] undefined -> NaN */
+  }
+}
+/* AHD.js:35-76 */
+static void tick_ahd(Unit *u) {
+  const float *a = INCH(u, 0)->ch[0], *h = INCH(u, 1)->ch[0], *d = INCH(u, 2)->ch[0];
+  float *out = OUTCH(u, 0)->ch[0];
+  const double sp = 1.0 / SR;
+  for (int t = 0; t < CHUNK; t++) {
+    switch (u->state) {
+    case 1: out[t] = (float)u->t;
+      if (u->playing) { u->t += sp / (double)a[t]; if (u->t >= 1) { u->state++; u->t--; } } break;
+    case 2: out[t] = 1;
+      if (u->playing) { u->t += sp / (double)h[t]; if (u->t >= 1) { u->state++; u->t--; } } break;
+    case 3: out[t] = (float)(1 - u->t);
+      if (u->playing) { u->t += sp / (double)d[t]; if (u->t >= 1) { u->state = 0; u->playing = 0; } } break;
+    case 0: out[t] = 0; break;
+    }
+  }
+}
+/* Timer.js:37-42 */
+static void tick_timer(Unit *u) {
+  float *out = OUTCH(u, 0)->ch[0]; const double sp = 1.0 / SR;
+  for (int t = 0; t < CHUNK; t++) { u->t += sp; out[t] = (float)u->t; }
+}
+/* Noise.js:16-28 (Math.random -> injected oracle_rand) */
+static void tick_noise(Unit *u) {
+  Chunk *oc = OUTCH(u, 0); const float *f0 = INCH(u, 0)->ch[0];
+  for (int c = 0; c < oc->nch; c++) {
+    float *out = oc->ch[c];
+    for (int t = 0; t < CHUNK; t++) {
+      u->phase += (double)f0[t];
+      if (u->phase >= SR) { u->phase = 0; u->y = 2 * oracle_rand(u->seed, u->draw++) - 1; }
+      out[t] = (float)u->y;
+    }
+  }
+}
+/* Filter.js:66-84 */
+static void filter_coeffs(Unit *u, double f) {
+  if (u->fkind == 0) {
+    double lamda = 1 / tan(M_PI * f / SR), l2 = lamda * lamda;
+    u->a0 = 1 / (1 + 2 * lamda + l2); u->a1 = 2 * u->a0; u->a2 = u->a0;
+    u->b1 = 2 * u->a0 * (1 - l2); u->b2 = u->a0 * (1 - 2 * lamda + l2);
+  } else {
+    double lamda = tan(M_PI * f / SR), l2 = lamda * lamda;
+    u->a0 = 1 / (1 + 2 * lamda + l2); u->a1 = 0; u->a2 = -u->a0;
+    u->b1 = 2 * u->a0 * (l2 - 1); u->b2 = u->a0 * (1 - 2 * lamda + l2);
+  }
+}
+/* Filter.js:27-51 */
+static void tick_filter(Unit *u) {
+  Chunk *ic = INCH(u, 0), *oc = OUTCH(u, 0); const float *f = INCH(u, 1)->ch[0];
+  int nc = ic->nch;
+  for (int c = 0; c < nc; c++) chunk_ensure(oc, c);
+  for (int t = 0; t < CHUNK; t++) {
+    double ft = f[t];
+    if (!u->lastf_defined || ft != u->lastf) { u->lastf_defined = 1; u->lastf = ft; filter_coeffs(u, ft); }
+    for (int c = 0; c < nc; c++) {
+      double x = ic->ch[c][t];
+      double y = u->a0 * x + u->a1 * js_or0(u->x1[c]) + u->a2 * js_or0(u->x2[c])
+               - u->b1 * js_or0(u->fy1[c]) - u->b2 * js_or0(u->fy2[c]);
+      oc->ch[c][t] = (float)y;
+      u->fy2[c] = js_or0(u->fy1[c]);
+      u->fy1[c] = (double)oc->ch[c][t];
+      u->x2[c] = js_or0(u->x1[c]);
+      u->x1[c] = x;
+    }
+  }
+}
+
+#define MAXI(a, b) ((a) > (b) ? (a) : (b))
+/* Multiply.js:23-34 / Divide.js:16-27 / Pow.js:19-30 (modulo channel broadcast) */
+static void tick_binary_mod(Unit *u, int op) {
+  Chunk *a = INCH(u, 0), *b = INCH(u, 1), *o = OUTCH(u, 0);
+  int n = MAXI(a->nch, b->nch);
+  for (int c = 0; c < n; c++) {
+    const float *ac = a->ch[c % a->nch], *bc = b->ch[c % b->nch]; float *oc = chunk_ensure(o, c);
+    for (int t = 0; t < CHUNK; t++) {
+      double x = ac[t], y = bc[t];
+      oc[t] = (float)(op == 0 ? x * y : op == 1 ? x / y : pow(x, y));
+    }
+  }
+}
+/* Sum.js:33-44 (a[c % a.length] is always defined, zeroChannel unreachable) */
+static void tick_sum(Unit *u) {
+  Chunk *a = INCH(u, 0), *b = INCH(u, 1), *o = OUTCH(u, 0);
+  int n = MAXI(a->nch, b->nch);
+  for (int c = 0; c < n; c++) {
+    const float *ac = a->ch[c % a->nch], *bc = b->ch[c % b->nch]; float *oc = chunk_ensure(o, c);
+    for (int t = 0; t < CHUNK; t++) oc[t] = (float)((double)ac[t] + (double)bc[t]);
+  }
+}
+/* Subtract.js:19-29 (zero-fill, not modulo) */
+static void tick_subtract(Unit *u) {
+  Chunk *a = INCH(u, 0), *b = INCH(u, 1), *o = OUTCH(u, 0);
+  int n = MAXI(a->nch, b->nch);
+  for (int c = 0; c < n; c++) {
+    float *oc = chunk_ensure(o, c);
+    const float *ac = c < a->nch ? a->ch[c] : ZERO_CHUNK, *bc = c < b->nch ? b->ch[c] : ZERO_CHUNK;
+    for (int t = 0; t < CHUNK; t++) oc[t] = (float)((double)ac[t] - (double)bc[t]);
+  }
+}
+static double dB(double db) { return pow(10, db / 20); } /* Gain.js:26-28, Pan.js:26-28 */
+/* Gain.js:17-24 */
+static void tick_gain(Unit *u) {
+  Chunk *in = INCH(u, 0), *o = OUTCH(u, 0); const float *g = INCH(u, 1)->ch[0];
+  for (int c = 0; c < in->nch; c++) {
+    float *oc = chunk_ensure(o, c);
+    for (int t = 0; t < CHUNK; t++) oc[t] = (float)(dB(g[t]) * (double)in->ch[c][t]);
+  }
+}
+/* PolarityInvert.js:13-20, Abs.js:17-24, Repeater.js:23-30, SecondsToSamples.js:13-20,
+ * SemitoneToRatio.js:14-22, DecibelToScaler.js:13-19 */
+static void tick_unary(Unit *u, int op) {
+  Chunk *in = INCH(u, 0), *o = OUTCH(u, 0);
+  for (int c = 0; c < in->nch; c++) {
+    float *oc = chunk_ensure(o, c);
+    for (int t = 0; t < CHUNK; t++) {
+      double x = in->ch[c][t], y;
+      switch (op) {
+      case 0: y = -x; break;
+      case 1: y = fabs(x); break;
+      case 2: y = x; break;
+      case 3: y = x * SR; break;
+      case 4: y = pow(2, x / 12); break;
+      default: y = pow(10, x / 20); break;
+      }
+      oc[t] = (float)y;
+    }
+  }
+}
+/* MidiToFrequency.js:14-21: `var fOut = this.frequency[c] || new Float32Array` is
+ * never stored back, so only already-existing outlet channels receive data. */
+static void tick_miditof(Unit *u) {
+  Chunk *in = INCH(u, 0), *o = OUTCH(u, 0);
+  for (int c = 0; c < in->nch && c < o->nch; c++)
+    for (int t = 0; t < CHUNK; t++) o->ch[c][t] = (float)(pow(2, (((double)in->ch[c][t] - 69) / 12)) * 440);
+}
+/* Clip.js:12-21, HardClipAbove.js:14-24, HardClipBelow.js:14-24 */
+static void tick_clip(Unit *u, int op) {
+  Chunk *in = INCH(u, 0), *th = INCH(u, 1), *o = OUTCH(u, 0);
+  for (int c = 0; c < in->nch; c++) {
+    float *oc = chunk_ensure(o, c); const float *ic = in->ch[c], *tc = th->ch[c % th->nch];
+    for (int t = 0; t < CHUNK; t++) {
+      if (op == 0) oc[t] = fabs((double)ic[t]) > fabs((double)tc[t]) ? tc[t] : ic[t];
+      else if (op == 1) oc[t] = ic[t] > tc[t] ? tc[t] : ic[t];
+      else oc[t] = ic[t] < tc[t] ? tc[t] : ic[t];
+    }
+  }
+}
+/* Rescale.js:24-37 */
+static void tick_rescale(Unit *u) {
+  Chunk *in = INCH(u, 0), *il = INCH(u, 1), *iu = INCH(u, 2), *ol = INCH(u, 3), *ou = INCH(u, 4), *o = OUTCH(u, 0);
+  for (int c = 0; c < in->nch; c++) {
+    float *oc = chunk_ensure(o, c);
+    const float *x = in->ch[c], *a = il->ch[c % il->nch], *b = iu->ch[c % iu->nch], *p = ol->ch[c % ol->nch], *q = ou->ch[c % ou->nch];
+    for (int t = 0; t < CHUNK; t++)
+      oc[t] = (float)(((double)x[t] - (double)a[t]) / ((double)b[t] - (double)a[t]) * ((double)q[t] - (double)p[t]) + (double)p[t]);
+  }
+}
+/* CrossFader.js:20-29 (zero-fill) */
+static void tick_crossfader(Unit *u) {
+  Chunk *a = INCH(u, 0), *b = INCH(u, 1), *o = OUTCH(u, 0); const float *dial = INCH(u, 2)->ch[0];
+  int n = MAXI(a->nch, b->nch);
+  for (int c = 0; c < n; c++) {
+    const float *ac = c < a->nch ? a->ch[c] : ZERO_CHUNK, *bc = c < b->nch ? b->ch[c] : ZERO_CHUNK;
+    float *oc = chunk_ensure(o, c);
+    for (int t = 0; t < CHUNK; t++) oc[t] = (float)((1 - (double)dial[t]) * (double)ac[t] + (double)dial[t] * (double)bc[t]);
+  }
+}
+/* Pan.js:18-24 */
+static void tick_pan(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0], *pan = INCH(u, 1)->ch[0];
+  float *o0 = chunk_ensure(OUTCH(u, 0), 0), *o1 = chunk_ensure(OUTCH(u, 0), 1);
+  for (int t = 0; t < CHUNK; t++) {
+    double p = pan[t], x = in[t];
+    double comp = dB((1 - fabs(p)) * u->comp_db);
+    o0[t] = (float)(x * (1 - p) / 2 * comp);
+    o1[t] = (float)(x * (1 + p) / 2 * comp);
+  }
+}
+/* FixedMultiply.js:19-22 */
+static void tick_fixedmultiply(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; float *o = OUTCH(u, 0)->ch[0];
+  for (int t = 0; t < CHUNK; t++) o[t] = (float)((double)in[t] * u->sf);
+}
+/* ConcatChannels.js:16-30 */
+static void tick_concat(Unit *u) {
+  Chunk *a = INCH(u, 0), *b = INCH(u, 1), *o = OUTCH(u, 0);
+  int na = a->nch, n = a->nch + b->nch;
+  for (int c = 0; c < na; c++) memcpy(chunk_ensure(o, c), a->ch[c], CHUNK * 4);
+  for (int c = na; c < n; c++) memcpy(chunk_ensure(o, c), b->ch[c - na], CHUNK * 4);
+}
+/* PickChannel.js:16-21 */
+static void tick_pickchannel(Unit *u) {
+  Chunk *in = INCH(u, 0); const float *cc = INCH(u, 1)->ch[0]; float *o = OUTCH(u, 0)->ch[0];
+  for (int t = 0; t < CHUNK; t++) {
+    double idx = fmod((double)cc[t], (double)in->nch);
+    o[t] = (idx == floor(idx) && idx >= 0 && idx < in->nch) ? in->ch[(int)idx][t] : NAN;
+  }
+}
+/* VectorMagnitude.js:16-28 */
+static void tick_vectormagnitude(Unit *u) {
+  Chunk *in = INCH(u, 0); float *o = OUTCH(u, 0)->ch[0];
+  for (int t = 0; t < CHUNK; t++) {
+    double s = 0;
+    for (int c = 0; c < in->nch; c++) { double x = in->ch[c][t]; s += x * x; }
+    o[t] = (float)sqrt(s);
+  }
+}
+/* Delay.js:20-41 */
+static void tick_delay(Unit *u, double clock) {
+  Chunk *in = INCH(u, 0), *dl = INCH(u, 1), *o = OUTCH(u, 0);
+  int nin0 = in->nch; /* loop bound re-evaluates this.in.length each iteration; :23 may grow it */
+  for (int c = 0; c < in->nch || c < dl->nch; c++) {
+    float *oc = chunk_ensure(o, c);
+    if (c >= in->nch) { /* this.in[c] = this.in[c % this.in.length]  (aliases, :23) */
+      if (c >= MAXCH) abort();
+      in->ch[c] = in->ch[c % in->nch]; in->nch = c + 1;
+    }
+    if (!u->bufs[c]) u->bufs[c] = (float *)calloc(u->maxdelay, 4);
+    float *buf = u->bufs[c]; long L = u->maxdelay;
+    const float *dc = dl->ch[c % dl->nch], *ic = in->ch[c];
+    for (int t = 0; t < CHUNK; t++) {
+      double tb = fmod(clock + t, (double)L);
+      oc[t] = (float)ta_read(buf, L, tb);
+      ta_write(buf, L, tb, 0);
+      double tw = fmod(tb + (double)dc[t], (double)L), fr = fmod(tw, 1.0);
+      double fl = floor(tw), ce = ceil(tw);
+      if (ta_valid(fl, L)) buf[(long)fl] = (float)((double)buf[(long)fl] + (double)ic[t] * (1 - fr));
+      if (ta_valid(ce, L)) buf[(long)ce] = (float)((double)buf[(long)ce] + (double)ic[t] * fr);
+    }
+  }
+  (void)nin0;
+}
+/* MonoDelay.js:19-30 */
+static void tick_monodelay(Unit *u, double clock) {
+  const float *in = INCH(u, 0)->ch[0], *dl = INCH(u, 1)->ch[0]; float *o = OUTCH(u, 0)->ch[0];
+  float *buf = u->bufs[0]; long L = u->maxdelay;
+  for (int t = 0; t < CHUNK; t++) {
+    double tb = fmod(clock + t, (double)L);
+    double tw = fmod(tb + (double)dl[t], (double)L), fr = fmod(tw, 1.0);
+    double fl = floor(tw), ce = fmod(ceil(tw), (double)L);
+    if (ta_valid(fl, L)) buf[(long)fl] = (float)((double)buf[(long)fl] + (double)in[t] * (1 - fr));
+    if (ta_valid(ce, L)) buf[(long)ce] = (float)((double)buf[(long)ce] + (double)in[t] * fr);
+    o[t] = (float)ta_read(buf, L, tb);
+    ta_write(buf, L, tb, 0);
+  }
+}
+/* ReadBackDelay.js:23-43 */
+static int tick_readbackdelay(Oracle *o_, Unit *u) {
+  Chunk *in = INCH(u, 0), *dl = INCH(u, 1), *o = OUTCH(u, 0);
+  double t0 = u->tbuffer, t1 = t0 + CHUNK; long L = u->buflen;
+  int n = MAXI(in->nch, dl->nch);
+  for (int c = 0; c < n; c++) {
+    const float *ic = in->ch[c % in->nch], *dc = dl->ch[c % dl->nch]; float *oc = chunk_ensure(o, c);
+    if (!u->bufs[c]) u->bufs[c] = (float *)calloc(L, 4);
+    float *buf = u->bufs[c];
+    int i = 0;
+    for (double t = t0; t < t1; t++) {
+      if ((double)dc[i] > (double)L) return fail(o_, "delay may not exceed buffer length");
+      ta_write(buf, L, fmod(t + L, (double)L), ic[i]);
+      oc[i] = (float)ta_read(buf, L, fmod(t - (double)dc[i] + L, (double)L));
+      i++;
+    }
+  }
+  u->tbuffer = t1;
+  return 0;
+}
+/* FixedDelay.js:14-20, CombFilter.js:11-17, AllPass.js:8-15 */
+static void tick_fixeddelay(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; float *o = OUTCH(u, 0)->ch[0]; float *buf = u->bufs[0]; long L = u->buflen;
+  const float *g = u->kind == K_FIXEDDELAY ? NULL : INCH(u, 1)->ch[0];
+  for (int t = 0; t < CHUNK; t++) {
+    u->tbuffer = fmod(u->tbuffer + 1, (double)L);
+    long p = (long)u->tbuffer;
+    if (u->kind == K_FIXEDDELAY) { o[t] = buf[p]; buf[p] = in[t]; }
+    else if (u->kind == K_COMBFILTER) { o[t] = buf[p]; buf[p] = (float)((double)in[t] + (double)o[t] * (double)g[t]); }
+    else { double d = buf[p]; buf[p] = (float)((double)in[t] + d * (double)g[t]); o[t] = (float)(d - (double)in[t] * (double)g[t]); }
+  }
+}
+/* CircleBufferWriter.js:12-25 */
+static void tick_cbwriter(Unit *u) {
+  Chunk *off = INCH(u, 0), *in = INCH(u, 1);
+  for (int c = 0; c < u->cb->nch; c++) {
+    const float *oc = off->ch[c % off->nch];
+    for (int t = 0; t < CHUNK; t++) {
+      double tw = u->t + t + (double)SR * (double)oc[t];
+      if (u->prewipe) cb_write(u->cb, c, tw, 0);
+      if (c < in->nch) cb_mix(u->cb, c, tw, (double)in->ch[c][t]);
+    }
+  }
+  u->t += CHUNK;
+}
+/* CircleBufferReader.js:12-25 */
+static void tick_cbreader(Unit *u) {
+  Chunk *off = INCH(u, 0), *o = OUTCH(u, 0);
+  for (int c = 0; c < u->cb->nch; c++) {
+    const float *oc = off->ch[c % off->nch]; float *out = chunk_ensure(o, c);
+    for (int t = 0; t < CHUNK; t++) {
+      double tr = u->t + t - (double)SR * (double)oc[t];
+      out[t] = (float)cb_read(u->cb, c, tr);
+      if (u->postwipe) cb_write(u->cb, c, tr, 0);
+    }
+  }
+  u->t += CHUNK;
+}
+
+/* Unit.js:111-119 tick -> _tick */
+static int unit_tick(Oracle *o, Unit *u, double clock) {
+  switch (u->kind) {
+  case K_OSC: tick_osc(u); break;
+  case K_MCOSC: tick_mcosc(u); break;
+  case K_RAMP: tick_ramp(u); break;
+  case K_SHAPE: tick_shape(u); break;
+  case K_AHD: tick_ahd(u); break;
+  case K_TIMER: tick_timer(u); break;
+  case K_NOISE: tick_noise(u); break;
+  case K_FILTER: tick_filter(u); break;
+  case K_MULTIPLY: tick_binary_mod(u, 0); break;
+  case K_DIVIDE: tick_binary_mod(u, 1); break;
+  case K_POW: tick_binary_mod(u, 2); break;
+  case K_SUM: tick_sum(u); break;
+  case K_SUBTRACT: tick_subtract(u); break;
+  case K_GAIN: tick_gain(u); break;
+  case K_POLARITYINVERT: tick_unary(u, 0); break;
+  case K_ABS: tick_unary(u, 1); break;
+  case K_REPEATER: tick_unary(u, 2); break;
+  case K_SECONDSTOSAMPLES: tick_unary(u, 3); break;
+  case K_SEMITONETORATIO: tick_unary(u, 4); break;
+  case K_DECIBELTOSCALER: tick_unary(u, 5); break;
+  case K_MIDITOFREQUENCY: tick_miditof(u); break;
+  case K_CLIP: tick_clip(u, 0); break;
+  case K_HARDCLIPABOVE: tick_clip(u, 1); break;
+  case K_HARDCLIPBELOW: tick_clip(u, 2); break;
+  case K_RESCALE: tick_rescale(u); break;
+  case K_CROSSFADER: tick_crossfader(u); break;
+  case K_PAN: tick_pan(u); break;
+  case K_FIXEDMULTIPLY: tick_fixedmultiply(u); break;
+  case K_CONCATCHANNELS: tick_concat(u); break;
+  case K_PICKCHANNEL: tick_pickchannel(u); break;
+  case K_VECTORMAGNITUDE: tick_vectormagnitude(u); break;
+  case K_DELAY: tick_delay(u, clock); break;
+  case K_MONODELAY: tick_monodelay(u, clock); break;
+  case K_READBACKDELAY: return tick_readbackdelay(o, u);
+  case K_FIXEDDELAY: case K_COMBFILTER: case K_ALLPASS: tick_fixeddelay(u); break;
+  case K_CBWRITER: tick_cbwriter(u); break;
+  case K_CBREADER: tick_cbreader(u); break;
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------ sink */
+/* renderChannelData.js:5-49.  out[c] is malloc'd here (caller frees with
+ * oracle_free_output); returns 0 or -1 (message via oracle_error). */
+int oracle_render(Oracle *o, double duration, float **out, int max_ch, int *nch_out, long *nsamples_out) {
+  if (!o->has_order) oracle_schedule(o, NULL);
+  double length = duration * SR;                  /* :24 */
+  long n = length > 0 ? (long)length : 0;         /* new Float32Array(x): ToIndex truncates */
+  Chunk *root = o->units[o->root_unit].out[o->root_outlet].chunk;
+  int nch = 0;
+  for (double t0 = 0; t0 < length; t0 += CHUNK) { /* :29 */
+    /* circuit.tickUntil(t1): Circuit.js:19-47 -- one tick per chunk (all hot-path units tick at 256) */
+    while (o->clock < t0 + CHUNK) {
+      for (int i = 0; i < o->norder; i++)
+        if (unit_tick(o, &o->units[o->order[i]], o->clock)) return -1;
+      o->clock += CHUNK;
+    }
+    while (root->nch > nch) {                     /* :38-39 */
+      if (nch >= max_ch) return fail(o, "too many output channels");
+      out[nch++] = (float *)calloc(n > 0 ? n : 1, sizeof(float));
+    }
+    for (int c = 0; c < root->nch; c++)           /* :42-44: `x || 0`, out-of-range stores dropped */
+      for (int t = 0; t < CHUNK; t++) {
+        long i = (long)t0 + t;
+        if (i < n) { float x = root->ch[c][t]; out[c][i] = (x != x || x == 0) ? 0.f : x; }
+      }
+  }
+  *nch_out = nch; *nsamples_out = n;
+  return 0;
+}
+void oracle_free_output(float **out, int nch) { for (int c = 0; c < nch; c++) free(out[c]); }
+const char *oracle_error(Oracle *o) { return o->err; }
+int oracle_num_units(Oracle *o) { return o->nunits; }

@@ -1,0 +1,274 @@
+"""Circuit factories shared by the CPU and GPU tests.  Each returns the thing a
+user would hand to renderChannelData (a Unit, Patch or Outlet).  `exact` says
+whether GPU output must equal the oracle bit for bit; circuits that evaluate
+tan / pow on the device (libdevice vs glibc differ in the last ulp of double)
+are held to the north-star tolerance instead (max-abs <= 1e-5 of full scale).
+"""
+import dusp_b200 as d
+from dusp_b200 import components as C, patches as P, quick
+
+
+def osc440():
+    return d.unDusp("[Osc 440]")
+
+
+def readme_fm_literal():  # SURVEY 3.1 trap: renders a 1 Hz sine
+    return d.unDusp("[Osc f:[Ramp from:200 to:100 duration:2]]")
+
+
+def w2_literal():
+    return d.unDusp("[Multiply A:[Osc #o f:[Ramp from:200 to:100 duration:2]] B:#o]")
+
+
+def w2_live(f0=313.7):
+    osc = C.Osc(C.Ramp(88200, f0, f0 / 2).trigger())
+    return C.Multiply(osc, osc)
+
+
+def sum_pan():  # test/test_renderChannelData.js:4
+    return d.unDusp("(O200 + O250) @ 0")
+
+
+def envelope_fm():
+    return d.unDusp("[Osc f:(D2 * 100 + 100)]")
+
+
+def attack_env():
+    return d.unDusp("A0.5 * O330.5")
+
+
+def waveforms():
+    return d.unDusp("Z110.25 + Sq220.5 * 0.25 + [Osc f:77.7 waveform:'triangle'] + [Osc f:55.5 waveform:'8bit']")
+
+
+def osc_negative_f():
+    return C.Osc(quick.add(quick.multiply(C.Osc(3.3), 900), -200))
+
+
+def arithmetic():
+    a, b = C.Osc(123.4), C.Osc(0.77, "saw")
+    x = C.Subtract(C.Multiply(a, b), C.Divide(a, quick.add(b, 1.5)))
+    y = C.CrossFader(x, C.Abs(a), quick.multiply(quick.add(b, 1), 0.5))
+    z = C.HardClipAbove(C.HardClipBelow(y, -0.4), 0.6)
+    clip = C.Clip(0.5)
+    clip.IN = C.PolarityInvert(z)
+    r = C.Rescale(-1, 1, 3, 7)
+    r.IN = clip
+    return C.FixedMultiply(0.37, C.Sum(r, C.Repeater(a)))
+
+
+def stereo_concat():
+    a, b = C.Osc(300), C.Osc(301)
+    st = quick.concat(a, b)                 # 2 channels
+    m = C.Multiply(st, [0.5, 0.25])         # per-channel constants
+    return C.Subtract(m, C.Osc(2))          # zero-fill broadcast: channel 1 gets 0 - ... no: a[1]-b[1] with b absent
+
+
+def vector_magnitude():
+    v = C.VectorMagnitude()
+    v.IN = quick.concat(C.Osc(100), C.Osc(150))
+    return v
+
+
+def transcendental():  # pow on the device: tolerance class
+    g = C.Gain(-6.5)
+    g.IN = C.Osc(220)
+    s = C.SemitoneToRatio(C.Multiply(C.Osc(0.5), 7))
+    m = C.MidiToFrequency(quick.add(C.Multiply(C.Osc(0.25), 12), 60))
+    db = C.DecibelToScaler(C.Multiply(C.Osc(1.5), 20))
+    return C.Sum(C.Multiply(g, s), C.Multiply(C.Osc(m), C.Pow(C.Abs(db), 0.5)))
+
+
+def pan_modulated():
+    return C.Pan(C.Osc(440), C.Multiply(C.Osc(0.7), 0.9))
+
+
+def noise_default():
+    return C.Noise()
+
+
+def noise_sample_hold():
+    return C.Noise(3000.5)
+
+
+def filter_lp():
+    return C.Filter(C.Noise(), 800)
+
+
+def filter_hp():
+    return d.unDusp("[Noise] -> HP2500")
+
+
+def filter_lp_low():
+    return C.Filter(C.Noise(), 1)  # the Worm patch default: brutal on rounding fidelity
+
+
+def filter_modulated():
+    return C.Filter(C.Osc(110, "saw"), quick.add(quick.multiply(C.Osc(0.8), 900), 1000))
+
+
+def filter_unset_f():  # NaN coefficients -> rendered as zeros
+    return C.Filter(C.Osc(100))
+
+
+def filter_stereo():
+    return C.Filter(quick.concat(C.Noise(), C.Osc(50, "square")), 1200)
+
+
+def shape_variants():
+    a = C.Shape("semiSine", 0.3, -1, 2).trigger()
+    b = C.Shape("decaySquared", 0.05).trigger()
+    c = C.Shape("attack", 0.2)  # never triggered: sits on its left edge
+    return C.Sum(C.Sum(a, b), c)
+
+
+def ahd_timer():
+    e = C.AHD(0.01, 0.02, 0.05).trigger()
+    return C.Sum(C.Multiply(e, C.Osc(500)), C.Multiply(C.Timer(), 0.1))
+
+
+def fixed_delays():
+    src = C.Multiply(C.Osc(220, "saw"), C.Shape("decay", 0.05).trigger())
+    fd = C.FixedDelay(0.01)
+    fd.IN = src
+    cf = C.CombFilter(0.0123, 0.6)
+    cf.IN = fd
+    ap = C.AllPass(0.00377, 0.5)
+    ap.IN = cf
+    ap2 = C.AllPass(0.0001, 0.7)  # 4-sample ring: recurrence inside a sub-block
+    ap2.IN = ap
+    return ap2
+
+
+def delay_interp():
+    src = C.Multiply(C.Noise(), C.Shape("decay", 0.02).trigger())
+    return C.Delay(src, quick.add(quick.multiply(C.Osc(3), 40.5), 300.25))
+
+
+def delay_short_and_mono():
+    src = C.Osc(333)
+    return C.Sum(C.Delay(src, 3.5), C.MonoDelay(src, 100.75))
+
+
+def readback_delay():
+    return C.ReadBackDelay(C.Osc(410), 64, 4096)
+
+
+def simple_delay():  # cyclic graph: one edge is read a chunk stale
+    return P.SimpleDelay(C.Filter(C.Noise(), 800), 0.25, 0.5, 0.4)
+
+
+def simple_delay_dusp():
+    return d.unDusp("[SimpleDelay IN:[Filter IN:[Noise] F:800] DELAY:0.25 FEEDBACK:0.5] @ 0.3")
+
+
+def w3_voice(f=1234.5, dly=0.137, g=0.55, p=-0.3):
+    filt = C.Filter(C.Noise(), f, "LP")
+    mt = P.MultiTapDelay(1, 1.0, filt)
+    tap = mt.addFeedback(dly, g, 0)
+    return C.Pan(C.Sum(filt, tap), p)
+
+
+def delay_mixer():
+    dm = P.DelayMixer(2, 0.5)
+    dm.addInput(quick.concat(C.Osc(200), C.Osc(300)), 0.1, 0.5)
+    dm.addInput(C.Osc(5, "square"), 0.25)
+    return dm
+
+
+def mixer_lfo():
+    m = P.Mixer(C.Osc(100), P.LFO(2, 0.3, 0.1), C.Multiply(C.Osc(150), 0.5))
+    m.addAttenuated(C.Osc(75), 0)
+    return m
+
+
+def worm():
+    return P.Worm(3)
+
+
+def boop():
+    return P.Boop(660, 0.1)
+
+
+def many_osc():
+    return P.ManyOsc.ofFrequencies(110, [1, 2.01, 3.5])
+
+
+def stereo_detune():
+    return C.Osc(0) if False else P.StereoDetune(C.Osc(440), 0.3)
+
+
+def fm_osc():
+    f = P.FMOsc(220)
+    f.addModulator(C.Osc(3), 2)
+    return f
+
+
+def ap_stack():
+    s = P.APStack(3, 0.02, 0.5)
+    s.IN = C.Multiply(C.Noise(), C.Shape("decay", 0.01).trigger())
+    return s
+
+
+def band_filter():
+    return P.BandFilter(C.Noise(), 300, 3000)
+
+
+def stereo_osc():
+    return P.StereoOsc(57, -3, 0.4)
+
+
+def midi_osc():
+    return P.MidiOsc(64)
+
+
+def at_zero():
+    return d.unDusp("[Osc f:([Ramp 44100 400 200] at 0)]")
+
+
+# name -> (factory, seconds, exact?)
+CASES = {
+    "osc440": (osc440, 1.0, True),
+    "readme_fm_literal": (readme_fm_literal, 1.0, True),
+    "w2_literal": (w2_literal, 0.5, True),
+    "w2_live": (w2_live, 2.5, True),
+    "sum_pan": (sum_pan, 1.0, False),
+    "envelope_fm": (envelope_fm, 2.2, True),
+    "attack_env": (attack_env, 0.7, True),
+    "waveforms": (waveforms, 0.5, True),
+    "osc_negative_f": (osc_negative_f, 0.5, True),
+    "arithmetic": (arithmetic, 0.3, True),
+    "stereo_concat": (stereo_concat, 0.2, True),
+    "vector_magnitude": (vector_magnitude, 0.2, True),
+    "transcendental": (transcendental, 0.5, False),
+    "pan_modulated": (pan_modulated, 0.5, False),
+    "noise_default": (noise_default, 0.3, True),
+    "noise_sample_hold": (noise_sample_hold, 0.5, True),
+    "filter_lp": (filter_lp, 0.5, False),
+    "filter_hp": (filter_hp, 0.5, False),
+    "filter_lp_low": (filter_lp_low, 1.0, False),
+    "filter_modulated": (filter_modulated, 0.5, False),
+    "filter_unset_f": (filter_unset_f, 0.1, True),
+    "filter_stereo": (filter_stereo, 0.3, False),
+    "shape_variants": (shape_variants, 0.5, True),
+    "ahd_timer": (ahd_timer, 0.2, True),
+    "fixed_delays": (fixed_delays, 0.3, True),
+    "delay_interp": (delay_interp, 0.3, True),
+    "delay_short_and_mono": (delay_short_and_mono, 0.2, True),
+    "readback_delay": (readback_delay, 0.2, True),
+    "simple_delay": (simple_delay, 1.0, False),
+    "simple_delay_dusp": (simple_delay_dusp, 1.0, False),
+    "w3_voice": (w3_voice, 1.5, False),
+    "delay_mixer": (delay_mixer, 0.8, True),
+    "mixer_lfo": (mixer_lfo, 0.5, False),
+    "worm": (worm, 0.5, False),
+    "boop": (boop, 0.2, True),
+    "many_osc": (many_osc, 0.3, True),
+    "stereo_detune": (stereo_detune, 0.2, True),
+    "fm_osc": (fm_osc, 0.3, False),
+    "ap_stack": (ap_stack, 0.3, True),
+    "band_filter": (band_filter, 0.3, False),
+    "stereo_osc": (stereo_osc, 0.3, False),
+    "midi_osc": (midi_osc, 0.2, False),
+    "at_zero": (at_zero, 1.2, True),
+}

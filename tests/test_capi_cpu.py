@@ -1,0 +1,106 @@
+"""C-ABI checks that need no GPU: the library loads, exports every declared
+symbol, compiles circuits to programs and rejects what it does not accelerate."""
+import ctypes
+import re
+import os
+
+import pytest
+
+import dusp_b200 as d
+from dusp_b200 import capi, components as C, patches as P, quick
+from dusp_b200.render import circuit_blob
+
+import circuits
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_symbols_are_exported(lib):
+    header = open(os.path.join(ROOT, "include", "dusp_b200.h")).read()
+    declared = set(re.findall(r"\b(dusp_[a-z0-9_]+)\s*\(", header))
+    assert declared == set(capi.SYMBOLS)
+    for s in declared:
+        assert hasattr(lib, s), s
+    assert lib.dusp_abi_version() == 1
+
+
+def test_rand53_agrees_across_host_library_and_oracle(lib, oracle):
+    for seed, k in [(0, 0), (77, 5), (2**64 - 1, 123456789), (0xDEADBEEF, 2**40)]:
+        assert lib.dusp_rand53(seed, k) == d.config.rand53(seed, k) == oracle.rand(seed, k)
+
+
+@pytest.mark.parametrize("name", sorted(circuits.CASES))
+def test_every_case_compiles(lib, oracle, name):
+    fac, _, _ = circuits.CASES[name]
+    blob, circuit = circuit_blob(fac())
+    p = capi.Program(blob)
+    assert p.num_units == len(circuit.units)
+    assert p.num_channels == len(oracle.render(blob, 0.01))
+    assert p.num_instructions >= 1 and 1 <= p.num_slots <= 16
+    assert "out" in p.disassemble()
+
+
+def test_program_parameters_are_named(lib):
+    blob, _ = circuit_blob(circuits.w3_voice())
+    p = capi.Program(blob)
+    names = dict(p.params())
+    pan = [n for n in names if n.endswith(".pan[0]")]
+    off = [n for n in names if n.endswith(".offset[0]")]
+    seed = [n for n in names if n.endswith(".seed_lo")]
+    assert len(pan) == 1 and len(off) == 3 and len(seed) == 1
+    assert names[pan[0]] == pytest.approx(-0.3)
+    assert p.bytes_per_voice_sample(capi.OUT_VOICES) == 24  # 8 out + 4 + 4 + 8
+    assert p.bytes_per_voice_sample(capi.OUT_MIX) == 16
+
+
+def test_cyclic_graph_uses_a_stale_buffer(lib):
+    blob, _ = circuit_blob(circuits.simple_delay())
+    text = capi.Program(blob).disassemble()
+    assert "ldstale" in text and "ststale" in text and "1 stale" in text
+
+
+def test_bad_blob_is_rejected(lib):
+    with pytest.raises(d.DuspError):
+        capi.Program("hello")
+    with pytest.raises(d.DuspError, match="expects an outlet"):
+        capi.Program("DUSPGRAPH 1\nEND\n")
+
+
+def test_unsupported_configurations_fail_loudly(lib):
+    # CircleBuffer taps closer than one chunk: sub-block order would differ from the reference
+    mt = P.MultiTapDelay(1, 1.0, C.Osc(100))
+    tap = mt.addFeedback(0.001, 0.5, 0)
+    blob, _ = circuit_blob(C.Sum(mt.writer.IN.outlet, tap))
+    with pytest.raises(capi.UnsupportedCircuit, match="closer than one"):
+        capi.Program(blob)
+    # a unit feeding itself
+    m = C.Multiply(1, 0.5)
+    m.A = m
+    blob, _ = circuit_blob(m)
+    with pytest.raises(capi.UnsupportedCircuit, match="own inlet"):
+        capi.Program(blob)
+    # events after the first chunk need run-time graph edits
+    with pytest.raises(capi.UnsupportedCircuit, match="event"):
+        circuit_blob(d.unDusp("[Osc f:([Ramp 100 1 2] at 1)]"))
+
+
+def test_no_cpu_fallback(lib):
+    """Without a CUDA device session creation must fail, not render on the host."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    blob, _ = circuit_blob(C.Osc(440))
+    p = capi.Program(blob)
+    with pytest.raises(d.DuspError, match="no CUDA device|CUDA"):
+        capi.Session([p], [1])
+    with pytest.raises(d.DuspError):
+        d.renderChannelData(C.Osc(440), 0.01)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "dusp_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cc", ".cu", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "liboracle" not in text and "import oracle" not in text and "from oracle" not in text, f

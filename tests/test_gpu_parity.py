@@ -1,0 +1,206 @@
+"""Parity tests proper: the CUDA path, called through the C ABI, against the
+oracle on the same inputs.  Bar: bit-exact wherever the device evaluates only
+IEEE +,-,*,/,sqrt and conversions; max-abs <= 1e-5 of full scale (north_star)
+where a libdevice transcendental (tan / pow) is involved."""
+import numpy as np
+import pytest
+
+import dusp_b200 as d
+from dusp_b200 import capi, components as C, patches as P
+from dusp_b200.render import circuit_blob, n_samples_for
+
+import circuits
+
+pytestmark = pytest.mark.gpu
+SR = 44100
+TOL = 1e-5
+
+
+def gpu_render(blob, seconds, n_voices=1):
+    p = capi.Program(blob)
+    s = capi.Session([p], [n_voices], 0)
+    try:
+        return s.render_host(n_samples_for(seconds))
+    finally:
+        s.close()
+
+
+def compare(got, want, exact, what=""):
+    assert got.shape[0] == len(want), what
+    for c, w in enumerate(want):
+        g = got[c]
+        assert g.shape == w.shape
+        assert not np.isnan(g).any()
+        if exact:
+            if not np.array_equal(g, w):
+                bad = np.flatnonzero(g != w)
+                raise AssertionError("%s ch%d: %d/%d samples differ, first at %d: %r vs %r" %
+                                     (what, c, bad.size, g.size, bad[0], g[bad[0]], w[bad[0]]))
+        else:
+            full = max(1.0, float(np.max(np.abs(w))) if w.size else 1.0)
+            err = float(np.max(np.abs(g.astype(np.float64) - w.astype(np.float64)))) if w.size else 0.0
+            assert err <= TOL * full, "%s ch%d: max-abs error %g (full scale %g)" % (what, c, err, full)
+
+
+@pytest.mark.parametrize("name", sorted(circuits.CASES))
+def test_case_matches_oracle(lib, oracle, name):
+    fac, seconds, exact = circuits.CASES[name]
+    blob, _ = circuit_blob(fac())
+    compare(gpu_render(blob, seconds)[0], oracle.render(blob, seconds), exact, name)
+
+
+def test_osc440_ten_seconds_bit_exact(lib, oracle):
+    """BASELINE config 0: [Osc 440] rendered 10 s mono."""
+    blob, _ = circuit_blob(circuits.osc440())
+    got = gpu_render(blob, 10)[0]
+    assert got.shape == (1, 441000)
+    compare(got, oracle.render(blob, 10), True, "osc440 10s")
+
+
+def test_render_channel_data_api(lib, oracle):
+    cd = d.renderChannelData(d.unDusp("(O200 + O250) @ 0"), 1)
+    assert len(cd) == 2 and cd[0].shape == (SR,) and cd.sampleRate == SR and cd[0].dtype == np.float32
+    blob, _ = circuit_blob(d.unDusp("(O200 + O250) @ 0"))
+    compare(np.stack(cd), oracle.render(blob, 1), False, "sum_pan api")
+    with pytest.raises(d.DuspError, match="expects an outlet"):
+        d.renderChannelData(None, 1)
+
+
+@pytest.mark.parametrize("seconds", [0, 1 / SR, 255 / SR, 256 / SR, 257 / SR, 0.0123])
+def test_ragged_durations(lib, oracle, seconds):
+    blob, _ = circuit_blob(circuits.w2_live())
+    got = gpu_render(blob, seconds)[0]
+    want = oracle.render(blob, seconds)
+    if not want:
+        assert got.shape[-1] == 0
+    else:
+        compare(got, want, True, "ragged %g" % seconds)
+
+
+def test_block_wise_render_continues_state(lib, oracle):
+    blob, _ = circuit_blob(circuits.w3_voice())
+    p = capi.Program(blob)
+    s = capi.Session([p], [1], 0)
+    a = s.render_host(1024)
+    b = s.render_host(2048)
+    s.reset()
+    whole = s.render_host(3072)
+    s.close()
+    assert np.array_equal(np.concatenate([a, b], axis=-1), whole)
+
+
+def unit_index(blob, kind, nth=0):
+    kinds = [l.split()[1] for l in blob.splitlines() if l.startswith("U ")]
+    return [i for i, k in enumerate(kinds) if k == kind][nth]
+
+
+def test_w2_live_batch_with_per_voice_parameters(lib, oracle):
+    """BASELINE config 1 shape (FM ring-mod), 96 voices with their own ramp, bit-exact."""
+    rng = np.random.default_rng(1001)
+    f0 = rng.uniform(100, 800, 96)
+    blob, _ = circuit_blob(circuits.w2_live(300.0))
+    ramp = unit_index(blob, "Ramp")
+    p = capi.Program(blob)
+    s = capi.Session([p], [96], 0)
+    s.set_params(0, ["u%d.y0" % ramp, "u%d.y1" % ramp], np.stack([f0, f0 / 2], axis=1))
+    got = s.render_host(SR // 2)
+    s.close()
+    for v in (0, 1, 31, 32, 63, 95):
+        vb, _ = circuit_blob(circuits.w2_live(float(f0[v])))
+        compare(got[v], oracle.render(vb, 0.5), True, "w2 voice %d" % v)
+
+
+def w3_overrides(blob, f, dly, g, pan, seeds):
+    filt, pan_u = unit_index(blob, "Filter"), unit_index(blob, "Pan")
+    reader, mult, noise = unit_index(blob, "CircleBufferReader"), unit_index(blob, "Multiply"), unit_index(blob, "Noise")
+    names = ["u%d.f[0]" % filt, "u%d.offset[0]" % reader, "u%d.b[0]" % mult, "u%d.pan[0]" % pan_u,
+             "u%d.seed_lo" % noise, "u%d.seed_hi" % noise, "u%d.y" % noise]
+    y0 = np.array([2 * d.config.rand53(int(sd), 0) - 1 for sd in seeds])
+    vals = np.stack([f, dly, g, pan, (seeds & 0xFFFFFFFF).astype(np.float64), (seeds >> 32).astype(np.float64), y0], axis=1)
+    return names, vals
+
+
+def test_w3_batch_with_per_voice_parameters(lib, oracle):
+    """BASELINE config 2 shape: Noise -> LP -> CircleBuffer feedback delay -> Pan, 40 voices."""
+    rng = np.random.default_rng(1002)
+    n = 40
+    f, dly = rng.uniform(200, 4000, n), rng.uniform(0.05, 0.5, n)
+    g, pan = rng.uniform(0.2, 0.7, n), rng.uniform(-1, 1, n)
+    seeds = rng.integers(0, 2**63, n, dtype=np.uint64)
+    blob, _ = circuit_blob(circuits.w3_voice())
+    p = capi.Program(blob)
+    s = capi.Session([p], [n], 0)
+    names, vals = w3_overrides(blob, f, dly, g, pan, seeds)
+    s.set_params(0, names, vals)
+    got = s.render_host(SR)
+    mix = None
+    s.reset()
+    mix = s.render_host(SR, capi.OUT_MIX)
+    s.close()
+    ref_mix = np.zeros((2, SR))
+    for v in range(n):
+        filt = C.Filter(C.Noise(seed=int(seeds[v])), float(f[v]), "LP")
+        mt = P.MultiTapDelay(1, 1.0, filt)
+        tap = mt.addFeedback(float(dly[v]), float(g[v]), 0)
+        vb, _ = circuit_blob(C.Pan(C.Sum(filt, tap), float(pan[v])))
+        want = oracle.render(vb, 1.0)
+        if v % 7 == 0:
+            compare(got[v], want, False, "w3 voice %d" % v)
+        ref_mix += np.stack(want).astype(np.float64)
+    assert np.max(np.abs(mix - ref_mix)) <= TOL * max(1.0, np.max(np.abs(ref_mix)))
+    assert np.max(np.abs(mix - got.astype(np.float64).sum(axis=0))) <= 1e-5 * max(1.0, np.max(np.abs(ref_mix)))
+
+
+def test_multi_program_session(lib, oracle):
+    cases = ["w2_live", "w3_voice", "fixed_delays", "stereo_concat"]
+    blobs = [circuit_blob(circuits.CASES[c][0]())[0] for c in cases]
+    progs = [capi.Program(b) for b in blobs]
+    s = capi.Session(progs, [3, 2, 1, 2], 0)
+    got = s.render_host(4096)
+    s.close()
+    assert got.shape == (8, 2, 4096)
+    row = 0
+    for c, b, nv in zip(cases, blobs, [3, 2, 1, 2]):
+        want = oracle.render(b, 4096 / SR)
+        for _ in range(nv):
+            compare(got[row][:len(want)], want, circuits.CASES[c][2], c)
+            assert np.all(got[row][len(want):] == 0)
+            row += 1
+
+
+def test_unsupported_voice_parameters_are_rejected(lib):
+    blob, _ = circuit_blob(circuits.w3_voice())
+    p = capi.Program(blob)
+    s = capi.Session([p], [2], 0)
+    reader = unit_index(blob, "CircleBufferReader")
+    with pytest.raises(capi.UnsupportedCircuit, match="closer than one"):
+        s.set_params(0, ["u%d.offset[0]" % reader], np.array([[0.2], [0.001]]))
+    s.close()
+
+
+def test_full_size_w2_properties(lib):
+    """BASELINE config 1 at full size (1000 voices x 10 s): size-independent properties.
+    Voices with equal parameters are identical; integer-frequency voices equal the
+    closed-form table read-out of Osc.js:39-45 squared."""
+    import math
+    n, secs = 1000, 10
+    blob, _ = circuit_blob(circuits.w2_live(400.0))
+    ramp = unit_index(blob, "Ramp")
+    p = capi.Program(blob)
+    s = capi.Session([p], [n], 0)
+    rng = np.random.default_rng(5)
+    y0 = rng.uniform(100, 800, n)
+    y0[::50] = 440.0
+    y1 = y0 / 2
+    y1[::50] = 440.0  # flat ramp: constant integer frequency
+    s.set_params(0, ["u%d.y0" % ramp, "u%d.y1" % ramp], np.stack([y0, y1], axis=1))
+    got = s.render_host(secs * SR)
+    s.close()
+    tab = np.array([math.sin(2 * math.pi * t / 44101) for t in range(44101)], dtype=np.float32)
+    k = np.arange(secs * SR, dtype=np.int64)
+    o = tab[(440 * (k + 1)) % SR]
+    assert np.array_equal(got[0, 0], o * o)
+    for v in range(50, n, 50):
+        assert np.array_equal(got[v, 0], got[0, 0])
+    assert not np.isnan(got).any() and float(np.abs(got).max()) <= 1.0
+    assert len({got[v, 0].tobytes() for v in range(1, 50)}) == 49  # distinct voices differ

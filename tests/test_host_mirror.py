@@ -1,0 +1,151 @@
+"""Host logic of the reference-facing API: parser, constructor, setter sugar,
+patches, errors."""
+import math
+
+import pytest
+
+import dusp_b200 as d
+from dusp_b200 import components as C, patches as P, parse, quick
+from dusp_b200.graph import DuspError
+
+
+def test_number_token_quirk():
+    """getNumber.js:1-18: a number is a run of [0-9.-] => `200-100` is ONE token -> 200."""
+    assert parse.getNumber("200-100")["n"] == 200
+    assert parse.getNumber("-3.5x")["n"] == -3.5
+    assert math.isnan(parse.getNumber("-")["n"])
+    assert parse.getNumber("abc") is None
+
+
+def test_operator_binding_order():
+    t = parse.getExpression("1 + 2 * 3")
+    assert t["operator"] == "+" and t["b"]["operator"] == "*"
+    assert d.unDusp("1 + 2 * 3") == 7
+    assert d.unDusp("(1 + 2) * 3") == 9
+    assert d.unDusp("2 ^ 3") == 8
+
+
+def test_object_parse_and_ids():
+    t = parse.getExpression("[Osc #myOsc f:330]")
+    assert t["type"] == "object" and t["constructor"] == "Osc" and t["id"] == "myOsc"
+    assert t["attributes"][0]["property"] == "f"
+    o = d.unDusp("[Multiply A:[Osc #yourOsc f:100] B:#yourOsc]")
+    assert o.A.outlet.unit is o.B.outlet.unit and o.A.outlet.unit.label == "yourOsc"
+
+
+def test_readme_ramp_trap():
+    """Ramp has no inlets, so from/to/duration become plain properties."""
+    osc = d.unDusp("[Osc f:[Ramp from:200 to:100 duration:2]]")
+    ramp = osc.F.outlet.unit
+    assert ramp.duration == 2 and ramp.y0 == 1 and ramp.y1 == 0 and not ramp.playing
+    assert getattr(ramp, "from") == 200 and ramp.to == 100
+
+
+def test_shorthands():
+    o = d.unDusp("O200")
+    assert isinstance(o, C.Osc) and o.F.constant == 200 and o.waveform == "sin"
+    assert d.unDusp("Z10").waveform == "saw" and d.unDusp("Sq10").waveform == "square"
+    e = d.unDusp("D2")
+    assert isinstance(e, C.Shape) and e.playing and e.shape == "decay" and e.DURATION.constant == 2
+    assert d.unDusp("A0.5").shape == "attack"
+    f = d.unDusp("LP300")
+    assert isinstance(f, C.Filter) and f.kind == "LP" and f.F.constant == 300
+    ap = d.unDusp("AP0.01,0.5")
+    assert isinstance(ap, C.AllPass) and ap.delayTimeInSamples == 441
+    assert isinstance(d.unDusp("Noise"), C.Noise)
+
+
+def test_operators_build_units():
+    s = d.unDusp("(O200 + O250) @ 0")
+    assert isinstance(s, C.Pan) and isinstance(s.IN.outlet.unit, C.Sum)
+    assert isinstance(d.unDusp("O1 , O2"), C.ConcatChannels)
+    assert isinstance(d.unDusp("O1 / 2"), C.Divide) and isinstance(d.unDusp("O1 - 2"), C.Subtract)
+    f = d.unDusp("[Noise] -> LP200")
+    assert isinstance(f, C.Filter) and isinstance(f.IN.outlet.unit, C.Noise)
+    assert isinstance(d.unDusp("O1 >| 0.5"), C.HardClipAbove) and isinstance(d.unDusp("0.1 |< O1"), C.HardClipBelow)
+
+
+def test_flags_and_string_attributes():
+    s = d.unDusp("[Shape trigger]")
+    assert s.playing
+    o = d.unDusp("[Osc f:50 waveform:'saw']")
+    assert o.waveform == "saw"
+    with pytest.raises(DuspError):
+        d.unDusp("[Osc waveform:'nope']")
+
+
+def test_unknown_constructor_and_bad_reference():
+    with pytest.raises(DuspError, match="Unknown object constructor"):
+        d.unDusp("[Nope 1]")
+    with pytest.raises(DuspError, match="not been declared"):
+        d.unDusp("[Multiply A:#ghost]")
+
+
+def test_out_of_scope_operators_raise():
+    for src in ("O1 then O2", "O1 for 2", "D1 ! 2"):
+        with pytest.raises(DuspError):
+            d.unDusp(src)
+
+
+def test_setter_sugar_and_constants():
+    o = C.Osc()
+    assert o.F.constant == 440 and o.F.chunk == [440.0]
+    o.F = [100, 200]
+    assert o.F.chunk == [100.0, 200.0]
+    o.F = 5                      # Inlet.js:82-92: existing channels are all refilled
+    assert o.F.chunk == [5.0, 5.0]
+    m = C.Multiply(o, 0.5)
+    assert m.A.connected and m.A.outlet is o.OUT and m.B.constant == 0.5
+    m.A = 3
+    assert not m.A.connected and o.OUT.connections == []
+    with pytest.raises(DuspError, match="Passed bad value"):
+        m.A = None
+
+
+def test_js_or_defaults():
+    assert C.Osc(0).F.constant == 440        # `f || 440`
+    assert C.Multiply(0, 0).A.constant == 1  # `a || 1`
+    assert C.Ramp(0, 0, 0).duration == 44100 and C.Ramp(0, 0, 0).y0 == 1
+
+
+def test_patch_alias():
+    lfo = P.LFO(2, 0.3, 0.1)
+    assert lfo.F.constant == 2 and lfo.A.constant == 0.3 and lfo.O.constant == 0.1
+    lfo.F = 7
+    assert lfo.osc.F.constant == 7
+    assert lfo.defaultOutlet.unit.KIND == "Sum"
+    sd = P.SimpleDelay()
+    assert sd.DELAY.constant == 4410 and sd.DRYWET.constant == 0.4
+
+
+def test_fixed_delay_validation():
+    with pytest.raises(DuspError, match="length 0"):
+        C.FixedDelay(0)
+    assert C.FixedDelay(0.01).delayTimeInSamples == 441
+
+
+def test_quick_constant_folding():
+    assert quick.add(1, 2) == 3 and quick.multiply(3, 4) == 12 and quick.multiply(1, 5) == 5
+    o = C.Osc()
+    assert quick.multiply(o, 1) is o and isinstance(quick.multiply(o, 2), C.Multiply)
+    assert quick.concat(1, [2, 3]) == [1, 2, 3]
+
+
+def test_circuit_conflict_and_bad_outlet():
+    from dusp_b200.render import circuit_blob
+    with pytest.raises(DuspError, match="expects an outlet"):
+        circuit_blob(None)
+    with pytest.raises(DuspError, match="expects an outlet"):
+        circuit_blob(42)
+    a, b = C.Osc(), C.Osc()
+    d.Circuit(a)
+    d.Circuit(b)
+    with pytest.raises(DuspError):
+        C.Multiply(a, b)
+
+
+def test_incremental_circuit_growth_keeps_order_valid():
+    a = C.Osc(100)
+    circ = d.Circuit(a)
+    m = C.Multiply(a, 0.5)  # Inlet.connect adds the new unit to a's circuit (Inlet.js:60-73)
+    assert m.circuit is circ and circ.units.index(a) < circ.units.index(m)

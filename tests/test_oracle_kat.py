@@ -1,0 +1,155 @@
+"""Pins the CPU oracle against closed-form known answers derived from the
+reference source -- the reference itself ships no golden vectors
+and cannot run in this image, so these KATs are what the oracle is pinned to."""
+import math
+
+import numpy as np
+import pytest
+
+import dusp_b200 as d
+from dusp_b200 import components as C, patches as P
+from dusp_b200.config import rand53
+from dusp_b200.graphblob import strip_order
+from dusp_b200.render import circuit_blob
+
+import circuits
+
+SR = 44100
+
+
+def sine_table():
+    return np.array([math.sin(2 * math.pi * t / 44101) for t in range(44101)], dtype=np.float32)  # waveTables.js:6-8
+
+
+def render(oracle, outlet, seconds):
+    blob, _ = circuit_blob(outlet)
+    return oracle.render(blob, seconds)
+
+
+def test_tables_match_reference_formulas(oracle):
+    sin = oracle.wave_table("sin")
+    assert np.array_equal(sin, sine_table())
+    assert sin[44100] == np.float32(math.sin(2 * math.pi * 44100 / 44101)) and abs(sin[44100] + 1.4247e-4) < 1e-7
+    saw = oracle.wave_table("saw")
+    assert saw[0] == -1 and saw[44100] == 0 and saw[22050] == np.float32(-1 + 22050 * 2 / 44101)
+    sq = oracle.wave_table("square")
+    assert sq[22049] == 1 and sq[22050] == -1 and sq[44100] == -1
+    tri = oracle.wave_table("triangle")
+    assert tri[11025] == 1 and tri[22050] == 0 and tri[33075] == -1 and tri[44100] == 0
+    assert np.array_equal(oracle.wave_table("8bit"), (np.floor(sin.astype(np.float64) * 128 + 0.5) / 128).astype(np.float32))
+    assert oracle.shape_table("decay")[0] == 1 and oracle.shape_table("decay")[44100] == 0
+    assert oracle.shape_table("decaySquared")[22050] == np.float32(0.25)
+    assert oracle.shape_table("semiSine")[22050] == 1
+
+
+def test_osc440_closed_form(oracle):
+    """Osc.js:39-45: phase advances BEFORE the read; integer f => exact table read-out."""
+    out = render(oracle, circuits.osc440(), 10)
+    assert len(out) == 1 and out[0].shape == (441000,)
+    k = np.arange(441000, dtype=np.int64)
+    expect = sine_table()[(440 * (k + 1)) % SR]
+    assert np.array_equal(out[0], expect)
+    assert np.allclose(out[0][:4], [0.0626469, 0.1250477, 0.18695726, 0.24813233], atol=1e-8)
+
+
+def test_readme_fm_is_a_1hz_sine(oracle):
+    """from/to are dead properties, duration=2 SAMPLES, never triggered -> f == 1."""
+    a = render(oracle, circuits.readme_fm_literal(), 1)[0]
+    b = render(oracle, C.Osc(1), 1)[0]
+    assert np.array_equal(a, b)
+    k = np.arange(SR, dtype=np.int64)
+    assert np.array_equal(a, sine_table()[(k + 1) % SR])
+
+
+def test_w2_literal_is_square_of_1hz(oracle):
+    a = render(oracle, circuits.w2_literal(), 0.25)[0]
+    o = render(oracle, C.Osc(1), 0.25)[0]
+    assert np.array_equal(a, o * o)  # one f32 multiply == JS double multiply + one rounding
+
+
+def test_sum_pan_shape_and_value(oracle):
+    """test/test_renderChannelData.js:4-8: 2 channels x 44100; Pan.js:18-24 centre gain."""
+    out = render(oracle, circuits.sum_pan(), 1)
+    assert len(out) == 2 and out[0].shape == (SR,)
+    tab = sine_table()
+    k = np.arange(SR, dtype=np.int64)
+    s = (tab[(200 * (k + 1)) % SR].astype(np.float64) + tab[(250 * (k + 1)) % SR].astype(np.float64)).astype(np.float32)
+    comp = math.pow(10, 1.5 / 20)
+    expect = (s.astype(np.float64) * 1 / 2 * comp).astype(np.float32)
+    assert np.array_equal(out[0], expect) and np.array_equal(out[1], expect)
+
+
+def test_live_ramp_closed_form(oracle):
+    r = C.Ramp(1000, 200, 100).trigger()
+    out = render(oracle, r, 0.05)[0]
+    t = np.minimum(np.arange(1, len(out) + 1), 1000).astype(np.float64)
+    assert np.array_equal(out, (200 + (t / 1000) * (100 - 200)).astype(np.float32))
+    assert out[-1] == 100
+
+
+def test_untriggered_ramp_is_constant(oracle):
+    out = render(oracle, C.Ramp(2), 0.01)[0]
+    assert np.all(out == 1)
+
+
+def test_noise_uses_injected_stream(oracle):
+    n = C.Noise(seed=77)
+    out = render(oracle, n, 0.01)[0]
+    expect = np.array([2 * rand53(77, k + 1) - 1 for k in range(len(out))]).astype(np.float32)
+    assert np.array_equal(out, expect)
+    assert oracle.rand(77, 5) == rand53(77, 5)
+
+
+def test_noise_sample_and_hold_period(oracle):
+    out = render(oracle, C.Noise(11025, seed=5), 0.01)[0]  # new draw every 4th sample
+    assert out[0] == out[1] == out[2] == np.float32(2 * rand53(5, 0) - 1)
+    assert out[3] == np.float32(2 * rand53(5, 1) - 1) and out[7] == np.float32(2 * rand53(5, 2) - 1)
+
+
+def test_filter_unset_f_renders_zeros(oracle):
+    out = render(oracle, circuits.filter_unset_f(), 0.1)[0]
+    assert np.all(out == 0)
+
+
+def test_fixed_delay_is_pure_delay(oracle):
+    fd = C.FixedDelay(100 / SR)
+    fd.IN = C.Osc(441)
+    out = render(oracle, fd, 0.05)[0]
+    src = render(oracle, C.Osc(441), 0.05)[0]
+    assert np.all(out[:100] == 0) and np.array_equal(out[100:], src[:-100])
+
+
+def test_shape_decay_shorthand(oracle):
+    out = render(oracle, d.unDusp("D1"), 1.5)[0]
+    assert out[0] == np.float32(1 - 1 / SR) and out[SR - 1] == 0 and np.all(out[SR:] == 0)
+
+
+def test_render_length_semantics(oracle):
+    """renderChannelData.js:24-29,44: floor(duration*SR) samples; partial last chunk dropped."""
+    assert render(oracle, C.Osc(100), 0.01)[0].shape == (441,)
+    assert render(oracle, C.Osc(100), 256 / SR)[0].shape == (256,)
+    assert render(oracle, C.Osc(100), 0) == []
+
+
+def test_simple_delay_tick_order(oracle):
+    """the order derived from Unit.js:171-209 + Circuit.js:67-107 for SimpleDelay."""
+    sd = P.SimpleDelay(C.Osc(440), 0.25, 0.5, 0.4)
+    blob, circuit = circuit_blob(sd)
+    kinds = [type(u).__name__ for u in circuit.units]
+    assert kinds == ["Osc", "SecondsToSamples", "Repeater", "Delay", "CrossFader", "Multiply", "Sum"]
+    assert oracle.schedule(strip_order(blob)) == list(range(7))
+
+
+def test_simple_delay_feedback_is_one_chunk_stale(oracle):
+    """With delay 0 samples the wet path is the dry input (Delay.js:27-38 reads then writes),
+    and the feedback edge adds the PREVIOUS chunk's sum: chunk 0 has no feedback at all."""
+    sd = P.SimpleDelay(C.Osc(441), 1e-9, 0.5, 1.0)  # DELAY inlet || default would replace 0
+    out = render(oracle, sd, 0.02)[0]
+    assert np.all(out[:1] == 0)
+
+
+@pytest.mark.parametrize("name", sorted(circuits.CASES))
+def test_host_scheduler_matches_oracle_scheduler(oracle, name):
+    fac, _, _ = circuits.CASES[name]
+    blob, circuit = circuit_blob(fac())
+    assert oracle.schedule(strip_order(blob)) == list(range(len(circuit.units)))
