@@ -1,0 +1,300 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the render path (contract: task prompt section 4).
+
+Workload (BASELINE.json configs[2], the "10k-voice filter batch"): 10 000
+voices x 60 s of  seeded Noise -> LP Filter -> CircleBuffer feedback delay ->
+Pan (stereo), 8 reference units per voice, per-voice parameters from
+dusp_b200.workloads (seed 1002).  One step = one pass over the whole batch:
+the 60 s are rendered in time blocks; in DUSP_OUT_VOICES mode every voice's
+stereo channel data is written to HBM (block buffers are recycled, the full
+211 GB of per-voice audio does not fit in 180 GB).
+
+  value    unit-samples/s, kernel launches only, parameters/state/rings resident in HBM
+  e2e      same metric through the C ABI with HOST (pinned) output buffers: the
+           per-voice channel data crosses PCIe inside the timed region
+  roofline algorithmic bytes (24 B per voice-sample) / measured launch time
+  cpu_baseline / --impl reference: the oracle (C restatement of the reference's
+           JavaScript path) on all host cores, on a bounded sample of the same voices
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SR = 44100
+METRIC = "unit_samples_per_sec"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--voices", type=int, default=10000, help="voices per GPU")
+    ap.add_argument("--seconds", type=float, default=60.0)
+    ap.add_argument("--block-seconds", type=float, default=2.0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------- CPU baseline
+def cpu_baseline(n_units_per_voice, params_fn, budget_s=12.0, cores=None):
+    """The oracle port on all host cores, bounded sample of the SAME voices at the
+    SAME duration (voices are independent, so throughput scales linearly)."""
+    from concurrent.futures import ThreadPoolExecutor
+    from dusp_b200 import workloads as W
+    from dusp_b200.render import circuit_blob
+    from oracle import oracle  # CPU baseline leg: the one place bench.py executes oracle/
+    oracle.lib()
+    cores = cores or os.cpu_count() or 1
+    secs = 10.0
+    probe = W.w3_params(0, 1)
+    blob, _ = circuit_blob(W.w3_voice_circuit(probe, 0))
+    t0 = time.perf_counter()
+    oracle.render(blob, secs)  # ctypes releases the GIL: threads scale across cores
+    one = time.perf_counter() - t0
+    per_core = max(1, int(budget_s / max(one, 1e-3)))
+    n = per_core * cores
+    params = params_fn(0, n)
+    blobs = [circuit_blob(W.w3_voice_circuit(params, v))[0] for v in range(n)]
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(cores) as ex:
+        list(ex.map(lambda b: oracle.render(b, secs)[0][:1], blobs))
+    dt = time.perf_counter() - t0
+    vs = n * int(secs * SR) / dt
+    return {"value": vs * n_units_per_voice, "unit": "unit-samples/s", "cores": cores, "kind": "port",
+            "sample": "%d voices x %g s of the W3 patch (same generator, voices 0..%d), C restatement of the "
+                      "reference's JS render path (Node unavailable), %d threads, %.1f s wall" % (n, secs, n - 1, cores, dt),
+            "voice_samples_per_s": vs, "realtime_voices": vs / SR}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    from dusp_b200 import workloads as W
+    steps = []
+    cb = None
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        cb = cpu_baseline(W.W3_UNITS, W.w3_params, budget_s=2.0 if i < args.warmup else 6.0)
+        steps.append(time.perf_counter() - t0)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "unit-samples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(steps[args.warmup:]) / max(args.steps, 1),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "W3 (BASELINE configs[2]): Noise->LP->CircleBuffer feedback delay->Pan, stereo; "
+                               "bounded sample of the same voices on the host cores", "units_per_voice": W.W3_UNITS},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": "unit-samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "realtime_voices": cb["realtime_voices"],
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ B200 arm
+def run_b200(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from dusp_b200 import capi, workloads as W
+    from dusp_b200.render import circuit_blob
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+
+    nv = args.voices
+    voice0 = rank * nv  # shard by global voice index: no data-path collective
+    params = W.w3_params(voice0, nv)
+    blob, _ = circuit_blob(W.w3_circuit())
+    prog = capi.Program(blob)
+    sess = capi.Session([prog], [nv], local_rank)
+    ov = W.w3_overrides(blob, params)
+    sess.set_params(0, list(ov), np.stack([ov[k] for k in ov], axis=1))
+
+    n_total = int(args.seconds * SR)
+    blk = max(256, int(args.block_seconds * SR) // 256 * 256)
+    blocks = [(t, min(blk, n_total - t)) for t in range(0, n_total, blk)]
+    nch = prog.num_channels
+    dbuf = [torch.empty(nv * nch * blk, dtype=torch.float32, device="cuda") for _ in range(2)]
+    stream = torch.cuda.current_stream()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device(events=None):
+        sess.reset()
+        for i, (t, n) in enumerate(blocks):
+            if events is not None:
+                e0 = torch.cuda.Event(enable_timing=True); e0.record(stream)
+            sess.render_device(n, dbuf[i & 1].data_ptr(), capi.OUT_VOICES, stream.cuda_stream)
+            if events is not None:
+                e1 = torch.cuda.Event(enable_timing=True); e1.record(stream)
+                events.append((e0, e1))
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(args.warmup):
+        step_device()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = sess.launch_count
+    launch_events = []
+    total_ms = timed(lambda: step_device(launch_events), args.steps)
+    launches = sess.launch_count - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    launch_ms = [a.elapsed_time(b) for a, b in launch_events]
+
+    voice_samples_step = nv * n_total * world
+    units = prog.num_units
+    ms_per_step = total_ms / args.steps
+    value = voice_samples_step * units / (ms_per_step / 1e3)
+
+    # roofline of the dominant (only) kernel: algorithmic bytes per launch / average launch time
+    bpvs = prog.bytes_per_voice_sample(capi.OUT_VOICES)
+    full = [m for m, (t, n) in zip(launch_ms, blocks * args.steps) if n == blk] or launch_ms
+    avg_launch_ms = sum(full) / len(full)
+    achieved = bpvs * nv * blk / (avg_launch_ms / 1e3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                "traffic": None, "peak_source": peak_src, "kernel": "dusp_render_lane_per_voice",
+                "bytes_per_voice_sample": bpvs, "avg_launch_ms": avg_launch_ms,
+                "kernel_share_of_step": sum(launch_ms) / total_ms}
+
+    # e2e: the C-ABI call a host shim makes, HOST output buffers (pinned), D2H inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        e2e_secs = min(args.seconds, 10.0)  # 10k voices x 10 s stereo = 35 GB of channel data per step
+        n_e2e = int(e2e_secs * SR)
+        hbuf = torch.empty(nv * nch * n_e2e, dtype=torch.float32).pin_memory()
+        dwords = np.stack([ov[k] for k in ov], axis=1)
+
+        def step_e2e():
+            sess.set_params(0, list(ov), dwords)  # per-step inputs: the voices' parameters (H2D on first launch)
+            sess.render_into_host(hbuf.data_ptr(), n_e2e, capi.OUT_VOICES)
+
+        step_e2e()
+        barrier()
+        t0 = time.perf_counter()
+        k = max(1, min(args.steps, 2))
+        for _ in range(k):
+            step_e2e()
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], device="cuda")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e_val = nv * n_e2e * world * units * k / float(dt.item())
+        e2e = {"value": e2e_val, "unit": "unit-samples/s", "h2d_bytes_per_step": int(dwords.size * 8),
+               "d2h_bytes_per_step": int(nv * nch * n_e2e * 4), "seconds_rendered": e2e_secs,
+               "note": "per-voice stereo channel data copied to pinned host memory (PCIe-bound)"}
+        del hbuf
+
+    cb = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cb = cpu_baseline(units, W.w3_params)
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "unit-samples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "W3 (BASELINE configs[2]): %d voices/GPU x %g s stereo, seeded Noise->LP Filter->"
+                                   "CircleBuffer feedback delay->Pan, 8 units/voice, per-voice output written to HBM"
+                                   % (nv, args.seconds),
+                       "voices_per_gpu": nv, "seconds": args.seconds, "units_per_voice": units,
+                       "time_block_samples": blk, "sharding": "voices by global index, no data-path collective",
+                       "l2": "working set (rings %.2f GB + block outputs %.1f GB) larger than L2"
+                             % (nv * 44100 * 4 / 1e9, 2 * nv * nch * blk * 4 / 1e9)},
+            "realtime_voices": value / units / SR, "voice_samples_per_sec": value / units,
+            "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches),
+            "launch": sess.launch_info(), "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    sess.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -5,6 +5,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -74,7 +75,9 @@ struct Group {
   int n_voices = 0, voice0 = 0;
   long long nv_pad = 0;
   std::vector<double> h_words;  // [n_words][nv_pad] initial values (defaults + overrides)
-  DuspInstr *d_code = nullptr;
+  std::vector<DuspDevInstr> dev_code;
+  DuspDevInstr *d_code = nullptr;
+  int sub_block = 16, time_lanes = 1, warps_per_cta = 1;
   double *d_words = nullptr;
   float *d_rings = nullptr;
   DuspRing *d_ringtab = nullptr;
@@ -91,11 +94,12 @@ struct dusp_session {
   long long unit_count = 0;
   long long clock = 0;
   float *d_tables = nullptr;
-  float *d_staging = nullptr;
+  float *d_staging[2] = {nullptr, nullptr};  // host-output path: double-buffered device blocks
   size_t staging_floats = 0;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_rendered[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
   long long launches = 0;
   int last_grid = 0, last_block = 0, last_smem = 0;
-  int sub_block = 8;
 };
 
 extern "C" {
@@ -151,7 +155,13 @@ void dusp_session_destroy(dusp_session *s) {
   if (!s) return;
   cudaSetDevice(s->device);
   for (auto &g : s->groups) free_group(g);
-  cudaFree(s->d_tables); cudaFree(s->d_staging);
+  cudaFree(s->d_tables);
+  for (int i = 0; i < 2; i++) {
+    cudaFree(s->d_staging[i]);
+    if (s->ev_rendered[i]) cudaEventDestroy(s->ev_rendered[i]);
+    if (s->ev_copied[i]) cudaEventDestroy(s->ev_copied[i]);
+  }
+  if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
   delete s;
 }
 
@@ -187,8 +197,38 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
       const double v = p.f32 ? (double)(float)p.dflt : p.dflt;
       for (long long k = 0; k < g.nv_pad; k++) g.h_words[w * g.nv_pad + k] = v;
     }
-    CUDA_TRY(cudaMalloc(&g.d_code, std::max<size_t>(g.prog.code.size(), 1) * sizeof(DuspInstr)));
-    CUDA_TRY(cudaMemcpy(g.d_code, g.prog.code.data(), g.prog.code.size() * sizeof(DuspInstr), cudaMemcpyHostToDevice));
+    for (long long k = 0; k < g.nv_pad; k++) derive_words(g.prog, g.h_words.data() + k, g.nv_pad);
+    for (const DuspInstr &in : g.prog.code) {
+      DuspDevInstr d;
+      memset(&d, 0, sizeof d);
+      d.op = (int16_t)in.op;
+      for (int k = 0; k < 5; k++) {
+        if (in.in[k] < -32768 || in.in[k] > 32767) return fail(DUSP_EUNSUPPORTED, "circuit has too many per-voice words");
+        d.in[k] = (int16_t)in.in[k];
+      }
+      for (int k = 0; k < 2; k++) d.out[k] = (int16_t)in.out[k];
+      d.p = in.p; d.aux0 = in.aux[0]; d.aux1 = (int16_t)in.aux[1]; d.aux2 = (int16_t)in.aux[2];
+      g.dev_code.push_back(d);
+    }
+    CUDA_TRY(cudaMalloc(&g.d_code, std::max<size_t>(g.dev_code.size(), 1) * sizeof(DuspDevInstr)));
+    CUDA_TRY(cudaMemcpy(g.d_code, g.dev_code.data(), g.dev_code.size() * sizeof(DuspDevInstr), cudaMemcpyHostToDevice));
+    {
+      // Tile shape: T time-lanes per voice so that the batch still fills the GPU (>= 8 warps per SM);
+      // B samples per lane.  DUSP_TILE="B,T" overrides (experiments).
+      const int choices[4] = {1, 4, 16, 32};
+      int T = 32;
+      for (int t : choices) if (((long long)voices[i] + (32 / t) - 1) / (32 / t) >= 148 * 8) { T = t; break; }
+      int B = T == 32 ? 8 : 16;
+      if (const char *env = getenv("DUSP_TILE")) { int b = 0, t = 0; if (sscanf(env, "%d,%d", &b, &t) == 2) { B = b; T = t; } }
+      if ((size_t)g.prog.n_slots * B * 128 > 200 * 1024 && T == 1) B = 8;
+      if (!dusp_launch_supported(B, T)) return fail(DUSP_EINVAL, "unsupported tile shape (DUSP_TILE)");
+      if ((size_t)g.prog.n_slots * B * 128 > 220 * 1024)
+        return fail(DUSP_EUNSUPPORTED, "circuit needs more live signal slots than shared memory holds");
+      const long long n_warps = ((long long)voices[i] + (32 / T) - 1) / (32 / T);
+      int wpc = n_warps >= 148 * 16 ? 4 : 1;
+      while (wpc > 1 && (size_t)g.prog.n_slots * B * 128 * wpc > 100 * 1024) wpc >>= 1;
+      g.sub_block = B; g.time_lanes = T; g.warps_per_cta = wpc;
+    }
     CUDA_TRY(cudaMalloc(&g.d_words, g.h_words.size() * sizeof(double)));
     const size_t ring_bytes = (size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad * sizeof(float);
     if (cudaMalloc(&g.d_rings, ring_bytes) != cudaSuccess) {
@@ -230,14 +270,17 @@ int dusp_session_set_params(dusp_session *s, int gi, const int *ids, int n_ids, 
       const double x = values[(size_t)v * n_ids + k];
       g.h_words[(size_t)ids[k] * g.nv_pad + v] = p.f32 ? (double)(float)x : x;
     }
-  if (!g.prog.tap_pairs.empty()) {  // per-voice CircleBuffer offsets must keep the reordering proof (compile.cc)
+  if (!g.prog.tap_pairs.empty() || !g.prog.locked.empty()) {
+    // per-voice values must keep what the compiler proved / specialised on (compile.cc)
     std::vector<double> wv(nw);
     for (int v = 0; v < g.n_voices; v++) {
       for (int w = 0; w < nw; w++) wv[w] = g.h_words[(size_t)w * g.nv_pad + v];
       std::string msg = g.prog.check_taps(wv.data());
+      if (msg.empty()) msg = g.prog.check_locked(wv.data());
       if (!msg.empty()) return fail(DUSP_EUNSUPPORTED, "voice " + std::to_string(v) + ": " + msg);
     }
   }
+  for (int v = 0; v < g.n_voices; v++) derive_words(g.prog, g.h_words.data() + v, g.nv_pad);
   g.dirty = true;
   s->clock = 0;
   return DUSP_OK;
@@ -250,27 +293,10 @@ int dusp_session_reset(dusp_session *s) {
   return DUSP_OK;
 }
 
-int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, float *out_host, float *out_device,
-                        void *cuda_stream) {
-  if (!s || n_samples < 0 || (out_mode != DUSP_OUT_VOICES && out_mode != DUSP_OUT_MIX) || (!out_host == !out_device))
-    return fail(DUSP_EINVAL, "dusp_session_render: bad arguments");
-  if (s->clock % DUSP_CHUNK) return fail(DUSP_EINVAL, "dusp_session_render: a previous render ended inside a chunk");
-  CUDA_TRY(cudaSetDevice(s->device));
-  cudaStream_t st = (cudaStream_t)cuda_stream;
-  const size_t out_floats = (out_mode == DUSP_OUT_VOICES ? (size_t)s->n_voices * s->out_nch : 2) * (size_t)n_samples;
-  float *d_out = out_device;
-  if (out_host) {
-    if (s->staging_floats < out_floats) {
-      cudaFree(s->d_staging); s->d_staging = nullptr; s->staging_floats = 0;
-      if (cudaMalloc(&s->d_staging, std::max<size_t>(out_floats, 1) * sizeof(float)) != cudaSuccess) {
-        cudaGetLastError();
-        return fail(DUSP_ENOMEM, "output does not fit on the device: render in shorter time blocks");
-      }
-      s->staging_floats = out_floats;
-    }
-    d_out = s->d_staging;
-  }
-  if (n_samples == 0) return DUSP_OK;
+// Enqueue the kernels that render the next `n` samples of every group into
+// d_out (row length `n`) on stream `st`.
+static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_out, cudaStream_t st) {
+  const size_t out_floats = (out_mode == DUSP_OUT_VOICES ? (size_t)s->n_voices * s->out_nch : 2) * (size_t)n;
   // channels a group does not produce (and the mix accumulator) start at zero
   bool need_zero = out_mode == DUSP_OUT_MIX;
   for (auto &g : s->groups) if (g.prog.out_nch != s->out_nch) need_zero = true;
@@ -284,28 +310,73 @@ int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, floa
     }
     DuspKernelParams kp;
     memset(&kp, 0, sizeof kp);
-    kp.prog = g.d_code; kp.n_instr = (int)g.prog.code.size(); kp.n_slots = g.prog.n_slots;
+    kp.prog_global = g.d_code; kp.n_instr = (int)g.dev_code.size(); kp.n_slots = g.prog.n_slots;
+    kp.use_inline = g.dev_code.size() <= DUSP_INLINE_INSTR;
+    if (kp.use_inline) memcpy(kp.prog_inline, g.dev_code.data(), g.dev_code.size() * sizeof(DuspDevInstr));
     kp.n_voices = g.n_voices; kp.voice0 = g.voice0; kp.nv_stride = g.nv_pad;
     kp.words = g.d_words; kp.rings = g.d_rings; kp.ring_stride = std::max<long long>(g.prog.ring_floats, 4);
     kp.ring_tab = g.d_ringtab; kp.stale = g.d_stale; kp.n_stale = g.prog.n_stale; kp.tables = s->d_tables;
     kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = g.prog.out_nch; kp.out_mode = out_mode;
-    kp.out_len = n_samples; kp.clock0 = s->clock; kp.n_samples = n_samples;
-    const int n_warps = (g.n_voices + 31) / 32;
-    int wpc = n_warps >= 148 * 16 ? 4 : 1;
-    const size_t per_warp = (size_t)g.prog.n_slots * s->sub_block * 32 * sizeof(float);
-    while (wpc > 1 && per_warp * wpc > 200 * 1024) wpc >>= 1;
-    if (per_warp > 220 * 1024) return fail(DUSP_EUNSUPPORTED, "circuit needs more live signal slots than shared memory holds");
+    kp.out_len = n; kp.clock0 = s->clock; kp.n_samples = n;
+    const int wpc = g.warps_per_cta;
     int grid = 0, smem = 0;
-    int e = dusp_launch_render(&kp, s->sub_block, wpc, st, &grid, &smem);
+    int e = dusp_launch_render(&kp, g.sub_block, g.time_lanes, wpc, st, &grid, &smem);
     if (e != 0) return fail(DUSP_ECUDA, std::string("render launch: ") + cudaGetErrorString((cudaError_t)e));
     s->launches++;
     s->last_grid = grid; s->last_block = wpc * 32; s->last_smem = smem;
   }
-  s->clock += (n_samples + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;
-  if (out_host) {
-    CUDA_TRY(cudaMemcpyAsync(out_host, d_out, out_floats * sizeof(float), cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
+  s->clock += (n + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;
+  return DUSP_OK;
+}
+
+int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, float *out_host, float *out_device,
+                        void *cuda_stream) {
+  if (!s || n_samples < 0 || (out_mode != DUSP_OUT_VOICES && out_mode != DUSP_OUT_MIX) || (!out_host == !out_device))
+    return fail(DUSP_EINVAL, "dusp_session_render: bad arguments");
+  if (s->clock % DUSP_CHUNK) return fail(DUSP_EINVAL, "dusp_session_render: a previous render ended inside a chunk");
+  CUDA_TRY(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  if (n_samples == 0) return DUSP_OK;
+  if (out_device) return enqueue_block(s, n_samples, out_mode, out_device, st);
+
+  // Host output: render time blocks into two device staging buffers and drain each
+  // over PCIe on a second stream while the next block renders.
+  const size_t rows = out_mode == DUSP_OUT_VOICES ? (size_t)s->n_voices * s->out_nch : 2;
+  long long blk = (long long)((256u << 20) / (rows * sizeof(float)));  // ~256 MB per staging buffer
+  blk = std::max<long long>(DUSP_CHUNK, blk / DUSP_CHUNK * DUSP_CHUNK);
+  blk = std::min<long long>(blk, (n_samples + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK);
+  const size_t need = rows * (size_t)blk;
+  if (s->staging_floats < need) {
+    for (int i = 0; i < 2; i++) { cudaFree(s->d_staging[i]); s->d_staging[i] = nullptr; }
+    s->staging_floats = 0;
+    for (int i = 0; i < 2; i++)
+      if (cudaMalloc(&s->d_staging[i], need * sizeof(float)) != cudaSuccess) {
+        cudaGetLastError();
+        return fail(DUSP_ENOMEM, "not enough device memory for the output staging blocks");
+      }
+    s->staging_floats = need;
   }
+  if (!s->copy_stream) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) {
+      CUDA_TRY(cudaEventCreateWithFlags(&s->ev_rendered[i], cudaEventDisableTiming));
+      CUDA_TRY(cudaEventCreateWithFlags(&s->ev_copied[i], cudaEventDisableTiming));
+    }
+  }
+  int i = 0;
+  for (long long t = 0; t < n_samples; t += blk, i ^= 1) {
+    const long long n = std::min(blk, n_samples - t);
+    CUDA_TRY(cudaStreamWaitEvent(st, s->ev_copied[i], 0));  // buffer i drained (no-op the first time)
+    int rc = enqueue_block(s, n, out_mode, s->d_staging[i], st);
+    if (rc != DUSP_OK) return rc;
+    CUDA_TRY(cudaEventRecord(s->ev_rendered[i], st));
+    CUDA_TRY(cudaStreamWaitEvent(s->copy_stream, s->ev_rendered[i], 0));
+    CUDA_TRY(cudaMemcpy2DAsync(out_host + t, (size_t)n_samples * sizeof(float), s->d_staging[i], (size_t)n * sizeof(float),
+                               (size_t)n * sizeof(float), rows, cudaMemcpyDeviceToHost, s->copy_stream));
+    CUDA_TRY(cudaEventRecord(s->ev_copied[i], s->copy_stream));
+  }
+  CUDA_TRY(cudaStreamSynchronize(s->copy_stream));
+  CUDA_TRY(cudaStreamSynchronize(st));
   return DUSP_OK;
 }
 

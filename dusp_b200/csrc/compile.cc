@@ -35,7 +35,7 @@ const char *OP_NAMES[OP_COUNT] = {
     "nop", "copy", "neg", "abs", "s2s", "semi", "db2s", "midi2f", "fixmul", "mul", "div", "pow", "add", "sub",
     "gain", "clip", "hca", "hcb", "rescale", "xfade", "pan", "vecmag", "osc", "mcosc", "ramp", "shape", "ahd",
     "timer", "noise", "filter", "fixdelay", "comb", "allpass", "delay", "monodelay", "readback", "cbwrite",
-    "cbread", "ldstale", "ststale", "out"};
+    "cbread", "ldstale", "ststale", "out", "filterc", "panc", "gainc", "noise1", "cbwritec", "cbreadc"};
 
 struct Opnd {
   int kind = 0;  // 0 none (reads 0), 1 value, 2 const word
@@ -276,6 +276,11 @@ Program compile(const Graph &g) {
       need_in(1);
       if (b.nch[ui][0] != 1) throw Unsupported("multi-channel Noise shares one phase across channels chunk by chunk (Noise.js:17-27)");
       IR &r = b.emit(OP_NOISE, ui, 0); r.in[0] = b.in_ref(ui, 0, 0);
+      // constant F >= sampleRate with phase 0: `phase += f` crosses the threshold on every sample (Noise.js:21-24)
+      if (r.in[0].kind == 2 && (float)b.prog.words[r.in[0].id].dflt >= (float)DUSP_SR && u.num("phase", 0) == 0) {
+        r.op = OP_NOISE1;
+        b.prog.locked.push_back({r.in[0].id, (double)DUSP_SR, INFINITY});
+      }
       r.p = b.word(un + ".phase", u.num("phase", 0), false);
       b.word(un + ".y", u.num("y", 0), false);
       b.word(un + ".draw", u.num("draw", 1), false);
@@ -289,10 +294,20 @@ Program compile(const Graph &g) {
       for (int c = 0; c < inn(0); c++) {
         IR &r = b.emit(OP_FILTER, ui, c); r.in[0] = b.in_ref(ui, 0, c); r.in[1] = b.in_ref(ui, 1, 0);
         std::string s = "[" + std::to_string(c) + "]";
-        const char *names[11] = {"a0", "a1", "a2", "b1", "b2", "lastF", "lastFdefined", "x1", "x2", "y1", "y2"};
-        for (int w = 0; w < 11; w++) {
-          int id = b.word(un + "." + names[w] + s, w < 5 ? NAN : 0.0, false);
-          if (w == 0) r.p = id;
+        if (r.in[1].kind == 2) {  // constant F: coefficients are a pure function of f (Filter.js:66-84)
+          r.op = OP_FILTERC;
+          const char *names[9] = {"~a0", "~a1", "~a2", "~b1", "~b2", "x1", "x2", "y1", "y2"};
+          for (int w = 0; w < 9; w++) {
+            int id = b.word(un + "." + names[w] + s, 0.0, false);
+            if (w == 0) r.p = id;
+          }
+          b.prog.derived.push_back({kind == "HP" ? DV_FILTER_HP : DV_FILTER_LP, r.p, r.in[1].id, -1, 0, 0});
+        } else {
+          const char *names[11] = {"a0", "a1", "a2", "b1", "b2", "lastF", "lastFdefined", "x1", "x2", "y1", "y2"};
+          for (int w = 0; w < 11; w++) {
+            int id = b.word(un + "." + names[w] + s, w < 5 ? NAN : 0.0, false);
+            if (w == 0) r.p = id;
+          }
         }
         r.aux[0] = kind == "HP";
         b.def(r, 0, ui, 0, c);
@@ -312,7 +327,15 @@ Program compile(const Graph &g) {
       }
     } else if (k == "Gain") {
       need_in(2);
-      for (int c = 0; c < inn(0); c++) { IR &r = b.emit(OP_GAIN, ui, c); r.in[0] = b.in_ref(ui, 0, c); r.in[1] = b.in_ref(ui, 1, 0); b.def(r, 0, ui, 0, c); }
+      for (int c = 0; c < inn(0); c++) {
+        IR &r = b.emit(OP_GAIN, ui, c); r.in[0] = b.in_ref(ui, 0, c); r.in[1] = b.in_ref(ui, 1, 0);
+        if (r.in[1].kind == 2) {  // constant GAIN: 10^(gain/20) once per voice
+          r.op = OP_GAINC;
+          r.p = b.word(un + ".~scale[" + std::to_string(c) + "]", 1.0, false);
+          b.prog.derived.push_back({DV_GAIN, r.p, r.in[1].id, -1, 0, 0});
+        }
+        b.def(r, 0, ui, 0, c);
+      }
     } else if (k == "PolarityInvert") unary(OP_NEG);
     else if (k == "Abs") unary(OP_ABS);
     else if (k == "Repeater") unary(OP_COPY);
@@ -336,7 +359,16 @@ Program compile(const Graph &g) {
     } else if (k == "Pan") {
       need_in(2);
       IR &r = b.emit(OP_PAN, ui, 0); r.in[0] = b.in_ref(ui, 0, 0); r.in[1] = b.in_ref(ui, 1, 0);
-      r.p = b.word(un + ".compensationDB", u.num("compensationDB", 1.5), false);
+      if (r.in[1].kind == 2) {  // constant PAN: (1-pan), (1+pan) and the dB compensation once per voice
+        r.op = OP_PANC;
+        r.p = b.word(un + ".~left", 0, false);
+        b.word(un + ".~right", 0, false);
+        b.word(un + ".~compensation", 0, false);
+        int cdb = b.word(un + ".compensationDB", u.num("compensationDB", 1.5), false);
+        b.prog.derived.push_back({DV_PAN, r.p, r.in[1].id, cdb, 0, 0});
+      } else {
+        r.p = b.word(un + ".compensationDB", u.num("compensationDB", 1.5), false);
+      }
       b.def(r, 0, ui, 0, 0); b.def(r, 1, ui, 0, 1);
     } else if (k == "FixedMultiply") {
       need_in(1);
@@ -405,6 +437,11 @@ Program compile(const Graph &g) {
         if (writer) r.in[1] = b.in_ref(ui, ii, c);  // `if(this.in[c])`: absent channel -> no mix
         r.p = b.word(un + ".t[" + std::to_string(c) + "]", u.num("t", 0), false);
         r.aux[0] = cb_ring[{bi, c}];
+        if (r.in[0].kind == 2) {  // constant OFFSET: the ring index just advances by one per sample
+          r.op = writer ? OP_CBWRITEC : OP_CBREADC;
+          int idx = b.word(un + ".~index[" + std::to_string(c) + "]", 0, false);
+          b.prog.derived.push_back({DV_CBIDX, idx, r.p, r.in[0].id, writer ? 1.0 : -1.0, (double)g.cbs[bi].len});
+        }
         r.aux[1] = (int)u.num(writer ? "preWipe" : "postWipe", 0);
         r.root = writer || r.aux[1];
         if (!writer) b.def(r, 0, ui, 0, c);
@@ -583,6 +620,58 @@ std::string Program::check_taps(const double *wv) const {
     d = std::min(d, (double)t.ring_len - d);
     if (d != 0 && d < DUSP_CHUNK)
       return "CircleBuffer taps closer than one 256-sample chunk (intra-chunk ordering differs from the reference)";
+  }
+  return "";
+}
+
+// Host evaluation of the per-voice words that depend only on other per-voice constants.  Same
+// formulas and the same libm calls as the reference's Math.* (and as the oracle), evaluated in double.
+void derive_words(const Program &p, double *w, long long stride) {
+  auto W = [&](int i) -> double & { return w[(long long)i * stride]; };
+  for (const Derived &d : p.derived) {
+    switch (d.kind) {
+      case DV_FILTER_LP: {  // Filter.js:67-75
+        const double f = (double)(float)W(d.src0);
+        const double lamda = 1 / std::tan(M_PI * f / DUSP_SR), l2 = lamda * lamda;
+        const double a0 = 1 / (1 + 2 * lamda + l2);
+        W(d.dst) = a0; W(d.dst + 1) = 2 * a0; W(d.dst + 2) = a0;
+        W(d.dst + 3) = 2 * a0 * (1 - l2); W(d.dst + 4) = a0 * (1 - 2 * lamda + l2);
+        break;
+      }
+      case DV_FILTER_HP: {  // Filter.js:76-84
+        const double f = (double)(float)W(d.src0);
+        const double lamda = std::tan(M_PI * f / DUSP_SR), l2 = lamda * lamda;
+        const double a0 = 1 / (1 + 2 * lamda + l2);
+        W(d.dst) = a0; W(d.dst + 1) = 0; W(d.dst + 2) = -a0;
+        W(d.dst + 3) = 2 * a0 * (l2 - 1); W(d.dst + 4) = a0 * (1 - 2 * lamda + l2);
+        break;
+      }
+      case DV_PAN: {  // Pan.js:20-22
+        const double pan = (double)(float)W(d.src0), cdb = W(d.src1);
+        W(d.dst) = 1 - pan; W(d.dst + 1) = 1 + pan;
+        W(d.dst + 2) = std::pow(10, ((1 - std::fabs(pan)) * cdb) / 20);
+        break;
+      }
+      case DV_GAIN:  // Gain.js:26-28
+        W(d.dst) = std::pow(10, (double)(float)W(d.src0) / 20);
+        break;
+      case DV_CBIDX: {  // CircleBuffer.js:17-20 applied to the unit's first access (sample 0)
+        const double t = W(d.src0) + d.aux0 * ((double)DUSP_SR * (double)(float)W(d.src1));
+        double i = std::floor(std::fmod(t, d.aux1));
+        if (i < 0) i += d.aux1;
+        W(d.dst) = (i == i && i >= 0 && i < d.aux1) ? i : -1.0;  // -1: never a valid index (NaN / Infinity offset)
+        break;
+      }
+    }
+  }
+}
+
+std::string Program::check_locked(const double *wv) const {
+  for (auto &l : locked) {
+    const float v = (float)wv[l.word];
+    if (!(v >= (float)l.lo && v <= (float)l.hi))
+      return "parameter " + words[l.word].name + " was specialised at compile time and must stay in [" +
+             std::to_string(l.lo) + ", " + std::to_string(l.hi) + "]";
   }
   return "";
 }

@@ -28,6 +28,16 @@ struct TapPair {
   long long ring_len;
 };
 
+// A word whose initial value is a function of other (user-settable) words of the same voice.
+enum DerivedKind { DV_FILTER_LP, DV_FILTER_HP, DV_PAN, DV_GAIN, DV_CBIDX };
+struct Derived {
+  int kind;
+  int dst;          // first destination word
+  int src0, src1;   // source words (-1 = unused)
+  double aux0;      // DV_CBIDX: +1 writer / -1 reader;  aux1: ring length
+  double aux1;
+};
+
 struct Program {
   std::vector<DuspInstr> code;
   std::vector<Param> words;     // per-voice words: parameters and unit state, in instruction order
@@ -39,12 +49,17 @@ struct Program {
   int n_units = 0;              // units the reference ticks per chunk (metric: unit-samples)
   double ring_bytes_per_sample = 0;  // SURVEY 8d accounting
   std::vector<TapPair> tap_pairs;
+  std::vector<Derived> derived;
+  struct Locked { int word; double lo, hi; };
+  std::vector<Locked> locked;  // constants a specialised op relies on: per-voice overrides must stay in range
+  std::string check_locked(const double *word_values) const;
   // returns "" if the offsets (one value per word, as the voice will see them) are admissible
   std::string check_taps(const double *word_values) const;
   std::string listing() const;
 };
 
 Program compile(const Graph &g);
+void derive_words(const Program &p, double *words, long long stride);  // words[i*stride] = word i of one voice
 const char *op_name(int op);
 
 }  // namespace dusp

@@ -4,18 +4,26 @@
 // every expression in IEEE double with a rounding after each operation and
 // rounds to binary32 only on the store into a Float32Array.
 //
-// Execution model ("lane = voice"):
-//   * one warp owns 32 voices for the whole render; a lane walks its voice
-//     forward in time, so every stateful unit (phase accumulators, biquads,
-//     delay lines) sees exactly the reference's sequential order -> bit-exact;
-//   * time is cut into sub-blocks of B samples.  For each sub-block the warp
-//     runs the program's instructions in tick order; an instruction processes
-//     B samples of all 32 voices.  Slots (the SignalChunk replacement) live in
-//     shared memory as [slot][sample][lane]: every access is bank-conflict free;
-//   * unit state and parameters live in HBM/L2 as f64 words [word][voice]
-//     (coalesced across the warp), delay lines as per-voice rings in HBM;
-//   * the rendered outlet is stored to HBM with the reference's `x || 0`.
-// Warps never communicate, so there is no block-level synchronisation at all.
+// Execution model: a warp renders a TILE of V voices x T time-lanes (V*T = 32).
+// Lane (vi, tl) walks B consecutive samples of voice vi; the T lanes of a voice
+// cover T*B consecutive samples (T*B divides the reference's 256-sample chunk).
+//   * T = 1 ("lane = voice"): every stateful unit runs in exactly the
+//     reference's sequential order.  Used when the batch alone fills the GPU.
+//   * T > 1: the batch has too few voices to fill 148 SMs, so time is spread
+//     across lanes as well.  Stateless units are unchanged.  Phase accumulators
+//     (Osc, Ramp, Noise draws, ring indices) become an exclusive warp-shuffle
+//     scan of per-lane partial sums -- exact whenever the f64 partial sums are
+//     exact, which holds for f32 increments of audio-range magnitude.  The biquad
+//     splits into a parallel feed-forward part and a short serial recurrence that
+//     the T lanes run in turn, handing (y1, y2) on by shuffle: same operations in
+//     the same order as the reference, so still bit-exact.  Units with no safe
+//     parallel form run lane after lane ("serial turns").
+//   * Slots (the SignalChunk replacement) live in shared memory as
+//     [slot][B/4][lane] float4: every access is a conflict-free LDS.128/STS.128.
+//   * Unit state and parameters are f64 words [word][voice] in HBM/L2; delay
+//     lines are per-voice rings in HBM; the rendered outlet goes to HBM with the
+//     reference's `x || 0`.
+// Warps never communicate with each other: no block-level synchronisation.
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -43,6 +51,15 @@ __device__ __forceinline__ double fmod_sr(double x) {
   }
   return fmod(x, SRD);
 }
+// x mod 44100 in [0, 44100) for |x| < 2^40: exact quotient correction with one fma
+__device__ __forceinline__ double posmod_sr(double x) {
+  if (!(fabs(x) < 1.0e12)) { x = fmod(x, SRD); return x < 0.0 ? x + SRD : x; }
+  const double q = floor(x / SRD);
+  double r = fma(-q, SRD, x);
+  if (r < 0.0) r += SRD;
+  if (r >= SRD) r -= SRD;
+  return r;
+}
 
 // typed-array read `table[i]` with a double index: out of range / NaN -> undefined -> NaN
 __device__ __forceinline__ double tab_read(const float *__restrict__ tab, double idx) {
@@ -65,14 +82,19 @@ __device__ __forceinline__ double rand53(uint64_t seed, uint64_t k) {
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
   z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
   z ^= z >> 31;
-  return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+  z >>= 11;  // 53 bits; hi 21 + lo 32 recombined exactly with one fma (cheaper than a u64 -> f64 convert)
+  return fma((double)(uint32_t)(z >> 32), 4294967296.0, (double)(uint32_t)z) * (1.0 / 9007199254740992.0);
 }
 
-template <int B>
+__device__ __forceinline__ double shfl_d(double x, int src) { return __shfl_sync(0xffffffffu, x, src); }
+
+template <int B, int T>
 struct Lane {
-  float *S;              // this lane's column of the warp's slot array: slot k, sample s -> S[(k*B+s)*32]
+  float4 *S;             // this lane's column of the warp's slot array: slot k, quad q -> S[(k*(B/4)+q)*32]
   double *W;             // this voice's words: word w -> W[w * nv]
-  long long nv;
+  unsigned nv;
+  int tl;                // time-lane 0..T-1
+  int lane;
   float *rings;          // this voice's ring arena
   const DuspRing *ring_tab;
   float *stale;          // this voice's stale buffers [k][256]
@@ -80,39 +102,68 @@ struct Lane {
 
   __device__ __forceinline__ void ld(float (&x)[B], int ref) const {
     if (ref >= 0) {
+      const float4 *s = S + ref * (B / 4) * 32;
 #pragma unroll
-      for (int s = 0; s < B; s++) x[s] = S[(ref * B + s) * 32];
+      for (int q = 0; q < B / 4; q++) {
+        const float4 v = s[q * 32];
+        x[4 * q] = v.x; x[4 * q + 1] = v.y; x[4 * q + 2] = v.z; x[4 * q + 3] = v.w;
+      }
     } else {
-      float c = ref == REF_NONE ? 0.0f : (float)W[(long long)(REF_CONST_BASE - ref) * nv];
+      const float c = ref == REF_NONE ? 0.0f : (float)W[(size_t)((unsigned)(REF_CONST_BASE - ref) * nv)];
 #pragma unroll
       for (int s = 0; s < B; s++) x[s] = c;
     }
   }
   __device__ __forceinline__ void st(const float (&x)[B], int ref) const {
     if (ref >= 0) {
+      float4 *s = S + ref * (B / 4) * 32;
 #pragma unroll
-      for (int s = 0; s < B; s++) S[(ref * B + s) * 32] = x[s];
+      for (int q = 0; q < B / 4; q++) s[q * 32] = make_float4(x[4 * q], x[4 * q + 1], x[4 * q + 2], x[4 * q + 3]);
     }
   }
-  __device__ __forceinline__ double &w(int p) const { return W[(long long)p * nv]; }
-  __device__ __forceinline__ float *ring(int r, double &len) const {
-    DuspRing rt = ring_tab[r];
-    len = (double)rt.length;
+  __device__ __forceinline__ double &w(int p) const { return W[(size_t)((unsigned)p * nv)]; }
+  __device__ __forceinline__ float *ring(int r, long long &len) const {
+    const DuspRing rt = ring_tab[r];
+    len = rt.length;
     return rings + rt.offset;
   }
+  // source lane of time-lane `t` of this lane's voice
+  __device__ __forceinline__ int peer(int t) const { return (lane & ~(T - 1)) | t; }
+  // exclusive prefix sum over the T time-lanes of a voice (exact when the adds are exact)
+  __device__ __forceinline__ double excl_scan(double x) const {
+    double incl = x;
+#pragma unroll
+    for (int o = 1; o < T; o <<= 1) {
+      const double y = __shfl_up_sync(0xffffffffu, incl, o, T);
+      if (tl >= o) incl += y;
+    }
+    const double up = __shfl_up_sync(0xffffffffu, incl, 1, T);
+    return tl == 0 ? 0.0 : up;
+  }
+  // serial turns: the T lanes of every voice run `body` one after the other (exact sequential order)
+  template <typename F>
+  __device__ __forceinline__ void serial(F body) const {
+    if (T == 1) { body(); return; }
+#pragma unroll 1
+    for (int turn = 0; turn < T; turn++) {
+      if (tl == turn) body();
+      __syncwarp();
+    }
+  }
+  __device__ __forceinline__ void sync() const { if (T > 1) __syncwarp(); }
 };
 
 // ------------------------------------------------------------ stateless ops
-template <int B, typename F>
-__device__ __forceinline__ void map1(const Lane<B> &L, const DuspInstr &I, F f) {
+template <int B, int T, typename F>
+__device__ __forceinline__ void map1(const Lane<B, T> &L, const DuspDevInstr &I, F f) {
   float a[B];
   L.ld(a, I.in[0]);
 #pragma unroll
   for (int s = 0; s < B; s++) a[s] = f(a[s]);
   L.st(a, I.out[0]);
 }
-template <int B, typename F>
-__device__ __forceinline__ void map2(const Lane<B> &L, const DuspInstr &I, F f) {
+template <int B, int T, typename F>
+__device__ __forceinline__ void map2(const Lane<B, T> &L, const DuspDevInstr &I, F f) {
   float a[B], b[B];
   L.ld(a, I.in[0]);
   L.ld(b, I.in[1]);
@@ -124,29 +175,76 @@ __device__ __forceinline__ void map2(const Lane<B> &L, const DuspInstr &I, F f) 
 __device__ __forceinline__ double dB(double db) { return pow(10.0, db / 20.0); }  // Gain.js:26-28
 
 // ------------------------------------------------------------- stateful ops
-template <int B>
-__device__ __forceinline__ void op_osc(const Lane<B> &L, const DuspInstr &I, bool negfix) {  // Osc.js:35-47
-  float f[B];
-  L.ld(f, I.in[0]);
-  const float *tab = L.tables + (size_t)I.aux[0] * DUSP_TABLE_LEN;
-  double ph = L.w(I.p);
+// Osc.js:35-47.  negfix=false is MultiChannelOsc.js:21-38 (its truncated-modulo phase has no canonical
+// range, so it only runs in sequential order).
+template <int B, int T>
+__device__ __forceinline__ void osc_body(const Lane<B, T> &L, const DuspDevInstr &I, float (&f)[B], double &ph, bool negfix) {
+  const float *tab = L.tables + (size_t)I.aux0 * DUSP_TABLE_LEN;
 #pragma unroll
   for (int s = 0; s < B; s++) {
     ph += (double)f[s];
     ph = fmod_sr(ph);
     if (negfix && ph < 0.0) ph += SRD;
-    double fl = floor(ph), ce = ceil(ph);
-    double fr = ph - trunc(ph);  // phase % 1
-    f[s] = (float)(tab_read(tab, fl) * (1.0 - fr) + tab_read(tab, ce) * fr);
+    if (ph >= 0.0 && ph < SRD) {  // the only reachable case for Osc unless f is NaN / Infinity
+      const int i = __double2int_rz(ph);
+      const double fr = ph - (double)i;  // phase % 1
+      const double a = (double)__ldg(tab + i), b = (double)__ldg(tab + i + (fr != 0.0));  // floor / ceil entries
+      f[s] = (float)(a * (1.0 - fr) + b * fr);
+    } else {
+      const double fl = floor(ph), ce = ceil(ph), fr = ph - trunc(ph);
+      f[s] = (float)(tab_read(tab, fl) * (1.0 - fr) + tab_read(tab, ce) * fr);
+    }
   }
-  L.w(I.p) = ph;
+}
+
+template <int B, int T>
+__device__ __forceinline__ void op_osc(const Lane<B, T> &L, const DuspDevInstr &I) {
+  float f[B];
+  L.ld(f, I.in[0]);
+  double ph = L.w(I.p);
+  if (T > 1) {
+    // phase at this lane's first sample = (phase + sum of all earlier increments) mod 44100
+    double sum = 0.0;
+#pragma unroll
+    for (int s = 0; s < B; s++) sum += (double)f[s];
+    const double before = L.excl_scan(sum);
+    const bool finite = __all_sync(0xffffffffu, fabs(before + sum) < 1.0e12);
+    if (!finite) {  // NaN / Infinity frequencies: keep the reference's exact sequential behaviour
+      L.serial([&] { double p2 = L.w(I.p); osc_body<B, T>(L, I, f, p2, true); L.w(I.p) = p2; });
+      L.st(f, I.out[0]);
+      return;
+    }
+    if (L.tl > 0) ph = posmod_sr(ph + before);
+  }
+  osc_body<B, T>(L, I, f, ph, true);
+  L.sync();
+  if (L.tl == T - 1) L.w(I.p) = ph;
   L.st(f, I.out[0]);
 }
 
-template <int B>
-__device__ __forceinline__ void op_ramp(const Lane<B> &L, const DuspInstr &I) {  // Ramp.js:25-40
+template <int B, int T>
+__device__ __forceinline__ void op_mcosc(const Lane<B, T> &L, const DuspDevInstr &I) {
+  float f[B];
+  L.ld(f, I.in[0]);
+  L.serial([&] { double ph = L.w(I.p); osc_body<B, T>(L, I, f, ph, false); L.w(I.p) = ph; });
+  L.st(f, I.out[0]);
+}
+
+template <int B, int T>
+__device__ __forceinline__ void op_ramp(const Lane<B, T> &L, const DuspDevInstr &I) {  // Ramp.js:25-40
   double t = L.w(I.p), playing = L.w(I.p + 1);
   const double dur = L.w(I.p + 2), y0 = L.w(I.p + 3), y1 = L.w(I.p + 4);
+  if (T > 1 && L.tl > 0 && playing != 0.0) {
+    // the tl*B steps before this lane's first sample: one literal step, then the closed form of
+    // "count up by one until t passes duration" (after the first step 0 <= t <= duration holds)
+    t += 1.0;
+    if (t > dur) { playing = 0.0; t = dur; }
+    if (t < 0.0) { playing = 0.0; t = 0.0; }
+    if (playing != 0.0) {
+      const double rem = (double)(L.tl * B - 1);
+      if (t + rem > dur) { t = dur; playing = 0.0; } else t += rem;
+    }
+  }
   float o[B];
 #pragma unroll
   for (int s = 0; s < B; s++) {
@@ -157,95 +255,115 @@ __device__ __forceinline__ void op_ramp(const Lane<B> &L, const DuspInstr &I) { 
     }
     o[s] = (float)(y0 + (t / dur) * (y1 - y0));
   }
-  L.w(I.p) = t;
-  L.w(I.p + 1) = playing;
+  L.sync();
+  if (L.tl == T - 1) { L.w(I.p) = t; L.w(I.p + 1) = playing; }
   L.st(o, I.out[0]);
 }
 
-template <int B>
-__device__ __forceinline__ void op_shape(const Lane<B> &L, const DuspInstr &I) {  // Shape/index.js:28-59
+template <int B, int T>
+__device__ __forceinline__ void op_shape(const Lane<B, T> &L, const DuspDevInstr &I) {  // Shape/index.js:28-59
   float d[B], mn[B], mx[B];
   L.ld(d, I.in[0]); L.ld(mn, I.in[1]); L.ld(mx, I.in[2]);
-  const float *tab = L.tables + (size_t)I.aux[0] * DUSP_TABLE_LEN;
-  double t = L.w(I.p);
+  const float *tab = L.tables + (size_t)I.aux0 * DUSP_TABLE_LEN;
   const double playing = L.w(I.p + 1);
-  const double le = (I.aux[1] & 1) ? (double)__ldg(tab) : L.w(I.p + 2);
-  const double re = (I.aux[1] & 2) ? (double)__ldg(tab + DUSP_SR) : L.w(I.p + 3);
+  const double le = (I.aux1 & 1) ? (double)__ldg(tab) : L.w(I.p + 2);
+  const double re = (I.aux1 & 2) ? (double)__ldg(tab + DUSP_SR) : L.w(I.p + 3);
+  L.serial([&] {  // t += 1/duration is an inexact f64 sum: keep the sequential order
+    double t = L.w(I.p);
 #pragma unroll
-  for (int s = 0; s < B; s++) {
-    if (playing != 0.0) t += 1.0 / (double)d[s];
-    const double lo = mn[s], hi = mx[s];
-    double y;
-    if (t <= 0.0) y = le * (hi - lo) + lo;
-    else if (t > SRD) y = re * (hi - lo) + lo;
-    else {
-      double fr = t - trunc(t);  // t % 1
-      y = lo + (hi - lo) * (tab_read(tab, ceil(t)) * fr + tab_read(tab, floor(t)) * (1.0 - fr));
+    for (int s = 0; s < B; s++) {
+      if (playing != 0.0) t += 1.0 / (double)d[s];
+      const double lo = mn[s], hi = mx[s];
+      double y;
+      if (t <= 0.0) y = le * (hi - lo) + lo;
+      else if (t > SRD) y = re * (hi - lo) + lo;
+      else {
+        const double fr = t - trunc(t);  // t % 1
+        y = lo + (hi - lo) * (tab_read(tab, ceil(t)) * fr + tab_read(tab, floor(t)) * (1.0 - fr));
+      }
+      d[s] = (float)y;
     }
-    d[s] = (float)y;
-  }
-  L.w(I.p) = t;
+    L.w(I.p) = t;
+  });
   L.st(d, I.out[0]);
 }
 
-template <int B>
-__device__ __forceinline__ void op_ahd(const Lane<B> &L, const DuspInstr &I) {  // AHD.js:35-76
+template <int B, int T>
+__device__ __forceinline__ void op_ahd(const Lane<B, T> &L, const DuspDevInstr &I) {  // AHD.js:35-76
   float a[B], h[B], d[B];
   L.ld(a, I.in[0]); L.ld(h, I.in[1]); L.ld(d, I.in[2]);
-  double t = L.w(I.p);
-  int state = (int)L.w(I.p + 1);
-  bool playing = L.w(I.p + 2) != 0.0;
-  const double sp = 1.0 / SRD;
+  L.serial([&] {
+    double t = L.w(I.p);
+    int state = (int)L.w(I.p + 1);
+    bool playing = L.w(I.p + 2) != 0.0;
+    const double sp = 1.0 / SRD;
 #pragma unroll
-  for (int s = 0; s < B; s++) {
-    float y = 0.0f;
-    if (state == 1) {
-      y = (float)t;
-      if (playing) { t += sp / (double)a[s]; if (t >= 1.0) { state++; t -= 1.0; } }
-    } else if (state == 2) {
-      y = 1.0f;
-      if (playing) { t += sp / (double)h[s]; if (t >= 1.0) { state++; t -= 1.0; } }
-    } else if (state == 3) {
-      y = (float)(1.0 - t);
-      if (playing) { t += sp / (double)d[s]; if (t >= 1.0) { state = 0; playing = false; } }
+    for (int s = 0; s < B; s++) {
+      float y = 0.0f;
+      if (state == 1) {
+        y = (float)t;
+        if (playing) { t += sp / (double)a[s]; if (t >= 1.0) { state++; t -= 1.0; } }
+      } else if (state == 2) {
+        y = 1.0f;
+        if (playing) { t += sp / (double)h[s]; if (t >= 1.0) { state++; t -= 1.0; } }
+      } else if (state == 3) {
+        y = (float)(1.0 - t);
+        if (playing) { t += sp / (double)d[s]; if (t >= 1.0) { state = 0; playing = false; } }
+      }
+      a[s] = y;
     }
-    a[s] = y;
-  }
-  L.w(I.p) = t;
-  L.w(I.p + 1) = (double)state;
-  L.w(I.p + 2) = playing ? 1.0 : 0.0;
+    L.w(I.p) = t; L.w(I.p + 1) = (double)state; L.w(I.p + 2) = playing ? 1.0 : 0.0;
+  });
   L.st(a, I.out[0]);
 }
 
-template <int B>
-__device__ __forceinline__ void op_timer(const Lane<B> &L, const DuspInstr &I) {  // Timer.js:37-42
-  double t = L.w(I.p);
-  const double sp = 1.0 / SRD;
+template <int B, int T>
+__device__ __forceinline__ void op_timer(const Lane<B, T> &L, const DuspDevInstr &I) {  // Timer.js:37-42
   float o[B];
+  L.serial([&] {
+    double t = L.w(I.p);
+    const double sp = 1.0 / SRD;
 #pragma unroll
-  for (int s = 0; s < B; s++) { t += sp; o[s] = (float)t; }
-  L.w(I.p) = t;
+    for (int s = 0; s < B; s++) { t += sp; o[s] = (float)t; }
+    L.w(I.p) = t;
+  });
   L.st(o, I.out[0]);
 }
 
-template <int B>
-__device__ __forceinline__ void op_noise(const Lane<B> &L, const DuspInstr &I) {  // Noise.js:16-28
+template <int B, int T>
+__device__ __forceinline__ void op_noise(const Lane<B, T> &L, const DuspDevInstr &I) {  // Noise.js:16-28
   float f[B];
   L.ld(f, I.in[0]);
-  double ph = L.w(I.p), y = L.w(I.p + 1), draw = L.w(I.p + 2);
   const uint64_t seed = (uint64_t)L.w(I.p + 3) | ((uint64_t)L.w(I.p + 4) << 32);
+  L.serial([&] {
+    double ph = L.w(I.p), y = L.w(I.p + 1), draw = L.w(I.p + 2);
 #pragma unroll
-  for (int s = 0; s < B; s++) {
-    ph += (double)f[s];
-    if (ph >= SRD) {
-      ph = 0.0;
-      y = 2.0 * rand53(seed, (uint64_t)draw) - 1.0;
-      draw += 1.0;
+    for (int s = 0; s < B; s++) {
+      ph += (double)f[s];
+      if (ph >= SRD) {
+        ph = 0.0;
+        y = 2.0 * rand53(seed, (uint64_t)draw) - 1.0;
+        draw += 1.0;
+      }
+      f[s] = (float)y;
     }
-    f[s] = (float)y;
-  }
-  L.w(I.p) = ph; L.w(I.p + 1) = y; L.w(I.p + 2) = draw;
+    L.w(I.p) = ph; L.w(I.p + 1) = y; L.w(I.p + 2) = draw;
+  });
   L.st(f, I.out[0]);
+}
+
+template <int B, int T>
+__device__ __forceinline__ void op_noise1(const Lane<B, T> &L, const DuspDevInstr &I) {  // Noise.js:16-28 with F >= sampleRate
+  const double draw = L.w(I.p + 2);
+  const uint64_t seed = (uint64_t)L.w(I.p + 3) | ((uint64_t)L.w(I.p + 4) << 32);
+  const uint64_t d0 = (uint64_t)draw + (uint64_t)(L.tl * B);  // counter-based stream: draws are independent
+  float o[B];
+  double y = 0.0;
+#pragma unroll
+  for (int s = 0; s < B; s++) { y = 2.0 * rand53(seed, d0 + s) - 1.0; o[s] = (float)y; }
+  L.sync();
+  if (L.tl == T - 1) { L.w(I.p + 1) = y; L.w(I.p + 2) = draw + (double)(T * B); }  // phase stays 0
+  L.st(o, I.out[0]);
 }
 
 // Filter.js:66-84
@@ -262,186 +380,314 @@ __device__ __forceinline__ void filter_coeffs(int hp, double f, double &a0, doub
   }
 }
 
-template <int B>
-__device__ __forceinline__ void op_filter(const Lane<B> &L, const DuspInstr &I) {  // Filter.js:27-51
+template <int B, int T>
+__device__ __forceinline__ void op_filter(const Lane<B, T> &L, const DuspDevInstr &I) {  // Filter.js:27-51
   float x[B], f[B];
   L.ld(x, I.in[0]); L.ld(f, I.in[1]);
   const int p = I.p;
-  double a0 = L.w(p), a1 = L.w(p + 1), a2 = L.w(p + 2), b1 = L.w(p + 3), b2 = L.w(p + 4);
-  double lastf = L.w(p + 5);
-  bool lastdef = L.w(p + 6) != 0.0;
-  double x1 = L.w(p + 7), x2 = L.w(p + 8), y1 = L.w(p + 9), y2 = L.w(p + 10);
+  L.serial([&] {
+    double a0 = L.w(p), a1 = L.w(p + 1), a2 = L.w(p + 2), b1 = L.w(p + 3), b2 = L.w(p + 4);
+    double lastf = L.w(p + 5);
+    bool lastdef = L.w(p + 6) != 0.0;
+    double x1 = L.w(p + 7), x2 = L.w(p + 8), y1 = L.w(p + 9), y2 = L.w(p + 10);
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      const double ft = f[s];
+      if (!lastdef || ft != lastf) { lastdef = true; lastf = ft; filter_coeffs(I.aux0, ft, a0, a1, a2, b1, b2); }
+      const double xin = x[s];
+      const double y = a0 * xin + a1 * js_or0(x1) + a2 * js_or0(x2) - b1 * js_or0(y1) - b2 * js_or0(y2);
+      const float yf = (float)y;
+      x[s] = yf;
+      y2 = js_or0(y1); y1 = (double)yf; x2 = js_or0(x1); x1 = xin;
+    }
+    L.w(p) = a0; L.w(p + 1) = a1; L.w(p + 2) = a2; L.w(p + 3) = b1; L.w(p + 4) = b2;
+    L.w(p + 5) = lastf; L.w(p + 6) = lastdef ? 1.0 : 0.0;
+    L.w(p + 7) = x1; L.w(p + 8) = x2; L.w(p + 9) = y1; L.w(p + 10) = y2;
+  });
+  L.st(x, I.out[0]);
+}
+
+// Filter.js:27-51 with host-derived coefficients.  y[n] = ((a0 x + a1 x1) + a2 x2) - b1 y1 - b2 y2:
+// the bracket depends only on inputs (all lanes at once); the two subtractions and the f32
+// rounding are the recurrence, run by the T lanes of a voice in turn.
+template <int B, int T>
+__device__ __forceinline__ void op_filterc(const Lane<B, T> &L, const DuspDevInstr &I) {
+  float x[B];
+  L.ld(x, I.in[0]);
+  const int p = I.p;
+  const double a0 = L.w(p), a1 = L.w(p + 1), a2 = L.w(p + 2), b1 = L.w(p + 3), b2 = L.w(p + 4);
+  double x1 = L.w(p + 5), x2 = L.w(p + 6), y1 = L.w(p + 7), y2 = L.w(p + 8);
+  if (T > 1) {  // inputs preceding this lane's first sample come from the previous time-lane
+    const float pm1 = __shfl_up_sync(0xffffffffu, x[B - 1], 1, T), pm2 = __shfl_up_sync(0xffffffffu, x[B - 2], 1, T);
+    if (L.tl > 0) { x1 = (double)pm1; x2 = js_or0((double)pm2); }
+  }
+  double c[B];
 #pragma unroll
   for (int s = 0; s < B; s++) {
-    const double ft = f[s];
-    if (!lastdef || ft != lastf) { lastdef = true; lastf = ft; filter_coeffs(I.aux[0], ft, a0, a1, a2, b1, b2); }
     const double xin = x[s];
-    const double y = a0 * xin + a1 * js_or0(x1) + a2 * js_or0(x2) - b1 * js_or0(y1) - b2 * js_or0(y2);
-    const float yf = (float)y;
-    x[s] = yf;
-    y2 = js_or0(y1); y1 = (double)yf; x2 = js_or0(x1); x1 = xin;
+    c[s] = a0 * xin + a1 * js_or0(x1) + a2 * js_or0(x2);
+    x2 = js_or0(x1); x1 = xin;
   }
-  L.w(p) = a0; L.w(p + 1) = a1; L.w(p + 2) = a2; L.w(p + 3) = b1; L.w(p + 4) = b2;
-  L.w(p + 5) = lastf; L.w(p + 6) = lastdef ? 1.0 : 0.0;
-  L.w(p + 7) = x1; L.w(p + 8) = x2; L.w(p + 9) = y1; L.w(p + 10) = y2;
+  if (T == 1) {
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      const float yf = (float)(c[s] - b1 * js_or0(y1) - b2 * js_or0(y2));
+      x[s] = yf;
+      y2 = js_or0(y1); y1 = (double)yf;
+    }
+  } else {
+#pragma unroll 1
+    for (int turn = 0; turn < T; turn++) {
+      if (L.tl == turn) {
+#pragma unroll
+        for (int s = 0; s < B; s++) {
+          const float yf = (float)(c[s] - b1 * js_or0(y1) - b2 * js_or0(y2));
+          x[s] = yf;
+          y2 = js_or0(y1); y1 = (double)yf;
+        }
+      }
+      const double n1 = shfl_d(y1, L.peer(turn)), n2 = shfl_d(y2, L.peer(turn));
+      if (L.tl == turn + 1) { y1 = n1; y2 = n2; }
+    }
+  }
+  L.sync();
+  if (L.tl == T - 1) { L.w(p + 5) = x1; L.w(p + 6) = x2; L.w(p + 7) = y1; L.w(p + 8) = y2; }
   L.st(x, I.out[0]);
 }
 
 // ----------------------------------------------------------------- rings
-template <int B>
-__device__ __forceinline__ void op_fixdelay(const Lane<B> &L, const DuspInstr &I) {  // FixedDelay.js:14-20 Comb :11-17 AllPass :8-15
+// FixedDelay.js:14-20, CombFilter.js:11-17, AllPass.js:8-15
+template <int B, int T>
+__device__ __forceinline__ void op_fixdelay(const Lane<B, T> &L, const DuspDevInstr &I) {
   float x[B], g[B];
   L.ld(x, I.in[0]);
   if (I.op != OP_FIXDELAY) L.ld(g, I.in[1]);
-  double len;
-  float *buf = L.ring(I.aux[0], len);
-  double tb = L.w(I.p);
-#pragma unroll
-  for (int s = 0; s < B; s++) {
-    tb = fmod(tb + 1.0, len);
-    const long long p = (long long)tb;
+  long long n;
+  float *buf = L.ring(I.aux0, n);
+  const double len = (double)n;
+  auto step = [&](long long p, int s) {
     const float d = buf[p];
     if (I.op == OP_FIXDELAY) { buf[p] = x[s]; x[s] = d; }
     else if (I.op == OP_COMB) { buf[p] = (float)((double)x[s] + (double)d * (double)g[s]); x[s] = d; }
     else { buf[p] = (float)((double)x[s] + (double)d * (double)g[s]); x[s] = (float)((double)d - (double)x[s] * (double)g[s]); }
+  };
+  const double tb0 = L.w(I.p);
+  if (T > 1 && n >= T * B && tb0 == floor(tb0) && tb0 >= 0.0 && tb0 < len) {
+    // every sample of the tile touches its own ring position: no dependence between time-lanes
+    long long p = (long long)tb0 + 1 + L.tl * B;
+    if (p >= n) p -= n;
+#pragma unroll
+    for (int s = 0; s < B; s++) { step(p, s); if (++p == n) p = 0; }
+    L.sync();
+    if (L.tl == T - 1) L.w(I.p) = (double)(p == 0 ? n - 1 : p - 1);
+  } else {
+    L.serial([&] {
+      double tb = L.w(I.p);
+#pragma unroll
+      for (int s = 0; s < B; s++) {
+        tb += 1.0;
+        if (!(tb < len)) tb = fmod(tb, len);  // (tBuffer + 1) % length
+        step((long long)tb, s);
+      }
+      L.w(I.p) = tb;
+    });
   }
-  L.w(I.p) = tb;
   L.st(x, I.out[0]);
 }
 
-template <int B>
-__device__ __forceinline__ void op_delay(const Lane<B> &L, const DuspInstr &I, long long t0) {  // Delay.js:20-41 / MonoDelay.js:19-30
+template <int B, int T>
+__device__ __forceinline__ void op_delay(const Lane<B, T> &L, const DuspDevInstr &I, long long t0) {  // Delay.js:20-41 / MonoDelay.js:19-30
   float x[B], dl[B];
   L.ld(x, I.in[0]); L.ld(dl, I.in[1]);
-  double len;
-  float *buf = L.ring(I.aux[0], len);
+  long long n;
+  float *buf = L.ring(I.aux0, n);
+  const double len = (double)n;
   const bool mono = I.op == OP_MONODELAY;
+  L.serial([&] {  // write-ahead scatter-add: later samples read what earlier ones added
 #pragma unroll
-  for (int s = 0; s < B; s++) {
-    const double tb = fmod((double)(t0 + s), len);
-    float y = 0.0f;
-    if (!mono) { y = (float)ring_read(buf, len, tb); if (ring_valid(tb, len)) buf[(long long)tb] = 0.0f; }
-    const double tw = fmod(tb + (double)dl[s], len);
-    const double fr = tw - trunc(tw);
-    const double fl = floor(tw);
-    const double ce = mono ? fmod(ceil(tw), len) : ceil(tw);
-    if (ring_valid(fl, len)) buf[(long long)fl] = (float)((double)buf[(long long)fl] + (double)x[s] * (1.0 - fr));
-    if (ring_valid(ce, len)) buf[(long long)ce] = (float)((double)buf[(long long)ce] + (double)x[s] * fr);
-    if (mono) { y = (float)ring_read(buf, len, tb); if (ring_valid(tb, len)) buf[(long long)tb] = 0.0f; }
-    x[s] = y;
-  }
+    for (int s = 0; s < B; s++) {
+      double tb = (double)(t0 + s);
+      if (!(tb < len)) tb = fmod(tb, len);  // (clock + t) % length
+      float y = 0.0f;
+      if (!mono) { y = (float)ring_read(buf, len, tb); if (ring_valid(tb, len)) buf[(long long)tb] = 0.0f; }
+      double tw = tb + (double)dl[s];  // (tBuffer + delay) % length, exact fast paths for the usual range
+      if (tw >= len) { tw = tw < 2.0 * len ? tw - len : fmod(tw, len); }
+      else if (!(tw > -len)) tw = fmod(tw, len);
+      const double fr = tw - trunc(tw);
+      const double fl = floor(tw);
+      double ce = ceil(tw);
+      if (mono && !(ce < len && ce > -len)) ce = fmod(ce, len);
+      if (ring_valid(fl, len)) buf[(long long)fl] = (float)((double)buf[(long long)fl] + (double)x[s] * (1.0 - fr));
+      if (ring_valid(ce, len)) buf[(long long)ce] = (float)((double)buf[(long long)ce] + (double)x[s] * fr);
+      if (mono) { y = (float)ring_read(buf, len, tb); if (ring_valid(tb, len)) buf[(long long)tb] = 0.0f; }
+      x[s] = y;
+    }
+  });
   L.st(x, I.out[0]);
 }
 
-template <int B>
-__device__ __forceinline__ void op_readback(const Lane<B> &L, const DuspInstr &I) {  // ReadBackDelay.js:23-43
+template <int B, int T>
+__device__ __forceinline__ void op_readback(const Lane<B, T> &L, const DuspDevInstr &I) {  // ReadBackDelay.js:23-43
   float x[B], dl[B];
   L.ld(x, I.in[0]); L.ld(dl, I.in[1]);
-  double len;
-  float *buf = L.ring(I.aux[0], len);
-  double t = L.w(I.p);
+  long long n;
+  float *buf = L.ring(I.aux0, n);
+  const double len = (double)n;
+  L.serial([&] {
+    double t = L.w(I.p);
 #pragma unroll
-  for (int s = 0; s < B; s++) {
-    const double wi = fmod(t + len, len);
-    if (ring_valid(wi, len)) buf[(long long)wi] = x[s];
-    x[s] = (float)ring_read(buf, len, fmod(t - (double)dl[s] + len, len));
-    t += 1.0;
-  }
-  L.w(I.p) = t;
+    for (int s = 0; s < B; s++) {
+      const double wi = fmod(t + len, len);
+      if (ring_valid(wi, len)) buf[(long long)wi] = x[s];
+      x[s] = (float)ring_read(buf, len, fmod(t - (double)dl[s] + len, len));
+      t += 1.0;
+    }
+    L.w(I.p) = t;
+  });
   L.st(x, I.out[0]);
 }
 
-template <int B>
-__device__ __forceinline__ void op_cbwrite(const Lane<B> &L, const DuspInstr &I, long long t0) {  // CircleBufferWriter.js:12-25
+// CircleBufferWriter.js:12-25 / CircleBufferReader.js:12-25 with a signal-rate OFFSET.  The compiler
+// only admits this form for a ring with a single tap unit, so serial turns keep the exact order.
+template <int B, int T>
+__device__ __forceinline__ void op_cbtap(const Lane<B, T> &L, const DuspDevInstr &I, long long t0) {
   float off[B], x[B];
   L.ld(off, I.in[0]);
-  const bool has_in = I.in[1] != REF_NONE;
+  const bool writer = I.op == OP_CBWRITE;
+  const bool has_in = writer && I.in[1] != REF_NONE;
   if (has_in) L.ld(x, I.in[1]);
-  double len;
-  float *buf = L.ring(I.aux[0], len);
+  long long n;
+  float *buf = L.ring(I.aux0, n);
+  const double len = (double)n;
   const double tu = L.w(I.p);
+  L.serial([&] {
 #pragma unroll
-  for (int s = 0; s < B; s++) {
-    const double tw = tu + (double)(t0 + s) + SRD * (double)off[s];
-    const double i = cb_index(tw, len);
-    if (ring_valid(i, len)) {
-      float v = buf[(long long)i];
-      if (I.aux[1]) v = 0.0f;                                   // preWipe: write(c, tWrite, 0)
-      if (has_in) v = (float)((double)v + (double)x[s]);        // mix: +=
-      buf[(long long)i] = v;
+    for (int s = 0; s < B; s++) {
+      const double tt = writer ? tu + (double)(t0 + s) + SRD * (double)off[s] : tu + (double)(t0 + s) - SRD * (double)off[s];
+      const double i = cb_index(tt, len);
+      float y = NAN;
+      if (ring_valid(i, len)) {
+        if (writer) {
+          float v = buf[(long long)i];
+          if (I.aux1) v = 0.0f;                                   // preWipe: write(c, tWrite, 0)
+          if (has_in) v = (float)((double)v + (double)x[s]);      // mix: +=
+          buf[(long long)i] = v;
+        } else {
+          y = buf[(long long)i];
+          if (I.aux1) buf[(long long)i] = 0.0f;                   // postWipe
+        }
+      }
+      off[s] = y;
     }
-  }
+  });
+  if (!writer) L.st(off, I.out[0]);
 }
 
-template <int B>
-__device__ __forceinline__ void op_cbread(const Lane<B> &L, const DuspInstr &I, long long t0) {  // CircleBufferReader.js:12-25
-  float off[B];
-  L.ld(off, I.in[0]);
-  double len;
-  float *buf = L.ring(I.aux[0], len);
-  const double tu = L.w(I.p);
+// Constant OFFSET: the ring index advances by one per sample; its start value is derived on the host.
+template <int B, int T>
+__device__ __forceinline__ void op_cbtapc(const Lane<B, T> &L, const DuspDevInstr &I) {
+  long long n;
+  float *buf = L.ring(I.aux0, n);
+  const long long i0 = (long long)L.w(I.p + 1);  // running index; -1 = the offset never yields a valid index
+  float x[B];
+  const bool writer = I.op == OP_CBWRITEC;
+  const bool has_in = writer && I.in[1] != REF_NONE;
+  if (has_in) L.ld(x, I.in[1]);
+  auto run = [&](long long i) {
 #pragma unroll
-  for (int s = 0; s < B; s++) {
-    const double tr = tu + (double)(t0 + s) - SRD * (double)off[s];
-    const double i = cb_index(tr, len);
-    float y = NAN;
-    if (ring_valid(i, len)) { y = buf[(long long)i]; if (I.aux[1]) buf[(long long)i] = 0.0f; }
-    off[s] = y;
+    for (int s = 0; s < B; s++) {
+      if (writer) {
+        float v = I.aux1 ? 0.0f : buf[i];                         // preWipe: write(c, tWrite, 0)
+        if (has_in) v = __fadd_rn(v, x[s]);                        // mix: `+=` (one f32 add == f64 add + rounding)
+        buf[i] = v;
+      } else {
+        x[s] = buf[i];
+        if (I.aux1) buf[i] = 0.0f;                                 // postWipe
+      }
+      if (++i == n) i = 0;
+    }
+    return i;
+  };
+  if (i0 < 0) {
+    if (!writer) {
+#pragma unroll
+      for (int s = 0; s < B; s++) x[s] = NAN;
+    }
+  } else if (T == 1 || n >= T * B) {  // distinct positions within the tile: time-lanes are independent
+    long long i = i0 + L.tl * B;
+    if (i >= n) i %= n;
+    i = run(i);
+    L.sync();
+    if (L.tl == T - 1) L.w(I.p + 1) = (double)i;
+  } else {
+    L.serial([&] { L.w(I.p + 1) = (double)run((long long)L.w(I.p + 1)); });
   }
-  L.st(off, I.out[0]);
+  if (!writer) L.st(x, I.out[0]);
 }
 
 // --------------------------------------------------------------- the kernel
-template <int B>
-__global__ void __launch_bounds__(DUSP_MAX_CTA_THREADS) dusp_render_lane_per_voice(const DuspKernelParams kp) {
-  extern __shared__ float smem[];
+template <int B, int T>
+__global__ void __launch_bounds__(DUSP_MAX_CTA_THREADS) dusp_render_tile(const __grid_constant__ DuspKernelParams kp) {
+  static_assert(B % 4 == 0 && (DUSP_CHUNK % (B * T)) == 0 && 32 % T == 0, "tile must divide the chunk");
+  extern __shared__ float4 smem[];
+  constexpr int V = 32 / T;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int warp = blockIdx.x * (blockDim.x >> 5) + wib;
-  const long long v = (long long)warp * 32 + lane;  // voice (allocations are padded to a multiple of 32)
-  if ((long long)warp * 32 >= kp.n_voices) return;
+  if ((long long)warp * V >= kp.n_voices) return;
+  const int vi = lane / T, tl = lane % T;
+  const long long v = (long long)warp * V + vi;  // voice (allocations are padded to a multiple of 32)
   const bool active = v < kp.n_voices;
 
-  Lane<B> L;
-  L.S = smem + (size_t)wib * kp.n_slots * B * 32 + lane;
+  Lane<B, T> L;
+  L.S = smem + (size_t)wib * kp.n_slots * (B / 4) * 32 + lane;
   L.W = kp.words + v;
-  L.nv = kp.nv_stride;
+  L.nv = (unsigned)kp.nv_stride;
+  L.tl = tl;
+  L.lane = lane;
   L.rings = kp.rings + v * kp.ring_stride;
   L.ring_tab = kp.ring_tab;
   L.stale = kp.stale + v * (long long)kp.n_stale * DUSP_CHUNK;
   L.tables = kp.tables;
 
   const long long n_proc = (kp.n_samples + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;  // whole chunks, like Circuit.tick
-  const long long vrow = (long long)(kp.voice0 + v) * kp.out_nch;
+  float *const out_row = kp.out + (long long)(kp.voice0 + v) * kp.out_nch * kp.out_len;
+  const int n_instr = kp.n_instr;
 
-  for (long long tl = 0; tl < n_proc; tl += B) {
-    const long long t0 = kp.clock0 + tl;   // absolute sample index (the reference's clock + t)
-    const int cpos = (int)(tl & (DUSP_CHUNK - 1));
-    for (int pc = 0; pc < kp.n_instr; pc++) {
-      DuspInstr I;
-      {
-        const int4 *src = reinterpret_cast<const int4 *>(kp.prog + pc);
+#pragma unroll 1
+  for (long long tile = 0; tile < n_proc; tile += T * B) {
+    const long long tl0 = tile + tl * B;   // this lane's first sample within the launch
+    const long long t0 = kp.clock0 + tl0;  // absolute sample index (the reference's clock + t)
+    const int cpos = (int)(tl0 & (DUSP_CHUNK - 1));
+#pragma unroll 1
+    for (int pc = 0; pc < n_instr; pc++) {
+      DuspDevInstr I;
+      if (kp.use_inline) {
+        I = kp.prog_inline[pc];
+      } else {
+        const int4 *src = reinterpret_cast<const int4 *>(kp.prog_global + pc);
         int4 *dst = reinterpret_cast<int4 *>(&I);
-        dst[0] = __ldg(src); dst[1] = __ldg(src + 1); dst[2] = __ldg(src + 2);
+        dst[0] = __ldg(src); dst[1] = __ldg(src + 1);
       }
       switch (I.op) {
-        case OP_COPY: map1<B>(L, I, [](float a) { return a; }); break;
-        case OP_NEG: map1<B>(L, I, [](float a) { return -a; }); break;
-        case OP_ABS: map1<B>(L, I, [](float a) { return fabsf(a); }); break;
-        case OP_S2S: map1<B>(L, I, [](float a) { return (float)((double)a * SRD); }); break;
-        case OP_SEMI: map1<B>(L, I, [](float a) { return (float)pow(2.0, (double)a / 12.0); }); break;
-        case OP_DB2S: map1<B>(L, I, [](float a) { return (float)pow(10.0, (double)a / 20.0); }); break;
-        case OP_MIDI2F: map1<B>(L, I, [](float a) { return (float)(pow(2.0, ((double)a - 69.0) / 12.0) * 440.0); }); break;
-        case OP_FIXMUL: { const double sf = L.w(I.p); map1<B>(L, I, [sf](float a) { return (float)((double)a * sf); }); break; }
+        case OP_COPY: map1<B, T>(L, I, [](float a) { return a; }); break;
+        case OP_NEG: map1<B, T>(L, I, [](float a) { return -a; }); break;
+        case OP_ABS: map1<B, T>(L, I, [](float a) { return fabsf(a); }); break;
+        case OP_S2S: map1<B, T>(L, I, [](float a) { return (float)((double)a * SRD); }); break;
+        case OP_SEMI: map1<B, T>(L, I, [](float a) { return (float)pow(2.0, (double)a / 12.0); }); break;
+        case OP_DB2S: map1<B, T>(L, I, [](float a) { return (float)pow(10.0, (double)a / 20.0); }); break;
+        case OP_MIDI2F: map1<B, T>(L, I, [](float a) { return (float)(pow(2.0, ((double)a - 69.0) / 12.0) * 440.0); }); break;
+        case OP_FIXMUL: { const double sf = L.w(I.p); map1<B, T>(L, I, [sf](float a) { return (float)((double)a * sf); }); break; }
         // a single IEEE operation on binary32 operands: double evaluation + one rounding == native f32 op
-        case OP_MUL: map2<B>(L, I, [](float a, float b) { return __fmul_rn(a, b); }); break;
-        case OP_DIV: map2<B>(L, I, [](float a, float b) { return __fdiv_rn(a, b); }); break;
-        case OP_ADD: map2<B>(L, I, [](float a, float b) { return __fadd_rn(a, b); }); break;
-        case OP_SUB: map2<B>(L, I, [](float a, float b) { return __fsub_rn(a, b); }); break;
-        case OP_POW: map2<B>(L, I, [](float a, float b) { return (float)pow((double)a, (double)b); }); break;
-        case OP_GAIN: map2<B>(L, I, [](float a, float g) { return (float)(dB((double)g) * (double)a); }); break;
-        case OP_CLIP: map2<B>(L, I, [](float a, float th) { return fabsf(a) > fabsf(th) ? th : a; }); break;
-        case OP_HCA: map2<B>(L, I, [](float a, float th) { return a > th ? th : a; }); break;
-        case OP_HCB: map2<B>(L, I, [](float a, float th) { return a < th ? th : a; }); break;
+        case OP_MUL: map2<B, T>(L, I, [](float a, float b) { return __fmul_rn(a, b); }); break;
+        case OP_DIV: map2<B, T>(L, I, [](float a, float b) { return __fdiv_rn(a, b); }); break;
+        case OP_ADD: map2<B, T>(L, I, [](float a, float b) { return __fadd_rn(a, b); }); break;
+        case OP_SUB: map2<B, T>(L, I, [](float a, float b) { return __fsub_rn(a, b); }); break;
+        case OP_POW: map2<B, T>(L, I, [](float a, float b) { return (float)pow((double)a, (double)b); }); break;
+        case OP_GAIN: map2<B, T>(L, I, [](float a, float g) { return (float)(dB((double)g) * (double)a); }); break;
+        case OP_GAINC: { const double k = L.w(I.p); map1<B, T>(L, I, [k](float a) { return (float)(k * (double)a); }); break; }
+        case OP_CLIP: map2<B, T>(L, I, [](float a, float th) { return fabsf(a) > fabsf(th) ? th : a; }); break;
+        case OP_HCA: map2<B, T>(L, I, [](float a, float th) { return a > th ? th : a; }); break;
+        case OP_HCB: map2<B, T>(L, I, [](float a, float th) { return a < th ? th : a; }); break;
         case OP_RESCALE: {  // Rescale.js:33-34
           float x[B], il[B], iu[B], ol[B], ou[B];
           L.ld(x, I.in[0]); L.ld(il, I.in[1]); L.ld(iu, I.in[2]); L.ld(ol, I.in[3]); L.ld(ou, I.in[4]);
@@ -473,11 +719,24 @@ __global__ void __launch_bounds__(DUSP_MAX_CTA_THREADS) dusp_render_lane_per_voi
           L.st(x, I.out[0]); L.st(o1, I.out[1]);
           break;
         }
+        case OP_PANC: {  // Pan.js:21-22 with (1-pan), (1+pan), compensation derived on the host
+          float x[B], o1[B];
+          L.ld(x, I.in[0]);
+          const double kl = L.w(I.p), kr = L.w(I.p + 1), comp = L.w(I.p + 2);
+#pragma unroll
+          for (int s = 0; s < B; s++) {
+            const double in = x[s];
+            x[s] = (float)(in * kl / 2.0 * comp);
+            o1[s] = (float)(in * kr / 2.0 * comp);
+          }
+          L.st(x, I.out[0]); L.st(o1, I.out[1]);
+          break;
+        }
         case OP_VECMAG: {  // VectorMagnitude.js:19-25
           double acc[B];
 #pragma unroll
           for (int s = 0; s < B; s++) acc[s] = 0.0;
-          for (int c = 0; c < I.aux[0]; c++) {
+          for (int c = 0; c < I.aux0; c++) {
             float x[B];
             L.ld(x, I.in[c]);
 #pragma unroll
@@ -489,58 +748,64 @@ __global__ void __launch_bounds__(DUSP_MAX_CTA_THREADS) dusp_render_lane_per_voi
           L.st(o, I.out[0]);
           break;
         }
-        case OP_OSC: op_osc<B>(L, I, true); break;
-        case OP_MCOSC: op_osc<B>(L, I, false); break;
-        case OP_RAMP: op_ramp<B>(L, I); break;
-        case OP_SHAPE: op_shape<B>(L, I); break;
-        case OP_AHD: op_ahd<B>(L, I); break;
-        case OP_TIMER: op_timer<B>(L, I); break;
-        case OP_NOISE: op_noise<B>(L, I); break;
-        case OP_FILTER: op_filter<B>(L, I); break;
-        case OP_FIXDELAY: case OP_COMB: case OP_ALLPASS: op_fixdelay<B>(L, I); break;
-        case OP_DELAY: case OP_MONODELAY: op_delay<B>(L, I, t0); break;
-        case OP_READBACK: op_readback<B>(L, I); break;
-        case OP_CBWRITE: op_cbwrite<B>(L, I, t0); break;
-        case OP_CBREAD: op_cbread<B>(L, I, t0); break;
+        case OP_OSC: op_osc<B, T>(L, I); break;
+        case OP_MCOSC: op_mcosc<B, T>(L, I); break;
+        case OP_RAMP: op_ramp<B, T>(L, I); break;
+        case OP_SHAPE: op_shape<B, T>(L, I); break;
+        case OP_AHD: op_ahd<B, T>(L, I); break;
+        case OP_TIMER: op_timer<B, T>(L, I); break;
+        case OP_NOISE: op_noise<B, T>(L, I); break;
+        case OP_NOISE1: op_noise1<B, T>(L, I); break;
+        case OP_FILTER: op_filter<B, T>(L, I); break;
+        case OP_FILTERC: op_filterc<B, T>(L, I); break;
+        case OP_FIXDELAY: case OP_COMB: case OP_ALLPASS: op_fixdelay<B, T>(L, I); break;
+        case OP_DELAY: case OP_MONODELAY: op_delay<B, T>(L, I, t0); break;
+        case OP_READBACK: op_readback<B, T>(L, I); break;
+        case OP_CBWRITE: case OP_CBREAD: op_cbtap<B, T>(L, I, t0); break;
+        case OP_CBWRITEC: case OP_CBREADC: op_cbtapc<B, T>(L, I); break;
         case OP_LDSTALE: {
           float x[B];
-          const float *src = L.stale + (size_t)I.aux[0] * DUSP_CHUNK + cpos;
+          const float4 *src = reinterpret_cast<const float4 *>(L.stale + (size_t)I.aux0 * DUSP_CHUNK + cpos);
 #pragma unroll
-          for (int s = 0; s < B; s++) x[s] = src[s];
+          for (int q = 0; q < B / 4; q++) { const float4 t = src[q]; x[4 * q] = t.x; x[4 * q + 1] = t.y; x[4 * q + 2] = t.z; x[4 * q + 3] = t.w; }
           L.st(x, I.out[0]);
           break;
         }
         case OP_STSTALE: {
           float x[B];
           L.ld(x, I.in[0]);
-          float *dst = L.stale + (size_t)I.aux[0] * DUSP_CHUNK + cpos;
+          float4 *dst = reinterpret_cast<float4 *>(L.stale + (size_t)I.aux0 * DUSP_CHUNK + cpos);
 #pragma unroll
-          for (int s = 0; s < B; s++) dst[s] = x[s];
+          for (int q = 0; q < B / 4; q++) dst[q] = make_float4(x[4 * q], x[4 * q + 1], x[4 * q + 2], x[4 * q + 3]);
           break;
         }
         case OP_OUT: {  // renderChannelData.js:42-44
           float x[B];
           L.ld(x, I.in[0]);
+#pragma unroll
+          for (int s = 0; s < B; s++) x[s] = js_or0f(x[s]);
           if (kp.out_mode == 0) {
             if (active) {
-              float *dst = kp.out + (vrow + I.aux[0]) * kp.out_len;
+              float *dst = out_row + (long long)I.aux0 * kp.out_len + tl0;
+              if (tl0 + B <= kp.n_samples && (kp.out_len & 3) == 0) {  // whole sub-block in range, rows 16-byte aligned
+                float4 *d4 = reinterpret_cast<float4 *>(dst);
 #pragma unroll
-              for (int s = 0; s < B; s++)
-                if (tl + s < kp.n_samples) dst[tl + s] = js_or0f(x[s]);
+                for (int q = 0; q < B / 4; q++) __stcs(d4 + q, make_float4(x[4 * q], x[4 * q + 1], x[4 * q + 2], x[4 * q + 3]));
+              } else {
+#pragma unroll
+                for (int s = 0; s < B; s++) if (tl0 + s < kp.n_samples) dst[s] = x[s];
+              }
             }
-          } else {
-            // stereo mixdown: mix[c] += out_v[c % nch_v]; warp tree-sum then one atomic per sample
-            const int ch = I.aux[0];
-            if (ch < 2) {
+          } else if (I.aux0 < 2) {
+            // stereo mixdown: mix[c] += out_v[c % nch_v]; tree-sum over the warp's voices, then one atomic per sample
 #pragma unroll
-              for (int s = 0; s < B; s++) {
-                float y = active ? js_or0f(x[s]) : 0.0f;
+            for (int s = 0; s < B; s++) {
+              float y = active ? x[s] : 0.0f;
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) y += __shfl_xor_sync(0xffffffffu, y, o);
-                if (lane == 0 && tl + s < kp.n_samples) {
-                  atomicAdd(kp.out + (long long)ch * kp.out_len + tl + s, y);
-                  if (kp.prog_nch == 1) atomicAdd(kp.out + kp.out_len + tl + s, y);
-                }
+              for (int o = 16; o >= T; o >>= 1) y += __shfl_xor_sync(0xffffffffu, y, o);
+              if (vi == 0 && tl0 + s < kp.n_samples) {
+                atomicAdd(kp.out + (long long)I.aux0 * kp.out_len + tl0 + s, y);
+                if (kp.prog_nch == 1) atomicAdd(kp.out + kp.out_len + tl0 + s, y);
               }
             }
           }
@@ -552,32 +817,37 @@ __global__ void __launch_bounds__(DUSP_MAX_CTA_THREADS) dusp_render_lane_per_voi
   }
 }
 
+template <int B, int T>
+int launch(const DuspKernelParams *kp, int warps_per_cta, cudaStream_t st, int *grid_out, int *smem_out) {
+  constexpr int V = 32 / T;
+  const int n_warps = (kp->n_voices + V - 1) / V;
+  const int grid = (n_warps + warps_per_cta - 1) / warps_per_cta;
+  const int block = warps_per_cta * 32;
+  const size_t smem = (size_t)warps_per_cta * kp->n_slots * B * 32 * sizeof(float);
+  if (grid_out) *grid_out = grid;
+  if (smem_out) *smem_out = (int)smem;
+  cudaError_t e = cudaFuncSetAttribute(dusp_render_tile<B, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  dusp_render_tile<B, T><<<grid, block, smem, st>>>(*kp);
+  return (int)cudaGetLastError();
+}
+
 }  // namespace
 
 // --------------------------------------------------------------- launcher
-extern "C" int dusp_launch_render(const DuspKernelParams *kp, int sub_block, int warps_per_cta, void *stream,
-                                  int *grid_out, int *smem_out) {
-  const int n_warps = (kp->n_voices + 31) / 32;
-  const int grid = (n_warps + warps_per_cta - 1) / warps_per_cta;
-  const int block = warps_per_cta * 32;
-  const size_t smem = (size_t)warps_per_cta * kp->n_slots * sub_block * 32 * sizeof(float);
-  cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e;
-  if (grid_out) *grid_out = grid;
-  if (smem_out) *smem_out = (int)smem;
-#define LAUNCH(BV)                                                                                         \
-  do {                                                                                                     \
-    e = cudaFuncSetAttribute(dusp_render_lane_per_voice<BV>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                             (int)smem);                                                                   \
-    if (e != cudaSuccess) return (int)e;                                                                   \
-    dusp_render_lane_per_voice<BV><<<grid, block, smem, st>>>(*kp);                                       \
-  } while (0)
-  switch (sub_block) {
-    case 4: LAUNCH(4); break;
-    case 8: LAUNCH(8); break;
-    case 16: LAUNCH(16); break;
-    default: return (int)cudaErrorInvalidValue;
-  }
-#undef LAUNCH
-  return (int)cudaGetLastError();
+#define DUSP_CONFIGS(X) X(16, 1) X(8, 1) X(16, 4) X(16, 16) X(8, 32)
+
+extern "C" int dusp_launch_supported(int sub_block, int time_lanes) {
+#define X(BV, TV) if (sub_block == BV && time_lanes == TV) return 1;
+  DUSP_CONFIGS(X)
+#undef X
+  return 0;
+}
+
+extern "C" int dusp_launch_render(const DuspKernelParams *kp, int sub_block, int time_lanes, int warps_per_cta,
+                                  void *stream, int *grid_out, int *smem_out) {
+#define X(BV, TV) if (sub_block == BV && time_lanes == TV) return launch<BV, TV>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
+  DUSP_CONFIGS(X)
+#undef X
+  return (int)cudaErrorInvalidValue;
 }

@@ -58,6 +58,15 @@ enum DuspOp : int32_t {
   OP_LDSTALE,   // slot <- previous chunk of a value produced later in the tick order (cyclic graphs)
   OP_STSTALE,   // stale buffer <- slot
   OP_OUT,       // renderChannelData.js:42-44: out[channel aux0][t] = slot || 0
+  // --- specialisations chosen by the compiler when an inlet is a per-voice constant: the
+  //     transcendental / index arithmetic that depends only on that constant is evaluated once
+  //     per voice on the host ("derived words") with the same libm formulas the reference uses
+  OP_FILTERC,   // Filter, constant F        [p: a0,a1,a2,b1,b2 (derived), x1,x2,y1,y2]
+  OP_PANC,      // Pan, constant PAN         [p: 1-pan, 1+pan, compensation (derived)]
+  OP_GAINC,     // Gain, constant GAIN       [p: 10^(gain/20) (derived)]
+  OP_NOISE1,    // Noise, constant F >= sampleRate: a new draw every sample   [p as OP_NOISE]
+  OP_CBWRITEC,  // CircleBufferWriter, constant OFFSET  [p: t0, running ring index (derived start)]
+  OP_CBREADC,   // CircleBufferReader, constant OFFSET
   OP_COUNT
 };
 
@@ -87,9 +96,23 @@ struct DuspRing {
 // table ids (waveTables.js:33-40, shapeTables.js:20-38)
 enum { TAB_SIN = 0, TAB_SAW, TAB_SQUARE, TAB_TRIANGLE, TAB_8BIT, TAB_DECAY, TAB_ATTACK, TAB_SEMISINE, TAB_DECAYSQ, TAB_COUNT };
 
-// One launch renders `n_blocks` sub-blocks for every voice of one program group.
+// Device encoding of an instruction (32 bytes).  Programs of up to DUSP_INLINE_INSTR instructions
+// travel inside the kernel parameter block (constant bank: fetched with a uniform LDC, no global load).
+struct __attribute__((aligned(16))) DuspDevInstr {
+  int16_t op;
+  int16_t aux1;
+  int16_t in[5];
+  int16_t out[2];
+  int16_t aux2;
+  int32_t p;
+  int32_t aux0;
+  int32_t pad;
+};
+static_assert(sizeof(DuspDevInstr) == 32, "DuspDevInstr layout");
+#define DUSP_INLINE_INSTR 112
+
+// One launch renders `n_samples` for every voice of one program group.
 struct DuspKernelParams {
-  const DuspInstr *prog;
   int32_t n_instr;
   int32_t n_slots;
   int32_t n_voices;      // voices in this group
@@ -101,12 +124,16 @@ struct DuspKernelParams {
   const DuspRing *ring_tab;
   float *stale;          // [voice][n_stale][256]
   int32_t n_stale;
+  int32_t use_inline;    // program is in prog_inline (else prog_global)
   const float *tables;   // [TAB_COUNT][DUSP_TABLE_LEN]
   float *out;            // DUSP_OUT_VOICES: [voice][out_nch][out_len]; DUSP_OUT_MIX: [2][out_len]
   int32_t out_nch;       // channel stride of the output (session-wide)
   int32_t prog_nch;      // channels this program produces
   int32_t out_mode;
+  int32_t pad0;
   int64_t out_len;       // samples per channel row in `out`
   int64_t clock0;        // absolute sample index of the first sample of this launch (multiple of 256)
   int64_t n_samples;     // samples to store (<= processed); processing covers whole chunks
+  const DuspDevInstr *prog_global;
+  DuspDevInstr prog_inline[DUSP_INLINE_INSTR];
 };

@@ -1,0 +1,101 @@
+"""Synthetic benchmark workloads W1..W5: deterministic
+generators of circuits and per-voice parameters.  All randomness comes from
+the injected counter-based generator (``config.rand53``), keyed by a stated
+seed and the GLOBAL voice index so any rank can build its own shard."""
+import numpy as np
+
+from . import components as C, patches as P, quick
+from .config import rand53, _mix64
+
+SR = 44100
+
+
+def _u(seed, voice, j, lo, hi):
+    return lo + (hi - lo) * rand53(seed, 8 * voice + j)
+
+
+def unit_indices(blob):
+    kinds = [l.split()[1] for l in blob.splitlines() if l.startswith("U ")]
+    out = {}
+    for i, k in enumerate(kinds):
+        out.setdefault(k, []).append(i)
+    return out
+
+
+# ---- W1: `[Osc 440]`, 10 s mono, one circuit (BASELINE configs[0]) ----
+def w1_circuit():
+    from .construct import unDusp
+    return unDusp("[Osc 440]")
+
+
+# ---- W2: FM / envelope ring-mod patch (BASELINE configs[1]) ----
+W2_SEED = 1001
+
+
+def w2_literal_circuit():
+    from .construct import unDusp
+    return unDusp("[Multiply A:[Osc #o f:[Ramp from:200 to:100 duration:2]] B:#o]")
+
+
+def w2_live_circuit(f0=300.0):
+    osc = C.Osc(C.Ramp(88200, f0, f0 / 2).trigger())
+    return C.Multiply(osc, osc)
+
+
+def w2_params(voice0, n):
+    """f0_v ~ U[100,800): Ramp(88200, f0, f0/2).trigger()"""
+    f0 = np.array([_u(W2_SEED, voice0 + v, 0, 100.0, 800.0) for v in range(n)])
+    return {"f0": f0}
+
+
+def w2_overrides(blob, params):
+    ramp = unit_indices(blob)["Ramp"][0]
+    return {"u%d.y0" % ramp: params["f0"], "u%d.y1" % ramp: params["f0"] / 2}
+
+
+# ---- W3: seeded Noise -> LP Filter -> CircleBuffer feedback delay -> Pan (BASELINE configs[2]) ----
+W3_SEED = 1002
+W3_UNITS = 8  # Noise, Filter, Writer, Reader, Multiply, Writer2, Sum, Pan
+
+
+def w3_circuit(f=1000.0, dly=0.2, g=0.5, pan=0.0, seed=1):
+    filt = C.Filter(C.Noise(seed=seed), f, "LP")
+    mt = P.MultiTapDelay(1, 1.0, filt)
+    tap = mt.addFeedback(dly, g, 0)
+    return C.Pan(C.Sum(filt, tap), pan)
+
+
+def w3_params(voice0, n):
+    """f_v ~ U[200,4000) Hz, d_v ~ U[0.05,0.5) s, g_v ~ U[0.2,0.7), p_v ~ U[-1,1), noise stream seed per voice."""
+    v = range(voice0, voice0 + n)
+    return {
+        "f": np.array([_u(W3_SEED, i, 0, 200.0, 4000.0) for i in v]),
+        "dly": np.array([_u(W3_SEED, i, 1, 0.05, 0.5) for i in v]),
+        "g": np.array([_u(W3_SEED, i, 2, 0.2, 0.7) for i in v]),
+        "pan": np.array([_u(W3_SEED, i, 3, -1.0, 1.0) for i in v]),
+        "seed": np.array([_mix64(W3_SEED * 0x10001 + i) for i in v], dtype=np.uint64),
+    }
+
+
+def w3_overrides(blob, params):
+    u = unit_indices(blob)
+    filt, pan, reader = u["Filter"][0], u["Pan"][0], u["CircleBufferReader"][0]
+    mult, noise = u["Multiply"][0], u["Noise"][0]
+    seeds = params["seed"]
+    y0 = np.array([2 * rand53(int(s), 0) - 1 for s in seeds])
+    return {
+        "u%d.f[0]" % filt: params["f"], "u%d.offset[0]" % reader: params["dly"], "u%d.b[0]" % mult: params["g"],
+        "u%d.pan[0]" % pan: params["pan"], "u%d.seed_lo" % noise: (seeds & np.uint64(0xFFFFFFFF)).astype(np.float64),
+        "u%d.seed_hi" % noise: (seeds >> np.uint64(32)).astype(np.float64), "u%d.y" % noise: y0,
+    }
+
+
+def w3_voice_circuit(params, v):
+    """The stand-alone circuit of voice v (what the reference / the oracle renders)."""
+    return w3_circuit(float(params["f"][v]), float(params["dly"][v]), float(params["g"][v]),
+                      float(params["pan"][v]), int(params["seed"][v]))
+
+
+# ---- W3b: cyclic-graph coverage, `Pan(SimpleDelay(Filter(Noise)))` ----
+def w3b_circuit(f=800.0, dly=0.25, g=0.5, pan=0.3, seed=1):
+    return C.Pan(P.SimpleDelay(C.Filter(C.Noise(seed=seed), f), dly, g, 0.4), pan)
