@@ -201,13 +201,10 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
     for (const DuspInstr &in : g.prog.code) {
       DuspDevInstr d;
       memset(&d, 0, sizeof d);
-      d.op = (int16_t)in.op;
-      for (int k = 0; k < 5; k++) {
-        if (in.in[k] < -32768 || in.in[k] > 32767) return fail(DUSP_EUNSUPPORTED, "circuit has too many per-voice words");
-        d.in[k] = (int16_t)in.in[k];
-      }
-      for (int k = 0; k < 2; k++) d.out[k] = (int16_t)in.out[k];
-      d.p = in.p; d.aux0 = in.aux[0]; d.aux1 = (int16_t)in.aux[1]; d.aux2 = (int16_t)in.aux[2];
+      d.op = in.op;
+      for (int k = 0; k < 5; k++) d.in[k] = in.in[k];
+      for (int k = 0; k < 2; k++) d.out[k] = in.out[k];
+      d.p = in.p; d.aux0 = in.aux[0]; d.aux1 = in.aux[1]; d.aux2 = in.aux[2];
       g.dev_code.push_back(d);
     }
     CUDA_TRY(cudaMalloc(&g.d_code, std::max<size_t>(g.dev_code.size(), 1) * sizeof(DuspDevInstr)));
@@ -215,10 +212,12 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
     {
       // Tile shape: T time-lanes per voice so that the batch still fills the GPU (>= 8 warps per SM);
       // B samples per lane.  DUSP_TILE="B,T" overrides (experiments).
-      const int choices[4] = {1, 4, 16, 32};
+      // (measured on B200, profiles/r1_tile_sweep.txt: for 10k voices B=8,T=4 wins; B=8 keeps the kernel
+      // at 128 registers so 16 warps/SM are resident and the whole batch runs as one wave)
+      const int choices[4] = {1, 4, 8, 32};
       int T = 32;
       for (int t : choices) if (((long long)voices[i] + (32 / t) - 1) / (32 / t) >= 148 * 8) { T = t; break; }
-      int B = T == 32 ? 8 : 16;
+      int B = T == 1 ? 16 : 8;
       if (const char *env = getenv("DUSP_TILE")) { int b = 0, t = 0; if (sscanf(env, "%d,%d", &b, &t) == 2) { B = b; T = t; } }
       if ((size_t)g.prog.n_slots * B * 128 > 200 * 1024 && T == 1) B = 8;
       if (!dusp_launch_supported(B, T)) return fail(DUSP_EINVAL, "unsupported tile shape (DUSP_TILE)");

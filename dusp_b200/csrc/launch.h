@@ -2,7 +2,7 @@
 #pragma once
 #include "vm.h"
 
-#define DUSP_MAX_CTA_THREADS 256
+#define DUSP_MAX_CTA_THREADS 128
 
 #ifdef __cplusplus
 extern "C" {

@@ -416,42 +416,43 @@ __device__ __forceinline__ void op_filterc(const Lane<B, T> &L, const DuspDevIns
   L.ld(x, I.in[0]);
   const int p = I.p;
   const double a0 = L.w(p), a1 = L.w(p + 1), a2 = L.w(p + 2), b1 = L.w(p + 3), b2 = L.w(p + 4);
-  double x1 = L.w(p + 5), x2 = L.w(p + 6), y1 = L.w(p + 7), y2 = L.w(p + 8);
+  // o1/o2: the previous two inputs after `|| 0` (the reference keeps x2, y2 already normalised and
+  // applies `|| 0` to x1, y1 on every read, Filter.js:38-47); q1/q2: same for the outputs.
+  double o1 = js_or0(L.w(p + 5)), o2 = js_or0(L.w(p + 6)), q1 = js_or0(L.w(p + 7)), q2 = js_or0(L.w(p + 8));
   if (T > 1) {  // inputs preceding this lane's first sample come from the previous time-lane
     const float pm1 = __shfl_up_sync(0xffffffffu, x[B - 1], 1, T), pm2 = __shfl_up_sync(0xffffffffu, x[B - 2], 1, T);
-    if (L.tl > 0) { x1 = (double)pm1; x2 = js_or0((double)pm2); }
+    if (L.tl > 0) { o1 = (double)js_or0f(pm1); o2 = (double)js_or0f(pm2); }
   }
   double c[B];
 #pragma unroll
   for (int s = 0; s < B; s++) {
     const double xin = x[s];
-    c[s] = a0 * xin + a1 * js_or0(x1) + a2 * js_or0(x2);
-    x2 = js_or0(x1); x1 = xin;
+    c[s] = a0 * xin + a1 * o1 + a2 * o2;
+    o2 = o1; o1 = (double)js_or0f(x[s]);
   }
-  if (T == 1) {
+  const double xlast = x[B - 1];  // raw x1 for the state block
+  auto recur = [&]() {
+    double b2q2 = b2 * q2;
 #pragma unroll
     for (int s = 0; s < B; s++) {
-      const float yf = (float)(c[s] - b1 * js_or0(y1) - b2 * js_or0(y2));
+      const float yf = (float)(c[s] - b1 * q1 - b2q2);
       x[s] = yf;
-      y2 = js_or0(y1); y1 = (double)yf;
+      b2q2 = b2 * q1;              // next sample's b2*y2, ready before it is needed
+      q2 = q1; q1 = (double)js_or0f(yf);
     }
+  };
+  if (T == 1) {
+    recur();
   } else {
 #pragma unroll 1
     for (int turn = 0; turn < T; turn++) {
-      if (L.tl == turn) {
-#pragma unroll
-        for (int s = 0; s < B; s++) {
-          const float yf = (float)(c[s] - b1 * js_or0(y1) - b2 * js_or0(y2));
-          x[s] = yf;
-          y2 = js_or0(y1); y1 = (double)yf;
-        }
-      }
-      const double n1 = shfl_d(y1, L.peer(turn)), n2 = shfl_d(y2, L.peer(turn));
-      if (L.tl == turn + 1) { y1 = n1; y2 = n2; }
+      if (L.tl == turn) recur();
+      const double n1 = shfl_d(q1, L.peer(turn)), n2 = shfl_d(q2, L.peer(turn));
+      if (L.tl == turn + 1) { q1 = n1; q2 = n2; }
     }
   }
   L.sync();
-  if (L.tl == T - 1) { L.w(p + 5) = x1; L.w(p + 6) = x2; L.w(p + 7) = y1; L.w(p + 8) = y2; }
+  if (L.tl == T - 1) { L.w(p + 5) = xlast; L.w(p + 6) = o2; L.w(p + 7) = (double)x[B - 1]; L.w(p + 8) = q2; }
   L.st(x, I.out[0]);
 }
 
@@ -586,23 +587,48 @@ __device__ __forceinline__ void op_cbtap(const Lane<B, T> &L, const DuspDevInstr
 // Constant OFFSET: the ring index advances by one per sample; its start value is derived on the host.
 template <int B, int T>
 __device__ __forceinline__ void op_cbtapc(const Lane<B, T> &L, const DuspDevInstr &I) {
-  long long n;
-  float *buf = L.ring(I.aux0, n);
-  const long long i0 = (long long)L.w(I.p + 1);  // running index; -1 = the offset never yields a valid index
+  long long n64;
+  float *buf = L.ring(I.aux0, n64);
+  const int n = (int)n64;
+  const int i0 = (int)L.w(I.p + 1);  // running index; -1 = the offset never yields a valid index
   float x[B];
   const bool writer = I.op == OP_CBWRITEC;
   const bool has_in = writer && I.in[1] != REF_NONE;
+  const bool wipe = I.aux1 != 0;
   if (has_in) L.ld(x, I.in[1]);
-  auto run = [&](long long i) {
+  // one lane's run of B consecutive ring positions starting at i (wraps at most once)
+  auto run = [&](int i) {
+    if (i + B <= n) {  // no wrap inside the run: plain pointer walk
+      float *q = buf + i;
+      if (!writer) {
 #pragma unroll
+        for (int s = 0; s < B; s++) x[s] = q[s];
+        if (wipe) {                                                // postWipe
+#pragma unroll
+          for (int s = 0; s < B; s++) q[s] = 0.0f;
+        }
+      } else if (wipe) {                                           // preWipe: write(0) then mix -> 0 + in
+#pragma unroll
+        for (int s = 0; s < B; s++) q[s] = has_in ? __fadd_rn(0.0f, x[s]) : 0.0f;
+      } else if (has_in) {                                         // mix: `+=` (one f32 add == f64 add + rounding)
+        float v[B];
+#pragma unroll
+        for (int s = 0; s < B; s++) v[s] = q[s];
+#pragma unroll
+        for (int s = 0; s < B; s++) q[s] = __fadd_rn(v[s], x[s]);
+      }
+      i += B;
+      return i == n ? 0 : i;
+    }
+#pragma unroll 1
     for (int s = 0; s < B; s++) {
       if (writer) {
-        float v = I.aux1 ? 0.0f : buf[i];                         // preWipe: write(c, tWrite, 0)
-        if (has_in) v = __fadd_rn(v, x[s]);                        // mix: `+=` (one f32 add == f64 add + rounding)
-        buf[i] = v;
+        float v = wipe ? 0.0f : buf[i];
+        if (has_in) v = __fadd_rn(v, x[s]);
+        if (has_in || wipe) buf[i] = v;
       } else {
         x[s] = buf[i];
-        if (I.aux1) buf[i] = 0.0f;                                 // postWipe
+        if (wipe) buf[i] = 0.0f;
       }
       if (++i == n) i = 0;
     }
@@ -614,20 +640,21 @@ __device__ __forceinline__ void op_cbtapc(const Lane<B, T> &L, const DuspDevInst
       for (int s = 0; s < B; s++) x[s] = NAN;
     }
   } else if (T == 1 || n >= T * B) {  // distinct positions within the tile: time-lanes are independent
-    long long i = i0 + L.tl * B;
+    int i = i0 + L.tl * B;
     if (i >= n) i %= n;
     i = run(i);
     L.sync();
     if (L.tl == T - 1) L.w(I.p + 1) = (double)i;
   } else {
-    L.serial([&] { L.w(I.p + 1) = (double)run((long long)L.w(I.p + 1)); });
+    L.serial([&] { L.w(I.p + 1) = (double)run((int)L.w(I.p + 1)); });
   }
   if (!writer) L.st(x, I.out[0]);
 }
 
 // --------------------------------------------------------------- the kernel
+// registers are capped so that at least 16 (B=8) / 8 (B=16) warps are resident per SM
 template <int B, int T>
-__global__ void __launch_bounds__(DUSP_MAX_CTA_THREADS) dusp_render_tile(const __grid_constant__ DuspKernelParams kp) {
+__global__ void __launch_bounds__(128, B == 8 ? 4 : 2) dusp_render_tile(const __grid_constant__ DuspKernelParams kp) {
   static_assert(B % 4 == 0 && (DUSP_CHUNK % (B * T)) == 0 && 32 % T == 0, "tile must divide the chunk");
   extern __shared__ float4 smem[];
   constexpr int V = 32 / T;
@@ -656,7 +683,6 @@ __global__ void __launch_bounds__(DUSP_MAX_CTA_THREADS) dusp_render_tile(const _
 #pragma unroll 1
   for (long long tile = 0; tile < n_proc; tile += T * B) {
     const long long tl0 = tile + tl * B;   // this lane's first sample within the launch
-    const long long t0 = kp.clock0 + tl0;  // absolute sample index (the reference's clock + t)
     const int cpos = (int)(tl0 & (DUSP_CHUNK - 1));
 #pragma unroll 1
     for (int pc = 0; pc < n_instr; pc++) {
@@ -666,7 +692,7 @@ __global__ void __launch_bounds__(DUSP_MAX_CTA_THREADS) dusp_render_tile(const _
       } else {
         const int4 *src = reinterpret_cast<const int4 *>(kp.prog_global + pc);
         int4 *dst = reinterpret_cast<int4 *>(&I);
-        dst[0] = __ldg(src); dst[1] = __ldg(src + 1);
+        dst[0] = __ldg(src); dst[1] = __ldg(src + 1); dst[2] = __ldg(src + 2);
       }
       switch (I.op) {
         case OP_COPY: map1<B, T>(L, I, [](float a) { return a; }); break;
@@ -736,11 +762,14 @@ __global__ void __launch_bounds__(DUSP_MAX_CTA_THREADS) dusp_render_tile(const _
           double acc[B];
 #pragma unroll
           for (int s = 0; s < B; s++) acc[s] = 0.0;
-          for (int c = 0; c < I.aux0; c++) {
-            float x[B];
-            L.ld(x, I.in[c]);
 #pragma unroll
-            for (int s = 0; s < B; s++) acc[s] += (double)x[s] * (double)x[s];
+          for (int c = 0; c < 5; c++) {
+            if (c < I.aux0) {
+              float x[B];
+              L.ld(x, I.in[c]);
+#pragma unroll
+              for (int s = 0; s < B; s++) acc[s] += (double)x[s] * (double)x[s];
+            }
           }
           float o[B];
 #pragma unroll
@@ -759,9 +788,9 @@ __global__ void __launch_bounds__(DUSP_MAX_CTA_THREADS) dusp_render_tile(const _
         case OP_FILTER: op_filter<B, T>(L, I); break;
         case OP_FILTERC: op_filterc<B, T>(L, I); break;
         case OP_FIXDELAY: case OP_COMB: case OP_ALLPASS: op_fixdelay<B, T>(L, I); break;
-        case OP_DELAY: case OP_MONODELAY: op_delay<B, T>(L, I, t0); break;
+        case OP_DELAY: case OP_MONODELAY: op_delay<B, T>(L, I, kp.clock0 + tl0); break;
         case OP_READBACK: op_readback<B, T>(L, I); break;
-        case OP_CBWRITE: case OP_CBREAD: op_cbtap<B, T>(L, I, t0); break;
+        case OP_CBWRITE: case OP_CBREAD: op_cbtap<B, T>(L, I, kp.clock0 + tl0); break;
         case OP_CBWRITEC: case OP_CBREADC: op_cbtapc<B, T>(L, I); break;
         case OP_LDSTALE: {
           float x[B];
@@ -835,7 +864,7 @@ int launch(const DuspKernelParams *kp, int warps_per_cta, cudaStream_t st, int *
 }  // namespace
 
 // --------------------------------------------------------------- launcher
-#define DUSP_CONFIGS(X) X(16, 1) X(8, 1) X(16, 4) X(16, 16) X(8, 32)
+#define DUSP_CONFIGS(X) X(16, 1) X(8, 1) X(8, 4) X(16, 4) X(8, 8) X(16, 8) X(16, 16) X(8, 32)
 
 extern "C" int dusp_launch_supported(int sub_block, int time_lanes) {
 #define X(BV, TV) if (sub_block == BV && time_lanes == TV) return 1;

@@ -96,20 +96,18 @@ struct DuspRing {
 // table ids (waveTables.js:33-40, shapeTables.js:20-38)
 enum { TAB_SIN = 0, TAB_SAW, TAB_SQUARE, TAB_TRIANGLE, TAB_8BIT, TAB_DECAY, TAB_ATTACK, TAB_SEMISINE, TAB_DECAYSQ, TAB_COUNT };
 
-// Device encoding of an instruction (32 bytes).  Programs of up to DUSP_INLINE_INSTR instructions
-// travel inside the kernel parameter block (constant bank: fetched with a uniform LDC, no global load).
+// Device encoding of an instruction (48 bytes, all fields 32-bit: no byte permutes to decode).
+// Programs of up to DUSP_INLINE_INSTR instructions travel inside the kernel parameter block
+// (constant bank: fetched with uniform LDCs, no global load).
 struct __attribute__((aligned(16))) DuspDevInstr {
-  int16_t op;
-  int16_t aux1;
-  int16_t in[5];
-  int16_t out[2];
-  int16_t aux2;
+  int32_t op;
+  int32_t in[5];
+  int32_t out[2];
   int32_t p;
-  int32_t aux0;
-  int32_t pad;
+  int32_t aux0, aux1, aux2;
 };
-static_assert(sizeof(DuspDevInstr) == 32, "DuspDevInstr layout");
-#define DUSP_INLINE_INSTR 112
+static_assert(sizeof(DuspDevInstr) == 48, "DuspDevInstr layout");
+#define DUSP_INLINE_INSTR 80
 
 // One launch renders `n_samples` for every voice of one program group.
 struct DuspKernelParams {
