@@ -27,6 +27,7 @@ SYMBOLS = [
     "dusp_program_disassemble", "dusp_session_create", "dusp_session_destroy", "dusp_session_num_voices",
     "dusp_session_num_channels", "dusp_session_unit_count", "dusp_session_set_params", "dusp_session_reset",
     "dusp_session_render", "dusp_session_launch_count", "dusp_session_launch_info", "dusp_rand53",
+    "dusp_session_tile_info", "dusp_session_warning", "dusp_program_specialise",
 ]
 
 
@@ -71,6 +72,11 @@ def load():
     L.dusp_session_launch_count.argtypes = [c.c_void_p]
     L.dusp_session_launch_count.restype = c.c_longlong
     L.dusp_session_launch_info.argtypes = [c.c_void_p, c.POINTER(c.c_int), c.POINTER(c.c_int), c.POINTER(c.c_int)]
+    L.dusp_session_tile_info.argtypes = [c.c_void_p, c.POINTER(c.c_int), c.POINTER(c.c_int), c.POINTER(c.c_int)]
+    L.dusp_session_warning.argtypes = [c.c_void_p]
+    L.dusp_session_warning.restype = c.c_char_p
+    L.dusp_program_specialise.argtypes = [c.c_void_p, c.c_int, c.c_int, c.c_char_p, c.c_size_t]
+    L.dusp_program_specialise.restype = c.c_size_t
     L.dusp_rand53.argtypes = [c.c_uint64, c.c_uint64]
     L.dusp_rand53.restype = c.c_double
     if L.dusp_abi_version() != 1:
@@ -123,6 +129,15 @@ class Program:
 
     def bytes_per_voice_sample(self, out_mode=OUT_VOICES):
         return load().dusp_program_bytes_per_voice_sample(self._h, out_mode)
+
+    def specialise(self, sub_block=8, time_lanes=4):
+        """(cubin size, generated CUDA source) of the kernel specialised for this circuit shape."""
+        L = load()
+        buf = ctypes.create_string_buffer(1 << 20)
+        n = L.dusp_program_specialise(self._h, sub_block, time_lanes, buf, len(buf))
+        if not n:
+            raise DuspError(L.dusp_last_error().decode())
+        return n, buf.value.decode()
 
     def disassemble(self):
         L = load()
@@ -192,4 +207,7 @@ class Session:
     def launch_info(self):
         g, b, s = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
         load().dusp_session_launch_info(self._h, ctypes.byref(g), ctypes.byref(b), ctypes.byref(s))
-        return {"grid": g.value, "block": b.value, "smem_bytes": s.value}
+        B, T, f = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        load().dusp_session_tile_info(self._h, ctypes.byref(B), ctypes.byref(T), ctypes.byref(f))
+        return {"grid": g.value, "block": b.value, "smem_bytes": s.value, "sub_block": B.value, "time_lanes": T.value,
+                "specialised": bool(f.value), "warning": load().dusp_session_warning(self._h).decode()}

@@ -14,6 +14,7 @@
 
 #include "../../include/dusp_b200.h"
 #include "compile.h"
+#include "fused.h"
 #include "graph.h"
 #include "launch.h"
 
@@ -78,6 +79,7 @@ struct Group {
   std::vector<DuspDevInstr> dev_code;
   DuspDevInstr *d_code = nullptr;
   int sub_block = 16, time_lanes = 1, warps_per_cta = 1;
+  FusedKernel *fused = nullptr;  // specialised straight-line kernel (fused.cc); null -> interpreter
   double *d_words = nullptr;
   float *d_rings = nullptr;
   DuspRing *d_ringtab = nullptr;
@@ -99,7 +101,9 @@ struct dusp_session {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_rendered[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
   long long launches = 0;
+  std::string warning;
   int last_grid = 0, last_block = 0, last_smem = 0;
+  bool last_fused = false;
 };
 
 extern "C" {
@@ -227,6 +231,16 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
       int wpc = n_warps >= 148 * 16 ? 4 : 1;
       while (wpc > 1 && (size_t)g.prog.n_slots * B * 128 * wpc > 100 * 1024) wpc >>= 1;
       g.sub_block = B; g.time_lanes = T; g.warps_per_cta = wpc;
+      // Circuit specialisation (fused.cc): batches get a straight-line kernel compiled for this circuit
+      // shape; single circuits keep the interpreter (no compile latency).  DUSP_FUSED=0/1 forces either.
+      const char *fe = getenv("DUSP_FUSED");
+      const bool want = fe ? atoi(fe) != 0 : voices[i] >= 64;
+      if (want) {
+        std::string err;
+        g.fused = fused_get(g.prog, B, T, B == 8 ? 4 : 2, err);
+        if (!g.fused && fe) return fail(DUSP_ECUDA, "circuit specialisation failed: " + err);
+        if (!g.fused) s->warning = "circuit specialisation unavailable, using the interpreter: " + err;
+      }
     }
     CUDA_TRY(cudaMalloc(&g.d_words, g.h_words.size() * sizeof(double)));
     const size_t ring_bytes = (size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad * sizeof(float);
@@ -319,8 +333,23 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     kp.out_len = n; kp.clock0 = s->clock; kp.n_samples = n;
     const int wpc = g.warps_per_cta;
     int grid = 0, smem = 0;
-    int e = dusp_launch_render(&kp, g.sub_block, g.time_lanes, wpc, st, &grid, &smem);
-    if (e != 0) return fail(DUSP_ECUDA, std::string("render launch: ") + cudaGetErrorString((cudaError_t)e));
+    if (g.fused) {
+      FusedParams fp;
+      memset(&fp, 0, sizeof fp);
+      fp.n_voices = kp.n_voices; fp.voice0 = kp.voice0; fp.nv_stride = kp.nv_stride; fp.words = kp.words;
+      fp.rings = kp.rings; fp.ring_stride = kp.ring_stride; fp.stale = kp.stale; fp.tables = kp.tables; fp.out = kp.out;
+      fp.n_stale = kp.n_stale; fp.out_nch = kp.out_nch; fp.prog_nch = kp.prog_nch; fp.out_mode = kp.out_mode;
+      fp.out_len = kp.out_len; fp.clock0 = kp.clock0; fp.n_samples = kp.n_samples;
+      const int V = 32 / g.time_lanes;
+      const int n_warps = (g.n_voices + V - 1) / V;
+      grid = (n_warps + wpc - 1) / wpc;
+      std::string err;
+      if (fused_launch(g.fused, fp, grid, wpc * 32, st, err) != 0) return fail(DUSP_ECUDA, err);
+    } else {
+      int e = dusp_launch_render(&kp, g.sub_block, g.time_lanes, wpc, st, &grid, &smem);
+      if (e != 0) return fail(DUSP_ECUDA, std::string("render launch: ") + cudaGetErrorString((cudaError_t)e));
+    }
+    s->last_fused = g.fused != nullptr;
     s->launches++;
     s->last_grid = grid; s->last_block = wpc * 32; s->last_smem = smem;
   }
@@ -377,6 +406,24 @@ int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, floa
   CUDA_TRY(cudaStreamSynchronize(s->copy_stream));
   CUDA_TRY(cudaStreamSynchronize(st));
   return DUSP_OK;
+}
+
+int dusp_session_tile_info(const dusp_session *s, int *sub_block, int *time_lanes, int *specialised) {
+  if (!s || s->groups.empty()) return fail(DUSP_EINVAL, "dusp_session_tile_info: empty session");
+  const Group &g = s->groups[0];
+  if (sub_block) *sub_block = g.sub_block;
+  if (time_lanes) *time_lanes = g.time_lanes;
+  if (specialised) *specialised = g.fused != nullptr;
+  return DUSP_OK;
+}
+const char *dusp_session_warning(const dusp_session *s) { return s ? s->warning.c_str() : ""; }
+
+size_t dusp_program_specialise(const dusp_program *p, int sub_block, int time_lanes, char *src_buf, size_t cap) {
+  std::string err, src;
+  size_t n = fused_compile_only(p->prog, sub_block, time_lanes, sub_block == 8 ? 4 : 2, err, &src);
+  if (src_buf && cap) { size_t m = std::min(cap - 1, src.size()); memcpy(src_buf, src.data(), m); src_buf[m] = 0; }
+  if (!n) fail(DUSP_ECUDA, err);
+  return n;
 }
 
 double dusp_rand53(uint64_t seed, uint64_t k) {

@@ -1,0 +1,37 @@
+// fused.h -- circuit specialisation: one straight-line sm_100a kernel per circuit shape,
+// generated from the flat op program and built from the hand-written cores in ops.cuh.
+#pragma once
+#include <string>
+
+#include "compile.h"
+
+namespace dusp {
+
+// Kernel parameter block of a specialised kernel (mirrored textually in the generated source).
+struct FusedParams {
+  int n_voices, voice0;
+  long long nv_stride;
+  double *words;
+  float *rings;
+  long long ring_stride;
+  float *stale;
+  const float *tables;
+  float *out;
+  int n_stale, out_nch, prog_nch, out_mode;
+  long long out_len, clock0, n_samples;
+};
+
+// CUDA C++ source of the specialised kernel `dusp_fused` for tile shape (B, T).
+std::string generate_fused_source(const Program &p, int B, int T, int min_blocks);
+
+struct FusedKernel;  // a loaded module + function (cached per source text, per device)
+
+// Compiles (NVRTC, sm_100a, -fmad=false) and loads the kernel on the current device.  Returns
+// nullptr and fills `err` on failure.  Results are cached for the life of the process.
+FusedKernel *fused_get(const Program &p, int B, int T, int min_blocks, std::string &err);
+// Enqueue; returns 0 or a CUresult/cudaError-like code with `err` filled.
+int fused_launch(FusedKernel *k, const FusedParams &kp, int grid, int block, void *stream, std::string &err);
+// NVRTC only (no device needed): returns the cubin size or 0 with `err` filled.  Used by build checks/tests.
+size_t fused_compile_only(const Program &p, int B, int T, int min_blocks, std::string &err, std::string *src_out);
+
+}  // namespace dusp

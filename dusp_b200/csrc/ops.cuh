@@ -1,0 +1,563 @@
+// ops.cuh -- the per-sample arithmetic of every hot-path unit, as register-level device
+// templates ("cores").  One core = one reference `_tick` for ONE channel, processing the B
+// consecutive samples a lane owns, with unit state passed by reference.
+//
+// Two kernels are built from these cores:
+//   * the specialised render kernel (fused.cc generates one straight-line kernel per circuit
+//     shape that calls the cores with every slot and every state word held in registers; it is
+//     compiled at session creation with NVRTC for sm_100a), and
+//   * (being migrated) the interpreter in render_sm100.cu.
+// The file must stay self-contained: NVRTC compiles it without any CUDA header.
+//
+// Tile model (see render_sm100.cu): a warp renders V voices x T time-lanes, lane (vi, tl) owns
+// samples [tl*B, tl*B+B) of the current tile.  On return from a core EVERY lane of a voice holds
+// the voice's state as of the END of the tile (cores broadcast it from the last time-lane).
+//
+// Rounding contract: every expression is evaluated in IEEE double exactly as the
+// JavaScript does (no FMA contraction: compile with -fmad=false), rounded to binary32 only where
+// the reference stores into a Float32Array.  Reference file:line is cited at each core.
+#pragma once
+
+#ifdef __CUDACC_RTC__
+typedef unsigned int uint32_t;
+typedef int int32_t;
+typedef unsigned long long uint64_t;
+typedef long long int64_t;
+#ifndef NAN
+#define NAN __int_as_float(0x7fffffff)
+#endif
+#else
+#include <stdint.h>
+#include <math.h>
+#endif
+
+#ifndef DUSP_SR
+#define DUSP_SR 44100
+#define DUSP_CHUNK 256
+#define DUSP_TABLE_LEN 44101
+#endif
+
+namespace dops {
+
+#define DOPS_DEV __device__ __forceinline__
+constexpr double SRD = 44100.0;
+
+// ---------------------------------------------------------------- helpers
+DOPS_DEV double js_or0(double x) { return (x != x || x == 0.0) ? 0.0 : x; }  // `x || 0`
+DOPS_DEV float js_or0f(float x) { return (x != x || x == 0.0f) ? 0.0f : x; }
+
+// JS `x % 44100` (= C fmod) with exact fast paths for the common range.
+DOPS_DEV double fmod_sr(double x) {
+  if (x >= 0.0) {
+    if (x < SRD) return x;
+    if (x < 2 * SRD) return x - SRD;  // exact (Sterbenz)
+  } else if (x > -SRD) {
+    return x;
+  } else if (x > -2 * SRD) {
+    return x + SRD;
+  }
+  return fmod(x, SRD);
+}
+// x mod 44100 in [0, 44100) for |x| < 1e12: exact quotient correction with one fma
+DOPS_DEV double posmod_sr(double x) {
+  if (!(fabs(x) < 1.0e12)) { x = fmod(x, SRD); return x < 0.0 ? x + SRD : x; }
+  const double q = floor(x / SRD);
+  double r = fma(-q, SRD, x);
+  if (r < 0.0) r += SRD;
+  if (r >= SRD) r -= SRD;
+  return r;
+}
+// typed-array read `table[i]` with a double index: out of range / NaN -> undefined -> NaN
+DOPS_DEV double tab_read(const float *__restrict__ tab, double idx) {
+  return (idx >= 0.0 && idx <= 44100.0) ? (double)__ldg(tab + (int)idx) : (double)NAN;
+}
+DOPS_DEV bool ring_valid(double idx, double len) { return idx == floor(idx) && idx >= 0.0 && idx < len; }
+DOPS_DEV double ring_read(const float *r, double len, double idx) {
+  return ring_valid(idx, len) ? (double)r[(long long)idx] : (double)NAN;
+}
+// CircleBuffer.js:17-20 index normalisation
+DOPS_DEV double cb_index(double t, double len) {
+  t = floor(fmod(t, len));
+  if (t < 0.0) t += len;
+  return t;
+}
+// injected PRNG (replaces Math.random, Noise.js:10,23): counter-based splitmix64 -> 53-bit uniform
+DOPS_DEV double rand53(uint64_t seed, uint64_t k) {
+  uint64_t z = seed + (k + 1) * 0x9E3779B97F4A7C15ULL;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  z ^= z >> 31;
+  z >>= 11;  // 53 bits; hi 21 + lo 32 recombined exactly with one fma
+  return fma((double)(uint32_t)(z >> 32), 4294967296.0, (double)(uint32_t)z) * (1.0 / 9007199254740992.0);
+}
+DOPS_DEV double dB(double db) { return pow(10.0, db / 20.0); }  // Gain.js:26-28, Pan.js:26-28
+
+// ------------------------------------------------------------------- lane context
+template <int B, int T>
+struct Cx {
+  int tl;    // time-lane 0..T-1
+  int lane;  // 0..31
+  DOPS_DEV int peer(int t) const { return (lane & ~(T - 1)) | t; }
+  DOPS_DEV double from(double x, int t) const { return T == 1 ? x : __shfl_sync(0xffffffffu, x, peer(t)); }
+  DOPS_DEV float from(float x, int t) const { return T == 1 ? x : __shfl_sync(0xffffffffu, x, peer(t)); }
+  // value held by the last time-lane -> every lane of the voice
+  DOPS_DEV void last(double &x) const { if (T > 1) x = __shfl_sync(0xffffffffu, x, peer(T - 1)); }
+  // exclusive prefix sum over the T time-lanes of a voice (exact when the adds are exact)
+  DOPS_DEV double excl_scan(double x) const {
+    double incl = x;
+#pragma unroll
+    for (int o = 1; o < T; o <<= 1) {
+      const double y = __shfl_up_sync(0xffffffffu, incl, o, T);
+      if (tl >= o) incl += y;
+    }
+    const double up = __shfl_up_sync(0xffffffffu, incl, 1, T);
+    return tl == 0 ? 0.0 : up;
+  }
+};
+
+// Serial turns: the T lanes of every voice run `body` one after the other, handing the listed
+// state variables on by shuffle -- exactly the reference's sequential order.  __syncwarp orders
+// ring (global memory) writes of one lane before the next lane's reads.
+template <int B, int T, typename F>
+DOPS_DEV void serial0(const Cx<B, T> &cx, F body) {
+  if (T == 1) { body(); return; }
+#pragma unroll 1
+  for (int turn = 0; turn < T; turn++) {
+    if (cx.tl == turn) body();
+    __syncwarp();
+  }
+}
+template <int B, int T, typename F>
+DOPS_DEV void serial1(const Cx<B, T> &cx, double &s0, F body) {
+  if (T == 1) { body(); return; }
+#pragma unroll 1
+  for (int turn = 0; turn < T; turn++) {
+    if (cx.tl == turn) body();
+    __syncwarp();
+    s0 = cx.from(s0, turn);
+  }
+}
+template <int B, int T, typename F>
+DOPS_DEV void serial3(const Cx<B, T> &cx, double &s0, double &s1, double &s2, F body) {
+  if (T == 1) { body(); return; }
+#pragma unroll 1
+  for (int turn = 0; turn < T; turn++) {
+    if (cx.tl == turn) body();
+    __syncwarp();
+    s0 = cx.from(s0, turn); s1 = cx.from(s1, turn); s2 = cx.from(s2, turn);
+  }
+}
+
+// ------------------------------------------------------------ oscillators
+// Osc.js:35-47 (negfix) / MultiChannelOsc.js:21-38 (!negfix): B samples from phase `ph`.
+template <int B>
+DOPS_DEV void osc_run(float (&f)[B], double &ph, const float *__restrict__ tab, bool negfix) {
+#pragma unroll
+  for (int s = 0; s < B; s++) {
+    ph += (double)f[s];
+    ph = fmod_sr(ph);
+    if (negfix && ph < 0.0) ph += SRD;
+    if (ph >= 0.0 && ph < SRD) {  // the only reachable case for Osc unless f is NaN / Infinity
+      const int i = __double2int_rz(ph);
+      const double fr = ph - (double)i;  // phase % 1
+      const double a = (double)__ldg(tab + i), b = (double)__ldg(tab + i + (fr != 0.0));  // floor / ceil entries
+      f[s] = (float)(a * (1.0 - fr) + b * fr);
+    } else {
+      const double fl = floor(ph), ce = ceil(ph), fr = ph - trunc(ph);
+      f[s] = (float)(tab_read(tab, fl) * (1.0 - fr) + tab_read(tab, ce) * fr);
+    }
+  }
+}
+
+// Osc.js:35-47.  T > 1: phase at a lane's first sample = (phase + all earlier increments) mod 44100,
+// from an exclusive scan of per-lane sums (exact for f32 increments of audio-range magnitude).
+template <int B, int T>
+DOPS_DEV void c_osc(const Cx<B, T> &cx, float (&f)[B], double &ph, const float *__restrict__ tab) {
+  if (T > 1) {
+    double sum = 0.0;
+#pragma unroll
+    for (int s = 0; s < B; s++) sum += (double)f[s];
+    const double before = cx.excl_scan(sum);
+    const bool finite = __all_sync(0xffffffffu, fabs(before + sum) < 1.0e12);
+    if (!finite) {  // NaN / Infinity frequencies: the reference's exact sequential behaviour
+      serial1<B, T>(cx, ph, [&] { osc_run<B>(f, ph, tab, true); });
+      return;
+    }
+    if (cx.tl > 0) ph = posmod_sr(ph + before);
+  }
+  osc_run<B>(f, ph, tab, true);
+  cx.last(ph);
+}
+
+// MultiChannelOsc.js:21-38: truncated-modulo phase has no canonical range -> sequential order only
+template <int B, int T>
+DOPS_DEV void c_mcosc(const Cx<B, T> &cx, float (&f)[B], double &ph, const float *__restrict__ tab) {
+  serial1<B, T>(cx, ph, [&] { osc_run<B>(f, ph, tab, false); });
+}
+
+// -------------------------------------------------------------- envelopes
+// Ramp.js:25-40
+template <int B, int T>
+DOPS_DEV void c_ramp(const Cx<B, T> &cx, float (&o)[B], double &t, double &playing, double dur, double y0, double y1) {
+  if (T > 1 && cx.tl > 0 && playing != 0.0) {
+    // the tl*B steps before this lane's first sample: one literal step, then the closed form of
+    // "count up by one until t passes duration" (after the first step 0 <= t <= duration holds)
+    t += 1.0;
+    if (t > dur) { playing = 0.0; t = dur; }
+    if (t < 0.0) { playing = 0.0; t = 0.0; }
+    if (playing != 0.0) {
+      const double rem = (double)(cx.tl * B - 1);
+      if (t + rem > dur) { t = dur; playing = 0.0; } else t += rem;
+    }
+  }
+#pragma unroll
+  for (int s = 0; s < B; s++) {
+    if (playing != 0.0) {
+      t += 1.0;
+      if (t > dur) { playing = 0.0; t = dur; }
+      if (t < 0.0) { playing = 0.0; t = 0.0; }
+    }
+    o[s] = (float)(y0 + (t / dur) * (y1 - y0));
+  }
+  cx.last(t); cx.last(playing);
+}
+
+// Shape/index.js:28-59.  d: duration in, output out.  t += 1/duration is an inexact f64 sum: serial.
+template <int B, int T>
+DOPS_DEV void c_shape(const Cx<B, T> &cx, float (&d)[B], const float (&mn)[B], const float (&mx)[B], double &t,
+                      double playing, double le, double re, const float *__restrict__ tab) {
+  serial1<B, T>(cx, t, [&] {
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      if (playing != 0.0) t += 1.0 / (double)d[s];
+      const double lo = mn[s], hi = mx[s];
+      double y;
+      if (t <= 0.0) y = le * (hi - lo) + lo;
+      else if (t > SRD) y = re * (hi - lo) + lo;
+      else {
+        const double fr = t - trunc(t);  // t % 1
+        y = lo + (hi - lo) * (tab_read(tab, ceil(t)) * fr + tab_read(tab, floor(t)) * (1.0 - fr));
+      }
+      d[s] = (float)y;
+    }
+  });
+}
+
+// AHD.js:35-76.  a: attack in, output out.
+template <int B, int T>
+DOPS_DEV void c_ahd(const Cx<B, T> &cx, float (&a)[B], const float (&h)[B], const float (&d)[B], double &t,
+                    double &state_d, double &playing_d) {
+  serial3<B, T>(cx, t, state_d, playing_d, [&] {
+    int state = (int)state_d;
+    bool playing = playing_d != 0.0;
+    const double sp = 1.0 / SRD;
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      float y = 0.0f;
+      if (state == 1) {
+        y = (float)t;
+        if (playing) { t += sp / (double)a[s]; if (t >= 1.0) { state++; t -= 1.0; } }
+      } else if (state == 2) {
+        y = 1.0f;
+        if (playing) { t += sp / (double)h[s]; if (t >= 1.0) { state++; t -= 1.0; } }
+      } else if (state == 3) {
+        y = (float)(1.0 - t);
+        if (playing) { t += sp / (double)d[s]; if (t >= 1.0) { state = 0; playing = false; } }
+      }
+      a[s] = y;
+    }
+    state_d = (double)state; playing_d = playing ? 1.0 : 0.0;
+  });
+}
+
+// Timer.js:37-42
+template <int B, int T>
+DOPS_DEV void c_timer(const Cx<B, T> &cx, float (&o)[B], double &t) {
+  serial1<B, T>(cx, t, [&] {
+    const double sp = 1.0 / SRD;
+#pragma unroll
+    for (int s = 0; s < B; s++) { t += sp; o[s] = (float)t; }
+  });
+}
+
+// ------------------------------------------------------------------ noise
+// Noise.js:16-28.  f: frequency in, output out.
+template <int B, int T>
+DOPS_DEV void c_noise(const Cx<B, T> &cx, float (&f)[B], double &ph, double &y, double &draw, uint64_t seed) {
+  serial3<B, T>(cx, ph, y, draw, [&] {
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      ph += (double)f[s];
+      if (ph >= SRD) {
+        ph = 0.0;
+        y = 2.0 * rand53(seed, (uint64_t)draw) - 1.0;
+        draw += 1.0;
+      }
+      f[s] = (float)y;
+    }
+  });
+}
+// Noise.js:16-28 with constant F >= sampleRate: a new draw on every sample; the counter-based
+// stream makes the draws of different time-lanes independent.
+template <int B, int T>
+DOPS_DEV void c_noise1(const Cx<B, T> &cx, float (&o)[B], double &y, double &draw, uint64_t seed) {
+  const uint64_t d0 = (uint64_t)draw + (uint64_t)(cx.tl * B);
+#pragma unroll
+  for (int s = 0; s < B; s++) { y = 2.0 * rand53(seed, d0 + s) - 1.0; o[s] = (float)y; }
+  draw += (double)(T * B);
+  cx.last(y);
+}
+
+// ---------------------------------------------------------------- filters
+// Filter.js:66-84
+DOPS_DEV void filter_coeffs(int hp, double f, double &a0, double &a1, double &a2, double &b1, double &b2) {
+  const double PI = 3.141592653589793;
+  if (!hp) {
+    double lamda = 1.0 / tan(PI * f / SRD), l2 = lamda * lamda;
+    a0 = 1.0 / (1.0 + 2.0 * lamda + l2); a1 = 2.0 * a0; a2 = a0;
+    b1 = 2.0 * a0 * (1.0 - l2); b2 = a0 * (1.0 - 2.0 * lamda + l2);
+  } else {
+    double lamda = tan(PI * f / SRD), l2 = lamda * lamda;
+    a0 = 1.0 / (1.0 + 2.0 * lamda + l2); a1 = 0.0; a2 = -a0;
+    b1 = 2.0 * a0 * (l2 - 1.0); b2 = a0 * (1.0 - 2.0 * lamda + l2);
+  }
+}
+
+struct FilterState {  // Filter.js:17-20 + coefficient cache (:29-32)
+  double a0, a1, a2, b1, b2, lastf, lastdef, x1, x2, y1, y2;
+};
+
+// Filter.js:27-51 with a signal-rate F: coefficients follow f[t], strictly sequential.
+template <int B, int T>
+DOPS_DEV void c_filter(const Cx<B, T> &cx, float (&x)[B], const float (&f)[B], int hp, FilterState &S) {
+  auto body = [&] {
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      const double ft = f[s];
+      if (S.lastdef == 0.0 || ft != S.lastf) { S.lastdef = 1.0; S.lastf = ft; filter_coeffs(hp, ft, S.a0, S.a1, S.a2, S.b1, S.b2); }
+      const double xin = x[s];
+      const double y = S.a0 * xin + S.a1 * js_or0(S.x1) + S.a2 * js_or0(S.x2) - S.b1 * js_or0(S.y1) - S.b2 * js_or0(S.y2);
+      const float yf = (float)y;
+      x[s] = yf;
+      S.y2 = js_or0(S.y1); S.y1 = (double)yf; S.x2 = js_or0(S.x1); S.x1 = xin;
+    }
+  };
+  if (T == 1) { body(); return; }
+#pragma unroll 1
+  for (int turn = 0; turn < T; turn++) {
+    if (cx.tl == turn) body();
+    S.a0 = cx.from(S.a0, turn); S.a1 = cx.from(S.a1, turn); S.a2 = cx.from(S.a2, turn);
+    S.b1 = cx.from(S.b1, turn); S.b2 = cx.from(S.b2, turn); S.lastf = cx.from(S.lastf, turn);
+    S.lastdef = cx.from(S.lastdef, turn); S.x1 = cx.from(S.x1, turn); S.x2 = cx.from(S.x2, turn);
+    S.y1 = cx.from(S.y1, turn); S.y2 = cx.from(S.y2, turn);
+  }
+}
+
+// Filter.js:27-51 with host-derived coefficients (constant F).
+//   y[n] = ((a0 x + a1 x1) + a2 x2) - b1 y1 - b2 y2
+// The bracket depends only on inputs: all lanes at once.  The two subtractions and the f32
+// rounding are the recurrence: the T lanes of a voice run it in turn, handing (y1, y2) on by
+// shuffle -- the same operations in the same order as the reference, so bit-exact.
+// State: x1 raw previous input, x2/y2 already `|| 0`-normalised, y1 previous output (f32-valued).
+template <int B, int T>
+DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1, double a2, double b1, double b2,
+                        double &x1, double &x2, double &y1, double &y2) {
+  double o1 = js_or0(x1), o2 = js_or0(x2), q1 = js_or0(y1), q2 = js_or0(y2);
+  if (T > 1) {  // inputs preceding this lane's first sample come from the previous time-lane
+    const float pm1 = __shfl_up_sync(0xffffffffu, x[B - 1], 1, T), pm2 = __shfl_up_sync(0xffffffffu, x[B - 2], 1, T);
+    if (cx.tl > 0) { o1 = (double)js_or0f(pm1); o2 = (double)js_or0f(pm2); }
+  }
+  double c[B];
+#pragma unroll
+  for (int s = 0; s < B; s++) {
+    const double xin = x[s];
+    c[s] = a0 * xin + a1 * o1 + a2 * o2;
+    o2 = o1; o1 = (double)js_or0f(x[s]);
+  }
+  const double xlast = x[B - 1];
+  auto recur = [&]() {
+    double b2q2 = b2 * q2;
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      const float yf = (float)(c[s] - b1 * q1 - b2q2);
+      x[s] = yf;
+      b2q2 = b2 * q1;  // next sample's b2*y2, ready before it is needed
+      q2 = q1; q1 = (double)js_or0f(yf);
+    }
+  };
+  if (T == 1) {
+    recur();
+  } else {
+#pragma unroll 1
+    for (int turn = 0; turn < T; turn++) {
+      if (cx.tl == turn) recur();
+      const double n1 = cx.from(q1, turn), n2 = cx.from(q2, turn);
+      if (cx.tl == turn + 1) { q1 = n1; q2 = n2; }
+    }
+  }
+  x1 = xlast; x2 = o2; y1 = (double)x[B - 1]; y2 = q2;
+  cx.last(x1); cx.last(x2); cx.last(y1); cx.last(y2);
+}
+
+// ------------------------------------------------------------------ rings
+// FixedDelay.js:14-20 (KIND 0), CombFilter.js:11-17 (1), AllPass.js:8-15 (2).  x: input in, output out.
+template <int B, int T, int KIND>
+DOPS_DEV void c_fixdelay(const Cx<B, T> &cx, float (&x)[B], const float (&g)[B], float *buf, int n, double &tb) {
+  const double len = (double)n;
+  auto step = [&](int p, int s) {
+    const float d = buf[p];
+    if (KIND == 0) { buf[p] = x[s]; x[s] = d; }
+    else if (KIND == 1) { buf[p] = (float)((double)x[s] + (double)d * (double)g[s]); x[s] = d; }
+    else { buf[p] = (float)((double)x[s] + (double)d * (double)g[s]); x[s] = (float)((double)d - (double)x[s] * (double)g[s]); }
+  };
+  if (T > 1 && n >= T * B && tb == floor(tb) && tb >= 0.0 && tb < len) {
+    // every sample of the tile touches its own ring position: no dependence between time-lanes
+    int p = (int)tb + 1 + cx.tl * B;
+    if (p >= n) p -= n;
+#pragma unroll
+    for (int s = 0; s < B; s++) { step(p, s); if (++p == n) p = 0; }
+    double e = (double)(p == 0 ? n - 1 : p - 1);
+    cx.last(e);
+    tb = e;
+    __syncwarp();
+  } else {
+    serial1<B, T>(cx, tb, [&] {
+#pragma unroll
+      for (int s = 0; s < B; s++) {
+        tb += 1.0;
+        if (!(tb < len)) tb = fmod(tb, len);  // (tBuffer + 1) % length
+        step((int)tb, s);
+      }
+    });
+  }
+}
+
+// Delay.js:20-41 (MONO false) / MonoDelay.js:19-30 (MONO true).  Write-ahead scatter-add: later
+// samples read what earlier ones added -> strictly sequential.  t0 = absolute index of x[0].
+template <int B, int T, bool MONO>
+DOPS_DEV void c_delay(const Cx<B, T> &cx, float (&x)[B], const float (&dl)[B], float *buf, int n, long long t0) {
+  const double len = (double)n;
+  serial0<B, T>(cx, [&] {
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      double tb = (double)(t0 + s);
+      if (!(tb < len)) tb = fmod(tb, len);  // (clock + t) % length
+      float y = 0.0f;
+      if (!MONO) { y = (float)ring_read(buf, len, tb); if (ring_valid(tb, len)) buf[(long long)tb] = 0.0f; }
+      double tw = tb + (double)dl[s];  // (tBuffer + delay) % length, exact fast paths for the usual range
+      if (tw >= len) { tw = tw < 2.0 * len ? tw - len : fmod(tw, len); }
+      else if (!(tw > -len)) tw = fmod(tw, len);
+      const double fr = tw - trunc(tw);
+      const double fl = floor(tw);
+      double ce = ceil(tw);
+      if (MONO && !(ce < len && ce > -len)) ce = fmod(ce, len);
+      if (ring_valid(fl, len)) buf[(long long)fl] = (float)((double)buf[(long long)fl] + (double)x[s] * (1.0 - fr));
+      if (ring_valid(ce, len)) buf[(long long)ce] = (float)((double)buf[(long long)ce] + (double)x[s] * fr);
+      if (MONO) { y = (float)ring_read(buf, len, tb); if (ring_valid(tb, len)) buf[(long long)tb] = 0.0f; }
+      x[s] = y;
+    }
+  });
+}
+
+// ReadBackDelay.js:23-43
+template <int B, int T>
+DOPS_DEV void c_readback(const Cx<B, T> &cx, float (&x)[B], const float (&dl)[B], float *buf, int n, double &t) {
+  const double len = (double)n;
+  serial1<B, T>(cx, t, [&] {
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      const double wi = fmod(t + len, len);
+      if (ring_valid(wi, len)) buf[(long long)wi] = x[s];
+      x[s] = (float)ring_read(buf, len, fmod(t - (double)dl[s] + len, len));
+      t += 1.0;
+    }
+  });
+}
+
+// CircleBufferWriter.js:12-25 / CircleBufferReader.js:12-25 with a signal-rate OFFSET (admitted only
+// for a ring with a single tap unit): sequential.  off: offsets in; for a reader, output out.
+template <int B, int T, bool WRITER, bool WIPE, bool HAS_IN>
+DOPS_DEV void c_cbtap(const Cx<B, T> &cx, float (&off)[B], const float (&x)[B], float *buf, int n, double tu, long long t0) {
+  const double len = (double)n;
+  serial0<B, T>(cx, [&] {
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      const double tt = WRITER ? tu + (double)(t0 + s) + SRD * (double)off[s] : tu + (double)(t0 + s) - SRD * (double)off[s];
+      const double i = cb_index(tt, len);
+      float y = NAN;
+      if (ring_valid(i, len)) {
+        if (WRITER) {
+          float v = buf[(long long)i];
+          if (WIPE) v = 0.0f;                                      // preWipe: write(c, tWrite, 0)
+          if (HAS_IN) v = (float)((double)v + (double)x[s]);       // mix: +=
+          buf[(long long)i] = v;
+        } else {
+          y = buf[(long long)i];
+          if (WIPE) buf[(long long)i] = 0.0f;                      // postWipe
+        }
+      }
+      off[s] = y;
+    }
+  });
+}
+
+// Same units with a constant OFFSET: the ring index advances by one per sample; its start value is
+// derived on the host (CircleBuffer.js:17-20 applied to the first access).  idx < 0: never valid.
+// x: writer input in / reader output out.
+template <int B, int T, bool WRITER, bool WIPE, bool HAS_IN>
+DOPS_DEV void c_cbtapc(const Cx<B, T> &cx, float (&x)[B], float *buf, int n, double &idx) {
+  auto run = [&](int i) {
+    if (i + B <= n) {  // no wrap inside the run: plain pointer walk
+      float *q = buf + i;
+      if (!WRITER) {
+#pragma unroll
+        for (int s = 0; s < B; s++) x[s] = q[s];
+        if (WIPE) {
+#pragma unroll
+          for (int s = 0; s < B; s++) q[s] = 0.0f;
+        }
+      } else if (WIPE) {                                           // preWipe: write(0) then mix -> 0 + in
+#pragma unroll
+        for (int s = 0; s < B; s++) q[s] = HAS_IN ? __fadd_rn(0.0f, x[s]) : 0.0f;
+      } else if (HAS_IN) {                                         // mix: `+=` (one f32 add == f64 add + rounding)
+        float v[B];
+#pragma unroll
+        for (int s = 0; s < B; s++) v[s] = q[s];
+#pragma unroll
+        for (int s = 0; s < B; s++) q[s] = __fadd_rn(v[s], x[s]);
+      }
+      i += B;
+      return i == n ? 0 : i;
+    }
+#pragma unroll 1
+    for (int s = 0; s < B; s++) {
+      if (WRITER) {
+        float v = WIPE ? 0.0f : buf[i];
+        if (HAS_IN) v = __fadd_rn(v, x[s]);
+        if (HAS_IN || WIPE) buf[i] = v;
+      } else {
+        x[s] = buf[i];
+        if (WIPE) buf[i] = 0.0f;
+      }
+      if (++i == n) i = 0;
+    }
+    return i;
+  };
+  if (idx < 0.0) {
+    if (!WRITER) {
+#pragma unroll
+      for (int s = 0; s < B; s++) x[s] = NAN;
+    }
+  } else if (T == 1 || n >= T * B) {  // distinct positions within the tile: time-lanes are independent
+    int i = (int)idx + cx.tl * B;
+    if (i >= n) i %= n;
+    double e = (double)run(i);
+    cx.last(e);
+    idx = e;
+    if (T > 1) __syncwarp();
+  } else {
+    serial1<B, T>(cx, idx, [&] { idx = (double)run((int)idx); });
+  }
+}
+
+}  // namespace dops

@@ -121,6 +121,15 @@ long long dusp_session_launch_count(const dusp_session *s);
 /* last launch geometry, for reporting: grid, block, dynamic smem bytes */
 int dusp_session_launch_info(const dusp_session *s, int *grid, int *block, int *smem_bytes);
 
+/* tile shape of the session's first program group (B samples per lane, T time-lanes per voice) and
+ * whether it renders with a kernel specialised for the circuit shape (1) or the interpreter (0) */
+int dusp_session_tile_info(const dusp_session *s, int *sub_block, int *time_lanes, int *specialised);
+const char *dusp_session_warning(const dusp_session *s); /* "" or why specialisation was skipped */
+/* Generates the specialised sm_100a kernel for tile shape (B, T) and compiles it with NVRTC (no GPU
+ * needed).  Returns the cubin size in bytes (0 on failure, see dusp_last_error); when src_buf is
+ * non-NULL the generated CUDA source is copied into it. */
+size_t dusp_program_specialise(const dusp_program *p, int sub_block, int time_lanes, char *src_buf, size_t cap);
+
 /* The injected PRNG (replaces Math.random in Noise.js:10,23): draw k of stream `seed`. */
 double dusp_rand53(uint64_t seed, uint64_t k);
 

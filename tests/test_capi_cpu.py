@@ -40,6 +40,17 @@ def test_every_case_compiles(lib, oracle, name):
     assert "out" in p.disassemble()
 
 
+@pytest.mark.parametrize("name", ["w2_live", "w3_voice", "simple_delay", "transcendental"])
+def test_specialised_kernel_compiles_for_sm100a(lib, name):
+    """fused.cc: the circuit shape becomes one straight-line kernel built from the cores in ops.cuh;
+    NVRTC targets sm_100a and needs no GPU."""
+    blob, _ = circuit_blob(circuits.CASES[name][0]())
+    p = capi.Program(blob)
+    size, src = p.specialise(8, 4)
+    assert size > 1000 and 'extern "C" __global__' in src and "#include \"ops.cuh\"" in src
+    assert src.count("{ // ") == p.num_instructions
+
+
 def test_program_parameters_are_named(lib):
     blob, _ = circuit_blob(circuits.w3_voice())
     p = capi.Program(blob)

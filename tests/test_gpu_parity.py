@@ -25,6 +25,14 @@ def gpu_render(blob, seconds, n_voices=1):
         s.close()
 
 
+@pytest.fixture(params=["interpreter", "specialised"])
+def kernel_mode(request, monkeypatch):
+    """Both device paths: the op-program interpreter (render_sm100.cu) and the straight-line kernel
+    specialised for the circuit shape (fused.cc + ops.cuh, NVRTC).  DUSP_FUSED forces one."""
+    monkeypatch.setenv("DUSP_FUSED", "1" if request.param == "specialised" else "0")
+    return request.param
+
+
 def compare(got, want, exact, what=""):
     assert got.shape[0] == len(want), what
     for c, w in enumerate(want):
@@ -43,7 +51,7 @@ def compare(got, want, exact, what=""):
 
 
 @pytest.mark.parametrize("name", sorted(circuits.CASES))
-def test_case_matches_oracle(lib, oracle, name):
+def test_case_matches_oracle(lib, oracle, name, kernel_mode):
     fac, seconds, exact = circuits.CASES[name]
     blob, _ = circuit_blob(fac())
     compare(gpu_render(blob, seconds)[0], oracle.render(blob, seconds), exact, name)
@@ -77,7 +85,7 @@ def test_ragged_durations(lib, oracle, seconds):
         compare(got, want, True, "ragged %g" % seconds)
 
 
-def test_block_wise_render_continues_state(lib, oracle):
+def test_block_wise_render_continues_state(lib, oracle, kernel_mode):
     blob, _ = circuit_blob(circuits.w3_voice())
     p = capi.Program(blob)
     s = capi.Session([p], [1], 0)
@@ -94,7 +102,19 @@ def unit_index(blob, kind, nth=0):
     return [i for i, k in enumerate(kinds) if k == kind][nth]
 
 
-def test_w2_live_batch_with_per_voice_parameters(lib, oracle):
+@pytest.mark.parametrize("tile", ["8,1", "16,1", "8,4", "8,8", "8,32"])
+@pytest.mark.parametrize("name", ["w2_live", "w3_voice", "simple_delay", "fixed_delays", "envelope_fm", "filter_modulated",
+                                  "noise_sample_hold", "delay_mixer", "ahd_timer", "fm_osc"])
+def test_tile_shapes(lib, oracle, name, tile, kernel_mode, monkeypatch):
+    """Every V x T tile shape must give the reference's result: time-lanes only change how the work
+    is spread over a warp (exact scans, serial turns), never the arithmetic."""
+    monkeypatch.setenv("DUSP_TILE", tile)
+    fac, seconds, exact = circuits.CASES[name]
+    blob, _ = circuit_blob(fac())
+    compare(gpu_render(blob, min(seconds, 0.5))[0], oracle.render(blob, min(seconds, 0.5)), exact, name + "@" + tile)
+
+
+def test_w2_live_batch_with_per_voice_parameters(lib, oracle, kernel_mode):
     """BASELINE config 1 shape (FM ring-mod), 96 voices with their own ramp, bit-exact."""
     rng = np.random.default_rng(1001)
     f0 = rng.uniform(100, 800, 96)
@@ -120,7 +140,7 @@ def w3_overrides(blob, f, dly, g, pan, seeds):
     return names, vals
 
 
-def test_w3_batch_with_per_voice_parameters(lib, oracle):
+def test_w3_batch_with_per_voice_parameters(lib, oracle, kernel_mode):
     """BASELINE config 2 shape: Noise -> LP -> CircleBuffer feedback delay -> Pan, 40 voices."""
     rng = np.random.default_rng(1002)
     n = 40
@@ -151,7 +171,7 @@ def test_w3_batch_with_per_voice_parameters(lib, oracle):
     assert np.max(np.abs(mix - got.astype(np.float64).sum(axis=0))) <= 1e-5 * max(1.0, np.max(np.abs(ref_mix)))
 
 
-def test_multi_program_session(lib, oracle):
+def test_multi_program_session(lib, oracle, kernel_mode):
     cases = ["w2_live", "w3_voice", "fixed_delays", "stereo_concat"]
     blobs = [circuit_blob(circuits.CASES[c][0]())[0] for c in cases]
     progs = [capi.Program(b) for b in blobs]
