@@ -80,6 +80,8 @@ struct Group {
   DuspDevInstr *d_code = nullptr;
   int sub_block = 16, time_lanes = 1, warps_per_cta = 1;
   FusedKernel *fused = nullptr;  // specialised straight-line kernel (fused.cc); null -> interpreter
+  bool piped = false;            // `fused` is the pipelined kernel (piped.cc)
+  PipedInfo pinfo;
   double *d_words = nullptr;
   float *d_rings = nullptr;
   DuspRing *d_ringtab = nullptr;
@@ -190,7 +192,7 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
     g.prog = programs[i]->prog;
     g.n_voices = voices[i];
     g.voice0 = voice0;
-    g.nv_pad = ((long long)voices[i] + 31) / 32 * 32;
+    g.nv_pad = ((long long)voices[i] + 95) / 96 * 96;  // whole warps / whole CTAs of 16, 24 or 32 voices
     voice0 += voices[i];
     s->out_nch = std::max(s->out_nch, g.prog.out_nch);
     s->unit_count += (long long)g.prog.n_units * voices[i];
@@ -223,23 +225,50 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
       for (int t : choices) if (((long long)voices[i] + (32 / t) - 1) / (32 / t) >= 148 * 8) { T = t; break; }
       int B = T == 1 ? 16 : 8;
       if (const char *env = getenv("DUSP_TILE")) { int b = 0, t = 0; if (sscanf(env, "%d,%d", &b, &t) == 2) { B = b; T = t; } }
-      if ((size_t)g.prog.n_slots * B * 128 > 200 * 1024 && T == 1) B = 8;
-      if (!dusp_launch_supported(B, T)) return fail(DUSP_EINVAL, "unsupported tile shape (DUSP_TILE)");
-      if ((size_t)g.prog.n_slots * B * 128 > 220 * 1024)
-        return fail(DUSP_EUNSUPPORTED, "circuit needs more live signal slots than shared memory holds");
-      const long long n_warps = ((long long)voices[i] + (32 / T) - 1) / (32 / T);
-      int wpc = n_warps >= 148 * 16 ? 4 : 1;
-      while (wpc > 1 && (size_t)g.prog.n_slots * B * 128 * wpc > 100 * 1024) wpc >>= 1;
-      g.sub_block = B; g.time_lanes = T; g.warps_per_cta = wpc;
       // Circuit specialisation (fused.cc): batches get a straight-line kernel compiled for this circuit
       // shape; single circuits keep the interpreter (no compile latency).  DUSP_FUSED=0/1 forces either.
       const char *fe = getenv("DUSP_FUSED");
       const bool want = fe ? atoi(fe) != 0 : voices[i] >= 64;
-      if (want) {
+      const bool pow2 = T >= 1 && T <= 32 && (T & (T - 1)) == 0 && (B == 4 || B == 8 || B == 16);
+      // Pipelined kernel (piped.cc): lanes along time for the parallel units, a lane-per-voice warp for the
+      // recurrences.  DUSP_PIPED=0/1 forces it off / on (default: off until a circuit has sequential units).
+      const char *pe = getenv("DUSP_PIPED");
+      if (want && pe && atoi(pe) != 0) {
+        int vc = 0;
+        if (const char *ve = getenv("DUSP_PIPED_VC")) vc = atoi(ve);
+        if (!vc) {  // fewest voices on the fullest SM
+          long long best = 1LL << 60;
+          for (int c : {32, 24, 16}) {
+            const long long ctas = ((long long)voices[i] + c - 1) / c, per_sm = (ctas + 147) / 148 * c;
+            if (per_sm < best) { best = per_sm; vc = c; }
+          }
+        }
         std::string err;
-        g.fused = fused_get(g.prog, B, T, B == 8 ? 4 : 2, err);
+        g.fused = piped_get(g.prog, vc, &g.pinfo, err);
+        if (g.fused) { g.piped = true; g.sub_block = 4; g.time_lanes = 32; g.warps_per_cta = 5; }
+        else s->warning = "pipelined kernel unavailable: " + err;
+      }
+      if (want && pow2 && !g.fused) {
+        // one-warp CTAs (warps never talk to each other); the register budget is set so that the whole
+        // batch is resident at once (no tail wave): W warps per SM, W in [8, 24].  DUSP_FUSED_WPS overrides.
+        const long long n_warps = ((long long)voices[i] + (32 / T) - 1) / (32 / T);
+        int wps = (int)std::min<long long>(24, std::max<long long>(8, (n_warps + 147) / 148));
+        if (const char *we = getenv("DUSP_FUSED_WPS")) wps = std::max(1, atoi(we));
+        std::string err;
+        g.fused = fused_get(g.prog, B, T, wps, err);
         if (!g.fused && fe) return fail(DUSP_ECUDA, "circuit specialisation failed: " + err);
         if (!g.fused) s->warning = "circuit specialisation unavailable, using the interpreter: " + err;
+        if (g.fused) { g.sub_block = B; g.time_lanes = T; g.warps_per_cta = 1; }
+      }
+      if (!g.fused) {
+        if ((size_t)g.prog.n_slots * B * 128 > 200 * 1024 && T == 1) B = 8;
+        if (!dusp_launch_supported(B, T)) return fail(DUSP_EINVAL, "unsupported tile shape (DUSP_TILE)");
+        if ((size_t)g.prog.n_slots * B * 128 > 220 * 1024)
+          return fail(DUSP_EUNSUPPORTED, "circuit needs more live signal slots than shared memory holds");
+        const long long n_warps = ((long long)voices[i] + (32 / T) - 1) / (32 / T);
+        int wpc = n_warps >= 148 * 16 ? 4 : 1;
+        while (wpc > 1 && (size_t)g.prog.n_slots * B * 128 * wpc > 100 * 1024) wpc >>= 1;
+        g.sub_block = B; g.time_lanes = T; g.warps_per_cta = wpc;
       }
     }
     CUDA_TRY(cudaMalloc(&g.d_words, g.h_words.size() * sizeof(double)));
@@ -340,18 +369,24 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
       fp.rings = kp.rings; fp.ring_stride = kp.ring_stride; fp.stale = kp.stale; fp.tables = kp.tables; fp.out = kp.out;
       fp.n_stale = kp.n_stale; fp.out_nch = kp.out_nch; fp.prog_nch = kp.prog_nch; fp.out_mode = kp.out_mode;
       fp.out_len = kp.out_len; fp.clock0 = kp.clock0; fp.n_samples = kp.n_samples;
-      const int V = 32 / g.time_lanes;
-      const int n_warps = (g.n_voices + V - 1) / V;
-      grid = (n_warps + wpc - 1) / wpc;
       std::string err;
-      if (fused_launch(g.fused, fp, grid, wpc * 32, st, err) != 0) return fail(DUSP_ECUDA, err);
+      if (g.piped) {
+        grid = (g.n_voices + g.pinfo.voices_per_cta - 1) / g.pinfo.voices_per_cta;
+        smem = g.pinfo.smem_bytes;
+        if (fused_launch(g.fused, fp, grid, g.pinfo.threads, smem, st, err) != 0) return fail(DUSP_ECUDA, err);
+      } else {
+        const int V = 32 / g.time_lanes;
+        const int n_warps = (g.n_voices + V - 1) / V;
+        grid = (n_warps + wpc - 1) / wpc;
+        if (fused_launch(g.fused, fp, grid, wpc * 32, 0, st, err) != 0) return fail(DUSP_ECUDA, err);
+      }
     } else {
       int e = dusp_launch_render(&kp, g.sub_block, g.time_lanes, wpc, st, &grid, &smem);
       if (e != 0) return fail(DUSP_ECUDA, std::string("render launch: ") + cudaGetErrorString((cudaError_t)e));
     }
     s->last_fused = g.fused != nullptr;
     s->launches++;
-    s->last_grid = grid; s->last_block = wpc * 32; s->last_smem = smem;
+    s->last_grid = grid; s->last_block = g.piped ? g.pinfo.threads : wpc * 32; s->last_smem = smem;
   }
   s->clock += (n + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;
   return DUSP_OK;
@@ -420,7 +455,16 @@ const char *dusp_session_warning(const dusp_session *s) { return s ? s->warning.
 
 size_t dusp_program_specialise(const dusp_program *p, int sub_block, int time_lanes, char *src_buf, size_t cap) {
   std::string err, src;
-  size_t n = fused_compile_only(p->prog, sub_block, time_lanes, sub_block == 8 ? 4 : 2, err, &src);
+  int wps = 8;
+  if (const char *we = getenv("DUSP_FUSED_WPS")) wps = std::max(1, atoi(we));
+  size_t n;
+  const char *pe = getenv("DUSP_PIPED");
+  if (pe && atoi(pe) != 0) {  // the pipelined kernel instead (time_lanes is then the voices per CTA)
+    PipedInfo info;
+    n = piped_compile_only(p->prog, time_lanes, &info, err, &src);
+  } else {
+    n = fused_compile_only(p->prog, sub_block, time_lanes, wps, err, &src);
+  }
   if (src_buf && cap) { size_t m = std::min(cap - 1, src.size()); memcpy(src_buf, src.data(), m); src_buf[m] = 0; }
   if (!n) fail(DUSP_ECUDA, err);
   return n;

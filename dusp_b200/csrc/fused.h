@@ -30,8 +30,19 @@ struct FusedKernel;  // a loaded module + function (cached per source text, per 
 // nullptr and fills `err` on failure.  Results are cached for the life of the process.
 FusedKernel *fused_get(const Program &p, int B, int T, int min_blocks, std::string &err);
 // Enqueue; returns 0 or a CUresult/cudaError-like code with `err` filled.
-int fused_launch(FusedKernel *k, const FusedParams &kp, int grid, int block, void *stream, std::string &err);
+int fused_launch(FusedKernel *k, const FusedParams &kp, int grid, int block, int smem_bytes, void *stream, std::string &err);
 // NVRTC only (no device needed): returns the cubin size or 0 with `err` filled.  Used by build checks/tests.
 size_t fused_compile_only(const Program &p, int B, int T, int min_blocks, std::string &err, std::string *src_out);
+
+// Pipelined kernel (piped.cc): a CTA renders VC voices; four warps run the time-parallel units with lanes along
+// time (coalesced rings / output), a fifth warp runs the time-sequential units (recursive filters ...) one
+// voice per lane, one 128-sample step behind, exchanging signals through swizzled shared memory.
+struct PipedInfo {
+  int voices_per_cta = 0, threads = 0, smem_bytes = 0, n_buffers = 0;
+};
+// "" when the program has no admissible 3-stage split (the caller falls back to the tile kernel).
+std::string generate_piped_source(const Program &p, int voices_per_cta, PipedInfo *info);
+FusedKernel *piped_get(const Program &p, int voices_per_cta, PipedInfo *info, std::string &err);
+size_t piped_compile_only(const Program &p, int voices_per_cta, PipedInfo *info, std::string &err, std::string *src_out);
 
 }  // namespace dusp

@@ -376,6 +376,26 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
   }
   const double xlast = x[B - 1];
   auto recur = [&]() {
+#ifdef DOPS_SPEC_FILTER
+    // The `|| 0` on the fed-back output (Filter.js:45-48) only ever changes a NaN or a -0.  Run the
+    // recurrence without it on the dependency chain, note whether such a value occurred, and in that
+    // (rare) case redo the run from the saved state with the literal form below.
+    const double s1 = q1, s2 = q2;
+    bool odd = false;
+    {
+      double b2q2 = b2 * q2;
+#pragma unroll
+      for (int s = 0; s < B; s++) {
+        const float yf = (float)(c[s] - b1 * q1 - b2q2);
+        x[s] = yf;
+        b2q2 = b2 * q1;
+        q2 = q1; q1 = (double)yf;
+        odd |= (yf != yf) | (__float_as_uint(yf) == 0x80000000u);
+      }
+    }
+    if (!odd) return;
+    q1 = s1; q2 = s2;
+#endif
     double b2q2 = b2 * q2;
 #pragma unroll
     for (int s = 0; s < B; s++) {
@@ -529,8 +549,8 @@ DOPS_DEV void c_cbtapc(const Cx<B, T> &cx, float (&x)[B], float *buf, int n, dou
       i += B;
       return i == n ? 0 : i;
     }
-#pragma unroll 1
-    for (int s = 0; s < B; s++) {
+#pragma unroll
+    for (int s = 0; s < B; s++) {  // the run wraps: sample by sample (x[] stays in registers: constant indices)
       if (WRITER) {
         float v = WIPE ? 0.0f : buf[i];
         if (HAS_IN) v = __fadd_rn(v, x[s]);

@@ -1,0 +1,346 @@
+// piped.cc -- the pipelined render kernel: one CTA renders VC voices, 128 samples per step.
+//
+// Why: inside a 256-sample chunk no unit depends on a later unit (every feedback path of the
+// reference has >= one chunk of latency), so a circuit's op program splits into
+//   stage 0  time-PARALLEL ops that feed the sequential ones       (e.g. Noise)
+//   stage 1  time-SEQUENTIAL ops: recursive filters, envelopes ... (e.g. the biquad recurrence)
+//   stage 2  time-parallel ops that consume them                   (rings, Multiply/Sum, Pan, copy-out)
+// and the stages can run on DIFFERENT steps at the same moment (software pipeline):
+//   * warps 0..3 ("P-warps", VC/4 voices each) run stage 0 of step k+1 and stage 2 of step k-1 with
+//     LANES ALONG TIME: lane l owns samples [4l, 4l+4) of the step, so a warp touches 512 contiguous
+//     bytes of a ring / stale buffer / output row per access (fully coalesced), phase accumulators
+//     are warp-shuffle scans (ops.cuh cores with T = 32);
+//   * warp 4 (the "S-warp") runs stage 1 of step k with ONE VOICE PER LANE: VC independent
+//     recurrences in exactly the reference's sequential order (ops.cuh cores with T = 1), unit
+//     state in registers for the whole launch;
+//   * signals crossing a stage boundary live in shared memory, [rotation 3][buffer][voice][128]
+//     floats; the float4 column is XOR-swizzled with the voice so that both access patterns (a row
+//     per warp / a column per warp) are bank-conflict free;
+//   * one __syncthreads per step.  The recurrences' latency (the bound of this path: VC chains per
+//     S-warp, ~60 cycles per sample) is hidden behind the P-warps' work instead of serialising it.
+// The arithmetic is the same ops.cuh cores the tile kernel uses: results are identical.
+#include <algorithm>
+#include <cstdlib>
+#include <map>
+#include <set>
+#include <sstream>
+#include <vector>
+
+#include "fused.h"
+#include "fusedgen.h"
+
+namespace dusp {
+
+namespace {
+
+constexpr int STEP = 128;  // samples per pipeline step (divides the 256-sample chunk)
+constexpr int PB = 4;      // samples per lane in the P-warps (32 lanes x 4 = STEP) and per S-warp group
+
+// ops with no time-parallel form (or none worth having): they run in the lane-per-voice warp
+bool sequential_only(const Program &p, const DuspInstr &I) {
+  switch (I.op) {
+    case OP_MCOSC: case OP_SHAPE: case OP_AHD: case OP_TIMER: case OP_NOISE: case OP_FILTER: case OP_FILTERC:
+    case OP_DELAY: case OP_MONODELAY: case OP_READBACK: case OP_CBWRITE: case OP_CBREAD:
+      return true;
+    case OP_FIXDELAY: case OP_COMB: case OP_ALLPASS: case OP_CBWRITEC: case OP_CBREADC:
+      return p.rings[I.aux[0]].length < STEP;  // the step's samples would collide inside the ring
+    default:
+      return false;
+  }
+}
+
+// ops that communicate through per-voice memory must stay in one stage (and keep their order)
+int coupling_key(const DuspInstr &I) {
+  switch (I.op) {
+    case OP_FIXDELAY: case OP_COMB: case OP_ALLPASS: case OP_DELAY: case OP_MONODELAY: case OP_READBACK:
+    case OP_CBWRITE: case OP_CBREAD: case OP_CBWRITEC: case OP_CBREADC:
+      return I.aux[0];
+    case OP_LDSTALE: case OP_STSTALE:
+      return 1000000 + I.aux[0];
+    default:
+      return -1;
+  }
+}
+
+struct Cross {       // a value that crosses a stage boundary
+  int def, k;        // defining instruction, output index
+  int slot;
+  int from, to;      // producing stage, last consuming stage
+  bool used_in[3] = {false, false, false};
+  int buf = -1;
+};
+
+struct Plan {
+  std::vector<int> stage;
+  std::vector<Cross> cross;
+  std::map<std::pair<int, int>, int> cross_of;  // (def, k) -> index
+  int n_buffers = 0;
+};
+
+bool make_plan(const Program &p, Plan &pl) {
+  const int n = (int)p.code.size();
+  std::vector<std::vector<std::pair<int, int>>> prod(n);  // per instruction: (def instr, output index) of each slot operand
+  std::map<int, std::pair<int, int>> def_of_slot;
+  for (int i = 0; i < n; i++) {
+    const DuspInstr &I = p.code[i];
+    for (int k = 0; k < 5; k++)
+      if (I.in[k] >= 0) {
+        auto it = def_of_slot.find(I.in[k]);
+        if (it != def_of_slot.end()) prod[i].push_back(it->second);
+      }
+    for (int k = 0; k < 2; k++) if (I.out[k] >= 0) def_of_slot[I.out[k]] = {i, k};
+  }
+  std::vector<char> seq(n), anc(n, 0), desc(n, 0);
+  for (int i = 0; i < n; i++) seq[i] = sequential_only(p, p.code[i]);
+  for (int i = 0; i < n; i++) {  // desc: depends on a sequential op
+    for (auto &d : prod[i]) if (seq[d.first] || desc[d.first]) desc[i] = 1;
+  }
+  for (int i = n - 1; i >= 0; i--) {  // anc: feeds a sequential op
+    if (seq[i] || anc[i]) for (auto &d : prod[i]) anc[d.first] = 1;
+  }
+  pl.stage.assign(n, 2);
+  for (int i = 0; i < n; i++) pl.stage[i] = seq[i] ? 1 : (anc[i] && desc[i]) ? 1 : anc[i] ? 0 : 2;
+  // fixed point: consumers never run before producers; memory-coupled ops share a stage
+  for (int round = 0; round < 64; round++) {
+    bool changed = false;
+    std::map<int, int> group_max;
+    for (int i = 0; i < n; i++) { int key = coupling_key(p.code[i]); if (key >= 0) group_max[key] = std::max(group_max[key], pl.stage[i]); }
+    for (int i = 0; i < n; i++) {
+      int s = pl.stage[i];
+      int key = coupling_key(p.code[i]);
+      if (key >= 0) s = std::max(s, group_max[key]);
+      for (auto &d : prod[i]) s = std::max(s, pl.stage[d.first]);
+      if (s != pl.stage[i]) { pl.stage[i] = s; changed = true; }
+    }
+    if (!changed) break;
+  }
+  for (int i = 0; i < n; i++) if (seq[i] && pl.stage[i] != 1) return false;  // a sequential op behind stage-2 data: needs > 3 stages
+  // crossing values
+  for (int i = 0; i < n; i++)
+    for (auto &d : prod[i]) {
+      if (pl.stage[i] == pl.stage[d.first]) continue;
+      auto key = std::make_pair(d.first, d.second);
+      if (!pl.cross_of.count(key)) {
+        Cross c;
+        c.def = d.first; c.k = d.second; c.slot = p.code[d.first].out[d.second]; c.from = pl.stage[d.first]; c.to = pl.stage[i];
+        pl.cross_of[key] = (int)pl.cross.size();
+        pl.cross.push_back(c);
+      }
+      Cross &c = pl.cross[pl.cross_of[key]];
+      c.to = std::max(c.to, pl.stage[i]);
+      c.used_in[pl.stage[i]] = true;
+    }
+  // buffers: a stage-1 output may take over the buffer of a stage-0 value that dies in stage 1
+  // (the S-warp loads a 4-sample group before it stores into it)
+  std::vector<int> reusable;
+  for (auto &c : pl.cross) if (c.from == 0) { c.buf = pl.n_buffers++; if (c.to == 1) reusable.push_back(c.buf); }
+  for (auto &c : pl.cross) if (c.from == 1) {
+    if (!reusable.empty()) { c.buf = reusable.back(); reusable.pop_back(); }
+    else c.buf = pl.n_buffers++;
+  }
+  return true;
+}
+
+}  // namespace
+
+std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
+  if (VC < 8 || VC > 32 || VC % 8) return "";
+  Plan pl;
+  if (!make_plan(p, pl)) return "";
+  const int n = (int)p.code.size();
+  const int NB = pl.n_buffers;
+
+  // ---- the three stage bodies
+  Gen g0(p, PB, 32), g1(p, PB, 1), g2(p, PB, 32);
+  Gen *gens[3] = {&g0, &g1, &g2};
+  std::ostringstream s_decl, s_load, s_store;  // S-warp: crossing loads first, stores last (in-place buffer reuse)
+  for (int st = 0; st < 3; st++) {
+    Gen &g = *gens[st];
+    for (int i = 0; i < n; i++) {
+      const DuspInstr &I = p.code[i];
+      if (pl.stage[i] == st) {
+        g.instr(i, I);
+        for (int k = 0; k < 2; k++) {
+          auto it = pl.cross_of.find({i, k});
+          if (it == pl.cross_of.end()) continue;
+          const Cross &c = pl.cross[it->second];
+          if (st == 1) {
+            s_decl << "        float xo" << i << "_" << k << "[B];\n";
+            g.o << "      CP(xo" << i << "_" << k << ", s" << c.slot << ")\n";
+            s_store << "        STX(" << c.buf << ", xo" << i << "_" << k << ")\n";
+          } else {
+            g.o << "      STX(" << c.buf << ", s" << c.slot << ")\n";
+          }
+        }
+      } else if (pl.stage[i] < st) {
+        for (int k = 0; k < 2; k++) {
+          auto it = pl.cross_of.find({i, k});
+          if (it == pl.cross_of.end() || !pl.cross[it->second].used_in[st]) continue;
+          const Cross &c = pl.cross[it->second];
+          if (st == 1) {
+            s_load << "        float xi" << i << "_" << k << "[B]; LDX(xi" << i << "_" << k << ", " << c.buf << ")\n";
+            g.o << "      CP(s" << c.slot << ", xi" << i << "_" << k << ")  // value of instruction " << i << " (stage " << c.from << ")\n";
+          } else {
+            g.o << "      LDX(s" << c.slot << ", " << c.buf << ")  // value of instruction " << i << " (stage " << c.from << ")\n";
+          }
+        }
+      }
+    }
+  }
+  std::set<int> p_words, p_mut, s_words, s_mut;
+  for (int st : {0, 2}) { p_words.insert(gens[st]->used_words.begin(), gens[st]->used_words.end()); p_mut.insert(gens[st]->mutable_words.begin(), gens[st]->mutable_words.end()); }
+  s_words = g1.used_words; s_mut = g1.mutable_words;
+  std::map<int, int> pj;  // word -> row of the shared-memory word table
+  for (int w : p_words) { int j = (int)pj.size(); pj[w] = j; }
+  const int NPW = (int)pj.size();
+  const size_t xb_bytes = (size_t)3 * NB * VC * STEP * sizeof(float);
+  const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double);
+  if (smem > 200 * 1024) return "";
+  if (info) { info->voices_per_cta = VC; info->threads = 160; info->smem_bytes = (int)smem; info->n_buffers = NB; }
+  int min_blocks = (int)std::min<size_t>(4, (220 * 1024) / (smem + 1024));
+  if (min_blocks < 1) min_blocks = 1;
+
+  bool stage_has[3] = {false, false, false};
+  for (int i = 0; i < n; i++) stage_has[pl.stage[i]] = true;
+
+  std::ostringstream s;
+  s << "// generated by libdusp_b200 (piped.cc) -- pipelined render kernel for one circuit shape\n"
+    << "// stages:";
+  for (int i = 0; i < n; i++) s << " " << i << ":" << op_name(p.code[i].op) << "=" << pl.stage[i];
+  s << "\n" << fused_prelude()
+    << "#define LDX(d, b) { const float4 t_ = xs[(b) * (VC * 32)]; d[0] = t_.x; d[1] = t_.y; d[2] = t_.z; d[3] = t_.w; }\n"
+    << "#define STX(b, v) xs[(b) * (VC * 32)] = make_float4(v[0], v[1], v[2], v[3]);\n"
+    // renderChannelData.js:42-44 for the P-warps: lanes along time, a warp stores 512 contiguous bytes
+    << "#define OUT_CHANNEL_P(a, CH) { UNROLL for (int i_ = 0; i_ < B; i_++) a[i_] = js_or0f(a[i_]);\\\n"
+    << "  if (kp.out_mode == 0) { if (active) { float *dst = out_row + (long long)(CH) * kp.out_len + tl0;\\\n"
+    << "      if (tl0 + B <= kp.n_samples && (kp.out_len & 3) == 0) __stcs(reinterpret_cast<float4 *>(dst), make_float4(a[0], a[1], a[2], a[3]));\\\n"
+    << "      else { UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) dst[i_] = a[i_]; } } }\\\n"
+    << "  else if ((CH) < 2 && active) { UNROLL for (int i_ = 0; i_ < B; i_++) macc[CH][i_] += a[i_]; } }\n"
+    // same for the S-warp (one voice per lane)
+    << "#define OUT_CHANNEL_S(a, CH) { UNROLL for (int i_ = 0; i_ < B; i_++) a[i_] = js_or0f(a[i_]);\\\n"
+    << "  if (kp.out_mode == 0) { if (active) { float *dst = out_row + (long long)(CH) * kp.out_len + tl0;\\\n"
+    << "      UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) dst[i_] = a[i_]; } }\\\n"
+    << "  else if ((CH) < 2 && active) { UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) {\\\n"
+    << "      atomicAdd(kp.out + (long long)(CH) * kp.out_len + tl0 + i_, a[i_]);\\\n"
+    << "      if (kp.prog_nch == 1) atomicAdd(kp.out + kp.out_len + tl0 + i_, a[i_]); } } }\n"
+    << "extern \"C\" __global__ void __launch_bounds__(160, " << min_blocks << ") dusp_piped(const __grid_constant__ FusedParams kp) {\n"
+    << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", VW = VC / 4;\n"
+    << "  extern __shared__ float4 smem4[];\n"
+    << "  float4 *const xb = smem4;                                                   // [3][NB][VC][32] float4, swizzled\n"
+    << "  double *const pw = reinterpret_cast<double *>(smem4 + 3 * NB * VC * 32);  // [" << NPW << "][VC] words of the P-warps' units\n"
+    << "  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;\n"
+    << "  const long long v0 = (long long)blockIdx.x * VC;  // allocations are padded to a multiple of 96 voices\n"
+    << "  const size_t nv = (size_t)kp.nv_stride;\n"
+    << "  const float *const tables = kp.tables; (void)tables; (void)xb; (void)pw;\n"
+    << "  const long long n_proc = (kp.n_samples + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;  // whole chunks, like Circuit.tick\n"
+    << "  const int n_steps = (int)(n_proc / STEP);\n";
+  for (auto &kv : pj)
+    s << "  if (wib == " << kv.second % 5 << " && lane < VC) pw[" << kv.second << " * VC + lane] = kp.words[" << kv.first << " * nv + v0 + lane];  // "
+      << p.words[kv.first].name << "\n";
+  s << "  __syncthreads();\n"
+    << "  if (wib < 4) {\n"
+    << "    // ---------------- P-warps: lanes along time, VW voices each\n"
+    << "    constexpr int T = 32;\n"
+    << "    Cx<B, T> cx; cx.tl = lane; cx.lane = lane;\n"
+    << "    _Pragma(\"unroll 1\")\n"
+    << "    for (int it = 0; it < n_steps + 2; it++) {\n"
+    << "      const bool do0 = it < n_steps, do2 = it >= 2;\n"
+    << "      const int rot0 = it % 3, rot2 = (it + 1) % 3;  // (it - 2) mod 3\n"
+    << "      float macc[2][B]; UNROLL for (int i_ = 0; i_ < B; i_++) { macc[0][i_] = 0.0f; macc[1][i_] = 0.0f; }\n"
+    << "      _Pragma(\"unroll 1\")\n"
+    << "      for (int j = 0; j < VW; j++) {\n"
+    << "        const int vl = wib * VW + j;\n"
+    << "        const long long v = v0 + vl;\n"
+    << "        const bool active = v < kp.n_voices;\n"
+    << "        float *const rings = kp.rings + v * kp.ring_stride;\n"
+    << "        float *const stale = kp.stale + v * (long long)kp.n_stale * DUSP_CHUNK;\n"
+    << "        float *const out_row = kp.out + (long long)(kp.voice0 + v) * kp.out_nch * kp.out_len;\n"
+    << "        (void)rings; (void)stale; (void)out_row; (void)active;\n";
+  for (auto &kv : pj) s << "        double w" << kv.first << " = pw[" << kv.second << " * VC + vl];\n";
+  s << "#define OUT_CHANNEL OUT_CHANNEL_P\n";
+  const char *rot[3] = {"rot0", "", "rot2"};
+  const char *cond[3] = {"do0", "", "do2"};
+  const char *when[3] = {"it", "", "(it - 2)"};
+  for (int st : {0, 2}) {
+    if (!stage_has[st]) continue;
+    s << "        if (" << cond[st] << ") {  // ---- stage " << st << "\n"
+      << "          const long long tl0 = (long long)" << when[st] << " * STEP + lane * B;\n"
+      << "          const int cpos = (int)(tl0 & (DUSP_CHUNK - 1)); (void)cpos;\n"
+      << "          float4 *const xs = xb + ((size_t)" << rot[st] << " * NB * VC + vl) * 32 + (lane ^ (vl & 7)); (void)xs;\n";
+    for (int k = 0; k < p.n_slots; k++) s << "          float s" << k << "[B];\n";
+    s << gens[st]->o.str() << "        }\n";
+  }
+  s << "#undef OUT_CHANNEL\n";
+  if (!p_mut.empty()) {
+    s << "        __syncwarp();\n        if (lane == 0) {\n";
+    for (int w : p_mut) s << "          pw[" << pj[w] << " * VC + vl] = w" << w << ";\n";
+    s << "        }\n        __syncwarp();\n";
+  }
+  s << "      }\n"
+    << "      if (do2 && kp.out_mode != 0) {  // stereo mixdown of this warp's voices: one atomic per sample and channel\n"
+    << "        const long long t2 = (long long)(it - 2) * STEP + lane * B;\n"
+    << "        UNROLL for (int i_ = 0; i_ < B; i_++) if (t2 + i_ < kp.n_samples) {\n"
+    << "          atomicAdd(kp.out + t2 + i_, macc[0][i_]);\n"
+    << "          atomicAdd(kp.out + kp.out_len + t2 + i_, kp.prog_nch == 1 ? macc[0][i_] : macc[1][i_]);\n"
+    << "        }\n"
+    << "      }\n"
+    << "      __syncthreads();\n"
+    << "    }\n"
+    << "  } else {\n"
+    << "    // ---------------- S-warp: one voice per lane, the reference's sequential order\n"
+    << "    constexpr int T = 1;\n"
+    << "    Cx<B, T> cx; cx.tl = 0; cx.lane = lane;\n"
+    << "    const int vl = lane < VC ? lane : VC - 1;\n"
+    << "    const long long v = v0 + vl;\n"
+    << "    const bool active = lane < VC && v < kp.n_voices;\n"
+    << "    float *const rings = kp.rings + v * kp.ring_stride;\n"
+    << "    float *const stale = kp.stale + v * (long long)kp.n_stale * DUSP_CHUNK;\n"
+    << "    float *const out_row = kp.out + (long long)(kp.voice0 + v) * kp.out_nch * kp.out_len;\n"
+    << "    (void)rings; (void)stale; (void)out_row; (void)active;\n";
+  for (int w : s_words) s << "    double w" << w << " = kp.words[" << w << " * nv + v];  // " << p.words[w].name << "\n";
+  s << "#define OUT_CHANNEL OUT_CHANNEL_S\n"
+    << "    _Pragma(\"unroll 1\")\n"
+    << "    for (int it = 0; it < n_steps + 2; it++) {\n";
+  if (stage_has[1]) {
+    s << "      if (it >= 1 && it <= n_steps && lane < VC) {\n"
+      << "        const int rot1 = (it + 2) % 3;  // (it - 1) mod 3\n"
+      << "        _Pragma(\"unroll 2\")\n"
+      << "        for (int g = 0; g < STEP / B; g++) {\n"
+      << "          const long long tl0 = (long long)(it - 1) * STEP + g * B;\n"
+      << "          const int cpos = (int)(tl0 & (DUSP_CHUNK - 1)); (void)cpos;\n"
+      << "          float4 *const xs = xb + ((size_t)rot1 * NB * VC + vl) * 32 + (g ^ (vl & 7)); (void)xs;\n";
+    for (int k = 0; k < p.n_slots; k++) s << "          float s" << k << "[B];\n";
+    s << s_decl.str() << s_load.str() << g1.o.str() << s_store.str() << "        }\n      }\n";
+  }
+  s << "      __syncthreads();\n"
+    << "    }\n"
+    << "#undef OUT_CHANNEL\n";
+  if (!s_mut.empty()) {
+    s << "    if (lane < VC) {\n";
+    for (int w : s_mut) s << "      kp.words[" << w << " * nv + v] = w" << w << ";\n";
+    s << "    }\n";
+  }
+  s << "  }\n";
+  if (!p_mut.empty()) {
+    s << "  __syncthreads();\n";
+    for (int w : p_mut)
+      s << "  if (wib == " << pj[w] % 5 << " && lane < VC) kp.words[" << w << " * nv + v0 + lane] = pw[" << pj[w] << " * VC + lane];\n";
+  }
+  s << "}\n";
+  return s.str();
+}
+
+size_t piped_compile_only(const Program &p, int VC, PipedInfo *info, std::string &err, std::string *src_out) {
+  const std::string src = generate_piped_source(p, VC, info);
+  if (src_out) *src_out = src;
+  if (src.empty()) { err = "the circuit has no 3-stage split"; return 0; }
+  return fused_build_cubin(src, err);
+}
+
+FusedKernel *piped_get(const Program &p, int VC, PipedInfo *info, std::string &err) {
+  const std::string src = generate_piped_source(p, VC, info);
+  if (src.empty()) { err = "the circuit has no 3-stage split"; return nullptr; }
+  return fused_build(src, "dusp_piped", err);
+}
+
+}  // namespace dusp

@@ -662,7 +662,7 @@ __global__ void __launch_bounds__(128, B == 8 ? 4 : 2) dusp_render_tile(const __
   const int warp = blockIdx.x * (blockDim.x >> 5) + wib;
   if ((long long)warp * V >= kp.n_voices) return;
   const int vi = lane / T, tl = lane % T;
-  const long long v = (long long)warp * V + vi;  // voice (allocations are padded to a multiple of 32)
+  const long long v = (long long)warp * V + vi;  // voice (allocations are padded to a multiple of 96)
   const bool active = v < kp.n_voices;
 
   Lane<B, T> L;

@@ -25,11 +25,14 @@ def gpu_render(blob, seconds, n_voices=1):
         s.close()
 
 
-@pytest.fixture(params=["interpreter", "specialised"])
+@pytest.fixture(params=["interpreter", "specialised", "pipelined"])
 def kernel_mode(request, monkeypatch):
-    """Both device paths: the op-program interpreter (render_sm100.cu) and the straight-line kernel
-    specialised for the circuit shape (fused.cc + ops.cuh, NVRTC).  DUSP_FUSED forces one."""
-    monkeypatch.setenv("DUSP_FUSED", "1" if request.param == "specialised" else "0")
+    """The device paths: the op-program interpreter (render_sm100.cu), the straight-line tile kernel
+    specialised for the circuit shape (fused.cc + ops.cuh, NVRTC) and the pipelined kernel (piped.cc:
+    lanes along time for the parallel units, a lane-per-voice warp for the recurrences; circuits with
+    no 3-stage split fall back to the tile kernel).  DUSP_FUSED / DUSP_PIPED force one."""
+    monkeypatch.setenv("DUSP_FUSED", "0" if request.param == "interpreter" else "1")
+    monkeypatch.setenv("DUSP_PIPED", "1" if request.param == "pipelined" else "0")
     return request.param
 
 
