@@ -228,7 +228,7 @@ def run_b200(args, rank, world, local_rank):
     avg_launch_ms = sum(full) / len(full)
     achieved = bpvs * nv * blk / (avg_launch_ms / 1e3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": None, "peak_source": peak_src, "kernel": "dusp_render_lane_per_voice",
+                "traffic": None, "peak_source": peak_src, "kernel": "dusp_piped" if sess.launch_info().get("block") == 160 else "dusp_fused",
                 "bytes_per_voice_sample": bpvs, "avg_launch_ms": avg_launch_ms,
                 "kernel_share_of_step": sum(launch_ms) / total_ms}
 

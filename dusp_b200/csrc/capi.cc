@@ -231,9 +231,9 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
       const bool want = fe ? atoi(fe) != 0 : voices[i] >= 64;
       const bool pow2 = T >= 1 && T <= 32 && (T & (T - 1)) == 0 && (B == 4 || B == 8 || B == 16);
       // Pipelined kernel (piped.cc): lanes along time for the parallel units, a lane-per-voice warp for the
-      // recurrences.  DUSP_PIPED=0/1 forces it off / on (default: off until a circuit has sequential units).
+      // recurrences.  Default for batches; circuits without a 3-stage split use the tile kernel.  DUSP_PIPED=0/1 forces.
       const char *pe = getenv("DUSP_PIPED");
-      if (want && pe && atoi(pe) != 0) {
+      if (want && (pe ? atoi(pe) != 0 : voices[i] >= 64)) {
         int vc = 0;
         if (const char *ve = getenv("DUSP_PIPED_VC")) vc = atoi(ve);
         if (!vc) {  // fewest voices on the fullest SM
@@ -246,7 +246,7 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
         std::string err;
         g.fused = piped_get(g.prog, vc, &g.pinfo, err);
         if (g.fused) { g.piped = true; g.sub_block = 4; g.time_lanes = 32; g.warps_per_cta = 5; }
-        else s->warning = "pipelined kernel unavailable: " + err;
+        else if (pe) s->warning = "pipelined kernel unavailable: " + err;
       }
       if (want && pow2 && !g.fused) {
         // one-warp CTAs (warps never talk to each other); the register budget is set so that the whole
@@ -312,7 +312,7 @@ int dusp_session_set_params(dusp_session *s, int gi, const int *ids, int n_ids, 
       const double x = values[(size_t)v * n_ids + k];
       g.h_words[(size_t)ids[k] * g.nv_pad + v] = p.f32 ? (double)(float)x : x;
     }
-  if (!g.prog.tap_pairs.empty() || !g.prog.locked.empty()) {
+  if (!g.prog.tap_pairs.empty() || !g.prog.locked.empty() || !g.prog.equal_words.empty()) {
     // per-voice values must keep what the compiler proved / specialised on (compile.cc)
     std::vector<double> wv(nw);
     for (int v = 0; v < g.n_voices; v++) {

@@ -35,7 +35,7 @@ const char *OP_NAMES[OP_COUNT] = {
     "nop", "copy", "neg", "abs", "s2s", "semi", "db2s", "midi2f", "fixmul", "mul", "div", "pow", "add", "sub",
     "gain", "clip", "hca", "hcb", "rescale", "xfade", "pan", "vecmag", "osc", "mcosc", "ramp", "shape", "ahd",
     "timer", "noise", "filter", "fixdelay", "comb", "allpass", "delay", "monodelay", "readback", "cbwrite",
-    "cbread", "ldstale", "ststale", "out", "filterc", "panc", "gainc", "noise1", "cbwritec", "cbreadc"};
+    "cbread", "ldstale", "ststale", "out", "filterc", "panc", "gainc", "noise1", "cbwritec", "cbreadc", "add0"};
 
 struct Opnd {
   int kind = 0;  // 0 none (reads 0), 1 value, 2 const word
@@ -208,7 +208,7 @@ Program compile(const Graph &g) {
   std::map<std::pair<int, int>, int> cb_ring;  // (buffer, channel) -> ring id
   for (size_t bi = 0; bi < g.cbs.size(); bi++)
     for (int c = 0; c < g.cbs[bi].nch; c++) cb_ring[{(int)bi, c}] = b.ring(g.cbs[bi].len);
-  struct Tap { int unit; bool writer; Opnd off; };
+  struct Tap { int unit; bool writer; Opnd off; int ir; };
   std::map<int, std::vector<Tap>> taps;  // ring -> taps (for the reordering check)
 
   for (int ui : g.order) {
@@ -445,7 +445,7 @@ Program compile(const Graph &g) {
         r.aux[1] = (int)u.num(writer ? "preWipe" : "postWipe", 0);
         r.root = writer || r.aux[1];
         if (!writer) b.def(r, 0, ui, 0, c);
-        taps[r.aux[0]].push_back({ui, writer || r.aux[1] != 0, r.in[0]});
+        taps[r.aux[0]].push_back({ui, writer || r.aux[1] != 0, r.in[0], (int)b.ir.size() - 1});
         b.prog.ring_bytes_per_sample += writer ? (r.aux[1] ? 4 : 8) : (r.aux[1] ? 8 : 4);
       }
     } else {
@@ -457,6 +457,7 @@ Program compile(const Graph &g) {
   // Two different units touching one ring see the same samples in the same
   // order as the reference (unit after unit per 256-chunk) iff their constant
   // time shifts are equal or at least one chunk apart on the ring.
+  std::set<int> not_hoistable;
   for (auto &kv : taps) {
     auto &tv = kv.second;
     long long len = b.prog.rings[kv.first].length;
@@ -468,14 +469,59 @@ Program compile(const Graph &g) {
         if (tv[i].off.kind != 2 || tv[j].off.kind != 2)
           throw Unsupported("CircleBuffer taps with signal-rate OFFSET sharing a buffer");
         auto sign = [&](const Tap &t) { return g.units[t.unit].kind == "CircleBufferWriter" ? 1 : -1; };
-        b.prog.tap_pairs.push_back({tv[i].off.id, tv[j].off.id, sign(tv[i]), sign(tv[j]), len});
+        TapPair tp{tv[i].off.id, tv[j].off.id, sign(tv[i]), sign(tv[j]), len};
+        if (!tv[i].writer || !tv[j].writer) {  // plain reader vs writer: strict when apart by default
+          double sa = tp.sign_a * (double)DUSP_SR * (double)(float)b.prog.words[tp.word_a].dflt;
+          double sb = tp.sign_b * (double)DUSP_SR * (double)(float)b.prog.words[tp.word_b].dflt;
+          double d = std::fmod(std::fabs(sa - sb), (double)len);
+          d = std::min(d, (double)len - d);
+          tp.strict = d >= DUSP_CHUNK;
+          if (!tp.strict) not_hoistable.insert(!tv[i].writer ? tv[i].ir : tv[j].ir);
+        }
+        b.prog.tap_pairs.push_back(tp);
       }
+    // a plain constant-offset reader whose every writer stays a chunk or more away: its ring loads do not
+    // depend on anything the same step stores, so a kernel may issue them early (aux[2] = 1)
+    for (auto &t : tv)
+      if (!t.writer && t.off.kind == 2 && !not_hoistable.count(t.ir) && b.ir[t.ir].op == OP_CBREADC) b.ir[t.ir].aux[2] = 1;
   }
   {
     std::vector<double> dv;
     for (auto &w : b.prog.words) dv.push_back(w.dflt);
     std::string msg = b.prog.check_taps(dv.data());
     if (!msg.empty()) throw Unsupported(msg);
+  }
+
+  // ---- peephole: preWipe writer + mixing writer on the same ring position -> one writer ----
+  // MultiTapDelay.addFeedback (MultiTapDelay.js:35-43) mixes the feedback into the position the input
+  // writer has just wiped and written.  With no other tap on that ring ticking in between, the pair
+  // leaves (0 + a) + b there: one store instead of store, load, add, store.  Needs the second input
+  // to be available where the first writer ticks (same fresh / stale status at both positions).
+  if (!getenv("DUSP_NO_WRITER_MERGE")) {
+    std::map<int, std::vector<int>> ring_ops;
+    for (size_t i = 0; i < b.ir.size(); i++)
+      if (b.ir[i].op == OP_CBWRITEC || b.ir[i].op == OP_CBREADC || b.ir[i].op == OP_CBWRITE || b.ir[i].op == OP_CBREAD)
+        ring_ops[b.ir[i].aux[0]].push_back((int)i);
+    for (auto &kv : ring_ops)
+      for (size_t k = 0; k + 1 < kv.second.size(); k++) {
+        const int i = kv.second[k], j = kv.second[k + 1];
+        IR &wi = b.ir[i], &wj = b.ir[j];
+        if (wi.op != OP_CBWRITEC || wj.op != OP_CBWRITEC || wi.aux[1] != 1 || wj.aux[1] != 0) continue;
+        if (wi.in[1].kind == 0 || wj.in[1].kind == 0) continue;
+        const Param &oi = b.prog.words[wi.in[0].id], &oj = b.prog.words[wj.in[0].id];
+        if ((float)oi.dflt != (float)oj.dflt || b.prog.words[wi.p].dflt != b.prog.words[wj.p].dflt) continue;
+        const Opnd bo = wj.in[1];
+        if (bo.kind == 1) { const int d = b.vals[bo.id].def; if (!(d >= 0 && d < i) && !(d >= j)) continue; }
+        b.prog.equal_words.push_back({wi.in[0].id, wj.in[0].id});
+        b.prog.equal_words.push_back({wi.p, wj.p});
+        b.vals.push_back({wi.unit, -1, wi.chan, i});
+        const int tmp = (int)b.vals.size() - 1;
+        const Opnd a = wi.in[1];
+        wi = IR();
+        wi.op = OP_ADD0; wi.in[0] = a; wi.in[1] = bo; wi.outv[0] = tmp; wi.unit = wj.unit; wi.chan = wj.chan; wi.pos = wj.pos;
+        wj.in[1].kind = 1; wj.in[1].id = tmp;
+        wj.aux[1] = 1;
+      }
   }
 
   // ---- rendered outlet -> OUT instructions ----
@@ -620,6 +666,9 @@ std::string Program::check_taps(const double *wv) const {
     d = std::min(d, (double)t.ring_len - d);
     if (d != 0 && d < DUSP_CHUNK)
       return "CircleBuffer taps closer than one 256-sample chunk (intra-chunk ordering differs from the reference)";
+    if (d == 0 && t.strict)
+      return "CircleBuffer reader OFFSET coincides with a writer's: the program was compiled with these taps apart "
+             "(compile it with the coinciding offsets as the inlet constants instead)";
   }
   return "";
 }
@@ -667,6 +716,10 @@ void derive_words(const Program &p, double *w, long long stride) {
 }
 
 std::string Program::check_locked(const double *wv) const {
+  for (auto &e : equal_words)
+    if ((float)wv[e.word_a] != (float)wv[e.word_b])
+      return "parameters " + words[e.word_a].name + " and " + words[e.word_b].name +
+             " were merged at compile time (two writers on one CircleBuffer position) and must stay equal";
   for (auto &l : locked) {
     const float v = (float)wv[l.word];
     if (!(v >= (float)l.lo && v <= (float)l.hi))

@@ -26,6 +26,8 @@ struct TapPair {
   int word_a, word_b;    // OFFSET constant words
   int sign_a, sign_b;    // +1 writer (t + SR*off), -1 reader (t - SR*off)
   long long ring_len;
+  bool strict = false;   // a plain reader against a writer, a chunk or more apart by default: must STAY apart
+                         // (not coincide), so the reader's loads may be issued ahead of the writer's stores
 };
 
 // A word whose initial value is a function of other (user-settable) words of the same voice.
@@ -51,6 +53,8 @@ struct Program {
   std::vector<TapPair> tap_pairs;
   std::vector<Derived> derived;
   struct Locked { int word; double lo, hi; };
+  struct EqualPair { int word_a, word_b; };
+  std::vector<EqualPair> equal_words;  // words a merged op relies on being equal in every voice
   std::vector<Locked> locked;  // constants a specialised op relies on: per-voice overrides must stay in range
   std::string check_locked(const double *word_values) const;
   // returns "" if the offsets (one value per word, as the voice will see them) are admissible

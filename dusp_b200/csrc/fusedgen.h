@@ -15,6 +15,7 @@ struct Gen {
   std::ostringstream o;
   std::set<int> mutable_words;
   mutable std::set<int> used_words;
+  std::set<size_t> hoisted;  // instructions whose loads were issued early into `pre<pc>[B]` (prefetch())
   Gen(const Program &pr, int b, int t) : p(pr), B(b), T(t) {}
 
   std::string w(int i) const { used_words.insert(i); return "w" + std::to_string(i); }
@@ -44,6 +45,8 @@ struct Gen {
     store("a", I.out[0]);
   }
   void instr(size_t pc, const DuspInstr &I);  // fused.cc
+  static bool can_prefetch(const Program &p, const DuspInstr &I, int step);
+  void prefetch(size_t pc, const DuspInstr &I, std::ostream &out);  // emits the early loads, marks pc hoisted
   std::string source(int min_blocks);          // fused.cc: the V x T tile kernel
 };
 

@@ -87,8 +87,11 @@ DOPS_DEV double rand53(uint64_t seed, uint64_t k) {
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
   z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
   z ^= z >> 31;
-  z >>= 11;  // 53 bits; hi 21 + lo 32 recombined exactly with one fma
-  return fma((double)(uint32_t)(z >> 32), 4294967296.0, (double)(uint32_t)z) * (1.0 / 9007199254740992.0);
+  z >>= 11;  // 53 bits = hi 21 + lo 32.  u32 -> f64 without the (slow) conversion pipe: 2^52 + u is exact and its
+  // bit pattern is 0x43300000:u, so (double)u = hiloint2double(0x43300000, u) - 2^52; recombined with one fma
+  const double hi = __hiloint2double(0x43300000, (int)(uint32_t)(z >> 32)) - 4503599627370496.0;
+  const double lo = __hiloint2double(0x43300000, (int)(uint32_t)z) - 4503599627370496.0;
+  return fma(hi, 4294967296.0, lo) * (1.0 / 9007199254740992.0);
 }
 DOPS_DEV double dB(double db) { return pow(10.0, db / 20.0); }  // Gain.js:26-28, Pan.js:26-28
 
@@ -578,6 +581,32 @@ DOPS_DEV void c_cbtapc(const Cx<B, T> &cx, float (&x)[B], float *buf, int n, dou
   } else {
     serial1<B, T>(cx, idx, [&] { idx = (double)run((int)idx); });
   }
+}
+
+// A plain CircleBufferReader with a constant OFFSET, split in two so that a kernel can issue the ring
+// loads early (before unrelated work of the same step) and consume them where the unit ticks:
+// c_cbpeek loads what c_cbtapc<reader> would read, c_cbadv advances the ring index like it does.
+// Only valid when no other tap stores into those positions during the step (compile.cc: aux[2]).
+template <int B, int T>
+DOPS_DEV void c_cbpeek(const Cx<B, T> &cx, float (&x)[B], const float *buf, int n, double idx) {
+  if (idx < 0.0) {
+#pragma unroll
+    for (int s = 0; s < B; s++) x[s] = NAN;
+    return;
+  }
+  int i = (int)idx + cx.tl * B;
+  if (i >= n) i %= n;
+  if (i + B <= n) {
+#pragma unroll
+    for (int s = 0; s < B; s++) x[s] = buf[i + s];
+  } else {
+#pragma unroll
+    for (int s = 0; s < B; s++) { x[s] = buf[i]; if (++i == n) i = 0; }
+  }
+}
+template <int B, int T>
+DOPS_DEV void c_cbadv(int n, double &idx) {
+  if (idx >= 0.0) idx = (double)(int)(((long long)idx + T * B) % n);
 }
 
 }  // namespace dops

@@ -33,8 +33,9 @@ namespace dusp {
 
 namespace {
 
-constexpr int STEP = 128;  // samples per pipeline step (divides the 256-sample chunk)
-constexpr int PB = 4;      // samples per lane in the P-warps (32 lanes x 4 = STEP) and per S-warp group
+// Samples per pipeline step: 256 (a chunk; lanes own 8 samples) when the exchange buffers leave room for
+// three CTAs per SM, else 128 (lanes own 4).  Rings shorter than a chunk never run time-parallel.
+constexpr int MAX_STEP = 256;
 
 // ops with no time-parallel form (or none worth having): they run in the lane-per-voice warp
 bool sequential_only(const Program &p, const DuspInstr &I) {
@@ -43,7 +44,7 @@ bool sequential_only(const Program &p, const DuspInstr &I) {
     case OP_DELAY: case OP_MONODELAY: case OP_READBACK: case OP_CBWRITE: case OP_CBREAD:
       return true;
     case OP_FIXDELAY: case OP_COMB: case OP_ALLPASS: case OP_CBWRITEC: case OP_CBREADC:
-      return p.rings[I.aux[0]].length < STEP;  // the step's samples would collide inside the ring
+      return p.rings[I.aux[0]].length < MAX_STEP;  // the step's samples would collide inside the ring
     default:
       return false;
   }
@@ -143,8 +144,24 @@ bool make_plan(const Program &p, Plan &pl) {
 
 }  // namespace
 
+namespace {
+std::string generate(const Program &p, int VC, int STEP, PipedInfo *info);
+}
+
 std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
   if (VC < 8 || VC > 32 || VC % 8) return "";
+  if (const char *se = getenv("DUSP_PIPED_STEP")) return generate(p, VC, atoi(se) == 128 ? 128 : 256, info);
+  PipedInfo pi;
+  std::string src = generate(p, VC, 256, &pi);
+  if (src.empty() || pi.smem_bytes > 76400) src = generate(p, VC, 128, &pi);
+  if (info) *info = pi;
+  return src;
+}
+
+namespace {
+
+std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
+  const int PB = STEP / 32;  // samples per lane in the P-warps and per S-warp group
   Plan pl;
   if (!make_plan(p, pl)) return "";
   const int n = (int)p.code.size();
@@ -154,6 +171,15 @@ std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
   Gen g0(p, PB, 32), g1(p, PB, 1), g2(p, PB, 32);
   Gen *gens[3] = {&g0, &g1, &g2};
   std::ostringstream s_decl, s_load, s_store;  // S-warp: crossing loads first, stores last (in-place buffer reuse)
+  // stage-2 loads that depend on nothing this step computes are issued before stage 0 of the next step,
+  // so their HBM / L2 latency hides behind that work
+  std::ostringstream pre_decl, pre_code;
+  if (!getenv("DUSP_PIPED_NOPREFETCH"))
+    for (int i = 0; i < n; i++)
+      if (pl.stage[i] == 2 && Gen::can_prefetch(p, p.code[i], STEP) && p.code[i].out[0] >= 0) {
+        pre_decl << "        float pre" << i << "[B];\n";
+        g2.prefetch(i, p.code[i], pre_code);
+      }
   for (int st = 0; st < 3; st++) {
     Gen &g = *gens[st];
     for (int i = 0; i < n; i++) {
@@ -197,7 +223,7 @@ std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
   const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double);
   if (smem > 200 * 1024) return "";
   if (info) { info->voices_per_cta = VC; info->threads = 160; info->smem_bytes = (int)smem; info->n_buffers = NB; }
-  int min_blocks = (int)std::min<size_t>(4, (220 * 1024) / (smem + 1024));
+  int min_blocks = (int)std::min<size_t>(4, (227 * 1024) / (smem + 1024));
   if (min_blocks < 1) min_blocks = 1;
 
   bool stage_has[3] = {false, false, false};
@@ -208,12 +234,16 @@ std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
     << "// stages:";
   for (int i = 0; i < n; i++) s << " " << i << ":" << op_name(p.code[i].op) << "=" << pl.stage[i];
   s << "\n" << fused_prelude()
-    << "#define LDX(d, b) { const float4 t_ = xs[(b) * (VC * 32)]; d[0] = t_.x; d[1] = t_.y; d[2] = t_.z; d[3] = t_.w; }\n"
-    << "#define STX(b, v) xs[(b) * (VC * 32)] = make_float4(v[0], v[1], v[2], v[3]);\n"
+    // exchange buffers: [rotation][buffer][voice][ROW float4]; samples [B*l + 4q, +4) of a step sit at float4
+    // q*32 + (l ^ (voice & 7)): a warp reading a row (P) or a column (S) touches every bank group once
+    << "#define LDX(d, b) { UNROLL for (int q_ = 0; q_ < B / 4; q_++) { const float4 t_ = xs[(b) * (VC * ROW) + q_ * 32];\\\n"
+    << "    d[4*q_] = t_.x; d[4*q_+1] = t_.y; d[4*q_+2] = t_.z; d[4*q_+3] = t_.w; } }\n"
+    << "#define STX(b, v) { UNROLL for (int q_ = 0; q_ < B / 4; q_++) xs[(b) * (VC * ROW) + q_ * 32] = make_float4(v[4*q_], v[4*q_+1], v[4*q_+2], v[4*q_+3]); }\n"
     // renderChannelData.js:42-44 for the P-warps: lanes along time, a warp stores 512 contiguous bytes
     << "#define OUT_CHANNEL_P(a, CH) { UNROLL for (int i_ = 0; i_ < B; i_++) a[i_] = js_or0f(a[i_]);\\\n"
     << "  if (kp.out_mode == 0) { if (active) { float *dst = out_row + (long long)(CH) * kp.out_len + tl0;\\\n"
-    << "      if (tl0 + B <= kp.n_samples && (kp.out_len & 3) == 0) __stcs(reinterpret_cast<float4 *>(dst), make_float4(a[0], a[1], a[2], a[3]));\\\n"
+    << "      if (tl0 + B <= kp.n_samples && (kp.out_len & 3) == 0) { UNROLL for (int q_ = 0; q_ < B / 4; q_++)\\\n"
+    << "        __stcs(reinterpret_cast<float4 *>(dst) + q_, make_float4(a[4*q_], a[4*q_+1], a[4*q_+2], a[4*q_+3])); }\\\n"
     << "      else { UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) dst[i_] = a[i_]; } } }\\\n"
     << "  else if ((CH) < 2 && active) { UNROLL for (int i_ = 0; i_ < B; i_++) macc[CH][i_] += a[i_]; } }\n"
     // same for the S-warp (one voice per lane)
@@ -224,10 +254,10 @@ std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
     << "      atomicAdd(kp.out + (long long)(CH) * kp.out_len + tl0 + i_, a[i_]);\\\n"
     << "      if (kp.prog_nch == 1) atomicAdd(kp.out + kp.out_len + tl0 + i_, a[i_]); } } }\n"
     << "extern \"C\" __global__ void __launch_bounds__(160, " << min_blocks << ") dusp_piped(const __grid_constant__ FusedParams kp) {\n"
-    << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", VW = VC / 4;\n"
+    << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", ROW = STEP / 4, VW = VC / 4;\n"
     << "  extern __shared__ float4 smem4[];\n"
-    << "  float4 *const xb = smem4;                                                   // [3][NB][VC][32] float4, swizzled\n"
-    << "  double *const pw = reinterpret_cast<double *>(smem4 + 3 * NB * VC * 32);  // [" << NPW << "][VC] words of the P-warps' units\n"
+    << "  float4 *const xb = smem4;                                                    // [3][NB][VC][ROW] float4, swizzled\n"
+    << "  double *const pw = reinterpret_cast<double *>(smem4 + 3 * NB * VC * ROW);  // [" << NPW << "][VC] words of the P-warps' units\n"
     << "  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;\n"
     << "  const long long v0 = (long long)blockIdx.x * VC;  // allocations are padded to a multiple of 96 voices\n"
     << "  const size_t nv = (size_t)kp.nv_stride;\n"
@@ -257,6 +287,11 @@ std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
     << "        float *const out_row = kp.out + (long long)(kp.voice0 + v) * kp.out_nch * kp.out_len;\n"
     << "        (void)rings; (void)stale; (void)out_row; (void)active;\n";
   for (auto &kv : pj) s << "        double w" << kv.first << " = pw[" << kv.second << " * VC + vl];\n";
+  if (!pre_code.str().empty())
+    s << pre_decl.str()
+      << "        if (do2) {  // ---- stage 2, early loads\n"
+      << "          const int cpos = (int)(((long long)(it - 2) * STEP + lane * B) & (DUSP_CHUNK - 1)); (void)cpos;\n"
+      << pre_code.str() << "        }\n";
   s << "#define OUT_CHANNEL OUT_CHANNEL_P\n";
   const char *rot[3] = {"rot0", "", "rot2"};
   const char *cond[3] = {"do0", "", "do2"};
@@ -266,7 +301,7 @@ std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
     s << "        if (" << cond[st] << ") {  // ---- stage " << st << "\n"
       << "          const long long tl0 = (long long)" << when[st] << " * STEP + lane * B;\n"
       << "          const int cpos = (int)(tl0 & (DUSP_CHUNK - 1)); (void)cpos;\n"
-      << "          float4 *const xs = xb + ((size_t)" << rot[st] << " * NB * VC + vl) * 32 + (lane ^ (vl & 7)); (void)xs;\n";
+      << "          float4 *const xs = xb + ((size_t)" << rot[st] << " * NB * VC + vl) * ROW + (lane ^ (vl & 7)); (void)xs;\n";
     for (int k = 0; k < p.n_slots; k++) s << "          float s" << k << "[B];\n";
     s << gens[st]->o.str() << "        }\n";
   }
@@ -304,11 +339,11 @@ std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
   if (stage_has[1]) {
     s << "      if (it >= 1 && it <= n_steps && lane < VC) {\n"
       << "        const int rot1 = (it + 2) % 3;  // (it - 1) mod 3\n"
-      << "        _Pragma(\"unroll 2\")\n"
+      << "        _Pragma(\"unroll " << (PB == 4 ? 2 : 1) << "\")\n"
       << "        for (int g = 0; g < STEP / B; g++) {\n"
       << "          const long long tl0 = (long long)(it - 1) * STEP + g * B;\n"
       << "          const int cpos = (int)(tl0 & (DUSP_CHUNK - 1)); (void)cpos;\n"
-      << "          float4 *const xs = xb + ((size_t)rot1 * NB * VC + vl) * 32 + (g ^ (vl & 7)); (void)xs;\n";
+      << "          float4 *const xs = xb + ((size_t)rot1 * NB * VC + vl) * ROW + (g ^ (vl & 7)); (void)xs;\n";
     for (int k = 0; k < p.n_slots; k++) s << "          float s" << k << "[B];\n";
     s << s_decl.str() << s_load.str() << g1.o.str() << s_store.str() << "        }\n      }\n";
   }
@@ -329,6 +364,8 @@ std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
   s << "}\n";
   return s.str();
 }
+
+}  // namespace
 
 size_t piped_compile_only(const Program &p, int VC, PipedInfo *info, std::string &err, std::string *src_out) {
   const std::string src = generate_piped_source(p, VC, info);

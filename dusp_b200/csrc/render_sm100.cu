@@ -708,6 +708,7 @@ __global__ void __launch_bounds__(128, B == 8 ? 4 : 2) dusp_render_tile(const __
         case OP_DIV: map2<B, T>(L, I, [](float a, float b) { return __fdiv_rn(a, b); }); break;
         case OP_ADD: map2<B, T>(L, I, [](float a, float b) { return __fadd_rn(a, b); }); break;
         case OP_SUB: map2<B, T>(L, I, [](float a, float b) { return __fsub_rn(a, b); }); break;
+        case OP_ADD0: map2<B, T>(L, I, [](float a, float b) { return __fadd_rn(__fadd_rn(0.0f, a), b); }); break;
         case OP_POW: map2<B, T>(L, I, [](float a, float b) { return (float)pow((double)a, (double)b); }); break;
         case OP_GAIN: map2<B, T>(L, I, [](float a, float g) { return (float)(dB((double)g) * (double)a); }); break;
         case OP_GAINC: { const double k = L.w(I.p); map1<B, T>(L, I, [k](float a) { return (float)(k * (double)a); }); break; }

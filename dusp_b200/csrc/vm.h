@@ -67,6 +67,8 @@ enum DuspOp : int32_t {
   OP_NOISE1,    // Noise, constant F >= sampleRate: a new draw every sample   [p as OP_NOISE]
   OP_CBWRITEC,  // CircleBufferWriter, constant OFFSET  [p: t0, running ring index (derived start)]
   OP_CBREADC,   // CircleBufferReader, constant OFFSET
+  OP_ADD0,      // (0 + in0) + in1: what a preWipe writer followed by a mixing writer leave on one ring position
+                //  (CircleBufferWriter.js:17-22 twice); feeds the single merged writer (compile.cc peephole)
   OP_COUNT
 };
 

@@ -2,7 +2,8 @@
 The cubin is regenerated here (NVRTC needs no GPU; generation is deterministic), disassembled with
 line info and joined with the report's per-SASS-instruction counters by instruction order.
 
-usage: ncu_fused_lines.py report.ncu-rep workload B T [top]     workload: w3 | w2 | w3b"""
+usage: ncu_fused_lines.py report.ncu-rep workload B T [top]     workload: w3 | w2 | w3b
+(B = 0: the pipelined kernel, T = voices per CTA)"""
 import collections, csv, glob, io, os, re, subprocess, sys, tempfile
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -12,6 +13,9 @@ rep, wl, B, T = sys.argv[1], sys.argv[2], int(sys.argv[3]), int(sys.argv[4])
 top = int(sys.argv[5]) if len(sys.argv) > 5 else 40
 tmp = tempfile.mkdtemp()
 os.environ["DUSP_FUSED_DUMP"] = tmp
+if B == 0:
+    os.environ["DUSP_PIPED"] = "1"
+    B = 4
 from dusp_b200 import capi, workloads as W
 from dusp_b200.render import circuit_blob
 import circuits
