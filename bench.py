@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--block-seconds", type=float, default=2.0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-mix", action="store_true", help="skip the W5 stereo-mixdown + NCCL reduce leg")
+    ap.add_argument("--mix-voices", type=int, default=12500, help="W5 voices per GPU (100 000 / 8)")
     return ap.parse_args()
 
 
@@ -141,6 +143,69 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------- W5: mixdown + the one collective
+def measure_mixdown(args, rank, world, local_rank, barrier):
+    """BASELINE configs[4] shape at N GPUs (weak scaling): every GPU renders 12 500 voices of W5 (even global
+    index: W2-live FM voice, odd: W3 filter + feedback-delay voice), 10 s, stereo mixdown only; each 2 s
+    block's [2][n] mix is sum-reduced onto rank 0 (NCCL over NVLink) while the next block renders."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from dusp_b200 import capi, mixdown as MD, workloads as W
+    from dusp_b200.render import circuit_blob
+
+    nv = args.mix_voices
+    voice0 = rank * nv
+    i2, i3 = W.w5_split(voice0, nv)
+    b2, _ = circuit_blob(W.w2_live_circuit())
+    b3, _ = circuit_blob(W.w3_circuit())
+    p2, p3 = capi.Program(b2), capi.Program(b3)
+    sess = capi.Session([p2, p3], [len(i2), len(i3)], local_rank)
+    o2 = W.w2_overrides(b2, W.w2_params(0, 0, i2))
+    o3 = W.w3_overrides(b3, W.w3_params(0, 0, i3))
+    sess.set_params(0, list(o2), np.stack([o2[k] for k in o2], axis=1))
+    sess.set_params(1, list(o3), np.stack([o3[k] for k in o3], axis=1))
+    secs = min(args.seconds, 10.0)
+    n_total = int(secs * SR)
+    blk = max(256, int(args.block_seconds * SR) // 256 * 256)
+    r = MD.MixdownRenderer(sess, blk, torch.device("cuda", local_rank))
+    peak = [0.0]
+
+    def on_block(t0, n, t):  # rank 0 consumes the reduced mix (device-side peak; the audio itself stays on the GPU)
+        if rank == 0:
+            peak[0] = max(peak[0], float(t.abs().max()))
+
+    def step():
+        sess.reset()
+        r.render(n_total, on_block)
+
+    stream = torch.cuda.current_stream()
+    for _ in range(2):
+        step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k = max(1, min(args.steps, 3))
+    e0.record(stream)
+    for _ in range(k):
+        step()
+    e1.record(stream)
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_step = float(ms.item()) / k
+    units = (len(i2) * p2.num_units + len(i3) * p3.num_units) * world
+    out = {"workload": "W5 (BASELINE configs[4] shape): %d voices/GPU (W2-live on even, W3 on odd global indices) x %g s, "
+                       "stereo mixdown only" % (nv, secs),
+           "value": units * n_total / (ms_step / 1e3), "unit": "unit-samples/s", "voices_total": nv * world,
+           "realtime_voices": nv * world * n_total / (ms_step / 1e3) / SR, "ms_per_step": ms_step,
+           "collective": ("ncclReduce(sum) of the [2][%d] f32 mix per block onto rank 0, async (overlaps the next block)" % blk)
+                         if world > 1 else "none (one GPU)",
+           "mix_peak": peak[0]}
+    sess.close()
+    return out
+
+
 # ------------------------------------------------------------------ B200 arm
 def run_b200(args, rank, world, local_rank):
     import numpy as np
@@ -227,8 +292,15 @@ def run_b200(args, rank, world, local_rank):
     full = [m for m, (t, n) in zip(launch_ms, blocks * args.steps) if n == blk] or launch_ms
     avg_launch_ms = sum(full) / len(full)
     achieved = bpvs * nv * blk / (avg_launch_ms / 1e3) / 1e9
+    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum of one such launch, from the committed ncu capture
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if tj["voices"] == nv and tj["samples"] == blk:
+            traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": None, "peak_source": peak_src, "kernel": "dusp_piped" if sess.launch_info().get("block") == 160 else "dusp_fused",
+                "traffic": traffic, "algorithmic_bytes_per_launch": bpvs * nv * blk, "peak_source": peak_src, "kernel": "dusp_piped" if sess.launch_info().get("block") == 160 else "dusp_fused",
                 "bytes_per_voice_sample": bpvs, "avg_launch_ms": avg_launch_ms,
                 "kernel_share_of_step": sum(launch_ms) / total_ms}
 
@@ -260,6 +332,10 @@ def run_b200(args, rank, world, local_rank):
                "note": "per-voice stereo channel data copied to pinned host memory (PCIe-bound)"}
         del hbuf
 
+    mixdown = None
+    if not args.no_mix:
+        mixdown = measure_mixdown(args, rank, world, local_rank, barrier)
+
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cb = cpu_baseline(units, W.w3_params)
@@ -276,7 +352,7 @@ def run_b200(args, rank, world, local_rank):
                        "l2": "working set (rings %.2f GB + block outputs %.1f GB) larger than L2"
                              % (nv * 44100 * 4 / 1e9, 2 * nv * nch * blk * 4 / 1e9)},
             "realtime_voices": value / units / SR, "voice_samples_per_sec": value / units,
-            "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "mixdown": mixdown, "gpu_launches": int(launches),
             "launch": sess.launch_info(), "clocks": clocks,
         }
         print(json.dumps(line), flush=True)

@@ -42,9 +42,10 @@ def w2_live_circuit(f0=300.0):
     return C.Multiply(osc, osc)
 
 
-def w2_params(voice0, n):
-    """f0_v ~ U[100,800): Ramp(88200, f0, f0/2).trigger()"""
-    f0 = np.array([_u(W2_SEED, voice0 + v, 0, 100.0, 800.0) for v in range(n)])
+def w2_params(voice0, n, indices=None):
+    """f0_v ~ U[100,800): Ramp(88200, f0, f0/2).trigger().  ``indices``: explicit global voice indices."""
+    idx = range(voice0, voice0 + n) if indices is None else indices
+    f0 = np.array([_u(W2_SEED, i, 0, 100.0, 800.0) for i in idx])
     return {"f0": f0}
 
 
@@ -65,9 +66,9 @@ def w3_circuit(f=1000.0, dly=0.2, g=0.5, pan=0.0, seed=1):
     return C.Pan(C.Sum(filt, tap), pan)
 
 
-def w3_params(voice0, n):
+def w3_params(voice0, n, indices=None):
     """f_v ~ U[200,4000) Hz, d_v ~ U[0.05,0.5) s, g_v ~ U[0.2,0.7), p_v ~ U[-1,1), noise stream seed per voice."""
-    v = range(voice0, voice0 + n)
+    v = list(range(voice0, voice0 + n)) if indices is None else list(indices)
     return {
         "f": np.array([_u(W3_SEED, i, 0, 200.0, 4000.0) for i in v]),
         "dly": np.array([_u(W3_SEED, i, 1, 0.05, 0.5) for i in v]),
@@ -99,3 +100,17 @@ def w3_voice_circuit(params, v):
 # ---- W3b: cyclic-graph coverage, `Pan(SimpleDelay(Filter(Noise)))` ----
 def w3b_circuit(f=800.0, dly=0.25, g=0.5, pan=0.3, seed=1):
     return C.Pan(P.SimpleDelay(C.Filter(C.Noise(seed=seed), f), dly, g, 0.4), pan)
+
+
+# ---- W5: 100 000 voices = W2-live (even global index) + W3 (odd), stereo mixdown only (BASELINE configs[4]) ----
+def w5_split(voice0, n):
+    """Global voice indices of a shard [voice0, voice0+n), by kind."""
+    idx = range(voice0, voice0 + n)
+    return [i for i in idx if i % 2 == 0], [i for i in idx if i % 2 == 1]
+
+
+def w5_voice_circuit(i):
+    """The stand-alone circuit of global voice i (what the reference / the oracle renders)."""
+    if i % 2 == 0:
+        return w2_live_circuit(float(w2_params(0, 0, [i])["f0"][0]))
+    return w3_voice_circuit(w3_params(0, 0, [i]), 0)

@@ -227,3 +227,31 @@ def test_full_size_w2_properties(lib):
         assert np.array_equal(got[v, 0], got[0, 0])
     assert not np.isnan(got).any() and float(np.abs(got).max()) <= 1.0
     assert len({got[v, 0].tobytes() for v in range(1, 50)}) == 49  # distinct voices differ
+
+
+def test_mixdown_renderer_blocks_match_whole_render(lib):
+    """dusp_b200.mixdown.MixdownRenderer (the multi-GPU mix path; here one GPU, no process group): block-wise
+    OUT_MIX renders into rotating device buffers equal one whole-length mix render."""
+    import torch
+    from dusp_b200 import mixdown, workloads as W
+    i2, i3 = W.w5_split(10, 12)
+    b2, _ = circuit_blob(W.w2_live_circuit())
+    b3, _ = circuit_blob(W.w3_circuit())
+    p2, p3 = capi.Program(b2), capi.Program(b3)
+    s = capi.Session([p2, p3], [len(i2), len(i3)], 0)
+    o2, o3 = W.w2_overrides(b2, W.w2_params(0, 0, i2)), W.w3_overrides(b3, W.w3_params(0, 0, i3))
+    s.set_params(0, list(o2), np.stack([o2[k] for k in o2], axis=1))
+    s.set_params(1, list(o3), np.stack([o3[k] for k in o3], axis=1))
+    n = 5000
+    whole = s.render_host(n, capi.OUT_MIX)
+    s.reset()
+    got = np.zeros((2, n), dtype=np.float32)
+
+    def on_block(t0, k, t):
+        got[:, t0:t0 + k] = t.cpu().numpy()
+
+    mixdown.MixdownRenderer(s, 2048, torch.device("cuda", 0)).render(n, on_block)
+    torch.cuda.synchronize()
+    s.close()
+    assert np.max(np.abs(got - whole)) <= 1e-5 * max(1.0, float(np.max(np.abs(whole))))
+    assert float(np.max(np.abs(whole))) > 0.1
