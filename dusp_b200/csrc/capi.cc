@@ -87,6 +87,8 @@ struct Group {
   DuspRing *d_ringtab = nullptr;
   float *d_stale = nullptr;
   bool dirty = true;  // device words/rings need (re)initialisation
+  size_t off_words = 0, off_rings = 0, off_stale = 0;  // this group's segments of the session pools (elements)
+  bool in_multi = false;  // rendered by the session's one multi-program interpreter launch
 };
 
 }  // namespace
@@ -98,6 +100,14 @@ struct dusp_session {
   long long unit_count = 0;
   long long clock = 0;
   float *d_tables = nullptr;
+  // every group's arrays are segments of five session-wide allocations (a heterogeneous batch of 10 000
+  // circuits is 10 000 groups: one upload / two memsets re-initialise them all)
+  double *d_words_pool = nullptr; float *d_rings_pool = nullptr; float *d_stale_pool = nullptr;
+  DuspRing *d_ringtab_pool = nullptr; DuspDevInstr *d_code_pool = nullptr;
+  size_t words_total = 0, rings_total = 0, stale_total = 0;
+  std::vector<double> h_all;  // staging image of the words pool
+  DuspWarpDesc *d_multi = nullptr;  // one descriptor per voice of the interpreter groups (multi-program launch)
+  int n_multi = 0, multi_slots = 1;
   float *d_staging[2] = {nullptr, nullptr};  // host-output path: double-buffered device blocks
   size_t staging_floats = 0;
   cudaStream_t copy_stream = nullptr;
@@ -152,15 +162,12 @@ size_t dusp_program_disassemble(const dusp_program *p, char *buf, size_t cap) {
   return p->listing.size() + 1;
 }
 
-static void free_group(Group &g) {
-  cudaFree(g.d_code); cudaFree(g.d_words); cudaFree(g.d_rings); cudaFree(g.d_ringtab); cudaFree(g.d_stale);
-  g.d_code = nullptr; g.d_words = nullptr; g.d_rings = nullptr; g.d_ringtab = nullptr; g.d_stale = nullptr;
-}
 
 void dusp_session_destroy(dusp_session *s) {
   if (!s) return;
   cudaSetDevice(s->device);
-  for (auto &g : s->groups) free_group(g);
+  cudaFree(s->d_words_pool); cudaFree(s->d_rings_pool); cudaFree(s->d_stale_pool); cudaFree(s->d_ringtab_pool);
+  cudaFree(s->d_code_pool); cudaFree(s->d_multi);
   cudaFree(s->d_tables);
   for (int i = 0; i < 2; i++) {
     cudaFree(s->d_staging[i]);
@@ -192,7 +199,9 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
     g.prog = programs[i]->prog;
     g.n_voices = voices[i];
     g.voice0 = voice0;
-    g.nv_pad = ((long long)voices[i] + 95) / 96 * 96;  // whole warps / whole CTAs of 16, 24 or 32 voices
+    // batches: whole warps / whole CTAs of 16, 24 or 32 voices; small groups render one voice per warp
+    const bool forced = getenv("DUSP_TILE") || getenv("DUSP_FUSED") || getenv("DUSP_PIPED");  // experiments / tests
+    g.nv_pad = voices[i] >= 64 || forced ? ((long long)voices[i] + 95) / 96 * 96 : ((long long)voices[i] + 7) / 8 * 8;
     voice0 += voices[i];
     s->out_nch = std::max(s->out_nch, g.prog.out_nch);
     s->unit_count += (long long)g.prog.n_units * voices[i];
@@ -213,8 +222,6 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
       d.p = in.p; d.aux0 = in.aux[0]; d.aux1 = in.aux[1]; d.aux2 = in.aux[2];
       g.dev_code.push_back(d);
     }
-    CUDA_TRY(cudaMalloc(&g.d_code, std::max<size_t>(g.dev_code.size(), 1) * sizeof(DuspDevInstr)));
-    CUDA_TRY(cudaMemcpy(g.d_code, g.dev_code.data(), g.dev_code.size() * sizeof(DuspDevInstr), cudaMemcpyHostToDevice));
     {
       // Tile shape: T time-lanes per voice so that the batch still fills the GPU (>= 8 warps per SM);
       // B samples per lane.  DUSP_TILE="B,T" overrides (experiments).
@@ -271,17 +278,70 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
         g.sub_block = B; g.time_lanes = T; g.warps_per_cta = wpc;
       }
     }
-    CUDA_TRY(cudaMalloc(&g.d_words, g.h_words.size() * sizeof(double)));
-    const size_t ring_bytes = (size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad * sizeof(float);
-    if (cudaMalloc(&g.d_rings, ring_bytes) != cudaSuccess) {
+  }
+  // ---- session pools: every group's words / rings / stale / ring table / code are 256-byte aligned segments
+  {
+    auto up = [](size_t n, size_t elem) { const size_t a = 256 / elem; return (n + a - 1) / a * a; };
+    size_t n_words = 0, n_rings = 0, n_stale = 0, n_rt = 0, n_code = 0;
+    std::vector<size_t> off_rt, off_code;
+    for (auto &g : s->groups) {
+      g.off_words = n_words; n_words += up(g.h_words.size(), sizeof(double));
+      g.off_rings = n_rings; n_rings += up((size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad, sizeof(float));
+      g.off_stale = n_stale; n_stale += up((size_t)std::max(g.prog.n_stale, 1) * DUSP_CHUNK * g.nv_pad, sizeof(float));
+      off_rt.push_back(n_rt); n_rt += up(std::max<size_t>(g.prog.rings.size(), 1), sizeof(DuspRing));
+      off_code.push_back(n_code); n_code += up(std::max<size_t>(g.dev_code.size(), 1), sizeof(DuspDevInstr));
+    }
+    s->words_total = n_words; s->rings_total = n_rings; s->stale_total = n_stale;
+    CUDA_TRY(cudaMalloc(&s->d_words_pool, n_words * sizeof(double)));
+    if (cudaMalloc(&s->d_rings_pool, n_rings * sizeof(float)) != cudaSuccess) {
       cudaGetLastError();
       char m[160];
-      snprintf(m, sizeof m, "delay lines need %.1f GB of device memory for %d voices", ring_bytes / 1e9, g.n_voices);
+      snprintf(m, sizeof m, "delay lines need %.1f GB of device memory for %d voices", n_rings * 4 / 1e9, voice0);
       return fail(DUSP_ENOMEM, m);
     }
-    CUDA_TRY(cudaMalloc(&g.d_ringtab, std::max<size_t>(g.prog.rings.size(), 1) * sizeof(DuspRing)));
-    CUDA_TRY(cudaMemcpy(g.d_ringtab, g.prog.rings.data(), g.prog.rings.size() * sizeof(DuspRing), cudaMemcpyHostToDevice));
-    CUDA_TRY(cudaMalloc(&g.d_stale, (size_t)std::max(g.prog.n_stale, 1) * DUSP_CHUNK * g.nv_pad * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&s->d_stale_pool, n_stale * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&s->d_ringtab_pool, n_rt * sizeof(DuspRing)));
+    CUDA_TRY(cudaMalloc(&s->d_code_pool, n_code * sizeof(DuspDevInstr)));
+    std::vector<DuspRing> h_rt(n_rt);
+    std::vector<DuspDevInstr> h_code(n_code);
+    memset(h_code.data(), 0, n_code * sizeof(DuspDevInstr));
+    for (size_t i = 0; i < s->groups.size(); i++) {
+      Group &g = s->groups[i];
+      g.d_words = s->d_words_pool + g.off_words; g.d_rings = s->d_rings_pool + g.off_rings;
+      g.d_stale = s->d_stale_pool + g.off_stale; g.d_ringtab = s->d_ringtab_pool + off_rt[i];
+      g.d_code = s->d_code_pool + off_code[i];
+      std::copy(g.prog.rings.begin(), g.prog.rings.end(), h_rt.begin() + off_rt[i]);
+      std::copy(g.dev_code.begin(), g.dev_code.end(), h_code.begin() + off_code[i]);
+    }
+    CUDA_TRY(cudaMemcpy(s->d_ringtab_pool, h_rt.data(), n_rt * sizeof(DuspRing), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(s->d_code_pool, h_code.data(), n_code * sizeof(DuspDevInstr), cudaMemcpyHostToDevice));
+  }
+  // ---- heterogeneous batches: all interpreter groups with the one-voice-per-warp tile (B = 8, T = 32)
+  //      render in ONE launch, every warp with its own program (vm.h DuspWarpDesc)
+  {
+    std::vector<DuspWarpDesc> descs;
+    int n_cand = 0;
+    for (auto &g : s->groups) if (!g.fused && g.sub_block == 8 && g.time_lanes == 32) n_cand++;
+    if (n_cand >= 2 && !getenv("DUSP_NO_MULTI"))
+      for (auto &g : s->groups) {
+        if (g.fused || g.sub_block != 8 || g.time_lanes != 32) continue;
+        g.in_multi = true;
+        s->multi_slots = std::max(s->multi_slots, g.prog.n_slots);
+        const long long rs = std::max<long long>(g.prog.ring_floats, 4);
+        for (int v = 0; v < g.n_voices; v++) {
+          DuspWarpDesc d;
+          memset(&d, 0, sizeof d);
+          d.code = g.d_code; d.words = g.d_words + v; d.rings = g.d_rings + (long long)v * rs; d.ring_tab = g.d_ringtab;
+          d.stale = g.d_stale + (long long)v * g.prog.n_stale * DUSP_CHUNK; d.nv_stride = g.nv_pad; d.out_row = g.voice0 + v;
+          d.n_instr = (int)g.dev_code.size(); d.n_stale = g.prog.n_stale; d.prog_nch = g.prog.out_nch;
+          descs.push_back(d);
+        }
+      }
+    s->n_multi = (int)descs.size();
+    if (s->n_multi) {
+      CUDA_TRY(cudaMalloc(&s->d_multi, descs.size() * sizeof(DuspWarpDesc)));
+      CUDA_TRY(cudaMemcpy(s->d_multi, descs.data(), descs.size() * sizeof(DuspWarpDesc), cudaMemcpyHostToDevice));
+    }
   }
   s->n_voices = voice0;
   *out = s.release();
@@ -343,13 +403,41 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
   bool need_zero = out_mode == DUSP_OUT_MIX;
   for (auto &g : s->groups) if (g.prog.out_nch != s->out_nch) need_zero = true;
   if (need_zero) CUDA_TRY(cudaMemsetAsync(d_out, 0, out_floats * sizeof(float), st));
-  for (auto &g : s->groups) {
-    if (g.dirty) {
-      CUDA_TRY(cudaMemcpyAsync(g.d_words, g.h_words.data(), g.h_words.size() * sizeof(double), cudaMemcpyHostToDevice, st));
-      CUDA_TRY(cudaMemsetAsync(g.d_rings, 0, (size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad * sizeof(float), st));
-      CUDA_TRY(cudaMemsetAsync(g.d_stale, 0, (size_t)std::max(g.prog.n_stale, 1) * DUSP_CHUNK * g.nv_pad * sizeof(float), st));
-      g.dirty = false;
+  {
+    bool all_dirty = true, any_dirty = false;
+    for (auto &g : s->groups) { all_dirty = all_dirty && g.dirty; any_dirty = any_dirty || g.dirty; }
+    if (all_dirty && s->groups.size() > 1) {  // one upload + two memsets for the whole session
+      s->h_all.resize(s->words_total);
+      for (auto &g : s->groups) { std::copy(g.h_words.begin(), g.h_words.end(), s->h_all.begin() + g.off_words); g.dirty = false; }
+      CUDA_TRY(cudaMemcpyAsync(s->d_words_pool, s->h_all.data(), s->words_total * sizeof(double), cudaMemcpyHostToDevice, st));
+      CUDA_TRY(cudaMemsetAsync(s->d_rings_pool, 0, s->rings_total * sizeof(float), st));
+      CUDA_TRY(cudaMemsetAsync(s->d_stale_pool, 0, s->stale_total * sizeof(float), st));
+    } else if (any_dirty) {
+      for (auto &g : s->groups) {
+        if (!g.dirty) continue;
+        CUDA_TRY(cudaMemcpyAsync(g.d_words, g.h_words.data(), g.h_words.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemsetAsync(g.d_rings, 0, (size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad * sizeof(float), st));
+        CUDA_TRY(cudaMemsetAsync(g.d_stale, 0, (size_t)std::max(g.prog.n_stale, 1) * DUSP_CHUNK * g.nv_pad * sizeof(float), st));
+        g.dirty = false;
+      }
     }
+  }
+  if (s->n_multi) {  // every one-voice-per-warp interpreter group in one launch
+    DuspKernelParams kp;
+    memset(&kp, 0, sizeof kp);
+    kp.multi = s->d_multi; kp.n_voices = s->n_multi; kp.n_slots = s->multi_slots; kp.nv_stride = 1;
+    kp.tables = s->d_tables; kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = 1; kp.out_mode = out_mode;
+    kp.out_len = n; kp.clock0 = s->clock; kp.n_samples = n;
+    int wpc = 4;
+    while (wpc > 1 && (size_t)s->multi_slots * 8 * 128 * wpc > 100 * 1024) wpc >>= 1;
+    int grid = 0, smem = 0;
+    int e = dusp_launch_render(&kp, 8, 32, wpc, st, &grid, &smem);
+    if (e != 0) return fail(DUSP_ECUDA, std::string("render launch: ") + cudaGetErrorString((cudaError_t)e));
+    s->launches++;
+    s->last_grid = grid; s->last_block = wpc * 32; s->last_smem = smem; s->last_fused = false;
+  }
+  for (auto &g : s->groups) {
+    if (g.in_multi) continue;
     DuspKernelParams kp;
     memset(&kp, 0, sizeof kp);
     kp.prog_global = g.d_code; kp.n_instr = (int)g.dev_code.size(); kp.n_slots = g.prog.n_slots;

@@ -667,18 +667,27 @@ __global__ void __launch_bounds__(128, B == 8 ? 4 : 2) dusp_render_tile(const __
 
   Lane<B, T> L;
   L.S = smem + (size_t)wib * kp.n_slots * (B / 4) * 32 + lane;
-  L.W = kp.words + v;
-  L.nv = (unsigned)kp.nv_stride;
   L.tl = tl;
   L.lane = lane;
-  L.rings = kp.rings + v * kp.ring_stride;
-  L.ring_tab = kp.ring_tab;
-  L.stale = kp.stale + v * (long long)kp.n_stale * DUSP_CHUNK;
   L.tables = kp.tables;
+  const DuspDevInstr *code = kp.prog_global;
+  bool use_inline = kp.use_inline != 0;
+  int n_instr = kp.n_instr, prog_nch = kp.prog_nch;
+  long long row = kp.voice0 + v;
+  if (T == 32 && kp.multi) {  // heterogeneous batch: this warp's voice has its own program and arenas
+    const DuspWarpDesc d = kp.multi[warp];
+    L.W = d.words; L.nv = (unsigned)d.nv_stride; L.rings = d.rings; L.ring_tab = d.ring_tab; L.stale = d.stale;
+    code = d.code; use_inline = false; n_instr = d.n_instr; prog_nch = d.prog_nch; row = d.out_row;
+  } else {
+    L.W = kp.words + v;
+    L.nv = (unsigned)kp.nv_stride;
+    L.rings = kp.rings + v * kp.ring_stride;
+    L.ring_tab = kp.ring_tab;
+    L.stale = kp.stale + v * (long long)kp.n_stale * DUSP_CHUNK;
+  }
 
   const long long n_proc = (kp.n_samples + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;  // whole chunks, like Circuit.tick
-  float *const out_row = kp.out + (long long)(kp.voice0 + v) * kp.out_nch * kp.out_len;
-  const int n_instr = kp.n_instr;
+  float *const out_row = kp.out + row * kp.out_nch * kp.out_len;
 
 #pragma unroll 1
   for (long long tile = 0; tile < n_proc; tile += T * B) {
@@ -687,10 +696,10 @@ __global__ void __launch_bounds__(128, B == 8 ? 4 : 2) dusp_render_tile(const __
 #pragma unroll 1
     for (int pc = 0; pc < n_instr; pc++) {
       DuspDevInstr I;
-      if (kp.use_inline) {
+      if (use_inline) {
         I = kp.prog_inline[pc];
       } else {
-        const int4 *src = reinterpret_cast<const int4 *>(kp.prog_global + pc);
+        const int4 *src = reinterpret_cast<const int4 *>(code + pc);
         int4 *dst = reinterpret_cast<int4 *>(&I);
         dst[0] = __ldg(src); dst[1] = __ldg(src + 1); dst[2] = __ldg(src + 2);
       }
@@ -835,7 +844,7 @@ __global__ void __launch_bounds__(128, B == 8 ? 4 : 2) dusp_render_tile(const __
               for (int o = 16; o >= T; o >>= 1) y += __shfl_xor_sync(0xffffffffu, y, o);
               if (vi == 0 && tl0 + s < kp.n_samples) {
                 atomicAdd(kp.out + (long long)I.aux0 * kp.out_len + tl0 + s, y);
-                if (kp.prog_nch == 1) atomicAdd(kp.out + kp.out_len + tl0 + s, y);
+                if (prog_nch == 1) atomicAdd(kp.out + kp.out_len + tl0 + s, y);
               }
             }
           }

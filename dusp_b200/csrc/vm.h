@@ -111,7 +111,21 @@ struct __attribute__((aligned(16))) DuspDevInstr {
 static_assert(sizeof(DuspDevInstr) == 48, "DuspDevInstr layout");
 #define DUSP_INLINE_INSTR 80
 
-// One launch renders `n_samples` for every voice of one program group.
+// Heterogeneous batches (many different circuits, one voice-warp each): per-warp descriptor of a
+// multi-program launch of the interpreter (tile shape B = 8, T = 32: a warp renders one voice).
+struct DuspWarpDesc {
+  const DuspDevInstr *code;
+  double *words;           // this voice's word 0; word w at words[w * nv_stride]
+  float *rings;            // this voice's ring arena
+  const DuspRing *ring_tab;
+  float *stale;            // this voice's stale buffers
+  int64_t nv_stride;
+  int64_t out_row;         // global voice index (output row)
+  int32_t n_instr, n_stale, prog_nch, pad;
+};
+
+// One launch renders `n_samples` for every voice of one program group (or, with `multi`, one voice per
+// warp of many program groups).
 struct DuspKernelParams {
   int32_t n_instr;
   int32_t n_slots;
@@ -135,5 +149,6 @@ struct DuspKernelParams {
   int64_t clock0;        // absolute sample index of the first sample of this launch (multiple of 256)
   int64_t n_samples;     // samples to store (<= processed); processing covers whole chunks
   const DuspDevInstr *prog_global;
+  const DuspWarpDesc *multi;  // non-null: n_voices descriptors, one per warp (requires T = 32)
   DuspDevInstr prog_inline[DUSP_INLINE_INSTR];
 };

@@ -114,3 +114,77 @@ def w5_voice_circuit(i):
     if i % 2 == 0:
         return w2_live_circuit(float(w2_params(0, 0, [i])["f0"][0]))
     return w3_voice_circuit(w3_params(0, 0, [i]), 0)
+
+
+# ---- W4: 10 000 random Dusp circuits, depth 4-8, Osc/Ramp/Multiply/Sum/filter/delay mix (BASELINE configs[3]) ----
+W4_SEED = 1003
+W4_MAX_UNITS = 64
+
+
+class _W4Gen:
+    """Recursive generator of circuit `index`: internal node in {Multiply 30 %, Sum 30 %, Filter-LP
+    15 %, AllPass / FixedDelay 10 %, Osc with modulated f 15 %}, leaf in {Osc const f 50 %, live Ramp 20 %, Shape
+    decay 15 %, Noise 15 %}; at most 64 units.  Builds the unit graph and the equivalent Dusp text side by side."""
+
+    def __init__(self, index):
+        self.index, self.k, self.units = index, 0, 0
+
+    def u(self, lo=0.0, hi=1.0):
+        self.k += 1
+        return lo + (hi - lo) * rand53(W4_SEED, (self.index << 12) + self.k)
+
+    def leaf(self):
+        r = self.u()
+        self.units += 1
+        if r < 0.5:
+            f = round(self.u(50.0, 2000.0), 3)
+            return C.Osc(f), "[Osc f:%r]" % f
+        if r < 0.7:
+            dur, y0, y1 = int(self.u(4410, 441000)), round(self.u(0.0, 1.0), 4), round(self.u(0.0, 1.0), 4)
+            return C.Ramp(dur, y0, y1).trigger(), "([Ramp %d %r %r] at 0)" % (dur, y0, y1)
+        if r < 0.85:
+            dur = round(self.u(0.2, 8.0), 3)
+            return C.Shape("decay", dur).trigger(), "D%r" % dur
+        return C.Noise(), "[Noise]"  # stream seed: the host generator's next Noise seed (config.seed, see w4_circuit)
+
+    def node(self, depth):
+        if depth <= 1 or self.units >= W4_MAX_UNITS - 4:
+            return self.leaf()
+        r = self.u()
+        if r < 0.6:
+            self.units += 1
+            a, ta = self.node(depth - 1)
+            b, tb = self.node(depth - 1)
+            if r < 0.3:
+                return C.Multiply(a, b), "(%s * %s)" % (ta, tb)
+            return C.Sum(a, b), "(%s + %s)" % (ta, tb)
+        if r < 0.75:
+            self.units += 1
+            f = round(self.u(100.0, 8000.0), 2)
+            a, ta = self.node(depth - 1)
+            return C.Filter(a, f, "LP"), "(%s -> LP%r)" % (ta, f)
+        if r < 0.85:
+            self.units += 1
+            dly = round(self.u(0.002, 0.03), 5)
+            a, ta = self.node(depth - 1)
+            if self.u() < 0.5:
+                ap = C.AllPass(dly, round(self.u(0.1, 0.8), 3))
+                ap.IN = a
+                return ap, "(%s -> [AllPass %r %r])" % (ta, dly, float(ap.inlets["feedbackGain"].constant))
+            fd = C.FixedDelay(dly)
+            fd.IN = a
+            return fd, "(%s -> [FixedDelay %r])" % (ta, dly)
+        self.units += 3  # Osc + the Multiply and Sum that scale the modulator
+        depth_hz, centre = round(self.u(1.0, 300.0), 2), round(self.u(80.0, 1500.0), 2)
+        a, ta = self.node(depth - 1)
+        return C.Osc(quick.add(quick.multiply(a, depth_hz), centre)), "[Osc f:(%s * %r + %r)]" % (ta, depth_hz, centre)
+
+
+def w4_circuit(index, with_text=False):
+    """Random circuit `index` of W4 (deterministic in `index`): the rendered unit, optionally with its Dusp text."""
+    from . import config
+    config.seed(_mix64(W4_SEED * 0x20003 + index))  # Noise units take their stream seeds in construction order
+    g = _W4Gen(index)
+    depth = 4 + int(g.u() * 5)  # uniform in 4..8
+    unit, text = g.node(depth)
+    return (unit, text) if with_text else unit

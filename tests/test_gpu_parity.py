@@ -255,3 +255,21 @@ def test_mixdown_renderer_blocks_match_whole_render(lib):
     s.close()
     assert np.max(np.abs(got - whole)) <= 1e-5 * max(1.0, float(np.max(np.abs(whole))))
     assert float(np.max(np.abs(whole))) > 0.1
+
+
+def test_w4_random_circuits_in_one_multi_program_launch(lib, oracle):
+    """BASELINE configs[3] shape at test size: 24 different random circuits (depth 4-8, Osc / Ramp / Shape / Noise /
+    Multiply / Sum / Filter / AllPass / FixedDelay) in ONE session: every circuit is its own program, all rendered by one
+    multi-program launch (a warp per circuit, vm.h DuspWarpDesc).  Every op here is in the bit-exact class."""
+    from dusp_b200 import workloads as W
+    n, secs = 24, 0.3
+    blobs = [circuit_blob(W.w4_circuit(i))[0] for i in range(n)]
+    progs = [capi.Program(b) for b in blobs]
+    s = capi.Session(progs, [1] * n, 0)
+    l0 = s.launch_count
+    got = s.render_host(n_samples_for(secs))
+    launches = s.launch_count - l0
+    s.close()
+    assert launches == 1, "heterogeneous batch must render in one launch per block"
+    for i, b in enumerate(blobs):
+        compare(got[i][:1], oracle.render(b, secs), True, "w4 circuit %d" % i)
