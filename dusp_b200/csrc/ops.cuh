@@ -604,6 +604,13 @@ DOPS_DEV void c_cbpeek(const Cx<B, T> &cx, float (&x)[B], const float *buf, int 
     for (int s = 0; s < B; s++) { x[s] = buf[i]; if (++i == n) i = 0; }
   }
 }
+// pulls the ring lines the NEXT step's c_cbpeek will read from HBM into L2 (no register cost)
+template <int B, int T>
+DOPS_DEV void c_cbprefetch(const Cx<B, T> &cx, const float *buf, int n, double idx) {
+  if (idx < 0.0) return;
+  const int i = (int)(((long long)idx + T * B + cx.tl * B) % n);
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(buf + i));
+}
 template <int B, int T>
 DOPS_DEV void c_cbadv(int n, double &idx) {
   if (idx >= 0.0) idx = (double)(int)(((long long)idx + T * B) % n);

@@ -220,7 +220,9 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   for (int w : p_words) { int j = (int)pj.size(); pj[w] = j; }
   const int NPW = (int)pj.size();
   const size_t xb_bytes = (size_t)3 * NB * VC * STEP * sizeof(float);
-  const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double);
+  // optional dynamic voice queue for the P-warps (measured slightly slower than the static split: off)
+  const bool dyn = getenv("DUSP_PIPED_DYN") != nullptr;
+  const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double) + 16;
   if (smem > 200 * 1024) return "";
   if (info) { info->voices_per_cta = VC; info->threads = 160; info->smem_bytes = (int)smem; info->n_buffers = NB; }
   int min_blocks = (int)std::min<size_t>(4, (227 * 1024) / (smem + 1024));
@@ -258,10 +260,12 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "  extern __shared__ float4 smem4[];\n"
     << "  float4 *const xb = smem4;                                                    // [3][NB][VC][ROW] float4, swizzled\n"
     << "  double *const pw = reinterpret_cast<double *>(smem4 + 3 * NB * VC * ROW);  // [" << NPW << "][VC] words of the P-warps' units\n"
+    << "  int *const qctr = reinterpret_cast<int *>(pw + " << NPW << " * VC);                 // [3] per-step voice queue heads\n"
+    << "  if (threadIdx.x < 3) qctr[threadIdx.x] = 0;\n"
     << "  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;\n"
     << "  const long long v0 = (long long)blockIdx.x * VC;  // allocations are padded to a multiple of 96 voices\n"
     << "  const size_t nv = (size_t)kp.nv_stride;\n"
-    << "  const float *const tables = kp.tables; (void)tables; (void)xb; (void)pw;\n"
+    << "  const float *const tables = kp.tables; (void)tables; (void)xb; (void)pw; (void)qctr;\n"
     << "  const long long n_proc = (kp.n_samples + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;  // whole chunks, like Circuit.tick\n"
     << "  const int n_steps = (int)(n_proc / STEP);\n";
   for (auto &kv : pj)
@@ -277,9 +281,15 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "      const bool do0 = it < n_steps, do2 = it >= 2;\n"
     << "      const int rot0 = it % 3, rot2 = (it + 1) % 3;  // (it - 2) mod 3\n"
     << "      float macc[2][B]; UNROLL for (int i_ = 0; i_ < B; i_++) { macc[0][i_] = 0.0f; macc[1][i_] = 0.0f; }\n"
+    << (dyn ? "      if (threadIdx.x == 0) qctr[(it + 1) % 3] = 0;  // next step's queue (last used two steps ago)\n" : "")
     << "      _Pragma(\"unroll 1\")\n"
-    << "      for (int j = 0; j < VW; j++) {\n"
-    << "        const int vl = wib * VW + j;\n"
+    << (dyn ? "      for (;;) {  // the CTA's VC voices are a queue: whichever P-warp is free takes the next one\n"
+              "        int vl = 0;\n"
+              "        if (lane == 0) vl = atomicAdd(&qctr[it % 3], 1);\n"
+              "        vl = __shfl_sync(0xffffffffu, vl, 0);\n"
+              "        if (vl >= VC) break;\n"
+            : "      for (int j = 0; j < VW; j++) {\n"
+              "        const int vl = wib * VW + j;\n")
     << "        const long long v = v0 + vl;\n"
     << "        const bool active = v < kp.n_voices;\n"
     << "        float *const rings = kp.rings + v * kp.ring_stride;\n"
