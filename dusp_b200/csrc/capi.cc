@@ -240,12 +240,14 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
       // Pipelined kernel (piped.cc): lanes along time for the parallel units, a lane-per-voice warp for the
       // recurrences.  Default for batches; circuits without a 3-stage split use the tile kernel.  DUSP_PIPED=0/1 forces.
       const char *pe = getenv("DUSP_PIPED");
-      if (want && (pe ? atoi(pe) != 0 : voices[i] >= 64)) {
+      const bool has_seq = program_has_sequential(g.prog);
+      if (!has_seq && !getenv("DUSP_TILE")) { T = 32; B = 8; }  // measured: W2 10k voices 4.6 ms at (8,32) vs 9.6 ms at (8,4)
+      if (want && (pe ? atoi(pe) != 0 : voices[i] >= 64 && has_seq)) {
         int vc = 0;
         if (const char *ve = getenv("DUSP_PIPED_VC")) vc = atoi(ve);
         if (!vc) {  // fewest voices on the fullest SM
           long long best = 1LL << 60;
-          for (int c : {32, 24, 16}) {
+          for (int c : {32, 24, 16, 8}) {  // ties go to the larger CTA (fuller lane-per-voice warp)
             const long long ctas = ((long long)voices[i] + c - 1) / c, per_sm = (ctas + 147) / 148 * c;
             if (per_sm < best) { best = per_sm; vc = c; }
           }
@@ -428,13 +430,19 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     kp.multi = s->d_multi; kp.n_voices = s->n_multi; kp.n_slots = s->multi_slots; kp.nv_stride = 1;
     kp.tables = s->d_tables; kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = 1; kp.out_mode = out_mode;
     kp.out_len = n; kp.clock0 = s->clock; kp.n_samples = n;
-    int wpc = 4;
-    while (wpc > 1 && (size_t)s->multi_slots * 8 * 128 * wpc > 100 * 1024) wpc >>= 1;
+    // samples per lane / warps per CTA: 4 / 1 keeps a warp's slots at 15 KB for the W4 circuits, so ~14 circuits are
+    // resident per SM (measured, 4000 circuits x 4 s: 689 ms against 1119 ms at 8 / 2); DUSP_MULTI_B / _WPC override
+    int mb = 4;
+    if (const char *e = getenv("DUSP_MULTI_B")) mb = atoi(e) == 8 ? 8 : 4;
+    int wpc = 1;
+    if (const char *e = getenv("DUSP_MULTI_WPC")) wpc = std::max(1, std::min(4, atoi(e)));
+    while (wpc > 1 && (size_t)s->multi_slots * mb * 128 * wpc > 100 * 1024) wpc >>= 1;
     int grid = 0, smem = 0;
-    int e = dusp_launch_render(&kp, 8, 32, wpc, st, &grid, &smem);
+    int e = dusp_launch_render(&kp, mb, 32, wpc, st, &grid, &smem);
     if (e != 0) return fail(DUSP_ECUDA, std::string("render launch: ") + cudaGetErrorString((cudaError_t)e));
     s->launches++;
     s->last_grid = grid; s->last_block = wpc * 32; s->last_smem = smem; s->last_fused = false;
+    for (auto &g : s->groups) if (g.in_multi) g.sub_block = mb;
   }
   for (auto &g : s->groups) {
     if (g.in_multi) continue;

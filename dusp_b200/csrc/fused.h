@@ -42,6 +42,9 @@ struct PipedInfo {
 };
 // "" when the program has no admissible 3-stage split (the caller falls back to the tile kernel).
 std::string generate_piped_source(const Program &p, int voices_per_cta, PipedInfo *info);
+// true when some op has no time-parallel form (recursive filter, Shape, scatter delay ...): only then does the
+// pipeline pay; purely time-parallel circuits run fastest on the tile kernel with all 32 lanes along time
+bool program_has_sequential(const Program &p);
 FusedKernel *piped_get(const Program &p, int voices_per_cta, PipedInfo *info, std::string &err);
 size_t piped_compile_only(const Program &p, int voices_per_cta, PipedInfo *info, std::string &err, std::string *src_out);
 

@@ -148,6 +148,11 @@ namespace {
 std::string generate(const Program &p, int VC, int STEP, PipedInfo *info);
 }
 
+bool program_has_sequential(const Program &p) {
+  for (const DuspInstr &I : p.code) if (sequential_only(p, I)) return true;
+  return false;
+}
+
 std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
   if (VC < 8 || VC > 32 || VC % 8) return "";
   if (const char *se = getenv("DUSP_PIPED_STEP")) return generate(p, VC, atoi(se) == 128 ? 128 : 256, info);

@@ -654,7 +654,7 @@ __device__ __forceinline__ void op_cbtapc(const Lane<B, T> &L, const DuspDevInst
 // --------------------------------------------------------------- the kernel
 // registers are capped so that at least 16 (B=8) / 8 (B=16) warps are resident per SM
 template <int B, int T>
-__global__ void __launch_bounds__(128, B == 8 ? 4 : 2) dusp_render_tile(const __grid_constant__ DuspKernelParams kp) {
+__global__ void __launch_bounds__(128, B <= 8 ? 4 : 2) dusp_render_tile(const __grid_constant__ DuspKernelParams kp) {
   static_assert(B % 4 == 0 && (DUSP_CHUNK % (B * T)) == 0 && 32 % T == 0, "tile must divide the chunk");
   extern __shared__ float4 smem[];
   constexpr int V = 32 / T;
@@ -874,7 +874,7 @@ int launch(const DuspKernelParams *kp, int warps_per_cta, cudaStream_t st, int *
 }  // namespace
 
 // --------------------------------------------------------------- launcher
-#define DUSP_CONFIGS(X) X(16, 1) X(8, 1) X(8, 4) X(16, 4) X(8, 8) X(16, 8) X(16, 16) X(8, 32)
+#define DUSP_CONFIGS(X) X(16, 1) X(8, 1) X(8, 4) X(16, 4) X(8, 8) X(16, 8) X(16, 16) X(8, 32) X(4, 32)
 
 extern "C" int dusp_launch_supported(int sub_block, int time_lanes) {
 #define X(BV, TV) if (sub_block == BV && time_lanes == TV) return 1;
