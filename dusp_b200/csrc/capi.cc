@@ -253,7 +253,11 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
           }
         }
         std::string err;
-        g.fused = piped_get(g.prog, vc, &g.pinfo, err);
+        // the pipeline pays while the lane-per-voice warp carries a small part of the circuit (W3: 1 op of 14);
+        // a feedback loop that runs there almost entirely (W3b: 7 of 13) is faster on the tile kernel (measured)
+        PipedInfo probe;
+        const bool worth = pe || (!generate_piped_source(g.prog, vc, &probe).empty() && probe.n_ops_sequential_stage * 3 <= probe.n_ops);
+        if (worth) g.fused = piped_get(g.prog, vc, &g.pinfo, err);
         if (g.fused) { g.piped = true; g.sub_block = 4; g.time_lanes = 32; g.warps_per_cta = 5; }
         else if (pe) s->warning = "pipelined kernel unavailable: " + err;
       }

@@ -39,6 +39,7 @@ size_t fused_compile_only(const Program &p, int B, int T, int min_blocks, std::s
 // voice per lane, one 128-sample step behind, exchanging signals through swizzled shared memory.
 struct PipedInfo {
   int voices_per_cta = 0, threads = 0, smem_bytes = 0, n_buffers = 0;
+  int n_ops = 0, n_ops_sequential_stage = 0;  // how much of the circuit lands on the one lane-per-voice warp
 };
 // "" when the program has no admissible 3-stage split (the caller falls back to the tile kernel).
 std::string generate_piped_source(const Program &p, int voices_per_cta, PipedInfo *info);

@@ -461,6 +461,45 @@ template <int B, int T, bool MONO>
 DOPS_DEV void c_delay(const Cx<B, T> &cx, float (&x)[B], const float (&dl)[B], float *buf, int n, long long t0) {
   const double len = (double)n;
   serial0<B, T>(cx, [&] {
+    // Fast path: the delay is one value over the lane's B samples, at least B + 1 samples long, and neither the
+    // read window [tb, tb+B) nor the write window [floor(tb+d), +B+1) wraps or meets the other.  Then the B reads
+    // see the ring as of the start of the run, and the 2B scatter-adds touch B + 1 consecutive slots in a fixed
+    // order -- done in registers in exactly that order: independent loads and stores instead of a chain of 4B
+    // dependent memory round trips.  Anything else takes the literal loop below.
+    {
+      bool same = true;
+#pragma unroll
+      for (int s = 1; s < B; s++) same = same && dl[s] == dl[0];
+      double tb0 = (double)t0;
+      if (!(tb0 < len)) tb0 = fmod(tb0, len);
+      const double dd = (double)dl[0];
+      if (same && dd >= (double)(B + 1) && dd <= len - (double)(B + 2) && tb0 + (double)B <= len) {
+        double tw0 = tb0 + dd;
+        if (tw0 >= len) tw0 -= len;
+        const double fr = tw0 - trunc(tw0);
+        const long long fl0 = (long long)tw0;
+        const int ceo = fr != 0.0 ? 1 : 0;
+        if (fl0 + B + ceo <= (long long)n) {
+          float *rd = buf + (long long)tb0, *wr = buf + fl0;
+          float y[B], w[B + 1];
+#pragma unroll
+          for (int s = 0; s < B; s++) y[s] = rd[s];
+#pragma unroll
+          for (int j = 0; j < B + 1; j++) w[j] = (j < B || ceo) ? wr[j] : 0.0f;
+#pragma unroll
+          for (int s = 0; s < B; s++) {
+            w[s] = (float)((double)w[s] + (double)x[s] * (1.0 - fr));
+            if (ceo) w[s + 1] = (float)((double)w[s + 1] + (double)x[s] * fr);
+            else w[s] = (float)((double)w[s] + (double)x[s] * fr);
+          }
+#pragma unroll
+          for (int j = 0; j < B + 1; j++) if (j < B || ceo) wr[j] = w[j];
+#pragma unroll
+          for (int s = 0; s < B; s++) { rd[s] = 0.0f; x[s] = y[s]; }
+          return;
+        }
+      }
+    }
 #pragma unroll
     for (int s = 0; s < B; s++) {
       double tb = (double)(t0 + s);

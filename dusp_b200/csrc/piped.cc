@@ -93,11 +93,25 @@ bool make_plan(const Program &p, Plan &pl) {
   }
   std::vector<char> seq(n), anc(n, 0), desc(n, 0);
   for (int i = 0; i < n; i++) seq[i] = sequential_only(p, p.code[i]);
-  for (int i = 0; i < n; i++) {  // desc: depends on a sequential op
-    for (auto &d : prod[i]) if (seq[d.first] || desc[d.first]) desc[i] = 1;
-  }
-  for (int i = n - 1; i >= 0; i--) {  // anc: feeds a sequential op
-    if (seq[i] || anc[i]) for (auto &d : prod[i]) anc[d.first] = 1;
+  // desc: depends on a sequential op; anc: feeds one.  Ops coupled through a ring or a stale buffer act as one
+  // node (a feedback loop closes through its stale buffer: the whole loop then sits between sequential ops and
+  // runs in the lane-per-voice warp), so the two properties are propagated to a fixed point.
+  for (bool changed = true; changed;) {
+    changed = false;
+    auto set = [&](std::vector<char> &v, int i) { if (!v[i]) { v[i] = 1; changed = true; } };
+    for (int i = 0; i < n; i++)
+      for (auto &d : prod[i]) {
+        if (seq[d.first] || desc[d.first]) set(desc, i);
+        if (seq[i] || anc[i]) set(anc, d.first);
+      }
+    std::map<int, std::pair<bool, bool>> grp;
+    for (int i = 0; i < n; i++) { int key = coupling_key(p.code[i]); if (key >= 0) { grp[key].first |= anc[i] != 0; grp[key].second |= (desc[i] || seq[i]); } }
+    for (int i = 0; i < n; i++) {
+      int key = coupling_key(p.code[i]);
+      if (key < 0) continue;
+      if (grp[key].first) set(anc, i);
+      if (grp[key].second && !seq[i]) set(desc, i);
+    }
   }
   pl.stage.assign(n, 2);
   for (int i = 0; i < n; i++) pl.stage[i] = seq[i] ? 1 : (anc[i] && desc[i]) ? 1 : anc[i] ? 0 : 2;
@@ -229,7 +243,11 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   const bool dyn = getenv("DUSP_PIPED_DYN") != nullptr;
   const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double) + 16;
   if (smem > 200 * 1024) return "";
-  if (info) { info->voices_per_cta = VC; info->threads = 160; info->smem_bytes = (int)smem; info->n_buffers = NB; }
+  if (info) {
+    info->voices_per_cta = VC; info->threads = 160; info->smem_bytes = (int)smem; info->n_buffers = NB;
+    info->n_ops = n; info->n_ops_sequential_stage = 0;
+    for (int i = 0; i < n; i++) info->n_ops_sequential_stage += pl.stage[i] == 1;
+  }
   int min_blocks = (int)std::min<size_t>(4, (227 * 1024) / (smem + 1024));
   if (min_blocks < 1) min_blocks = 1;
 
