@@ -1,4 +1,4 @@
-// piped.cc -- the pipelined render kernel: one CTA renders VC voices, 128 samples per step.
+// piped.cc -- the pipelined render kernel: one CTA renders VC voices, 256 (or 128) samples per step.
 //
 // Why: inside a 256-sample chunk no unit depends on a later unit (every feedback path of the
 // reference has >= one chunk of latency), so a circuit's op program splits into
@@ -7,13 +7,13 @@
 //   stage 2  time-parallel ops that consume them                   (rings, Multiply/Sum, Pan, copy-out)
 // and the stages can run on DIFFERENT steps at the same moment (software pipeline):
 //   * warps 0..3 ("P-warps", VC/4 voices each) run stage 0 of step k+1 and stage 2 of step k-1 with
-//     LANES ALONG TIME: lane l owns samples [4l, 4l+4) of the step, so a warp touches 512 contiguous
-//     bytes of a ring / stale buffer / output row per access (fully coalesced), phase accumulators
+//     LANES ALONG TIME: lane l owns samples [8l, 8l+8) of the step, so a warp touches 1 KB contiguous
+//     of a ring / stale buffer / output row per access (fully coalesced), phase accumulators
 //     are warp-shuffle scans (ops.cuh cores with T = 32);
 //   * warp 4 (the "S-warp") runs stage 1 of step k with ONE VOICE PER LANE: VC independent
 //     recurrences in exactly the reference's sequential order (ops.cuh cores with T = 1), unit
 //     state in registers for the whole launch;
-//   * signals crossing a stage boundary live in shared memory, [rotation 3][buffer][voice][128]
+//   * signals crossing a stage boundary live in shared memory, [rotation 3][buffer][voice][256]
 //     floats; the float4 column is XOR-swizzled with the voice so that both access patterns (a row
 //     per warp / a column per warp) are bank-conflict free;
 //   * one __syncthreads per step.  The recurrences' latency (the bound of this path: VC chains per
