@@ -27,7 +27,7 @@ SYMBOLS = [
     "dusp_program_disassemble", "dusp_session_create", "dusp_session_destroy", "dusp_session_num_voices",
     "dusp_session_num_channels", "dusp_session_unit_count", "dusp_session_set_params", "dusp_session_reset",
     "dusp_session_render", "dusp_session_launch_count", "dusp_session_launch_info", "dusp_rand53",
-    "dusp_session_tile_info", "dusp_session_warning", "dusp_program_specialise",
+    "dusp_session_tile_info", "dusp_session_warning", "dusp_program_specialise", "dusp_session_poke",
 ]
 
 
@@ -68,6 +68,7 @@ def load():
     L.dusp_session_unit_count.restype = c.c_longlong
     L.dusp_session_set_params.argtypes = [c.c_void_p, c.c_int, c.POINTER(c.c_int), c.c_int, c.POINTER(c.c_double)]
     L.dusp_session_reset.argtypes = [c.c_void_p]
+    L.dusp_session_poke.argtypes = [c.c_void_p, c.c_int, c.c_int, c.c_int, c.POINTER(c.c_int), c.POINTER(c.c_double), c.c_void_p]
     L.dusp_session_render.argtypes = [c.c_void_p, c.c_longlong, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p]
     L.dusp_session_launch_count.argtypes = [c.c_void_p]
     L.dusp_session_launch_count.restype = c.c_longlong
@@ -183,6 +184,18 @@ class Session:
 
     def reset(self):
         check(load().dusp_session_reset(self._h))
+
+    def poke(self, program_index, voice, names, values):
+        """Assign unit state / parameter words on the device between two renders (events):
+        ``voice`` = index within the program group, or -1 for every voice of the group."""
+        L = load()
+        prog = self.programs[program_index]
+        try:
+            ids = (ctypes.c_int * len(names))(*[prog.param_index(n) if isinstance(n, str) else int(n) for n in names])
+        except DuspError as e:
+            raise UnsupportedCircuit("event assigns state the compiled program does not hold: " + str(e))
+        vals = (ctypes.c_double * len(names))(*[float(v) for v in values])
+        check(L.dusp_session_poke(self._h, program_index, int(voice), len(names), ids, vals, None))
 
     def render_host(self, n_samples, out_mode=OUT_VOICES):
         """Render into a fresh host array: [voices][channels][n] or [2][n] (mix)."""

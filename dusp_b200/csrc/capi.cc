@@ -394,6 +394,46 @@ int dusp_session_set_params(dusp_session *s, int gi, const int *ids, int n_ids, 
   return DUSP_OK;
 }
 
+int dusp_session_poke(dusp_session *s, int gi, int voice, int n_ids, const int *ids, const double *values, void *cuda_stream) {
+  if (!s || gi < 0 || gi >= (int)s->groups.size() || n_ids < 0 || (n_ids && (!ids || !values)))
+    return fail(DUSP_EINVAL, "dusp_session_poke: bad arguments");
+  Group &g = s->groups[gi];
+  if (voice < -1 || voice >= g.n_voices) return fail(DUSP_EINVAL, "dusp_session_poke: no such voice");
+  const int nw = (int)g.prog.words.size();
+  for (int k = 0; k < n_ids; k++) {
+    if (ids[k] < 0 || ids[k] >= nw) return fail(DUSP_EINVAL, "dusp_session_poke: no such parameter");
+    for (const Derived &d : g.prog.derived)
+      if (d.src0 == ids[k] || d.src1 == ids[k])
+        return fail(DUSP_EUNSUPPORTED, "parameter " + g.prog.words[ids[k]].name + " was specialised at compile time and cannot change during a render");
+    for (auto &l : g.prog.locked) if (l.word == ids[k]) return fail(DUSP_EUNSUPPORTED, "parameter " + g.prog.words[ids[k]].name + " is locked by a compile-time specialisation");
+    for (auto &e : g.prog.equal_words) if (e.word_a == ids[k] || e.word_b == ids[k]) return fail(DUSP_EUNSUPPORTED, "parameter " + g.prog.words[ids[k]].name + " belongs to merged units");
+    for (auto &t : g.prog.tap_pairs) if (t.word_a == ids[k] || t.word_b == ids[k]) return fail(DUSP_EUNSUPPORTED, "CircleBuffer tap offsets cannot change during a render");
+  }
+  CUDA_TRY(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  // pending (re)initialisation must land first, or it would overwrite the poke
+  if (g.dirty) {
+    CUDA_TRY(cudaMemcpyAsync(g.d_words, g.h_words.data(), g.h_words.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemsetAsync(g.d_rings, 0, (size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad * sizeof(float), st));
+    CUDA_TRY(cudaMemsetAsync(g.d_stale, 0, (size_t)std::max(g.prog.n_stale, 1) * DUSP_CHUNK * g.nv_pad * sizeof(float), st));
+    g.dirty = false;
+  }
+  std::vector<double> row;
+  for (int k = 0; k < n_ids; k++) {  // in order: a later assignment of the same word wins, like the event's own statements
+    const Param &p = g.prog.words[ids[k]];
+    const double v = p.f32 ? (double)(float)values[k] : values[k];
+    double *dst = g.d_words + (size_t)ids[k] * g.nv_pad;
+    if (voice >= 0) {
+      CUDA_TRY(cudaMemcpyAsync(dst + voice, &v, sizeof(double), cudaMemcpyHostToDevice, st));
+    } else {
+      row.assign((size_t)g.nv_pad, v);
+      CUDA_TRY(cudaMemcpyAsync(dst, row.data(), row.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+    }
+    CUDA_TRY(cudaStreamSynchronize(st));  // the staging values live on this stack frame
+  }
+  return DUSP_OK;
+}
+
 int dusp_session_reset(dusp_session *s) {
   if (!s) return fail(DUSP_EINVAL, "dusp_session_reset: null session");
   for (auto &g : s->groups) g.dirty = true;

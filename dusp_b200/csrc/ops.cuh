@@ -43,8 +43,8 @@ namespace dops {
 constexpr double SRD = 44100.0;
 
 // ---------------------------------------------------------------- helpers
-DOPS_DEV double js_or0(double x) { return (x != x || x == 0.0) ? 0.0 : x; }  // `x || 0`
-DOPS_DEV float js_or0f(float x) { return (x != x || x == 0.0f) ? 0.0f : x; }
+DOPS_DEV double js_or0(double x) { return fabs(x) > 0.0 ? x : 0.0; }  // `x || 0`: NaN, +0, -0 -> +0 (one compare: |x| > 0 is false for all three)
+DOPS_DEV float js_or0f(float x) { return fabsf(x) > 0.0f ? x : 0.0f; }
 
 // JS `x % 44100` (= C fmod) with exact fast paths for the common range.
 DOPS_DEV double fmod_sr(double x) {

@@ -181,6 +181,8 @@ namespace {
 
 std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   const int PB = STEP / 32;  // samples per lane in the P-warps and per S-warp group
+  int NP = 4;                // P-warps per CTA (VC / NP voices each); DUSP_PIPED_PWARPS overrides (experiments)
+  if (const char *e = getenv("DUSP_PIPED_PWARPS")) { int v = atoi(e); if (v >= 1 && v <= 8 && VC % v == 0) NP = v; }
   Plan pl;
   if (!make_plan(p, pl)) return "";
   const int n = (int)p.code.size();
@@ -244,7 +246,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double) + 16;
   if (smem > 200 * 1024) return "";
   if (info) {
-    info->voices_per_cta = VC; info->threads = 160; info->smem_bytes = (int)smem; info->n_buffers = NB;
+    info->voices_per_cta = VC; info->threads = (NP + 1) * 32; info->smem_bytes = (int)smem; info->n_buffers = NB;
     info->n_ops = n; info->n_ops_sequential_stage = 0;
     for (int i = 0; i < n; i++) info->n_ops_sequential_stage += pl.stage[i] == 1;
   }
@@ -278,8 +280,8 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "  else if ((CH) < 2 && active) { UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) {\\\n"
     << "      atomicAdd(kp.out + (long long)(CH) * kp.out_len + tl0 + i_, a[i_]);\\\n"
     << "      if (kp.prog_nch == 1) atomicAdd(kp.out + kp.out_len + tl0 + i_, a[i_]); } } }\n"
-    << "extern \"C\" __global__ void __launch_bounds__(160, " << min_blocks << ") dusp_piped(const __grid_constant__ FusedParams kp) {\n"
-    << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", ROW = STEP / 4, VW = VC / 4;\n"
+    << "extern \"C\" __global__ void __launch_bounds__(" << (NP + 1) * 32 << ", " << min_blocks << ") dusp_piped(const __grid_constant__ FusedParams kp) {\n"
+    << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", ROW = STEP / 4, NP = " << NP << ", VW = VC / NP;\n"
     << "  extern __shared__ float4 smem4[];\n"
     << "  float4 *const xb = smem4;                                                    // [3][NB][VC][ROW] float4, swizzled\n"
     << "  double *const pw = reinterpret_cast<double *>(smem4 + 3 * NB * VC * ROW);  // [" << NPW << "][VC] words of the P-warps' units\n"
@@ -292,10 +294,10 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "  const long long n_proc = (kp.n_samples + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;  // whole chunks, like Circuit.tick\n"
     << "  const int n_steps = (int)(n_proc / STEP);\n";
   for (auto &kv : pj)
-    s << "  if (wib == " << kv.second % 5 << " && lane < VC) pw[" << kv.second << " * VC + lane] = kp.words[" << kv.first << " * nv + v0 + lane];  // "
+    s << "  if (wib == " << kv.second % (NP + 1) << " && lane < VC) pw[" << kv.second << " * VC + lane] = kp.words[" << kv.first << " * nv + v0 + lane];  // "
       << p.words[kv.first].name << "\n";
   s << "  __syncthreads();\n"
-    << "  if (wib < 4) {\n"
+    << "  if (wib < NP) {\n"
     << "    // ---------------- P-warps: lanes along time, VW voices each\n"
     << "    constexpr int T = 32;\n"
     << "    Cx<B, T> cx; cx.tl = lane; cx.lane = lane;\n"
@@ -392,7 +394,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   if (!p_mut.empty()) {
     s << "  __syncthreads();\n";
     for (int w : p_mut)
-      s << "  if (wib == " << pj[w] % 5 << " && lane < VC) kp.words[" << w << " * nv + v0 + lane] = pw[" << pj[w] << " * VC + lane];\n";
+      s << "  if (wib == " << pj[w] % (NP + 1) << " && lane < VC) kp.words[" << w << " * nv + v0 + lane] = pw[" << pj[w] << " * VC + lane];\n";
   }
   s << "}\n";
   return s.str();

@@ -36,8 +36,8 @@ namespace {
 constexpr double SRD = 44100.0;
 
 // ---------------------------------------------------------------- helpers
-__device__ __forceinline__ double js_or0(double x) { return (x != x || x == 0.0) ? 0.0 : x; }  // `x || 0`
-__device__ __forceinline__ float js_or0f(float x) { return (x != x || x == 0.0f) ? 0.0f : x; }
+__device__ __forceinline__ double js_or0(double x) { return fabs(x) > 0.0 ? x : 0.0; }  // `x || 0`: NaN, +0, -0 -> +0 (one compare: |x| > 0 is false for all three)
+__device__ __forceinline__ float js_or0f(float x) { return fabsf(x) > 0.0f ? x : 0.0f; }
 
 // JS `x % 44100` (= C fmod) with exact fast paths for the common range.
 __device__ __forceinline__ double fmod_sr(double x) {

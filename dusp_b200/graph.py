@@ -148,6 +148,24 @@ class Inlet(Piglet):
 
 
 # ---------------------------------------------------------------- events
+# While an event function runs for the accelerated path (render.collect_events), every attribute a unit is
+# assigned is recorded here: the assignments ARE the event as far as the device is concerned (they become
+# word pokes between two launches).
+_recorder = None
+
+
+class record_assignments:
+    def __enter__(self):
+        global _recorder
+        _recorder = []
+        return _recorder
+
+    def __exit__(self, *exc):
+        global _recorder
+        _recorder = None
+        return False
+
+
 class Event:
     """src/Event.js:3-30 (``time`` in seconds, ``t`` in samples)."""
 
@@ -244,11 +262,15 @@ class Unit(UnitOrPatch):
             inlet = sugar[name]
             if val is None:
                 raise DuspError("Passed bad value to " + inlet.label)
+            if _recorder is not None:
+                _recorder.append((self, "@" + inlet.name, val))
             if _is_number(val) or isinstance(val, (list, tuple)):
                 inlet.setConstant(val)
             if isinstance(val, (Outlet, UnitOrPatch)):
                 inlet.connect(val)
             return
+        if _recorder is not None:
+            _recorder.append((self, name, val))
         object.__setattr__(self, name, val)
 
     def __getattr__(self, name):

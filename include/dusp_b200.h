@@ -102,6 +102,16 @@ int dusp_session_set_params(dusp_session *s, int program_index, const int *param
                             const double *values);
 int dusp_session_reset(dusp_session *s); /* back to clock 0 / initial unit state */
 
+/* Replaces: an Event's function running before a tick (Event.js:18-30, Circuit.js:23,57-65), e.g. the
+ * `trigger()` that scheduleTrigger / the `at` operator queue (UnitOrPatch.js:25-33,
+ * constructOperation.js:63-69): between two renders (the session clock is chunk-aligned there, like the
+ * reference's event granularity) assign unit-state words of voice `voice` of program `program_index`
+ * (-1 = every voice of the group) on the device.  Unlike dusp_session_set_params this keeps the clock and
+ * all other state.  Words that compile-time specialisations derive from (a constant filter cutoff, a
+ * constant pan ...) cannot be poked: DUSP_EUNSUPPORTED.  Enqueued on `cuda_stream`. */
+int dusp_session_poke(dusp_session *s, int program_index, int voice, int n_ids, const int *param_ids,
+                      const double *values, void *cuda_stream);
+
 /* Replaces: the `for t0 ... await circuit.tickUntil(t1)` loop and the copy-out
  * (renderChannelData.js:29-45), for all voices at once.  Renders the next
  * `n_samples` samples (the session clock advances by whole chunks, like

@@ -147,7 +147,13 @@ typedef struct Unit {
   CircleBuffer *cb; int prewipe, postwipe;
 } Unit;
 
+/* An Event (Event.js:3-30) whose function only assigns numeric unit state, e.g. the trigger() queued by
+ * scheduleTrigger / the `at` operator (UnitOrPatch.js:25-33): runs before the tick of chunk `chunk`
+ * (Circuit.js:23,57-65: events with t < clock + 256). */
+typedef struct OEvent { long chunk; int unit; char prop[24]; double value; } OEvent;
+
 typedef struct Oracle {
+  int nevents; OEvent *events;
   int nunits;
   Unit *units;
   int ncb;
@@ -382,6 +388,13 @@ Oracle *oracle_load(const char *blob, char *err, int errlen) {
       pt->chunk = chunk_new(atoi(strtok_r(NULL, " ", &save))); pt->owns = 1;
       char *cv; /* outlet.connections in connect order (Inlet.js:52) */
       while ((cv = strtok_r(NULL, " ", &save)) && pt->nconn < 64) pt->conn_unit[pt->nconn++] = atoi(cv);
+    } else if (!strcmp(tok, "EV")) {
+      o->events = (OEvent *)realloc(o->events, (o->nevents + 1) * sizeof(OEvent));
+      OEvent *ev = &o->events[o->nevents++];
+      ev->chunk = atol(strtok_r(NULL, " ", &save));
+      ev->unit = atoi(strtok_r(NULL, " ", &save));
+      snprintf(ev->prop, sizeof ev->prop, "%s", strtok_r(NULL, " ", &save));
+      ev->value = strtod(strtok_r(NULL, " ", &save), NULL);
     } else if (!strcmp(tok, "ORDER")) {
       o->order = (int *)calloc(o->nunits + 1, sizeof(int));
       char *v;
@@ -415,6 +428,7 @@ Oracle *oracle_load(const char *blob, char *err, int errlen) {
 
 void oracle_free(Oracle *o) {
   if (!o) return;
+  free(o->events);
   for (int i = 0; i < o->nunits; i++) {
     Unit *u = &o->units[i];
     for (int j = 0; j < u->nin; j++) if (u->in[j].owns) chunk_free(u->in[j].chunk);
@@ -947,6 +961,25 @@ static int unit_tick(Oracle *o, Unit *u, double clock) {
 }
 
 /* ------------------------------------------------------------------ sink */
+/* the assignments an event function makes (Ramp.js:19-23 trigger, Shape/index.js:92-99, AHD.js:23-33, Timer.js) */
+static int apply_event(Oracle *o, const OEvent *ev) {
+  if (ev->unit < 0 || ev->unit >= o->nunits) return fail(o, "event names a missing unit");
+  Unit *u = &o->units[ev->unit];
+  const char *p = ev->prop; double v = ev->value;
+  if (!strcmp(p, "t")) u->t = v;
+  else if (!strcmp(p, "playing")) u->playing = v != 0;
+  else if (!strcmp(p, "state")) u->state = (int)v;
+  else if (!strcmp(p, "phase")) u->phase = v;
+  else if (!strcmp(p, "y0")) u->y0 = v;
+  else if (!strcmp(p, "y1")) u->y1 = v;
+  else if (!strcmp(p, "duration")) u->duration = v;
+  else if (!strcmp(p, "y")) u->y = v;
+  else if (!strcmp(p, "sf")) u->sf = v;
+  else if (!strcmp(p, "finished")) u->finished = v != 0;
+  else return fail(o, "event assigns a property the oracle does not model");
+  return 0;
+}
+
 /* renderChannelData.js:5-49.  out[c] is malloc'd here (caller frees with
  * oracle_free_output); returns 0 or -1 (message via oracle_error). */
 int oracle_render(Oracle *o, double duration, float **out, int max_ch, int *nch_out, long *nsamples_out) {
@@ -958,6 +991,8 @@ int oracle_render(Oracle *o, double duration, float **out, int max_ch, int *nch_
   for (double t0 = 0; t0 < length; t0 += CHUNK) { /* :29 */
     /* circuit.tickUntil(t1): Circuit.js:19-47 -- one tick per chunk (all hot-path units tick at 256) */
     while (o->clock < t0 + CHUNK) {
+      for (int e = 0; e < o->nevents; e++)          /* Circuit.js:23 runEvents(clock + 256), in queue order */
+        if (o->events[e].chunk == (long)(o->clock / CHUNK) && apply_event(o, &o->events[e])) return -1;
       for (int i = 0; i < o->norder; i++)
         if (unit_tick(o, &o->units[o->order[i]], o->clock)) return -1;
       o->clock += CHUNK;

@@ -226,6 +226,35 @@ def at_zero():
     return d.unDusp("[Osc f:([Ramp 44100 400 200] at 0)]")
 
 
+def at_later():  # a trigger event after the first chunk (constructOperation.js:63-69, UnitOrPatch.js:25-33)
+    return d.unDusp("[Osc f:([Ramp 44100 400 200] at 0.5)]")
+
+
+def scheduled_retriggers():  # Shape envelope re-triggered by events; a Ramp whose targets an event rewrites
+    env = C.Shape("decay", 0.25).trigger()
+    env.scheduleTrigger([0.3, 0.61, 0.9])
+    ramp = C.Ramp(22050, 300, 600).trigger()
+
+    def retarget(unit):
+        unit.y0 = 600
+        unit.y1 = 150
+        unit.trigger()
+
+    ramp.schedule(0.5, retarget)
+    return C.Multiply(C.Osc(ramp), env)
+
+
+def periodic_event():  # an event function returning a positive number re-schedules itself (Event.js:18-30)
+    env = C.Shape("decay", 0.1).trigger()
+
+    def again(unit):
+        unit.trigger()
+        return 0.2
+
+    env.schedule(0.2, again)
+    return C.Multiply(C.Osc(330), env)
+
+
 # name -> (factory, seconds, exact?)
 CASES = {
     "osc440": (osc440, 1.0, True),
@@ -271,4 +300,7 @@ CASES = {
     "stereo_osc": (stereo_osc, 0.3, False),
     "midi_osc": (midi_osc, 0.2, False),
     "at_zero": (at_zero, 1.2, True),
+    "at_later": (at_later, 1.2, True),
+    "scheduled_retriggers": (scheduled_retriggers, 1.1, True),
+    "periodic_event": (periodic_event, 0.9, True),
 }

@@ -90,9 +90,14 @@ def test_unsupported_configurations_fail_loudly(lib):
     blob, _ = circuit_blob(m)
     with pytest.raises(capi.UnsupportedCircuit, match="own inlet"):
         capi.Program(blob)
-    # events after the first chunk need run-time graph edits
+    # events after the first chunk are carried as state assignments (EV records) ...
+    blob, circ = circuit_blob(d.unDusp("[Osc f:([Ramp 100 1 2] at 1)]"))
+    assert circ.device_events == [(172, 0, "playing", 1.0), (172, 0, "t", 0.0)] and "EV 172 0 playing 1" in blob
+    # ... but an event that rewires the graph (or assigns a non-number) is outside the accelerated path
+    o = C.Osc(100)
+    o.schedule(1.0, lambda unit: setattr(unit, "F", C.Osc(3)))
     with pytest.raises(capi.UnsupportedCircuit, match="event"):
-        circuit_blob(d.unDusp("[Osc f:([Ramp 100 1 2] at 1)]"))
+        circuit_blob(o)
 
 
 def test_no_cpu_fallback(lib):

@@ -46,7 +46,8 @@ def test_gpu_reproduces_golden(lib, name):
     p = capi.Program(blob)
     s = capi.Session([p], [1], 0)
     try:
-        got = s.render_host(n_samples_for(seconds))[0]
+        from dusp_b200.render import blob_events, render_segments
+        got = render_segments(s, n_samples_for(seconds), {0: blob_events(blob)})[0]
     finally:
         s.close()
     check(name, got, exact)

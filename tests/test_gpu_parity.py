@@ -17,10 +17,11 @@ TOL = 1e-5
 
 
 def gpu_render(blob, seconds, n_voices=1):
+    from dusp_b200.render import blob_events, render_segments
     p = capi.Program(blob)
     s = capi.Session([p], [n_voices], 0)
     try:
-        return s.render_host(n_samples_for(seconds))
+        return render_segments(s, n_samples_for(seconds), {0: blob_events(blob)})  # events -> pokes between segments
     finally:
         s.close()
 
@@ -273,3 +274,29 @@ def test_w4_random_circuits_in_one_multi_program_launch(lib, oracle):
     assert launches == 1, "heterogeneous batch must render in one launch per block"
     for i, b in enumerate(blobs):
         compare(got[i][:1], oracle.render(b, secs), True, "w4 circuit %d" % i)
+
+
+def test_batch_with_scheduled_events(lib, oracle, kernel_mode):
+    """trigger / state-assigning events after the first chunk, for a whole batch: the session renders
+    chunk-aligned segments and pokes the events' assignments into every voice between them (dusp_session_poke)."""
+    fac, seconds, exact = circuits.CASES["scheduled_retriggers"]
+    b = d.Batch(fac(), 70)
+    try:
+        got = b.render(seconds)
+    finally:
+        b.close()
+    want = oracle.render(b.blob, seconds)
+    for v in (0, 33, 69):
+        compare(got[v], want, exact, "events voice %d" % v)
+
+
+def test_poke_rejects_specialised_parameters(lib):
+    blob, _ = circuit_blob(circuits.w3_voice())
+    p = capi.Program(blob)
+    s = capi.Session([p], [2], 0)
+    filt = unit_index(blob, "Filter")
+    with pytest.raises(capi.UnsupportedCircuit, match="specialised"):
+        s.poke(0, -1, ["u%d.f[0]" % filt], [500.0])
+    with pytest.raises(capi.UnsupportedCircuit, match="does not hold"):
+        s.poke(0, 0, ["u%d.nonexistent" % filt], [1.0])
+    s.close()

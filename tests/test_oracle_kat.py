@@ -153,3 +153,18 @@ def test_host_scheduler_matches_oracle_scheduler(oracle, name):
     fac, _, _ = circuits.CASES[name]
     blob, circuit = circuit_blob(fac())
     assert oracle.schedule(strip_order(blob)) == list(range(len(circuit.units)))
+
+
+def test_trigger_event_after_the_first_chunk_closed_form(oracle):
+    """`x at 0.5` = stop() + scheduleTrigger(0.5) (constructOperation.js:63-69): the event's time is sample 22050,
+    so it runs before the tick of the chunk that starts at 22016 (Circuit.js:23,57-65: events with t < clock + 256).
+    Until then the stopped Ramp holds y0; from sample 22016 on it counts t = 1, 2, ... (Ramp.js:25-40)."""
+    import dusp_b200 as d
+    from dusp_b200.render import circuit_blob
+    blob, circ = circuit_blob(d.unDusp("([Ramp 44100 400 200] at 0.5)"))
+    assert circ.device_events == [(86, 0, "playing", 1.0), (86, 0, "t", 0.0)]
+    out = oracle.render(blob, 1.0)[0]
+    n = np.arange(44100)
+    t = np.clip(n - 22016 + 1, 0, 44100).astype(np.float64)
+    want = np.where(n < 22016, 400.0, 400.0 + (t / 44100.0) * (200.0 - 400.0)).astype(np.float32)
+    assert np.array_equal(out, want)
