@@ -16,6 +16,7 @@ _lib = None
 
 OUT_VOICES = 0
 OUT_MIX = 1
+OUT_VOICES_RAW = 2  # per-voice channel data exactly as the outlet's chunk holds it (NaN / -0 kept)
 E_UNSUPPORTED = -2
 
 # every symbol include/dusp_b200.h declares (tests check the .so exports them all)
@@ -200,7 +201,7 @@ class Session:
     def render_host(self, n_samples, out_mode=OUT_VOICES):
         """Render into a fresh host array: [voices][channels][n] or [2][n] (mix)."""
         import numpy as np
-        shape = (self.num_voices, self.num_channels, n_samples) if out_mode == OUT_VOICES else (2, n_samples)
+        shape = (self.num_voices, self.num_channels, n_samples) if out_mode != OUT_MIX else (2, n_samples)
         out = np.empty(shape, dtype=np.float32)
         check(load().dusp_session_render(self._h, int(n_samples), out_mode, out.ctypes.data_as(ctypes.c_void_p), None, None))
         return out

@@ -144,7 +144,7 @@ int dusp_program_num_units(const dusp_program *p) { return p->prog.n_units; }
 int dusp_program_num_instructions(const dusp_program *p) { return (int)p->prog.code.size(); }
 int dusp_program_num_slots(const dusp_program *p) { return p->prog.n_slots; }
 double dusp_program_bytes_per_voice_sample(const dusp_program *p, int out_mode) {
-  return p->prog.ring_bytes_per_sample + (out_mode == DUSP_OUT_VOICES ? 4.0 * p->prog.out_nch : 0.0);
+  return p->prog.ring_bytes_per_sample + (out_mode != DUSP_OUT_MIX ? 4.0 * p->prog.out_nch : 0.0);
 }
 int dusp_program_num_params(const dusp_program *p) { return (int)p->prog.words.size(); }
 const char *dusp_program_param_name(const dusp_program *p, int i) {
@@ -444,6 +444,8 @@ int dusp_session_reset(dusp_session *s) {
 // Enqueue the kernels that render the next `n` samples of every group into
 // d_out (row length `n`) on stream `st`.
 static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_out, cudaStream_t st) {
+  const int raw = out_mode == DUSP_OUT_VOICES_RAW;
+  if (raw) out_mode = DUSP_OUT_VOICES;
   const size_t out_floats = (out_mode == DUSP_OUT_VOICES ? (size_t)s->n_voices * s->out_nch : 2) * (size_t)n;
   // channels a group does not produce (and the mix accumulator) start at zero
   bool need_zero = out_mode == DUSP_OUT_MIX;
@@ -472,7 +474,7 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     DuspKernelParams kp;
     memset(&kp, 0, sizeof kp);
     kp.multi = s->d_multi; kp.n_voices = s->n_multi; kp.n_slots = s->multi_slots; kp.nv_stride = 1;
-    kp.tables = s->d_tables; kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = 1; kp.out_mode = out_mode;
+    kp.tables = s->d_tables; kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = 1; kp.out_mode = out_mode; kp.out_raw = raw;
     kp.out_len = n; kp.clock0 = s->clock; kp.n_samples = n;
     // samples per lane / warps per CTA: 4 / 1 keeps a warp's slots at 15 KB for the W4 circuits, so ~14 circuits are
     // resident per SM (measured, 4000 circuits x 4 s: 689 ms against 1119 ms at 8 / 2); DUSP_MULTI_B / _WPC override
@@ -498,7 +500,7 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     kp.n_voices = g.n_voices; kp.voice0 = g.voice0; kp.nv_stride = g.nv_pad;
     kp.words = g.d_words; kp.rings = g.d_rings; kp.ring_stride = std::max<long long>(g.prog.ring_floats, 4);
     kp.ring_tab = g.d_ringtab; kp.stale = g.d_stale; kp.n_stale = g.prog.n_stale; kp.tables = s->d_tables;
-    kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = g.prog.out_nch; kp.out_mode = out_mode;
+    kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = g.prog.out_nch; kp.out_mode = out_mode; kp.out_raw = raw;
     kp.out_len = n; kp.clock0 = s->clock; kp.n_samples = n;
     const int wpc = g.warps_per_cta;
     int grid = 0, smem = 0;
@@ -507,7 +509,7 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
       memset(&fp, 0, sizeof fp);
       fp.n_voices = kp.n_voices; fp.voice0 = kp.voice0; fp.nv_stride = kp.nv_stride; fp.words = kp.words;
       fp.rings = kp.rings; fp.ring_stride = kp.ring_stride; fp.stale = kp.stale; fp.tables = kp.tables; fp.out = kp.out;
-      fp.n_stale = kp.n_stale; fp.out_nch = kp.out_nch; fp.prog_nch = kp.prog_nch; fp.out_mode = kp.out_mode;
+      fp.n_stale = kp.n_stale; fp.out_nch = kp.out_nch; fp.prog_nch = kp.prog_nch; fp.out_mode = kp.out_mode; fp.out_raw = kp.out_raw;
       fp.out_len = kp.out_len; fp.clock0 = kp.clock0; fp.n_samples = kp.n_samples;
       std::string err;
       if (g.piped) {
@@ -534,7 +536,7 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
 
 int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, float *out_host, float *out_device,
                         void *cuda_stream) {
-  if (!s || n_samples < 0 || (out_mode != DUSP_OUT_VOICES && out_mode != DUSP_OUT_MIX) || (!out_host == !out_device))
+  if (!s || n_samples < 0 || (out_mode != DUSP_OUT_VOICES && out_mode != DUSP_OUT_MIX && out_mode != DUSP_OUT_VOICES_RAW) || (!out_host == !out_device))
     return fail(DUSP_EINVAL, "dusp_session_render: bad arguments");
   if (s->clock % DUSP_CHUNK) return fail(DUSP_EINVAL, "dusp_session_render: a previous render ended inside a chunk");
   CUDA_TRY(cudaSetDevice(s->device));
@@ -544,7 +546,7 @@ int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, floa
 
   // Host output: render time blocks into two device staging buffers and drain each
   // over PCIe on a second stream while the next block renders.
-  const size_t rows = out_mode == DUSP_OUT_VOICES ? (size_t)s->n_voices * s->out_nch : 2;
+  const size_t rows = out_mode != DUSP_OUT_MIX ? (size_t)s->n_voices * s->out_nch : 2;
   size_t staging_mb = 1024;  // per staging buffer (measured on B200: 1 GB blocks drain at 50 GB/s, 256 MB at 46); DUSP_STAGING_MB overrides (longer rows per 2-D copy)
   if (const char *e = getenv("DUSP_STAGING_MB")) staging_mb = (size_t)std::max(16, atoi(e));
   long long blk = (long long)((staging_mb << 20) / (rows * sizeof(float)));

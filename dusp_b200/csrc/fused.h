@@ -18,6 +18,7 @@ struct FusedParams {
   const float *tables;
   float *out;
   int n_stale, out_nch, prog_nch, out_mode;
+  int out_raw, pad_;
   long long out_len, clock0, n_samples;
 };
 

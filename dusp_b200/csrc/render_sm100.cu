@@ -821,8 +821,10 @@ __global__ void __launch_bounds__(128, B <= 8 ? 4 : 2) dusp_render_tile(const __
         case OP_OUT: {  // renderChannelData.js:42-44
           float x[B];
           L.ld(x, I.in[0]);
+if (!kp.out_raw) {
 #pragma unroll
-          for (int s = 0; s < B; s++) x[s] = js_or0f(x[s]);
+            for (int s = 0; s < B; s++) x[s] = js_or0f(x[s]);
+          }
           if (kp.out_mode == 0) {
             if (active) {
               float *dst = out_row + (long long)I.aux0 * kp.out_len + tl0;

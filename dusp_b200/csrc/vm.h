@@ -144,7 +144,7 @@ struct DuspKernelParams {
   int32_t out_nch;       // channel stride of the output (session-wide)
   int32_t prog_nch;      // channels this program produces
   int32_t out_mode;
-  int32_t pad0;
+  int32_t out_raw;       // 1: store samples as the outlet's chunk holds them (no `x || 0`): the streaming sink's view
   int64_t out_len;       // samples per channel row in `out`
   int64_t clock0;        // absolute sample index of the first sample of this launch (multiple of 256)
   int64_t n_samples;     // samples to store (<= processed); processing covers whole chunks

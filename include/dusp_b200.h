@@ -45,8 +45,10 @@ enum {
 enum {
   DUSP_OUT_VOICES = 0, /* per-voice channel data, layout [voice][channel][n_samples] f32
                           == what renderChannelData returns for each circuit (renderChannelData.js:26-45) */
-  DUSP_OUT_MIX = 1     /* stereo mixdown only, layout [2][n_samples] f32:
+  DUSP_OUT_MIX = 1,    /* stereo mixdown only, layout [2][n_samples] f32:
                           mix[c] = sum over voices of out_v[c % nch_v]  (Sum's modulo broadcast, Sum.js:33-44) */
+  DUSP_OUT_VOICES_RAW = 2 /* as DUSP_OUT_VOICES but exactly what outlet.signalChunk.channelData holds (NaN and -0
+                          kept): the view of the streaming sink, which throws on NaN (RenderStream.js:38-52) */
 };
 
 typedef struct dusp_program dusp_program; /* a circuit compiled to a flat op program */

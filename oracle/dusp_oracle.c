@@ -982,6 +982,10 @@ static int apply_event(Oracle *o, const OEvent *ev) {
 
 /* renderChannelData.js:5-49.  out[c] is malloc'd here (caller frees with
  * oracle_free_output); returns 0 or -1 (message via oracle_error). */
+static int g_raw_copy = 0;
+/* 1: copy the root outlet's chunk as it is (what RenderStream reads, RenderStream.js:38), no `x || 0` */
+void oracle_set_raw(int raw) { g_raw_copy = raw; }
+
 int oracle_render(Oracle *o, double duration, float **out, int max_ch, int *nch_out, long *nsamples_out) {
   if (!o->has_order) oracle_schedule(o, NULL);
   double length = duration * SR;                  /* :24 */
@@ -1004,7 +1008,7 @@ int oracle_render(Oracle *o, double duration, float **out, int max_ch, int *nch_
     for (int c = 0; c < root->nch; c++)           /* :42-44: `x || 0`, out-of-range stores dropped */
       for (int t = 0; t < CHUNK; t++) {
         long i = (long)t0 + t;
-        if (i < n) { float x = root->ch[c][t]; out[c][i] = (x != x || x == 0) ? 0.f : x; }
+        if (i < n) { float x = root->ch[c][t]; out[c][i] = g_raw_copy ? x : (x != x || x == 0) ? 0.f : x; }
       }
   }
   *nch_out = nch; *nsamples_out = n;

@@ -69,9 +69,11 @@ def schedule(blob):
         lib().oracle_free(h)
 
 
-def render(blob, seconds):
-    """renderChannelData on the CPU: list of float32 arrays (one per channel)."""
+def render(blob, seconds, raw=False):
+    """renderChannelData on the CPU: list of float32 arrays (one per channel).  raw=True: the outlet's chunks as
+    they are (no `x || 0`), what the streaming sink reads (RenderStream.js:38)."""
     h = _load(blob)
+    lib().oracle_set_raw(1 if raw else 0)
     try:
         outs = (ctypes.POINTER(ctypes.c_float) * 16)()
         nch = ctypes.c_int(0)
@@ -83,6 +85,7 @@ def render(blob, seconds):
         lib().oracle_free_output(outs, nch.value)
         return res
     finally:
+        lib().oracle_set_raw(0)
         lib().oracle_free(h)
 
 
