@@ -82,8 +82,10 @@ DOPS_DEV double cb_index(double t, double len) {
   return t;
 }
 // injected PRNG (replaces Math.random, Noise.js:10,23): counter-based splitmix64 -> 53-bit uniform
-DOPS_DEV double rand53(uint64_t seed, uint64_t k) {
-  uint64_t z = seed + (k + 1) * 0x9E3779B97F4A7C15ULL;
+DOPS_DEV double rand53_mixed(uint64_t z);
+DOPS_DEV double rand53(uint64_t seed, uint64_t k) { return rand53_mixed(seed + (k + 1) * 0x9E3779B97F4A7C15ULL); }
+// the finaliser on a pre-formed counter word z = seed + (k+1)*GOLD (consecutive draws: z += GOLD, no multiply)
+DOPS_DEV double rand53_mixed(uint64_t z) {
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
   z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
   z ^= z >> 31;
@@ -229,21 +231,30 @@ DOPS_DEV void c_ramp(const Cx<B, T> &cx, float (&o)[B], double &t, double &playi
 template <int B, int T>
 DOPS_DEV void c_shape(const Cx<B, T> &cx, float (&d)[B], const float (&mn)[B], const float (&mx)[B], double &t,
                       double playing, double le, double re, const float *__restrict__ tab) {
+  // only the f64 running sum t += 1/duration is order-dependent: the divisions before it and the table
+  // interpolation after it run on every time-lane at once
+  double tt[B];
+#pragma unroll
+  for (int s = 0; s < B; s++) tt[s] = 1.0 / (double)d[s];
   serial1<B, T>(cx, t, [&] {
 #pragma unroll
     for (int s = 0; s < B; s++) {
-      if (playing != 0.0) t += 1.0 / (double)d[s];
-      const double lo = mn[s], hi = mx[s];
-      double y;
-      if (t <= 0.0) y = le * (hi - lo) + lo;
-      else if (t > SRD) y = re * (hi - lo) + lo;
-      else {
-        const double fr = t - trunc(t);  // t % 1
-        y = lo + (hi - lo) * (tab_read(tab, ceil(t)) * fr + tab_read(tab, floor(t)) * (1.0 - fr));
-      }
-      d[s] = (float)y;
+      if (playing != 0.0) t += tt[s];
+      tt[s] = t;
     }
   });
+#pragma unroll
+  for (int s = 0; s < B; s++) {
+    const double ts = tt[s], lo = mn[s], hi = mx[s];
+    double y;
+    if (ts <= 0.0) y = le * (hi - lo) + lo;
+    else if (ts > SRD) y = re * (hi - lo) + lo;
+    else {
+      const double fr = ts - trunc(ts);  // t % 1
+      y = lo + (hi - lo) * (tab_read(tab, ceil(ts)) * fr + tab_read(tab, floor(ts)) * (1.0 - fr));
+    }
+    d[s] = (float)y;
+  }
 }
 
 // AHD.js:35-76.  a: attack in, output out.
@@ -305,8 +316,9 @@ DOPS_DEV void c_noise(const Cx<B, T> &cx, float (&f)[B], double &ph, double &y, 
 template <int B, int T>
 DOPS_DEV void c_noise1(const Cx<B, T> &cx, float (&o)[B], double &y, double &draw, uint64_t seed) {
   const uint64_t d0 = (uint64_t)draw + (uint64_t)(cx.tl * B);
+  uint64_t z = seed + (d0 + 1) * 0x9E3779B97F4A7C15ULL;
 #pragma unroll
-  for (int s = 0; s < B; s++) { y = 2.0 * rand53(seed, d0 + s) - 1.0; o[s] = (float)y; }
+  for (int s = 0; s < B; s++) { y = 2.0 * rand53_mixed(z) - 1.0; o[s] = (float)y; z += 0x9E3779B97F4A7C15ULL; }
   draw += (double)(T * B);
   cx.last(y);
 }

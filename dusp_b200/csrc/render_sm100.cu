@@ -268,23 +268,32 @@ __device__ __forceinline__ void op_shape(const Lane<B, T> &L, const DuspDevInstr
   const double playing = L.w(I.p + 1);
   const double le = (I.aux1 & 1) ? (double)__ldg(tab) : L.w(I.p + 2);
   const double re = (I.aux1 & 2) ? (double)__ldg(tab + DUSP_SR) : L.w(I.p + 3);
-  L.serial([&] {  // t += 1/duration is an inexact f64 sum: keep the sequential order
+  // only the f64 running sum t += 1/duration is order-dependent: the divisions before it and the table
+  // interpolation after it run on every time-lane at once
+  double tt[B];
+#pragma unroll
+  for (int s = 0; s < B; s++) tt[s] = 1.0 / (double)d[s];
+  L.serial([&] {
     double t = L.w(I.p);
 #pragma unroll
     for (int s = 0; s < B; s++) {
-      if (playing != 0.0) t += 1.0 / (double)d[s];
-      const double lo = mn[s], hi = mx[s];
-      double y;
-      if (t <= 0.0) y = le * (hi - lo) + lo;
-      else if (t > SRD) y = re * (hi - lo) + lo;
-      else {
-        const double fr = t - trunc(t);  // t % 1
-        y = lo + (hi - lo) * (tab_read(tab, ceil(t)) * fr + tab_read(tab, floor(t)) * (1.0 - fr));
-      }
-      d[s] = (float)y;
+      if (playing != 0.0) t += tt[s];
+      tt[s] = t;
     }
     L.w(I.p) = t;
   });
+#pragma unroll
+  for (int s = 0; s < B; s++) {
+    const double ts = tt[s], lo = mn[s], hi = mx[s];
+    double y;
+    if (ts <= 0.0) y = le * (hi - lo) + lo;
+    else if (ts > SRD) y = re * (hi - lo) + lo;
+    else {
+      const double fr = ts - trunc(ts);  // t % 1
+      y = lo + (hi - lo) * (tab_read(tab, ceil(ts)) * fr + tab_read(tab, floor(ts)) * (1.0 - fr));
+    }
+    d[s] = (float)y;
+  }
   L.st(d, I.out[0]);
 }
 
