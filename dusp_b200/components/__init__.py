@@ -703,11 +703,57 @@ class CircleBufferWriter(CircleBufferNode):
         return {"t": self.t, "preWipe": int(bool(self.preWipe))}, {}
 
 
+class Retriggerer(Unit):
+    """src/components/Retriggerer.js:3-35.  No outlet: accumulates ``rate`` and calls ``target.trigger()`` whenever
+    the sum crosses the sample rate; chained before its target so the trigger lands before the target's tick.
+    On the device the decision is taken once per 256-sample chunk (every call inside one tick assigns the same
+    constants) and ``target.trigger()``'s assignments travel with the graph as ``TG`` records (render.py)."""
+    KIND = "Retriggerer"
+
+    def __init__(self, target=None, rate=None):
+        super().__init__()
+        self.addInlet("rate", {"mono": True, "type": "frequency"})
+        object.__setattr__(self, "_target", None)
+        if target:
+            self.target = target
+        self.t = 0
+        self.RATE = js_or(rate, 1)
+
+    @property
+    def target(self):
+        return self._target
+
+    @target.setter
+    def target(self, target):
+        if self._target is not None:
+            raise DuspError("re-targeting a retriggerer needs Unit.unChain, which the reference does not define")
+        if target:
+            object.__setattr__(self, "_target", target)
+            self.chainBefore(target)  # throws for a Patch, like the reference (Patch has no chainAfter)
+
+    def blob_props(self):
+        return {"t": self.t}, {}
+
+
+class SporadicRetriggerer(Retriggerer):
+    """src/components/SporadicRetrigger.js:3-32.  One ``Math.random()`` draw per tick, replaced by the unit's own
+    counter-based stream (as Noise)."""
+    KIND = "SporadicRetriggerer"
+
+    def __init__(self, target=None, rate=None, seed=None):
+        super().__init__(target, rate)
+        self.seed = config.host_random.next_noise_seed() if seed is None else int(seed) & ((1 << 64) - 1)
+        self.draw = 0
+
+    def blob_props(self):
+        return {"seed_lo": self.seed & 0xFFFFFFFF, "seed_hi": self.seed >> 32, "draw": self.draw}, {}
+
+
 __all__ = [
     "AHD", "Abs", "AllPass", "CircleBuffer", "CircleBufferNode", "CircleBufferReader", "CircleBufferWriter",
     "Clip", "CombFilter", "ConcatChannels", "CrossFader", "DecibelToScaler", "Delay", "Divide", "Filter",
     "FixedDelay", "FixedMultiply", "Gain", "HardClipAbove", "HardClipBelow", "MidiToFrequency", "MonoDelay",
     "Multiply", "Noise", "MultiChannelOsc", "Osc", "Pan", "PickChannel", "PolarityInvert", "Pow", "Ramp",
-    "ReadBackDelay", "Repeater", "Rescale", "SecondsToSamples", "SemitoneToRatio", "Shape", "SignalCombiner",
-    "Subtract", "Sum", "Timer", "VectorMagnitude",
+    "ReadBackDelay", "Repeater", "Rescale", "Retriggerer", "SecondsToSamples", "SemitoneToRatio", "Shape", "SignalCombiner",
+    "SporadicRetriggerer", "Subtract", "Sum", "Timer", "VectorMagnitude",
 ]

@@ -155,7 +155,18 @@ def constructOperation(o, index=None, destinations=None):  # constructOperation.
         a.stop()
         a.scheduleTrigger(b)
         return a
-    if op in ("for", "then", "!", "~!"):
+    if op == "!":  # regular retrigger :71-76
+        if not hasattr(a, "stop") or not hasattr(a, "trigger"):
+            raise DuspError("invalid use of '!' operator")
+        a.trigger()
+        _components.Retriggerer(a, b)
+        return a
+    if op == "~!":  # SporadicRetriggerer :78-82
+        if not hasattr(a, "stop") or not hasattr(a, "trigger"):
+            raise DuspError("invalide use of '!~' operator")
+        _components.SporadicRetriggerer(a, b)
+        return a
+    if op in ("for", "then"):
         raise DuspError("operator '" + op + "' needs run-time graph edits: outside the accelerated render path")
     raise DuspError("Unknown operator: " + op)
 

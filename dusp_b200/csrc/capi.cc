@@ -235,13 +235,16 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
       // Circuit specialisation (fused.cc): batches get a straight-line kernel compiled for this circuit
       // shape; single circuits keep the interpreter (no compile latency).  DUSP_FUSED=0/1 forces either.
       const char *fe = getenv("DUSP_FUSED");
-      const bool want = fe ? atoi(fe) != 0 : voices[i] >= 64;
+      // per-chunk control ops (Retriggerer ...) need whole-chunk tiles: the interpreter at B = 8, T = 32
+      const bool chunky = g.prog.chunk_tiles;
+      if (chunky) { B = 8; T = 32; }
+      const bool want = !chunky && (fe ? atoi(fe) != 0 : voices[i] >= 64);
       const bool pow2 = T >= 1 && T <= 32 && (T & (T - 1)) == 0 && (B == 4 || B == 8 || B == 16);
       // Pipelined kernel (piped.cc): lanes along time for the parallel units, a lane-per-voice warp for the
       // recurrences.  Default for batches; circuits without a 3-stage split use the tile kernel.  DUSP_PIPED=0/1 forces.
       const char *pe = getenv("DUSP_PIPED");
       const bool has_seq = program_has_sequential(g.prog);
-      if (!has_seq && !getenv("DUSP_TILE")) { T = 32; B = 8; }  // measured: W2 10k voices 4.6 ms at (8,32) vs 9.6 ms at (8,4)
+      if ((!has_seq && !getenv("DUSP_TILE")) || chunky) { T = 32; B = 8; }  // measured: W2 10k voices 4.6 ms at (8,32) vs 9.6 ms at (8,4)
       if (want && (pe ? atoi(pe) != 0 : voices[i] >= 64 && has_seq)) {
         int vc = 0;
         if (const char *ve = getenv("DUSP_PIPED_VC")) vc = atoi(ve);
@@ -274,7 +277,7 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
         if (g.fused) { g.sub_block = B; g.time_lanes = T; g.warps_per_cta = 1; }
       }
       if (!g.fused) {
-        if ((size_t)g.prog.n_slots * B * 128 > 200 * 1024 && T == 1) B = 8;
+        if ((size_t)g.prog.n_slots * B * 128 > 200 * 1024 && T == 1 && !chunky) B = 8;
         if (!dusp_launch_supported(B, T)) return fail(DUSP_EINVAL, "unsupported tile shape (DUSP_TILE)");
         if ((size_t)g.prog.n_slots * B * 128 > 220 * 1024)
           return fail(DUSP_EUNSUPPORTED, "circuit needs more live signal slots than shared memory holds");
@@ -327,10 +330,10 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
   {
     std::vector<DuspWarpDesc> descs;
     int n_cand = 0;
-    for (auto &g : s->groups) if (!g.fused && g.sub_block == 8 && g.time_lanes == 32) n_cand++;
+    for (auto &g : s->groups) if (!g.fused && g.sub_block == 8 && g.time_lanes == 32 && !g.prog.chunk_tiles) n_cand++;
     if (n_cand >= 2 && !getenv("DUSP_NO_MULTI"))
       for (auto &g : s->groups) {
-        if (g.fused || g.sub_block != 8 || g.time_lanes != 32) continue;
+        if (g.fused || g.sub_block != 8 || g.time_lanes != 32 || g.prog.chunk_tiles) continue;
         g.in_multi = true;
         s->multi_slots = std::max(s->multi_slots, g.prog.n_slots);
         const long long rs = std::max<long long>(g.prog.ring_floats, 4);

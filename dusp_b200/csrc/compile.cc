@@ -35,7 +35,8 @@ const char *OP_NAMES[OP_COUNT] = {
     "nop", "copy", "neg", "abs", "s2s", "semi", "db2s", "midi2f", "fixmul", "mul", "div", "pow", "add", "sub",
     "gain", "clip", "hca", "hcb", "rescale", "xfade", "pan", "vecmag", "osc", "mcosc", "ramp", "shape", "ahd",
     "timer", "noise", "filter", "fixdelay", "comb", "allpass", "delay", "monodelay", "readback", "cbwrite",
-    "cbread", "ldstale", "ststale", "out", "filterc", "panc", "gainc", "noise1", "cbwritec", "cbreadc", "add0"};
+    "cbread", "ldstale", "ststale", "out", "filterc", "panc", "gainc", "noise1", "cbwritec", "cbreadc", "add0",
+    "retrig", "sretrig", "pokeif"};
 
 struct Opnd {
   int kind = 0;  // 0 none (reads 0), 1 value, 2 const word
@@ -211,6 +212,8 @@ Program compile(const Graph &g) {
   struct Tap { int unit; bool writer; Opnd off; int ir; };
   std::map<int, std::vector<Tap>> taps;  // ring -> taps (for the reordering check)
 
+  struct TriggerFixup { int ir; std::string word; };
+  std::vector<TriggerFixup> trigger_fixups;  // OP_POKEIF targets: the retriggered unit's words come later in the order
   for (int ui : g.order) {
     const GUnit &u = g.units[ui];
     const std::string &k = u.kind;
@@ -272,6 +275,35 @@ Program compile(const Graph &g) {
       IR &r = b.emit(OP_TIMER, ui, 0);
       r.p = b.word(un + ".t", u.num("t", 0), false);
       b.def(r, 0, ui, 0, 0);
+    } else if (k == "Retriggerer" || k == "SporadicRetriggerer") {
+      // control-rate units: no outlet; they decide once per chunk whether to run target.trigger(),
+      // whose assignments travel as TG records and become conditional word stores placed right after the unit
+      if (u.in.empty()) throw std::runtime_error("unit " + k + " has too few ports in graph blob");
+      const bool sporadic = k == "SporadicRetriggerer";
+      int flag;
+      {
+        IR &r = b.emit(sporadic ? OP_SRETRIG : OP_RETRIG, ui, 0); r.in[0] = b.in_ref(ui, 0, 0); r.root = true;
+        if (sporadic) {
+          r.p = b.word(un + ".draw", u.num("draw", 0), false);
+          b.word(un + ".seed_lo", u.num("seed_lo", 0), false);
+          b.word(un + ".seed_hi", u.num("seed_hi", 0), false);
+          flag = b.word(un + ".~fired", 0, false);
+        } else {
+          r.p = b.word(un + ".t", u.num("t", 0), false);
+          flag = b.word(un + ".~fired", 0, false);
+        }
+      }
+      int k_tg = 0;
+      for (const GTrigger &tg : g.triggers) {
+        if (tg.unit != ui) continue;
+        // (a unit that ticks BEFORE this one -- an input of the chained target, reached through the default
+        //  Unit.trigger, Unit.js:293-297 -- sees the assignment from its next tick on, here as in the reference)
+        IR &q = b.emit(OP_POKEIF, ui, k_tg); q.root = true;
+        q.aux[0] = flag;
+        q.aux[1] = b.word(un + ".~tg" + std::to_string(k_tg++), tg.value, false);
+        trigger_fixups.push_back({(int)b.ir.size() - 1, Builder::uname(tg.target) + "." + tg.prop});
+      }
+      b.prog.chunk_tiles = true;
     } else if (k == "Noise") {
       need_in(1);
       if (b.nch[ui][0] != 1) throw Unsupported("multi-channel Noise shares one phase across channels chunk by chunk (Noise.js:17-27)");
@@ -451,6 +483,17 @@ Program compile(const Graph &g) {
     } else {
       throw Unsupported("unit kind " + k + " is outside the accelerated render path");
     }
+  }
+
+  // ---- retrigger targets: the state words target.trigger() assigns ----
+  for (auto &f : trigger_fixups) {
+    int w = -1;
+    for (size_t i = 0; i < b.prog.words.size(); i++) if (b.prog.words[i].name == f.word) { w = (int)i; break; }
+    if (w < 0) throw Unsupported("trigger() assigns " + f.word + ", which is not unit state on the device");
+    for (const Derived &d : b.prog.derived)
+      if (d.src0 == w || d.src1 == w) throw Unsupported("trigger() assigns " + f.word + ", which was specialised at compile time");
+    for (auto &l : b.prog.locked) if (l.word == w) throw Unsupported("trigger() assigns " + f.word + ", which is locked by a specialisation");
+    b.ir[f.ir].p = w;
   }
 
   // ---- CircleBuffer taps: sub-block interleaving must not reorder accesses --

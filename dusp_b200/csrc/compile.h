@@ -49,6 +49,7 @@ struct Program {
   int n_stale = 0;
   int out_nch = 0;
   int n_units = 0;              // units the reference ticks per chunk (metric: unit-samples)
+  bool chunk_tiles = false;     // has per-chunk control ops (OP_RETRIG ...): must render in whole-chunk tiles (B*T = 256)
   double ring_bytes_per_sample = 0;  // SURVEY 8d accounting
   std::vector<TapPair> tap_pairs;
   std::vector<Derived> derived;

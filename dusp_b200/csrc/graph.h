@@ -28,11 +28,14 @@ struct GUnit {
 };
 
 struct GCircleBuffer { int nch; long long len; };
+// one assignment of `target.trigger()` for a (Sporadic)Retriggerer unit: TG <unit> <target> <prop> <value>
+struct GTrigger { int unit, target; std::string prop; double value; };
 
 struct Graph {
   std::vector<GUnit> units;
   std::vector<GCircleBuffer> cbs;
   std::vector<int> order;
+  std::vector<GTrigger> triggers;
   int root_unit = -1, root_outlet = 0;
 };
 

@@ -361,6 +361,45 @@ __device__ __forceinline__ void op_noise(const Lane<B, T> &L, const DuspDevInstr
   L.st(f, I.out[0]);
 }
 
+// Control-rate retriggering.  The decision covers one whole 256-sample chunk and must land before
+// the target ticks that chunk: the host only runs these programs with whole-chunk tiles (B * T = 256).
+template <int B, int T>
+__device__ __forceinline__ void op_retrig(const Lane<B, T> &L, const DuspDevInstr &I) {  // Retriggerer.js:13-22
+  float r[B];
+  L.ld(r, I.in[0]);
+  if (L.tl == 0) L.w(I.p + 1) = 0.0;
+  L.sync();
+  L.serial([&] {
+    double t = L.w(I.p);
+    bool fired = false;
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      t += (double)r[s];
+      if (t >= SRD) { fired = true; t -= SRD; }
+    }
+    L.w(I.p) = t;
+    if (fired) L.w(I.p + 1) = 1.0;
+  });
+}
+template <int B, int T>
+__device__ __forceinline__ void op_sretrig(const Lane<B, T> &L, const DuspDevInstr &I) {  // SporadicRetrigger.js:12-16
+  float r[B];
+  L.ld(r, I.in[0]);
+  if (L.tl == 0) {
+    const double draw = L.w(I.p);
+    const uint64_t seed = (uint64_t)L.w(I.p + 1) | ((uint64_t)L.w(I.p + 2) << 32);
+    const bool fired = rand53(seed, (uint64_t)draw) < (double)r[0] * (double)DUSP_CHUNK / SRD;
+    L.w(I.p) = draw + 1.0;
+    L.w(I.p + 3) = fired ? 1.0 : 0.0;
+  }
+  L.sync();
+}
+template <int B, int T>
+__device__ __forceinline__ void op_pokeif(const Lane<B, T> &L, const DuspDevInstr &I) {  // one assignment of target.trigger()
+  if (L.tl == 0 && L.w(I.aux0) != 0.0) L.w(I.p) = L.w(I.aux1);
+  L.sync();
+}
+
 template <int B, int T>
 __device__ __forceinline__ void op_noise1(const Lane<B, T> &L, const DuspDevInstr &I) {  // Noise.js:16-28 with F >= sampleRate
   const double draw = L.w(I.p + 2);
@@ -804,6 +843,9 @@ __global__ void __launch_bounds__(128, B <= 8 ? 4 : 2) dusp_render_tile(const __
         case OP_TIMER: op_timer<B, T>(L, I); break;
         case OP_NOISE: op_noise<B, T>(L, I); break;
         case OP_NOISE1: op_noise1<B, T>(L, I); break;
+        case OP_RETRIG: if (B * T == DUSP_CHUNK) op_retrig<B, T>(L, I); break;
+        case OP_SRETRIG: if (B * T == DUSP_CHUNK) op_sretrig<B, T>(L, I); break;
+        case OP_POKEIF: if (B * T == DUSP_CHUNK) op_pokeif<B, T>(L, I); break;
         case OP_FILTER: op_filter<B, T>(L, I); break;
         case OP_FILTERC: op_filterc<B, T>(L, I); break;
         case OP_FIXDELAY: case OP_COMB: case OP_ALLPASS: op_fixdelay<B, T>(L, I); break;

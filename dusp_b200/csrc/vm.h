@@ -69,6 +69,10 @@ enum DuspOp : int32_t {
   OP_CBREADC,   // CircleBufferReader, constant OFFSET
   OP_ADD0,      // (0 + in0) + in1: what a preWipe writer followed by a mixing writer leave on one ring position
                 //  (CircleBufferWriter.js:17-22 twice); feeds the single merged writer (compile.cc peephole)
+  // --- control-rate retriggering: decided once per 256-sample chunk, before the target ticks
+  OP_RETRIG,    // Retriggerer.js:13-22        in0=rate [p: t, fired]: fired = 1 if t crossed sampleRate in this chunk
+  OP_SRETRIG,   // SporadicRetrigger.js:12-16  in0=rate [p: draw, seed_lo, seed_hi, fired]: fired = rand() < rate[0]*256/SR
+  OP_POKEIF,    // the assignments of target.trigger(): if word aux0 != 0 then word p = word aux1
   OP_COUNT
 };
 

@@ -17,6 +17,8 @@ Format (one record per line, space separated, doubles as ``%.17g``):
                                               outlet.connections in connect order (scheduler input)
   ORDER <u0> <u1> ...                         circuit.units (tick order)
   ROOT <unit> <outlet>                        the rendered outlet
+  EV <chunk> <unit> <prop> <number>           an event's assignment, applied before the tick of chunk <chunk>
+  TG <unit> <target> <prop> <number>          one assignment of target.trigger() for (Sporadic)Retriggerer <unit>
   END
 """
 from .graph import DuspError

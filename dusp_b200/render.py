@@ -73,6 +73,41 @@ def collect_events(circuit, horizon_seconds=EVENT_HORIZON_S):
     return out
 
 
+def _numeric_assignments(rec, index, what):
+    out = []
+    for unit, name, val in rec:
+        if name in _IGNORED_EVENT_PROPS or name.startswith("_"):
+            continue
+        if id(unit) not in index:
+            raise capi.UnsupportedCircuit(what + " touches a unit outside the rendered circuit: " + unit.label)
+        if isinstance(val, bool):
+            val = 1.0 if val else 0.0
+        elif name.startswith("@") or not isinstance(val, (int, float)):
+            raise capi.UnsupportedCircuit("%s assigns %s.%s: only numeric unit state can change during an "
+                                          "accelerated render" % (what, unit.label, name.lstrip("@")))
+        out.append((index[id(unit)], name, float(val)))
+    return out
+
+
+def collect_triggers(circuit):
+    """(Sporadic)Retriggerer units (Retriggerer.js:17-18): ``target.trigger()`` is run ONCE on the
+    host mirror with its assignments recorded: [(retriggerer_index, unit_index, property, value)].  The device
+    and the oracle replay them whenever the retriggerer fires."""
+    from . import graph
+    index = {id(u): i for i, u in enumerate(circuit.units)}
+    out = []
+    for i, u in enumerate(circuit.units):
+        if u.KIND not in ("Retriggerer", "SporadicRetriggerer"):
+            continue
+        target = u.target
+        if target is None or not hasattr(target, "trigger"):
+            continue
+        with graph.record_assignments() as rec:
+            target.trigger()
+        out += [(i,) + a for a in _numeric_assignments(rec, index, "trigger() of " + target.label)]
+    return out
+
+
 def circuit_blob(outlet, horizon_seconds=EVENT_HORIZON_S):
     """(blob, circuit) for a rendered outlet -- `outlet.unit.circuit || new Circuit(outlet.unit)`.
     Events after the first chunk are appended to the blob as `EV` records (the oracle applies them) and kept
@@ -85,8 +120,9 @@ def circuit_blob(outlet, horizon_seconds=EVENT_HORIZON_S):
     blob = circuit_to_blob(circuit, outlet)
     events = collect_events(circuit, horizon_seconds)
     circuit.device_events = events
-    if events:
-        lines = ["EV %d %d %s %.17g" % e for e in events]
+    lines = ["EV %d %d %s %.17g" % e for e in events]
+    lines += ["TG %d %d %s %.17g" % t for t in collect_triggers(circuit)]
+    if lines:
         blob = blob[:-len("END\n")] + "\n".join(lines) + "\nEND\n"
     return blob, circuit
 

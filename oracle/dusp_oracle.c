@@ -96,7 +96,7 @@ enum Kind {
   K_FIXEDMULTIPLY, K_SEMITONETORATIO, K_MIDITOFREQUENCY, K_DECIBELTOSCALER, K_SECONDSTOSAMPLES,
   K_CONCATCHANNELS, K_PICKCHANNEL, K_VECTORMAGNITUDE,
   K_DELAY, K_MONODELAY, K_READBACKDELAY, K_FIXEDDELAY, K_COMBFILTER, K_ALLPASS,
-  K_CBWRITER, K_CBREADER, K_NKINDS
+  K_CBWRITER, K_CBREADER, K_RETRIGGERER, K_SPORADICRETRIGGERER, K_NKINDS
 };
 static const char *KIND_NAMES[K_NKINDS] = {
   "Osc", "MultiChannelOsc", "Ramp", "Shape", "AHD", "Timer", "Noise", "Filter",
@@ -105,7 +105,7 @@ static const char *KIND_NAMES[K_NKINDS] = {
   "FixedMultiply", "SemitoneToRatio", "MidiToFrequency", "DecibelToScaler", "SecondsToSamples",
   "ConcatChannels", "PickChannel", "VectorMagnitude",
   "Delay", "MonoDelay", "ReadBackDelay", "FixedDelay", "CombFilter", "AllPass",
-  "CircleBufferWriter", "CircleBufferReader"};
+  "CircleBufferWriter", "CircleBufferReader", "Retriggerer", "SporadicRetriggerer"};
 
 struct Unit;
 typedef struct Port {
@@ -152,7 +152,10 @@ typedef struct Unit {
  * (Circuit.js:23,57-65: events with t < clock + 256). */
 typedef struct OEvent { long chunk; int unit; char prop[24]; double value; } OEvent;
 
+/* One assignment made by `target.trigger()` of a (Sporadic)Retriggerer (Retriggerer.js:17-18): `chunk` holds the
+ * retriggering unit's index instead of a time. */
 typedef struct Oracle {
+  int ntriggers; OEvent *triggers;
   int nevents; OEvent *events;
   int nunits;
   Unit *units;
@@ -289,6 +292,10 @@ static int init_unit_state(Oracle *o, Unit *u) {
     u->draw = (uint64_t)propd(u, "draw", 1);
     u->y = propd(u, "y", 0);
     break;
+  case K_SPORADICRETRIGGERER: /* Math.random -> the unit's own injected stream */
+    u->seed = (uint64_t)propd(u, "seed_lo", 0) | ((uint64_t)propd(u, "seed_hi", 0) << 32);
+    u->draw = (uint64_t)propd(u, "draw", 0);
+    break;
   case K_FILTER: { /* Filter.js:56-64 */
     const char *k = sprop(u, "kind", "LP");
     if (!strcmp(k, "LP")) u->fkind = 0; else if (!strcmp(k, "HP")) u->fkind = 1;
@@ -395,6 +402,13 @@ Oracle *oracle_load(const char *blob, char *err, int errlen) {
       ev->unit = atoi(strtok_r(NULL, " ", &save));
       snprintf(ev->prop, sizeof ev->prop, "%s", strtok_r(NULL, " ", &save));
       ev->value = strtod(strtok_r(NULL, " ", &save), NULL);
+    } else if (!strcmp(tok, "TG")) {
+      o->triggers = (OEvent *)realloc(o->triggers, (o->ntriggers + 1) * sizeof(OEvent));
+      OEvent *ev = &o->triggers[o->ntriggers++];
+      ev->chunk = atol(strtok_r(NULL, " ", &save));
+      ev->unit = atoi(strtok_r(NULL, " ", &save));
+      snprintf(ev->prop, sizeof ev->prop, "%s", strtok_r(NULL, " ", &save));
+      ev->value = strtod(strtok_r(NULL, " ", &save), NULL);
     } else if (!strcmp(tok, "ORDER")) {
       o->order = (int *)calloc(o->nunits + 1, sizeof(int));
       char *v;
@@ -429,6 +443,7 @@ Oracle *oracle_load(const char *blob, char *err, int errlen) {
 void oracle_free(Oracle *o) {
   if (!o) return;
   free(o->events);
+  free(o->triggers);
   for (int i = 0; i < o->nunits; i++) {
     Unit *u = &o->units[i];
     for (int j = 0; j < u->nin; j++) if (u->in[j].owns) chunk_free(u->in[j].chunk);
@@ -916,6 +931,33 @@ static void tick_cbreader(Unit *u) {
   u->t += CHUNK;
 }
 
+static int apply_event(Oracle *o, const OEvent *ev);
+/* this._target.trigger(): the assignments recorded for unit `u` (TG records) */
+static int fire_trigger(Oracle *o, Unit *u) {
+  const long me = (long)(u - o->units);
+  for (int i = 0; i < o->ntriggers; i++)
+    if (o->triggers[i].chunk == me && apply_event(o, &o->triggers[i])) return -1;
+  return 0;
+}
+/* Retriggerer.js:13-22 */
+static int tick_retriggerer(Oracle *o, Unit *u) {
+  const float *rate = INCH(u, 0)->ch[0];
+  for (int t = 0; t < CHUNK; t++) {
+    u->t += (double)rate[t];
+    if (u->t >= SR) {
+      if (fire_trigger(o, u)) return -1;
+      u->t -= SR;
+    }
+  }
+  return 0;
+}
+/* SporadicRetrigger.js:12-16 (tickInterval = 256) */
+static int tick_sporadic_retriggerer(Oracle *o, Unit *u) {
+  const float *rate = INCH(u, 0)->ch[0];
+  if (oracle_rand(u->seed, u->draw++) < (double)rate[0] * CHUNK / SR) return fire_trigger(o, u);
+  return 0;
+}
+
 /* Unit.js:111-119 tick -> _tick */
 static int unit_tick(Oracle *o, Unit *u, double clock) {
   switch (u->kind) {
@@ -925,6 +967,8 @@ static int unit_tick(Oracle *o, Unit *u, double clock) {
   case K_SHAPE: tick_shape(u); break;
   case K_AHD: tick_ahd(u); break;
   case K_TIMER: tick_timer(u); break;
+  case K_RETRIGGERER: return tick_retriggerer(o, u);
+  case K_SPORADICRETRIGGERER: return tick_sporadic_retriggerer(o, u);
   case K_NOISE: tick_noise(u); break;
   case K_FILTER: tick_filter(u); break;
   case K_MULTIPLY: tick_binary_mod(u, 0); break;

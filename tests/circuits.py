@@ -255,6 +255,29 @@ def periodic_event():  # an event function returning a positive number re-schedu
     return C.Multiply(C.Osc(330), env)
 
 
+def bang_retrigger():  # `!` = Retriggerer (constructOperation.js:71-76, Retriggerer.js:13-22), 5 per second
+    return d.unDusp("O330 * (D0.15 ! 5)")
+
+
+def retrigger_modulated():  # a signal-rate RATE inlet: the trigger instants follow an LFO; an AHD and a Ramp as targets
+    env = C.AHD(0.01, 0.02, 0.05)
+    C.Retriggerer(env, C.Sum(C.Multiply(C.Osc(0.7), 6), 9))
+    ramp = C.Ramp(4000, 500, 250)
+    C.Retriggerer(ramp, 3.5)
+    return C.Multiply(C.Osc(ramp), env)
+
+
+def sporadic_retrigger():  # `~!` = SporadicRetriggerer (constructOperation.js:78-82): one injected-random draw per chunk
+    return d.unDusp("O220 * (D0.08 ~! 12)")
+
+
+def retrigger_chain():  # the default Unit.trigger walks the target's input units (Unit.js:293-297): both envelopes restart
+    both = C.Multiply(C.Shape("decay", 0.2), C.Shape("attack", 0.1))
+    both.trigger()
+    C.Retriggerer(both, 4)
+    return C.Multiply(C.Osc(440), both)
+
+
 # name -> (factory, seconds, exact?)
 CASES = {
     "osc440": (osc440, 1.0, True),
@@ -303,4 +326,8 @@ CASES = {
     "at_later": (at_later, 1.2, True),
     "scheduled_retriggers": (scheduled_retriggers, 1.1, True),
     "periodic_event": (periodic_event, 0.9, True),
+    "bang_retrigger": (bang_retrigger, 1.3, True),
+    "retrigger_modulated": (retrigger_modulated, 1.5, True),
+    "sporadic_retrigger": (sporadic_retrigger, 1.5, True),
+    "retrigger_chain": (retrigger_chain, 1.1, True),
 }

@@ -300,3 +300,38 @@ def test_poke_rejects_specialised_parameters(lib):
     with pytest.raises(capi.UnsupportedCircuit, match="does not hold"):
         s.poke(0, 0, ["u%d.nonexistent" % filt], [1.0])
     s.close()
+
+
+def test_retriggerer_batch_with_per_voice_rates(lib, oracle, kernel_mode):
+    """Retriggerer on the device for a batch (whole-chunk tiles whatever kernel the batch would
+    otherwise get), every voice with its own retrigger rate and envelope length, bit-exact."""
+    def build(rate, dur):
+        env = d.components.Shape("decay", dur).trigger()
+        d.components.Retriggerer(env, rate)
+        return d.components.Multiply(d.components.Osc(330), env)
+    rng = np.random.default_rng(5)
+    rates, durs = rng.uniform(1, 30, 80), rng.uniform(0.02, 0.3, 80)
+    blob, _ = circuit_blob(build(4.0, 0.1))
+    rt, shape = unit_index(blob, "Retriggerer"), unit_index(blob, "Shape")
+    p = capi.Program(blob)
+    s = capi.Session([p], [80], 0)
+    assert s.launch_info()["sub_block"] * s.launch_info()["time_lanes"] == 256 and not s.launch_info()["specialised"]
+    s.set_params(0, ["u%d.rate[0]" % rt, "u%d.duration[0]" % shape], np.stack([rates, durs], axis=1))
+    got = s.render_host(SR)
+    s.close()
+    for v in (0, 1, 40, 79):
+        vb, _ = circuit_blob(build(float(rates[v]), float(durs[v])))
+        compare(got[v], oracle.render(vb, 1.0), True, "retrigger voice %d" % v)
+
+
+def test_retriggered_circuits_next_to_others_in_one_session(lib, oracle):
+    """Circuits with per-chunk control ops stay out of the multi-program launch (its tiles are half chunks)."""
+    names = ["bang_retrigger", "osc440", "sporadic_retrigger", "w2_live", "retrigger_modulated"]
+    blobs = [circuit_blob(circuits.CASES[n][0]())[0] for n in names]
+    progs = [capi.Program(b) for b in blobs]
+    s = capi.Session(progs, [1] * len(progs), 0)
+    got = s.render_host(SR // 2)
+    s.close()
+    for i, n in enumerate(names):
+        want = oracle.render(blobs[i], 0.5)
+        compare(got[i][:len(want)], want, True, n)

@@ -82,9 +82,22 @@ def test_unknown_constructor_and_bad_reference():
 
 
 def test_out_of_scope_operators_raise():
-    for src in ("O1 then O2", "O1 for 2", "D1 ! 2"):
+    for src in ("O1 then O2", "O1 for 2"):
         with pytest.raises(DuspError):
             d.unDusp(src)
+
+
+def test_retrigger_operators_build_chained_units():  # constructOperation.js:71-82
+    env = d.unDusp("D1 ! 2")
+    assert env.playing and isinstance(env, C.Shape)
+    rt = [i.outlet.unit for i in env.inlets.values() if i.connected and i.noData]
+    assert len(rt) == 1 and isinstance(rt[0], C.Retriggerer) and rt[0].target is env and rt[0].RATE.constant == 2
+    env = d.unDusp("[Shape] ~! 3")
+    assert not env.playing  # `~!` does not trigger at construction (constructOperation.js:78-82)
+    rt = [i.outlet.unit for i in env.inlets.values() if i.connected and i.noData]
+    assert isinstance(rt[0], C.SporadicRetriggerer) and rt[0].RATE.constant == 3
+    with pytest.raises(DuspError):
+        d.unDusp("5 ! 2")  # a Number has no trigger
 
 
 def test_setter_sugar_and_constants():

@@ -168,3 +168,38 @@ def test_trigger_event_after_the_first_chunk_closed_form(oracle):
     t = np.clip(n - 22016 + 1, 0, 44100).astype(np.float64)
     want = np.where(n < 22016, 400.0, 400.0 + (t / 44100.0) * (200.0 - 400.0)).astype(np.float32)
     assert np.array_equal(out, want)
+
+
+def test_retriggerer_closed_form(oracle):
+    """`x ! r` = trigger() + new Retriggerer(x, r) (constructOperation.js:71-76).  With r = 44100/512 (exact in
+    f32, every partial sum exact) the accumulator reaches the sample rate on the 512th sample, i.e. inside the
+    SECOND chunk of every pair; the Retriggerer is chained before its target (Retriggerer.js:31), so the Ramp's
+    counter restarts at the first sample of chunks 1, 3, 5, ... and counts on through chunks 2, 4, ... (Ramp.js:25-40)."""
+    import dusp_b200 as d
+    from dusp_b200.render import circuit_blob
+    blob, _ = circuit_blob(d.unDusp("[Ramp 1000 3 1] ! 86.1328125"))
+    assert [l for l in blob.splitlines() if l.startswith("TG")] == ["TG 0 1 playing 1", "TG 0 1 t 0"]
+    out = oracle.render(blob, 0.1)[0]
+    n = np.arange(len(out))
+    start = np.where(n < 256, 0, ((n // 256 - 1) // 2 * 2 + 1) * 256)  # sample at which the running count began
+    t = np.minimum(n - start + 1, 1000).astype(np.float64)
+    want = (3.0 + (t / 1000.0) * (1.0 - 3.0)).astype(np.float32)
+    assert np.array_equal(out, want)
+
+
+def test_sporadic_retriggerer_uses_injected_stream(oracle):
+    """SporadicRetrigger.js:12-16: one draw per tick, trigger iff draw < rate[0] * 256 / 44100."""
+    from dusp_b200 import components as C, config
+    from dusp_b200.render import circuit_blob
+    ramp = C.Ramp(131072, 1, 131073).trigger()  # out = 1 + t exactly
+    sr = C.SporadicRetriggerer(ramp, 40, seed=77)
+    blob, _ = circuit_blob(ramp)
+    out = oracle.render(blob, 0.5)[0]
+    t, want = 0, []
+    for k in range((len(out) + 255) // 256):
+        if config.rand53(77, k) < float(np.float32(40)) * 256 / 44100:
+            t = 0
+        want += [1 + t + 1 + i for i in range(256)]
+        t += 256
+    assert np.array_equal(out, np.array(want[:len(out)], dtype=np.float32))
+    assert len(set(np.flatnonzero(np.diff(out) < 0))) > 3  # it did fire a few times
