@@ -29,6 +29,7 @@ SYMBOLS = [
     "dusp_session_num_channels", "dusp_session_unit_count", "dusp_session_set_params", "dusp_session_reset",
     "dusp_session_render", "dusp_session_launch_count", "dusp_session_launch_info", "dusp_rand53",
     "dusp_session_tile_info", "dusp_session_warning", "dusp_program_specialise", "dusp_session_poke",
+    "dusp_session_adopt",
 ]
 
 
@@ -70,6 +71,7 @@ def load():
     L.dusp_session_set_params.argtypes = [c.c_void_p, c.c_int, c.POINTER(c.c_int), c.c_int, c.POINTER(c.c_double)]
     L.dusp_session_reset.argtypes = [c.c_void_p]
     L.dusp_session_poke.argtypes = [c.c_void_p, c.c_int, c.c_int, c.c_int, c.POINTER(c.c_int), c.POINTER(c.c_double), c.c_void_p]
+    L.dusp_session_adopt.argtypes = [c.c_void_p, c.c_int, c.c_void_p, c.c_int, c.c_void_p]
     L.dusp_session_render.argtypes = [c.c_void_p, c.c_longlong, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p]
     L.dusp_session_launch_count.argtypes = [c.c_void_p]
     L.dusp_session_launch_count.restype = c.c_longlong
@@ -197,6 +199,11 @@ class Session:
             raise UnsupportedCircuit("event assigns state the compiled program does not hold: " + str(e))
         vals = (ctypes.c_double * len(names))(*[float(v) for v in values])
         check(L.dusp_session_poke(self._h, program_index, int(voice), len(names), ids, vals, None))
+
+    def adopt(self, program_index, src, src_program_index):
+        """Take over the device state of a program group of session ``src`` (a graph edit: this session's
+        program is the circuit after the edit; units are matched by label).  SURVEY 8f-1."""
+        check(load().dusp_session_adopt(self._h, int(program_index), src._h, int(src_program_index), None))
 
     def render_host(self, n_samples, out_mode=OUT_VOICES):
         """Render into a fresh host array: [voices][channels][n] or [2][n] (mix)."""

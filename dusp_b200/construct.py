@@ -7,7 +7,7 @@ supported for times the reference fires before the first tick (t < 256 samples).
 from . import components as _components
 from . import patches as _patches
 from . import config, parse, quick
-from .graph import DuspError, UnitOrPatch, Outlet, Inlet
+from .graph import DuspError, UnitOrPatch, Outlet, Inlet, _is_number
 
 
 def _namespace():  # src/patchesAndComponents.js:1-8 (patches overwrite components)
@@ -166,8 +166,27 @@ def constructOperation(o, index=None, destinations=None):  # constructOperation.
             raise DuspError("invalide use of '!~' operator")
         _components.SporadicRetriggerer(a, b)
         return a
-    if op in ("for", "then"):
-        raise DuspError("operator '" + op + "' needs run-time graph edits: outside the accelerated render path")
+    if op == "for":  # :36-43
+        if _is_number(a):
+            a = _components.Repeater(a)
+        if hasattr(a, "scheduleFinish"):
+            a.scheduleFinish(b)
+        else:
+            raise DuspError("invalid use of 'for' operator. First operand has no scheduleFinish function")
+        return a
+    if op == "then":  # :45-60 -- a run-time graph edit: when `a` finishes, the inlet that read it is handed `b`
+        out = None
+        if not destinations:
+            out = _components.Repeater()
+            out.IN = a
+            destinations = [lambda x: setattr(out, "IN", x)]
+
+        def on_finish(dst=destinations):
+            for f in dst:
+                f(b)
+        if isinstance(a, UnitOrPatch):  # (a Number silently drops the property in JS)
+            a.onFinish = on_finish
+        return out if out is not None else a
     raise DuspError("Unknown operator: " + op)
 
 

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -434,6 +435,96 @@ int dusp_session_poke(dusp_session *s, int gi, int voice, int n_ids, const int *
     }
     CUDA_TRY(cudaStreamSynchronize(st));  // the staging values live on this stack frame
   }
+  return DUSP_OK;
+}
+
+// Graph edits (`then`, events that assign inlets).  `dst` holds the program compiled from the circuit
+// AFTER the edit; group `dgi` takes over the device state of group `sgi` of `src`: units are matched by kind and
+// label, and everything the units own travels -- state words, per-voice constants (unless the edit changed the
+// constant's value), delay lines, CircleBuffers and the previous-chunk buffers of feedback edges.  New units keep
+// the construction state the blob gave them.  The sessions must be on the same device with equal voice counts.
+int dusp_session_adopt(dusp_session *dst, int dgi, dusp_session *src, int sgi, void *cuda_stream) {
+  if (!dst || !src || dst == src || dgi < 0 || dgi >= (int)dst->groups.size() || sgi < 0 || sgi >= (int)src->groups.size())
+    return fail(DUSP_EINVAL, "dusp_session_adopt: bad arguments");
+  Group &d = dst->groups[dgi], &o = src->groups[sgi];
+  if (dst->device != src->device || d.n_voices != o.n_voices || d.nv_pad != o.nv_pad)
+    return fail(DUSP_EINVAL, "dusp_session_adopt: sessions differ in device or voice count");
+  CUDA_TRY(cudaSetDevice(dst->device));
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  for (Group *g : {&d, &o})
+    if (g->dirty) {  // pending (re)initialisation lands first
+      CUDA_TRY(cudaMemcpyAsync(g->d_words, g->h_words.data(), g->h_words.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+      CUDA_TRY(cudaMemsetAsync(g->d_rings, 0, (size_t)std::max<long long>(g->prog.ring_floats, 4) * g->nv_pad * sizeof(float), st));
+      CUDA_TRY(cudaMemsetAsync(g->d_stale, 0, (size_t)std::max(g->prog.n_stale, 1) * DUSP_CHUNK * g->nv_pad * sizeof(float), st));
+      g->dirty = false;
+    }
+  // "u<j>.<rest>" of the new program -> "u<i>.<rest>" of the old one
+  std::map<std::string, int> old_unit;
+  for (size_t i = 0; i < o.prog.unit_labels.size(); i++) old_unit[o.prog.unit_labels[i]] = (int)i;
+  auto translate = [&](const std::string &name, bool *known_unit) -> std::string {
+    *known_unit = false;
+    const size_t dot = name.find('.');
+    if (name.size() < 2 || name[0] != 'u' || dot == std::string::npos) return "";
+    const int j = atoi(name.c_str() + 1);
+    if (j < 0 || j >= (int)d.prog.unit_labels.size()) return "";
+    auto it = old_unit.find(d.prog.unit_labels[j]);
+    if (it == old_unit.end()) return "";
+    *known_unit = true;
+    return "u" + std::to_string(it->second) + name.substr(dot);
+  };
+  std::map<std::string, int> ow, orr, os;
+  for (size_t i = 0; i < o.prog.words.size(); i++) ow[o.prog.words[i].name] = (int)i;
+  for (size_t i = 0; i < o.prog.ring_names.size(); i++) orr[o.prog.ring_names[i]] = (int)i;
+  for (size_t i = 0; i < o.prog.stale_names.size(); i++) os[o.prog.stale_names[i]] = (int)i;
+  // ---- words
+  const size_t nw = d.prog.words.size();
+  std::vector<int> from(nw, -1);
+  for (size_t w = 0; w < nw; w++) {
+    bool known;
+    const std::string on = translate(d.prog.words[w].name, &known);
+    auto it = ow.find(on);
+    if (on.empty() || it == ow.end()) continue;
+    const Param &pn = d.prog.words[w], &po = o.prog.words[it->second];
+    if (pn.f32 && !(pn.dflt == po.dflt || (pn.dflt != pn.dflt && po.dflt != po.dflt))) continue;  // the edit set this constant
+    from[w] = it->second;
+  }
+  // words derived from a constant that the edit changed keep their fresh values
+  auto derived_count = [](int kind) { return kind == DV_FILTER_LP || kind == DV_FILTER_HP ? 5 : kind == DV_PAN ? 3 : 1; };
+  for (const Derived &dv : d.prog.derived) {
+    bool fresh = false;
+    for (int sw : {dv.src0, dv.src1}) if (sw >= 0 && d.prog.words[sw].f32 && from[sw] < 0) fresh = true;
+    if (fresh) for (int k = 0; k < derived_count(dv.kind); k++) from[dv.dst + k] = -1;
+  }
+  for (size_t w = 0; w < nw; w++)
+    if (from[w] >= 0)
+      CUDA_TRY(cudaMemcpyAsync(d.d_words + w * d.nv_pad, o.d_words + (size_t)from[w] * o.nv_pad, (size_t)d.nv_pad * sizeof(double),
+                               cudaMemcpyDeviceToDevice, st));
+  // ---- delay lines and CircleBuffers: [voice][ring_floats] arenas with different strides
+  const size_t dpitch = (size_t)std::max<long long>(d.prog.ring_floats, 4) * sizeof(float);
+  const size_t opitch = (size_t)std::max<long long>(o.prog.ring_floats, 4) * sizeof(float);
+  for (size_t r = 0; r < d.prog.rings.size(); r++) {
+    bool known;
+    auto it = orr.find(translate(d.prog.ring_names[r], &known));
+    if (it == orr.end()) continue;
+    const DuspRing &rn = d.prog.rings[r], &ro = o.prog.rings[it->second];
+    if (rn.length != ro.length) return fail(DUSP_EUNSUPPORTED, "graph edit changes the length of delay line " + d.prog.ring_names[r]);
+    CUDA_TRY(cudaMemcpy2DAsync(d.d_rings + rn.offset, dpitch, o.d_rings + ro.offset, opitch, (size_t)rn.length * sizeof(float),
+                               (size_t)d.n_voices, cudaMemcpyDeviceToDevice, st));
+  }
+  // ---- previous-chunk buffers of feedback edges: [voice][n_stale][256]
+  for (size_t k = 0; k < d.prog.stale_names.size(); k++) {
+    bool known;
+    auto it = os.find(translate(d.prog.stale_names[k], &known));
+    if (it == os.end()) {
+      if (known) return fail(DUSP_EUNSUPPORTED, "graph edit makes " + d.prog.stale_names[k] + " a feedback edge: its previous chunk was not kept");
+      continue;
+    }
+    CUDA_TRY(cudaMemcpy2DAsync(d.d_stale + k * DUSP_CHUNK, (size_t)d.prog.n_stale * DUSP_CHUNK * sizeof(float),
+                               o.d_stale + (size_t)it->second * DUSP_CHUNK, (size_t)o.prog.n_stale * DUSP_CHUNK * sizeof(float),
+                               DUSP_CHUNK * sizeof(float), (size_t)d.n_voices, cudaMemcpyDeviceToDevice, st));
+  }
+  CUDA_TRY(cudaStreamSynchronize(st));
+  dst->clock = src->clock;
   return DUSP_OK;
 }
 

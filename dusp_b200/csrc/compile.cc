@@ -81,8 +81,9 @@ struct Builder {
     prog.words.push_back({name, dflt, f32});
     return (int)prog.words.size() - 1;
   }
-  int ring(long long len) {
+  int ring(long long len, const std::string &name) {
     if (len < 1) throw Unsupported("delay line of length < 1 sample");
+    prog.ring_names.push_back(name);
     prog.rings.push_back({prog.ring_floats, len});
     prog.ring_floats += (len + 3) & ~3LL;  // keep every ring 16-byte aligned
     return (int)prog.rings.size() - 1;
@@ -181,6 +182,7 @@ Program compile(const Graph &g) {
     if (b.pos_of_unit[u] < 0) b.pos_of_unit[u] = 1 << 28;  // not ticked: never produces
   if (b.pos_of_unit[g.root_unit] >= (1 << 28)) throw std::runtime_error("rendered unit is not in the circuit");
   b.prog.n_units = (int)g.order.size();
+  for (auto &u : g.units) b.prog.unit_labels.push_back(u.kind + ":" + u.label);
 
   // ---- channel counts: steady state, then check tick 0 already sees it ----
   std::vector<std::vector<int>> init(NU);
@@ -208,7 +210,11 @@ Program compile(const Graph &g) {
   // ---- emit one instruction per unit-channel, in tick order ----
   std::map<std::pair<int, int>, int> cb_ring;  // (buffer, channel) -> ring id
   for (size_t bi = 0; bi < g.cbs.size(); bi++)
-    for (int c = 0; c < g.cbs[bi].nch; c++) cb_ring[{(int)bi, c}] = b.ring(g.cbs[bi].len);
+    for (int c = 0; c < g.cbs[bi].nch; c++) {
+      int owner = 0;  // named after the first unit that holds the buffer (units are matched by label across graph edits)
+      for (int u = NU - 1; u >= 0; u--) if (g.units[u].has("buffer") && (size_t)g.units[u].num("buffer", -1) == bi) owner = u;
+      cb_ring[{(int)bi, c}] = b.ring(g.cbs[bi].len, Builder::uname(owner) + ".cb[" + std::to_string(c) + "]");
+    }
   struct Tap { int unit; bool writer; Opnd off; int ir; };
   std::map<int, std::vector<Tap>> taps;  // ring -> taps (for the reordering check)
 
@@ -434,9 +440,10 @@ Program compile(const Graph &g) {
         IR &r = b.emit(k == "Delay" ? OP_DELAY : OP_READBACK, ui, c);
         // Delay.js:23 aliases in[c % length] while the array grows: every added channel is channel c % (original count)
         r.in[0] = b.in_ref(ui, 0, c % inn(0)); r.in[1] = b.in_ref(ui, 1, c % inn(1));
-        if (k == "Delay") r.aux[0] = b.ring((long long)u.num("maxDelay", DUSP_SR * 5));
+        const std::string rn = un + ".ring[" + std::to_string(c) + "]";
+        if (k == "Delay") r.aux[0] = b.ring((long long)u.num("maxDelay", DUSP_SR * 5), rn);
         else {
-          r.aux[0] = b.ring((long long)u.num("bufferLength", DUSP_SR));
+          r.aux[0] = b.ring((long long)u.num("bufferLength", DUSP_SR), rn);
           r.p = b.word(un + ".tBuffer[" + std::to_string(c) + "]", u.num("tBuffer", 0), false);
         }
         b.prog.ring_bytes_per_sample += k == "Delay" ? 24 : 8;
@@ -445,7 +452,7 @@ Program compile(const Graph &g) {
     } else if (k == "MonoDelay") {
       need_in(2);
       IR &r = b.emit(OP_MONODELAY, ui, 0); r.in[0] = b.in_ref(ui, 0, 0); r.in[1] = b.in_ref(ui, 1, 0);
-      r.aux[0] = b.ring(DUSP_SR * 5);
+      r.aux[0] = b.ring(DUSP_SR * 5, un + ".ring[0]");
       b.prog.ring_bytes_per_sample += 24;
       b.def(r, 0, ui, 0, 0);
     } else if (k == "FixedDelay" || k == "CombFilter" || k == "AllPass") {
@@ -453,7 +460,7 @@ Program compile(const Graph &g) {
       IR &r = b.emit(k == "FixedDelay" ? OP_FIXDELAY : k == "CombFilter" ? OP_COMB : OP_ALLPASS, ui, 0);
       r.in[0] = b.in_ref(ui, 0, 0);
       if (k != "FixedDelay") r.in[1] = b.in_ref(ui, 1, 0);
-      r.aux[0] = b.ring((long long)u.num("delayTimeInSamples", 0));
+      r.aux[0] = b.ring((long long)u.num("delayTimeInSamples", 0), un + ".ring[0]");
       r.p = b.word(un + ".tBuffer", u.num("tBuffer", 0), false);
       b.prog.ring_bytes_per_sample += 8;
       b.def(r, 0, ui, 0, 0);
@@ -585,7 +592,8 @@ Program compile(const Graph &g) {
   // re-index defs (emit() may have reallocated; defs were recorded by index so they are valid)
   std::vector<char> live(ir.size(), 0);
   std::vector<int> stack;
-  for (size_t i = 0; i < ir.size(); i++) if (ir[i].root) { live[i] = 1; stack.push_back((int)i); }
+  // (a graph edit ahead: a later program may read any of this one's values one chunk late, see KEEP below)
+  for (size_t i = 0; i < ir.size(); i++) if (ir[i].root || g.keep_all) { live[i] = 1; stack.push_back((int)i); }
   while (!stack.empty()) {
     int i = stack.back(); stack.pop_back();
     for (auto &o : ir[i].in)
@@ -628,6 +636,16 @@ Program compile(const Graph &g) {
     std::map<int, int> stale_id;   // value -> stale buffer
     std::map<int, int> stale_tmp;  // value -> temp value holding the loaded previous chunk
     std::vector<IR> res;
+    auto keep = [&](int v) {
+      stale_id[v] = b.prog.n_stale++;
+      b.prog.stale_names.push_back(Builder::uname(b.vals[v].unit) + ".stale[" + std::to_string(b.vals[v].outlet) + "][" +
+                                   std::to_string(b.vals[v].chan) + "]");
+    };
+    // KEEP: the circuit is edited at a later chunk.  The edit may re-level units so that an
+    // existing outlet is then read one chunk late (a new feedback edge): every outlet value leaves its last
+    // chunk in a stale buffer, where dusp_session_adopt finds it by name.
+    if (g.keep_all)
+      for (size_t v = 0; v < b.vals.size(); v++) if (b.vals[v].def >= 0 && b.vals[v].outlet >= 0) keep((int)v);
     for (size_t i = 0; i < seq.size(); i++) {
       IR r = seq[i];
       for (auto &o : r.in) {
@@ -635,8 +653,8 @@ Program compile(const Graph &g) {
         int d = b.vals[o.id].def;
         if (d >= 0 && d >= (int)i) {
           int v = o.id;
-          if (!stale_id.count(v)) {
-            stale_id[v] = b.prog.n_stale++;
+          if (!stale_tmp.count(v)) {
+            if (!stale_id.count(v)) keep(v);
             b.vals.push_back({b.vals[v].unit, b.vals[v].outlet, b.vals[v].chan, -1});
             stale_tmp[v] = (int)b.vals.size() - 1;
             IR ld; ld.op = OP_LDSTALE; ld.unit = b.vals[v].unit; ld.chan = b.vals[v].chan;

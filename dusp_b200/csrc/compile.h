@@ -44,6 +44,9 @@ struct Program {
   std::vector<DuspInstr> code;
   std::vector<Param> words;     // per-voice words: parameters and unit state, in instruction order
   std::vector<DuspRing> rings;  // per-voice delay lines / CircleBuffer channels
+  // identities across graph edits (dusp_session_adopt): "<Kind>:<label>" per blob unit; rings and stale buffers
+  // are named "u<unit>.<what>" like the words
+  std::vector<std::string> unit_labels, ring_names, stale_names;
   long long ring_floats = 0;
   int n_slots = 0;
   int n_stale = 0;

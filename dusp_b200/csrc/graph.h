@@ -36,6 +36,7 @@ struct Graph {
   std::vector<GCircleBuffer> cbs;
   std::vector<int> order;
   std::vector<GTrigger> triggers;
+  bool keep_all = false;  // KEEP record: a graph edit follows, keep every outlet's last chunk (compile.cc)
   int root_unit = -1, root_outlet = 0;
 };
 

@@ -19,7 +19,10 @@ Format (one record per line, space separated, doubles as ``%.17g``):
   ROOT <unit> <outlet>                        the rendered outlet
   EV <chunk> <unit> <prop> <number>           an event's assignment, applied before the tick of chunk <chunk>
   TG <unit> <target> <prop> <number>          one assignment of target.trigger() for (Sporadic)Retriggerer <unit>
+  KEEP                                        a graph edit follows: keep every outlet's last chunk (device hint)
   END
+  EPOCH <chunk>                               then another DUSPGRAPH section: the circuit after an event edited the
+                                              graph, valid from that chunk on (units matched by kind and label)
 """
 from .graph import DuspError
 

@@ -26,7 +26,9 @@ def _resolve_outlet(outlet):  # renderChannelData.js:12-17
 
 
 EVENT_HORIZON_S = 600.0  # self-rescheduling events are expanded up to this render time
-_IGNORED_EVENT_PROPS = {"finished"}  # assigned by trigger()/finish(); no effect without onFinish graph edits
+# host-side bookkeeping an event may assign: finish flags (acted on by the host mirror itself, which runs onFinish)
+# and what Circuit.add / computeProcessIndex write while an edit adds units (Circuit.js:67-107, Unit.js:171-209)
+_IGNORED_EVENT_PROPS = {"finished", "onFinish", "processIndex", "circuit", "events", "promises", "nChains"}
 
 
 def _fold_early_events(circuit):
@@ -35,68 +37,108 @@ def _fold_early_events(circuit):
     circuit.runEvents(circuit.clock + circuit.gcdTickInterval)
 
 
-def collect_events(circuit, horizon_seconds=EVENT_HORIZON_S):
-    """Later events (scheduleTrigger / `at`, schedule(t, f)): the reference runs an event's
-    function before the tick of the chunk that contains its time (Circuit.js:23,57-65).  Here every pending
-    event is run ONCE on the host mirror, in the reference's order, with all unit attribute assignments
-    recorded: [(chunk, unit_index, property, value)].  The device applies them as word pokes between the
-    launches of chunk-aligned segments; the oracle applies them before ticking that chunk.  Event functions
-    may only ASSIGN numeric unit state (trigger / stop do); graph edits stay outside the accelerated path."""
+def _structure(circuit):
+    """What a graph edit changes: the unit list and every inlet's source / constant."""
+    sig = []
+    for u in circuit.units:
+        ins = []
+        for inlet in u.inletsOrdered:
+            if inlet.connected:
+                src = inlet.outlet
+                ins.append((inlet.name, src.unit.label, src.name))
+            else:
+                ins.append((inlet.name, tuple(inlet.chunk)))
+        sig.append((u.label, tuple(ins)))
+    return tuple(sig)
+
+
+def _numeric_assignments(rec, what):
+    """[(unit, property, value)] of a recorded run: numeric unit state only.  Inlet assignments are graph edits
+    (picked up by the structure comparison in ``collect_timeline``) and are skipped here."""
+    out = []
+    for unit, name, val in rec:
+        if name in _IGNORED_EVENT_PROPS or name.startswith("_") or name.startswith("@"):
+            continue
+        if isinstance(val, bool):
+            val = 1.0 if val else 0.0
+        elif not isinstance(val, (int, float)):
+            raise capi.UnsupportedCircuit("%s assigns %s.%s: only numeric unit state and inlets can change during an "
+                                          "accelerated render" % (what, unit.label, name))
+        out.append((unit, name, float(val)))
+    return out
+
+
+def collect_timeline(circuit, outlet, horizon_seconds=EVENT_HORIZON_S):
+    """Later events.  The reference runs an event's function before the tick of the chunk that
+    contains its time (Circuit.js:23,57-65).  Here every pending event is run ONCE on the host mirror, in the
+    reference's order, and what it did is recorded:
+
+    * numeric unit-state assignments (trigger / stop / schedule(t, f)) -> ``(chunk, unit, property, value)``,
+      applied as word pokes between the launches of chunk-aligned segments (the oracle: before that chunk's tick);
+    * graph edits (`then` hands an inlet a new source, an event assigns an inlet; Inlet.js:40-93) -> a new EPOCH:
+      the circuit as it stands after the edit, from that chunk on.  Units are matched by label across epochs:
+      those that were there keep their device state, new ones start from their construction state.
+
+    Returns [(start_chunk, graph_text, units, [(chunk, unit_index, property, value)])]."""
     from . import graph
-    index = {id(u): i for i, u in enumerate(circuit.units)}
     chunk = circuit.gcdTickInterval
     horizon = horizon_seconds * config.sampleRate
-    out = []
-    guard = 0
+    epochs = [[0, circuit_to_blob(circuit, outlet), list(circuit.units)]]
+    pending = []
+    sig = _structure(circuit)
+    guard = k_now = 0
     while circuit.events and circuit.events[0].t < horizon:
         ev = circuit.events.pop(0)
-        k = max(0, int(math.floor(ev.t / chunk)))
+        # (an event queued in the past by a unit that joined the circuit late runs in the same runEvents pass)
+        k = k_now = max(k_now, int(math.floor(ev.t / chunk)))
+        before = {id(u) for u in circuit.units}
         with graph.record_assignments() as rec:
             follow = ev.run()
-        for unit, name, val in rec:
-            if name in _IGNORED_EVENT_PROPS or name.startswith("_"):
-                continue
-            if id(unit) not in index:
-                raise capi.UnsupportedCircuit("event touches a unit outside the rendered circuit: " + unit.label)
-            if name.startswith("@") or isinstance(val, bool) or not isinstance(val, (int, float)):
-                if isinstance(val, bool):
-                    val = 1.0 if val else 0.0
-                else:
-                    raise capi.UnsupportedCircuit("event at t=%g assigns %s.%s: only numeric unit state can change "
-                                                  "during an accelerated render" % (ev.t, unit.label, name.lstrip("@")))
-            out.append((k, index[id(unit)], name, float(val)))
+        rec = [r for r in rec if id(r[0]) in before]  # units the event constructs arrive with the snapshot
+        pending += [(k,) + a for a in _numeric_assignments(rec, "event at t=%g" % ev.t)]
+        now = _structure(circuit)
+        if now != sig:
+            sig = now
+            snap = [k, circuit_to_blob(circuit, outlet), list(circuit.units)]
+            if k == epochs[-1][0] and len(epochs) > 1:
+                epochs[-1] = snap
+            elif k == 0:
+                raise capi.UnsupportedCircuit("graph edit before the first chunk")
+            else:
+                epochs.append(snap)
         if follow is not None:
             circuit.addEvent(follow)
         guard += 1
         if guard > 200000:
             raise capi.UnsupportedCircuit("more than 200000 events inside the event horizon")
-    return out
-
-
-def _numeric_assignments(rec, index, what):
+    if len(epochs) > 1:
+        for _, _, units in epochs:
+            labels = [u.label for u in units]
+            if len(set(labels)) != len(labels):
+                raise capi.UnsupportedCircuit("graph edits need unique unit labels (units are matched by label)")
     out = []
-    for unit, name, val in rec:
-        if name in _IGNORED_EVENT_PROPS or name.startswith("_"):
-            continue
-        if id(unit) not in index:
-            raise capi.UnsupportedCircuit(what + " touches a unit outside the rendered circuit: " + unit.label)
-        if isinstance(val, bool):
-            val = 1.0 if val else 0.0
-        elif name.startswith("@") or not isinstance(val, (int, float)):
-            raise capi.UnsupportedCircuit("%s assigns %s.%s: only numeric unit state can change during an "
-                                          "accelerated render" % (what, unit.label, name.lstrip("@")))
-        out.append((index[id(unit)], name, float(val)))
+    for e, (k0, text, units) in enumerate(epochs):
+        k1 = epochs[e + 1][0] if e + 1 < len(epochs) else None
+        index = {id(u): i for i, u in enumerate(units)}
+        evs = []
+        for (k, unit, name, val) in pending:
+            if k < k0 or (k1 is not None and k >= k1):
+                continue
+            if id(unit) not in index:
+                raise capi.UnsupportedCircuit("event touches a unit outside the rendered circuit: " + unit.label)
+            evs.append((k, index[id(unit)], name, val))
+        out.append((k0, text, units, evs))
     return out
 
 
-def collect_triggers(circuit):
+def collect_triggers(units):
     """(Sporadic)Retriggerer units (Retriggerer.js:17-18): ``target.trigger()`` is run ONCE on the
     host mirror with its assignments recorded: [(retriggerer_index, unit_index, property, value)].  The device
     and the oracle replay them whenever the retriggerer fires."""
     from . import graph
-    index = {id(u): i for i, u in enumerate(circuit.units)}
+    index = {id(u): i for i, u in enumerate(units)}
     out = []
-    for i, u in enumerate(circuit.units):
+    for i, u in enumerate(units):
         if u.KIND not in ("Retriggerer", "SporadicRetriggerer"):
             continue
         target = u.target
@@ -104,27 +146,69 @@ def collect_triggers(circuit):
             continue
         with graph.record_assignments() as rec:
             target.trigger()
-        out += [(i,) + a for a in _numeric_assignments(rec, index, "trigger() of " + target.label)]
+        for unit, name, val in _numeric_assignments(rec, "trigger() of " + target.label):
+            if id(unit) not in index:
+                raise capi.UnsupportedCircuit("trigger() of %s touches a unit outside the rendered circuit: %s"
+                                              % (target.label, unit.label))
+            out.append((i, index[id(unit)], name, val))
     return out
 
 
 def circuit_blob(outlet, horizon_seconds=EVENT_HORIZON_S):
     """(blob, circuit) for a rendered outlet -- `outlet.unit.circuit || new Circuit(outlet.unit)`.
-    Events after the first chunk are appended to the blob as `EV` records (the oracle applies them) and kept
-    in ``circuit.device_events`` for the device path (``render_segments``)."""
+    Events after the first chunk are appended as `EV` records, retriggerer targets as `TG` records, and every
+    graph edit starts a new `EPOCH <chunk>` section holding the circuit after the edit (graphblob.py).  The
+    epochs are also kept in ``circuit.timeline`` = [(start_chunk, text, events)]."""
     outlet = _resolve_outlet(outlet)
     circuit = outlet.unit.circuit or Circuit(outlet.unit)  # renderChannelData.js:20
     if circuit.rendered:
         raise DuspError("this circuit has already been rendered: renders are one-shot (SURVEY section 5)")
     _fold_early_events(circuit)
-    blob = circuit_to_blob(circuit, outlet)
-    events = collect_events(circuit, horizon_seconds)
-    circuit.device_events = events
-    lines = ["EV %d %d %s %.17g" % e for e in events]
-    lines += ["TG %d %d %s %.17g" % t for t in collect_triggers(circuit)]
-    if lines:
-        blob = blob[:-len("END\n")] + "\n".join(lines) + "\nEND\n"
-    return blob, circuit
+    parts, timeline = [], []
+    epochs = collect_timeline(circuit, outlet, horizon_seconds)
+    trig = [collect_triggers(units) for (_, _, units, _) in epochs]
+    for e, ((k0, text, units, evs), tgs) in enumerate(zip(epochs, trig)):
+        lines = ["EV %d %d %s %.17g" % ev for ev in evs] + ["TG %d %d %s %.17g" % t for t in tgs]
+        if e + 1 < len(epochs):
+            lines.append("KEEP")  # an edit follows: the program keeps every outlet's last chunk for its successor
+        if lines:
+            text = text[:-len("END\n")] + "\n".join(lines) + "\nEND\n"
+        parts.append(("EPOCH %d\n" % k0 if k0 else "") + text)
+        timeline.append((k0, text, evs))
+    circuit.timeline = timeline
+    circuit.device_events = timeline[0][2]
+    _reject_mid_tick_finish(circuit, {id(u): u for (_, _, units, _) in epochs for u in units}.values())
+    return "".join(parts), circuit
+
+
+def _reject_mid_tick_finish(circuit, units):
+    """A Shape calls ``finish()`` from inside its ``_tick`` when its envelope runs out (Shape/index.js:40-42): an
+    ``onFinish`` that edits the graph or assigns unit state would then act in the middle of ``Circuit.tick``, at a
+    data-dependent sample.  That is outside the accelerated path; an ``onFinish`` that only raises finish flags
+    (Boop.js:15-17) is fine.  Dry run on the host mirror, after all snapshots have been taken."""
+    from . import graph
+    for u in units:
+        if u.KIND != "Shape" or not callable(getattr(u, "onFinish", None)):
+            continue
+        sig = _structure(circuit)
+        with graph.record_assignments() as rec:
+            u.onFinish()
+        if _structure(circuit) != sig or _numeric_assignments(rec, "onFinish of " + u.label):
+            raise capi.UnsupportedCircuit("onFinish of %s would act from inside a tick when the envelope runs out "
+                                          "(Shape/index.js:40-42): outside the accelerated render path" % u.label)
+
+
+def split_epochs(blob):
+    """[(start_chunk, graph_text)] of a blob (one entry unless events edit the graph)."""
+    out, k, cur = [], 0, []
+    for l in blob.splitlines():
+        if l.startswith("EPOCH "):
+            out.append((k, "\n".join(cur) + "\n"))
+            k, cur = int(l.split()[1]), []
+        else:
+            cur.append(l)
+    out.append((k, "\n".join(cur) + "\n"))
+    return out
 
 
 def blob_events(blob):
@@ -137,10 +221,86 @@ def blob_events(blob):
     return ev
 
 
+class SessionRun:
+    """A session driven through its circuits' timelines: chunk-aligned segments, the events of chunk
+    k poked into every voice of their program group before the segment that starts at sample 256*k, and a new
+    session that adopts the old one's device state wherever an event edits a graph (``EPOCH`` sections).
+
+    ``blobs``: one per program group (``circuit_blob``); ``voices``: voices per group."""
+
+    def __init__(self, blobs, voices, device=0):
+        self.device = device
+        self.voices = [int(v) for v in voices]
+        self.timelines = [split_epochs(b) for b in blobs]
+        self.epoch = [0] * len(blobs)
+        self.programs = [capi.Program(tl[0][1]) for tl in self.timelines]
+        self.events = [blob_events(tl[0][1]) for tl in self.timelines]
+        self.session = capi.Session(self.programs, self.voices, device)
+        self.pos = 0  # samples rendered so far (a multiple of 256 between renders, except after the last one)
+
+    def set_params(self, program_index, names, values):
+        self.session.set_params(program_index, names, values)
+
+    def _cuts(self, n):
+        cuts = set()
+        for tl, evs in zip(self.timelines, self.events):
+            for (k, _) in tl[1:]:
+                cuts.add(k * 256)
+            for tl_epoch in tl:
+                for (k, _, _, _) in blob_events(tl_epoch[1]):
+                    cuts.add(k * 256)
+        return sorted(c for c in cuts if self.pos < c < self.pos + n)
+
+    def _enter(self, pos):
+        """What the reference does in runEvents before the tick of the chunk at ``pos``: graph edits, then pokes."""
+        k = pos // 256
+        switch = [i for i, tl in enumerate(self.timelines)
+                  if self.epoch[i] + 1 < len(tl) and tl[self.epoch[i] + 1][0] <= k]
+        if switch:
+            for i in switch:
+                while self.epoch[i] + 1 < len(self.timelines[i]) and self.timelines[i][self.epoch[i] + 1][0] <= k:
+                    self.epoch[i] += 1
+                text = self.timelines[i][self.epoch[i]][1]
+                self.programs[i] = capi.Program(text)
+                self.events[i] = blob_events(text)
+            new = capi.Session(self.programs, self.voices, self.device)
+            try:
+                for i in range(len(self.programs)):
+                    new.adopt(i, self.session, i)
+            except Exception:
+                new.close()
+                raise
+            self.session.close()
+            self.session = new
+        if pos > 0:
+            for i, evs in enumerate(self.events):
+                now = [e for e in evs if e[0] == k]
+                if now:
+                    self.session.poke(i, -1, ["u%d.%s" % (u, name) for (_, u, name, _) in now], [v for (_, _, _, v) in now])
+
+    def render(self, n, out_mode=capi.OUT_VOICES):
+        """The next ``n`` samples: [voices][channels][n] or [2][n] (mix)."""
+        if self.pos % 256:
+            raise DuspError("a render that stopped inside a chunk cannot be continued")
+        parts = []
+        for b in self._cuts(n) + [self.pos + n]:
+            self._enter(self.pos)
+            parts.append(self.session.render_host(b - self.pos, out_mode))
+            self.pos = b
+        if len(parts) == 1:
+            return parts[0]
+        if out_mode != capi.OUT_MIX:  # an edit may add output channels: earlier segments read as silence there
+            nch = max(p.shape[1] for p in parts)
+            parts = [p if p.shape[1] == nch else np.pad(p, ((0, 0), (0, nch - p.shape[1]), (0, 0))) for p in parts]
+        return np.concatenate(parts, axis=-1)
+
+    def close(self):
+        self.session.close()
+
+
 def render_segments(sess, n, events_by_program, out_mode=capi.OUT_VOICES):
-    """``sess.render_host(n)`` with events: chunk-aligned segments, the events of chunk k poked into every
-    voice of their program group before the segment that starts at sample 256*k.  events_by_program:
-    {program_index: [(chunk, unit, property, value)]}."""
+    """``sess.render_host(n)`` from clock 0 with events but no graph edits (see ``SessionRun`` for the general
+    driver).  events_by_program: {program_index: [(chunk, unit, property, value)]}."""
     chunk = 256
     cuts = sorted({k * chunk for evs in events_by_program.values() for (k, _, _, _) in evs if 0 < k * chunk < n})
     if not cuts:
@@ -166,15 +326,13 @@ def renderChannelData(outlet, duration=1, TypedArray=np.float32, device=0):
     """Render ``duration`` seconds of ``outlet`` (an Outlet, Unit or Patch) on the
     GPU.  Returns a ``ChannelData`` list with one float32 array per channel."""
     blob, circuit = circuit_blob(outlet)
-    prog = capi.Program(blob)
-    sess = capi.Session([prog], [1], device)
+    run = SessionRun([blob], [1], device)
     try:
-        n = n_samples_for(duration)
-        out = render_segments(sess, n, {0: circuit.device_events})
+        out = run.render(n_samples_for(duration))
     finally:
-        sess.close()
+        run.close()
     circuit.rendered = True
-    res = ChannelData(np.asarray(out[0, c], dtype=TypedArray) for c in range(prog.num_channels))
+    res = ChannelData(np.asarray(out[0, c], dtype=TypedArray) for c in range(out.shape[1]))
     return res
 
 
@@ -185,34 +343,37 @@ class Batch:
 
     def __init__(self, outlet, n_voices, overrides=None, device=0):
         self.blob, self.circuit = circuit_blob(outlet)
-        self.program = capi.Program(self.blob)
-        self.session = capi.Session([self.program], [n_voices], device)
+        self.run = SessionRun([self.blob], [n_voices], device)
+        self.program = self.run.programs[0]
         self.n_voices = n_voices
         if overrides:
             names = list(overrides)
             vals = np.stack([np.asarray(overrides[k], dtype=np.float64) for k in names], axis=1)
             if vals.shape[0] != n_voices:
                 raise DuspError("override arrays must hold one value per voice")
-            self.session.set_params(0, names, vals)
+            self.run.set_params(0, names, vals)
+
+    @property
+    def session(self):
+        return self.run.session
 
     def render(self, duration, out_mode=capi.OUT_VOICES):
-        return render_segments(self.session, n_samples_for(duration), {0: self.circuit.device_events}, out_mode)
+        return self.run.render(n_samples_for(duration), out_mode)
 
     def close(self):
-        self.session.close()
+        self.run.close()
 
 
 def render_batch(outlets, duration=1, device=0, out_mode=capi.OUT_VOICES):
     """Render a list of independent circuits in one session (one program group
     each).  Returns [circuit][channel][n] (zero-padded to the widest circuit)."""
-    progs, events = [], {}
-    for i, o in enumerate(outlets):
+    blobs = []
+    for o in outlets:
         blob, circuit = circuit_blob(o)
-        progs.append(capi.Program(blob))
-        events[i] = circuit.device_events
+        blobs.append(blob)
         circuit.rendered = True
-    sess = capi.Session(progs, [1] * len(progs), device)
+    run = SessionRun(blobs, [1] * len(blobs), device)
     try:
-        return render_segments(sess, n_samples_for(duration), events, out_mode)
+        return run.render(n_samples_for(duration), out_mode)
     finally:
-        sess.close()
+        run.close()

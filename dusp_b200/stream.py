@@ -12,7 +12,7 @@ import numpy as np
 
 from . import capi, config
 from .graph import DuspError, Outlet, UnitOrPatch
-from .render import circuit_blob, render_segments
+from .render import circuit_blob, SessionRun
 
 CHUNK = config.standardChunkSize if hasattr(config, "standardChunkSize") else 256
 
@@ -33,14 +33,14 @@ class RenderStream:
         self.format = {"channels": self.numberOfChannels, "bitDepth": 32, "sampleRate": self.sampleRate,
                        "endianness": "LE"}                               # :63-68
         self.blob, self.circuit = circuit_blob(outlet)
-        self.program = capi.Program(self.blob)
+        self.run = SessionRun([self.blob], [1], device)
+        self.program = self.run.programs[0]
         if self.program.num_channels < self.numberOfChannels:
+            self.run.close()
             # the reference dereferences channelData[c] === undefined here (TypeError in onTick, :38)
             raise DuspError("RenderStream: the outlet has %d channel(s), %d requested"
                             % (self.program.num_channels, self.numberOfChannels))
-        self.session = capi.Session([self.program], [1], device)
         self.block = int(block_chunks) * CHUNK
-        self._events = list(self.circuit.device_events)
         self._pending = []   # chunks of the current block, ready to hand out
         self._pos = 0        # samples rendered so far
         self._stopped = False
@@ -69,12 +69,7 @@ class RenderStream:
         return buf
 
     def _render_block(self):
-        lo = self._pos // CHUNK
-        evs = [(k - lo, u, name, v) for (k, u, name, v) in self._events if k >= lo]
-        first = [e for e in evs if e[0] == 0 and lo > 0]
-        if first:  # events of the block's first chunk (render_segments pokes only between ITS segments)
-            self.session.poke(0, -1, ["u%d.%s" % (u, name) for (_, u, name, _) in first], [v for (_, _, _, v) in first])
-        out = render_segments(self.session, self.block, {0: [e for e in evs if e[0] > 0]}, capi.OUT_VOICES_RAW)[0]
+        out = self.run.render(self.block, capi.OUT_VOICES_RAW)[0]  # events and graph edits at their chunks
         self._pos += self.block
         for i in range(0, self.block, CHUNK):
             self._pending.append(out[:, i:i + CHUNK])
@@ -99,4 +94,4 @@ class RenderStream:
 
     def stop(self):  # RenderStream.js:76-79
         self._stopped = True
-        self.session.close()
+        self.run.close()

@@ -114,6 +114,18 @@ int dusp_session_reset(dusp_session *s); /* back to clock 0 / initial unit state
 int dusp_session_poke(dusp_session *s, int program_index, int voice, int n_ids, const int *param_ids,
                       const double *values, void *cuda_stream);
 
+/* Replaces: a graph edit made by an event while the circuit runs -- `then` handing an inlet a new source from
+ * onFinish (constructOperation.js:45-60, UnitOrPatch.js:77-84), an event assigning an inlet (Unit.js:59-67):
+ * Inlet.connect re-aliases a chunk and adds the new units to the live circuit (Inlet.js:40-74,
+ * Circuit.js:67-107) while every existing unit object keeps its state.  Here the host compiles the circuit as it
+ * stands after the edit into a new program (a new session `dst`) and group `dst_program` takes over the device
+ * state of group `src_program` of `src` between two renders: units are matched by kind and label; their state
+ * words, per-voice constants (unless the edit changed that constant), delay lines, CircleBuffers and the
+ * previous-chunk buffers of feedback edges are copied device to device, and `dst` continues at `src`'s clock.
+ * Same device and voice counts required; DUSP_EUNSUPPORTED if the edit turns an existing value into a feedback
+ * edge (its previous chunk was never kept) or changes a delay-line length.  Enqueued on `cuda_stream`. */
+int dusp_session_adopt(dusp_session *dst, int dst_program, dusp_session *src, int src_program, void *cuda_stream);
+
 /* Replaces: the `for t0 ... await circuit.tickUntil(t1)` loop and the copy-out
  * (renderChannelData.js:29-45), for all voices at once.  Renders the next
  * `n_samples` samples (the session clock advances by whole chunks, like

@@ -155,6 +155,7 @@ typedef struct OEvent { long chunk; int unit; char prop[24]; double value; } OEv
 /* One assignment made by `target.trigger()` of a (Sporadic)Retriggerer (Retriggerer.js:17-18): `chunk` holds the
  * retriggering unit's index instead of a time. */
 typedef struct Oracle {
+  struct Oracle *next; long next_chunk; /* graph edit: the circuit as it stands from chunk next_chunk on */
   int ntriggers; OEvent *triggers;
   int nevents; OEvent *events;
   int nunits;
@@ -402,6 +403,7 @@ Oracle *oracle_load(const char *blob, char *err, int errlen) {
       ev->unit = atoi(strtok_r(NULL, " ", &save));
       snprintf(ev->prop, sizeof ev->prop, "%s", strtok_r(NULL, " ", &save));
       ev->value = strtod(strtok_r(NULL, " ", &save), NULL);
+    } else if (!strcmp(tok, "KEEP")) { /* device hint: a graph edit follows (unit objects keep everything here anyway) */
     } else if (!strcmp(tok, "TG")) {
       o->triggers = (OEvent *)realloc(o->triggers, (o->ntriggers + 1) * sizeof(OEvent));
       OEvent *ev = &o->triggers[o->ntriggers++];
@@ -432,6 +434,15 @@ Oracle *oracle_load(const char *blob, char *err, int errlen) {
   }
   for (int i = 0; i < o->nunits && !bad; i++) if (init_unit_state(o, &o->units[i])) bad = 1;
   if (!bad && (o->root_unit < 0 || o->root_unit >= o->nunits)) { fail(o, "renderAudioBuffer expects an outlet"); bad = 1; }
+  /* "EPOCH <chunk>" + another graph: a run-time graph edit made by an event (`then`, an inlet assignment):
+   * the host mirror's snapshot of the circuit after the edit; units are matched by label (adopt_state) */
+  while (!bad && (*p == '\n' || *p == ' ' || *p == '\r')) p++;
+  if (!bad && !strncmp(p, "EPOCH ", 6)) {
+    o->next_chunk = atol(p + 6);
+    const char *e = strchr(p, '\n');
+    o->next = e ? oracle_load(e + 1, o->err, sizeof o->err) : NULL;
+    if (!o->next) { if (!o->err[0]) fail(o, "EPOCH record without a graph"); bad = 1; }
+  }
   if (bad) {
     if (err) snprintf(err, errlen, "%s", o->err[0] ? o->err : "malformed graph blob");
     oracle_free(o);
@@ -442,6 +453,7 @@ Oracle *oracle_load(const char *blob, char *err, int errlen) {
 
 void oracle_free(Oracle *o) {
   if (!o) return;
+  oracle_free(o->next);
   free(o->events);
   free(o->triggers);
   for (int i = 0; i < o->nunits; i++) {
@@ -1024,13 +1036,48 @@ static int apply_event(Oracle *o, const OEvent *ev) {
   return 0;
 }
 
+static int chain_fail(Oracle *first, Oracle *o) { if (o != first) snprintf(first->err, sizeof first->err, "%s", o->err); return -1; }
+
 /* renderChannelData.js:5-49.  out[c] is malloc'd here (caller frees with
  * oracle_free_output); returns 0 or -1 (message via oracle_error). */
 static int g_raw_copy = 0;
 /* 1: copy the root outlet's chunk as it is (what RenderStream reads, RenderStream.js:38), no `x || 0` */
 void oracle_set_raw(int raw) { g_raw_copy = raw; }
 
-int oracle_render(Oracle *o, double duration, float **out, int max_ch, int *nch_out, long *nsamples_out) {
+/* A graph edit leaves every unit object as it is (Inlet.connect only re-aliases chunks and adds units,
+ * Inlet.js:40-74, Circuit.js:67-107): units of the new snapshot that existed before keep their run-time state,
+ * their outlets' chunk contents (a feedback edge reads them one chunk late) and their delay lines. */
+static void adopt_state(Oracle *n, Oracle *o) {
+  n->clock = o->clock;
+  for (int j = 0; j < n->nunits; j++) {
+    Unit *a = &n->units[j], *b = NULL;
+    for (int i = 0; i < o->nunits && !b; i++)
+      if (o->units[i].kind == a->kind && !strcmp(o->units[i].label, a->label)) b = &o->units[i];
+    if (!b) continue;
+    a->phase = b->phase; a->t = b->t; a->y = b->y; a->y0 = b->y0; a->y1 = b->y1; a->duration = b->duration;
+    a->left_edge = b->left_edge; a->right_edge = b->right_edge; a->sf = b->sf; a->comp_db = b->comp_db;
+    a->playing = b->playing; a->state = b->state; a->finished = b->finished; a->seed = b->seed; a->draw = b->draw;
+    memcpy(a->mc_phase, b->mc_phase, sizeof a->mc_phase); memcpy(a->mc_phase_set, b->mc_phase_set, sizeof a->mc_phase_set);
+    a->lastf_defined = b->lastf_defined; a->lastf = b->lastf;
+    a->a0 = b->a0; a->a1 = b->a1; a->a2 = b->a2; a->b1 = b->b1; a->b2 = b->b2;
+    memcpy(a->x1, b->x1, sizeof a->x1); memcpy(a->x2, b->x2, sizeof a->x2);
+    memcpy(a->fy1, b->fy1, sizeof a->fy1); memcpy(a->fy2, b->fy2, sizeof a->fy2); memcpy(a->sdef, b->sdef, sizeof a->sdef);
+    a->tbuffer = b->tbuffer;
+    if (a->maxdelay == b->maxdelay && a->buflen == b->buflen)
+      for (int c = 0; c < MAXCH; c++) if (b->bufs[c]) { free(a->bufs[c]); a->bufs[c] = b->bufs[c]; b->bufs[c] = NULL; }
+    if (a->cb && b->cb && a->cb->nch == b->cb->nch && a->cb->len == b->cb->len)
+      for (int c = 0; c < a->cb->nch; c++) memcpy(a->cb->ch[c], b->cb->ch[c], (size_t)a->cb->len * 4);
+    for (int k = 0; k < a->nout; k++)
+      for (int m = 0; m < b->nout; m++) {
+        if (strcmp(a->out[k].name, b->out[m].name) || !a->out[k].chunk || !b->out[m].chunk) continue;
+        for (int c = 0; c < b->out[m].chunk->nch; c++)
+          memcpy(chunk_ensure(a->out[k].chunk, c), b->out[m].chunk->ch[c], CHUNK * sizeof(float));
+      }
+  }
+}
+
+int oracle_render(Oracle *first, double duration, float **out, int max_ch, int *nch_out, long *nsamples_out) {
+  Oracle *o = first;
   if (!o->has_order) oracle_schedule(o, NULL);
   double length = duration * SR;                  /* :24 */
   long n = length > 0 ? (long)length : 0;         /* new Float32Array(x): ToIndex truncates */
@@ -1039,14 +1086,20 @@ int oracle_render(Oracle *o, double duration, float **out, int max_ch, int *nch_
   for (double t0 = 0; t0 < length; t0 += CHUNK) { /* :29 */
     /* circuit.tickUntil(t1): Circuit.js:19-47 -- one tick per chunk (all hot-path units tick at 256) */
     while (o->clock < t0 + CHUNK) {
+      while (o->next && (long)(o->clock / CHUNK) >= o->next_chunk) { /* the event that edits the graph runs first */
+        adopt_state(o->next, o);
+        o = o->next;
+        if (!o->has_order) oracle_schedule(o, NULL);
+        root = o->units[o->root_unit].out[o->root_outlet].chunk;
+      }
       for (int e = 0; e < o->nevents; e++)          /* Circuit.js:23 runEvents(clock + 256), in queue order */
-        if (o->events[e].chunk == (long)(o->clock / CHUNK) && apply_event(o, &o->events[e])) return -1;
+        if (o->events[e].chunk == (long)(o->clock / CHUNK) && apply_event(o, &o->events[e])) return chain_fail(first, o);
       for (int i = 0; i < o->norder; i++)
-        if (unit_tick(o, &o->units[o->order[i]], o->clock)) return -1;
+        if (unit_tick(o, &o->units[o->order[i]], o->clock)) return chain_fail(first, o);
       o->clock += CHUNK;
     }
     while (root->nch > nch) {                     /* :38-39 */
-      if (nch >= max_ch) return fail(o, "too many output channels");
+      if (nch >= max_ch) return fail(first, "too many output channels");
       out[nch++] = (float *)calloc(n > 0 ? n : 1, sizeof(float));
     }
     for (int c = 0; c < root->nch; c++)           /* :42-44: `x || 0`, out-of-range stores dropped */

@@ -278,6 +278,42 @@ def retrigger_chain():  # the default Unit.trigger walks the target's input unit
     return C.Multiply(C.Osc(440), both)
 
 
+def for_then():  # `for` = scheduleFinish, `then` = onFinish hands the Repeater a new source (graph edit)
+    return d.unDusp("(O440 for 0.5) then O220")
+
+
+def for_then_chain():  # finish times are absolute: the second switch comes 0.2 s after the first
+    return d.unDusp("((O440 for 0.2) then ((Z330 for 0.4) then O220)) * 0.5")
+
+
+def then_number():  # the new source is a Number: Inlet.setConstant (Inlet.js:76-93)
+    return d.unDusp("[Osc f:((100 for 0.25) then 300)]")
+
+
+def then_into_filter():  # units downstream of the edit keep their state (the filter rings on across the switch)
+    return d.unDusp("((Noise for 0.3) then O100) -> LP500")
+
+
+def then_with_delay():  # a feedback delay patch downstream: CircleBuffer contents and the stale edge survive the edit
+    src = d.unDusp("(O660 * D0.1 for 0.35) then (O220 * 0.5)")
+    return P.SimpleDelay(src, 0.11, 0.5, 0.4)
+
+
+def event_assigns_inlet():  # an event that assigns an inlet constant and later connects a unit (Unit.js:59-67)
+    osc = C.Osc(200)
+    out = C.Multiply(osc, 0.5)
+
+    def retune(unit):
+        unit.F = 310.5
+
+    def modulate(unit):
+        unit.F = C.Sum(C.Multiply(C.Osc(5), 20), 400)
+
+    osc.schedule(0.2, retune)
+    osc.schedule(0.5, modulate)
+    return out
+
+
 # name -> (factory, seconds, exact?)
 CASES = {
     "osc440": (osc440, 1.0, True),
@@ -330,4 +366,10 @@ CASES = {
     "retrigger_modulated": (retrigger_modulated, 1.5, True),
     "sporadic_retrigger": (sporadic_retrigger, 1.5, True),
     "retrigger_chain": (retrigger_chain, 1.1, True),
+    "for_then": (for_then, 1.0, True),
+    "for_then_chain": (for_then_chain, 0.8, True),
+    "then_number": (then_number, 0.6, True),
+    "then_into_filter": (then_into_filter, 0.7, True),
+    "then_with_delay": (then_with_delay, 0.9, True),
+    "event_assigns_inlet": (event_assigns_inlet, 0.8, True),
 }

@@ -32,12 +32,15 @@ def test_rand53_agrees_across_host_library_and_oracle(lib, oracle):
 @pytest.mark.parametrize("name", sorted(circuits.CASES))
 def test_every_case_compiles(lib, oracle, name):
     fac, _, _ = circuits.CASES[name]
+    from dusp_b200.render import split_epochs
     blob, circuit = circuit_blob(fac())
-    p = capi.Program(blob)
-    assert p.num_units == len(circuit.units)
-    assert p.num_channels == len(oracle.render(blob, 0.01))
-    assert p.num_instructions >= 1 and 1 <= p.num_slots <= 16
-    assert "out" in p.disassemble()
+    epochs = split_epochs(blob)  # one program per epoch (graph edits)
+    for k, text in epochs:
+        p = capi.Program(text)
+        assert p.num_instructions >= 1 and 1 <= p.num_slots <= 16
+        assert "out" in p.disassemble()
+    assert p.num_units == len(circuit.units)  # the host circuit is left as the last epoch found it
+    assert capi.Program(epochs[0][1]).num_channels == len(oracle.render(blob, 0.01))
 
 
 @pytest.mark.parametrize("name", ["w2_live", "w3_voice", "simple_delay", "transcendental"])
@@ -93,11 +96,25 @@ def test_unsupported_configurations_fail_loudly(lib):
     # events after the first chunk are carried as state assignments (EV records) ...
     blob, circ = circuit_blob(d.unDusp("[Osc f:([Ramp 100 1 2] at 1)]"))
     assert circ.device_events == [(172, 0, "playing", 1.0), (172, 0, "t", 0.0)] and "EV 172 0 playing 1" in blob
-    # ... but an event that rewires the graph (or assigns a non-number) is outside the accelerated path
+    # ... an event that rewires the graph starts a new EPOCH section holding the circuit after the edit ...
+    from dusp_b200.render import split_epochs
     o = C.Osc(100)
     o.schedule(1.0, lambda unit: setattr(unit, "F", C.Osc(3)))
+    blob, circ = circuit_blob(o)
+    epochs = split_epochs(blob)
+    assert [k for k, _ in epochs] == [0, 172] and len(circ.units) == 2
+    assert capi.Program(epochs[0][1]).num_units == 1 and capi.Program(epochs[1][1]).num_units == 2
+    # ... and an event that assigns anything but numbers and inlets is outside the accelerated path
+    o = C.Osc(100)
+    o.schedule(1.0, lambda unit: setattr(unit, "waveform", "saw"))
     with pytest.raises(capi.UnsupportedCircuit, match="event"):
         circuit_blob(o)
+    # a Shape finishes from inside its own tick (Shape/index.js:40-42): an onFinish that edits the graph there is refused,
+    # one that only raises finish flags (Boop.js:15-17) is not
+    with pytest.raises(capi.UnsupportedCircuit, match="inside a tick"):
+        circuit_blob(d.unDusp("D0.1 then 0.5"))
+    from dusp_b200 import patches as P
+    assert "EPOCH" not in circuit_blob(P.Boop(440, 0.2))[0]
 
 
 def test_no_cpu_fallback(lib):

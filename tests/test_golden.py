@@ -43,13 +43,12 @@ def test_gpu_reproduces_golden(lib, name):
     from dusp_b200 import capi
     fac, seconds, exact = circuits.CASES[name]
     blob, _ = circuit_blob(fac())
-    p = capi.Program(blob)
-    s = capi.Session([p], [1], 0)
+    from dusp_b200.render import SessionRun
+    run = SessionRun([blob], [1], 0)
     try:
-        from dusp_b200.render import blob_events, render_segments
-        got = render_segments(s, n_samples_for(seconds), {0: blob_events(blob)})[0]
+        got = run.render(n_samples_for(seconds))[0]
     finally:
-        s.close()
+        run.close()
     check(name, got, exact)
 
 

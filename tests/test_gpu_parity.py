@@ -17,13 +17,12 @@ TOL = 1e-5
 
 
 def gpu_render(blob, seconds, n_voices=1):
-    from dusp_b200.render import blob_events, render_segments
-    p = capi.Program(blob)
-    s = capi.Session([p], [n_voices], 0)
+    from dusp_b200.render import SessionRun
+    run = SessionRun([blob], [n_voices], 0)  # events -> pokes between segments, graph edits -> adopted sessions
     try:
-        return render_segments(s, n_samples_for(seconds), {0: blob_events(blob)})  # events -> pokes between segments
+        return run.render(n_samples_for(seconds))
     finally:
-        s.close()
+        run.close()
 
 
 @pytest.fixture(params=["interpreter", "specialised", "pipelined"])
@@ -335,3 +334,46 @@ def test_retriggered_circuits_next_to_others_in_one_session(lib, oracle):
     for i, n in enumerate(names):
         want = oracle.render(blobs[i], 0.5)
         compare(got[i][:len(want)], want, True, n)
+
+
+def test_graph_edit_for_a_batch_with_per_voice_parameters(lib, oracle, kernel_mode):
+    """`then` for a whole batch.  Every voice has its own filter cutoff and noise stream; after the
+    edit the adopted session keeps the per-voice constants, the filter state and the delay line of every voice."""
+    rng = np.random.default_rng(8)
+    fs = rng.uniform(300, 3000, 72)
+    seeds = rng.integers(1, 2 ** 62, 72)
+
+    def circuit(f, seed):
+        noise = d.components.Noise(seed=int(seed))
+        noise.scheduleFinish(0.2)
+        out = d.components.Repeater(noise)
+        osc = d.components.Multiply(d.components.Osc(150), 0.7)
+        noise.onFinish = lambda: setattr(out, "IN", osc)
+        ap = d.components.AllPass(0.013, 0.6)
+        ap.IN = d.components.Filter(out, f, "LP")
+        return ap
+
+    b = d.Batch(circuit(1000.0, 1), 72)
+    blob0 = b.blob
+    filt, noise = unit_index(blob0, "Filter"), unit_index(blob0, "Noise")
+    y0 = np.array([2 * d.config.rand53(int(sd), 0) - 1 for sd in seeds])
+    b.run.set_params(0, ["u%d.f[0]" % filt, "u%d.seed_lo" % noise, "u%d.seed_hi" % noise, "u%d.y" % noise],
+                     np.stack([fs, (seeds & 0xFFFFFFFF).astype(np.float64), (seeds >> 32).astype(np.float64), y0], axis=1))
+    try:
+        got = b.render(0.5)
+    finally:
+        b.close()
+    for v in (0, 35, 71):
+        vb, _ = circuit_blob(circuit(float(fs[v]), seeds[v]))
+        compare(got[v], oracle.render(vb, 0.5), True, "graph edit voice %d" % v)
+
+
+def test_render_stream_crosses_a_graph_edit(lib, oracle):
+    """The streaming sink renders block-wise: the edit falls inside a later block."""
+    from dusp_b200.render import circuit_blob as cb
+    blob, _ = cb(circuits.for_then())
+    want = oracle.render(blob, 1.0, raw=True)[0]
+    rs = d.RenderStream(circuits.for_then(), 1, block_chunks=32)
+    got = np.concatenate([rs.read() for _ in range(172)])
+    rs.stop()
+    assert np.array_equal(got[:44032], want[:44032])

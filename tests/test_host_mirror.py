@@ -81,10 +81,18 @@ def test_unknown_constructor_and_bad_reference():
         d.unDusp("[Multiply A:#ghost]")
 
 
-def test_out_of_scope_operators_raise():
-    for src in ("O1 then O2", "O1 for 2"):
-        with pytest.raises(DuspError):
-            d.unDusp(src)
+def test_for_then_operators():  # constructOperation.js:36-60
+    a = d.unDusp("O1 for 2")
+    assert isinstance(a, C.Osc) and len(a.events) == 1 and a.events[0].t == 2 * 44100
+    r = d.unDusp("7 for 1")
+    assert isinstance(r, C.Repeater) and r.IN.constant == 7  # a Number is wrapped in a Repeater first
+    out = d.unDusp("(O1 for 2) then O2")
+    first = out.IN.outlet.unit
+    assert isinstance(out, C.Repeater) and first.F.constant == 1 and callable(first.onFinish)
+    first.finish()  # what the scheduled event does: finished = true, then onFinish hands the Repeater its new source
+    assert first.finished and out.IN.outlet.unit.F.constant == 2 and first.OUT.connections == []
+    with pytest.raises(DuspError, match="scheduleFinish"):
+        d.unDusp("'abc' for 2")
 
 
 def test_retrigger_operators_build_chained_units():  # constructOperation.js:71-82

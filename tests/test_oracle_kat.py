@@ -151,8 +151,10 @@ def test_simple_delay_feedback_is_one_chunk_stale(oracle):
 @pytest.mark.parametrize("name", sorted(circuits.CASES))
 def test_host_scheduler_matches_oracle_scheduler(oracle, name):
     fac, _, _ = circuits.CASES[name]
+    from dusp_b200.render import split_epochs
     blob, circuit = circuit_blob(fac())
-    assert oracle.schedule(strip_order(blob)) == list(range(len(circuit.units)))
+    first = split_epochs(blob)[0][1]  # (later epochs grow by Circuit.add, one unit at a time: host mirror only)
+    assert oracle.schedule(strip_order(first)) == list(range(sum(l.startswith("U ") for l in first.splitlines())))
 
 
 def test_trigger_event_after_the_first_chunk_closed_form(oracle):
@@ -203,3 +205,33 @@ def test_sporadic_retriggerer_uses_injected_stream(oracle):
         t += 256
     assert np.array_equal(out, np.array(want[:len(out)], dtype=np.float32))
     assert len(set(np.flatnonzero(np.diff(out) < 0))) > 3  # it did fire a few times
+
+
+def test_for_then_closed_form(oracle):
+    """`(O440 for 0.5) then O220` (constructOperation.js:36-60): the finish event's time is sample 22050, so it runs
+    before the tick of chunk 86 (Circuit.js:23,57-65) and hands the Repeater the second oscillator, which joins
+    the circuit there with phase 0 (Inlet.js:40-74): from sample 22016 on the output is a 220 Hz table read-out
+    that starts from its first sample."""
+    import dusp_b200 as d
+    from dusp_b200.render import circuit_blob, split_epochs
+    blob, _ = circuit_blob(d.unDusp("(O440 for 0.5) then O220"))
+    assert [k for k, _ in split_epochs(blob)] == [0, 86]
+    out = oracle.render(blob, 1.0)[0]
+    tab = oracle.wave_table("sin")
+    n = np.arange(44100)
+    want = np.where(n < 86 * 256, tab[(440 * (n + 1)) % 44100], tab[(220 * (n - 86 * 256 + 1)) % 44100])
+    assert np.array_equal(out, want.astype(np.float32))
+
+
+def test_then_number_and_downstream_state(oracle):
+    """`[Osc f:((100 for 0.25) then 300)]`: the Repeater's inlet becomes the constant 300 at chunk 43; the Osc
+    downstream keeps its phase (integer frequencies: every phase is exact)."""
+    import dusp_b200 as d
+    from dusp_b200.render import circuit_blob
+    blob, _ = circuit_blob(d.unDusp("[Osc f:((100 for 0.25) then 300)]"))
+    out = oracle.render(blob, 0.5)[0]
+    tab = oracle.wave_table("sin")
+    n = np.arange(22050)
+    n0 = 43 * 256
+    phase = np.where(n < n0, 100 * (n + 1), 100 * n0 + 300 * (n - n0 + 1)) % 44100
+    assert np.array_equal(out, tab[phase].astype(np.float32))
