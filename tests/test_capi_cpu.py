@@ -113,8 +113,8 @@ def test_unsupported_configurations_fail_loudly(lib):
     # one that only raises finish flags (Boop.js:15-17) is not
     with pytest.raises(capi.UnsupportedCircuit, match="inside a tick"):
         circuit_blob(d.unDusp("D0.1 then 0.5"))
-    from dusp_b200 import patches as P
-    assert "EPOCH" not in circuit_blob(P.Boop(440, 0.2))[0]
+    from dusp_b200 import patches as patches_
+    assert "EPOCH" not in circuit_blob(patches_.Boop(440, 0.2))[0]
 
 
 def test_no_cpu_fallback(lib):
