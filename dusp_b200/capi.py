@@ -29,7 +29,7 @@ SYMBOLS = [
     "dusp_session_num_channels", "dusp_session_unit_count", "dusp_session_set_params", "dusp_session_reset",
     "dusp_session_render", "dusp_session_launch_count", "dusp_session_launch_info", "dusp_rand53",
     "dusp_session_tile_info", "dusp_session_warning", "dusp_program_specialise", "dusp_session_poke",
-    "dusp_session_adopt",
+    "dusp_session_adopt", "dusp_program_warmup_ticks",
 ]
 
 
@@ -50,7 +50,7 @@ def load():
     L.dusp_program_create.argtypes = [c.c_char_p, c.c_size_t, c.POINTER(c.c_void_p)]
     L.dusp_program_destroy.argtypes = [c.c_void_p]
     L.dusp_program_destroy.restype = None
-    for nm in ("num_channels", "num_units", "num_instructions", "num_slots", "num_params"):
+    for nm in ("num_channels", "num_units", "num_instructions", "num_slots", "num_params", "warmup_ticks"):
         getattr(L, "dusp_program_" + nm).argtypes = [c.c_void_p]
     L.dusp_program_bytes_per_voice_sample.argtypes = [c.c_void_p, c.c_int]
     L.dusp_program_bytes_per_voice_sample.restype = c.c_double
@@ -113,6 +113,7 @@ class Program:
         self.num_units = L.dusp_program_num_units(h)
         self.num_instructions = L.dusp_program_num_instructions(h)
         self.num_slots = L.dusp_program_num_slots(h)
+        self.warmup_ticks = L.dusp_program_warmup_ticks(h)
 
     def __del__(self):
         if getattr(self, "_h", None) and _lib is not None:
@@ -193,6 +194,20 @@ class Session:
         ``voice`` = index within the program group, or -1 for every voice of the group."""
         L = load()
         prog = self.programs[program_index]
+        if any(isinstance(n, str) and n.endswith("[*]") for n in names):  # every channel the program holds
+            all_names = [nm for nm, _ in prog.params()]
+            ex_n, ex_v = [], []
+            for n, v in zip(names, values):
+                if isinstance(n, str) and n.endswith("[*]"):
+                    hits = [a for a in all_names if a.startswith(n[:-2])]
+                    ex_n += hits
+                    ex_v += [v] * len(hits)
+                else:
+                    ex_n.append(n)
+                    ex_v.append(v)
+            names, values = ex_n, ex_v
+            if not names:
+                return
         try:
             ids = (ctypes.c_int * len(names))(*[prog.param_index(n) if isinstance(n, str) else int(n) for n in names])
         except DuspError as e:

@@ -67,8 +67,11 @@ class MultiChannelOsc(Osc):
         self.phase = []
         self.waveform = js_or(waveform, "sin")
 
-    def resetPhase(self):
-        self.phase = [0 for _ in self.phase]
+    def resetPhase(self):  # :52-55 -- element assignments: as an event it zeroes every channel that exists by then
+        from .. import graph
+        object.__setattr__(self, "phase", [0 for _ in self.phase])
+        if graph._recorder is not None:
+            graph._recorder.append((self, "phase[*]", 0))
 
     def randomPhaseFlip(self):  # :57-61 -- iterates an empty phase array before the first tick
         if config.host_random.random() < 0.5:
@@ -134,6 +137,40 @@ class Shape(Unit):
         return self._shape
 
     dusp_flags = {"trigger": lambda self: self.trigger()}  # index.js:62-67
+
+    @staticmethod
+    def randomShapeStr():  # index.js:137-140
+        return SHAPES[int(config.host_random.random() * len(SHAPES))]
+
+    @staticmethod
+    def randomInRange(maxDuration=None, minMin=None, maxMax=None):  # index.js:114-135
+        maxDuration = js_or(maxDuration, 1)
+        r = config.host_random.random
+        nan = float("nan")
+        lo = nan if minMin is None else minMin
+        span = nan if (maxMax is None or minMin is None) else maxMax - minMin
+        a = lo + r() * span
+        b = lo + r() * span
+        mn, mx = (b, a) if a > b else (a, b)
+        return Shape(Shape.randomShapeStr(), r() * maxDuration, mn, mx)
+
+    class _RandomDecay:
+        """``Shape.randomDecay(maxDuration)`` (static, index.js:142-147: a NEW decaySquared
+        Shape) and ``shape.randomDecay(maxDuration)`` (method, :149-154: re-randomise this one)."""
+
+        def __get__(self, obj, cls):
+            r = config.host_random.random
+            if obj is None:
+                return lambda maxDuration=None, *_: Shape("decaySquared", r() * js_or(maxDuration, 5))
+
+            def method(maxDuration=None):
+                obj.shape = "decay"
+                obj.DURATION = r() * js_or(maxDuration, 5)
+                obj.MIN = 0
+                obj.MAX = 1
+            return method
+
+    randomDecay = _RandomDecay()
 
     def trigger(self):
         self.playing = True
@@ -396,6 +433,35 @@ class Repeater(Unit):
         self.addOutlet("out", {"measuredIn": measuredIn})
         self.measuredIn = measuredIn
         self.IN = js_or(val, 0)
+
+
+class SampleRateRedux(Unit):
+    """src/components/SampleRateRedux.js:3-37 (sample-and-hold every ``ammount`` samples)"""
+    KIND = "SampleRateRedux"
+
+    def __init__(self, input=None, ammount=None):
+        super().__init__()
+        self.addInlet("in")
+        self.addInlet("ammount", {"mono": True})
+        self.addOutlet("out")
+        self.val = [0]
+        self.timeSinceLastUpdate = float("inf")
+        self.IN = js_or(input, 0)
+        self.AMMOUNT = js_or(ammount, 0)
+
+    def blob_props(self):
+        return {"timeSinceLastUpdate": self.timeSinceLastUpdate}, {}
+
+
+class Monitor(Unit):
+    """src/components/Monitor.js:3-16 -- ``console.log(this.in)`` once per tick: no outlet, no effect on any
+    signal.  Kept for graph compatibility; it cannot be rendered (no outlets) and the device ignores it."""
+    KIND = "Monitor"
+
+    def __init__(self, input=None):
+        super().__init__()
+        self.addInlet("in")
+        self.IN = input
 
 
 class FixedMultiply(Unit):
@@ -752,8 +818,8 @@ class SporadicRetriggerer(Retriggerer):
 __all__ = [
     "AHD", "Abs", "AllPass", "CircleBuffer", "CircleBufferNode", "CircleBufferReader", "CircleBufferWriter",
     "Clip", "CombFilter", "ConcatChannels", "CrossFader", "DecibelToScaler", "Delay", "Divide", "Filter",
-    "FixedDelay", "FixedMultiply", "Gain", "HardClipAbove", "HardClipBelow", "MidiToFrequency", "MonoDelay",
+    "FixedDelay", "FixedMultiply", "Gain", "HardClipAbove", "HardClipBelow", "MidiToFrequency", "Monitor", "MonoDelay",
     "Multiply", "Noise", "MultiChannelOsc", "Osc", "Pan", "PickChannel", "PolarityInvert", "Pow", "Ramp",
-    "ReadBackDelay", "Repeater", "Rescale", "Retriggerer", "SecondsToSamples", "SemitoneToRatio", "Shape", "SignalCombiner",
+    "ReadBackDelay", "Repeater", "Rescale", "Retriggerer", "SampleRateRedux", "SecondsToSamples", "SemitoneToRatio", "Shape", "SignalCombiner",
     "SporadicRetriggerer", "Subtract", "Sum", "Timer", "VectorMagnitude",
 ]

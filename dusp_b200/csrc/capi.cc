@@ -142,6 +142,7 @@ int dusp_program_create(const char *blob, size_t len, dusp_program **out) {
 void dusp_program_destroy(dusp_program *p) { delete p; }
 int dusp_program_num_channels(const dusp_program *p) { return p->prog.out_nch; }
 int dusp_program_num_units(const dusp_program *p) { return p->prog.n_units; }
+int dusp_program_warmup_ticks(const dusp_program *p) { return p->prog.warmup_ticks; }
 int dusp_program_num_instructions(const dusp_program *p) { return (int)p->prog.code.size(); }
 int dusp_program_num_slots(const dusp_program *p) { return p->prog.n_slots; }
 double dusp_program_bytes_per_voice_sample(const dusp_program *p, int out_mode) {
@@ -516,7 +517,10 @@ int dusp_session_adopt(dusp_session *dst, int dgi, dusp_session *src, int sgi, v
     bool known;
     auto it = os.find(translate(d.prog.stale_names[k], &known));
     if (it == os.end()) {
-      if (known) return fail(DUSP_EUNSUPPORTED, "graph edit makes " + d.prog.stale_names[k] + " a feedback edge: its previous chunk was not kept");
+      // a predecessor that kept every value it produced never had this one: a channel (or outlet) that is new in
+      // this program, zero-filled like the reference's `new Float32Array` until its producer first writes it
+      if (known && !o.prog.keeps_all)
+        return fail(DUSP_EUNSUPPORTED, "graph edit makes " + d.prog.stale_names[k] + " a feedback edge: its previous chunk was not kept");
       continue;
     }
     CUDA_TRY(cudaMemcpy2DAsync(d.d_stale + k * DUSP_CHUNK, (size_t)d.prog.n_stale * DUSP_CHUNK * sizeof(float),

@@ -36,7 +36,7 @@ const char *OP_NAMES[OP_COUNT] = {
     "gain", "clip", "hca", "hcb", "rescale", "xfade", "pan", "vecmag", "osc", "mcosc", "ramp", "shape", "ahd",
     "timer", "noise", "filter", "fixdelay", "comb", "allpass", "delay", "monodelay", "readback", "cbwrite",
     "cbread", "ldstale", "ststale", "out", "filterc", "panc", "gainc", "noise1", "cbwritec", "cbreadc", "add0",
-    "retrig", "sretrig", "pokeif"};
+    "retrig", "sretrig", "pokeif", "srredux"};
 
 struct Opnd {
   int kind = 0;  // 0 none (reads 0), 1 value, 2 const word
@@ -155,7 +155,7 @@ int written_channels(const Graph &g, const std::vector<std::vector<int>> &n, int
   if (k == "MultiChannelOsc") return in(0);
   if (k == "Filter" || k == "Gain" || k == "PolarityInvert" || k == "Abs" || k == "Repeater" ||
       k == "SecondsToSamples" || k == "SemitoneToRatio" || k == "DecibelToScaler" || k == "Clip" ||
-      k == "HardClipAbove" || k == "HardClipBelow" || k == "Rescale")
+      k == "HardClipAbove" || k == "HardClipBelow" || k == "Rescale" || k == "SampleRateRedux")
     return in(0);
   if (k == "Multiply" || k == "Divide" || k == "Pow" || k == "Sum" || k == "Subtract" || k == "CrossFader" ||
       k == "Delay" || k == "ReadBackDelay")
@@ -202,9 +202,29 @@ Program compile(const Graph &g) {
   auto ns = n1;
   for (int it = 0; it < 16; it++) { auto nn = simulate(ns, nullptr); if (nn == ns) break; ns = nn; }
   simulate(ns, &seenS);
-  if (seen0 != seenS || n1[g.root_unit][g.root_outlet] != ns[g.root_unit][g.root_outlet])
-    throw Unsupported("channel counts keep growing after the first chunk (multi-channel signal through a feedback edge)");
-  b.nch = ns;
+  // Warm-up ticks: a unit that the reference's order ticks BEFORE its producer sees the producer's outlet with the
+  // channel count of the previous tick, so a multi-channel signal takes a few ticks to spread (`out[c] = out[c] ||
+  // new Float32Array`).  Tick k is compiled from the counts its units see, n_k = simulate^k(init); from tick S on
+  // the program is the steady one.  The host renders chunk k < S with the program of a `WARMUP k` record and hands
+  // the state over like a graph edit (render.SessionRun).
+  bool dynamic_nch = false;
+  {
+    auto nk = init;
+    int S = 0;
+    for (; S < 64; S++) {
+      std::vector<std::vector<int>> seenk(NU);
+      auto nn = simulate(nk, &seenk);
+      if (seenk == seenS && nn[g.root_unit][g.root_outlet] == ns[g.root_unit][g.root_outlet]) break;
+      if (S == g.warmup_tick) { b.nch = nk; dynamic_nch = true; }
+      nk = nn;
+    }
+    if (S >= 64) throw Unsupported("channel counts do not settle within 64 ticks");
+    b.prog.warmup_ticks = S;
+    if (S > 0 && g.warmup_tick < 0)
+      throw Unsupported("channel counts keep growing after the first chunk (multi-channel signal through a feedback edge): "
+                        "needs " + std::to_string(S) + " warm-up program(s)");
+  }
+  if (!dynamic_nch) b.nch = ns;
   for (auto &v : b.nch) for (int c : v) if (c > 16) throw Unsupported("more than 16 channels on one outlet");
 
   // ---- emit one instruction per unit-channel, in tick order ----
@@ -277,6 +297,16 @@ Program compile(const Graph &g) {
       b.word(un + ".state", u.num("state", 0), false);
       b.word(un + ".playing", u.num("playing", 0), false);
       b.def(r, 0, ui, 0, 0);
+    } else if (k == "SampleRateRedux") {
+      need_in(2);
+      for (int c = 0; c < inn(0); c++) {
+        IR &r = b.emit(OP_SRREDUX, ui, c); r.in[0] = b.in_ref(ui, 0, c); r.in[1] = b.in_ref(ui, 1, 0);
+        r.p = b.word(un + ".timeSinceLastUpdate[" + std::to_string(c) + "]", u.num("timeSinceLastUpdate", INFINITY), false);
+        b.word(un + ".val[" + std::to_string(c) + "]", 0.0, false);
+        b.def(r, 0, ui, 0, c);
+      }
+    } else if (k == "Monitor") {
+      // Monitor.js:14-16: console.log only
     } else if (k == "Timer") {
       IR &r = b.emit(OP_TIMER, ui, 0);
       r.p = b.word(un + ".t", u.num("t", 0), false);
@@ -490,6 +520,8 @@ Program compile(const Graph &g) {
     } else {
       throw Unsupported("unit kind " + k + " is outside the accelerated render path");
     }
+    // warm-up tick: units later in the order see this outlet with the channels it has just grown
+    if (dynamic_nch && !u.out.empty()) b.nch[ui][0] = std::max(b.nch[ui][0], written_channels(g, b.nch, ui, b));
   }
 
   // ---- retrigger targets: the state words target.trigger() assigns ----
@@ -644,6 +676,7 @@ Program compile(const Graph &g) {
     // KEEP: the circuit is edited at a later chunk.  The edit may re-level units so that an
     // existing outlet is then read one chunk late (a new feedback edge): every outlet value leaves its last
     // chunk in a stale buffer, where dusp_session_adopt finds it by name.
+    b.prog.keeps_all = g.keep_all;
     if (g.keep_all)
       for (size_t v = 0; v < b.vals.size(); v++) if (b.vals[v].def >= 0 && b.vals[v].outlet >= 0) keep((int)v);
     for (size_t i = 0; i < seq.size(); i++) {

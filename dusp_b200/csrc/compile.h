@@ -52,6 +52,8 @@ struct Program {
   int n_stale = 0;
   int out_nch = 0;
   int n_units = 0;              // units the reference ticks per chunk (metric: unit-samples)
+  bool keeps_all = false;       // compiled from a KEEP record: every outlet value it produces leaves its last chunk behind
+  int warmup_ticks = 0;         // ticks before the channel counts every unit sees are the steady ones (compile.cc)
   bool chunk_tiles = false;     // has per-chunk control ops (OP_RETRIG ...): must render in whole-chunk tiles (B*T = 256)
   double ring_bytes_per_sample = 0;  // SURVEY 8d accounting
   std::vector<TapPair> tap_pairs;

@@ -36,6 +36,7 @@ Graph parse_graph(const char *blob, size_t len) {
     if (tag == "U") { need(t, 2); g.units.emplace_back(); u = &g.units.back(); u->kind = t[1]; u->label = t.size() > 2 ? t[2] : ""; continue; }
     if (tag == "EV") continue;  // events after the first chunk: applied by the host as pokes (dusp_session_poke)
     if (tag == "KEEP") { g.keep_all = true; continue; }
+    if (tag == "WARMUP") { need(t, 2); g.warmup_tick = atoi(t[1].c_str()); continue; }
     if (tag == "TG") { need(t, 5); g.triggers.push_back({atoi(t[1].c_str()), atoi(t[2].c_str()), t[3], strtod(t[4].c_str(), nullptr)}); continue; }
     if (tag == "ORDER") { for (size_t i = 1; i < t.size(); i++) g.order.push_back(atoi(t[i].c_str())); has_order = true; continue; }
     if (tag == "ROOT") { need(t, 3); g.root_unit = atoi(t[1].c_str()); g.root_outlet = atoi(t[2].c_str()); continue; }

@@ -37,6 +37,7 @@ struct Graph {
   std::vector<int> order;
   std::vector<GTrigger> triggers;
   bool keep_all = false;  // KEEP record: a graph edit follows, keep every outlet's last chunk (compile.cc)
+  int warmup_tick = -1;   // WARMUP k record: compile the circuit as its k-th tick sees it (channel counts still growing)
   int root_unit = -1, root_outlet = 0;
 };
 

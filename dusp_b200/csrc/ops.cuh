@@ -294,6 +294,20 @@ DOPS_DEV void c_timer(const Cx<B, T> &cx, float (&o)[B], double &t) {
   });
 }
 
+// SampleRateRedux.js:20-37, one channel.  x: input in, held value out.
+template <int B, int T>
+DOPS_DEV void c_srredux(const Cx<B, T> &cx, float (&x)[B], const float (&amt)[B], double &ts, double &val) {
+  double unused = 0.0;
+  serial3<B, T>(cx, ts, val, unused, [&] {
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      ts += 1.0;
+      if (ts > (double)amt[s]) { val = (double)x[s]; ts = 0.0; }
+      x[s] = (float)val;
+    }
+  });
+}
+
 // ------------------------------------------------------------------ noise
 // Noise.js:16-28.  f: frequency in, output out.
 template <int B, int T>

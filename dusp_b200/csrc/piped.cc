@@ -40,7 +40,7 @@ constexpr int MAX_STEP = 256;
 // ops with no time-parallel form (or none worth having): they run in the lane-per-voice warp
 bool sequential_only(const Program &p, const DuspInstr &I) {
   switch (I.op) {
-    case OP_MCOSC: case OP_SHAPE: case OP_AHD: case OP_TIMER: case OP_NOISE: case OP_FILTER: case OP_FILTERC:
+    case OP_MCOSC: case OP_SHAPE: case OP_AHD: case OP_TIMER: case OP_SRREDUX: case OP_NOISE: case OP_FILTER: case OP_FILTERC:
     case OP_DELAY: case OP_MONODELAY: case OP_READBACK: case OP_CBWRITE: case OP_CBREAD:
       return true;
     case OP_FIXDELAY: case OP_COMB: case OP_ALLPASS: case OP_CBWRITEC: case OP_CBREADC:

@@ -340,6 +340,23 @@ __device__ __forceinline__ void op_timer(const Lane<B, T> &L, const DuspDevInstr
 }
 
 template <int B, int T>
+__device__ __forceinline__ void op_srredux(const Lane<B, T> &L, const DuspDevInstr &I) {  // SampleRateRedux.js:20-37
+  float x[B], m[B];
+  L.ld(x, I.in[0]); L.ld(m, I.in[1]);
+  L.serial([&] {
+    double ts = L.w(I.p), val = L.w(I.p + 1);
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      ts += 1.0;
+      if (ts > (double)m[s]) { val = (double)x[s]; ts = 0.0; }
+      x[s] = (float)val;
+    }
+    L.w(I.p) = ts; L.w(I.p + 1) = val;
+  });
+  L.st(x, I.out[0]);
+}
+
+template <int B, int T>
 __device__ __forceinline__ void op_noise(const Lane<B, T> &L, const DuspDevInstr &I) {  // Noise.js:16-28
   float f[B];
   L.ld(f, I.in[0]);
@@ -841,6 +858,7 @@ __global__ void __launch_bounds__(128, B <= 8 ? 4 : 2) dusp_render_tile(const __
         case OP_SHAPE: op_shape<B, T>(L, I); break;
         case OP_AHD: op_ahd<B, T>(L, I); break;
         case OP_TIMER: op_timer<B, T>(L, I); break;
+        case OP_SRREDUX: op_srredux<B, T>(L, I); break;
         case OP_NOISE: op_noise<B, T>(L, I); break;
         case OP_NOISE1: op_noise1<B, T>(L, I); break;
         case OP_RETRIG: if (B * T == DUSP_CHUNK) op_retrig<B, T>(L, I); break;

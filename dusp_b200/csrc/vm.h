@@ -73,6 +73,8 @@ enum DuspOp : int32_t {
   OP_RETRIG,    // Retriggerer.js:13-22        in0=rate [p: t, fired]: fired = 1 if t crossed sampleRate in this chunk
   OP_SRETRIG,   // SporadicRetrigger.js:12-16  in0=rate [p: draw, seed_lo, seed_hi, fired]: fired = rand() < rate[0]*256/SR
   OP_POKEIF,    // the assignments of target.trigger(): if word aux0 != 0 then word p = word aux1
+  OP_SRREDUX,   // SampleRateRedux.js:20-37    in0=in in1=ammount [p: timeSinceLastUpdate, val]  (per channel; each keeps
+                //                              its own copy of the shared counter, which only depends on `ammount`)
   OP_COUNT
 };
 

@@ -376,5 +376,420 @@ class ManyOsc(Patch):
         return ManyOsc.ofFrequencies(1, freqs)
 
 
-__all__ = ["APStack", "BandFilter", "Boop", "DelayMixer", "FMOsc", "FrequencyGroup", "LFO", "ManyOsc",
-           "MidiOsc", "Mixer", "MultiTapDelay", "SimpleDelay", "StereoDetune", "StereoOsc", "Worm"]
+class Synth(Patch):
+    """src/patches/Synth.js:3-28 (note-triggered patches: trigger() fans out to the registered envelopes)"""
+
+    def __init__(self):
+        super().__init__()
+        self.triggerList = []
+
+    def trigger(self, p=None, note=None):  # :10-19
+        if hasattr(self, "_trigger"):
+            self._trigger(p, note)
+        for env in self.triggerList:
+            env.trigger()
+        return self
+
+    def addEnvelope(self, env):  # :21-26
+        if getattr(env, "isOutlet", False):
+            env = env.unit
+        self.triggerList.append(env)
+        return env
+
+
+class TriggerGroup(Patch):
+    """src/patches/TriggerGroup.js:4-35"""
+
+    def __init__(self):
+        super().__init__()
+        self.mixer = Mixer()
+        self.addUnits(self.mixer)
+        self.triggers = {}
+        self.aliasOutlet(self.mixer.OUT)
+
+    def addTrigger(self, trigger, name=None):  # :18-26
+        if name is None:
+            name = 0
+            while name in self.triggers:
+                name += 1
+        self.triggers[name] = trigger
+        self.mixer.addInput(trigger)
+
+    def trigger(self, which=None):  # :28-35
+        t = self.triggers.get(which)
+        if t:
+            t.trigger()
+        elif getattr(self, "handleUnknownTrigger", None):
+            self.handleUnknownTrigger(which)
+        # else: the reference only logs "unknown trigger"
+
+
+class FMSynth(Synth):
+    """src/patches/FMSynth.js:13-190.  ``seed`` = {fundamental, mod, envelopes, oscs:[{h, stereoDetune,
+    modulation, mix}], resetOscsOnTrigger}; every entry goes through unDusp, and ``self.seed`` is the seed
+    written back as Dusp text by the serialiser (dusp.js)."""
+
+    def __init__(self, seed):
+        super().__init__()
+        from ..construct import unDusp
+        from ..dusp import dusp
+        self.resetOscsOnTrigger = True  # `seed.resetOscsOnTrigger || true` (:17)
+        fundamental = unDusp(seed.get("fundamental"))
+        globalModulation = unDusp(js_or(seed.get("mod"), 1))
+        envelopes = [unDusp(e) for e in (seed.get("envelopes") or [])]
+        oscSeeds = [{
+            "h": unDusp(o.get("h")),
+            "stereoDetune": unDusp(js_or(o.get("stereoDetune"), 0)),
+            "modulation": [unDusp(a) for a in (o.get("modulation") or [])],
+            "mix": unDusp(js_or(o.get("mix"), 0)),
+        } for o in seed["oscs"]]
+
+        def truthy(v):  # JS truthiness of a number / unit
+            return js_or(v, None) is not None
+
+        duspIndex = {}
+        out = {"fundamental": dusp(fundamental, duspIndex), "mod": dusp(globalModulation, duspIndex), "oscs": []}
+        for o in oscSeeds:  # :34-50
+            e = {"h": dusp(o["h"], duspIndex)}
+            if truthy(o["stereoDetune"]):
+                e["stereoDetune"] = dusp(o["stereoDetune"], duspIndex)
+            if truthy(o["mix"]):
+                e["mix"] = dusp(o["mix"], duspIndex)
+            if o["modulation"]:
+                e["modulation"] = [dusp(a, duspIndex) for a in o["modulation"]]
+            out["oscs"].append(e)
+        out["resetOscsOnTrigger"] = self.resetOscsOnTrigger
+        if envelopes:
+            out["envelopes"] = [dusp(e, duspIndex) for e in envelopes]
+        self.seed = out
+
+        for e in envelopes:
+            self.addEnvelope(e)
+        fGroup = FrequencyGroup(fundamental)
+        for o in oscSeeds:
+            fGroup.addHarmonic(o["h"])
+        oscs = []
+        for i, o in enumerate(oscSeeds):  # :65-73
+            if truthy(o["stereoDetune"]):
+                oscs.append(FMOsc(StereoDetune(fGroup.fOuts[i + 1], o["stereoDetune"])))
+            else:
+                oscs.append(FMOsc(fGroup.fOuts[i + 1]))
+        for carrier, o in enumerate(oscSeeds):  # :76-84 (`modulator` is the POSITION in the modulation list)
+            for modulator, ammount in enumerate(o["modulation"]):
+                if truthy(ammount):
+                    src = oscs[modulator] if modulator < len(oscs) else None
+                    oscs[carrier].addModulator(src, quick.multiply(ammount, globalModulation))
+        mixer = Mixer()
+        for i, o in enumerate(oscSeeds):
+            if truthy(o["mix"]):
+                mixer.addInput(quick.multiply(oscs[i], o["mix"]))
+        self.oscs = oscs
+        self.addUnits(fGroup, oscs, mixer)
+        self.aliasOutlet(mixer.OUT, "OUT")
+        self.aliasInlet(fGroup.F, "F")
+
+    def _trigger(self, p=None, note=None):  # :98-103
+        self.F = quick.pToF(p)
+        if self.resetOscsOnTrigger:
+            for o in self.oscs:
+                o.resetPhase()
+
+    @staticmethod
+    def randomSeed(f=50, duration=1, nOscs=8, pConnection=0.1, maxModulationAmmount=6, pMix=0.5,
+                   maxStereoDetune=1 / 2):  # :105-143
+        nOscs = js_or(nOscs, 4)
+        r = config.host_random.random
+        import math
+        oscs, envelopes = [], []
+        for _ in range(nOscs):
+            osc = {"h": math.ceil(r() * 32), "modulation": []}
+            if r() < pMix:
+                envelope = C.Shape.randomDecay(duration, 0, 1)
+                envelopes.append(envelope)
+                osc["mix"] = quick.multiply(envelope, r())
+            for _j in range(nOscs):
+                if r() < pConnection:
+                    envelope = C.Shape.randomInRange(duration, 0, 1)
+                    envelopes.append(envelope)
+                    osc["modulation"] += [envelope, quick.multiply(r(), maxModulationAmmount)]
+            oscs.append(osc)
+        return {"fundamental": f, "oscs": oscs, "envelopes": envelopes}
+
+    @staticmethod
+    def wormSeed(f=50, nOscs=8, pConnection=0.1, maxModulationAmmount=6, pMix=0.5, maxStereoDetune=1 / 2,
+                 maxHarmonic=16, maxWormFrequency=5):  # :145-188
+        nOscs = js_or(nOscs, 4)
+        r = config.host_random.random
+        import math
+        oscs, envelopes = [], []
+        for _ in range(nOscs):
+            osc = {"h": math.ceil(quick.multiply(r(), maxHarmonic)), "modulation": [],
+                   "stereoDetune": r() * maxStereoDetune}
+            if r() < pMix:
+                envelope = r()
+                envelopes.append(envelope)
+                osc["mix"] = quick.multiply(envelope, r())
+            for _j in range(nOscs):
+                if r() < pConnection:
+                    envelope = Worm.random(maxWormFrequency)
+                    envelopes.append(envelope)
+                    osc["modulation"] += [envelope, quick.multiply(r(), maxModulationAmmount)]
+            oscs.append(osc)
+        return {"fundamental": f, "oscs": oscs, "envelopes": envelopes}
+
+
+class OldFMSynth(Patch):
+    """src/patches/OldFMSynth.js:8-66 (constructor name in the reference is also ``FMSynth``)"""
+
+    def __init__(self, f=None):
+        super().__init__()
+        self.mixer = Mixer()
+        self.fgroup = FrequencyGroup()
+        self.addUnits(self.mixer, self.fgroup)
+        self.oscs = []
+        self.aliasInlet(self.fgroup.F, "f")
+        self.aliasOutlet(self.mixer.OUT, "out")
+        self.F = js_or(f, 440)
+        self.stereo = True
+
+    def addOsc(self, fRatio=None, master=None, inAmmounts=None, outAmmounts=None):  # :28-51
+        fRatio = js_or(fRatio, 1)
+        f = self.fgroup.addHarmonic(fRatio)
+        if self.stereo:
+            f = StereoDetune(f)
+        osc = FMOsc(f)
+        self.oscs.append(osc)
+        self.addUnits(osc)
+        if js_or(master, None) is not None:
+            self.mixer.addMultiplied(osc, master)
+        if inAmmounts:
+            for i in range(min(len(inAmmounts), len(self.oscs))):
+                if js_or(inAmmounts[i], None) is not None:
+                    osc.addModulator(self.oscs[i], inAmmounts[i])
+        if outAmmounts:
+            for i in range(min(len(outAmmounts), len(self.oscs))):
+                if js_or(outAmmounts[i], None) is not None:
+                    self.oscs[i].addModulator(osc, outAmmounts[i])
+        return osc
+
+    def clearModulation(self):
+        for o in self.oscs:
+            o.clearModulation()
+
+    def applyModulationMatrix(self, matrix):  # :58-66
+        self.clearModulation()
+        for i, row in enumerate(matrix):
+            for j, a in enumerate(row):
+                if js_or(a, None) is not None and i < len(self.oscs) and j < len(self.oscs):
+                    self.oscs[j].addModulator(self.oscs[i], a)
+
+
+class SineBoop(Patch):
+    """src/patches/SineBoop.js:8-43"""
+
+    def __init__(self, p=None, duration=None):
+        super().__init__()
+        self.osc = MidiOsc(p)
+        self.ramp = C.Shape("decay", duration)
+        self.multiply = C.Multiply(self.ramp, self.osc.OUT)
+        self.addUnits(self.osc, self.ramp, self.multiply)
+        self.alias(self.osc.P, "p")
+        self.alias(self.ramp.DURATION)
+        self.alias(self.multiply.OUT)
+        self.P = js_or(p, 60)
+        self.DURATION = js_or(duration, 1)
+
+    @staticmethod
+    def randomTwinkle(maxDuration=None):  # :32-37
+        boop = SineBoop()
+        boop.P = 100 + config.host_random.random() * 37
+        boop.ramp.randomDecay(js_or(maxDuration, 1))
+        return boop
+
+    def trigger(self):  # :39-43 (`this.osc` is the MidiOsc PATCH: the phase assignment never reaches the Osc unit)
+        self.ramp.trigger()
+        self.osc.phase = 0
+        return self
+
+
+class SpaceChannel(Patch):
+    """src/patches/SpaceChannel.js:9-47 (one speaker: distance -> attenuation in dB + propagation delay)"""
+
+    def __init__(self, speakerPosition=None):
+        super().__init__()
+        self.speakerPositionSubtracter = C.Subtract()
+        self.distanceCalculator = C.VectorMagnitude()
+        self.attenuationScaler = C.Multiply()
+        self.delayScaler = C.Multiply()
+        self.delayer = C.MonoDelay()
+        self.attenuator = C.Gain()
+        self.addUnits(self.speakerPositionSubtracter, self.distanceCalculator, self.attenuationScaler,
+                      self.delayScaler, self.delayer, self.attenuator)
+        self.distanceCalculator.IN = self.speakerPositionSubtracter.OUT
+        self.attenuationScaler.A = self.distanceCalculator.OUT
+        self.delayScaler.A = self.distanceCalculator.OUT
+        self.attenuator.GAIN = self.attenuationScaler.OUT
+        self.delayer.DELAY = self.delayScaler.OUT
+        self.delayer.IN = self.attenuator.OUT
+        self.aliasInlet(self.attenuator.IN)
+        self.aliasInlet(self.speakerPositionSubtracter.A, "placement")
+        self.aliasInlet(self.speakerPositionSubtracter.B, "speakerPosition")
+        self.aliasInlet(self.attenuationScaler.B, "decibelsPerMeter")
+        self.aliasInlet(self.delayScaler.B, "sampleDelayPerMeter")
+        self.aliasOutlet(self.delayer.OUT)
+        self.IN = 0
+        self.PLACEMENT = [0, 0]
+        self.SPEAKERPOSITION = js_or(speakerPosition, None) or [0, 0]
+        self.DECIBELSPERMETER = -3
+        self.SAMPLEDELAYPERMETER = config.sampleRate / 343
+
+
+class Space(Patch):
+    """src/patches/Space.js:8-64 (a SpaceChannel per speaker, concatenated into one multichannel outlet)"""
+
+    def __init__(self, input=None, place=None):
+        super().__init__()
+        import math
+        self.signalIn = C.Repeater()
+        self.placementIn = C.Repeater()
+        self.outRepeater = C.Repeater()
+        self.addUnits(self.signalIn, self.placementIn, self.outRepeater)
+        self.spaceChannels = []
+        self.alias(self.signalIn.IN)
+        self.alias(self.placementIn.IN, "placement")
+        self.alias(self.outRepeater.OUT)
+        self.IN = js_or(input, 0)
+        self.PLACEMENT = js_or(place, None) or [0, 0]
+        if config.channelFormat == "stereo":
+            self.addSpeaker([-1, 0])
+            self.addSpeaker([1, 0])
+        elif config.channelFormat == "surround":
+            for pos in ([-1, 1], [1, 1], [0, math.sqrt(2)], [0, 0], [-1, -1], [1, -1]):
+                self.addSpeaker(pos)
+
+    @staticmethod
+    def stereo(input=None, place=None):  # :46-51 (on top of the constructor's own speakers)
+        space = Space(input, place)
+        space.addSpeaker([-1, 0])
+        space.addSpeaker([1, 0])
+        return space
+
+    def addSpeaker(self, speakerPosition):  # :53-64
+        chan = SpaceChannel()
+        chan.SPEAKERPOSITION = speakerPosition
+        chan.PLACEMENT = self.placementIn.OUT
+        chan.IN = self.signalIn
+        if self.outRepeater.IN.connected:
+            self.outRepeater.IN = C.ConcatChannels(self.outRepeater.IN.outlet, chan)
+        else:
+            self.outRepeater.IN = chan
+        self.spaceChannels.append(chan)
+        self.addUnit(chan)
+
+
+class SpaceBoop(Patch):
+    """src/patches/SpaceBoop.js:11-58"""
+
+    def __init__(self, p=None, waveform=None, d=None, decayForm=None, place=None):
+        super().__init__()
+        self.mToF = C.MidiToFrequency()
+        self.osc = C.Osc(self.mToF)
+        self.durationToRate = C.Divide(1 / config.sampleRate)
+        self.envelope = C.Shape("decay", self.durationToRate)
+        self.envelopeAttenuator = C.Multiply(self.osc, self.envelope)
+        self.space = Space(self.envelopeAttenuator.OUT)
+        self.addUnits(self.mToF, self.osc, self.durationToRate, self.envelope, self.envelopeAttenuator, self.space)
+        self.aliasInlet(self.mToF.MIDI, "p")
+        self.aliasInlet(self.space.PLACEMENT, "placement")
+        self.aliasInlet(self.durationToRate.B, "duration")
+        self.aliasOutlet(self.space.OUT)
+        self.P = js_or(p, 60)
+        self.PLACEMENT = js_or(place, None) or [0, 0]
+        self.DURATION = js_or(d, 1)
+        self.waveform = js_or(waveform, "sin")
+        self.decayForm = js_or(decayForm, "decay")
+
+    def trigger(self, pitch=None, duration=None):  # :37-44
+        if js_or(pitch, None) is not None:
+            self.P = pitch
+        if js_or(duration, None) is not None:
+            self.DURATION = duration
+        self.osc.phase = 0
+        self.envelope.trigger()
+
+    @property
+    def waveform(self):
+        return self.osc.waveform
+
+    @waveform.setter
+    def waveform(self, w):
+        self.osc.waveform = w
+
+    @property
+    def decayForm(self):
+        return self.envelope.shape
+
+    @decayForm.setter
+    def decayForm(self, shape):
+        self.envelope.shape = shape
+
+
+class ScaryPatch(Patch):
+    """src/patches/ScaryPatch.js:6-27 (the signal is its own position in space)"""
+
+    def __init__(self, input=None, ammount=None):
+        super().__init__()
+        self.inRepeater = C.Repeater()
+        self.ammountScaler = C.Multiply(self.inRepeater, 1)
+        self.space = Space(self.inRepeater, self.ammountScaler)
+        self.addUnits(self.inRepeater, self.ammountScaler, self.space)
+        self.alias(self.inRepeater.IN)
+        self.aliasInlet(self.ammountScaler.B, "ammount")
+        self.alias(self.space.OUT)
+        self.IN = js_or(input, None) or [0, 0]
+        self.AMMOUNT = js_or(ammount, 1)
+
+
+class AttenuationMatrix(Patch):
+    """src/patches/AttenuationMatrix.js:4-41 (random Gain-weighted routing between ``nodes``; draws from the
+    injected host generator in the reference's order)"""
+
+    def __init__(self, nodes, pConnection=0.5, pMix=0.5, maxAmmount=1, minAmmount=0, maxMixAmmount=1,
+                 minMixAmmount=0, allowFeedback=True):
+        super().__init__()
+        r = config.host_random.random
+        outMixer = Mixer()
+        for i in range(len(nodes)):
+            mixer = Mixer()
+            for j in range(len(nodes)):
+                if j < i and not allowFeedback:
+                    continue
+                if r() < pConnection:
+                    ammount = r() * (maxAmmount - minAmmount) + minAmmount
+                    mixer.addAttenuated(nodes[j].OUT, ammount)
+            if mixer.numberOfInputs:
+                self.addUnits(mixer)
+                nodes[i].IN = mixer
+            if r() < pMix:
+                ammount = r() * (maxMixAmmount - minMixAmmount) + minAmmount  # sic: minAmmount (:32)
+                outMixer.addAttenuated(nodes[i].OUT, ammount)
+        self.aliasInlet(nodes[0].IN, "in")
+        self.aliasOutlet(outMixer.OUT, "out")
+
+
+class APWeb(Patch):
+    """src/patches/APWeb.js:5-24"""
+
+    def __init__(self, n=4, maxDelay=0.01, maxFeedback=0.1):
+        super().__init__()
+        nodes = C.AllPass.manyRandom(n, maxDelay, maxFeedback)
+        matrix = AttenuationMatrix(nodes=nodes, allowFeedback=False, pMix=1)
+        self.addUnits(matrix)
+        self.aliasInlet(matrix.IN, "in")
+        self.aliasOutlet(matrix.OUT, "out")
+
+
+__all__ = ["APStack", "APWeb", "AttenuationMatrix", "BandFilter", "Boop", "DelayMixer", "FMOsc", "FMSynth",
+           "FrequencyGroup", "LFO", "ManyOsc", "MidiOsc", "Mixer", "MultiTapDelay", "ScaryPatch", "SimpleDelay",
+           "SineBoop", "Space", "SpaceBoop", "SpaceChannel", "StereoDetune", "StereoOsc", "Synth", "TriggerGroup",
+           "Worm"]

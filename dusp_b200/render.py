@@ -221,6 +221,32 @@ def blob_events(blob):
     return ev
 
 
+def _with_records(text, records):
+    assert text.endswith("END\n")
+    return text[:-len("END\n")] + "".join(r + "\n" for r in records) + "END\n"
+
+
+def expand_warmup(timeline):
+    """Channel growth at the start of a render.  The reference's tick order is not topological (Unit.js:171-209), so
+    a unit can tick before its producer and see that outlet with the channel count of the previous tick: a
+    multi-channel signal takes S ticks to reach every unit (Space / ScaryPatch / stereo-detuned FM patches).  The
+    library compiles tick k < S from a ``WARMUP k`` record (``dusp_program_warmup_ticks``); here those programs become
+    one-chunk epochs in front of the steady program, with ``KEEP`` so each hands every outlet's last chunk on."""
+    k0, text = timeline[0]
+    try:
+        capi.Program(text)
+        return timeline
+    except capi.UnsupportedCircuit as e:
+        if "warm-up" not in str(e):
+            raise
+    s = capi.Program(_with_records(text, ["WARMUP 0"])).warmup_ticks
+    if len(timeline) > 1 and timeline[1][0] <= s:
+        raise capi.UnsupportedCircuit("graph edit while channel counts are still growing")
+    keep = [] if "\nKEEP\n" in text else ["KEEP"]
+    return [(k, _with_records(text, ["WARMUP %d" % k] + keep)) for k in range(s)] + \
+        [(s, _with_records(text, ["WARMUP %d" % s]))] + timeline[1:]
+
+
 class SessionRun:
     """A session driven through its circuits' timelines: chunk-aligned segments, the events of chunk
     k poked into every voice of their program group before the segment that starts at sample 256*k, and a new
@@ -231,7 +257,7 @@ class SessionRun:
     def __init__(self, blobs, voices, device=0):
         self.device = device
         self.voices = [int(v) for v in voices]
-        self.timelines = [split_epochs(b) for b in blobs]
+        self.timelines = [expand_warmup(split_epochs(b)) for b in blobs]
         self.epoch = [0] * len(blobs)
         self.programs = [capi.Program(tl[0][1]) for tl in self.timelines]
         self.events = [blob_events(tl[0][1]) for tl in self.timelines]

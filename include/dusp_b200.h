@@ -70,6 +70,14 @@ void dusp_program_destroy(dusp_program *p);
 int dusp_program_num_channels(const dusp_program *p); /* channels of the rendered outlet */
 int dusp_program_num_units(const dusp_program *p);    /* units the reference would tick per chunk */
 int dusp_program_num_instructions(const dusp_program *p);
+/* Replaces: outlet channel arrays growing while the circuit runs (`out[c] = out[c] || new Float32Array`, e.g.
+ * Repeater.js:25, Multiply.js:26).  A unit the reference's order ticks before its producer (Unit.js:171-209 is not
+ * a topological sort) sees the producer's outlet one tick late, so a multi-channel signal needs a few ticks to
+ * reach every unit.  A blob holding a `WARMUP k` record compiles the circuit as its k-th tick runs; this returns
+ * S, the number of such ticks before the program is the steady one (0 for most circuits).  A blob that needs
+ * warm-up programs and has no WARMUP record fails with DUSP_EUNSUPPORTED; the host renders chunk k < S with
+ * program k and hands state over with dusp_session_adopt (dusp_b200/render.py: SessionRun). */
+int dusp_program_warmup_ticks(const dusp_program *p);
 int dusp_program_num_slots(const dusp_program *p);
 /* bytes of compulsory HBM traffic per voice-sample in DUSP_OUT_VOICES mode
  * (SURVEY.md 8d accounting: 4*C_out + ring traffic) and the ring part alone */

@@ -96,7 +96,7 @@ enum Kind {
   K_FIXEDMULTIPLY, K_SEMITONETORATIO, K_MIDITOFREQUENCY, K_DECIBELTOSCALER, K_SECONDSTOSAMPLES,
   K_CONCATCHANNELS, K_PICKCHANNEL, K_VECTORMAGNITUDE,
   K_DELAY, K_MONODELAY, K_READBACKDELAY, K_FIXEDDELAY, K_COMBFILTER, K_ALLPASS,
-  K_CBWRITER, K_CBREADER, K_RETRIGGERER, K_SPORADICRETRIGGERER, K_NKINDS
+  K_CBWRITER, K_CBREADER, K_RETRIGGERER, K_SPORADICRETRIGGERER, K_SAMPLERATEREDUX, K_MONITOR, K_NKINDS
 };
 static const char *KIND_NAMES[K_NKINDS] = {
   "Osc", "MultiChannelOsc", "Ramp", "Shape", "AHD", "Timer", "Noise", "Filter",
@@ -105,7 +105,7 @@ static const char *KIND_NAMES[K_NKINDS] = {
   "FixedMultiply", "SemitoneToRatio", "MidiToFrequency", "DecibelToScaler", "SecondsToSamples",
   "ConcatChannels", "PickChannel", "VectorMagnitude",
   "Delay", "MonoDelay", "ReadBackDelay", "FixedDelay", "CombFilter", "AllPass",
-  "CircleBufferWriter", "CircleBufferReader", "Retriggerer", "SporadicRetriggerer"};
+  "CircleBufferWriter", "CircleBufferReader", "Retriggerer", "SporadicRetriggerer", "SampleRateRedux", "Monitor"};
 
 struct Unit;
 typedef struct Port {
@@ -145,6 +145,8 @@ typedef struct Unit {
   /* delays */
   long maxdelay; float *bufs[MAXCH]; long buflen; double tbuffer;
   CircleBuffer *cb; int prewipe, postwipe;
+  /* SampleRateRedux.js:9-10 */
+  double srr_val[MAXCH]; int srr_nval; double srr_ts;
 } Unit;
 
 /* An Event (Event.js:3-30) whose function only assigns numeric unit state, e.g. the trigger() queued by
@@ -305,6 +307,7 @@ static int init_unit_state(Oracle *o, Unit *u) {
     u->lastf_defined = 0;
     break; }
   case K_PAN: u->comp_db = propd(u, "compensationDB", 1.5); break; /* Pan.js:12 */
+  case K_SAMPLERATEREDUX: u->srr_val[0] = 0; u->srr_nval = 1; u->srr_ts = propd(u, "timeSinceLastUpdate", INFINITY); break; /* SampleRateRedux.js:9-10 */
   case K_FIXEDMULTIPLY: u->sf = propd(u, "sf", NAN); break;
   case K_DELAY: u->maxdelay = (long)propd(u, "maxDelay", SR * 5); break;            /* Delay.js:13-14 */
   case K_MONODELAY: u->maxdelay = SR * 5; u->bufs[0] = (float *)calloc(u->maxdelay, 4); break; /* MonoDelay.js:9-10 */
@@ -655,6 +658,20 @@ static void tick_ahd(Unit *u) {
     }
   }
 }
+/* SampleRateRedux.js:20-37 */
+static void tick_sampleratereux(Unit *u) {
+  Chunk *in = INCH(u, 0), *o = OUTCH(u, 0); const float *amt = INCH(u, 1)->ch[0];
+  for (int c = 0; c < in->nch; c++) chunk_ensure(o, c);          /* while(out.length < in.length) push */
+  for (int t = 0; t < CHUNK; t++) {
+    u->srr_ts++;
+    if (u->srr_ts > (double)amt[t]) {
+      u->srr_nval = in->nch;
+      for (int c = 0; c < in->nch; c++) u->srr_val[c] = (double)in->ch[c][t];
+      u->srr_ts = 0;
+    }
+    for (int c = 0; c < u->srr_nval; c++) o->ch[c][t] = (float)u->srr_val[c];
+  }
+}
 /* Timer.js:37-42 */
 static void tick_timer(Unit *u) {
   float *out = OUTCH(u, 0)->ch[0]; const double sp = 1.0 / SR;
@@ -979,6 +996,8 @@ static int unit_tick(Oracle *o, Unit *u, double clock) {
   case K_SHAPE: tick_shape(u); break;
   case K_AHD: tick_ahd(u); break;
   case K_TIMER: tick_timer(u); break;
+  case K_SAMPLERATEREDUX: tick_sampleratereux(u); break;
+  case K_MONITOR: break; /* Monitor.js:14-16: console.log only */
   case K_RETRIGGERER: return tick_retriggerer(o, u);
   case K_SPORADICRETRIGGERER: return tick_sporadic_retriggerer(o, u);
   case K_NOISE: tick_noise(u); break;
@@ -1026,6 +1045,7 @@ static int apply_event(Oracle *o, const OEvent *ev) {
   else if (!strcmp(p, "playing")) u->playing = v != 0;
   else if (!strcmp(p, "state")) u->state = (int)v;
   else if (!strcmp(p, "phase")) u->phase = v;
+  else if (!strcmp(p, "phase[*]")) { for (int c = 0; c < MAXCH; c++) if (u->mc_phase_set[c]) u->mc_phase[c] = v; } /* MultiChannelOsc.js:52-55 */
   else if (!strcmp(p, "y0")) u->y0 = v;
   else if (!strcmp(p, "y1")) u->y1 = v;
   else if (!strcmp(p, "duration")) u->duration = v;
@@ -1063,6 +1083,7 @@ static void adopt_state(Oracle *n, Oracle *o) {
     memcpy(a->x1, b->x1, sizeof a->x1); memcpy(a->x2, b->x2, sizeof a->x2);
     memcpy(a->fy1, b->fy1, sizeof a->fy1); memcpy(a->fy2, b->fy2, sizeof a->fy2); memcpy(a->sdef, b->sdef, sizeof a->sdef);
     a->tbuffer = b->tbuffer;
+    memcpy(a->srr_val, b->srr_val, sizeof a->srr_val); a->srr_nval = b->srr_nval; a->srr_ts = b->srr_ts;
     if (a->maxdelay == b->maxdelay && a->buflen == b->buflen)
       for (int c = 0; c < MAXCH; c++) if (b->bufs[c]) { free(a->bufs[c]); a->bufs[c] = b->bufs[c]; b->bufs[c] = NULL; }
     if (a->cb && b->cb && a->cb->nch == b->cb->nch && a->cb->len == b->cb->len)

@@ -315,6 +315,92 @@ def event_assigns_inlet():  # an event that assigns an inlet constant and later 
 
 
 # name -> (factory, seconds, exact?)
+def sample_rate_redux():  # SampleRateRedux.js: sample-and-hold with a modulated period, stereo input
+    src = C.ConcatChannels(C.Osc(441), C.Osc(100.5, "saw"))
+    return C.SampleRateRedux(src, quick.add(quick.multiply(C.Osc(0.9), 6), 8))
+
+
+def sample_rate_redux_static():
+    return d.unDusp("[SampleRateRedux in:O330 ammount:4.5]")
+
+
+def fm_synth():  # note-triggered FM patch built from a seeded random seed (FMSynth.js:105-143)
+    d.config.seed(5)
+    fm = P.FMSynth(P.FMSynth.randomSeed(f=110, nOscs=4, pConnection=0.4))
+    fm.trigger(57)
+    return fm
+
+
+def fm_synth_worm():  # Worm LFO envelopes + stereo detune: channel counts settle over the first ticks
+    d.config.seed(6)
+    fm = P.FMSynth(P.FMSynth.wormSeed(f=110, nOscs=3, pConnection=0.5, pMix=0))
+    fm.oscs[0].OUT  # (all oscillators silent in the mix when pMix = 0: render one of them instead)
+    fm.trigger(50)
+    return fm.oscs[1]
+
+
+def fm_synth_retriggered():  # the synth's trigger() as scheduled events: F assignment + phase resets + envelopes
+    d.config.seed(11)
+    fm = P.FMSynth(P.FMSynth.randomSeed(f=80, nOscs=3, pConnection=0.3, pMix=1))
+    fm.trigger(45)
+    fm.schedule(0.25, lambda s: s.trigger(52))
+    fm.schedule(0.5, lambda s: s.trigger(40))
+    return fm
+
+
+def old_fm_synth():
+    d.config.seed(2)
+    s = P.OldFMSynth(220)
+    s.addOsc(1, 0.5)
+    s.addOsc(2, 0.25, [3])
+    s.addOsc(3.01, None, None, [1.5, 0.5])
+    return s
+
+
+def sine_boop():
+    b = P.SineBoop(72, 0.3)
+    b.trigger()
+    return b
+
+
+def space_boop():
+    b = P.SpaceBoop(64, "triangle", 0.4, "decaySquared", [0.5, 1.0])
+    b.trigger()
+    return b
+
+
+def space_moving():  # a source circling between two speakers: distance -> Gain (pow) and MonoDelay
+    place = C.ConcatChannels(C.Multiply(C.Osc(0.7), 3), C.Multiply(C.Osc(0.45, "triangle"), 2))
+    return P.Space(C.Osc(330), place)
+
+
+def scary_patch():  # the signal is its own position; 3 warm-up ticks before every unit sees both channels
+    return P.ScaryPatch(C.ConcatChannels(C.Osc(220), C.Osc(1.3)), 2.5)
+
+
+def trigger_group():
+    g = P.TriggerGroup()
+    a, b = P.SineBoop(60, 0.2), P.SineBoop(67, 0.4)
+    g.addTrigger(a, "a")
+    g.addTrigger(b)
+    g.trigger("a")
+    g.trigger(0)
+    g.trigger("zzz")
+    return g
+
+
+def ap_web():
+    d.config.seed(9)
+    w = P.APWeb(4, 0.01, 0.3)
+    w.IN = C.Noise(seed=3)
+    return w
+
+
+def dusp_roundtrip():  # dusp.js text of a circuit, parsed again, renders like the original (see test_dusp.py)
+    from dusp_b200.dusp import dusp
+    return d.unDusp(dusp(d.unDusp("[Filter in:(Z110.25 * D0.5) f:(O2 * 300 + 900)] @ -0.5")))
+
+
 CASES = {
     "osc440": (osc440, 1.0, True),
     "readme_fm_literal": (readme_fm_literal, 1.0, True),
@@ -372,4 +458,17 @@ CASES = {
     "then_into_filter": (then_into_filter, 0.7, True),
     "then_with_delay": (then_with_delay, 0.9, True),
     "event_assigns_inlet": (event_assigns_inlet, 0.8, True),
+    "sample_rate_redux": (sample_rate_redux, 0.4, True),
+    "sample_rate_redux_static": (sample_rate_redux_static, 0.2, True),
+    "fm_synth": (fm_synth, 0.6, False),
+    "fm_synth_worm": (fm_synth_worm, 0.5, False),
+    "fm_synth_retriggered": (fm_synth_retriggered, 0.8, False),
+    "old_fm_synth": (old_fm_synth, 0.4, False),
+    "sine_boop": (sine_boop, 0.4, False),
+    "space_boop": (space_boop, 0.5, False),
+    "space_moving": (space_moving, 0.6, False),
+    "scary_patch": (scary_patch, 0.4, False),
+    "trigger_group": (trigger_group, 0.5, False),
+    "ap_web": (ap_web, 0.4, False),
+    "dusp_roundtrip": (dusp_roundtrip, 0.6, False),
 }
