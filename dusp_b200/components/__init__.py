@@ -815,7 +815,268 @@ class SporadicRetriggerer(Retriggerer):
         return {"seed_lo": self.seed & 0xFFFFFFFF, "seed_hi": self.seed >> 32, "draw": self.draw}, {}
 
 
+# ------------------------------------------------------------ spectral units
+# SURVEY 8f-3.  Frame-rate units: their ports carry chunks of `windowSize` / `2*windowSize` / `hopSize` samples
+# and they tick every `tickInterval` samples (Circuit.js:34-37).  `_tick`s live in csrc/render_sm100.cu.
+def _is_pow2(n):
+    return isinstance(n, int) and n > 1 and (n & (n - 1)) == 0
+
+
+def _need_int(what, v):
+    if not isinstance(v, int) or isinstance(v, bool) or v <= 0:
+        raise DuspError(what + " must be a positive integer number of samples")
+    return v
+
+
+class Hopper(Unit):
+    """src/components/spectral/Hopper.js:4-38 -- collects the input into overlapping frames of `frameSize`
+    samples, one every `hopSize`."""
+    KIND = "Hopper"
+
+    def __init__(self, hopSize=None, frameSize=None):
+        super().__init__()
+        import math
+        _need_int("Hopper hopSize", hopSize)
+        _need_int("Hopper frameSize", frameSize)
+        self.addInlet("in")
+        self.addOutlet("out", {"chunkSize": frameSize})
+        self.hopSize = hopSize
+        self.frameSize = frameSize
+        self.t = 0
+        self.tickInterval = math.gcd(hopSize, self.IN.chunkSize)
+
+    def blob_props(self):
+        return {"hopSize": self.hopSize, "frameSize": self.frameSize, "t": self.t, "tickInterval": self.tickInterval}, {}
+
+
+class Windower(Unit):
+    """src/components/spectral/Windower.js:3-49"""
+    KIND = "Windower"
+
+    def __init__(self, windowSize=None, kind="hamming", hopSize=None):
+        super().__init__()
+        if not windowSize:
+            raise DuspError("Windower constructor expects a windowSize")
+        _need_int("Windower windowSize", windowSize)
+        self.addInlet("in", {"chunkSize": windowSize})
+        self.addOutlet("out", {"chunkSize": windowSize})
+        self.tickInterval = _need_int("Windower hopSize (its tick interval)", hopSize)
+        self.windowSize = windowSize
+        self.windowKind = kind
+        if kind != "hamming":  # Windower.js:31-35,38-39
+            raise DuspError("Window type '" + str(kind) + "' is not defined.")
+
+    def blob_props(self):
+        return {"windowSize": self.windowSize, "tickInterval": self.tickInterval}, {"windowKind": self.windowKind}
+
+
+class FFT(Unit):
+    """src/components/spectral/FFT.js:4-26 (fft.js realTransform + completeSpectrum)"""
+    KIND = "FFT"
+
+    def __init__(self, windowSize=None, hopSize=None):
+        super().__init__()
+        if not windowSize:
+            raise DuspError("FFT expects window size")
+        if not _is_pow2(windowSize):  # fft.js constructor
+            raise DuspError("FFT size must be a power of two and bigger than 1")
+        self.windowSize = windowSize
+        self.frameSize = windowSize * 2
+        self.tickInterval = _need_int("FFT hopSize (its tick interval)", hopSize)
+        self.addInlet("in", {"chunkSize": windowSize})
+        self.addOutlet("out", {"chunkSize": self.frameSize, "type": "spectral"})
+
+    def blob_props(self):
+        return {"windowSize": self.windowSize, "tickInterval": self.tickInterval}, {}
+
+
+class IFFT(Unit):
+    """src/components/spectral/IFFT.js:4-34 (fft.js inverseTransform, real part kept)"""
+    KIND = "IFFT"
+
+    def __init__(self, windowSize=None, hopSize=None):
+        super().__init__()
+        if not windowSize:
+            raise DuspError("IFFT constructor requires argument: windowSize")
+        if not _is_pow2(windowSize):
+            raise DuspError("FFT size must be a power of two and bigger than 1")
+        self.windowSize = windowSize
+        self.frameSize = windowSize * 2
+        self.tickInterval = _need_int("IFFT hopSize (its tick interval)", hopSize)
+        self.addInlet("in", {"type": "spectral", "chunkSize": self.frameSize})
+        self.addOutlet("out", {"chunkSize": windowSize})
+
+    def blob_props(self):
+        return {"windowSize": self.windowSize, "tickInterval": self.tickInterval}, {}
+
+
+class UnHopper(Unit):
+    """src/components/spectral/UnHopper.js:3-45 -- overlap-add of `windowSize` frames, one hop out per tick"""
+    KIND = "UnHopper"
+
+    def __init__(self, hopSize=None, windowSize=None):
+        super().__init__()
+        self.windowSize = _need_int("UnHopper windowSize", windowSize)
+        self.hopSize = _need_int("UnHopper hopSize", hopSize)
+        self.tickInterval = hopSize
+        self.addInlet("in", {"chunkSize": windowSize})
+        self.addOutlet("out", {"chunkSize": hopSize})
+        self.t = 0
+
+    def blob_props(self):
+        return {"hopSize": self.hopSize, "windowSize": self.windowSize, "t": self.t, "tickInterval": self.tickInterval}, {}
+
+
+class ReChunk(Unit):
+    """src/components/spectral/ReChunk.js:5-51 -- re-blocks a signal between two chunk sizes"""
+    KIND = "ReChunk"
+
+    def __init__(self, inputInterval=None, outputInterval=None):
+        super().__init__()
+        import math
+        if not inputInterval or not outputInterval:
+            raise DuspError("ReChunk expects 2 numeric contructor arguments")
+        self.inputInterval = _need_int("ReChunk inputInterval", inputInterval)
+        self.outputInterval = _need_int("ReChunk outputInterval", outputInterval)
+        self.addInlet("in", {"chunkSize": inputInterval})
+        self.addOutlet("out", {"chunkSize": outputInterval})
+        self.tickInterval = math.gcd(inputInterval, outputInterval)
+        self.bufferSize = inputInterval * outputInterval // self.tickInterval  # compute-lcm
+        self.t = 0
+
+    def blob_props(self):
+        return {"inputInterval": self.inputInterval, "outputInterval": self.outputInterval, "t": self.t,
+                "bufferSize": self.bufferSize, "tickInterval": self.tickInterval}, {}
+
+
+class SpectralUnit(Unit):
+    """src/components/spectral/SpectralUnit.js:8-33"""
+    isSpectralUnit = True
+
+    def __init__(self):
+        super().__init__()
+        self.windowSize = config.fft["windowSize"]
+        self.frameSize = self.windowSize * 2
+        self.hopInterval = config.fft["hopSize"]
+        self.tickInterval = self.hopInterval
+
+    def addSpectralInlet(self, name, options=None):
+        options = dict(options or {}, type="spectral", chunkSize=self.frameSize)
+        return self.addInlet(name, options)
+
+    def addSpectralOutlet(self, name, options=None):
+        options = dict(options or {}, type="spectral", chunkSize=self.frameSize)
+        return self.addOutlet(name, options)
+
+    def _frame_props(self):
+        return {"windowSize": self.windowSize, "tickInterval": self.tickInterval}
+
+    def blob_props(self):
+        return self._frame_props(), {}
+
+
+class HardLowPass(SpectralUnit):
+    """src/components/spectral/HardLowPass.js:7-32"""
+    KIND = "HardLowPass"
+
+    def __init__(self, f=None):
+        super().__init__()
+        self.addSpectralInlet("in")
+        self.addInlet("f", {"mono": True, "type": "frequency"})
+        self.addSpectralOutlet("out")
+        self.fPerBin = self.sampleRate / self.windowSize
+        self.F = f
+
+
+class HardHighPass(HardLowPass):
+    """src/components/spectral/HardHighPass.js:7-32"""
+    KIND = "HardHighPass"
+
+
+class SpectralGate(SpectralUnit):
+    """src/components/spectral/SpectralGate.js:3-33"""
+    KIND = "SpectralGate"
+
+    def __init__(self, threshold=None):
+        super().__init__()
+        self.addSpectralInlet("in")
+        self.addInlet("threshold", {"mono": True})
+        self.addSpectralOutlet("out")
+        self.invert = True
+        self.THRESHOLD = js_or(threshold, 0.5)
+
+    def blob_props(self):
+        return dict(self._frame_props(), invert=int(bool(self.invert))), {}
+
+
+class BinShift(SpectralUnit):
+    """src/components/spectral/BinShift.js:3-27"""
+    KIND = "BinShift"
+
+    def __init__(self, shift=None):
+        super().__init__()
+        self.addSpectralInlet("in")
+        self.addInlet("shift", {"mono": True})
+        self.addSpectralOutlet("out")
+        self.SHIFT = js_or(shift, 0)
+
+
+class Augment(SpectralUnit):
+    """src/components/spectral/Augment.js:3-28.  ``incrementMapping`` {ratio: gain}: every bin is added, scaled,
+    into bin round(bin * ratio); keys iterate in JavaScript's own-property order (integer keys ascending first)."""
+    KIND = "Augment"
+
+    def __init__(self, incrementMapping=None, windowSize=None, hopInterval=None):
+        super().__init__()
+        self.addSpectralInlet("in")
+        self.addSpectralOutlet("out")
+        self.incrementMapping = {1: 1} if incrementMapping is None else dict(incrementMapping)
+
+    def mapping_in_js_order(self):
+        def is_index(k):
+            s = _js_key(k)
+            return s.isdigit() and (s == "0" or not s.startswith("0")) and int(s) < 2 ** 32 - 1
+        keys = list(self.incrementMapping)
+        ints = sorted((k for k in keys if is_index(k)), key=lambda k: int(_js_key(k)))
+        rest = [k for k in keys if not is_index(k)]
+        return [(float(_js_key(k)), float(self.incrementMapping[k])) for k in ints + rest]
+
+    def blob_props(self):
+        p = self._frame_props()
+        m = self.mapping_in_js_order()
+        if len(m) > 8:
+            raise DuspError("Augment with more than 8 mapping entries has no device implementation")
+        p["nmap"] = len(m)
+        for i, (r, g) in enumerate(m):
+            p["ratio%d" % i] = r
+            p["gain%d" % i] = g
+        return p, {}
+
+
+def _js_key(k):
+    """Property-key string of a number used as an object key."""
+    if isinstance(k, str):
+        return k
+    from ..dusp import js_number_string
+    return js_number_string(k)
+
+
+class SpectralSum(SpectralUnit):
+    """src/components/spectral/SpectralSum.js:3-25"""
+    KIND = "SpectralSum"
+
+    def __init__(self, a=None, b=None, windowSize=None, hopInterval=None):
+        super().__init__()
+        self.addSpectralInlet("a")
+        self.addSpectralInlet("b")
+        self.addSpectralOutlet("out")
+        self.A = a
+        self.B = b
+
+
 __all__ = [
+    "Hopper", "Windower", "FFT", "IFFT", "UnHopper", "ReChunk", "SpectralUnit", "HardLowPass", "HardHighPass",
+    "SpectralGate", "BinShift", "Augment", "SpectralSum",
     "AHD", "Abs", "AllPass", "CircleBuffer", "CircleBufferNode", "CircleBufferReader", "CircleBufferWriter",
     "Clip", "CombFilter", "ConcatChannels", "CrossFader", "DecibelToScaler", "Delay", "Divide", "Filter",
     "FixedDelay", "FixedMultiply", "Gain", "HardClipAbove", "HardClipBelow", "MidiToFrequency", "Monitor", "MonoDelay",

@@ -16,6 +16,7 @@ import math
 standardChunkSize = 256  # src/config.js:6
 sampleRate = 44100       # src/config.js:7
 channelFormat = "stereo"
+fft = {"windowSize": 4096, "hopSize": 4096 // 4, "windowKind": "hamming"}  # src/config.js:10-14
 useDuspShorthands = True
 sampleInterval = 1 / sampleRate
 

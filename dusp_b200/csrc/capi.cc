@@ -87,6 +87,7 @@ struct Group {
   float *d_rings = nullptr;
   DuspRing *d_ringtab = nullptr;
   float *d_stale = nullptr;
+  double *d_ctab = nullptr;  // program constants (FFT twiddles, window envelopes); owned by the session
   bool dirty = true;  // device words/rings need (re)initialisation
   size_t off_words = 0, off_rings = 0, off_stale = 0;  // this group's segments of the session pools (elements)
   bool in_multi = false;  // rendered by the session's one multi-program interpreter launch
@@ -171,6 +172,7 @@ void dusp_session_destroy(dusp_session *s) {
   cudaFree(s->d_words_pool); cudaFree(s->d_rings_pool); cudaFree(s->d_stale_pool); cudaFree(s->d_ringtab_pool);
   cudaFree(s->d_code_pool); cudaFree(s->d_multi);
   cudaFree(s->d_tables);
+  for (auto &g : s->groups) cudaFree(g.d_ctab);
   for (int i = 0; i < 2; i++) {
     cudaFree(s->d_staging[i]);
     if (s->ev_rendered[i]) cudaEventDestroy(s->ev_rendered[i]);
@@ -324,6 +326,11 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
       std::copy(g.prog.rings.begin(), g.prog.rings.end(), h_rt.begin() + off_rt[i]);
       std::copy(g.dev_code.begin(), g.dev_code.end(), h_code.begin() + off_code[i]);
     }
+    for (auto &g : s->groups)
+      if (!g.prog.ctab.empty()) {
+        CUDA_TRY(cudaMalloc(&g.d_ctab, g.prog.ctab.size() * sizeof(double)));
+        CUDA_TRY(cudaMemcpy(g.d_ctab, g.prog.ctab.data(), g.prog.ctab.size() * sizeof(double), cudaMemcpyHostToDevice));
+      }
     CUDA_TRY(cudaMemcpy(s->d_ringtab_pool, h_rt.data(), n_rt * sizeof(DuspRing), cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(s->d_code_pool, h_code.data(), n_code * sizeof(DuspDevInstr), cudaMemcpyHostToDevice));
   }
@@ -598,6 +605,7 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     kp.n_voices = g.n_voices; kp.voice0 = g.voice0; kp.nv_stride = g.nv_pad;
     kp.words = g.d_words; kp.rings = g.d_rings; kp.ring_stride = std::max<long long>(g.prog.ring_floats, 4);
     kp.ring_tab = g.d_ringtab; kp.stale = g.d_stale; kp.n_stale = g.prog.n_stale; kp.tables = s->d_tables;
+    kp.ctab = g.d_ctab;
     kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = g.prog.out_nch; kp.out_mode = out_mode; kp.out_raw = raw;
     kp.out_len = n; kp.clock0 = s->clock; kp.n_samples = n;
     const int wpc = g.warps_per_cta;

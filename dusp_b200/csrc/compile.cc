@@ -36,10 +36,11 @@ const char *OP_NAMES[OP_COUNT] = {
     "gain", "clip", "hca", "hcb", "rescale", "xfade", "pan", "vecmag", "osc", "mcosc", "ramp", "shape", "ahd",
     "timer", "noise", "filter", "fixdelay", "comb", "allpass", "delay", "monodelay", "readback", "cbwrite",
     "cbread", "ldstale", "ststale", "out", "filterc", "panc", "gainc", "noise1", "cbwritec", "cbreadc", "add0",
-    "retrig", "sretrig", "pokeif", "srredux"};
+    "retrig", "sretrig", "pokeif", "srredux", "hopper", "window", "fft", "ifft", "unhop", "rechunk", "specpass",
+    "specgate", "binshift", "augment", "specsum", "ldframe", "stframe", "outring"};
 
 struct Opnd {
-  int kind = 0;  // 0 none (reads 0), 1 value, 2 const word
+  int kind = 0;  // 0 none (reads 0), 1 value, 2 const word, 3 immediate (frame ops: ring ids / sizes travel in `in`)
   int id = -1;
 };
 
@@ -146,6 +147,30 @@ int table_id(const std::string &s, bool shape) {
   throw std::runtime_error("invalid shape function: " + s);
 }
 
+// ---- frame-rate units (components/spectral) ----
+bool is_spectral_unit(const std::string &k) {
+  return k == "HardLowPass" || k == "HardHighPass" || k == "SpectralGate" || k == "BinShift" || k == "Augment" || k == "SpectralSum";
+}
+bool is_frame_kind(const std::string &k) {
+  return k == "Hopper" || k == "Windower" || k == "FFT" || k == "IFFT" || k == "UnHopper" || k == "ReChunk" || is_spectral_unit(k);
+}
+// chunkSize of a frame-family unit's outlet (the option its constructor passes to addOutlet)
+long long frame_out_size(const GUnit &u) {
+  const std::string &k = u.kind;
+  if (k == "Hopper") return (long long)u.num("frameSize", 0);
+  if (k == "Windower" || k == "IFFT") return (long long)u.num("windowSize", 0);
+  if (k == "FFT") return 2 * (long long)u.num("windowSize", 0);
+  if (k == "UnHopper") return (long long)u.num("hopSize", 0);
+  if (k == "ReChunk") return (long long)u.num("outputInterval", 0);
+  return 2 * (long long)u.num("windowSize", 4096);
+}
+// does inlet `i` of a frame-family unit read a whole frame (as opposed to a standard 256-sample chunk)?
+bool is_frame_inlet(const GUnit &u, int i) {
+  if (!is_frame_kind(u.kind) || u.kind == "Hopper") return false;
+  if (u.kind == "SpectralSum") return i < 2;
+  return i == 0;
+}
+
 // How many channels of outlet 0 a unit's _tick writes / grows to, given the
 // channel counts it sees (the `out[c] = out[c] || new Float32Array` lines).
 int written_channels(const Graph &g, const std::vector<std::vector<int>> &n, int ui, const Builder &b) {
@@ -235,6 +260,53 @@ Program compile(const Graph &g) {
       for (int u = NU - 1; u >= 0; u--) if (g.units[u].has("buffer") && (size_t)g.units[u].num("buffer", -1) == bi) owner = u;
       cb_ring[{(int)bi, c}] = b.ring(g.cbs[bi].len, Builder::uname(owner) + ".cb[" + std::to_string(c) + "]");
     }
+  // ---- frame-rate units: every frame outlet is a per-voice ring that keeps its content between the unit's ticks
+  std::map<int, int> frame_ring;  // unit -> ring of its outlet 0
+  bool has_frames = false;
+  for (int ui : g.order) {
+    const GUnit &u = g.units[ui];
+    if (!is_frame_kind(u.kind)) continue;
+    has_frames = true;
+    const long long n = frame_out_size(u);
+    if (n < 1 || n > (1 << 20)) throw Unsupported("unit " + u.kind + " with a frame of " + std::to_string(n) + " samples");
+    const long long ti = (long long)u.num("tickInterval", DUSP_CHUNK);
+    if (ti < DUSP_CHUNK || ti % DUSP_CHUNK)
+      throw Unsupported("unit " + u.kind + " ticks every " + std::to_string(ti) + " samples: only multiples of the 256-sample chunk run on the device");
+    frame_ring[ui] = b.ring(n, Builder::uname(ui) + ".frame");
+  }
+  if (has_frames) {
+    b.prog.chunk_tiles = true;
+    // a standard inlet (or a frame unit's control inlet) wired to a frame outlet reads its first 256 samples
+    for (int ui : g.order) {
+      const GUnit &u = g.units[ui];
+      for (size_t i = 0; i < u.in.size(); i++) {
+        const GPort &p = u.in[i];
+        if (!p.connected || p.nodata || !frame_ring.count(p.src_unit) || is_frame_inlet(u, (int)i)) continue;
+        if (frame_out_size(g.units[p.src_unit]) != DUSP_CHUNK)
+          throw Unsupported("standard inlet " + u.label + "." + p.name + " wired to a " + std::to_string(frame_out_size(g.units[p.src_unit])) +
+                            "-sample frame outlet (chunk size mismatch; put a ReChunk in between)");
+      }
+    }
+  }
+  auto ctab_put = [&](const std::vector<double> &v) {
+    const int off = (int)b.prog.ctab.size();
+    b.prog.ctab.insert(b.prog.ctab.end(), v.begin(), v.end());
+    return off;
+  };
+  std::map<long long, int> twiddle_at, envelope_at;
+  auto twiddles = [&](long long size) {  // fft.js constructor: table[i] = cos(pi i / size), table[i+1] = -sin(pi i / size)
+    if (twiddle_at.count(size)) return twiddle_at[size];
+    std::vector<double> t((size_t)size * 2);
+    for (long long i = 0; i < size * 2; i += 2) { const double a = M_PI * (double)i / (double)size; t[i] = std::cos(a); t[i + 1] = -std::sin(a); }
+    return twiddle_at[size] = ctab_put(t);
+  };
+  auto envelope = [&](long long size) {  // Windower.js:28-47 ("hamming": sin^2), values as the Float32Array holds them
+    if (envelope_at.count(size)) return envelope_at[size];
+    std::vector<double> t((size_t)size);
+    for (long long n = 0; n < size; n++) t[n] = (double)(float)std::pow(std::sin((M_PI * (double)n) / (double)(size - 1)), 2);
+    return envelope_at[size] = ctab_put(t);
+  };
+
   struct Tap { int unit; bool writer; Opnd off; int ir; };
   std::map<int, std::vector<Tap>> taps;  // ring -> taps (for the reordering check)
 
@@ -517,6 +589,105 @@ Program compile(const Graph &g) {
         taps[r.aux[0]].push_back({ui, writer || r.aux[1] != 0, r.in[0], (int)b.ir.size() - 1});
         b.prog.ring_bytes_per_sample += writer ? (r.aux[1] ? 4 : 8) : (r.aux[1] ? 8 : 4);
       }
+    } else if (is_frame_kind(k)) {
+      // SURVEY 8f-3.  Channel 0 of every port is the Float32Array its SignalChunk was built with; further channels
+      // would be untyped Arrays (`out[c] = out[c] || new Array(n)`: doubles) -- refused, not approximated.
+      const int gate = (int)u.num("tickInterval", DUSP_CHUNK);
+      // ring holding the frame that frame inlet `i` reads (`need` samples)
+      auto frame_in = [&](int i, long long need) {
+        if ((int)u.in.size() <= i) throw std::runtime_error("unit " + k + " has too few ports in graph blob");
+        const GPort &p = u.in[i];
+        if (!p.connected) throw Unsupported("frame inlet " + u.label + "." + p.name + " is not connected");
+        if (b.nch[p.src_unit][p.src_outlet] != 1) throw Unsupported("multi-channel signal into " + k + " (extra channels of the spectral units are untyped Arrays)");
+        if (frame_ring.count(p.src_unit)) {
+          if (frame_out_size(g.units[p.src_unit]) < need)
+            throw Unsupported("frame inlet " + u.label + "." + p.name + " is fed by a shorter chunk (the reference reads undefined)");
+          return frame_ring[p.src_unit];
+        }
+        if (need > DUSP_CHUNK) throw Unsupported("frame inlet " + u.label + "." + p.name + " is fed by a standard 256-sample outlet (the reference reads undefined)");
+        const int r = b.ring(DUSP_CHUNK, un + ".in" + std::to_string(i));
+        IR &st = b.emit(OP_STFRAME, ui, 0); st.in[0] = b.in_ref(ui, i, 0); st.aux[0] = r; st.root = true;
+        return r;
+      };
+      auto gated = [&](int op) -> IR & { IR &r = b.emit(op, ui, 0); r.root = true; r.in[4].kind = 3; r.in[4].id = gate; return r; };
+      auto pow2 = [](long long n) { return n > 1 && (n & (n - 1)) == 0; };
+      if (k == "Hopper") {
+        need_in(1);
+        if (inn(0) != 1) throw Unsupported("multi-channel signal into Hopper (extra channels of the spectral units are untyped Arrays)");
+        if (gate != DUSP_CHUNK) throw Unsupported("Hopper whose hop is not a multiple of 256 samples");
+        const long long frame = (long long)u.num("frameSize", 0), hop = (long long)u.num("hopSize", 0);
+        const int buf = b.ring(frame, un + ".buffer");
+        IR &r = gated(OP_HOPPER);
+        r.in[0] = b.in_ref(ui, 0, 0);
+        r.aux[0] = buf; r.aux[1] = frame_ring[ui]; r.aux[2] = (int)hop;
+        r.p = b.word(un + ".t", u.num("t", 0), false);
+      } else if (k == "Windower") {
+        const long long win = (long long)u.num("windowSize", 0);
+        if (u.str("windowKind", "hamming") != "hamming") throw std::runtime_error("Window type '" + u.str("windowKind", "") + "' is not defined.");
+        const int in = frame_in(0, win);
+        IR &r = gated(OP_WINDOW);
+        r.aux[0] = in; r.aux[1] = frame_ring[ui]; r.aux[2] = envelope(win);
+      } else if (k == "FFT") {
+        const long long win = (long long)u.num("windowSize", 0);
+        if (!pow2(win)) throw std::runtime_error("FFT size must be a power of two and bigger than 1");
+        const int in = frame_in(0, win);
+        IR &r = gated(OP_FFT);
+        r.aux[0] = in; r.aux[1] = frame_ring[ui]; r.aux[2] = twiddles(win);
+      } else if (k == "IFFT") {
+        const long long win = (long long)u.num("windowSize", 0);
+        if (!pow2(win)) throw std::runtime_error("FFT size must be a power of two and bigger than 1");
+        const int in = frame_in(0, 2 * win);
+        const int cplx = b.ring(4 * win, un + ".complexOut");  // 2*win doubles
+        IR &r = gated(OP_IFFT);
+        r.aux[0] = in; r.aux[1] = frame_ring[ui]; r.aux[2] = twiddles(win);
+        r.in[0].kind = 3; r.in[0].id = cplx;
+      } else if (k == "UnHopper") {
+        const long long win = (long long)u.num("windowSize", 0), hop = (long long)u.num("hopSize", 0);
+        if (hop > win) throw Unsupported("UnHopper with a hop longer than its window");
+        const int in = frame_in(0, win);
+        const int acc = b.ring(2 * win, un + ".buffer");  // win doubles
+        IR &r = gated(OP_UNHOP);
+        r.aux[0] = in; r.aux[1] = frame_ring[ui]; r.aux[2] = acc;
+        r.p = b.word(un + ".t", u.num("t", 0), false);
+      } else if (k == "ReChunk") {
+        const long long ii = (long long)u.num("inputInterval", 0), oi = (long long)u.num("outputInterval", 0);
+        const long long bs = (long long)u.num("bufferSize", 0);
+        if (ii < 1 || oi < 1 || bs < 1) throw std::runtime_error("ReChunk expects 2 numeric contructor arguments");
+        const int in = frame_in(0, ii);
+        const int buf = b.ring(bs, un + ".buffer");
+        IR &r = gated(OP_RECHUNK);
+        r.aux[0] = in; r.aux[1] = frame_ring[ui]; r.aux[2] = buf;
+        r.in[0].kind = 3; r.in[0].id = (int)ii; r.in[1].kind = 3; r.in[1].id = (int)oi;
+        r.p = b.word(un + ".t", u.num("t", 0), false);
+      } else {
+        const long long frame = 2 * (long long)u.num("windowSize", 4096);
+        const int in = frame_in(0, frame);
+        if (k == "SpectralSum") {
+          const int in_b = frame_in(1, frame);
+          IR &r = gated(OP_SPECSUM);
+          r.aux[0] = in; r.aux[1] = frame_ring[ui]; r.aux[2] = in_b;
+        } else if (k == "Augment") {
+          IR &r = gated(OP_AUGMENT);
+          const int n = (int)u.num("nmap", 0);
+          r.aux[0] = in; r.aux[1] = frame_ring[ui]; r.aux[2] = n;
+          for (int m = 0; m < n; m++) {
+            const int w = b.word(un + ".ratio" + std::to_string(m), u.num("ratio" + std::to_string(m), 1), false);
+            b.word(un + ".gain" + std::to_string(m), u.num("gain" + std::to_string(m), 1), false);
+            if (m == 0) r.p = w;
+          }
+        } else {
+          need_in(2);
+          IR &r = gated(k == "SpectralGate" ? OP_SPECGATE : k == "BinShift" ? OP_BINSHIFT : OP_SPECPASS);
+          r.in[0] = b.in_ref(ui, 1, 0);
+          r.aux[0] = in; r.aux[1] = frame_ring[ui];
+          r.aux[2] = k == "SpectralGate" ? (int)u.num("invert", 1) : k == "HardHighPass" ? 1 : 0;
+        }
+      }
+      // a 256-sample frame outlet can feed standard units: their slots are loaded from the ring every chunk
+      if (frame_out_size(u) == DUSP_CHUNK) {
+        IR &ld = b.emit(OP_LDFRAME, ui, 0); ld.aux[0] = frame_ring[ui];
+        b.def(ld, 0, ui, 0, 0);
+      }
     } else {
       throw Unsupported("unit kind " + k + " is outside the accelerated render path");
     }
@@ -612,6 +783,18 @@ Program compile(const Graph &g) {
   std::vector<IR> outs;
   for (int c = 0; c < out_nch; c++) {
     IR r; r.op = OP_OUT; r.unit = g.root_unit; r.chan = c; r.aux[0] = c; r.root = true;
+    if (frame_ring.count(g.root_unit) && frame_out_size(g.units[g.root_unit]) != DUSP_CHUNK) {
+      // renderChannelData.js:25-45 copies outlet.chunkSize samples after every tickUntil(t0 + chunkSize).  A unit that
+      // ticks once per such span (at its start) leaves the whole span in its outlet, so each 256-sample chunk can be
+      // stored as soon as it is reached.
+      const GUnit &ru = g.units[g.root_unit];
+      const long long cs = frame_out_size(ru), ti = (long long)ru.num("tickInterval", DUSP_CHUNK);
+      if (cs % DUSP_CHUNK || ti % cs) throw Unsupported("rendered outlet has chunks of " + std::to_string(cs) + " samples but its unit ticks every " + std::to_string(ti));
+      r.op = OP_OUTRING; r.aux[1] = frame_ring[g.root_unit]; r.aux[2] = (int)cs;
+      r.pos = 1 << 29;
+      outs.push_back(r);
+      continue;
+    }
     auto it = b.valmap.find(std::make_tuple(g.root_unit, g.root_outlet, c));
     if (it != b.valmap.end() && b.vals[it->second].def >= 0) { r.in[0].kind = 1; r.in[0].id = it->second; }
     r.pos = 1 << 29;
@@ -740,7 +923,7 @@ Program compile(const Graph &g) {
     std::memset(&di, 0, sizeof di);
     di.op = r.op;
     for (int k = 0; k < 5; k++)
-      di.in[k] = r.in[k].kind == 1 ? slot_of[r.in[k].id] : r.in[k].kind == 2 ? ref_const(r.in[k].id) : REF_NONE;
+      di.in[k] = r.in[k].kind == 1 ? slot_of[r.in[k].id] : r.in[k].kind == 2 ? ref_const(r.in[k].id) : r.in[k].kind == 3 ? r.in[k].id : REF_NONE;
     for (int k = 0; k < 2; k++) di.out[k] = r.outv[k] >= 0 ? slot_of[r.outv[k]] : REF_NONE;
     di.p = r.p;
     for (int k = 0; k < 3; k++) di.aux[k] = r.aux[k];

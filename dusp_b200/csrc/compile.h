@@ -43,7 +43,8 @@ struct Derived {
 struct Program {
   std::vector<DuspInstr> code;
   std::vector<Param> words;     // per-voice words: parameters and unit state, in instruction order
-  std::vector<DuspRing> rings;  // per-voice delay lines / CircleBuffer channels
+  std::vector<DuspRing> rings;  // per-voice delay lines / CircleBuffer channels / frames of the spectral units
+  std::vector<double> ctab;     // program constants evaluated on the host with libm (FFT twiddles, window envelopes)
   // identities across graph edits (dusp_session_adopt): "<Kind>:<label>" per blob unit; rings and stale buffers
   // are named "u<unit>.<what>" like the words
   std::vector<std::string> unit_labels, ring_names, stale_names;

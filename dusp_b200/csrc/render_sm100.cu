@@ -716,6 +716,290 @@ __device__ __forceinline__ void op_cbtapc(const Lane<B, T> &L, const DuspDevInst
   if (!writer) L.st(x, I.out[0]);
 }
 
+
+// ------------------------------------------------- frame-rate units (components/spectral)
+// Whole-chunk tiles only (B = 8, T = 32: one voice per warp, one 256-sample chunk per tile).  Frames are per-voice
+// rings that persist between a unit's ticks; the 32 lanes share every loop and meet at __syncwarp between passes.
+// Kept out of line so that the register allocation of the sample-rate ops above is unaffected.
+struct FrameCtx {
+  float *rings;
+  const DuspRing *ring_tab;
+  double *W;
+  unsigned nv;
+  int lane;
+  const double *ctab;
+  __device__ __forceinline__ float *ring(int r, int &len) const { const DuspRing rt = ring_tab[r]; len = (int)rt.length; return rings + rt.offset; }
+  __device__ __forceinline__ double &w(int p) const { return W[(size_t)((unsigned)p * nv)]; }
+};
+
+// fft.js (the package FFT.js:2 / IFFT.js:2 require; not part of the reference tree): radix-4 passes exactly as the
+// oracle restates them (oracle/dusp_oracle.c), one butterfly per lane per step.  Every butterfly of a pass reads and
+// writes elements no other butterfly of that pass writes, so the order inside a pass is free; arithmetic is the
+// same f64 sequence (no contraction), stores round to the storage type like the JS array they model.
+__device__ __forceinline__ int fft_bitrev(int j, int width) {
+  int r = 0;
+  for (int shift = 0; shift < width; shift += 2) { const int rev = width - shift - 2; if (rev >= 0) r |= ((j >> shift) & 3) << rev; }
+  return r;
+}
+__device__ __forceinline__ int fft_width(int size) {
+  int power = 0;
+  for (int t = 1; size > t; t <<= 1) power++;
+  return power % 2 == 0 ? power - 1 : power;
+}
+template <typename ST>
+__device__ __forceinline__ void fft_butterfly(ST *out, const double *__restrict__ table, int A, int quarterLen, int k, double inv,
+                                              double &T0r, double &T0i, double &T1r, double &T1i, double &T2r, double &T2i, double &T3r, double &T3i) {
+  const int Bq = A + quarterLen, C = Bq + quarterLen, D = C + quarterLen;
+  const double Ar = (double)out[A], Ai = (double)out[A + 1], Br = (double)out[Bq], Bi = (double)out[Bq + 1];
+  const double Cr = (double)out[C], Ci = (double)out[C + 1], Dr = (double)out[D], Di = (double)out[D + 1];
+  const double tableBr = __ldg(table + k), tableBi = inv * __ldg(table + k + 1);
+  const double MBr = Br * tableBr - Bi * tableBi, MBi = Br * tableBi + Bi * tableBr;
+  const double tableCr = __ldg(table + 2 * k), tableCi = inv * __ldg(table + 2 * k + 1);
+  const double MCr = Cr * tableCr - Ci * tableCi, MCi = Cr * tableCi + Ci * tableCr;
+  const double tableDr = __ldg(table + 3 * k), tableDi = inv * __ldg(table + 3 * k + 1);
+  const double MDr = Dr * tableDr - Di * tableDi, MDi = Dr * tableDi + Di * tableDr;
+  T0r = Ar + MCr; T0i = Ai + MCi; T1r = Ar - MCr; T1i = Ai - MCi;
+  T2r = MBr + MDr; T2i = MBi + MDi; T3r = inv * (MBr - MDr); T3i = inv * (MBi - MDi);
+}
+// _transform4 with this._inv = 1 (inverseTransform), `data` = interleaved complex input
+template <typename ST>
+__device__ __noinline__ void fft_inverse(ST *out, const float *data, const double *__restrict__ table, int n, int lane) {
+  const int size = n << 1, width = fft_width(n);
+  int step = 1 << width, len = (size / step) << 1;
+  const double inv = -1.0;
+  const int nblk = size / len;
+  if (len == 4) {
+    for (int t = lane; t < nblk; t += 32) {
+      const int outOff = t * len, off = fft_bitrev(t, width);
+      const double evenR = data[off], evenI = data[off + 1], oddR = data[off + step], oddI = data[off + step + 1];
+      out[outOff] = (ST)(evenR + oddR); out[outOff + 1] = (ST)(evenI + oddI); out[outOff + 2] = (ST)(evenR - oddR); out[outOff + 3] = (ST)(evenI - oddI);
+    }
+  } else {
+    for (int t = lane; t < nblk; t += 32) {
+      const int outOff = t * len, off = fft_bitrev(t, width), step2 = step * 2, step3 = step * 3;
+      const double Ar = data[off], Ai = data[off + 1], Br = data[off + step], Bi = data[off + step + 1];
+      const double Cr = data[off + step2], Ci = data[off + step2 + 1], Dr = data[off + step3], Di = data[off + step3 + 1];
+      const double T0r = Ar + Cr, T0i = Ai + Ci, T1r = Ar - Cr, T1i = Ai - Ci;
+      const double T2r = Br + Dr, T2i = Bi + Di, T3r = inv * (Br - Dr), T3i = inv * (Bi - Di);
+      out[outOff] = (ST)(T0r + T2r); out[outOff + 1] = (ST)(T0i + T2i); out[outOff + 2] = (ST)(T1r + T3i); out[outOff + 3] = (ST)(T1i - T3r);
+      out[outOff + 4] = (ST)(T0r - T2r); out[outOff + 5] = (ST)(T0i - T2i); out[outOff + 6] = (ST)(T1r - T3i); out[outOff + 7] = (ST)(T1i + T3r);
+    }
+  }
+  __syncwarp();
+  for (step >>= 2; step >= 2; step >>= 2) {
+    len = (size / step) << 1;
+    const int quarterLen = len >> 2, per = quarterLen >> 1, total = size >> 3;
+#pragma unroll 1
+    for (int idx = lane; idx < total; idx += 32) {
+      const int blk = idx / per, j = idx - blk * per;
+      const int A = blk * len + 2 * j, k = j * step;
+      double T0r, T0i, T1r, T1i, T2r, T2i, T3r, T3i;
+      fft_butterfly(out, table, A, quarterLen, k, inv, T0r, T0i, T1r, T1i, T2r, T2i, T3r, T3i);
+      const int Bq = A + quarterLen, C = Bq + quarterLen, D = C + quarterLen;
+      out[A] = (ST)(T0r + T2r); out[A + 1] = (ST)(T0i + T2i); out[Bq] = (ST)(T1r + T3i); out[Bq + 1] = (ST)(T1i - T3r);
+      out[C] = (ST)(T0r - T2r); out[C + 1] = (ST)(T0i - T2i); out[D] = (ST)(T1r - T3i); out[D + 1] = (ST)(T1i + T3r);
+    }
+    __syncwarp();
+  }
+}
+// realTransform + completeSpectrum, `data` = n reals
+template <typename ST>
+__device__ __noinline__ void fft_real(ST *out, const float *data, const double *__restrict__ table, int n, int lane) {
+  const int size = n << 1, width = fft_width(n);
+  int step = 1 << width, len = (size / step) << 1;
+  const double inv = 1.0;
+  const int nblk = size / len;
+  if (len == 4) {
+    for (int t = lane; t < nblk; t += 32) {
+      const int outOff = t * len, off = fft_bitrev(t, width) >> 1, st = step >> 1;
+      const double evenR = data[off], oddR = data[off + st];
+      out[outOff] = (ST)(evenR + oddR); out[outOff + 1] = (ST)0.0; out[outOff + 2] = (ST)(evenR - oddR); out[outOff + 3] = (ST)0.0;
+    }
+  } else {
+    for (int t = lane; t < nblk; t += 32) {
+      const int outOff = t * len, off = fft_bitrev(t, width) >> 1, st = step >> 1;
+      const double Ar = data[off], Br = data[off + st], Cr = data[off + 2 * st], Dr = data[off + 3 * st];
+      const double T0r = Ar + Cr, T1r = Ar - Cr, T2r = Br + Dr, T3r = inv * (Br - Dr);
+      out[outOff] = (ST)(T0r + T2r); out[outOff + 1] = (ST)0.0; out[outOff + 2] = (ST)T1r; out[outOff + 3] = (ST)(-T3r);
+      out[outOff + 4] = (ST)(T0r - T2r); out[outOff + 5] = (ST)0.0; out[outOff + 6] = (ST)T1r; out[outOff + 7] = (ST)T3r;
+    }
+  }
+  __syncwarp();
+  for (step >>= 2; step >= 2; step >>= 2) {
+    len = (size / step) << 1;
+    const int halfLen = len >> 1, quarterLen = halfLen >> 1, hquarterLen = quarterLen >> 1;
+    const int per = (hquarterLen >> 1) + 1, total = (size / len) * per;
+#pragma unroll 1
+    for (int idx = lane; idx < total; idx += 32) {
+      const int blk = idx / per, j = idx - blk * per;
+      const int outOff = blk * len, i = 2 * j, A = outOff + i, k = j * step;
+      double T0r, T0i, T1r, T1i, T2r, T2i, T3r, T3i;
+      fft_butterfly(out, table, A, quarterLen, k, inv, T0r, T0i, T1r, T1i, T2r, T2i, T3r, T3i);
+      const int Bq = A + quarterLen, C = Bq + quarterLen;
+      out[A] = (ST)(T0r + T2r); out[A + 1] = (ST)(T0i + T2i); out[Bq] = (ST)(T1r + T3i); out[Bq + 1] = (ST)(T1i - T3r);
+      if (i == 0) { out[C] = (ST)(T0r - T2r); out[C + 1] = (ST)(T0i - T2i); continue; }
+      if (i == hquarterLen) continue;
+      const double ST0r = T1r, ST0i = -T1i, ST1r = T0r, ST1i = -T0i;
+      const double ST2r = -inv * T3i, ST2i = -inv * T3r, ST3r = -inv * T2i, ST3i = -inv * T2r;
+      const int SA = outOff + quarterLen - i, SB = outOff + halfLen - i;
+      out[SA] = (ST)(ST0r + ST2r); out[SA + 1] = (ST)(ST0i + ST2i); out[SB] = (ST)(ST1r + ST3i); out[SB + 1] = (ST)(ST1i - ST3r);
+    }
+    __syncwarp();
+  }
+  const int half = size >> 1;  // completeSpectrum
+  for (int i = 2 + 2 * lane; i < half; i += 64) { out[size - i] = out[i]; out[size - i + 1] = (ST)(-(double)out[i + 1]); }
+  __syncwarp();
+}
+
+__device__ __forceinline__ double js_round_d(double x) { return floor(x + 0.5); }  // Math.round
+
+// `x0`: sample 0 of the op's control inlet (f / threshold / shift), already broadcast to every lane
+__device__ __noinline__ void frame_op(const FrameCtx &F, const DuspDevInstr &I, const float (&x)[8], double x0) {
+  const int lane = F.lane;
+  int n_in, n_out;
+  switch (I.op) {
+    case OP_HOPPER: {  // Hopper.js:19-37 (tickInterval 256: the whole input chunk enters the circular buffer)
+      float *buf = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      long long t = (long long)F.w(I.p);
+      const int frame = n_in;
+#pragma unroll
+      for (int s = 0; s < 8; s++) buf[(int)((t + lane * 8 + s) % frame)] = x[s];
+      t += DUSP_CHUNK;
+      __syncwarp();
+      if (t % I.aux2 == 0) {
+        const int rot = (int)(t % frame);
+        for (int i = lane; i < frame; i += 32) { int j = i + rot; if (j >= frame) j -= frame; out[i] = buf[j]; }
+      }
+      if (lane == 0) F.w(I.p) = (double)t;
+      break;
+    }
+    case OP_WINDOW: {  // Windower.js:17-23: one binary32 product per sample
+      const float *in = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      const double *env = F.ctab + I.aux2;
+      for (int i = lane; i < n_out; i += 32) out[i] = __fmul_rn(in[i], (float)__ldg(env + i));
+      break;
+    }
+    case OP_FFT: {  // FFT.js:19-25, into the outlet's Float32Array
+      const float *in = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      fft_real<float>(out, in, F.ctab + I.aux2, n_out >> 1, lane);
+      break;
+    }
+    case OP_IFFT: {  // IFFT.js:21-33, through the untyped (f64) complexOut
+      const float *in = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      int nc;
+      double *cplx = reinterpret_cast<double *>(F.ring(I.in[0], nc));
+      const int n = n_out;
+      fft_inverse<double>(cplx, in, F.ctab + I.aux2, n, lane);
+      const double size = (double)n;
+      for (int i = lane; i < 2 * n; i += 32) cplx[i] = cplx[i] / size;
+      __syncwarp();
+      for (int t = lane; t < n; t += 32) out[t] = (float)cplx[2 * t];
+      break;
+    }
+    case OP_UNHOP: {  // UnHopper.js:19-44
+      const float *in = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      int na;
+      double *acc = reinterpret_cast<double *>(F.ring(I.aux2, na));
+      const int win = na >> 1, hop = n_out;
+      long long t = (long long)F.w(I.p);
+      const int rot = (int)(t % win);
+      for (int i = lane; i < win; i += 32) { int j = i + rot; if (j >= win) j -= win; acc[j] += (double)in[i]; }
+      t += hop;
+      __syncwarp();
+      if (t > hop) {
+        const int r0 = (int)((t - hop) % win);
+        for (int i = lane; i < hop; i += 32) { int j = (r0 + i) % win; out[i] = (float)acc[j]; acc[j] = 0.0; }
+      }
+      if (lane == 0) F.w(I.p) = (double)t;
+      break;
+    }
+    case OP_RECHUNK: {  // ReChunk.js:26-49
+      const float *in = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      int bs;
+      float *buf = F.ring(I.aux2, bs);
+      const int ii = I.in[0], oi = I.in[1];
+      long long t = (long long)F.w(I.p);
+      if (t % ii == 0) {
+        const int rot = (int)(t % bs);
+        for (int i = lane; i < ii; i += 32) buf[(rot + i) % bs] = in[i];
+      }
+      t += I.in[4];
+      __syncwarp();
+      if (t % oi == 0) {
+        const int r0 = (int)((t - oi) % bs);
+        for (int i = lane; i < oi; i += 32) out[i] = buf[(r0 + i) % bs];
+      }
+      if (lane == 0) F.w(I.p) = (double)t;
+      break;
+    }
+    case OP_SPECPASS: {  // HardLowPass.js:20-31 / HardHighPass.js:20-31
+      const float *in = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      const double cut = js_round_d(x0 / (SRD / (double)(n_out >> 1))) * 2.0;
+      if (cut != cut) break;  // NaN: neither loop of the reference runs, the outlet keeps its frame
+      const bool high = I.aux2 != 0;
+      for (int i = lane; i < n_out; i += 32) out[i] = (((double)i < cut) != high) ? in[i] : 0.0f;
+      break;
+    }
+    case OP_SPECGATE: {  // SpectralGate.js:15-32
+      const float *in = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      const bool invert = I.aux2 != 0;
+      for (int b = 2 * lane; b < n_out; b += 64) {
+        const double re = in[b], im = in[b + 1], mag = sqrt(re * re + im * im);
+        const bool keep = invert ? mag < x0 : mag > x0;
+        out[b] = keep ? in[b] : 0.0f; out[b + 1] = keep ? in[b + 1] : 0.0f;
+      }
+      break;
+    }
+    case OP_BINSHIFT: {  // BinShift.js:14-26: out[bin + shift] = in[bin] for every bin that lands inside the frame
+      const float *in = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      const double shift = js_round_d(x0) * 2.0;
+      for (int d = 2 * lane; d < n_out; d += 64) {  // d = destination of the real part (bin + shift - 1)
+        const double src = (double)d - shift;       // source real index (bin - 1), bin odd >= 1
+        const bool ok = shift == shift && src >= 0.0 && src + 1.0 < (double)n_out;
+        out[d] = ok ? in[(int)src] : 0.0f; out[d + 1] = ok ? in[(int)src + 1] : 0.0f;
+      }
+      break;
+    }
+    case OP_AUGMENT: {  // Augment.js:14-27: sequential `+=` into a Float32Array; lane 0 keeps the reference's order
+      const float *in = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      for (int i = lane; i < n_out; i += 32) out[i] = 0.0f;
+      __syncwarp();
+      if (lane == 0) {
+        const int win = n_out >> 1;
+        for (int bin = 0; bin < win; bin++)
+          for (int m = 0; m < I.aux2; m++) {
+            const double b2 = js_round_d((double)bin * F.w(I.p + 2 * m)) * 2.0, g = F.w(I.p + 2 * m + 1);
+            if (!(b2 >= 0.0 && b2 < (double)n_out)) continue;
+            const int d = (int)b2;
+            out[d] = (float)((double)out[d] + (double)in[bin * 2] * g);
+            out[d + 1] = (float)((double)out[d + 1] + (double)in[bin * 2 + 1] * g);
+          }
+      }
+      break;
+    }
+    case OP_SPECSUM: {  // SpectralSum.js:15-24
+      const float *a = F.ring(I.aux0, n_in);
+      float *out = F.ring(I.aux1, n_out);
+      int nb;
+      const float *b = F.ring(I.aux2, nb);
+      for (int i = lane; i < n_out; i += 32) out[i] = __fadd_rn(a[i], b[i]);
+      break;
+    }
+    default: break;
+  }
+  __syncwarp();
+}
+
 // --------------------------------------------------------------- the kernel
 // registers are capped so that at least 16 (B=8) / 8 (B=16) warps are resident per SM
 template <int B, int T>
@@ -887,9 +1171,48 @@ __global__ void __launch_bounds__(128, B <= 8 ? 4 : 2) dusp_render_tile(const __
           for (int q = 0; q < B / 4; q++) dst[q] = make_float4(x[4 * q], x[4 * q + 1], x[4 * q + 2], x[4 * q + 3]);
           break;
         }
-        case OP_OUT: {  // renderChannelData.js:42-44
+        case OP_HOPPER: case OP_WINDOW: case OP_FFT: case OP_IFFT: case OP_UNHOP: case OP_RECHUNK: case OP_SPECPASS:
+        case OP_SPECGATE: case OP_BINSHIFT: case OP_AUGMENT: case OP_SPECSUM: {
+          if constexpr (B == 8 && T == 32) {
+            const long long clock = kp.clock0 + tile;
+            if (I.in[4] > 0 && clock % I.in[4] != 0) break;  // Circuit.js:35
+            float x[8];
+            double x0 = 0.0;
+            const bool ctl = I.op == OP_HOPPER || I.op == OP_SPECPASS || I.op == OP_SPECGATE || I.op == OP_BINSHIFT;
+            if (ctl) { L.ld(x, I.in[0]); x0 = (double)__shfl_sync(0xffffffffu, x[0], 0); }
+            FrameCtx F;
+            F.rings = L.rings; F.ring_tab = L.ring_tab; F.W = L.W; F.nv = L.nv; F.lane = lane; F.ctab = kp.ctab;
+            frame_op(F, I, x, x0);
+          }
+          break;
+        }
+        case OP_LDFRAME: {  // a standard unit reads the 256-sample chunk a frame-rate unit left in its outlet
+          float x[B];
+          long long n;
+          const float4 *src = reinterpret_cast<const float4 *>(L.ring(I.aux0, n) + cpos);
+#pragma unroll
+          for (int q = 0; q < B / 4; q++) { const float4 t = src[q]; x[4 * q] = t.x; x[4 * q + 1] = t.y; x[4 * q + 2] = t.z; x[4 * q + 3] = t.w; }
+          L.st(x, I.out[0]);
+          break;
+        }
+        case OP_STFRAME: {
           float x[B];
           L.ld(x, I.in[0]);
+          long long n;
+          float4 *dst = reinterpret_cast<float4 *>(L.ring(I.aux0, n) + cpos);
+#pragma unroll
+          for (int q = 0; q < B / 4; q++) dst[q] = make_float4(x[4 * q], x[4 * q + 1], x[4 * q + 2], x[4 * q + 3]);
+          L.sync();
+          break;
+        }
+        case OP_OUT: case OP_OUTRING: {  // renderChannelData.js:42-44
+          float x[B];
+          if (I.op == OP_OUTRING) {  // outlet.chunkSize = aux2 > 256: this chunk's part of the frame the unit left behind
+            long long n;
+            const float4 *src = reinterpret_cast<const float4 *>(L.ring(I.aux1, n) + (int)((kp.clock0 + tl0) % I.aux2));
+#pragma unroll
+            for (int q = 0; q < B / 4; q++) { const float4 t = src[q]; x[4 * q] = t.x; x[4 * q + 1] = t.y; x[4 * q + 2] = t.z; x[4 * q + 3] = t.w; }
+          } else L.ld(x, I.in[0]);
 if (!kp.out_raw) {
 #pragma unroll
             for (int s = 0; s < B; s++) x[s] = js_or0f(x[s]);

@@ -75,6 +75,23 @@ enum DuspOp : int32_t {
   OP_POKEIF,    // the assignments of target.trigger(): if word aux0 != 0 then word p = word aux1
   OP_SRREDUX,   // SampleRateRedux.js:20-37    in0=in in1=ammount [p: timeSinceLastUpdate, val]  (per channel; each keeps
                 //                              its own copy of the shared counter, which only depends on `ammount`)
+  // --- frame-rate units (components/spectral).  Frames live in per-voice rings (persistent, like the
+  //     SignalChunk a slow unit leaves behind between its ticks); whole-chunk tiles only; in[4] = tick interval in
+  //     samples (Circuit.js:35: the op runs when clock % interval == 0)
+  OP_HOPPER,    // Hopper.js:19-37        in0=in  aux0=buffer ring aux1=out ring aux2=hopSize [p: t]
+  OP_WINDOW,    // Windower.js:17-23      aux0=in ring aux1=out ring aux2=ctab offset of the envelope
+  OP_FFT,       // FFT.js:19-25           aux0=in ring aux1=out ring aux2=ctab offset of the twiddle table
+  OP_IFFT,      // IFFT.js:21-33          aux0=in ring aux1=out ring aux2=ctab offset, in0=complexOut ring (f64)
+  OP_UNHOP,     // UnHopper.js:19-44      aux0=in ring aux1=out ring aux2=accumulator ring (f64) [p: t]
+  OP_RECHUNK,   // ReChunk.js:26-49       aux0=in ring aux1=out ring aux2=buffer ring, in0=inputInterval in1=outputInterval [p: t]
+  OP_SPECPASS,  // HardLowPass.js:20-31 / HardHighPass.js:20-31   in0=f aux0=in ring aux1=out ring aux2=high
+  OP_SPECGATE,  // SpectralGate.js:15-32  in0=threshold aux0=in ring aux1=out ring aux2=invert
+  OP_BINSHIFT,  // BinShift.js:14-26      in0=shift aux0=in ring aux1=out ring
+  OP_AUGMENT,   // Augment.js:14-27       aux0=in ring aux1=out ring aux2=entries [p: ratio0, gain0, ratio1, ...]
+  OP_SPECSUM,   // SpectralSum.js:15-24   aux0=a ring aux1=out ring aux2=b ring
+  OP_LDFRAME,   // slot <- first 256 samples of a frame ring (a standard unit reading a 256-sample frame outlet)
+  OP_STFRAME,   // frame ring <- slot (a frame inlet fed by a standard outlet)
+  OP_OUTRING,   // renderChannelData.js:25-45 with outlet.chunkSize = aux2 > 256: out[aux0][t] = ring aux1 [t % aux2] || 0
   OP_COUNT
 };
 
@@ -154,6 +171,7 @@ struct DuspKernelParams {
   int64_t out_len;       // samples per channel row in `out`
   int64_t clock0;        // absolute sample index of the first sample of this launch (multiple of 256)
   int64_t n_samples;     // samples to store (<= processed); processing covers whole chunks
+  const double *ctab;    // program constants built on the host with libm: FFT twiddles, window envelopes (f64)
   const DuspDevInstr *prog_global;
   const DuspWarpDesc *multi;  // non-null: n_voices descriptors, one per warp (requires T = 32)
   DuspDevInstr prog_inline[DUSP_INLINE_INSTR];

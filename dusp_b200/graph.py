@@ -43,8 +43,8 @@ class Piglet:
         self.type = model.pop("type", None)
         nch = model.pop("numberOfChannels", None) or 1
         mono = model.pop("mono", False)
+        self.chunkSize = model.pop("chunkSize", None) or config.standardChunkSize  # Piglet.js:10
         self.options = model
-        self.chunkSize = config.standardChunkSize
         self.sampleRate = config.sampleRate
         if nch == "mono" or mono:  # Piglet.js:13-17
             nch = 1

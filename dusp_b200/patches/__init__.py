@@ -265,6 +265,25 @@ class BandFilter(Patch):
         self.aliasOutlet(self.highPass.OUT)
 
 
+class HardBandPass(Patch):
+    """src/patches/HardBandPass.js:12-34 (spectral low-pass into spectral high-pass; the constructor hands `low` to
+    the low-pass and `high` to the high-pass before the aliased LOW / HIGH setters swap them into place)"""
+
+    def __init__(self, input=None, low=None, high=None):
+        super().__init__()
+        self.lp = C.HardLowPass(low)
+        self.hp = C.HardHighPass(high)
+        self.addUnits(self.lp, self.hp)
+        self.hp.IN = self.lp.OUT
+        self.aliasInlet(self.lp.IN, "in")
+        self.aliasInlet(self.hp.F, "low")
+        self.aliasInlet(self.lp.F, "high")
+        self.aliasOutlet(self.hp.OUT)
+        self.IN = js_or(input, 0)
+        self.LOW = js_or(low, 0)
+        self.HIGH = js_or(high, 22000)
+
+
 class APStack(Patch):
     """src/patches/APStack.js:4-32 (random all-pass chain; draws from the injected host generator)"""
 
@@ -790,6 +809,6 @@ class APWeb(Patch):
 
 
 __all__ = ["APStack", "APWeb", "AttenuationMatrix", "BandFilter", "Boop", "DelayMixer", "FMOsc", "FMSynth",
-           "FrequencyGroup", "LFO", "ManyOsc", "MidiOsc", "Mixer", "MultiTapDelay", "ScaryPatch", "SimpleDelay",
+           "FrequencyGroup", "HardBandPass", "LFO", "ManyOsc", "MidiOsc", "Mixer", "MultiTapDelay", "ScaryPatch", "SimpleDelay",
            "SineBoop", "Space", "SpaceBoop", "SpaceChannel", "StereoDetune", "StereoOsc", "Synth", "TriggerGroup",
            "Worm"]

@@ -37,18 +37,20 @@
 /* src/SignalChunk.js:1-11 -- channelData: Float32Array(chunkSize)[nChannels] */
 typedef struct Chunk {
   int nch;
+  long size;   /* Piglet.js:10 chunkSize: 256 unless the port says otherwise (spectral units) */
   float *ch[MAXCH];
 } Chunk;
 
-static Chunk *chunk_new(int nch) {
+static Chunk *chunk_new_sized(int nch, long size) {
   Chunk *c = (Chunk *)calloc(1, sizeof(Chunk));
-  c->nch = nch;
-  for (int i = 0; i < nch; i++) c->ch[i] = (float *)calloc(CHUNK, sizeof(float));
+  c->nch = nch; c->size = size;
+  for (int i = 0; i < nch; i++) c->ch[i] = (float *)calloc(size, sizeof(float));
   return c;
 }
+static Chunk *chunk_new(int nch) { return chunk_new_sized(nch, CHUNK); }
 static float *chunk_ensure(Chunk *c, int i) { /* `out[c] = out[c] || new Float32Array(chunkSize)` */
   if (i >= MAXCH) { fprintf(stderr, "oracle: too many channels\n"); abort(); }
-  while (c->nch <= i) { c->ch[c->nch] = (float *)calloc(CHUNK, sizeof(float)); c->nch++; }
+  while (c->nch <= i) { c->ch[c->nch] = (float *)calloc(c->size, sizeof(float)); c->nch++; }
   return c->ch[i];
 }
 static void chunk_free(Chunk *c) {
@@ -96,7 +98,9 @@ enum Kind {
   K_FIXEDMULTIPLY, K_SEMITONETORATIO, K_MIDITOFREQUENCY, K_DECIBELTOSCALER, K_SECONDSTOSAMPLES,
   K_CONCATCHANNELS, K_PICKCHANNEL, K_VECTORMAGNITUDE,
   K_DELAY, K_MONODELAY, K_READBACKDELAY, K_FIXEDDELAY, K_COMBFILTER, K_ALLPASS,
-  K_CBWRITER, K_CBREADER, K_RETRIGGERER, K_SPORADICRETRIGGERER, K_SAMPLERATEREDUX, K_MONITOR, K_NKINDS
+  K_CBWRITER, K_CBREADER, K_RETRIGGERER, K_SPORADICRETRIGGERER, K_SAMPLERATEREDUX, K_MONITOR,
+  K_HOPPER, K_WINDOWER, K_FFT, K_IFFT, K_UNHOPPER, K_RECHUNK, K_HARDLOWPASS, K_HARDHIGHPASS, K_SPECTRALGATE, K_BINSHIFT,
+  K_AUGMENT, K_SPECTRALSUM, K_NKINDS
 };
 static const char *KIND_NAMES[K_NKINDS] = {
   "Osc", "MultiChannelOsc", "Ramp", "Shape", "AHD", "Timer", "Noise", "Filter",
@@ -105,7 +109,9 @@ static const char *KIND_NAMES[K_NKINDS] = {
   "FixedMultiply", "SemitoneToRatio", "MidiToFrequency", "DecibelToScaler", "SecondsToSamples",
   "ConcatChannels", "PickChannel", "VectorMagnitude",
   "Delay", "MonoDelay", "ReadBackDelay", "FixedDelay", "CombFilter", "AllPass",
-  "CircleBufferWriter", "CircleBufferReader", "Retriggerer", "SporadicRetriggerer", "SampleRateRedux", "Monitor"};
+  "CircleBufferWriter", "CircleBufferReader", "Retriggerer", "SporadicRetriggerer", "SampleRateRedux", "Monitor",
+  "Hopper", "Windower", "FFT", "IFFT", "UnHopper", "ReChunk", "HardLowPass", "HardHighPass", "SpectralGate", "BinShift",
+  "Augment", "SpectralSum"};
 
 struct Unit;
 typedef struct Port {
@@ -147,6 +153,12 @@ typedef struct Unit {
   CircleBuffer *cb; int prewipe, postwipe;
   /* SampleRateRedux.js:9-10 */
   double srr_val[MAXCH]; int srr_nval; double srr_ts;
+  /* frame-rate units (components/spectral): Circuit.js:34-37 ticks a unit when clock % tickInterval == 0 */
+  long tick_interval, hop, win, frame, in_iv, out_iv;
+  double *dbuf;            /* untyped JS Arrays: Hopper / UnHopper / ReChunk `buffer[0]`, IFFT `complexOut` */
+  float *env;              /* Windower.envelopeBuffer (Float32Array) */
+  struct FFTPlan *fft;
+  int invert, nmap; double map_ratio[8], map_gain[8];
 } Unit;
 
 /* An Event (Event.js:3-30) whose function only assigns numeric unit state, e.g. the trigger() queued by
@@ -265,6 +277,9 @@ static int kind_from_name(const char *s) {
 
 void oracle_free(Oracle *o);
 
+struct FFTPlan;
+static struct FFTPlan *fft_plan(long size);
+static void fft_plan_free(struct FFTPlan *f);
 static int fail(Oracle *o, const char *msg) { snprintf(o->err, sizeof o->err, "%s", msg); return -1; }
 
 static int init_unit_state(Oracle *o, Unit *u) {
@@ -327,9 +342,64 @@ static int init_unit_state(Oracle *o, Unit *u) {
     if (u->kind == K_CBREADER) /* set buffer(): grow out to buffer.numberOfChannels */
       for (int c = 0; c < u->cb->nch; c++) chunk_ensure(u->out[0].chunk, c);
     break; }
+  case K_HOPPER: /* Hopper.js:5-17 */
+    u->hop = (long)propd(u, "hopSize", 0); u->frame = (long)propd(u, "frameSize", 0);
+    if (u->hop < 1 || u->frame < 1) return fail(o, "Hopper needs hopSize and frameSize");
+    u->dbuf = (double *)calloc(u->frame, sizeof(double));
+    break;
+  case K_WINDOWER: { /* Windower.js:4-15,28-47 */
+    u->win = (long)propd(u, "windowSize", 0);
+    if (u->win < 1) return fail(o, "Windower constructor expects a windowSize");
+    if (strcmp(sprop(u, "windowKind", "hamming"), "hamming")) return fail(o, "Window type is not defined.");
+    u->env = (float *)calloc(u->win, sizeof(float));
+    for (long n = 0; n < u->win; n++) u->env[n] = (float)pow(sin((M_PI * (double)n) / (double)(u->win - 1)), 2);
+    break; }
+  case K_FFT: case K_IFFT: /* FFT.js:5-17, IFFT.js:5-19 */
+    u->win = (long)propd(u, "windowSize", 0); u->frame = u->win * 2;
+    if (u->win < 2 || (u->win & (u->win - 1))) return fail(o, "FFT size must be a power of two and bigger than 1");
+    u->fft = fft_plan(u->win);
+    u->dbuf = (double *)calloc(u->frame * 3, sizeof(double));
+    break;
+  case K_UNHOPPER: /* UnHopper.js:4-17 */
+    u->hop = (long)propd(u, "hopSize", 0); u->win = (long)propd(u, "windowSize", 0);
+    if (u->hop < 1 || u->win < 1) return fail(o, "UnHopper needs hopSize and windowSize");
+    u->dbuf = (double *)calloc(u->win, sizeof(double));
+    break;
+  case K_RECHUNK: /* ReChunk.js:6-24 */
+    u->in_iv = (long)propd(u, "inputInterval", 0); u->out_iv = (long)propd(u, "outputInterval", 0);
+    u->frame = (long)propd(u, "bufferSize", 0);
+    if (u->in_iv < 1 || u->out_iv < 1 || u->frame < 1) return fail(o, "ReChunk expects 2 numeric contructor arguments");
+    u->dbuf = (double *)calloc(u->frame, sizeof(double));
+    break;
+  case K_HARDLOWPASS: case K_HARDHIGHPASS: case K_SPECTRALGATE: case K_BINSHIFT: case K_AUGMENT: case K_SPECTRALSUM:
+    u->win = (long)propd(u, "windowSize", 4096); u->frame = u->win * 2; /* SpectralUnit.js:12-16 */
+    u->invert = (int)propd(u, "invert", 1);
+    u->nmap = (int)propd(u, "nmap", 0);
+    for (int m = 0; m < u->nmap && m < 8; m++) {
+      char nm[24];
+      snprintf(nm, sizeof nm, "ratio%d", m); u->map_ratio[m] = propd(u, nm, 1);
+      snprintf(nm, sizeof nm, "gain%d", m); u->map_gain[m] = propd(u, nm, 1);
+    }
+    break;
   default: break;
   }
+  u->tick_interval = (long)propd(u, "tickInterval", CHUNK);
+  if (u->tick_interval < 1) return fail(o, "unit with a tick interval below one sample");
   return 0;
+}
+
+/* chunkSize of a unit's outlet (the `chunkSize` option its constructor passes to addOutlet) */
+static long outlet_chunk_size(Unit *u) {
+  switch (u->kind) {
+  case K_HOPPER: return (long)propd(u, "frameSize", CHUNK);
+  case K_WINDOWER: case K_IFFT: return (long)propd(u, "windowSize", CHUNK);
+  case K_FFT: return 2 * (long)propd(u, "windowSize", CHUNK);
+  case K_UNHOPPER: return (long)propd(u, "hopSize", CHUNK);
+  case K_RECHUNK: return (long)propd(u, "outputInterval", CHUNK);
+  case K_HARDLOWPASS: case K_HARDHIGHPASS: case K_SPECTRALGATE: case K_BINSHIFT: case K_AUGMENT: case K_SPECTRALSUM:
+    return 2 * (long)propd(u, "windowSize", 4096);
+  default: return CHUNK;
+  }
 }
 
 Oracle *oracle_load(const char *blob, char *err, int errlen) {
@@ -396,7 +466,7 @@ Oracle *oracle_load(const char *blob, char *err, int errlen) {
       Port *pt = &u->out[u->nout++];
       snprintf(pt->name, 32, "%s", strtok_r(NULL, " ", &save));
       pt->mono = atoi(strtok_r(NULL, " ", &save));
-      pt->chunk = chunk_new(atoi(strtok_r(NULL, " ", &save))); pt->owns = 1;
+      pt->chunk = chunk_new_sized(atoi(strtok_r(NULL, " ", &save)), outlet_chunk_size(u)); pt->owns = 1;
       char *cv; /* outlet.connections in connect order (Inlet.js:52) */
       while ((cv = strtok_r(NULL, " ", &save)) && pt->nconn < 64) pt->conn_unit[pt->nconn++] = atoi(cv);
     } else if (!strcmp(tok, "EV")) {
@@ -464,6 +534,7 @@ void oracle_free(Oracle *o) {
     for (int j = 0; j < u->nin; j++) if (u->in[j].owns) chunk_free(u->in[j].chunk);
     for (int j = 0; j < u->nout; j++) if (u->out[j].owns) chunk_free(u->out[j].chunk);
     for (int c = 0; c < MAXCH; c++) free(u->bufs[c]);
+    free(u->dbuf); free(u->env); fft_plan_free(u->fft);
   }
   for (int i = 0; i < o->ncb; i++) { for (int c = 0; c < o->cbs[i].nch; c++) free(o->cbs[i].ch[c]); free(o->cbs[i].ch); }
   free(o->cbs); free(o->units); free(o->order); free(o);
@@ -987,6 +1058,278 @@ static int tick_sporadic_retriggerer(Oracle *o, Unit *u) {
   return 0;
 }
 
+
+/* ------------------------------------------------------- spectral units */
+/* THIRD-PARTY ALGORITHM, NOT IN /root/reference: FFT.js:2,16 / IFFT.js:2,12 call `fft.js` (package.json pins
+ * "^4.0.3"; node_modules is not vendored).  What follows restates that package's published radix-4 algorithm
+ * (constructor tables, _transform4, _realTransform4, _singleTransform2/4, _singleRealTransform2/4,
+ * completeSpectrum, inverseTransform) from its documented structure; it cannot be diffed against the package here.
+ * It is pinned numerically instead: tests/test_oracle_kat.py checks it against numpy's DFT for every size
+ * 4 .. 8192.  Storage rounding follows the call sites: FFT.js:21 transforms into the outlet's Float32Array
+ * (every store rounds to binary32, `r32` below), IFFT.js:23 into an untyped Array (doubles). */
+typedef struct FFTPlan { long size, csize; int width; double *table; long *bitrev; } FFTPlan;
+
+static struct FFTPlan *fft_plan(long size) {
+  FFTPlan *f = (FFTPlan *)calloc(1, sizeof(FFTPlan));
+  f->size = size; f->csize = size << 1;
+  f->table = (double *)malloc(sizeof(double) * size * 2);
+  for (long i = 0; i < size * 2; i += 2) {
+    const double angle = M_PI * (double)i / (double)size;
+    f->table[i] = cos(angle); f->table[i + 1] = -sin(angle);
+  }
+  int power = 0;
+  for (long t = 1; size > t; t <<= 1) power++;
+  f->width = power % 2 == 0 ? power - 1 : power;
+  long nb = 1L << f->width;
+  f->bitrev = (long *)calloc(nb, sizeof(long));
+  for (long j = 0; j < nb; j++)
+    for (int shift = 0; shift < f->width; shift += 2) {
+      int rev = f->width - shift - 2;
+      /* (JS `<< -1` only ever meets a zero digit for the entries the transforms use: j < size / 4) */
+      if (rev >= 0) f->bitrev[j] |= ((j >> shift) & 3) << rev;
+    }
+  return f;
+}
+static void fft_plan_free(struct FFTPlan *f) { if (f) { free(f->table); free(f->bitrev); free(f); } }
+
+#define FST(i, v) out[i] = r32 ? (double)(float)(v) : (v)
+/* the butterflies after the first pass, shared by the complex and the real transform's "full" part */
+static void fft_transform4(const FFTPlan *f, double *out, const double *data, int inverse, int r32) {
+  const long size = f->csize; long step = 1L << f->width; long len = (size / step) << 1;
+  const double inv = inverse ? -1 : 1;
+  long outOff, t;
+  if (len == 4) {
+    for (outOff = 0, t = 0; outOff < size; outOff += len, t++) { /* _singleTransform2 */
+      const long off = f->bitrev[t];
+      const double evenR = data[off], evenI = data[off + 1], oddR = data[off + step], oddI = data[off + step + 1];
+      FST(outOff, evenR + oddR); FST(outOff + 1, evenI + oddI); FST(outOff + 2, evenR - oddR); FST(outOff + 3, evenI - oddI);
+    }
+  } else {
+    for (outOff = 0, t = 0; outOff < size; outOff += len, t++) { /* _singleTransform4 */
+      const long off = f->bitrev[t], step2 = step * 2, step3 = step * 3;
+      const double Ar = data[off], Ai = data[off + 1], Br = data[off + step], Bi = data[off + step + 1];
+      const double Cr = data[off + step2], Ci = data[off + step2 + 1], Dr = data[off + step3], Di = data[off + step3 + 1];
+      const double T0r = Ar + Cr, T0i = Ai + Ci, T1r = Ar - Cr, T1i = Ai - Ci;
+      const double T2r = Br + Dr, T2i = Bi + Di, T3r = inv * (Br - Dr), T3i = inv * (Bi - Di);
+      FST(outOff, T0r + T2r); FST(outOff + 1, T0i + T2i); FST(outOff + 2, T1r + T3i); FST(outOff + 3, T1i - T3r);
+      FST(outOff + 4, T0r - T2r); FST(outOff + 5, T0i - T2i); FST(outOff + 6, T1r - T3i); FST(outOff + 7, T1i + T3r);
+    }
+  }
+  const double *table = f->table;
+  for (step >>= 2; step >= 2; step >>= 2) {
+    len = (size / step) << 1;
+    const long quarterLen = len >> 2;
+    for (outOff = 0; outOff < size; outOff += len) {
+      const long limit = outOff + quarterLen;
+      for (long i = outOff, k = 0; i < limit; i += 2, k += step) {
+        const long A = i, B = A + quarterLen, C = B + quarterLen, D = C + quarterLen;
+        const double Ar = out[A], Ai = out[A + 1], Br = out[B], Bi = out[B + 1], Cr = out[C], Ci = out[C + 1], Dr = out[D], Di = out[D + 1];
+        const double MAr = Ar, MAi = Ai;
+        const double tableBr = table[k], tableBi = inv * table[k + 1];
+        const double MBr = Br * tableBr - Bi * tableBi, MBi = Br * tableBi + Bi * tableBr;
+        const double tableCr = table[2 * k], tableCi = inv * table[2 * k + 1];
+        const double MCr = Cr * tableCr - Ci * tableCi, MCi = Cr * tableCi + Ci * tableCr;
+        const double tableDr = table[3 * k], tableDi = inv * table[3 * k + 1];
+        const double MDr = Dr * tableDr - Di * tableDi, MDi = Dr * tableDi + Di * tableDr;
+        const double T0r = MAr + MCr, T0i = MAi + MCi, T1r = MAr - MCr, T1i = MAi - MCi;
+        const double T2r = MBr + MDr, T2i = MBi + MDi, T3r = inv * (MBr - MDr), T3i = inv * (MBi - MDi);
+        FST(A, T0r + T2r); FST(A + 1, T0i + T2i); FST(B, T1r + T3i); FST(B + 1, T1i - T3r);
+        FST(C, T0r - T2r); FST(C + 1, T0i - T2i); FST(D, T1r - T3i); FST(D + 1, T1i + T3r);
+      }
+    }
+  }
+}
+/* realTransform: `data` holds `size` reals; only the first half (+1 bin) of `out` is meaningful afterwards */
+static void fft_real_transform4(const FFTPlan *f, double *out, const double *data, int r32) {
+  const long size = f->csize; long step = 1L << f->width; long len = (size / step) << 1;
+  const double inv = 1;
+  long outOff, t;
+  if (len == 4) {
+    for (outOff = 0, t = 0; outOff < size; outOff += len, t++) { /* _singleRealTransform2(outOff, off >>> 1, step >>> 1) */
+      const long off = f->bitrev[t] >> 1, st = step >> 1;
+      const double evenR = data[off], oddR = data[off + st];
+      FST(outOff, evenR + oddR); FST(outOff + 1, 0.0); FST(outOff + 2, evenR - oddR); FST(outOff + 3, 0.0);
+    }
+  } else {
+    for (outOff = 0, t = 0; outOff < size; outOff += len, t++) { /* _singleRealTransform4 */
+      const long off = f->bitrev[t] >> 1, st = step >> 1;
+      const double Ar = data[off], Br = data[off + st], Cr = data[off + 2 * st], Dr = data[off + 3 * st];
+      const double T0r = Ar + Cr, T1r = Ar - Cr, T2r = Br + Dr, T3r = inv * (Br - Dr);
+      FST(outOff, T0r + T2r); FST(outOff + 1, 0.0); FST(outOff + 2, T1r); FST(outOff + 3, -T3r);
+      FST(outOff + 4, T0r - T2r); FST(outOff + 5, 0.0); FST(outOff + 6, T1r); FST(outOff + 7, T3r);
+    }
+  }
+  const double *table = f->table;
+  for (step >>= 2; step >= 2; step >>= 2) {
+    len = (size / step) << 1;
+    const long halfLen = len >> 1, quarterLen = halfLen >> 1, hquarterLen = quarterLen >> 1;
+    for (outOff = 0; outOff < size; outOff += len) {
+      for (long i = 0, k = 0; i <= hquarterLen; i += 2, k += step) {
+        const long A = outOff + i, B = A + quarterLen, C = B + quarterLen, D = C + quarterLen;
+        const double Ar = out[A], Ai = out[A + 1], Br = out[B], Bi = out[B + 1], Cr = out[C], Ci = out[C + 1], Dr = out[D], Di = out[D + 1];
+        const double MAr = Ar, MAi = Ai;
+        const double tableBr = table[k], tableBi = inv * table[k + 1];
+        const double MBr = Br * tableBr - Bi * tableBi, MBi = Br * tableBi + Bi * tableBr;
+        const double tableCr = table[2 * k], tableCi = inv * table[2 * k + 1];
+        const double MCr = Cr * tableCr - Ci * tableCi, MCi = Cr * tableCi + Ci * tableCr;
+        const double tableDr = table[3 * k], tableDi = inv * table[3 * k + 1];
+        const double MDr = Dr * tableDr - Di * tableDi, MDi = Dr * tableDi + Di * tableDr;
+        const double T0r = MAr + MCr, T0i = MAi + MCi, T1r = MAr - MCr, T1i = MAi - MCi;
+        const double T2r = MBr + MDr, T2i = MBi + MDi, T3r = inv * (MBr - MDr), T3i = inv * (MBi - MDi);
+        FST(A, T0r + T2r); FST(A + 1, T0i + T2i); FST(B, T1r + T3i); FST(B + 1, T1i - T3r);
+        if (i == 0) { FST(C, T0r - T2r); FST(C + 1, T0i - T2i); continue; }   /* output final middle point */
+        if (i == hquarterLen) continue;                                         /* do not overwrite ourselves */
+        /* the mirrored butterfly, by symmetry of a real signal's spectrum */
+        const double ST0r = T1r, ST0i = -T1i, ST1r = T0r, ST1i = -T0i;
+        const double ST2r = -inv * T3i, ST2i = -inv * T3r, ST3r = -inv * T2i, ST3i = -inv * T2r;
+        const long SA = outOff + quarterLen - i, SB = outOff + halfLen - i;
+        FST(SA, ST0r + ST2r); FST(SA + 1, ST0i + ST2i); FST(SB, ST1r + ST3i); FST(SB + 1, ST1i - ST3r);
+      }
+    }
+  }
+}
+static void fft_complete_spectrum(const FFTPlan *f, double *sp, int r32) {
+  const long size = f->csize, half = size >> 1;
+  double *out = sp;
+  for (long i = 2; i < half; i += 2) { FST(size - i, sp[i]); FST(size - i + 1, -sp[i + 1]); }
+}
+#undef FST
+/* test hooks (tests/test_oracle_kat.py): one transform on caller arrays */
+int oracle_fft(long size, int mode, const double *in, double *out, int r32) {
+  if (size < 2 || (size & (size - 1))) return -1;
+  FFTPlan *f = fft_plan(size);
+  if (mode == 0) { fft_real_transform4(f, out, in, r32); fft_complete_spectrum(f, out, r32); }
+  else if (mode == 1) fft_transform4(f, out, in, 0, r32);
+  else { fft_transform4(f, out, in, 1, r32); for (long i = 0; i < f->csize; i++) out[i] = r32 ? (double)(float)(out[i] / (double)size) : out[i] / (double)size; }
+  fft_plan_free(f);
+  return 0;
+}
+
+/* Hopper.js:19-37 (buffer: untyped Array; in / out channel 0: the ports' Float32Arrays) */
+static void tick_hopper(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; const long inlen = INCH(u, 0)->size; float *out = OUTCH(u, 0)->ch[0];
+  for (long t = 0; t < u->tick_interval; t++)
+    u->dbuf[(long)fmod(u->t + t, (double)u->frame)] = (double)in[(long)fmod(u->t + t, (double)inlen)];
+  u->t += (double)u->tick_interval;
+  if (fmod(u->t, (double)u->hop) == 0)
+    for (long t = 0; t < u->frame; t++) out[t] = (float)u->dbuf[(long)fmod((double)t + u->t, (double)u->frame)];
+}
+/* Windower.js:17-23; envelope :28-47 (Math.pow(Math.sin(pi n / (N-1)), 2) stored in a Float32Array) */
+static void tick_windower(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  for (long t = 0; t < u->win; t++) out[t] = (float)((double)in[t] * (double)u->env[t]);
+}
+/* FFT.js:19-25 */
+static void tick_fft(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  double *d = u->dbuf, *w = u->dbuf + u->win; /* scratch: input widened, output image of the Float32Array */
+  for (long t = 0; t < u->win; t++) d[t] = (double)in[t];
+  for (long t = 0; t < u->frame; t++) w[t] = (double)out[t];
+  fft_real_transform4(u->fft, w, d, 1);
+  fft_complete_spectrum(u->fft, w, 1);
+  for (long t = 0; t < u->frame; t++) out[t] = (float)w[t];
+}
+/* IFFT.js:21-33 */
+static void tick_ifft(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  double *d = u->dbuf, *cplx = u->dbuf + u->frame; /* cplx = this.complexOut (persists, untyped Array) */
+  for (long t = 0; t < u->frame; t++) d[t] = (double)in[t];
+  fft_transform4(u->fft, cplx, d, 1, 0);
+  for (long t = 0; t < u->frame; t++) cplx[t] /= (double)u->win; /* inverseTransform: out[i] /= this.size */
+  for (long t = 0; t < u->win; t++) out[t] = (float)cplx[t * 2];
+}
+/* UnHopper.js:19-44 */
+static void tick_unhopper(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  for (long t = 0; t < u->win; t++) u->dbuf[(long)fmod((double)t + u->t, (double)u->win)] += (double)in[t];
+  u->t += (double)u->hop;
+  if (u->t > (double)u->hop) {
+    const double t0 = u->t - (double)u->hop;
+    for (long t = 0; t < u->hop; t++) {
+      const long tb = (long)fmod(t0 + (double)t, (double)u->win);
+      out[t] = (float)u->dbuf[tb];
+      u->dbuf[tb] = 0;
+    }
+  }
+}
+/* ReChunk.js:26-49 */
+static void tick_rechunk(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  if (fmod(u->t, (double)u->in_iv) == 0)
+    for (long t = 0; t < u->in_iv; t++) u->dbuf[(long)fmod(u->t + (double)t, (double)u->frame)] = (double)in[t];
+  u->t += (double)u->tick_interval;
+  if (fmod(u->t, (double)u->out_iv) == 0) {
+    const double t0 = u->t - (double)u->out_iv;
+    for (long t = 0; t < u->out_iv; t++) out[t] = (float)u->dbuf[(long)fmod(t0 + (double)t, (double)u->frame)];
+  }
+}
+static double js_round(double x) { return floor(x + 0.5); } /* Math.round */
+/* HardLowPass.js:20-31 / HardHighPass.js:20-31 */
+static void tick_hardpass(Unit *u, int high) {
+  const float *in = INCH(u, 0)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  const double f0 = (double)INCH(u, 1)->ch[0][0];
+  const double cut = js_round(f0 / ((double)SR / (double)u->win)) * 2;
+  if (cut != cut) return; /* NaN cutoff: neither loop runs, `out` keeps the previous frame */
+  for (long i = 0; i < u->frame; i++) {
+    const int below = (double)i < cut; /* NaN cutoff: no index is below it */
+    out[i] = (below != high) ? in[i] : 0.0f;
+  }
+}
+/* SpectralGate.js:15-32 */
+static void tick_spectralgate(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  const double th = (double)INCH(u, 1)->ch[0][0];
+  for (long b = 0; b < u->frame; b += 2) {
+    const double re = in[b], im = in[b + 1], mag = sqrt(re * re + im * im);
+    if (u->invert ? mag < th : mag > th) { out[b] = (float)re; out[b + 1] = (float)im; } else { out[b] = 0; out[b + 1] = 0; }
+  }
+}
+/* BinShift.js:14-26 */
+static void tick_binshift(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  const double shift = js_round((double)INCH(u, 1)->ch[0][0]) * 2;
+  for (long i = 0; i < u->frame; i++) out[i] = 0;
+  /* `bin + shift < frameSize` is false for a NaN shift: nothing moves */
+  for (long bin = 1; bin < u->frame && (double)bin + shift < (double)u->frame; bin += 2) {
+    if ((double)bin + shift < 0) continue;
+    const long d = (long)((double)bin + shift);
+    out[d] = in[bin]; out[d - 1] = in[bin - 1];
+  }
+}
+/* Augment.js:14-27 (`out` is the port's Float32Array: every `+=` rounds to binary32) */
+static void tick_augment(Unit *u) {
+  const float *in = INCH(u, 0)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  for (long i = 0; i < u->frame; i++) out[i] = 0;
+  for (long bin = 0; bin < u->win; bin++)
+    for (int m = 0; m < u->nmap; m++) {
+      const double b2 = js_round((double)bin * u->map_ratio[m]) * 2;
+      if (!(b2 >= 0 && b2 < (double)u->frame)) continue; /* (a NaN index is a no-op store on a typed array) */
+      const long d = (long)b2;
+      out[d] = (float)((double)out[d] + (double)in[bin * 2] * u->map_gain[m]);
+      out[d + 1] = (float)((double)out[d + 1] + (double)in[bin * 2 + 1] * u->map_gain[m]);
+    }
+}
+/* SpectralSum.js:15-24 */
+static void tick_spectralsum(Unit *u) {
+  const float *a = INCH(u, 0)->ch[0], *b = INCH(u, 1)->ch[0]; float *out = OUTCH(u, 0)->ch[0];
+  for (long i = 0; i < u->frame; i++) out[i] = (float)((double)a[i] + (double)b[i]);
+}
+/* Channels beyond the first of these units are untyped Arrays (`out[c] = out[c] || new Array(n)`: doubles, no
+ * binary32 rounding) -- not modelled; and every frame inlet must see a chunk at least as long as it reads. */
+static int spectral_check(Oracle *o, Unit *u) {
+  for (int i = 0; i < u->nin; i++) if (!u->in[i].nodata && u->in[i].chunk->nch > 1 && i == 0) return fail(o, "multi-channel spectral chains are not modelled (extra channels are untyped Arrays)");
+  long need = 0;
+  switch (u->kind) {
+  case K_WINDOWER: case K_FFT: case K_UNHOPPER: need = u->win; break;
+  case K_RECHUNK: need = u->in_iv; break;
+  case K_IFFT: case K_HARDLOWPASS: case K_HARDHIGHPASS: case K_SPECTRALGATE: case K_BINSHIFT: case K_AUGMENT: case K_SPECTRALSUM: need = u->frame; break;
+  default: break;
+  }
+  if (need && INCH(u, 0)->size < need) return fail(o, "frame inlet fed by a shorter chunk (reads undefined)");
+  if (u->kind == K_SPECTRALSUM && INCH(u, 1)->size < need) return fail(o, "frame inlet fed by a shorter chunk (reads undefined)");
+  return 0;
+}
+
 /* Unit.js:111-119 tick -> _tick */
 static int unit_tick(Oracle *o, Unit *u, double clock) {
   switch (u->kind) {
@@ -1031,6 +1374,18 @@ static int unit_tick(Oracle *o, Unit *u, double clock) {
   case K_FIXEDDELAY: case K_COMBFILTER: case K_ALLPASS: tick_fixeddelay(u); break;
   case K_CBWRITER: tick_cbwriter(u); break;
   case K_CBREADER: tick_cbreader(u); break;
+  case K_HOPPER: if (spectral_check(o, u)) return -1; tick_hopper(u); break;
+  case K_WINDOWER: if (spectral_check(o, u)) return -1; tick_windower(u); break;
+  case K_FFT: if (spectral_check(o, u)) return -1; tick_fft(u); break;
+  case K_IFFT: if (spectral_check(o, u)) return -1; tick_ifft(u); break;
+  case K_UNHOPPER: if (spectral_check(o, u)) return -1; tick_unhopper(u); break;
+  case K_RECHUNK: if (spectral_check(o, u)) return -1; tick_rechunk(u); break;
+  case K_HARDLOWPASS: if (spectral_check(o, u)) return -1; tick_hardpass(u, 0); break;
+  case K_HARDHIGHPASS: if (spectral_check(o, u)) return -1; tick_hardpass(u, 1); break;
+  case K_SPECTRALGATE: if (spectral_check(o, u)) return -1; tick_spectralgate(u); break;
+  case K_BINSHIFT: if (spectral_check(o, u)) return -1; tick_binshift(u); break;
+  case K_AUGMENT: if (spectral_check(o, u)) return -1; tick_augment(u); break;
+  case K_SPECTRALSUM: if (spectral_check(o, u)) return -1; tick_spectralsum(u); break;
   }
   return 0;
 }
@@ -1092,7 +1447,8 @@ static void adopt_state(Oracle *n, Oracle *o) {
       for (int m = 0; m < b->nout; m++) {
         if (strcmp(a->out[k].name, b->out[m].name) || !a->out[k].chunk || !b->out[m].chunk) continue;
         for (int c = 0; c < b->out[m].chunk->nch; c++)
-          memcpy(chunk_ensure(a->out[k].chunk, c), b->out[m].chunk->ch[c], CHUNK * sizeof(float));
+          if (a->out[k].chunk->size == b->out[m].chunk->size)
+            memcpy(chunk_ensure(a->out[k].chunk, c), b->out[m].chunk->ch[c], (size_t)b->out[m].chunk->size * sizeof(float));
       }
   }
 }
@@ -1104,9 +1460,15 @@ int oracle_render(Oracle *first, double duration, float **out, int max_ch, int *
   long n = length > 0 ? (long)length : 0;         /* new Float32Array(x): ToIndex truncates */
   Chunk *root = o->units[o->root_unit].out[o->root_outlet].chunk;
   int nch = 0;
-  for (double t0 = 0; t0 < length; t0 += CHUNK) { /* :29 */
-    /* circuit.tickUntil(t1): Circuit.js:19-47 -- one tick per chunk (all hot-path units tick at 256) */
-    while (o->clock < t0 + CHUNK) {
+  /* Circuit.js:125-143: the circuit advances by the gcd of its units' tick intervals; only multiples of the
+   * standard chunk are modelled (every frame-rate unit of the reference ticks at a multiple of 256 by default) */
+  for (Oracle *q = first; q; q = q->next)
+    for (int i = 0; i < q->nunits; i++)
+      if (q->units[i].tick_interval % CHUNK) return fail(first, "tick interval that is not a multiple of 256 samples");
+  long csize = root->size;                        /* :25 outlet.chunkSize */
+  for (double t0 = 0; t0 < length; t0 += (double)csize) { /* :29 */
+    /* circuit.tickUntil(t1): Circuit.js:19-47 -- one tick per 256 samples; a unit ticks when clock % tickInterval == 0 */
+    while (o->clock < t0 + (double)csize) {
       while (o->next && (long)(o->clock / CHUNK) >= o->next_chunk) { /* the event that edits the graph runs first */
         adopt_state(o->next, o);
         o = o->next;
@@ -1115,8 +1477,11 @@ int oracle_render(Oracle *first, double duration, float **out, int max_ch, int *
       }
       for (int e = 0; e < o->nevents; e++)          /* Circuit.js:23 runEvents(clock + 256), in queue order */
         if (o->events[e].chunk == (long)(o->clock / CHUNK) && apply_event(o, &o->events[e])) return chain_fail(first, o);
-      for (int i = 0; i < o->norder; i++)
-        if (unit_tick(o, &o->units[o->order[i]], o->clock)) return chain_fail(first, o);
+      for (int i = 0; i < o->norder; i++) {
+        Unit *w = &o->units[o->order[i]];
+        if (fmod(o->clock, (double)w->tick_interval) != 0) continue; /* Circuit.js:35 */
+        if (unit_tick(o, w, o->clock)) return chain_fail(first, o);
+      }
       o->clock += CHUNK;
     }
     while (root->nch > nch) {                     /* :38-39 */
@@ -1124,7 +1489,7 @@ int oracle_render(Oracle *first, double duration, float **out, int max_ch, int *
       out[nch++] = (float *)calloc(n > 0 ? n : 1, sizeof(float));
     }
     for (int c = 0; c < root->nch; c++)           /* :42-44: `x || 0`, out-of-range stores dropped */
-      for (int t = 0; t < CHUNK; t++) {
+      for (long t = 0; t < csize; t++) {
         long i = (long)t0 + t;
         if (i < n) { float x = root->ch[c][t]; out[c][i] = g_raw_copy ? x : (x != x || x == 0) ? 0.f : x; }
       }

@@ -41,6 +41,8 @@ def lib():
         L.oracle_wave_table.argtypes = [ctypes.c_char_p]
         L.oracle_shape_table.restype = ctypes.POINTER(ctypes.c_float)
         L.oracle_shape_table.argtypes = [ctypes.c_char_p]
+        L.oracle_fft.argtypes = [ctypes.c_long, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
+                                 ctypes.POINTER(ctypes.c_double), ctypes.c_int]
         _LIB = L
     return _LIB
 
@@ -101,3 +103,16 @@ def shape_table(name):
 
 def rand(seed, k):
     return lib().oracle_rand(seed, k)
+
+
+def fft(x, mode="real", r32=False):
+    """The oracle's restatement of fft.js on one array.  mode "real": realTransform + completeSpectrum of N reals;
+    "complex" / "inverse": transform / inverseTransform of N interleaved complex values.  Returns 2N doubles."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    n = len(x) if mode == "real" else len(x) // 2
+    out = np.zeros(2 * n, dtype=np.float64)
+    dp = ctypes.POINTER(ctypes.c_double)
+    rc = lib().oracle_fft(n, {"real": 0, "complex": 1, "inverse": 2}[mode], x.ctypes.data_as(dp), out.ctypes.data_as(dp), int(r32))
+    if rc != 0:
+        raise OracleError("FFT size must be a power of two and bigger than 1")
+    return out

@@ -401,6 +401,83 @@ def dusp_roundtrip():  # dusp.js text of a circuit, parsed again, renders like t
     return d.unDusp(dusp(d.unDusp("[Filter in:(Z110.25 * D0.5) f:(O2 * 300 + 900)] @ -0.5")))
 
 
+# ---- frame-rate units (components/spectral)
+def _stft(src, W, H, mid=None, post_window=False):
+    """src -> Hopper -> Windower -> FFT -> [mid] -> IFFT -> (Windower) -> UnHopper"""
+    h = C.Hopper(H, W); h.IN = src
+    w = C.Windower(W, "hamming", H); w.IN = h
+    f = C.FFT(W, H); f.IN = w
+    x = mid(f) if mid else f
+    i = C.IFFT(W, H); i.IN = x
+    y = i
+    if post_window:
+        y = C.Windower(W, "hamming", H); y.IN = i
+    u = C.UnHopper(H, W); u.IN = y
+    return u
+
+
+def spectral_identity_small():  # hop = the standard chunk: the UnHopper's outlet feeds standard units directly
+    u = _stft(C.Sum(C.Osc(441), C.Multiply(C.Osc(1234.5, "saw"), 0.3)), 1024, 256)
+    return C.Multiply(u, 0.5)
+
+
+def spectral_identity():  # the reference's default sizes (config.fft: window 4096, hop 1024), back to 256 through a ReChunk
+    u = _stft(C.Sum(C.Osc(441), C.Noise(seed=5)), 4096, 1024, post_window=True)
+    r = C.ReChunk(1024, 256); r.IN = u
+    return C.Multiply(r, 0.25)
+
+
+def spectral_unhopper_root():  # renderChannelData straight off a 1024-sample outlet (outlet.chunkSize = 1024)
+    return _stft(C.Osc(330.3, "triangle"), 4096, 1024)
+
+
+def spectral_lowpass():
+    def mid(f):
+        lp = C.HardLowPass(1000); lp.IN = f
+        return lp
+    u = _stft(C.Sum(C.Osc(441), C.Osc(3000.7)), 4096, 1024, mid)
+    r = C.ReChunk(1024, 256); r.IN = u
+    return r
+
+
+def spectral_bandpass_modulated():  # HardBandPass patch, LOW from a signal: read once per 1024-sample tick
+    def mid(f):
+        bp = P.HardBandPass(f, 100, 5000)
+        bp.LOW = quick.add(quick.multiply(C.Osc(1.5), 400), 600)
+        return bp
+    u = _stft(C.Noise(seed=8), 4096, 1024, mid)
+    r = C.ReChunk(1024, 256); r.IN = u
+    return r
+
+
+def spectral_gate_shift_sum():
+    def mid(f):
+        gate = C.SpectralGate(40.0); gate.IN = f; gate.invert = False
+        shift = C.BinShift(7); shift.IN = gate
+        quiet = C.SpectralGate(3.0); quiet.IN = f
+        hp = C.HardHighPass(200); hp.IN = quiet
+        return C.SpectralSum(shift, hp)
+    u = _stft(C.Sum(C.Osc(220.5), C.Multiply(C.Noise(seed=21), 0.05)), 4096, 1024, mid)
+    r = C.ReChunk(1024, 256); r.IN = u
+    return r
+
+
+def spectral_augment():
+    def mid(f):
+        a = C.Augment({1: 0.5, 2: 0.25, 0.5: 0.125}); a.IN = f
+        down = C.BinShift(-3.4); down.IN = a
+        return down
+    u = _stft(C.Osc(500.25, "square"), 4096, 1024, mid)
+    r = C.ReChunk(1024, 256); r.IN = u
+    return C.Abs(r)
+
+
+def rechunk_up_down():  # a standard signal re-blocked to 512-sample chunks and back
+    up = C.ReChunk(256, 512); up.IN = C.Osc(777.7)
+    down = C.ReChunk(512, 256); down.IN = up
+    return down
+
+
 CASES = {
     "osc440": (osc440, 1.0, True),
     "readme_fm_literal": (readme_fm_literal, 1.0, True),
@@ -471,4 +548,12 @@ CASES = {
     "trigger_group": (trigger_group, 0.5, False),
     "ap_web": (ap_web, 0.4, False),
     "dusp_roundtrip": (dusp_roundtrip, 0.6, False),
+    "spectral_identity_small": (spectral_identity_small, 0.3, True),
+    "spectral_identity": (spectral_identity, 0.5, True),
+    "spectral_unhopper_root": (spectral_unhopper_root, 0.4, True),
+    "spectral_lowpass": (spectral_lowpass, 0.5, True),
+    "spectral_bandpass_modulated": (spectral_bandpass_modulated, 0.5, True),
+    "spectral_gate_shift_sum": (spectral_gate_shift_sum, 0.5, True),
+    "spectral_augment": (spectral_augment, 0.4, True),
+    "rechunk_up_down": (rechunk_up_down, 0.2, True),
 }

@@ -377,3 +377,30 @@ def test_render_stream_crosses_a_graph_edit(lib, oracle):
     got = np.concatenate([rs.read() for _ in range(172)])
     rs.stop()
     assert np.array_equal(got[:44032], want[:44032])
+
+
+def test_spectral_batch_with_per_voice_parameters(lib, oracle):
+    """70 voices of Osc -> STFT -> HardLowPass -> ISTFT -> ReChunk, each with its own oscillator
+    frequency and cut-off (per-voice words); frames are per-voice rings, one warp per voice."""
+    rng = np.random.default_rng(1006)
+    n = 70
+    f = rng.uniform(100, 4000, n)
+    cut = rng.uniform(200, 6000, n)
+    blob, _ = circuit_blob(circuits.spectral_lowpass())
+    osc0 = unit_index(blob, "Osc", 0)
+    lp = unit_index(blob, "HardLowPass")
+    p = capi.Program(blob)
+    s = capi.Session([p], [n], 0)
+    s.set_params(0, ["u%d.f[0]" % osc0, "u%d.f[0]" % lp], np.stack([f, cut], axis=1))
+    a = s.render_host(19 * 256)   # launches are chunk-aligned, not aligned to the 1024-sample hop
+    b = s.render_host(SR // 2 + 6 - 19 * 256)
+    s.close()
+    got = np.concatenate([a, b], axis=-1)
+    for v in (0, 1, 33, 69):
+        def mid(x, c=float(cut[v])):
+            l = C.HardLowPass(c); l.IN = x
+            return l
+        u = circuits._stft(C.Sum(C.Osc(float(f[v])), C.Osc(3000.7)), 4096, 1024, mid)
+        r = C.ReChunk(1024, 256); r.IN = u
+        vb, _ = circuit_blob(r)
+        compare(got[v], oracle.render(vb, 0.5 + 6 / SR), True, "spectral voice %d" % v)
