@@ -44,6 +44,9 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-mix", action="store_true", help="skip the W5 stereo-mixdown + NCCL reduce leg")
     ap.add_argument("--mix-voices", type=int, default=12500, help="W5 voices per GPU (100 000 / 8)")
+    ap.add_argument("--mix-collective", default="auto", choices=["auto", "p2p", "nccl"],
+                    help="transport of the mixdown sum: one-sided adds into rank 0's accumulator over NVLink peer memory "
+                         "(default for N > 1) or ncclReduce per block")
     return ap.parse_args()
 
 
@@ -168,7 +171,7 @@ def measure_mixdown(args, rank, world, local_rank, barrier):
     secs = min(args.seconds, 10.0)
     n_total = int(secs * SR)
     blk = max(256, int(args.block_seconds * SR) // 256 * 256)
-    r = MD.MixdownRenderer(sess, blk, torch.device("cuda", local_rank))
+    r = MD.MixdownRenderer(sess, blk, torch.device("cuda", local_rank), collective=args.mix_collective)
     peak = [0.0]
 
     def on_block(t0, n, t):  # rank 0 consumes the reduced mix (device-side peak; the audio itself stays on the GPU)
@@ -199,9 +202,13 @@ def measure_mixdown(args, rank, world, local_rank, barrier):
                        "stereo mixdown only" % (nv, secs),
            "value": units * n_total / (ms_step / 1e3), "unit": "unit-samples/s", "voices_total": nv * world,
            "realtime_voices": nv * world * n_total / (ms_step / 1e3) / SR, "ms_per_step": ms_step,
-           "collective": ("ncclReduce(sum) of the [2][%d] f32 mix per block onto rank 0, async (overlaps the next block)" % blk)
-                         if world > 1 else "none (one GPU)",
+           "collective": ("none (one GPU)" if world == 1 else
+                          "one-sided: every rank adds its [2][%d] f32 block into rank 0's accumulator over NVLink peer memory "
+                          "(system-scope float reductions + arrival counters, csrc/mixpush.cu); no rendezvous kernel" % blk
+                          if r.collective == "p2p" else
+                          "ncclReduce(sum) of the [2][%d] f32 mix per block onto rank 0, async (overlaps the next block)" % blk),
            "mix_peak": peak[0]}
+    r.close()
     sess.close()
     return out
 

@@ -30,6 +30,7 @@ SYMBOLS = [
     "dusp_session_render", "dusp_session_launch_count", "dusp_session_launch_info", "dusp_rand53",
     "dusp_session_tile_info", "dusp_session_warning", "dusp_program_specialise", "dusp_session_poke",
     "dusp_session_adopt", "dusp_program_warmup_ticks",
+    "dusp_mix_acc_create", "dusp_mix_acc_open", "dusp_mix_acc_close", "dusp_mix_acc_clear", "dusp_mix_push", "dusp_mix_wait",
 ]
 
 
@@ -83,6 +84,12 @@ def load():
     L.dusp_program_specialise.restype = c.c_size_t
     L.dusp_rand53.argtypes = [c.c_uint64, c.c_uint64]
     L.dusp_rand53.restype = c.c_double
+    L.dusp_mix_acc_create.argtypes = [c.c_int, c.c_size_t, c.c_size_t, c.POINTER(c.c_void_p), c.POINTER(c.c_void_p), c.c_char_p]
+    L.dusp_mix_acc_open.argtypes = [c.c_int, c.c_char_p, c.c_size_t, c.POINTER(c.c_void_p), c.POINTER(c.c_void_p)]
+    L.dusp_mix_acc_close.argtypes = [c.c_void_p, c.c_int]
+    L.dusp_mix_acc_clear.argtypes = [c.c_void_p, c.c_size_t, c.c_size_t, c.c_void_p]
+    L.dusp_mix_push.argtypes = [c.c_void_p, c.c_void_p, c.c_size_t, c.c_void_p, c.c_void_p, c.c_void_p]
+    L.dusp_mix_wait.argtypes = [c.c_void_p, c.c_uint, c.c_void_p]
     if L.dusp_abi_version() != 1:
         raise RuntimeError("libdusp_b200.so ABI version mismatch")
     assert config.sampleRate == 44100 and config.standardChunkSize == 256  # compiled into the kernels
@@ -247,3 +254,38 @@ class Session:
         load().dusp_session_tile_info(self._h, ctypes.byref(B), ctypes.byref(T), ctypes.byref(f))
         return {"grid": g.value, "block": b.value, "smem_bytes": s.value, "sub_block": B.value, "time_lanes": T.value,
                 "specialised": bool(f.value), "warning": load().dusp_session_warning(self._h).decode()}
+
+
+class MixAccumulator:
+    """The root GPU's mixdown accumulator shared through CUDA IPC (csrc/mixpush.cu): ``n_floats`` f32 sums and
+    ``n_counters`` u32 arrival counters.  The root creates it (``handle`` is the 64 bytes to send to the other
+    processes); peers open it from the handle.  Pointers are raw device addresses valid in this process."""
+
+    def __init__(self, device, n_floats, n_counters, handle=None):
+        L = load()
+        self.n_floats, self.n_counters, self.owner = int(n_floats), int(n_counters), handle is None
+        acc, ctr = ctypes.c_void_p(), ctypes.c_void_p()
+        if self.owner:
+            buf = ctypes.create_string_buffer(64)
+            check(L.dusp_mix_acc_create(device, self.n_floats, self.n_counters, ctypes.byref(acc), ctypes.byref(ctr), buf))
+            self.handle = buf.raw
+        else:
+            self.handle = bytes(handle)
+            check(L.dusp_mix_acc_open(device, self.handle, self.n_floats, ctypes.byref(acc), ctypes.byref(ctr)))
+        self.acc, self.counters = acc.value, ctr.value
+
+    def clear(self, stream=None):
+        check(load().dusp_mix_acc_clear(self.acc, self.n_floats, self.n_counters, stream))
+
+    def push(self, local_ptr, offset_floats, n_floats, counter_index, ticket_ptr, stream=None):
+        """acc[offset .. offset+n) += local[0..n) (system-scope reductions over NVLink), then counter[index] += 1."""
+        check(load().dusp_mix_push(local_ptr, self.acc + 4 * int(offset_floats), int(n_floats),
+                                   self.counters + 4 * int(counter_index), ticket_ptr, stream))
+
+    def wait(self, counter_index, target, stream=None):
+        check(load().dusp_mix_wait(self.counters + 4 * int(counter_index), int(target), stream))
+
+    def close(self):
+        if self.acc:
+            load().dusp_mix_acc_close(self.acc, 1 if self.owner else 0)
+            self.acc = None

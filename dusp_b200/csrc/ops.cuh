@@ -46,6 +46,22 @@ constexpr double SRD = 44100.0;
 DOPS_DEV double js_or0(double x) { return fabs(x) > 0.0 ? x : 0.0; }  // `x || 0`: NaN, +0, -0 -> +0 (one compare: |x| > 0 is false for all three)
 DOPS_DEV float js_or0f(float x) { return fabsf(x) > 0.0f ? x : 0.0f; }
 
+// Stereo mixdown accumulation (DUSP_OUT_MIX): y[0..B) += into dst[0..B), `room` = samples left before the requested
+// length.  A lane owns B consecutive samples, so the adds go out as 16-byte vector reductions (REDG.ADD.F32x4: one L2
+// atomic per four samples) when the destination is aligned and the run is whole; scalar adds otherwise.
+template <int B>
+DOPS_DEV void mix_add(float *dst, const float (&y)[B], long long room) {
+  if (room >= B && (reinterpret_cast<unsigned long long>(dst) & 15ull) == 0) {
+#pragma unroll
+    for (int q = 0; q < B / 4; q++)
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * q), "f"(y[4 * q]), "f"(y[4 * q + 1]),
+                   "f"(y[4 * q + 2]), "f"(y[4 * q + 3]) : "memory");
+  } else {
+#pragma unroll
+    for (int s = 0; s < B; s++) if (s < room) atomicAdd(dst + s, y[s]);
+  }
+}
+
 // JS `x % 44100` (= C fmod) with exact fast paths for the common range.
 DOPS_DEV double fmod_sr(double x) {
   if (x >= 0.0) {
@@ -405,6 +421,13 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
   }
   const double xlast = x[B - 1];
   auto recur = [&]() {
+#ifdef DOPS_FILT_FENCE
+    // Lane-per-voice warps (T == 1) issue in order: keep the feed-forward half above as one batch of independent
+    // operations (its 2B conversions pipeline through the XU) and the dependent chain below on its own, instead of
+    // ptxas interleaving the two so that every conversion's latency is exposed.  A warp-level sync of the lanes
+    // that are here is the scheduling boundary; it orders nothing the arithmetic depends on.
+    if (T == 1) __syncwarp(__activemask());
+#endif
 #ifdef DOPS_SPEC_FILTER
     // The `|| 0` on the fed-back output (Filter.js:45-48) only ever changes a NaN or a -0.  Run the
     // recurrence without it on the dependency chain, note whether such a value occurred, and in that

@@ -277,9 +277,8 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "#define OUT_CHANNEL_S(a, CH) { if (!kp.out_raw) { UNROLL for (int i_ = 0; i_ < B; i_++) a[i_] = js_or0f(a[i_]); }\\\n"
     << "  if (kp.out_mode == 0) { if (active) { float *dst = out_row + (long long)(CH) * kp.out_len + tl0;\\\n"
     << "      UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) dst[i_] = a[i_]; } }\\\n"
-    << "  else if ((CH) < 2 && active) { UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) {\\\n"
-    << "      atomicAdd(kp.out + (long long)(CH) * kp.out_len + tl0 + i_, a[i_]);\\\n"
-    << "      if (kp.prog_nch == 1) atomicAdd(kp.out + kp.out_len + tl0 + i_, a[i_]); } } }\n"
+    << "  else if ((CH) < 2 && active) { mix_add<B>(kp.out + (long long)(CH) * kp.out_len + tl0, a, kp.n_samples - tl0);\\\n"
+    << "      if (kp.prog_nch == 1) mix_add<B>(kp.out + kp.out_len + tl0, a, kp.n_samples - tl0); } }\n"
     << "extern \"C\" __global__ void __launch_bounds__(" << (NP + 1) * 32 << ", " << min_blocks << ") dusp_piped(const __grid_constant__ FusedParams kp) {\n"
     << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", ROW = STEP / 4, NP = " << NP << ", VW = VC / NP;\n"
     << "  extern __shared__ float4 smem4[];\n"
@@ -349,10 +348,9 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   s << "      }\n"
     << "      if (do2 && kp.out_mode != 0) {  // stereo mixdown of this warp's voices: one atomic per sample and channel\n"
     << "        const long long t2 = (long long)(it - 2) * STEP + lane * B;\n"
-    << "        UNROLL for (int i_ = 0; i_ < B; i_++) if (t2 + i_ < kp.n_samples) {\n"
-    << "          atomicAdd(kp.out + t2 + i_, macc[0][i_]);\n"
-    << "          atomicAdd(kp.out + kp.out_len + t2 + i_, kp.prog_nch == 1 ? macc[0][i_] : macc[1][i_]);\n"
-    << "        }\n"
+    << "        mix_add<B>(kp.out + t2, macc[0], kp.n_samples - t2);\n"
+    << "        if (kp.prog_nch == 1) mix_add<B>(kp.out + kp.out_len + t2, macc[0], kp.n_samples - t2);\n"
+    << "        else mix_add<B>(kp.out + kp.out_len + t2, macc[1], kp.n_samples - t2);\n"
     << "      }\n"
     << "      __syncthreads();\n"
     << "    }\n"

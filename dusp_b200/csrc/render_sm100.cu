@@ -38,6 +38,19 @@ constexpr double SRD = 44100.0;
 // ---------------------------------------------------------------- helpers
 __device__ __forceinline__ double js_or0(double x) { return fabs(x) > 0.0 ? x : 0.0; }  // `x || 0`: NaN, +0, -0 -> +0 (one compare: |x| > 0 is false for all three)
 __device__ __forceinline__ float js_or0f(float x) { return fabsf(x) > 0.0f ? x : 0.0f; }
+// DUSP_OUT_MIX accumulation: 16-byte vector reductions where the run is whole and aligned (same as ops.cuh mix_add)
+template <int B>
+__device__ __forceinline__ void mix_add(float *dst, const float (&y)[B], long long room) {
+  if (room >= B && (reinterpret_cast<unsigned long long>(dst) & 15ull) == 0) {
+#pragma unroll
+    for (int q = 0; q < B / 4; q++)
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * q), "f"(y[4 * q]), "f"(y[4 * q + 1]),
+                   "f"(y[4 * q + 2]), "f"(y[4 * q + 3]) : "memory");
+  } else {
+#pragma unroll
+    for (int s = 0; s < B; s++) if (s < room) atomicAdd(dst + s, y[s]);
+  }
+}
 
 // JS `x % 44100` (= C fmod) with exact fast paths for the common range.
 __device__ __forceinline__ double fmod_sr(double x) {
@@ -1231,15 +1244,17 @@ if (!kp.out_raw) {
             }
           } else if (I.aux0 < 2) {
             // stereo mixdown: mix[c] += out_v[c % nch_v]; tree-sum over the warp's voices, then one atomic per sample
+            float ym[B];
 #pragma unroll
             for (int s = 0; s < B; s++) {
               float y = active ? x[s] : 0.0f;
 #pragma unroll
               for (int o = 16; o >= T; o >>= 1) y += __shfl_xor_sync(0xffffffffu, y, o);
-              if (vi == 0 && tl0 + s < kp.n_samples) {
-                atomicAdd(kp.out + (long long)I.aux0 * kp.out_len + tl0 + s, y);
-                if (prog_nch == 1) atomicAdd(kp.out + kp.out_len + tl0 + s, y);
-              }
+              ym[s] = y;
+            }
+            if (vi == 0) {
+              mix_add<B>(kp.out + (long long)I.aux0 * kp.out_len + tl0, ym, kp.n_samples - tl0);
+              if (prog_nch == 1) mix_add<B>(kp.out + kp.out_len + tl0, ym, kp.n_samples - tl0);
             }
           }
           break;

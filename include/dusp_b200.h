@@ -162,6 +162,27 @@ const char *dusp_session_warning(const dusp_session *s); /* "" or why specialisa
  * non-NULL the generated CUDA source is copied into it. */
 size_t dusp_program_specialise(const dusp_program *p, int sub_block, int time_lanes, char *src_buf, size_t cap);
 
+/* ---- multi-GPU mixdown: one-sided sum over NVLink peer memory ----------------
+ * The reference sums all voices into one stereo signal (Sum.many, src/components/Sum.js:18-29, then
+ * renderChannelData.js:42-44).  With voices sharded over the GPUs of a box, every process adds its DUSP_OUT_MIX
+ * block into an accumulator that lives on the root GPU (csrc/mixpush.cu):
+ *   root:  dusp_mix_acc_create -> device buffer of n_floats f32 + n_counters u32 arrival counters, and a 64-byte
+ *          CUDA IPC handle to hand to the other processes (any byte transport);
+ *   peers: dusp_mix_acc_open maps it (NVLink peer access);  dusp_mix_acc_close(ptr, owner) unmaps / frees;
+ *   all:   dusp_mix_push(local, remote, n, remote_counter, ticket, stream) adds local[0..n) into remote[0..n) with
+ *          system-scope float reductions and then increments *remote_counter once; `ticket` is one zeroed u32 of
+ *          scratch on the pushing GPU;
+ *   root:  dusp_mix_wait(counter, target, stream) holds `stream` until *counter >= target (all ranks arrived);
+ *          dusp_mix_acc_clear zeroes floats and counters for the next render. */
+int dusp_mix_acc_create(int device, size_t n_floats, size_t n_counters, float **acc, unsigned **counters,
+                        unsigned char handle[64]);
+int dusp_mix_acc_open(int device, const unsigned char handle[64], size_t n_floats, float **acc, unsigned **counters);
+int dusp_mix_acc_close(float *acc, int owner);
+int dusp_mix_acc_clear(float *acc, size_t n_floats, size_t n_counters, void *cuda_stream);
+int dusp_mix_push(const float *local, float *remote, size_t n_floats, unsigned *remote_counter, unsigned *ticket,
+                  void *cuda_stream);
+int dusp_mix_wait(const unsigned *counter, unsigned target, void *cuda_stream);
+
 /* The injected PRNG (replaces Math.random in Noise.js:10,23): draw k of stream `seed`. */
 double dusp_rand53(uint64_t seed, uint64_t k);
 

@@ -2,6 +2,8 @@
 oracle on the same inputs.  Bar: bit-exact wherever the device evaluates only
 IEEE +,-,*,/,sqrt and conversions; max-abs <= 1e-5 of full scale (north_star)
 where a libdevice transcendental (tan / pow) is involved."""
+import os
+
 import numpy as np
 import pytest
 
@@ -255,6 +257,47 @@ def test_mixdown_renderer_blocks_match_whole_render(lib):
     s.close()
     assert np.max(np.abs(got - whole)) <= 1e-5 * max(1.0, float(np.max(np.abs(whole))))
     assert float(np.max(np.abs(whole))) > 0.1
+
+
+def test_mix_push_adds_blocks_and_counts_arrivals(lib):
+    """csrc/mixpush.cu on one GPU: three pushes of different blocks into the accumulator (the transport of the
+    multi-GPU mixdown sum, here without a peer) add up exactly and raise the block's arrival counter to 3;
+    dusp_mix_wait then lets the stream through."""
+    import torch
+    n = 2 * 3000 + 2  # not a multiple of the grid stride
+    acc = capi.MixAccumulator(0, 2 * n, 2)
+    ticket = torch.zeros(1, dtype=torch.int32, device="cuda")
+    rng = np.random.default_rng(5)
+    parts = [rng.integers(-8, 9, size=n).astype(np.float32) / 4 for _ in range(3)]  # dyadic: float sums are exact
+    st = torch.cuda.current_stream().cuda_stream
+    acc.clear(st)
+    for part in parts:
+        t = torch.from_numpy(part).cuda()
+        acc.push(t.data_ptr(), n, n, 1, ticket.data_ptr(), st)  # into the second block
+        torch.cuda.synchronize()
+    acc.wait(1, 3, st)
+    torch.cuda.synchronize()
+    from dusp_b200.mixdown import _DevArray
+    got = torch.as_tensor(_DevArray(acc.acc, 2 * n), device="cuda").cpu().numpy()
+    ctr = np.frombuffer(torch.as_tensor(_DevArray(acc.counters, 2), device="cuda").cpu().numpy().tobytes(), dtype=np.uint32)
+    acc.close()
+    assert np.array_equal(got[:n], np.zeros(n, dtype=np.float32))
+    assert np.array_equal(got[n:], parts[0] + parts[1] + parts[2])
+    assert ctr.tolist() == [0, 3] and int(ticket.item()) == 0
+
+
+def test_mixdown_two_gpus_p2p_matches_nccl_and_single_process(lib):
+    """The W5 mixdown on two GPUs (torchrun, one process per GPU): the one-sided NVLink sum and the ncclReduce
+    transport give the same [2][n] mix as one process rendering all voices (1e-5 of the mix's full scale)."""
+    import subprocess, sys, torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    script = os.path.join(os.path.dirname(os.path.abspath(__file__)), "mgpu_mix_check.py")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29731", script],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "MIX-CHECK OK" in r.stdout
 
 
 def test_w4_random_circuits_in_one_multi_program_launch(lib, oracle):
