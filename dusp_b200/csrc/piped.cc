@@ -243,6 +243,9 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   const size_t xb_bytes = (size_t)3 * NB * VC * STEP * sizeof(float);
   // optional dynamic voice queue for the P-warps (measured slightly slower than the static split: off)
   const bool dyn = getenv("DUSP_PIPED_DYN") != nullptr;
+  const char *srot_env = getenv("DUSP_PIPED_SROT");  // "rot" or a fixed warp index 0..NP (experiments)
+  const bool srot = srot_env != nullptr;
+  const int srot_fixed = srot && srot_env[0] >= '0' && srot_env[0] <= '9' ? std::min(atoi(srot_env), NP) : -1;
   const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double) + 16;
   if (smem > 200 * 1024) return "";
   if (info) {
@@ -286,7 +289,13 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "  double *const pw = reinterpret_cast<double *>(smem4 + 3 * NB * VC * ROW);  // [" << NPW << "][VC] words of the P-warps' units\n"
     << "  int *const qctr = reinterpret_cast<int *>(pw + " << NPW << " * VC);                 // [3] per-step voice queue heads\n"
     << "  if (threadIdx.x < 3) qctr[threadIdx.x] = 0;\n"
-    << "  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;\n"
+    << "  const int lane = threadIdx.x & 31, wraw = threadIdx.x >> 5;\n"
+    // Which warp of the CTA is the lane-per-voice warp.  Warps go to the SM's four schedulers by warp index, and the
+    // CTAs resident on one SM are blockIdx, blockIdx + #SMs, ...: rotating the role by blockIdx / #SMs puts the
+    // (latency-critical) S-warps of co-resident CTAs on different schedulers.  wib: P-warps 0..NP-1, S-warp NP.
+    << (srot ? std::string("  const int s_raw = ") + (srot_fixed >= 0 ? std::to_string(srot_fixed) : std::string("(blockIdx.x / 148) % (NP + 1)")) + ";\n"
+               "  const int wib = wraw == s_raw ? NP : wraw - (wraw > s_raw ? 1 : 0);\n"
+             : std::string("  const int wib = wraw;\n"))
     << "  const long long v0 = (long long)blockIdx.x * VC;  // allocations are padded to a multiple of 96 voices\n"
     << "  const size_t nv = (size_t)kp.nv_stride;\n"
     << "  const float *const tables = kp.tables; (void)tables; (void)xb; (void)pw; (void)qctr;\n"

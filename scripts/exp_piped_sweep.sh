@@ -1,6 +1,4 @@
 cd /root/repo
 W=w3:10000:88064:0
-python scripts/perf_probe4.py "p24;p24,DOPS_FILT_FENCE;p32,DOPS_FILT_FENCE;p16,DOPS_FILT_FENCE" $W
-DUSP_PIPED_PWARPS=3 python scripts/perf_probe4.py "p24,DOPS_FILT_FENCE" $W
-DUSP_PIPED_PWARPS=6 python scripts/perf_probe4.py "p24,DOPS_FILT_FENCE" $W
-DUSP_PIPED_PWARPS=2 python scripts/perf_probe4.py "p24,DOPS_FILT_FENCE" $W
+python scripts/perf_probe4.py "p24" $W
+for v in rot 0 1 2 3; do DUSP_PIPED_SROT=$v python scripts/perf_probe4.py "p24" $W; done

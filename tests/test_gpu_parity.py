@@ -231,6 +231,51 @@ def test_full_size_w2_properties(lib):
     assert len({got[v, 0].tobytes() for v in range(1, 50)}) == 49  # distinct voices differ
 
 
+def test_full_size_w3_properties(lib, oracle):
+    """BASELINE config 2 at its full voice count (10 000 voices of the Noise -> LP -> feedback delay -> Pan patch,
+    bench.py's generator, 1 s): a spread of voices equals the oracle's stand-alone render of that voice's circuit
+    bit for bit; rendering in two blocks equals rendering at once for EVERY voice; the stereo mixdown of the same
+    batch equals the sum of the per-voice renders; no NaN anywhere."""
+    import torch
+    from dusp_b200 import workloads as W
+    n, ns = 10000, SR
+    blob, _ = circuit_blob(W.w3_circuit())
+    params = W.w3_params(0, n)
+    ov = W.w3_overrides(blob, params)
+    p = capi.Program(blob)
+    s = capi.Session([p], [n], 0)
+    s.set_params(0, list(ov), np.stack([ov[k] for k in ov], axis=1))
+    whole = torch.empty(n * 2 * ns, dtype=torch.float32, device="cuda")
+    s.render_device(ns, whole.data_ptr())
+    torch.cuda.synchronize()
+    assert s.launch_info()["specialised"] and s.launch_info()["block"] == 160  # the pipelined kernel, as benchmarked
+    whole = whole.view(n, 2, ns)
+    for v in (0, 1, 23, 24, 4999, 7777, 9983, 9999):  # first / last lanes and CTAs of the 24-voice tiling
+        vb, _ = circuit_blob(W.w3_voice_circuit(params, v))
+        compare(whole[v].cpu().numpy(), oracle.render(vb, 1.0), False, "full-size w3 voice %d" % v)
+    assert not bool(torch.isnan(whole).any())
+    # two blocks (second one not chunk-aligned in length) == one render, for every voice
+    s.reset()
+    n1 = 20480
+    a = torch.empty(n * 2 * n1, dtype=torch.float32, device="cuda")
+    b = torch.empty(n * 2 * (ns - n1), dtype=torch.float32, device="cuda")
+    s.render_device(n1, a.data_ptr())
+    s.render_device(ns - n1, b.data_ptr())
+    torch.cuda.synchronize()
+    assert torch.equal(a.view(n, 2, n1), whole[:, :, :n1])
+    assert torch.equal(b.view(n, 2, ns - n1), whole[:, :, n1:])
+    del a, b
+    # mixdown of the batch == sum over voices (float summation order differs: tolerance of the mix's full scale)
+    s.reset()
+    mix = torch.empty(2 * ns, dtype=torch.float32, device="cuda")
+    s.render_device(ns, mix.data_ptr(), capi.OUT_MIX)
+    torch.cuda.synchronize()
+    want = whole.double().sum(dim=0)
+    scale = max(1.0, float(want.abs().max()))
+    assert float((mix.view(2, ns).double() - want).abs().max()) <= 1e-5 * scale
+    s.close()
+
+
 def test_mixdown_renderer_blocks_match_whole_render(lib):
     """dusp_b200.mixdown.MixdownRenderer (the multi-GPU mix path; here one GPU, no process group): block-wise
     OUT_MIX renders into rotating device buffers equal one whole-length mix render."""
