@@ -421,13 +421,6 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
   }
   const double xlast = x[B - 1];
   auto recur = [&]() {
-#ifdef DOPS_FILT_FENCE
-    // Lane-per-voice warps (T == 1) issue in order: keep the feed-forward half above as one batch of independent
-    // operations (its 2B conversions pipeline through the XU) and the dependent chain below on its own, instead of
-    // ptxas interleaving the two so that every conversion's latency is exposed.  A warp-level sync of the lanes
-    // that are here is the scheduling boundary; it orders nothing the arithmetic depends on.
-    if (T == 1) __syncwarp(__activemask());
-#endif
 #ifdef DOPS_SPEC_FILTER
     // The `|| 0` on the fed-back output (Filter.js:45-48) only ever changes a NaN or a -0.  Run the
     // recurrence without it on the dependency chain, note whether such a value occurred, and in that
