@@ -235,3 +235,30 @@ def test_then_number_and_downstream_state(oracle):
     n0 = 43 * 256
     phase = np.where(n < n0, 100 * (n + 1), 100 * n0 + 300 * (n - n0 + 1)) % 44100
     assert np.array_equal(out, tab[phase].astype(np.float32))
+
+
+@pytest.mark.parametrize("n", [2, 4, 8, 16, 64, 256, 1024, 4096])
+def test_fft_restatement_matches_the_dft(oracle, n):
+    """Third-party arithmetic: spectral/FFT.js:2,16 and IFFT.js:2,12 call the un-vendored package `fft.js`
+    (package.json "^4.0.3").  The oracle restates its radix-4 realTransform + completeSpectrum, transform and
+    inverseTransform; this pins the restatement against the definition of the DFT (numpy) at the sizes the
+    reference uses (config.js:10-14: window 4096) and the small ones its radix-2 / radix-4 base cases hit."""
+    rng = np.random.default_rng(n)
+    x = rng.standard_normal(n)
+    ref = np.fft.fft(x)
+    got = oracle.fft(x, "real")
+    assert np.max(np.abs((got[0::2] + 1j * got[1::2]) - ref)) <= 1e-12 * max(1.0, float(np.max(np.abs(ref))))
+    z = rng.standard_normal(2 * n)
+    zc = z[0::2] + 1j * z[1::2]
+    ref = np.fft.fft(zc)
+    got = oracle.fft(z, "complex")
+    assert np.max(np.abs((got[0::2] + 1j * got[1::2]) - ref)) <= 1e-12 * max(1.0, float(np.max(np.abs(ref))))
+    got = oracle.fft(z, "inverse")  # fft.js divides by N, like numpy's ifft
+    assert np.max(np.abs((got[0::2] + 1j * got[1::2]) - np.fft.ifft(zc))) <= 1e-12
+
+
+def test_fft_rejects_sizes_fft_js_rejects(oracle):
+    from oracle.oracle import OracleError
+    for n in (1, 3, 12, 100):
+        with pytest.raises(OracleError):
+            oracle.fft(np.zeros(n), "real")
