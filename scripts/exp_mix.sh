@@ -1,4 +1,4 @@
-cd /root/repo
+cd "$(dirname "$0")/.."
 python -m pytest tests -m gpu -x -q -k "mix or Mix or w5 or W5" 2>&1 | tail -2
 # mix-mode probes of the two W5 voice kinds (6250 voices each, 2 s block)
 DUSP_PIPED=0 python scripts/perf_probe4.py "t" w2:6250:88064:1 w2:6250:88064:0
