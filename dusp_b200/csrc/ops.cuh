@@ -111,6 +111,20 @@ DOPS_DEV double rand53_mixed(uint64_t z) {
   const double lo = __hiloint2double(0x43300000, (int)(uint32_t)z) - 4503599627370496.0;
   return fma(hi, 4294967296.0, lo) * (1.0 / 9007199254740992.0);
 }
+// Noise.js:10,23 `Math.random()*2 - 1` on a pre-formed counter word, in one FP64 operation.  With k the 53-bit draw,
+// rand = k 2^-53 and 2 rand - 1 = (k - 2^52) 2^-52, every step exact in double.  Writing k = b 2^52 + m, the double
+// 1.m (exponent 0x3FF, mantissa m) is 1 + m 2^-52, so the result is 1.m - 1 (b = 1) or 1.m - 2 (b = 0): both exact
+// differences, bit-identical to the two-rounding-free products of the literal form (6 FP64 operations).
+DOPS_DEV double noise_bipolar_mixed(uint64_t z) {
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  z ^= z >> 31;
+  z >>= 11;
+  const uint32_t hi = (uint32_t)(z >> 32), lo = (uint32_t)z;  // hi: 21 bits, bit 20 = b
+  const double one_m = __hiloint2double((int)(0x3FF00000u | (hi & 0xFFFFFu)), (int)lo);
+  const double off = __hiloint2double((int)(0x40000000u - (hi & 0x100000u)), 0);  // b ? 1.0 : 2.0
+  return one_m - off;
+}
 DOPS_DEV double dB(double db) { return pow(10.0, db / 20.0); }  // Gain.js:26-28, Pan.js:26-28
 
 // ------------------------------------------------------------------- lane context
@@ -334,7 +348,7 @@ DOPS_DEV void c_noise(const Cx<B, T> &cx, float (&f)[B], double &ph, double &y, 
       ph += (double)f[s];
       if (ph >= SRD) {
         ph = 0.0;
-        y = 2.0 * rand53(seed, (uint64_t)draw) - 1.0;
+        y = noise_bipolar_mixed(seed + ((uint64_t)draw + 1) * 0x9E3779B97F4A7C15ULL);
         draw += 1.0;
       }
       f[s] = (float)y;
@@ -348,7 +362,7 @@ DOPS_DEV void c_noise1(const Cx<B, T> &cx, float (&o)[B], double &y, double &dra
   const uint64_t d0 = (uint64_t)draw + (uint64_t)(cx.tl * B);
   uint64_t z = seed + (d0 + 1) * 0x9E3779B97F4A7C15ULL;
 #pragma unroll
-  for (int s = 0; s < B; s++) { y = 2.0 * rand53_mixed(z) - 1.0; o[s] = (float)y; z += 0x9E3779B97F4A7C15ULL; }
+  for (int s = 0; s < B; s++) { y = noise_bipolar_mixed(z); o[s] = (float)y; z += 0x9E3779B97F4A7C15ULL; }
   draw += (double)(T * B);
   cx.last(y);
 }
