@@ -243,6 +243,8 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   const size_t xb_bytes = (size_t)3 * NB * VC * STEP * sizeof(float);
   // optional dynamic voice queue for the P-warps (measured slightly slower than the static split: off)
   const bool dyn = getenv("DUSP_PIPED_DYN") != nullptr;
+  int s_unroll = PB == 4 ? 2 : 1;  // S-warp groups per loop body; DUSP_PIPED_SUNROLL overrides (experiments)
+  if (const char *e = getenv("DUSP_PIPED_SUNROLL")) s_unroll = std::max(1, std::min(8, atoi(e)));
   const char *srot_env = getenv("DUSP_PIPED_SROT");  // "rot" or a fixed warp index 0..NP (experiments)
   const bool srot = srot_env != nullptr;
   const int srot_fixed = srot && srot_env[0] >= '0' && srot_env[0] <= '9' ? std::min(atoi(srot_env), NP) : -1;
@@ -381,7 +383,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   if (stage_has[1]) {
     s << "      if (it >= 1 && it <= n_steps && lane < VC) {\n"
       << "        const int rot1 = (it + 2) % 3;  // (it - 1) mod 3\n"
-      << "        _Pragma(\"unroll " << (PB == 4 ? 2 : 1) << "\")\n"
+      << "        _Pragma(\"unroll " << s_unroll << "\")\n"
       << "        for (int g = 0; g < STEP / B; g++) {\n"
       << "          const long long tl0 = (long long)(it - 1) * STEP + g * B;\n"
       << "          const int cpos = (int)(tl0 & (DUSP_CHUNK - 1)); (void)cpos;\n"
