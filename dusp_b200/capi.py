@@ -89,7 +89,7 @@ def load():
     L.dusp_mix_acc_close.argtypes = [c.c_void_p, c.c_int]
     L.dusp_mix_acc_clear.argtypes = [c.c_void_p, c.c_size_t, c.c_size_t, c.c_void_p]
     L.dusp_mix_push.argtypes = [c.c_void_p, c.c_void_p, c.c_size_t, c.c_void_p, c.c_void_p, c.c_void_p]
-    L.dusp_mix_wait.argtypes = [c.c_void_p, c.c_uint, c.c_void_p]
+    L.dusp_mix_wait.argtypes = [c.c_void_p, c.c_uint, c.c_void_p, c.c_void_p]
     if L.dusp_abi_version() != 1:
         raise RuntimeError("libdusp_b200.so ABI version mismatch")
     assert config.sampleRate == 44100 and config.standardChunkSize == 256  # compiled into the kernels
@@ -283,7 +283,13 @@ class MixAccumulator:
                                    self.counters + 4 * int(counter_index), ticket_ptr, stream))
 
     def wait(self, counter_index, target, stream=None):
-        check(load().dusp_mix_wait(self.counters + 4 * int(counter_index), int(target), stream))
+        """Holds ``stream`` until counter[index] >= target; a wait that gives up (~30 s) bumps the spare counter
+        behind the last one, which ``timed_out_ptr`` addresses (the host reads it after the render)."""
+        check(load().dusp_mix_wait(self.counters + 4 * int(counter_index), int(target), self.timed_out_ptr, stream))
+
+    @property
+    def timed_out_ptr(self):
+        return self.counters + 4 * self.n_counters
 
     def close(self):
         if self.acc:

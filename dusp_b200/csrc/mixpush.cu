@@ -10,6 +10,7 @@
 //   rank r: dusp_mix_push  -- grid-stride kernel on the render stream: red.add.f32 (system scope) of the local block
 //           into acc[b] over NVLink, then __threadfence_system and one counter increment by the last CTA
 //   root:   dusp_mix_wait  -- a one-thread kernel on the consumer stream polls counter[b] until all ranks arrived
+//           (bounded: after ~30 s it records the miss in a flag the host checks)
 //
 // Nothing waits for a peer except the root's consumer, so a late rank delays only the block it is late for.
 #include <cuda_runtime.h>
@@ -43,8 +44,13 @@ __global__ void mix_push_kernel(const float *__restrict__ local, float *remote, 
   }
 }
 
-__global__ void mix_wait_kernel(const volatile unsigned *counter, unsigned target) {
-  while (*counter < target) __nanosleep(200);
+// Bounded: a rank that died must not leave the root's stream spinning for ever.  ~30 s of polling, then the miss is
+// recorded in *timed_out (checked by the host after the render) and the stream moves on.
+__global__ void mix_wait_kernel(const volatile unsigned *counter, unsigned target, unsigned *timed_out) {
+  for (long long spins = 0; *counter < target; spins++) {
+    if (spins > 30000000LL) { if (timed_out) atomicAdd(timed_out, 1u); break; }
+    __nanosleep(1000);
+  }
   __threadfence_system();
 }
 
@@ -107,9 +113,9 @@ int dusp_mix_push(const float *local, float *remote, size_t n_floats, unsigned *
   return e == cudaSuccess ? DUSP_OK : dusp::fail_public(DUSP_ECUDA, std::string("dusp_mix_push: ") + cudaGetErrorString(e));
 }
 
-int dusp_mix_wait(const unsigned *counter, unsigned target, void *cuda_stream) {
+int dusp_mix_wait(const unsigned *counter, unsigned target, unsigned *timed_out, void *cuda_stream) {
   if (!counter) return dusp::fail_public(DUSP_EINVAL, "dusp_mix_wait: null argument");
-  mix_wait_kernel<<<1, 1, 0, (cudaStream_t)cuda_stream>>>(counter, target);
+  mix_wait_kernel<<<1, 1, 0, (cudaStream_t)cuda_stream>>>(counter, target, timed_out);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? DUSP_OK : dusp::fail_public(DUSP_ECUDA, std::string("dusp_mix_wait: ") + cudaGetErrorString(e));
 }

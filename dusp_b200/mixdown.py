@@ -148,6 +148,9 @@ class MixdownRenderer:
                 consume(b - 1)  # one block late: the peers have had a whole block's time to arrive
         if self.rank == 0:
             consume(len(blocks) - 1)
+            flag = torch.as_tensor(_DevArray(self.acc.timed_out_ptr, 1), device=self.device)  # 4 bytes, bit pattern of a u32
+            if int(flag.view(torch.int32).item()) != 0:
+                raise capi.DuspError("mixdown: a rank's block never arrived at the accumulator (waited 30 s)")
 
     def close(self):
         if self.acc is not None:

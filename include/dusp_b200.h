@@ -172,7 +172,8 @@ size_t dusp_program_specialise(const dusp_program *p, int sub_block, int time_la
  *   all:   dusp_mix_push(local, remote, n, remote_counter, ticket, stream) adds local[0..n) into remote[0..n) with
  *          system-scope float reductions and then increments *remote_counter once; `ticket` is one zeroed u32 of
  *          scratch on the pushing GPU;
- *   root:  dusp_mix_wait(counter, target, stream) holds `stream` until *counter >= target (all ranks arrived);
+ *   root:  dusp_mix_wait(counter, target, timed_out, stream) holds `stream` until *counter >= target (all ranks
+ *          arrived) or ~30 s have passed, in which case *timed_out (device memory, may be NULL) is incremented;
  *          dusp_mix_acc_clear zeroes floats and counters for the next render. */
 int dusp_mix_acc_create(int device, size_t n_floats, size_t n_counters, float **acc, unsigned **counters,
                         unsigned char handle[64]);
@@ -181,7 +182,7 @@ int dusp_mix_acc_close(float *acc, int owner);
 int dusp_mix_acc_clear(float *acc, size_t n_floats, size_t n_counters, void *cuda_stream);
 int dusp_mix_push(const float *local, float *remote, size_t n_floats, unsigned *remote_counter, unsigned *ticket,
                   void *cuda_stream);
-int dusp_mix_wait(const unsigned *counter, unsigned target, void *cuda_stream);
+int dusp_mix_wait(const unsigned *counter, unsigned target, unsigned *timed_out, void *cuda_stream);
 
 /* The injected PRNG (replaces Math.random in Noise.js:10,23): draw k of stream `seed`. */
 double dusp_rand53(uint64_t seed, uint64_t k);
