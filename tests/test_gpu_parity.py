@@ -276,6 +276,33 @@ def test_full_size_w3_properties(lib, oracle):
     s.close()
 
 
+@pytest.mark.parametrize("n", [1001, 4999, 256 * 9 + 3])
+def test_mixdown_ragged_lengths_all_kernel_paths(lib, kernel_mode, n):
+    """DUSP_OUT_MIX at lengths that are no multiple of 4: channel 1 of the [2][n] mix then starts unaligned and the
+    last run of every lane is partial, so the epilogue's 16-byte vector reductions must fall back to scalar adds
+    exactly there (ops.cuh / render_sm100.cu mix_add).  Mix == sum over the per-voice renders, mono (W2: copied to
+    both channels) and stereo (W3) programs in one session."""
+    from dusp_b200 import workloads as W
+    i2, i3 = W.w5_split(0, 14)
+    b2, _ = circuit_blob(W.w2_live_circuit())
+    b3, _ = circuit_blob(W.w3_circuit())
+    p2, p3 = capi.Program(b2), capi.Program(b3)
+    s = capi.Session([p2, p3], [len(i2), len(i3)], 0)
+    o2, o3 = W.w2_overrides(b2, W.w2_params(0, 0, i2)), W.w3_overrides(b3, W.w3_params(0, 0, i3))
+    s.set_params(0, list(o2), np.stack([o2[k] for k in o2], axis=1))
+    s.set_params(1, list(o3), np.stack([o3[k] for k in o3], axis=1))
+    voices = s.render_host(n).astype(np.float64)          # [14][2][n]; a mono program leaves channel 1 zero
+    s.reset()
+    mix = s.render_host(n, capi.OUT_MIX).astype(np.float64)
+    s.close()
+    want = voices.sum(axis=0)
+    want[1] += voices[:len(i2), 0].sum(axis=0)             # mono voices go to both mix channels
+    scale = max(1.0, float(np.max(np.abs(want))))
+    assert mix.shape == (2, n)
+    assert float(np.max(np.abs(mix - want))) <= 1e-5 * scale
+    assert float(np.max(np.abs(want))) > 0.1
+
+
 def test_mixdown_renderer_blocks_match_whole_render(lib):
     """dusp_b200.mixdown.MixdownRenderer (the multi-GPU mix path; here one GPU, no process group): block-wise
     OUT_MIX renders into rotating device buffers equal one whole-length mix render."""
