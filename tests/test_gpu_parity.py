@@ -193,6 +193,28 @@ def test_multi_program_session(lib, oracle, kernel_mode):
             row += 1
 
 
+def test_concurrent_group_launches_give_the_same_render(lib, oracle, kernel_mode, monkeypatch):
+    """DUSP_CONCURRENT_GROUPS=1 (opt-in, capi.cc enqueue_block): the program groups of a session launch on side
+    streams between a fork and a join event instead of in sequence.  Same output, block after block."""
+    cases = ["w2_live", "w3_voice", "fixed_delays", "stereo_concat"]
+    blobs = [circuit_blob(circuits.CASES[c][0]())[0] for c in cases]
+
+    def render():
+        progs = [capi.Program(b) for b in blobs]
+        s = capi.Session(progs, [3, 2, 1, 2], 0)
+        a = s.render_host(3072)
+        b = s.render_host(1536)  # a second block (whole chunks) continues the state through the join
+        s.close()
+        return np.concatenate([a, b], axis=2)
+
+    seq = render()
+    monkeypatch.setenv("DUSP_CONCURRENT_GROUPS", "1")
+    par = render()
+    assert np.array_equal(seq, par)
+    want = oracle.render(blobs[1], 4608 / SR)
+    compare(par[3][:len(want)], want, circuits.CASES["w3_voice"][2], "w3_voice on a side stream")
+
+
 def test_unsupported_voice_parameters_are_rejected(lib):
     blob, _ = circuit_blob(circuits.w3_voice())
     p = capi.Program(blob)
