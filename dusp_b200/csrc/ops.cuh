@@ -187,6 +187,36 @@ DOPS_DEV void serial3(const Cx<B, T> &cx, double &s0, double &s1, double &s2, F 
 // Osc.js:35-47 (negfix) / MultiChannelOsc.js:21-38 (!negfix): B samples from phase `ph`.
 template <int B>
 DOPS_DEV void osc_run(float (&f)[B], double &ph, const float *__restrict__ tab, bool negfix) {
+  if (negfix) {
+    // Straight-line form for the usual case: while phase + f stays inside (-SR, 2 SR), `% SR` and the negative fix are
+    // one exact add or subtract chosen by two compares (Osc.js:40-42), so the B samples run without a branch; whether
+    // every phase stayed in range is checked once, and if not the run is redone from the saved phase below.
+    double p = ph, q[B];
+    bool ok = true;
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      const double x = p + (double)f[s];
+      ok = ok && x > -SRD && x < 2.0 * SRD;
+      p = x < 0.0 ? x + SRD : (x >= SRD ? x - SRD : x);
+      q[s] = p;
+    }
+    // (p == SR can still come out of x + SR for a tiny negative x: the literal code reads the table's end there too)
+    if (ok) {
+#pragma unroll
+      for (int s = 0; s < B; s++) ok = ok && q[s] < SRD;
+    }
+    if (ok) {
+#pragma unroll
+      for (int s = 0; s < B; s++) {
+        const int i = __double2int_rz(q[s]);
+        const double fr = q[s] - (double)i;
+        const double a = (double)__ldg(tab + i), b = (double)__ldg(tab + i + (fr != 0.0));
+        f[s] = (float)(a * (1.0 - fr) + b * fr);
+      }
+      ph = p;
+      return;
+    }
+  }
 #pragma unroll
   for (int s = 0; s < B; s++) {
     ph += (double)f[s];
