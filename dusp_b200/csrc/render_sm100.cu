@@ -193,6 +193,34 @@ __device__ __forceinline__ double dB(double db) { return pow(10.0, db / 20.0); }
 template <int B, int T>
 __device__ __forceinline__ void osc_body(const Lane<B, T> &L, const DuspDevInstr &I, float (&f)[B], double &ph, bool negfix) {
   const float *tab = L.tables + (size_t)I.aux0 * DUSP_TABLE_LEN;
+  if (negfix) {
+    // straight-line form while phase + f stays inside (-SR, 2 SR) (same as ops.cuh osc_run): `% SR` and the negative fix
+    // are one exact add or subtract chosen by two compares; validity is checked once per run, else the literal loop below
+    double p = ph, q[B];
+    bool ok = true;
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      const double x = p + (double)f[s];
+      ok = ok && x > -SRD && x < 2.0 * SRD;
+      p = x < 0.0 ? x + SRD : (x >= SRD ? x - SRD : x);
+      q[s] = p;
+    }
+    if (ok) {
+#pragma unroll
+      for (int s = 0; s < B; s++) ok = ok && q[s] < SRD;
+    }
+    if (ok) {
+#pragma unroll
+      for (int s = 0; s < B; s++) {
+        const int i = __double2int_rz(q[s]);
+        const double fr = q[s] - (double)i;
+        const double a = (double)__ldg(tab + i), b = (double)__ldg(tab + i + (fr != 0.0));
+        f[s] = (float)(a * (1.0 - fr) + b * fr);
+      }
+      ph = p;
+      return;
+    }
+  }
 #pragma unroll
   for (int s = 0; s < B; s++) {
     ph += (double)f[s];
