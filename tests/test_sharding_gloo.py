@@ -50,6 +50,10 @@ def _worker(rank, world, port, out_path):
     t = torch.from_numpy(_local_mix(range(v0, v0 + n)))
     work = mixdown.reduce_mix(t, dst=0, async_op=True)
     work.wait()
+    # transport selection of the renderer: the one-sided NVLink path is for CUDA ranks only; CPU ranks reduce through
+    # torch.distributed, and an explicit request is honoured
+    assert mixdown.MixdownRenderer(None, 256, "cpu").collective == "nccl"
+    assert mixdown.MixdownRenderer(None, 256, "cpu", collective="nccl").collective == "nccl"
     if rank == 0:
         np.save(out_path, t.numpy())
     dist.barrier()
@@ -73,3 +77,9 @@ def test_reduce_without_process_group_is_a_noop():
     import torch
     t = torch.ones(2, 4)
     assert mixdown.reduce_mix(t) is None and float(t.sum()) == 8.0
+
+
+def test_renderer_without_process_group_has_no_collective():
+    r = mixdown.MixdownRenderer(None, 256, "cpu")
+    assert r.collective == "none" and r.world == 1 and r.rank == 0 and r.acc is None and r.ticket is None
+    r.close()
