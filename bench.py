@@ -321,6 +321,7 @@ def run_b200(args, rank, world, local_rank):
         dwords = np.stack([ov[k] for k in ov], axis=1)
 
         def step_e2e():
+            sess.reset()                          # a step is a whole render from clock 0
             sess.set_params(0, list(ov), dwords)  # per-step inputs: the voices' parameters (H2D on first launch)
             sess.render_into_host(hbuf.data_ptr(), n_e2e, capi.OUT_VOICES)
 

@@ -390,6 +390,9 @@ int dusp_session_launch_info(const dusp_session *s, int *grid, int *block, int *
 int dusp_session_set_params(dusp_session *s, int gi, const int *ids, int n_ids, const double *values) {
   if (!s || gi < 0 || gi >= (int)s->groups.size() || !ids || !values || n_ids < 0)
     return fail(DUSP_EINVAL, "dusp_session_set_params: bad arguments");
+  // parameters (re)initialise a group at clock 0; in a session that has rendered, the other groups would keep
+  // their advanced oscillator phases / filter memory / rings while clock-indexed units restart: refuse instead
+  if (s->clock != 0) return fail(DUSP_EINVAL, "dusp_session_set_params: the session has rendered; call dusp_session_reset first");
   Group &g = s->groups[gi];
   const int nw = (int)g.prog.words.size();
   for (int k = 0; k < n_ids; k++)
@@ -412,7 +415,6 @@ int dusp_session_set_params(dusp_session *s, int gi, const int *ids, int n_ids, 
   }
   for (int v = 0; v < g.n_voices; v++) derive_words(g.prog, g.h_words.data() + v, g.nv_pad);
   g.dirty = true;
-  s->clock = 0;
   return DUSP_OK;
 }
 
@@ -679,7 +681,6 @@ int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, floa
                         void *cuda_stream) {
   if (!s || n_samples < 0 || (out_mode != DUSP_OUT_VOICES && out_mode != DUSP_OUT_MIX && out_mode != DUSP_OUT_VOICES_RAW) || (!out_host == !out_device))
     return fail(DUSP_EINVAL, "dusp_session_render: bad arguments");
-  if (s->clock % DUSP_CHUNK) return fail(DUSP_EINVAL, "dusp_session_render: a previous render ended inside a chunk");
   CUDA_TRY(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)cuda_stream;
   if (n_samples == 0) return DUSP_OK;

@@ -234,21 +234,44 @@ DOPS_DEV void osc_run(float (&f)[B], double &ph, const float *__restrict__ tab, 
   }
 }
 
-// Osc.js:35-47.  T > 1: phase at a lane's first sample = (phase + all earlier increments) mod 44100,
-// from an exclusive scan of per-lane sums (exact for f32 increments of audio-range magnitude).
+// (a + b) mod 44100 for a, b in [0, 44100): exact when a + b is
+DOPS_DEV double wrap_add_sr(double a, double b) {
+  const double x = a + b;
+  return x >= SRD ? x - SRD : x;
+}
+
+// Osc.js:35-47.  T > 1: phase at a lane's first sample = (phase + all earlier increments) mod 44100, from an
+// exclusive scan over the time-lanes.  The scan works on phases REDUCED to [0, 44100) (per-lane partial sums wrap
+// like the oscillator itself does, partial results combine with wrap_add_sr), so every number it forms is below
+// 2^17.  It equals the reference's sample-by-sample `phase += f; phase %= SR` exactly when no addition on either
+// side rounds: guaranteed here by checking that the start phase and every increment of the tile are multiples of
+// 2^-36 (any f32 with |f| >= 2^-13, or 0) and |f| < 44100 -- then all intermediate values are multiples of 2^-36
+// below 2^17, i.e. representable.  Tiles that fail the check (sub-audio increments below 1.3e-4 Hz, |f| >= SR,
+// NaN / Infinity, a start phase with finer bits) run the lanes one after the other in the reference's order.
 template <int B, int T>
 DOPS_DEV void c_osc(const Cx<B, T> &cx, float (&f)[B], double &ph, const float *__restrict__ tab) {
   if (T > 1) {
-    double sum = 0.0;
+    bool ok = ph >= 0.0 && ph < SRD && (ph + 65536.0) - 65536.0 == ph;  // multiple of 2^-36 (ulp of [2^16, 2^17))
+    double part = 0.0;  // this lane's increments, reduced to [0, 44100)
 #pragma unroll
-    for (int s = 0; s < B; s++) sum += (double)f[s];
-    const double before = cx.excl_scan(sum);
-    const bool finite = __all_sync(0xffffffffu, fabs(before + sum) < 1.0e12);
-    if (!finite) {  // NaN / Infinity frequencies: the reference's exact sequential behaviour
+    for (int s = 0; s < B; s++) {
+      const uint32_t u = __float_as_uint(f[s]) & 0x7fffffffu;
+      ok = ok && (u == 0u || (u >= 0x39000000u && u < 0x472C4400u));  // 0, or 2^-13 <= |f| < 44100
+      const double x = part + (double)f[s];
+      part = x < 0.0 ? x + SRD : (x >= SRD ? x - SRD : x);
+    }
+    if (!__all_sync(0xffffffffu, ok)) {
       serial1<B, T>(cx, ph, [&] { osc_run<B>(f, ph, tab, true); });
       return;
     }
-    if (cx.tl > 0) ph = posmod_sr(ph + before);
+    double incl = part;
+#pragma unroll
+    for (int o = 1; o < T; o <<= 1) {
+      const double y = __shfl_up_sync(0xffffffffu, incl, o, T);
+      if (cx.tl >= o) incl = wrap_add_sr(incl, y);
+    }
+    const double before = __shfl_up_sync(0xffffffffu, incl, 1, T);
+    if (cx.tl > 0) ph = wrap_add_sr(ph, before);
   }
   osc_run<B>(f, ph, tab, true);
   cx.last(ph);

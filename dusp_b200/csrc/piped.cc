@@ -274,7 +274,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     // renderChannelData.js:42-44 for the P-warps: lanes along time, a warp stores 512 contiguous bytes
     << "#define OUT_CHANNEL_P(a, CH) { if (!kp.out_raw) { UNROLL for (int i_ = 0; i_ < B; i_++) a[i_] = js_or0f(a[i_]); }\\\n"
     << "  if (kp.out_mode == 0) { if (active) { float *dst = out_row + (long long)(CH) * kp.out_len + tl0;\\\n"
-    << "      if (tl0 + B <= kp.n_samples && (kp.out_len & 3) == 0) { UNROLL for (int q_ = 0; q_ < B / 4; q_++)\\\n"
+    << "      if (tl0 + B <= kp.n_samples && ((kp.out_len & 3) | (reinterpret_cast<unsigned long long>(kp.out) & 15ull)) == 0) { UNROLL for (int q_ = 0; q_ < B / 4; q_++)\\\n"
     << "        __stcs(reinterpret_cast<float4 *>(dst) + q_, make_float4(a[4*q_], a[4*q_+1], a[4*q_+2], a[4*q_+3])); }\\\n"
     << "      else { UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) dst[i_] = a[i_]; } } }\\\n"
     << "  else if ((CH) < 2 && active) { UNROLL for (int i_ = 0; i_ < B; i_++) macc[CH][i_] += a[i_]; } }\n"

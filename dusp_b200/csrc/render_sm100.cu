@@ -30,6 +30,7 @@
 
 #include "vm.h"
 #include "launch.h"
+#include "ops.cuh"  // the unit cores shared with the specialised kernels
 
 namespace {
 
@@ -239,25 +240,12 @@ __device__ __forceinline__ void osc_body(const Lane<B, T> &L, const DuspDevInstr
 }
 
 template <int B, int T>
-__device__ __forceinline__ void op_osc(const Lane<B, T> &L, const DuspDevInstr &I) {
+__device__ __forceinline__ void op_osc(const Lane<B, T> &L, const DuspDevInstr &I) {  // Osc.js:35-47: the core in ops.cuh
   float f[B];
   L.ld(f, I.in[0]);
   double ph = L.w(I.p);
-  if (T > 1) {
-    // phase at this lane's first sample = (phase + sum of all earlier increments) mod 44100
-    double sum = 0.0;
-#pragma unroll
-    for (int s = 0; s < B; s++) sum += (double)f[s];
-    const double before = L.excl_scan(sum);
-    const bool finite = __all_sync(0xffffffffu, fabs(before + sum) < 1.0e12);
-    if (!finite) {  // NaN / Infinity frequencies: keep the reference's exact sequential behaviour
-      L.serial([&] { double p2 = L.w(I.p); osc_body<B, T>(L, I, f, p2, true); L.w(I.p) = p2; });
-      L.st(f, I.out[0]);
-      return;
-    }
-    if (L.tl > 0) ph = posmod_sr(ph + before);
-  }
-  osc_body<B, T>(L, I, f, ph, true);
+  dops::Cx<B, T> cx; cx.tl = L.tl; cx.lane = L.lane;
+  dops::c_osc<B, T>(cx, f, ph, L.tables + (size_t)I.aux0 * DUSP_TABLE_LEN);  // every lane returns with the end-of-tile phase
   L.sync();
   if (L.tl == T - 1) L.w(I.p) = ph;
   L.st(f, I.out[0]);
@@ -1261,7 +1249,7 @@ if (!kp.out_raw) {
           if (kp.out_mode == 0) {
             if (active) {
               float *dst = out_row + (long long)I.aux0 * kp.out_len + tl0;
-              if (tl0 + B <= kp.n_samples && (kp.out_len & 3) == 0) {  // whole sub-block in range, rows 16-byte aligned
+              if (tl0 + B <= kp.n_samples && ((kp.out_len & 3) | (reinterpret_cast<unsigned long long>(kp.out) & 15ull)) == 0) {  // whole sub-block in range, rows 16-byte aligned (else scalar stores)
                 float4 *d4 = reinterpret_cast<float4 *>(dst);
 #pragma unroll
                 for (int q = 0; q < B / 4; q++) __stcs(d4 + q, make_float4(x[4 * q], x[4 * q + 1], x[4 * q + 2], x[4 * q + 3]));

@@ -107,7 +107,8 @@ long long dusp_session_unit_count(const dusp_session *s); /* sum over voices of 
 
 /* values[v * n_ids + k] overrides parameter param_ids[k] of voice v of program
  * `program_index` (v counts within that program).  Call before the first render
- * or after dusp_session_reset. */
+ * or after dusp_session_reset: a session that has rendered (clock != 0) is refused
+ * with DUSP_EINVAL, because the other program groups would keep their advanced state. */
 int dusp_session_set_params(dusp_session *s, int program_index, const int *param_ids, int n_ids,
                             const double *values);
 int dusp_session_reset(dusp_session *s); /* back to clock 0 / initial unit state */
@@ -144,7 +145,10 @@ int dusp_session_adopt(dusp_session *dst, int dst_program, dusp_session *src, in
  *                 and the call returns without synchronising
  * Buffer size: DUSP_OUT_VOICES n_voices*n_channels*n_samples floats,
  *              DUSP_OUT_MIX 2*n_samples floats.  NaN and -0 samples are stored
- *              as +0 (`x || 0`, renderChannelData.js:44). */
+ *              as +0 (`x || 0`, renderChannelData.js:44).
+ * Alignment:   any 4-byte aligned `out_device` is accepted.  The kernels store 16 bytes at a time when the
+ *              buffer is 16-byte aligned and n_samples is a multiple of 4 (every row then is); otherwise they
+ *              fall back to 4-byte stores (slower, same result). */
 int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, float *out_host,
                         float *out_device, void *cuda_stream);
 

@@ -314,6 +314,37 @@ def event_assigns_inlet():  # an event that assigns an inlet constant and later 
     return out
 
 
+def pick_channel():  # PickChannel.js:16-21 with constant indices: `c % in.length` selects the channel
+    st = quick.concat(C.Osc(300), C.Osc(301.5, "saw"))
+    return C.Sum(C.PickChannel(st, 1), C.Multiply(C.PickChannel(st, 2), 0.5))  # 2 % 2 = channel 0
+
+
+def delay_ring_wrap():  # rendered past the 5 s wrap of the Delay / MonoDelay rings: (clock + t) % 220500, Delay.js:27, MonoDelay.js:21
+    src = C.Multiply(C.Osc(0.7, "square"), C.Osc(441))
+    return C.Sum(C.Delay(src, quick.add(quick.multiply(C.Osc(0.31), 2000.25), 9000.5)), C.MonoDelay(src, 30000.75))
+
+
+def osc_tiny_f():  # increments below 2^-13 Hz: `phase += f` rounds on every sample (Osc.js:40), no exact scan exists
+    return C.Sum(C.Osc(1e-6, "saw"), C.Multiply(C.Osc(3.1e-5), 1000))
+
+
+def osc_fm_wide():  # instantaneous f jumps between +-20000 and +-1e-5 inside a chunk (a 2^31 span) and changes sign
+    gate = quick.multiply(quick.add(C.Osc(1000, "square"), 1), 10000)  # 20000 / 0
+    f = C.Multiply(quick.add(gate, 1e-5), C.Osc(3, "square"))
+    return C.Osc(f)
+
+
+def osc_fm_through_zero():  # deep audio-rate FM through zero: sub-2^-13 increments occur only near the crossings
+    return C.Osc(quick.add(quick.multiply(C.Osc(110.5), 9000), 12.5))
+
+
+def osc_phase_offset():  # a start phase with bits far below 2^-36 (not reachable from phase 0 by audio-range increments)
+    o = C.Osc(440.25)
+    o.phase = 0.3
+    return o
+
+
+
 # name -> (factory, seconds, exact?)
 def sample_rate_redux():  # SampleRateRedux.js: sample-and-hold with a modulated period, stereo input
     src = C.ConcatChannels(C.Osc(441), C.Osc(100.5, "saw"))
@@ -509,7 +540,7 @@ CASES = {
     "readback_delay": (readback_delay, 0.2, True),
     "simple_delay": (simple_delay, 1.0, False),
     "simple_delay_dusp": (simple_delay_dusp, 1.0, False),
-    "w3_voice": (w3_voice, 1.5, False),
+    "w3_voice": (w3_voice, 1.5, True),  # constant F: the biquad coefficients come from the host libm on both sides
     "delay_mixer": (delay_mixer, 0.8, True),
     "mixer_lfo": (mixer_lfo, 0.5, False),
     "worm": (worm, 0.5, False),
@@ -556,4 +587,10 @@ CASES = {
     "spectral_gate_shift_sum": (spectral_gate_shift_sum, 0.5, True),
     "spectral_augment": (spectral_augment, 0.4, True),
     "rechunk_up_down": (rechunk_up_down, 0.2, True),
+    "pick_channel": (pick_channel, 0.2, True),
+    "delay_ring_wrap": (delay_ring_wrap, 5.3, True),
+    "osc_tiny_f": (osc_tiny_f, 1.0, True),
+    "osc_fm_wide": (osc_fm_wide, 1.0, True),
+    "osc_fm_through_zero": (osc_fm_through_zero, 1.0, True),
+    "osc_phase_offset": (osc_phase_offset, 0.5, True),
 }
