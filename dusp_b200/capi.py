@@ -31,6 +31,9 @@ SYMBOLS = [
     "dusp_session_tile_info", "dusp_session_warning", "dusp_program_specialise", "dusp_session_poke",
     "dusp_session_adopt", "dusp_program_warmup_ticks",
     "dusp_mix_acc_create", "dusp_mix_acc_open", "dusp_mix_acc_close", "dusp_mix_acc_clear", "dusp_mix_push", "dusp_mix_wait",
+    "dusp_session_clock", "dusp_run_create", "dusp_run_destroy", "dusp_run_num_voices", "dusp_run_num_channels",
+    "dusp_run_channels_rendered", "dusp_run_position", "dusp_run_session", "dusp_run_program", "dusp_run_num_epochs",
+    "dusp_run_epoch_program", "dusp_run_set_params", "dusp_run_render",
 ]
 
 
@@ -90,6 +93,24 @@ def load():
     L.dusp_mix_acc_clear.argtypes = [c.c_void_p, c.c_size_t, c.c_size_t, c.c_void_p]
     L.dusp_mix_push.argtypes = [c.c_void_p, c.c_void_p, c.c_size_t, c.c_void_p, c.c_void_p, c.c_void_p]
     L.dusp_mix_wait.argtypes = [c.c_void_p, c.c_uint, c.c_void_p, c.c_void_p]
+    L.dusp_session_clock.argtypes = [c.c_void_p]
+    L.dusp_session_clock.restype = c.c_longlong
+    L.dusp_run_create.argtypes = [c.POINTER(c.c_char_p), c.POINTER(c.c_size_t), c.POINTER(c.c_int), c.c_int, c.c_int, c.POINTER(c.c_void_p)]
+    L.dusp_run_destroy.argtypes = [c.c_void_p]
+    L.dusp_run_destroy.restype = None
+    for nm in ("num_voices", "num_channels", "channels_rendered"):
+        getattr(L, "dusp_run_" + nm).argtypes = [c.c_void_p]
+    L.dusp_run_position.argtypes = [c.c_void_p]
+    L.dusp_run_position.restype = c.c_longlong
+    L.dusp_run_session.argtypes = [c.c_void_p]
+    L.dusp_run_session.restype = c.c_void_p
+    L.dusp_run_program.argtypes = [c.c_void_p, c.c_int]
+    L.dusp_run_program.restype = c.c_void_p
+    L.dusp_run_num_epochs.argtypes = [c.c_void_p, c.c_int]
+    L.dusp_run_epoch_program.argtypes = [c.c_void_p, c.c_int, c.c_int, c.POINTER(c.c_longlong)]
+    L.dusp_run_epoch_program.restype = c.c_void_p
+    L.dusp_run_set_params.argtypes = [c.c_void_p, c.c_int, c.POINTER(c.c_char_p), c.c_int, c.POINTER(c.c_double)]
+    L.dusp_run_render.argtypes = [c.c_void_p, c.c_longlong, c.c_int, c.c_void_p, c.c_void_p, c.c_void_p]
     if L.dusp_abi_version() != 1:
         raise RuntimeError("libdusp_b200.so ABI version mismatch")
     assert config.sampleRate == 44100 and config.standardChunkSize == 256  # compiled into the kernels
@@ -109,12 +130,16 @@ def check(rc):
 class Program:
     """A circuit compiled to a flat op program (``dusp_program``)."""
 
-    def __init__(self, blob):
+    def __init__(self, blob, _borrowed=None):
         L = load()
         self.blob = blob
-        h = ctypes.c_void_p()
-        data = blob.encode()
-        check(L.dusp_program_create(data, len(data), ctypes.byref(h)))
+        self._owned = _borrowed is None
+        if self._owned:
+            h = ctypes.c_void_p()
+            data = blob.encode()
+            check(L.dusp_program_create(data, len(data), ctypes.byref(h)))
+        else:
+            h = ctypes.c_void_p(_borrowed)  # owned by a dusp_run
         self._h = h
         self.num_channels = L.dusp_program_num_channels(h)
         self.num_units = L.dusp_program_num_units(h)
@@ -123,7 +148,7 @@ class Program:
         self.warmup_ticks = L.dusp_program_warmup_ticks(h)
 
     def __del__(self):
-        if getattr(self, "_h", None) and _lib is not None:
+        if getattr(self, "_h", None) and _lib is not None and getattr(self, "_owned", False):
             _lib.dusp_program_destroy(self._h)
             self._h = None
 
@@ -162,14 +187,18 @@ class Program:
 class Session:
     """n voices of one or more programs resident on one GPU (``dusp_session``)."""
 
-    def __init__(self, programs, voices, device=0):
+    def __init__(self, programs, voices, device=0, _borrowed=None):
         L = load()
         self.programs = list(programs)
-        n = len(self.programs)
-        ph = (ctypes.c_void_p * n)(*[p._h for p in self.programs])
-        vc = (ctypes.c_int * n)(*[int(v) for v in voices])
-        h = ctypes.c_void_p()
-        check(L.dusp_session_create(ph, vc, n, int(device), ctypes.byref(h)))
+        self._owned = _borrowed is None
+        if self._owned:
+            n = len(self.programs)
+            ph = (ctypes.c_void_p * n)(*[p._h for p in self.programs])
+            vc = (ctypes.c_int * n)(*[int(v) for v in voices])
+            h = ctypes.c_void_p()
+            check(L.dusp_session_create(ph, vc, n, int(device), ctypes.byref(h)))
+        else:
+            h = ctypes.c_void_p(_borrowed)  # owned by a dusp_run
         self._h = h
         self.device = device
         self.num_voices = L.dusp_session_num_voices(h)
@@ -177,11 +206,15 @@ class Session:
         self.unit_count = L.dusp_session_unit_count(h)
 
     def close(self):
-        if getattr(self, "_h", None) and _lib is not None:
+        if getattr(self, "_h", None) and _lib is not None and getattr(self, "_owned", False):
             _lib.dusp_session_destroy(self._h)
-            self._h = None
+        self._h = None
 
     __del__ = close
+
+    @property
+    def clock(self):
+        return load().dusp_session_clock(self._h)
 
     def set_params(self, program_index, names, values):
         """values: array [n_voices_of_program][len(names)] of float64."""
@@ -254,6 +287,89 @@ class Session:
         load().dusp_session_tile_info(self._h, ctypes.byref(B), ctypes.byref(T), ctypes.byref(f))
         return {"grid": g.value, "block": b.value, "smem_bytes": s.value, "sub_block": B.value, "time_lanes": T.value,
                 "specialised": bool(f.value), "warning": load().dusp_session_warning(self._h).decode()}
+
+
+class Run:
+    """A render driven through its circuits' timelines (``dusp_run``, csrc/run.cc): the blobs' EV / EPOCH / KEEP /
+    WARMUP records become chunk-aligned segments, pokes and adopted sessions inside the library."""
+
+    def __init__(self, blobs, voices, device=0):
+        L = load()
+        n = len(blobs)
+        data = [b.encode() for b in blobs]
+        arr = (ctypes.c_char_p * n)(*data)
+        lens = (ctypes.c_size_t * n)(*[len(x) for x in data])
+        vc = (ctypes.c_int * n)(*[int(v) for v in voices])
+        h = ctypes.c_void_p()
+        check(L.dusp_run_create(arr, lens, vc, n, int(device), ctypes.byref(h)))
+        self._h = h
+        self.blobs, self.voices, self.device = list(blobs), [int(v) for v in voices], device
+        self.num_voices = L.dusp_run_num_voices(h)
+        self.num_channels = L.dusp_run_num_channels(h)
+
+    def close(self):
+        if getattr(self, "_h", None) and _lib is not None:
+            _lib.dusp_run_destroy(self._h)
+        self._h = None
+
+    __del__ = close
+
+    @property
+    def pos(self):
+        return load().dusp_run_position(self._h)
+
+    @property
+    def channels_rendered(self):
+        return load().dusp_run_channels_rendered(self._h)
+
+    @property
+    def session(self):
+        """The session rendering right now (borrowed: replaced when an epoch begins; created on first use)."""
+        h = load().dusp_run_session(self._h)
+        if not h:
+            msg = load().dusp_last_error().decode()
+            raise (UnsupportedCircuit if "unsupported" in msg.lower() else DuspError)(msg)
+        return Session(self.programs, self.voices, self.device, _borrowed=h)
+
+    @property
+    def programs(self):
+        """The programs rendering right now, one per group (borrowed)."""
+        L = load()
+        return [Program(None, _borrowed=L.dusp_run_program(self._h, i)) for i in range(len(self.blobs))]
+
+    def epochs(self, program_index=0):
+        """[(first chunk, Program)] of a group's timeline: warm-up ticks, then one program per EPOCH section."""
+        L = load()
+        out = []
+        for e in range(L.dusp_run_num_epochs(self._h, program_index)):
+            k0 = ctypes.c_longlong()
+            h = L.dusp_run_epoch_program(self._h, program_index, e, ctypes.byref(k0))
+            out.append((k0.value, Program(None, _borrowed=h)))
+        return out
+
+    def set_params(self, program_index, names, values):
+        """values: array [n_voices_of_program][len(names)] of float64 (before the first render)."""
+        import numpy as np
+        nm = (ctypes.c_char_p * len(names))(*[n.encode() for n in names])
+        vals = np.ascontiguousarray(values, dtype=np.float64)
+        check(load().dusp_run_set_params(self._h, int(program_index), nm, len(names),
+                                         vals.ctypes.data_as(ctypes.POINTER(ctypes.c_double))))
+
+    def render_host(self, n_samples, out_mode=OUT_VOICES):
+        """The next n samples: [voices][channels][n] (channels = what the reference's result would hold so far) or
+        [2][n] (mix)."""
+        import numpy as np
+        n_samples = int(n_samples)
+        shape = (self.num_voices, self.num_channels, n_samples) if out_mode != OUT_MIX else (2, n_samples)
+        out = np.empty(shape, dtype=np.float32)
+        check(load().dusp_run_render(self._h, n_samples, out_mode, out.ctypes.data_as(ctypes.c_void_p), None, None))
+        if out_mode != OUT_MIX and n_samples and self.channels_rendered < self.num_channels:
+            out = out[:, :self.channels_rendered]
+        return out
+
+    def render_device(self, n_samples, device_ptr, out_mode=OUT_VOICES, stream=None):
+        check(load().dusp_run_render(self._h, int(n_samples), out_mode, None, ctypes.c_void_p(device_ptr),
+                                     ctypes.c_void_p(stream) if stream else None))
 
 
 class MixAccumulator:

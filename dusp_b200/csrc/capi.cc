@@ -558,16 +558,20 @@ int dusp_session_reset(dusp_session *s) {
   return DUSP_OK;
 }
 
-// Enqueue the kernels that render the next `n` samples of every group into
-// d_out (row length `n`) on stream `st`.
-static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_out, cudaStream_t st) {
+// Enqueue the kernels that render the next `n` samples of every group into d_out on stream `st`.  Rows of d_out
+// are `pitch` floats apart (>= n); per-voice output has `nch` channel rows per voice (>= the session's own count:
+// a run whose later epochs have more channels, run.cc).
+static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_out, cudaStream_t st, long long pitch, int nch) {
   const int raw = out_mode == DUSP_OUT_VOICES_RAW;
   if (raw) out_mode = DUSP_OUT_VOICES;
-  const size_t out_floats = (out_mode == DUSP_OUT_VOICES ? (size_t)s->n_voices * s->out_nch : 2) * (size_t)n;
+  const size_t out_rows = out_mode == DUSP_OUT_VOICES ? (size_t)s->n_voices * nch : 2;
   // channels a group does not produce (and the mix accumulator) start at zero
   bool need_zero = out_mode == DUSP_OUT_MIX;
-  for (auto &g : s->groups) if (g.prog.out_nch != s->out_nch) need_zero = true;
-  if (need_zero) CUDA_TRY(cudaMemsetAsync(d_out, 0, out_floats * sizeof(float), st));
+  for (auto &g : s->groups) if (g.prog.out_nch != nch) need_zero = true;
+  if (need_zero) {
+    if (pitch == n) CUDA_TRY(cudaMemsetAsync(d_out, 0, out_rows * (size_t)n * sizeof(float), st));
+    else CUDA_TRY(cudaMemset2DAsync(d_out, (size_t)pitch * sizeof(float), 0, (size_t)n * sizeof(float), out_rows, st));
+  }
   {
     bool all_dirty = true, any_dirty = false;
     for (auto &g : s->groups) { all_dirty = all_dirty && g.dirty; any_dirty = any_dirty || g.dirty; }
@@ -591,8 +595,8 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     DuspKernelParams kp;
     memset(&kp, 0, sizeof kp);
     kp.multi = s->d_multi; kp.n_voices = s->n_multi; kp.n_slots = s->multi_slots; kp.nv_stride = 1;
-    kp.tables = s->d_tables; kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = 1; kp.out_mode = out_mode; kp.out_raw = raw;
-    kp.out_len = n; kp.clock0 = s->clock; kp.n_samples = n;
+    kp.tables = s->d_tables; kp.out = d_out; kp.out_nch = nch; kp.prog_nch = 1; kp.out_mode = out_mode; kp.out_raw = raw;
+    kp.out_len = pitch; kp.clock0 = s->clock; kp.n_samples = n;
     // samples per lane / warps per CTA: 4 / 1 keeps a warp's slots at 15 KB for the W4 circuits, so ~14 circuits are
     // resident per SM (measured, 4000 circuits x 4 s: 689 ms against 1119 ms at 8 / 2); DUSP_MULTI_B / _WPC override
     int mb = 4;
@@ -640,8 +644,8 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     kp.words = g.d_words; kp.rings = g.d_rings; kp.ring_stride = std::max<long long>(g.prog.ring_floats, 4);
     kp.ring_tab = g.d_ringtab; kp.stale = g.d_stale; kp.n_stale = g.prog.n_stale; kp.tables = s->d_tables;
     kp.ctab = g.d_ctab;
-    kp.out = d_out; kp.out_nch = s->out_nch; kp.prog_nch = g.prog.out_nch; kp.out_mode = out_mode; kp.out_raw = raw;
-    kp.out_len = n; kp.clock0 = s->clock; kp.n_samples = n;
+    kp.out = d_out; kp.out_nch = nch; kp.prog_nch = g.prog.out_nch; kp.out_mode = out_mode; kp.out_raw = raw;
+    kp.out_len = pitch; kp.clock0 = s->clock; kp.n_samples = n;
     const int wpc = g.warps_per_cta;
     int grid = 0, smem = 0;
     if (g.fused) {
@@ -677,18 +681,21 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
   return DUSP_OK;
 }
 
-int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, float *out_host, float *out_device,
-                        void *cuda_stream) {
+// dusp_session_render with the destination's row pitch (floats) and per-voice channel stride made explicit: a run
+// (run.cc) renders chunk-aligned segments side by side into one caller buffer.
+int dusp_render_impl(dusp_session *s, long long n_samples, int out_mode, float *out_host, float *out_device, void *cuda_stream,
+                     long long pitch, int nch) {
   if (!s || n_samples < 0 || (out_mode != DUSP_OUT_VOICES && out_mode != DUSP_OUT_MIX && out_mode != DUSP_OUT_VOICES_RAW) || (!out_host == !out_device))
     return fail(DUSP_EINVAL, "dusp_session_render: bad arguments");
+  if (pitch < n_samples || nch < s->out_nch) return fail(DUSP_EINVAL, "dusp_session_render: destination too narrow");
   CUDA_TRY(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)cuda_stream;
   if (n_samples == 0) return DUSP_OK;
-  if (out_device) return enqueue_block(s, n_samples, out_mode, out_device, st);
+  if (out_device) return enqueue_block(s, n_samples, out_mode, out_device, st, pitch, nch);
 
   // Host output: render time blocks into two device staging buffers and drain each
   // over PCIe on a second stream while the next block renders.
-  const size_t rows = out_mode != DUSP_OUT_MIX ? (size_t)s->n_voices * s->out_nch : 2;
+  const size_t rows = out_mode != DUSP_OUT_MIX ? (size_t)s->n_voices * nch : 2;
   size_t staging_mb = 1024;  // per staging buffer (measured on B200: 1 GB blocks drain at 50 GB/s, 256 MB at 46); DUSP_STAGING_MB overrides (longer rows per 2-D copy)
   if (const char *e = getenv("DUSP_STAGING_MB")) staging_mb = (size_t)std::max(16, atoi(e));
   long long blk = (long long)((staging_mb << 20) / (rows * sizeof(float)));
@@ -716,11 +723,11 @@ int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, floa
   for (long long t = 0; t < n_samples; t += blk, i ^= 1) {
     const long long n = std::min(blk, n_samples - t);
     CUDA_TRY(cudaStreamWaitEvent(st, s->ev_copied[i], 0));  // buffer i drained (no-op the first time)
-    int rc = enqueue_block(s, n, out_mode, s->d_staging[i], st);
+    int rc = enqueue_block(s, n, out_mode, s->d_staging[i], st, n, nch);
     if (rc != DUSP_OK) return rc;
     CUDA_TRY(cudaEventRecord(s->ev_rendered[i], st));
     CUDA_TRY(cudaStreamWaitEvent(s->copy_stream, s->ev_rendered[i], 0));
-    CUDA_TRY(cudaMemcpy2DAsync(out_host + t, (size_t)n_samples * sizeof(float), s->d_staging[i], (size_t)n * sizeof(float),
+    CUDA_TRY(cudaMemcpy2DAsync(out_host + t, (size_t)pitch * sizeof(float), s->d_staging[i], (size_t)n * sizeof(float),
                                (size_t)n * sizeof(float), rows, cudaMemcpyDeviceToHost, s->copy_stream));
     CUDA_TRY(cudaEventRecord(s->ev_copied[i], s->copy_stream));
   }
@@ -728,6 +735,14 @@ int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, floa
   CUDA_TRY(cudaStreamSynchronize(st));
   return DUSP_OK;
 }
+
+int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, float *out_host, float *out_device,
+                        void *cuda_stream) {
+  if (!s) return fail(DUSP_EINVAL, "dusp_session_render: bad arguments");
+  return dusp_render_impl(s, n_samples, out_mode, out_host, out_device, cuda_stream, n_samples, s->out_nch);
+}
+
+long long dusp_session_clock(const dusp_session *s) { return s ? s->clock : 0; }
 
 int dusp_session_tile_info(const dusp_session *s, int *sub_block, int *time_lanes, int *specialised) {
   if (!s || s->groups.empty()) return fail(DUSP_EINVAL, "dusp_session_tile_info: empty session");

@@ -221,126 +221,41 @@ def blob_events(blob):
     return ev
 
 
-def _with_records(text, records):
-    assert text.endswith("END\n")
-    return text[:-len("END\n")] + "".join(r + "\n" for r in records) + "END\n"
-
-
-def expand_warmup(timeline):
-    """Channel growth at the start of a render.  The reference's tick order is not topological (Unit.js:171-209), so
-    a unit can tick before its producer and see that outlet with the channel count of the previous tick: a
-    multi-channel signal takes S ticks to reach every unit (Space / ScaryPatch / stereo-detuned FM patches).  The
-    library compiles tick k < S from a ``WARMUP k`` record (``dusp_program_warmup_ticks``); here those programs become
-    one-chunk epochs in front of the steady program, with ``KEEP`` so each hands every outlet's last chunk on."""
-    k0, text = timeline[0]
-    try:
-        capi.Program(text)
-        return timeline
-    except capi.UnsupportedCircuit as e:
-        if "warm-up" not in str(e):
-            raise
-    s = capi.Program(_with_records(text, ["WARMUP 0"])).warmup_ticks
-    if len(timeline) > 1 and timeline[1][0] <= s:
-        raise capi.UnsupportedCircuit("graph edit while channel counts are still growing")
-    keep = [] if "\nKEEP\n" in text else ["KEEP"]
-    return [(k, _with_records(text, ["WARMUP %d" % k] + keep)) for k in range(s)] + \
-        [(s, _with_records(text, ["WARMUP %d" % s]))] + timeline[1:]
-
-
 class SessionRun:
-    """A session driven through its circuits' timelines: chunk-aligned segments, the events of chunk
-    k poked into every voice of their program group before the segment that starts at sample 256*k, and a new
-    session that adopts the old one's device state wherever an event edits a graph (``EPOCH`` sections).
+    """A render driven through its circuits' timelines.  The protocol itself -- chunk-aligned
+    segments, the events of chunk k poked into every voice before the segment that starts at sample 256*k, a new
+    session that adopts the old one's device state wherever an event edits a graph (``EPOCH`` sections), warm-up
+    programs while channel counts still grow -- lives behind the C ABI (``dusp_run_*``, csrc/run.cc); this is the
+    host-side handle.
 
     ``blobs``: one per program group (``circuit_blob``); ``voices``: voices per group."""
 
     def __init__(self, blobs, voices, device=0):
+        self.run = capi.Run(blobs, voices, device)
         self.device = device
         self.voices = [int(v) for v in voices]
-        self.timelines = [expand_warmup(split_epochs(b)) for b in blobs]
-        self.epoch = [0] * len(blobs)
-        self.programs = [capi.Program(tl[0][1]) for tl in self.timelines]
-        self.events = [blob_events(tl[0][1]) for tl in self.timelines]
-        self.session = capi.Session(self.programs, self.voices, device)
-        self.pos = 0  # samples rendered so far (a multiple of 256 between renders, except after the last one)
+
+    @property
+    def session(self):
+        return self.run.session
+
+    @property
+    def programs(self):
+        return self.run.programs
+
+    @property
+    def pos(self):
+        return self.run.pos
 
     def set_params(self, program_index, names, values):
-        self.session.set_params(program_index, names, values)
-
-    def _cuts(self, n):
-        cuts = set()
-        for tl, evs in zip(self.timelines, self.events):
-            for (k, _) in tl[1:]:
-                cuts.add(k * 256)
-            for tl_epoch in tl:
-                for (k, _, _, _) in blob_events(tl_epoch[1]):
-                    cuts.add(k * 256)
-        return sorted(c for c in cuts if self.pos < c < self.pos + n)
-
-    def _enter(self, pos):
-        """What the reference does in runEvents before the tick of the chunk at ``pos``: graph edits, then pokes."""
-        k = pos // 256
-        switch = [i for i, tl in enumerate(self.timelines)
-                  if self.epoch[i] + 1 < len(tl) and tl[self.epoch[i] + 1][0] <= k]
-        if switch:
-            for i in switch:
-                while self.epoch[i] + 1 < len(self.timelines[i]) and self.timelines[i][self.epoch[i] + 1][0] <= k:
-                    self.epoch[i] += 1
-                text = self.timelines[i][self.epoch[i]][1]
-                self.programs[i] = capi.Program(text)
-                self.events[i] = blob_events(text)
-            new = capi.Session(self.programs, self.voices, self.device)
-            try:
-                for i in range(len(self.programs)):
-                    new.adopt(i, self.session, i)
-            except Exception:
-                new.close()
-                raise
-            self.session.close()
-            self.session = new
-        if pos > 0:
-            for i, evs in enumerate(self.events):
-                now = [e for e in evs if e[0] == k]
-                if now:
-                    self.session.poke(i, -1, ["u%d.%s" % (u, name) for (_, u, name, _) in now], [v for (_, _, _, v) in now])
+        self.run.set_params(program_index, list(names), values)
 
     def render(self, n, out_mode=capi.OUT_VOICES):
         """The next ``n`` samples: [voices][channels][n] or [2][n] (mix)."""
-        if self.pos % 256:
-            raise DuspError("a render that stopped inside a chunk cannot be continued")
-        parts = []
-        for b in self._cuts(n) + [self.pos + n]:
-            self._enter(self.pos)
-            parts.append(self.session.render_host(b - self.pos, out_mode))
-            self.pos = b
-        if len(parts) == 1:
-            return parts[0]
-        if out_mode != capi.OUT_MIX:  # an edit may add output channels: earlier segments read as silence there
-            nch = max(p.shape[1] for p in parts)
-            parts = [p if p.shape[1] == nch else np.pad(p, ((0, 0), (0, nch - p.shape[1]), (0, 0))) for p in parts]
-        return np.concatenate(parts, axis=-1)
+        return self.run.render_host(n, out_mode)
 
     def close(self):
-        self.session.close()
-
-
-def render_segments(sess, n, events_by_program, out_mode=capi.OUT_VOICES):
-    """``sess.render_host(n)`` from clock 0 with events but no graph edits (see ``SessionRun`` for the general
-    driver).  events_by_program: {program_index: [(chunk, unit, property, value)]}."""
-    chunk = 256
-    cuts = sorted({k * chunk for evs in events_by_program.values() for (k, _, _, _) in evs if 0 < k * chunk < n})
-    if not cuts:
-        return sess.render_host(n, out_mode)
-    pending = {pi: sorted(evs, key=lambda e: e[0]) for pi, evs in events_by_program.items()}  # stable: keeps run order
-    parts, pos = [], 0
-    for b in cuts + [n]:
-        for pi, evs in pending.items():
-            now = [e for e in evs if e[0] * chunk == pos and pos > 0]
-            if now:
-                sess.poke(pi, -1, ["u%d.%s" % (u, name) for (_, u, name, _) in now], [v for (_, _, _, v) in now])
-        parts.append(sess.render_host(b - pos, out_mode))
-        pos = b
-    return np.concatenate(parts, axis=-1)
+        self.run.close()
 
 
 def n_samples_for(duration):

@@ -152,6 +152,45 @@ int dusp_session_adopt(dusp_session *dst, int dst_program, dusp_session *src, in
 int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, float *out_host,
                         float *out_device, void *cuda_stream);
 
+long long dusp_session_clock(const dusp_session *s); /* samples ticked so far (whole chunks, like Circuit.clock) */
+
+/* ---- runs: a render driven through the circuits' timelines -----------------
+ * Replaces: the whole `for t0 ... await circuit.tickUntil(t1)` loop of renderChannelData.js:29-45 INCLUDING what
+ * Circuit.tick does before each chunk -- runEvents (Circuit.js:23,57-65; Event.js:18-30): triggers / state
+ * assignments (UnitOrPatch.js:25-33, constructOperation.js:63-69) and graph edits (`for` / `then`,
+ * constructOperation.js:36-60, Inlet.js:40-93).  The host shim runs the circuit's event queue once on the
+ * reference's own objects and records what happened in the blob (format: dusp_b200/graphblob.py):
+ *   EV <chunk> <unit> <prop> <value>    unit state assigned by an event, applied before that chunk's tick
+ *   EPOCH <chunk> + DUSPGRAPH section   the circuit after an event edited the graph, from that chunk on
+ *   KEEP / WARMUP <k>                   compile hints (keep every outlet's last chunk / channel counts still growing)
+ * A run owns one program per section and the session that renders the current one.  dusp_run_render renders the
+ * next n_samples in chunk-aligned segments: before the segment that starts at chunk k it switches every group whose
+ * next EPOCH has begun to a new session that adopts the old one's device state (dusp_session_adopt), then pokes
+ * chunk k's EV records into every voice of their group (dusp_session_poke).  Circuits whose channel counts grow over
+ * their first ticks (dusp_program_warmup_ticks) get their warm-up programs as one-chunk epochs automatically.
+ * `blobs[i]` is instantiated `voices[i]` times, as in dusp_session_create. */
+typedef struct dusp_run dusp_run;
+int dusp_run_create(const char *const *blobs, const size_t *lens, const int *voices, int n_programs, int device,
+                    dusp_run **out);
+void dusp_run_destroy(dusp_run *r);
+int dusp_run_num_voices(const dusp_run *r);
+int dusp_run_num_channels(const dusp_run *r);      /* widest program of ANY epoch: the channel rows per voice of every render */
+int dusp_run_channels_rendered(const dusp_run *r); /* widest program of the epochs entered so far: what the reference's
+                                                      result holds (renderChannelData.js:35-45 grows channels as they appear) */
+long long dusp_run_position(const dusp_run *r);    /* samples rendered so far */
+/* the session / program rendering group `program_index` right now (borrowed; replaced at the next epoch).  The
+ * session is created on first use (first set_params / render / this call): NULL + dusp_last_error() without a GPU. */
+dusp_session *dusp_run_session(dusp_run *r);
+const dusp_program *dusp_run_program(const dusp_run *r, int program_index);
+/* the timeline of group `program_index`: its programs (warm-up ticks, then one per EPOCH) and their first chunks */
+int dusp_run_num_epochs(const dusp_run *r, int program_index);
+const dusp_program *dusp_run_epoch_program(const dusp_run *r, int program_index, int epoch, long long *first_chunk);
+/* per-voice parameters by name (dusp_session_set_params), before the first render */
+int dusp_run_set_params(dusp_run *r, int program_index, const char *const *names, int n_names, const double *values);
+/* as dusp_session_render; rows are [voice][dusp_run_num_channels][n_samples] (channels a segment's programs do not
+ * produce read as silence) or [2][n_samples] (DUSP_OUT_MIX).  A render that ended inside a chunk cannot be continued. */
+int dusp_run_render(dusp_run *r, long long n_samples, int out_mode, float *out_host, float *out_device, void *cuda_stream);
+
 /* number of kernel launches issued by this session so far (bench accounting) */
 long long dusp_session_launch_count(const dusp_session *s);
 /* last launch geometry, for reporting: grid, block, dynamic smem bytes */

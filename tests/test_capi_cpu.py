@@ -32,16 +32,19 @@ def test_rand53_agrees_across_host_library_and_oracle(lib, oracle):
 @pytest.mark.parametrize("name", sorted(circuits.CASES))
 def test_every_case_compiles(lib, oracle, name):
     fac, _, _ = circuits.CASES[name]
-    from dusp_b200.render import split_epochs, expand_warmup
     blob, circuit = circuit_blob(fac())
-    # one program per epoch (graph edits; warm-up ticks while channel counts still grow)
-    epochs = expand_warmup(split_epochs(blob))
-    for k, text in epochs:
-        p = capi.Program(text)
+    # one program per epoch (graph edits; warm-up ticks while channel counts still grow): the library
+    # splits the blob and compiles every section when the run is created (no GPU needed until the first render)
+    run = capi.Run([blob], [1])
+    epochs = run.epochs(0)
+    assert [k for k, _ in epochs] == sorted(k for k, _ in epochs) and epochs[0][0] == 0
+    for k, p in epochs:
         assert p.num_instructions >= 1 and 1 <= p.num_slots <= 32
         assert "out" in p.disassemble()
     assert p.num_units == len(circuit.units)  # the host circuit is left as the last epoch found it
-    assert capi.Program(epochs[0][1]).num_channels == len(oracle.render(blob, 0.005))  # one chunk
+    assert epochs[0][1].num_channels == len(oracle.render(blob, 0.005))  # one chunk
+    assert run.num_channels == max(p.num_channels for _, p in epochs)
+    run.close()
 
 
 @pytest.mark.parametrize("name", ["w2_live", "w3_voice", "simple_delay", "transcendental"])
@@ -118,6 +121,30 @@ def test_unsupported_configurations_fail_loudly(lib):
     assert "EPOCH" not in circuit_blob(patches_.Boop(440, 0.2))[0]
 
 
+def test_run_splits_a_multi_section_blob(lib):
+    """dusp_run_create (csrc/run.cc) owns the run-time protocol: EPOCH sections become programs with their first
+    chunk, circuits whose channel counts grow get their warm-up ticks as one-chunk epochs, and nothing needs a GPU
+    until the first render."""
+    blob, _ = circuit_blob(circuits.for_then())              # `(O440 for 0.5) then O220`: one graph edit at chunk 86
+    run = capi.Run([blob], [3])
+    ep = run.epochs(0)
+    assert [k for k, _ in ep] == [0, 86] and run.num_voices == 3 and run.pos == 0
+    assert ep[0][1].num_units < ep[1][1].num_units           # the edit added the second oscillator
+    run.close()
+    blob, _ = circuit_blob(circuits.scary_patch())           # 3 warm-up ticks before every unit sees both channels
+    run = capi.Run([blob], [1])
+    ep = run.epochs(0)
+    assert [k for k, _ in ep] == list(range(len(ep))) and len(ep) >= 2
+    assert [p.warmup_ticks for _, p in ep] == [len(ep) - 1] * len(ep)
+    assert ep[0][1].num_channels <= ep[-1][1].num_channels == run.num_channels
+    run.close()
+    two = capi.Run([circuit_blob(circuits.at_later())[0], circuit_blob(circuits.then_number())[0]], [2, 5])
+    assert len(two.epochs(0)) == 1 and len(two.epochs(1)) == 2 and two.num_voices == 7
+    two.close()
+    with pytest.raises(d.DuspError):
+        capi.Run(["DUSPGRAPH 1\nEND\n"], [1])
+
+
 def test_no_cpu_fallback(lib):
     """Without a CUDA device session creation must fail, not render on the host."""
     import torch
@@ -129,6 +156,10 @@ def test_no_cpu_fallback(lib):
         capi.Session([p], [1])
     with pytest.raises(d.DuspError):
         d.renderChannelData(C.Osc(440), 0.01)
+    run = capi.Run([blob], [1])
+    with pytest.raises(d.DuspError, match="no CUDA device|CUDA"):
+        run.render_host(256)
+    run.close()
 
 
 def test_product_never_imports_the_oracle():
