@@ -103,6 +103,7 @@ struct dusp_session {
   long long unit_count = 0;
   long long clock = 0;
   float *d_tables = nullptr;
+  unsigned *d_sm_slots = nullptr;  // [256] per-SM CTA arrival counters of the pipelined kernel (never reset: only differences matter)
   // every group's arrays are segments of five session-wide allocations (a heterogeneous batch of 10 000
   // circuits is 10 000 groups: one upload / two memsets re-initialise them all)
   double *d_words_pool = nullptr; float *d_rings_pool = nullptr; float *d_stale_pool = nullptr;
@@ -178,7 +179,7 @@ void dusp_session_destroy(dusp_session *s) {
   cudaSetDevice(s->device);
   cudaFree(s->d_words_pool); cudaFree(s->d_rings_pool); cudaFree(s->d_stale_pool); cudaFree(s->d_ringtab_pool);
   cudaFree(s->d_code_pool); cudaFree(s->d_multi);
-  cudaFree(s->d_tables);
+  cudaFree(s->d_tables); cudaFree(s->d_sm_slots);
   for (auto &g : s->groups) cudaFree(g.d_ctab);
   for (int i = 0; i < 2; i++) {
     cudaFree(s->d_staging[i]);
@@ -205,6 +206,8 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
   const auto &tabs = host_tables();
   CUDA_TRY(cudaMalloc(&s->d_tables, tabs.size() * sizeof(float)));
   CUDA_TRY(cudaMemcpy(s->d_tables, tabs.data(), tabs.size() * sizeof(float), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMalloc(&s->d_sm_slots, 256 * sizeof(unsigned)));
+  CUDA_TRY(cudaMemset(s->d_sm_slots, 0, 256 * sizeof(unsigned)));
   int voice0 = 0;
   for (int i = 0; i < n_programs; i++) {
     if (!programs[i] || voices[i] < 1) return fail(DUSP_EINVAL, "dusp_session_create: empty program group");
@@ -654,7 +657,7 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
       fp.n_voices = kp.n_voices; fp.voice0 = kp.voice0; fp.nv_stride = kp.nv_stride; fp.words = kp.words;
       fp.rings = kp.rings; fp.ring_stride = kp.ring_stride; fp.stale = kp.stale; fp.tables = kp.tables; fp.out = kp.out;
       fp.n_stale = kp.n_stale; fp.out_nch = kp.out_nch; fp.prog_nch = kp.prog_nch; fp.out_mode = kp.out_mode; fp.out_raw = kp.out_raw;
-      fp.out_len = kp.out_len; fp.clock0 = kp.clock0; fp.n_samples = kp.n_samples;
+      fp.out_len = kp.out_len; fp.clock0 = kp.clock0; fp.n_samples = kp.n_samples; fp.sm_slots = s->d_sm_slots;
       std::string err;
       if (g.piped) {
         grid = (g.n_voices + g.pinfo.voices_per_cta - 1) / g.pinfo.voices_per_cta;

@@ -20,6 +20,7 @@ struct FusedParams {
   int n_stale, out_nch, prog_nch, out_mode;
   int out_raw, pad_;
   long long out_len, clock0, n_samples;
+  unsigned *sm_slots;  // [256] per-SM arrival counters (pipelined kernel: which warp of a CTA takes the lane-per-voice role)
 };
 
 // CUDA C++ source of the specialised kernel `dusp_fused` for tile shape (B, T).

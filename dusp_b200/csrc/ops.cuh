@@ -46,6 +46,26 @@ constexpr double SRD = 44100.0;
 DOPS_DEV double js_or0(double x) { return fabs(x) > 0.0 ? x : 0.0; }  // `x || 0`: NaN, +0, -0 -> +0 (one compare: |x| > 0 is false for all three)
 DOPS_DEV float js_or0f(float x) { return fabsf(x) > 0.0f ? x : 0.0f; }
 
+// f32 -> f64 on the integer pipe (the conversion instruction runs on the XU pipe, 16 lanes per clock and SM: the lane-per-
+// voice warp of the pipelined kernel is bound by it).  A normal f32 widens exactly with a shift and an add: sign and
+// exponent move from bits 31..23 to 31..20 (the exponent bias grows by 896), the mantissa's low 3 bits start the low
+// word.  Zeros, denormals, Inf and NaN (exponent field 0 or 255) take the conversion instruction.
+DOPS_DEV double widen_f32(float x) {
+  const uint32_t u = __float_as_uint(x);
+  const uint32_t e = (u >> 23) & 0xffu;
+  double d = __hiloint2double((int)((u >> 3) + ((u >> 31) ? 0xA8000000u : 0x38000000u)), (int)(u << 29));
+  if (e == 0u || e == 0xffu) d = (double)x;
+  return d;
+}
+// (double)(x || 0) the same way: +-0 and NaN give +0
+DOPS_DEV double widen_or0_f32(float x) {
+  const uint32_t u = __float_as_uint(x);
+  const uint32_t a = u & 0x7fffffffu, e = a >> 23;
+  double d = __hiloint2double((int)((u >> 3) + ((u >> 31) ? 0xA8000000u : 0x38000000u)), (int)(u << 29));
+  if (e == 0u || e == 0xffu) d = (a == 0u || a > 0x7f800000u) ? 0.0 : (double)x;
+  return d;
+}
+
 // Stereo mixdown accumulation (DUSP_OUT_MIX): y[0..B) += into dst[0..B), `room` = samples left before the requested
 // length.  A lane owns B consecutive samples, so the adds go out as 16-byte vector reductions (REDG.ADD.F32x4: one L2
 // atomic per four samples) when the destination is aligned and the run is whole; scalar adds otherwise.
@@ -482,9 +502,15 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
   double c[B];
 #pragma unroll
   for (int s = 0; s < B; s++) {
+#ifdef DOPS_WIDEN_FF
+    const double xin = widen_f32(x[s]);
+    c[s] = a0 * xin + a1 * o1 + a2 * o2;
+    o2 = o1; o1 = widen_or0_f32(x[s]);
+#else
     const double xin = x[s];
     c[s] = a0 * xin + a1 * o1 + a2 * o2;
     o2 = o1; o1 = (double)js_or0f(x[s]);
+#endif
   }
   const double xlast = x[B - 1];
   auto recur = [&]() {
@@ -514,7 +540,11 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
       const float yf = (float)(c[s] - b1 * q1 - b2q2);
       x[s] = yf;
       b2q2 = b2 * q1;  // next sample's b2*y2, ready before it is needed
+#ifdef DOPS_WIDEN_CHAIN
+      q2 = q1; q1 = widen_or0_f32(yf);
+#else
       q2 = q1; q1 = (double)js_or0f(yf);
+#endif
     }
   };
   if (T == 1) {

@@ -248,7 +248,9 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   const char *srot_env = getenv("DUSP_PIPED_SROT");  // "rot" or a fixed warp index 0..NP (experiments)
   const bool srot = srot_env != nullptr;
   const int srot_fixed = srot && srot_env[0] >= '0' && srot_env[0] <= '9' ? std::min(atoi(srot_env), NP) : -1;
-  const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double) + 16;
+  const bool slot = getenv("DUSP_PIPED_SLOT") != nullptr && NP == 4;  // S-warp role by per-SM ticket (experiments)
+  const bool slot_hw = slot && atoi(getenv("DUSP_PIPED_SLOT")) == 2;   // ... matched against the hardware warp slot
+  const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double) + 16;  // (+16: qctr[3] queue heads, qctr[3] = S-warp ticket)
   if (smem > 200 * 1024) return "";
   if (info) {
     info->voices_per_cta = VC; info->threads = (NP + 1) * 32; info->smem_bytes = (int)smem; info->n_buffers = NB;
@@ -295,7 +297,22 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     // Which warp of the CTA is the lane-per-voice warp.  Warps go to the SM's four schedulers by warp index, and the
     // CTAs resident on one SM are blockIdx, blockIdx + #SMs, ...: rotating the role by blockIdx / #SMs puts the
     // (latency-critical) S-warps of co-resident CTAs on different schedulers.  wib: P-warps 0..NP-1, S-warp NP.
-    << (srot ? std::string("  const int s_raw = ") + (srot_fixed >= 0 ? std::to_string(srot_fixed) : std::string("(blockIdx.x / 148) % (NP + 1)")) + ";\n"
+    << (slot ? std::string(
+                   // co-resident CTAs take consecutive tickets of their SM's counter: their lane-per-voice warps get different
+                   // warp indices 0..3, i.e. different SM sub-partitions, whatever the block scheduler's placement was
+                   "  if (threadIdx.x == 0) { unsigned smid_; asm volatile(\"mov.u32 %0, %%smid;\" : \"=r\"(smid_));\n"
+                   "    qctr[3] = (int)(atomicAdd(kp.sm_slots + (smid_ & 255u), 1u) & 3u); }\n"
+                   "  __syncthreads();\n"
+                   + std::string(slot_hw ?
+                   // by hardware warp slot: the first warp of the CTA whose %warpid % 4 equals the ticket
+                   "  __shared__ int hw_of_[8];\n"
+                   "  if (lane == 0) { unsigned wid_; asm volatile(\"mov.u32 %0, %%warpid;\" : \"=r\"(wid_)); hw_of_[wraw] = (int)(wid_ & 3u); }\n"
+                   "  __syncthreads();\n"
+                   "  int s_raw = NP;\n"
+                   "  for (int w_ = NP; w_ >= 0; w_--) if (hw_of_[w_] == qctr[3]) s_raw = w_;\n"
+                   : "  const int s_raw = qctr[3];\n") +
+                   "  const int wib = wraw == s_raw ? NP : wraw - (wraw > s_raw ? 1 : 0);\n")
+        : srot ? std::string("  const int s_raw = ") + (srot_fixed >= 0 ? std::to_string(srot_fixed) : std::string("(blockIdx.x / 148) % (NP + 1)")) + ";\n"
                "  const int wib = wraw == s_raw ? NP : wraw - (wraw > s_raw ? 1 : 0);\n"
              : std::string("  const int wib = wraw;\n"))
     << "  const long long v0 = (long long)blockIdx.x * VC;  // allocations are padded to a multiple of 96 voices\n"

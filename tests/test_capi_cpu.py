@@ -121,6 +121,21 @@ def test_unsupported_configurations_fail_loudly(lib):
     assert "EPOCH" not in circuit_blob(patches_.Boop(440, 0.2))[0]
 
 
+DEVICE_TRANSCENDENTAL = {"semi", "db2s", "midi2f", "pow", "gain", "pan", "filter"}  # libdevice pow / tan in the op
+
+
+@pytest.mark.parametrize("name", sorted(circuits.CASES))
+def test_exact_flag_follows_the_op_set(lib, name):
+    """A case is held to bit-exactness iff no program of its timeline evaluates a transcendental on the device."""
+    fac, _, exact = circuits.CASES[name]
+    d.config.seed(12345)
+    blob, _ = circuit_blob(fac())
+    run = capi.Run([blob], [1])
+    ops = {l.split()[1] for _, p in run.epochs(0) for l in p.disassemble().splitlines()[1:] if len(l.split()) > 1}
+    run.close()
+    assert exact == (not (ops & DEVICE_TRANSCENDENTAL)), sorted(ops & DEVICE_TRANSCENDENTAL)
+
+
 def test_run_splits_a_multi_section_blob(lib):
     """dusp_run_create (csrc/run.cc) owns the run-time protocol: EPOCH sections become programs with their first
     chunk, circuits whose channel counts grow get their warm-up ticks as one-chunk epochs, and nothing needs a GPU
