@@ -562,6 +562,92 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
 }
 
 // ------------------------------------------------------------------ rings
+// A warp whose 32 lanes walk ONE ring along time (T = 32): lane tl owns the B consecutive ring positions
+// [i0 + tl*B, +B).  The tap offset is arbitrary, so i0 is in general not a multiple of 4 and a lane's run is not
+// 16-byte aligned; scalar accesses at a stride of B floats between lanes touch 32 sectors per instruction for 128
+// useful bytes (the L1 pipeline of the SM was the bound of the pipelined kernel, profiles/r1_v13_piped_ncu_summary.txt).
+// Instead every lane moves the ALIGNED float4s [i0 - m + tl*B, +B) (m = i0 & 3, the same for all lanes) and the m
+// elements that belong to a neighbour's run travel by shuffle; only the window's first and last partial float4 use
+// scalar accesses (lane 0 / lane 31).  Requires a 16-byte aligned ring base and i0 + 32*B <= n (no wrap inside the
+// window): the callers check both (warp-uniform) and otherwise keep the element-wise path.
+template <int B>
+DOPS_DEV void ring_load_shifted(float (&x)[B], const float *buf, int i0, int tl) {
+  const int m = i0 & 3;
+  const float4 *b4 = reinterpret_cast<const float4 *>(buf + (i0 - m)) + tl * (B / 4);
+  float f[B + 3];
+#pragma unroll
+  for (int q = 0; q < B / 4; q++) { const float4 t = b4[q]; f[4 * q] = t.x; f[4 * q + 1] = t.y; f[4 * q + 2] = t.z; f[4 * q + 3] = t.w; }
+#pragma unroll
+  for (int j = 0; j < 3; j++) f[B + j] = __shfl_down_sync(0xffffffffu, f[j], 1);  // the next lane's first elements
+  if (tl == 31 && m > 0) {
+#pragma unroll
+    for (int j = 0; j < 3; j++) if (j < m) f[B + j] = buf[i0 - m + 32 * B + j];     // (inside the window: index <= i0 + 32 B - 1)
+  }
+  switch (m) {
+    case 0:
+#pragma unroll
+      for (int s = 0; s < B; s++) x[s] = f[s];
+      break;
+    case 1:
+#pragma unroll
+      for (int s = 0; s < B; s++) x[s] = f[s + 1];
+      break;
+    case 2:
+#pragma unroll
+      for (int s = 0; s < B; s++) x[s] = f[s + 2];
+      break;
+    default:
+#pragma unroll
+      for (int s = 0; s < B; s++) x[s] = f[s + 3];
+  }
+}
+template <int B>
+DOPS_DEV void ring_store_shifted(const float (&y)[B], float *buf, int i0, int tl) {
+  const int m = i0 & 3;
+  float p[3];  // the previous lane's last three values
+#pragma unroll
+  for (int j = 0; j < 3; j++) p[j] = __shfl_up_sync(0xffffffffu, y[B - 3 + j], 1);
+  float f[B];  // the aligned run [i0 - m + tl*B, +B): m elements of the previous lane, then this lane's first B - m
+  switch (m) {
+    case 0:
+#pragma unroll
+      for (int k = 0; k < B; k++) f[k] = y[k];
+      break;
+    case 1:
+      f[0] = p[2];
+#pragma unroll
+      for (int k = 1; k < B; k++) f[k] = y[k - 1];
+      break;
+    case 2:
+      f[0] = p[1]; f[1] = p[2];
+#pragma unroll
+      for (int k = 2; k < B; k++) f[k] = y[k - 2];
+      break;
+    default:
+      f[0] = p[0]; f[1] = p[1]; f[2] = p[2];
+#pragma unroll
+      for (int k = 3; k < B; k++) f[k] = y[k - 3];
+  }
+  float *a = buf + (i0 - m) + tl * B;
+  if (tl == 0 && m > 0) {  // the window's first float4 is partial: positions before i0 are not ours
+#pragma unroll
+    for (int k = 1; k < 4; k++) if (k >= m) a[k] = f[k];
+  } else {
+    *reinterpret_cast<float4 *>(a) = make_float4(f[0], f[1], f[2], f[3]);
+  }
+#pragma unroll
+  for (int q = 1; q < B / 4; q++) reinterpret_cast<float4 *>(a)[q] = make_float4(f[4 * q], f[4 * q + 1], f[4 * q + 2], f[4 * q + 3]);
+  if (tl == 31) {          // ... and so is its last one
+#pragma unroll
+    for (int j = 0; j < 3; j++) if (j < m) a[B + j] = y[B - m + j];
+  }
+}
+#ifdef DOPS_NO_SHIFT  // (experiments: the element-wise path everywhere)
+DOPS_DEV bool ring_base_aligned(const float *) { return false; }
+#else
+DOPS_DEV bool ring_base_aligned(const float *buf) { return (reinterpret_cast<unsigned long long>(buf) & 15ull) == 0; }
+#endif
+
 // FixedDelay.js:14-20 (KIND 0), CombFilter.js:11-17 (1), AllPass.js:8-15 (2).  x: input in, output out.
 template <int B, int T, int KIND>
 DOPS_DEV void c_fixdelay(const Cx<B, T> &cx, float (&x)[B], const float (&g)[B], float *buf, int n, double &tb) {
@@ -749,6 +835,34 @@ DOPS_DEV void c_cbtapc(const Cx<B, T> &cx, float (&x)[B], float *buf, int n, dou
 #pragma unroll
       for (int s = 0; s < B; s++) x[s] = NAN;
     }
+  } else if (T == 32 && (int)idx + T * B <= n && ring_base_aligned(buf)) {
+    // the warp's window does not wrap: aligned 16-byte accesses, neighbours' elements by shuffle (see ring_load_shifted)
+    const int i0 = (int)idx;
+    if (!WRITER) {
+      ring_load_shifted<B>(x, buf, i0, cx.tl);
+      if (WIPE) {
+        float z[B];
+#pragma unroll
+        for (int s = 0; s < B; s++) z[s] = 0.0f;
+        __syncwarp();                                              // every lane has read before any lane wipes
+        ring_store_shifted<B>(z, buf, i0, cx.tl);
+      }
+    } else if (WIPE) {                                             // preWipe: write(0) then mix -> 0 + in
+      float v[B];
+#pragma unroll
+      for (int s = 0; s < B; s++) v[s] = HAS_IN ? __fadd_rn(0.0f, x[s]) : 0.0f;
+      ring_store_shifted<B>(v, buf, i0, cx.tl);
+    } else if (HAS_IN) {                                           // mix: `+=`
+      float v[B];
+      ring_load_shifted<B>(v, buf, i0, cx.tl);
+#pragma unroll
+      for (int s = 0; s < B; s++) v[s] = __fadd_rn(v[s], x[s]);
+      __syncwarp();
+      ring_store_shifted<B>(v, buf, i0, cx.tl);
+    }
+    const int e = i0 + T * B;
+    idx = (double)(e == n ? 0 : e);
+    __syncwarp();
   } else if (T == 1 || n >= T * B) {  // distinct positions within the tile: time-lanes are independent
     int i = (int)idx + cx.tl * B;
     if (i >= n) i %= n;
@@ -772,6 +886,7 @@ DOPS_DEV void c_cbpeek(const Cx<B, T> &cx, float (&x)[B], const float *buf, int 
     for (int s = 0; s < B; s++) x[s] = NAN;
     return;
   }
+  if (T == 32 && (int)idx + T * B <= n && ring_base_aligned(buf)) { ring_load_shifted<B>(x, buf, (int)idx, cx.tl); return; }
   int i = (int)idx + cx.tl * B;
   if (i >= n) i %= n;
   if (i + B <= n) {
@@ -791,7 +906,11 @@ DOPS_DEV void c_cbprefetch(const Cx<B, T> &cx, const float *buf, int n, double i
 }
 template <int B, int T>
 DOPS_DEV void c_cbadv(int n, double &idx) {
-  if (idx >= 0.0) idx = (double)(int)(((long long)idx + T * B) % n);
+  if (idx >= 0.0) {
+    int i = (int)idx + T * B;
+    if (i >= n) i = T * B <= n ? i - n : i % n;
+    idx = (double)i;
+  }
 }
 
 }  // namespace dops

@@ -5,7 +5,8 @@ mkdir -p gpurun_out
 ./scripts/ubench/place > gpurun_out/c2_place.txt 2>&1
 ./scripts/ubench/chain > gpurun_out/c2_chain.txt 2>&1
 W=w3:10000:88064:0
-( python scripts/perf_probe4.py "p24" $W
+( python scripts/perf_probe4.py "p24,DOPS_NO_SHIFT" $W
+  python scripts/perf_probe4.py "p24" $W
   DUSP_PIPED_SLOT=1 python scripts/perf_probe4.py "p24" $W
   DUSP_PIPED_SLOT=2 python scripts/perf_probe4.py "p24" $W
   python scripts/perf_probe4.py "p24,DOPS_WIDEN_CHAIN" $W
