@@ -27,7 +27,7 @@ SYMBOLS = [
     "dusp_program_param_name", "dusp_program_param_index", "dusp_program_param_default",
     "dusp_program_disassemble", "dusp_session_create", "dusp_session_destroy", "dusp_session_num_voices",
     "dusp_session_num_channels", "dusp_session_unit_count", "dusp_session_set_params", "dusp_session_reset",
-    "dusp_session_render", "dusp_session_launch_count", "dusp_session_launch_info", "dusp_rand53",
+    "dusp_session_render", "dusp_session_launch_count", "dusp_session_launch_info", "dusp_rand",
     "dusp_session_tile_info", "dusp_session_warning", "dusp_program_specialise", "dusp_session_poke",
     "dusp_session_adopt", "dusp_program_warmup_ticks",
     "dusp_mix_acc_create", "dusp_mix_acc_open", "dusp_mix_acc_close", "dusp_mix_acc_clear", "dusp_mix_push", "dusp_mix_wait",
@@ -85,8 +85,8 @@ def load():
     L.dusp_session_warning.restype = c.c_char_p
     L.dusp_program_specialise.argtypes = [c.c_void_p, c.c_int, c.c_int, c.c_char_p, c.c_size_t]
     L.dusp_program_specialise.restype = c.c_size_t
-    L.dusp_rand53.argtypes = [c.c_uint64, c.c_uint64]
-    L.dusp_rand53.restype = c.c_double
+    L.dusp_rand.argtypes = [c.c_uint64, c.c_uint64]
+    L.dusp_rand.restype = c.c_double
     L.dusp_mix_acc_create.argtypes = [c.c_int, c.c_size_t, c.c_size_t, c.POINTER(c.c_void_p), c.POINTER(c.c_void_p), c.c_char_p]
     L.dusp_mix_acc_open.argtypes = [c.c_int, c.c_char_p, c.c_size_t, c.POINTER(c.c_void_p), c.POINTER(c.c_void_p)]
     L.dusp_mix_acc_close.argtypes = [c.c_void_p, c.c_int]

@@ -253,12 +253,12 @@ class Noise(Unit):
         self.phase = 0
         self.seed = config.host_random.next_noise_seed() if seed is None else int(seed) & ((1 << 64) - 1)
         self.draw = 1
-        self.y = config.rand53(self.seed, 0) * 2 - 1
+        self.y = config.rand_tick(self.seed, 0) * 2 - 1
 
     def reseed(self, seed):
         self.seed = int(seed) & ((1 << 64) - 1)
         self.draw = 1
-        self.y = config.rand53(self.seed, 0) * 2 - 1
+        self.y = config.rand_tick(self.seed, 0) * 2 - 1
         return self
 
     def blob_props(self):

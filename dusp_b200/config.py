@@ -7,9 +7,11 @@ The device kernels are compiled for exactly these values (``DUSP_SR`` /
 ``Math.random()`` both at graph-construction time (``Osc`` waveform "random",
 ``AllPass.random`` ...) and inside ``Noise._tick`` (``Noise.js:10,23``).  Per
 BASELINE.json's north_star the stochastic units are driven by an injected,
-seeded generator: counter-based splitmix64 keyed by (unit seed, draw index).
-``rand53`` below is the host copy of that function; the oracle and the CUDA
-kernels carry their own restatements and the tests check all three agree.
+seeded generator.  Two functions: ``rand_tick`` is what replaces ``Math.random``
+inside a tick (counter-based, keyed by (unit seed, draw index); the oracle and
+the CUDA kernels carry their own restatements and the tests check all three
+agree); ``rand53`` (splitmix64) serves the construction-time draws of the host
+mirror and the workload generators -- it never runs on the device.
 """
 import math
 
@@ -34,6 +36,21 @@ def _mix64(z):
 def rand53(seed, k):
     """Uniform double in [0,1): draw ``k`` of the stream ``seed``."""
     return (_mix64(seed + (k + 1) * _GOLD) >> 11) * (1.0 / 9007199254740992.0)
+
+
+def rand_tick(seed, k):
+    """The generator injected for ``Math.random`` INSIDE a tick (Noise.js:10,23, SporadicRetrigger.js:13): draw ``k``
+    of the stream ``seed``, uniform in [0,1) with 32 bits of resolution.  Host copy of ``dusp_rand``
+    (include/dusp_b200.h) / ``oracle_rand``; the tests check all three agree."""
+    m = 0xFFFFFFFF
+    x = ((k & m) + (seed & m)) & m
+    x ^= x >> 16
+    x = (x * 0x7FEB352D) & m
+    x ^= x >> 15
+    x = (x * 0x846CA68B) & m
+    x ^= x >> 16
+    x ^= (seed >> 32) & m
+    return x * (1.0 / 4294967296.0)
 
 
 class _HostRandom:

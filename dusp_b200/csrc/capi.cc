@@ -81,7 +81,9 @@ struct Group {
   std::vector<DuspDevInstr> dev_code;
   DuspDevInstr *d_code = nullptr;
   int sub_block = 16, time_lanes = 1, warps_per_cta = 1;
-  FusedKernel *fused = nullptr;  // specialised straight-line kernel (fused.cc); null -> interpreter
+  FusedKernel *fused = nullptr;  // specialised straight-line kernel (fused.cc); null -> interpreter.  Built for DUSP_OUT_VOICES;
+  FusedKernel *fused_mode[3] = {nullptr, nullptr, nullptr};  // ... the other output modes are built on first use (enqueue_block)
+  int piped_vc = 0, fused_wps = 0;
   bool piped = false;            // `fused` is the pipelined kernel (piped.cc)
   PipedInfo pinfo;
   double *d_words = nullptr;
@@ -278,7 +280,7 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
         PipedInfo probe;
         const bool worth = pe || (!generate_piped_source(g.prog, vc, &probe).empty() && probe.n_ops_sequential_stage * 3 <= probe.n_ops);
         if (worth) g.fused = piped_get(g.prog, vc, &g.pinfo, err);
-        if (g.fused) { g.piped = true; g.sub_block = 4; g.time_lanes = 32; g.warps_per_cta = 5; }
+        if (g.fused) { g.piped = true; g.piped_vc = vc; g.sub_block = 4; g.time_lanes = 32; g.warps_per_cta = 5; }
         else if (pe) s->warning = "pipelined kernel unavailable: " + err;
       }
       if (want && pow2 && !g.fused) {
@@ -291,7 +293,7 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
         g.fused = fused_get(g.prog, B, T, wps, err);
         if (!g.fused && fe) return fail(DUSP_ECUDA, "circuit specialisation failed: " + err);
         if (!g.fused) s->warning = "circuit specialisation unavailable, using the interpreter: " + err;
-        if (g.fused) { g.sub_block = B; g.time_lanes = T; g.warps_per_cta = 1; }
+        if (g.fused) { g.fused_wps = wps; g.sub_block = B; g.time_lanes = T; g.warps_per_cta = 1; }
       }
       if (!g.fused) {
         if ((size_t)g.prog.n_slots * B * 128 > 200 * 1024 && T == 1 && !chunky) B = 8;
@@ -651,6 +653,18 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     kp.out_len = pitch; kp.clock0 = s->clock; kp.n_samples = n;
     const int wpc = g.warps_per_cta;
     int grid = 0, smem = 0;
+    FusedKernel *kernel = nullptr;
+    if (g.fused) {  // the kernel compiled for this output mode (NVRTC on first use of a mode, cached per process)
+      const int m = raw ? 2 : out_mode == DUSP_OUT_MIX ? 1 : 0;
+      if (!g.fused_mode[0]) g.fused_mode[0] = g.fused;
+      if (!g.fused_mode[m]) {
+        std::string err;
+        PipedInfo pi;
+        g.fused_mode[m] = g.piped ? piped_get(g.prog, g.piped_vc, &pi, err, m) : fused_get(g.prog, g.sub_block, g.time_lanes, g.fused_wps, err, m);
+        if (!g.fused_mode[m]) return fail(DUSP_ECUDA, "circuit specialisation for this output mode failed: " + err);
+      }
+      kernel = g.fused_mode[m];
+    }
     if (g.fused) {
       FusedParams fp;
       memset(&fp, 0, sizeof fp);
@@ -662,12 +676,12 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
       if (g.piped) {
         grid = (g.n_voices + g.pinfo.voices_per_cta - 1) / g.pinfo.voices_per_cta;
         smem = g.pinfo.smem_bytes;
-        if (fused_launch(g.fused, fp, grid, g.pinfo.threads, smem, st, err) != 0) return fail(DUSP_ECUDA, err);
+        if (fused_launch(kernel, fp, grid, g.pinfo.threads, smem, st, err) != 0) return fail(DUSP_ECUDA, err);
       } else {
         const int V = 32 / g.time_lanes;
         const int n_warps = (g.n_voices + V - 1) / V;
         grid = (n_warps + wpc - 1) / wpc;
-        if (fused_launch(g.fused, fp, grid, wpc * 32, 0, st, err) != 0) return fail(DUSP_ECUDA, err);
+        if (fused_launch(kernel, fp, grid, wpc * 32, 0, st, err) != 0) return fail(DUSP_ECUDA, err);
       }
     } else {
       int e = dusp_launch_render(&kp, g.sub_block, g.time_lanes, wpc, st, &grid, &smem);
@@ -774,12 +788,13 @@ size_t dusp_program_specialise(const dusp_program *p, int sub_block, int time_la
   return n;
 }
 
-double dusp_rand53(uint64_t seed, uint64_t k) {
-  uint64_t z = seed + (k + 1) * 0x9E3779B97F4A7C15ULL;
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
-  z ^= z >> 31;
-  return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+double dusp_rand(uint64_t seed, uint64_t k) {
+  uint32_t x = (uint32_t)k + (uint32_t)seed;
+  x ^= x >> 16; x *= 0x7feb352dU;
+  x ^= x >> 15; x *= 0x846ca68bU;
+  x ^= x >> 16;
+  x ^= (uint32_t)(seed >> 32);
+  return (double)x * (1.0 / 4294967296.0);
 }
 
 }  // extern "C"

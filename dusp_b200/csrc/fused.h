@@ -24,13 +24,14 @@ struct FusedParams {
 };
 
 // CUDA C++ source of the specialised kernel `dusp_fused` for tile shape (B, T).
-std::string generate_fused_source(const Program &p, int B, int T, int min_blocks);
+std::string generate_fused_source(const Program &p, int B, int T, int min_blocks, int out_mode = 0);
+std::string fused_mode_prefix(int out_mode);  // "#define KP_OUT_MODE ...": the output mode as a compile-time constant (< 0: read from the parameters)
 
 struct FusedKernel;  // a loaded module + function (cached per source text, per device)
 
 // Compiles (NVRTC, sm_100a, -fmad=false) and loads the kernel on the current device.  Returns
 // nullptr and fills `err` on failure.  Results are cached for the life of the process.
-FusedKernel *fused_get(const Program &p, int B, int T, int min_blocks, std::string &err);
+FusedKernel *fused_get(const Program &p, int B, int T, int min_blocks, std::string &err, int out_mode = 0);
 // Enqueue; returns 0 or a CUresult/cudaError-like code with `err` filled.
 int fused_launch(FusedKernel *k, const FusedParams &kp, int grid, int block, int smem_bytes, void *stream, std::string &err);
 // NVRTC only (no device needed): returns the cubin size or 0 with `err` filled.  Used by build checks/tests.
@@ -44,11 +45,11 @@ struct PipedInfo {
   int n_ops = 0, n_ops_sequential_stage = 0;  // how much of the circuit lands on the one lane-per-voice warp
 };
 // "" when the program has no admissible 3-stage split (the caller falls back to the tile kernel).
-std::string generate_piped_source(const Program &p, int voices_per_cta, PipedInfo *info);
+std::string generate_piped_source(const Program &p, int voices_per_cta, PipedInfo *info, int out_mode = 0);
 // true when some op has no time-parallel form (recursive filter, Shape, scatter delay ...): only then does the
 // pipeline pay; purely time-parallel circuits run fastest on the tile kernel with all 32 lanes along time
 bool program_has_sequential(const Program &p);
-FusedKernel *piped_get(const Program &p, int voices_per_cta, PipedInfo *info, std::string &err);
+FusedKernel *piped_get(const Program &p, int voices_per_cta, PipedInfo *info, std::string &err, int out_mode = 0);
 size_t piped_compile_only(const Program &p, int voices_per_cta, PipedInfo *info, std::string &err, std::string *src_out);
 
 }  // namespace dusp

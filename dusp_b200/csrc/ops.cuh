@@ -117,34 +117,21 @@ DOPS_DEV double cb_index(double t, double len) {
   if (t < 0.0) t += len;
   return t;
 }
-// injected PRNG (replaces Math.random, Noise.js:10,23): counter-based splitmix64 -> 53-bit uniform
-DOPS_DEV double rand53_mixed(uint64_t z);
-DOPS_DEV double rand53(uint64_t seed, uint64_t k) { return rand53_mixed(seed + (k + 1) * 0x9E3779B97F4A7C15ULL); }
-// the finaliser on a pre-formed counter word z = seed + (k+1)*GOLD (consecutive draws: z += GOLD, no multiply)
-DOPS_DEV double rand53_mixed(uint64_t z) {
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
-  z ^= z >> 31;
-  z >>= 11;  // 53 bits = hi 21 + lo 32.  u32 -> f64 without the (slow) conversion pipe: 2^52 + u is exact and its
-  // bit pattern is 0x43300000:u, so (double)u = hiloint2double(0x43300000, u) - 2^52; recombined with one fma
-  const double hi = __hiloint2double(0x43300000, (int)(uint32_t)(z >> 32)) - 4503599627370496.0;
-  const double lo = __hiloint2double(0x43300000, (int)(uint32_t)z) - 4503599627370496.0;
-  return fma(hi, 4294967296.0, lo) * (1.0 / 9007199254740992.0);
+// Injected PRNG (replaces Math.random inside a tick: Noise.js:10,23, SporadicRetrigger.js:13; include/dusp_b200.h
+// dusp_rand): draw k of stream `seed` = lowbias32(low32(k) + low32(seed)) ^ high32(seed), as a fraction of 2^32.
+DOPS_DEV uint32_t tick_hash(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du;
+  x ^= x >> 15; x *= 0x846ca68bu;
+  return x ^ (x >> 16);
 }
-// Noise.js:10,23 `Math.random()*2 - 1` on a pre-formed counter word, in one FP64 operation.  With k the 53-bit draw,
-// rand = k 2^-53 and 2 rand - 1 = (k - 2^52) 2^-52, every step exact in double.  Writing k = b 2^52 + m, the double
-// 1.m (exponent 0x3FF, mantissa m) is 1 + m 2^-52, so the result is 1.m - 1 (b = 1) or 1.m - 2 (b = 0): both exact
-// differences, bit-identical to the two-rounding-free products of the literal form (6 FP64 operations).
-DOPS_DEV double noise_bipolar_mixed(uint64_t z) {
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
-  z ^= z >> 31;
-  z >>= 11;
-  const uint32_t hi = (uint32_t)(z >> 32), lo = (uint32_t)z;  // hi: 21 bits, bit 20 = b
-  const double one_m = __hiloint2double((int)(0x3FF00000u | (hi & 0xFFFFFu)), (int)lo);
-  const double off = __hiloint2double((int)(0x40000000u - (hi & 0x100000u)), 0);  // b ? 1.0 : 2.0
-  return one_m - off;
+DOPS_DEV double tick_rand(uint64_t seed, uint64_t k) {
+  return (double)(tick_hash((uint32_t)k + (uint32_t)seed) ^ (uint32_t)(seed >> 32)) * (1.0 / 4294967296.0);
 }
+// `Math.random() * 2 - 1` (Noise.js:10,23) for a 32-bit draw u: (u - 2^31) 2^-31, exactly the signed integer
+// int32(u ^ 0x80000000) scaled by a power of two -- exact in double, and its rounding to f32 (the store into the
+// outlet's Float32Array) is the integer-to-float conversion's own round-to-nearest-even.
+DOPS_DEV double noise_bipolar(uint32_t u) { return (double)(int32_t)(u ^ 0x80000000u) * (1.0 / 2147483648.0); }
+DOPS_DEV float noise_bipolar_f32(uint32_t u) { return __int2float_rn((int32_t)(u ^ 0x80000000u)) * (1.0f / 2147483648.0f); }
 DOPS_DEV double dB(double db) { return pow(10.0, db / 20.0); }  // Gain.js:26-28, Pan.js:26-28
 
 // ------------------------------------------------------------------- lane context
@@ -421,7 +408,7 @@ DOPS_DEV void c_noise(const Cx<B, T> &cx, float (&f)[B], double &ph, double &y, 
       ph += (double)f[s];
       if (ph >= SRD) {
         ph = 0.0;
-        y = noise_bipolar_mixed(seed + ((uint64_t)draw + 1) * 0x9E3779B97F4A7C15ULL);
+        y = noise_bipolar(tick_hash((uint32_t)(uint64_t)draw + (uint32_t)seed) ^ (uint32_t)(seed >> 32));
         draw += 1.0;
       }
       f[s] = (float)y;
@@ -432,10 +419,12 @@ DOPS_DEV void c_noise(const Cx<B, T> &cx, float (&f)[B], double &ph, double &y, 
 // stream makes the draws of different time-lanes independent.
 template <int B, int T>
 DOPS_DEV void c_noise1(const Cx<B, T> &cx, float (&o)[B], double &y, double &draw, uint64_t seed) {
-  const uint64_t d0 = (uint64_t)draw + (uint64_t)(cx.tl * B);
-  uint64_t z = seed + (d0 + 1) * 0x9E3779B97F4A7C15ULL;
+  const uint32_t x0 = (uint32_t)(uint64_t)draw + (uint32_t)(cx.tl * B) + (uint32_t)seed;
+  const uint32_t hi = (uint32_t)(seed >> 32);
+  uint32_t u = 0;
 #pragma unroll
-  for (int s = 0; s < B; s++) { y = noise_bipolar_mixed(z); o[s] = (float)y; z += 0x9E3779B97F4A7C15ULL; }
+  for (int s = 0; s < B; s++) { u = tick_hash(x0 + (uint32_t)s) ^ hi; o[s] = noise_bipolar_f32(u); }
+  y = noise_bipolar(u);  // the unit's held value (Noise.js:23): the last draw, unrounded
   draw += (double)(T * B);
   cx.last(y);
 }
@@ -533,6 +522,32 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
     }
     if (!odd) return;
     q1 = s1; q2 = s2;
+#endif
+#ifdef DOPS_MAGIC
+    // The f32 rounding of y (the store into the outlet's Float32Array, Filter.js:43) WITHOUT leaving the FP64 pipe: for
+    // t with exponent E, (t + M) - M with M = 1.5 * 2^(E+29) rounds t to a multiple of 2^(E-23) -- its 24-bit
+    // significand, ties to even like the conversion -- and the result is already the double the next sample needs, so
+    // neither conversion (2 x ~18 cycles on the XU pipe) sits on the recurrence.  Exact whenever every output of the
+    // run is a normal f32 (then `|| 0` changes nothing either); checked once per run from the min / max of the
+    // results' exponent words, anything else (zeros, denormals, overflow, NaN) redoes the run literally below.
+    {
+      const double s1 = q1, s2 = q2;
+      uint32_t lo_ = 0xffffffffu, hi_ = 0u;
+      double b2q2 = b2 * q2;
+#pragma unroll
+      for (int s = 0; s < B; s++) {
+        const double t = c[s] - b1 * q1 - b2q2;
+        const double M = __hiloint2double((int)(((uint32_t)__double2hiint(t) & 0x7ff00000u) + 0x01D80000u), 0);
+        const double r = (t + M) - M;
+        const uint32_t rh = (uint32_t)__double2hiint(r) & 0x7fffffffu;
+        lo_ = min(lo_, rh); hi_ = max(hi_, rh);
+        b2q2 = b2 * q1;
+        q2 = q1; q1 = r;
+        x[s] = (float)r;  // exact
+      }
+      if (lo_ >= 0x38100000u && hi_ < 0x47F00000u) return;  // 2^-126 <= |y| < 2^128 throughout
+      q1 = s1; q2 = s2;
+    }
 #endif
     double b2q2 = b2 * q2;
 #pragma unroll
@@ -642,10 +657,13 @@ DOPS_DEV void ring_store_shifted(const float (&y)[B], float *buf, int i0, int tl
     for (int j = 0; j < 3; j++) if (j < m) a[B + j] = y[B - m + j];
   }
 }
-#ifdef DOPS_NO_SHIFT  // (experiments: the element-wise path everywhere)
-DOPS_DEV bool ring_base_aligned(const float *) { return false; }
-#else
+// Measured on B200 (W3, 10 000 voices): 6.42 ms per launch against 5.87 ms for the element-wise path -- the P-warps are
+// bound by instruction issue / latency, not by L1 sectors, and the shuffles and selects cost more than the wider
+// accesses save.  Kept behind DOPS_SHIFT (DUSP_FUSED_DEFS) for circuits with many taps per voice.
+#ifdef DOPS_SHIFT
 DOPS_DEV bool ring_base_aligned(const float *buf) { return (reinterpret_cast<unsigned long long>(buf) & 15ull) == 0; }
+#else
+DOPS_DEV bool ring_base_aligned(const float *) { return false; }
 #endif
 
 // FixedDelay.js:14-20 (KIND 0), CombFilter.js:11-17 (1), AllPass.js:8-15 (2).  x: input in, output out.

@@ -167,14 +167,17 @@ bool program_has_sequential(const Program &p) {
   return false;
 }
 
-std::string generate_piped_source(const Program &p, int VC, PipedInfo *info) {
+std::string generate_piped_source(const Program &p, int VC, PipedInfo *info, int out_mode) {
   if (VC < 8 || VC > 32 || VC % 8) return "";
-  if (const char *se = getenv("DUSP_PIPED_STEP")) return generate(p, VC, atoi(se) == 128 ? 128 : 256, info);
-  PipedInfo pi;
-  std::string src = generate(p, VC, 256, &pi);
-  if (src.empty() || pi.smem_bytes > 76400) src = generate(p, VC, 128, &pi);
-  if (info) *info = pi;
-  return src;
+  std::string src;
+  if (const char *se = getenv("DUSP_PIPED_STEP")) src = generate(p, VC, atoi(se) == 128 ? 128 : 256, info);
+  else {
+    PipedInfo pi;
+    src = generate(p, VC, 256, &pi);
+    if (src.empty() || pi.smem_bytes > 76400) src = generate(p, VC, 128, &pi);
+    if (info) *info = pi;
+  }
+  return src.empty() ? src : fused_mode_prefix(out_mode) + src;
 }
 
 namespace {
@@ -274,15 +277,15 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "    d[4*q_] = t_.x; d[4*q_+1] = t_.y; d[4*q_+2] = t_.z; d[4*q_+3] = t_.w; } }\n"
     << "#define STX(b, v) { UNROLL for (int q_ = 0; q_ < B / 4; q_++) xs[(b) * (VC * ROW) + q_ * 32] = make_float4(v[4*q_], v[4*q_+1], v[4*q_+2], v[4*q_+3]); }\n"
     // renderChannelData.js:42-44 for the P-warps: lanes along time, a warp stores 512 contiguous bytes
-    << "#define OUT_CHANNEL_P(a, CH) { if (!kp.out_raw) { UNROLL for (int i_ = 0; i_ < B; i_++) a[i_] = js_or0f(a[i_]); }\\\n"
-    << "  if (kp.out_mode == 0) { if (active) { float *dst = out_row + (long long)(CH) * kp.out_len + tl0;\\\n"
+    << "#define OUT_CHANNEL_P(a, CH) { if (!KP_OUT_RAW) { UNROLL for (int i_ = 0; i_ < B; i_++) a[i_] = js_or0f(a[i_]); }\\\n"
+    << "  if (KP_OUT_MODE == 0) { if (active) { float *dst = out_row + (long long)(CH) * kp.out_len + tl0;\\\n"
     << "      if (tl0 + B <= kp.n_samples && ((kp.out_len & 3) | (reinterpret_cast<unsigned long long>(kp.out) & 15ull)) == 0) { UNROLL for (int q_ = 0; q_ < B / 4; q_++)\\\n"
     << "        __stcs(reinterpret_cast<float4 *>(dst) + q_, make_float4(a[4*q_], a[4*q_+1], a[4*q_+2], a[4*q_+3])); }\\\n"
     << "      else { UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) dst[i_] = a[i_]; } } }\\\n"
     << "  else if ((CH) < 2 && active) { UNROLL for (int i_ = 0; i_ < B; i_++) macc[CH][i_] += a[i_]; } }\n"
     // same for the S-warp (one voice per lane)
-    << "#define OUT_CHANNEL_S(a, CH) { if (!kp.out_raw) { UNROLL for (int i_ = 0; i_ < B; i_++) a[i_] = js_or0f(a[i_]); }\\\n"
-    << "  if (kp.out_mode == 0) { if (active) { float *dst = out_row + (long long)(CH) * kp.out_len + tl0;\\\n"
+    << "#define OUT_CHANNEL_S(a, CH) { if (!KP_OUT_RAW) { UNROLL for (int i_ = 0; i_ < B; i_++) a[i_] = js_or0f(a[i_]); }\\\n"
+    << "  if (KP_OUT_MODE == 0) { if (active) { float *dst = out_row + (long long)(CH) * kp.out_len + tl0;\\\n"
     << "      UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) dst[i_] = a[i_]; } }\\\n"
     << "  else if ((CH) < 2 && active) { mix_add<B>(kp.out + (long long)(CH) * kp.out_len + tl0, a, kp.n_samples - tl0);\\\n"
     << "      if (kp.prog_nch == 1) mix_add<B>(kp.out + kp.out_len + tl0, a, kp.n_samples - tl0); } }\n"
@@ -374,7 +377,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     s << "        }\n        __syncwarp();\n";
   }
   s << "      }\n"
-    << "      if (do2 && kp.out_mode != 0) {  // stereo mixdown of this warp's voices: one atomic per sample and channel\n"
+    << "      if (do2 && KP_OUT_MODE != 0) {  // stereo mixdown of this warp's voices: one atomic per sample and channel\n"
     << "        const long long t2 = (long long)(it - 2) * STEP + lane * B;\n"
     << "        mix_add<B>(kp.out + t2, macc[0], kp.n_samples - t2);\n"
     << "        if (kp.prog_nch == 1) mix_add<B>(kp.out + kp.out_len + t2, macc[0], kp.n_samples - t2);\n"
@@ -435,8 +438,8 @@ size_t piped_compile_only(const Program &p, int VC, PipedInfo *info, std::string
   return fused_build_cubin(src, err);
 }
 
-FusedKernel *piped_get(const Program &p, int VC, PipedInfo *info, std::string &err) {
-  const std::string src = generate_piped_source(p, VC, info);
+FusedKernel *piped_get(const Program &p, int VC, PipedInfo *info, std::string &err, int out_mode) {
+  const std::string src = generate_piped_source(p, VC, info, out_mode);
   if (src.empty()) { err = "the circuit has no 3-stage split"; return nullptr; }
   return fused_build(src, "dusp_piped", err);
 }

@@ -90,16 +90,7 @@ __device__ __forceinline__ double cb_index(double t, double len) {
   return t;
 }
 
-// injected PRNG (replaces Math.random): counter-based splitmix64 -> 53-bit uniform
-__device__ __forceinline__ double rand53(uint64_t seed, uint64_t k) {
-  uint64_t z = seed + (k + 1) * 0x9E3779B97F4A7C15ULL;
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
-  z ^= z >> 31;
-  z >>= 11;  // 53 bits; hi 21 + lo 32 recombined exactly with one fma (cheaper than a u64 -> f64 convert)
-  return fma((double)(uint32_t)(z >> 32), 4294967296.0, (double)(uint32_t)z) * (1.0 / 9007199254740992.0);
-}
-
+// injected PRNG (replaces Math.random inside a tick): dops::tick_rand / noise_bipolar in ops.cuh
 __device__ __forceinline__ double shfl_d(double x, int src) { return __shfl_sync(0xffffffffu, x, src); }
 
 template <int B, int T>
@@ -397,7 +388,7 @@ __device__ __forceinline__ void op_noise(const Lane<B, T> &L, const DuspDevInstr
       ph += (double)f[s];
       if (ph >= SRD) {
         ph = 0.0;
-        y = 2.0 * rand53(seed, (uint64_t)draw) - 1.0;
+        y = dops::noise_bipolar(dops::tick_hash((uint32_t)(uint64_t)draw + (uint32_t)seed) ^ (uint32_t)(seed >> 32));
         draw += 1.0;
       }
       f[s] = (float)y;
@@ -434,7 +425,7 @@ __device__ __forceinline__ void op_sretrig(const Lane<B, T> &L, const DuspDevIns
   if (L.tl == 0) {
     const double draw = L.w(I.p);
     const uint64_t seed = (uint64_t)L.w(I.p + 1) | ((uint64_t)L.w(I.p + 2) << 32);
-    const bool fired = rand53(seed, (uint64_t)draw) < (double)r[0] * (double)DUSP_CHUNK / SRD;
+    const bool fired = dops::tick_rand(seed, (uint64_t)draw) < (double)r[0] * (double)DUSP_CHUNK / SRD;
     L.w(I.p) = draw + 1.0;
     L.w(I.p + 3) = fired ? 1.0 : 0.0;
   }
@@ -447,16 +438,14 @@ __device__ __forceinline__ void op_pokeif(const Lane<B, T> &L, const DuspDevInst
 }
 
 template <int B, int T>
-__device__ __forceinline__ void op_noise1(const Lane<B, T> &L, const DuspDevInstr &I) {  // Noise.js:16-28 with F >= sampleRate
-  const double draw = L.w(I.p + 2);
+__device__ __forceinline__ void op_noise1(const Lane<B, T> &L, const DuspDevInstr &I) {  // Noise.js:16-28 with F >= sampleRate: the core in ops.cuh
+  double y = L.w(I.p + 1), draw = L.w(I.p + 2);
   const uint64_t seed = (uint64_t)L.w(I.p + 3) | ((uint64_t)L.w(I.p + 4) << 32);
-  const uint64_t d0 = (uint64_t)draw + (uint64_t)(L.tl * B);  // counter-based stream: draws are independent
+  dops::Cx<B, T> cx; cx.tl = L.tl; cx.lane = L.lane;
   float o[B];
-  double y = 0.0;
-#pragma unroll
-  for (int s = 0; s < B; s++) { y = 2.0 * rand53(seed, d0 + s) - 1.0; o[s] = (float)y; }
+  dops::c_noise1<B, T>(cx, o, y, draw, seed);  // counter-based stream: the draws of the time-lanes are independent
   L.sync();
-  if (L.tl == T - 1) { L.w(I.p + 1) = y; L.w(I.p + 2) = draw + (double)(T * B); }  // phase stays 0
+  if (L.tl == T - 1) { L.w(I.p + 1) = y; L.w(I.p + 2) = draw; }  // phase stays 0
   L.st(o, I.out[0]);
 }
 

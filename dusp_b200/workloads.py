@@ -5,7 +5,7 @@ seed and the GLOBAL voice index so any rank can build its own shard."""
 import numpy as np
 
 from . import components as C, patches as P, quick
-from .config import rand53, _mix64
+from .config import rand53, rand_tick, _mix64
 
 SR = 44100
 
@@ -83,7 +83,7 @@ def w3_overrides(blob, params):
     filt, pan, reader = u["Filter"][0], u["Pan"][0], u["CircleBufferReader"][0]
     mult, noise = u["Multiply"][0], u["Noise"][0]
     seeds = params["seed"]
-    y0 = np.array([2 * rand53(int(s), 0) - 1 for s in seeds])
+    y0 = np.array([2 * rand_tick(int(s), 0) - 1 for s in seeds])
     return {
         "u%d.f[0]" % filt: params["f"], "u%d.offset[0]" % reader: params["dly"], "u%d.b[0]" % mult: params["g"],
         "u%d.pan[0]" % pan: params["pan"], "u%d.seed_lo" % noise: (seeds & np.uint64(0xFFFFFFFF)).astype(np.float64),

@@ -227,8 +227,13 @@ int dusp_mix_push(const float *local, float *remote, size_t n_floats, unsigned *
                   void *cuda_stream);
 int dusp_mix_wait(const unsigned *counter, unsigned target, unsigned *timed_out, void *cuda_stream);
 
-/* The injected PRNG (replaces Math.random in Noise.js:10,23): draw k of stream `seed`. */
-double dusp_rand53(uint64_t seed, uint64_t k);
+/* The injected PRNG (replaces Math.random inside a tick: Noise.js:10,23, SporadicRetrigger.js:13): draw k of stream
+ * `seed`, uniform in [0,1) with 32 bits of resolution:
+ *   x = low32(k) + low32(seed); x ^= x >> 16; x *= 0x7feb352d; x ^= x >> 15; x *= 0x846ca68b; x ^= x >> 16;
+ *   rand = (x ^ high32(seed)) / 2^32
+ * Counter-based, so the draws of a chunk are independent of each other (lanes along time) and a Noise sample
+ * `2 rand - 1` rounded to f32 is one integer-to-float conversion: float(int32(u ^ 0x80000000)) * 2^-31. */
+double dusp_rand(uint64_t seed, uint64_t k);
 
 #ifdef __cplusplus
 }

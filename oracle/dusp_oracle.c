@@ -241,14 +241,19 @@ const float *oracle_shape_table(const char *name) {
   return NULL;
 }
 
-/* Injected PRNG replacing Math.random (Noise.js:10,23): counter-based
- * splitmix64 keyed by (unit seed, draw index) -> 53-bit uniform in [0,1). */
+/* Injected PRNG replacing Math.random inside a tick (Noise.js:10,23, SporadicRetrigger.js:13): counter-based,
+ * keyed by (unit seed, draw index), 32 bits of resolution (a legal Math.random: the result is only ever rounded to
+ * a Float32Array sample or compared with a probability).  Draw k of stream `seed`:
+ *   x = low32(k) + low32(seed);  x ^= x >> 16;  x *= 0x7feb352d;  x ^= x >> 15;  x *= 0x846ca68b;  x ^= x >> 16;
+ *   u = x ^ high32(seed);        rand = u / 2^32
+ * (the 32-bit integer finaliser "lowbias32"; the stream's low word offsets the counter, its high word the output). */
 double oracle_rand(uint64_t seed, uint64_t k) {
-  uint64_t z = seed + (k + 1) * 0x9E3779B97F4A7C15ULL;
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
-  z ^= z >> 31;
-  return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+  uint32_t x = (uint32_t)k + (uint32_t)seed;
+  x ^= x >> 16; x *= 0x7feb352dU;
+  x ^= x >> 15; x *= 0x846ca68bU;
+  x ^= x >> 16;
+  x ^= (uint32_t)(seed >> 32);
+  return (double)x * (1.0 / 4294967296.0);
 }
 
 /* ----------------------------------------------------------- blob parser */

@@ -24,9 +24,11 @@ def test_header_symbols_are_exported(lib):
     assert lib.dusp_abi_version() == 1
 
 
-def test_rand53_agrees_across_host_library_and_oracle(lib, oracle):
-    for seed, k in [(0, 0), (77, 5), (2**64 - 1, 123456789), (0xDEADBEEF, 2**40)]:
-        assert lib.dusp_rand53(seed, k) == d.config.rand53(seed, k) == oracle.rand(seed, k)
+def test_tick_generator_agrees_across_host_library_and_oracle(lib, oracle):
+    for seed, k in [(0, 0), (77, 5), (2**64 - 1, 123456789), (0xDEADBEEF, 2**40), (0x0123456789ABCDEF, 2**32 - 1)]:
+        assert lib.dusp_rand(seed, k) == d.config.rand_tick(seed, k) == oracle.rand(seed, k)
+    u = [d.config.rand_tick(0xC0FFEE1234, k) for k in range(4096)]
+    assert 0.0 <= min(u) and max(u) < 1.0 and abs(sum(u) / len(u) - 0.5) < 0.02 and len(set(u)) == len(u)
 
 
 @pytest.mark.parametrize("name", sorted(circuits.CASES))

@@ -140,7 +140,7 @@ def w3_overrides(blob, f, dly, g, pan, seeds):
     reader, mult, noise = unit_index(blob, "CircleBufferReader"), unit_index(blob, "Multiply"), unit_index(blob, "Noise")
     names = ["u%d.f[0]" % filt, "u%d.offset[0]" % reader, "u%d.b[0]" % mult, "u%d.pan[0]" % pan_u,
              "u%d.seed_lo" % noise, "u%d.seed_hi" % noise, "u%d.y" % noise]
-    y0 = np.array([2 * d.config.rand53(int(sd), 0) - 1 for sd in seeds])
+    y0 = np.array([2 * d.config.rand_tick(int(sd), 0) - 1 for sd in seeds])
     vals = np.stack([f, dly, g, pan, (seeds & 0xFFFFFFFF).astype(np.float64), (seeds >> 32).astype(np.float64), y0], axis=1)
     return names, vals
 
@@ -556,7 +556,7 @@ def test_graph_edit_for_a_batch_with_per_voice_parameters(lib, oracle, kernel_mo
     b = d.Batch(circuit(1000.0, 1), 72)
     blob0 = b.blob
     filt, noise = unit_index(blob0, "Filter"), unit_index(blob0, "Noise")
-    y0 = np.array([2 * d.config.rand53(int(sd), 0) - 1 for sd in seeds])
+    y0 = np.array([2 * d.config.rand_tick(int(sd), 0) - 1 for sd in seeds])
     b.run.set_params(0, ["u%d.f[0]" % filt, "u%d.seed_lo" % noise, "u%d.seed_hi" % noise, "u%d.y" % noise],
                      np.stack([fs, (seeds & 0xFFFFFFFF).astype(np.float64), (seeds >> 32).astype(np.float64), y0], axis=1))
     try:

@@ -8,7 +8,7 @@ import pytest
 
 import dusp_b200 as d
 from dusp_b200 import components as C, patches as P
-from dusp_b200.config import rand53
+from dusp_b200.config import rand_tick
 from dusp_b200.graphblob import strip_order
 from dusp_b200.render import circuit_blob
 
@@ -95,15 +95,15 @@ def test_untriggered_ramp_is_constant(oracle):
 def test_noise_uses_injected_stream(oracle):
     n = C.Noise(seed=77)
     out = render(oracle, n, 0.01)[0]
-    expect = np.array([2 * rand53(77, k + 1) - 1 for k in range(len(out))]).astype(np.float32)
+    expect = np.array([2 * rand_tick(77, k + 1) - 1 for k in range(len(out))]).astype(np.float32)
     assert np.array_equal(out, expect)
-    assert oracle.rand(77, 5) == rand53(77, 5)
+    assert oracle.rand(77, 5) == rand_tick(77, 5)
 
 
 def test_noise_sample_and_hold_period(oracle):
     out = render(oracle, C.Noise(11025, seed=5), 0.01)[0]  # new draw every 4th sample
-    assert out[0] == out[1] == out[2] == np.float32(2 * rand53(5, 0) - 1)
-    assert out[3] == np.float32(2 * rand53(5, 1) - 1) and out[7] == np.float32(2 * rand53(5, 2) - 1)
+    assert out[0] == out[1] == out[2] == np.float32(2 * rand_tick(5, 0) - 1)
+    assert out[3] == np.float32(2 * rand_tick(5, 1) - 1) and out[7] == np.float32(2 * rand_tick(5, 2) - 1)
 
 
 def test_filter_unset_f_renders_zeros(oracle):
@@ -199,7 +199,7 @@ def test_sporadic_retriggerer_uses_injected_stream(oracle):
     out = oracle.render(blob, 0.5)[0]
     t, want = 0, []
     for k in range((len(out) + 255) // 256):
-        if config.rand53(77, k) < float(np.float32(40)) * 256 / 44100:
+        if config.rand_tick(77, k) < float(np.float32(40)) * 256 / 44100:
             t = 0
         want += [1 + t + 1 + i for i in range(256)]
         t += 256
