@@ -41,9 +41,12 @@ def parse_args():
     ap.add_argument("--seconds", type=float, default=60.0)
     ap.add_argument("--block-seconds", type=float, default=2.0)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-seconds", type=float, default=2.5, help="audio rendered per e2e step (the same at every N)")
+    ap.add_argument("--no-workloads", action="store_true", help="skip the W1 / W2 / W4 sub-records (N = 1 only)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-mix", action="store_true", help="skip the W5 stereo-mixdown + NCCL reduce leg")
     ap.add_argument("--mix-voices", type=int, default=12500, help="W5 voices per GPU (100 000 / 8)")
+    ap.add_argument("--w4-circuits", type=int, default=10000)
     ap.add_argument("--mix-collective", default="auto", choices=["auto", "p2p", "nccl"],
                     help="transport of the mixdown sum: one-sided adds into rank 0's accumulator over NVLink peer memory "
                          "(default for N > 1) or ncclReduce per block")
@@ -197,7 +200,61 @@ def measure_mixdown(args, rank, world, local_rank, barrier):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_step = float(ms.item()) / k
+    r.close()
+
+    # ---- self-check of the sum (every N > 1 run): block 0 of every rank's LOCAL mix is all-gathered and added in
+    # f64 on rank 0; both transports must deliver that sum (1e-5 of the mix's full scale).
+    mix_check = None
+    if world > 1:
+        n0 = min(blk, n_total)
+        local = torch.zeros(2 * n0, dtype=torch.float32, device="cuda")
+        sess.reset()
+        sess.render_device(n0, local.data_ptr(), capi.OUT_MIX, stream.cuda_stream)
+        torch.cuda.synchronize()
+        gathered = [torch.empty_like(local) for _ in range(world)] if rank == 0 else None
+        dist.gather(local, gathered, dst=0)
+        want = torch.stack(gathered).double().sum(dim=0) if rank == 0 else None
+        mix_check = {}
+        for transport in ("p2p", "nccl"):
+            got = {}
+
+            def keep(t0, n, t):
+                if t0 == 0:
+                    got["b0"] = t.reshape(-1).clone()
+
+            rr = MD.MixdownRenderer(sess, blk, torch.device("cuda", local_rank), collective=transport)
+            sess.reset()
+            rr.render(n0, keep)
+            torch.cuda.synchronize()
+            used = rr.collective
+            rr.close()
+            barrier()
+            if rank == 0:
+                full = max(1.0, float(want.abs().max()))
+                err = float((got["b0"].double() - want).abs().max())
+                mix_check[transport] = {"max_abs_err": err, "full_scale": full, "ok": err <= 1e-5 * full, "transport_used": used}
+
+    # ---- e2e of the mix path: the whole W5 render through dusp_session_render with a HOST [2][n] buffer (this is the
+    # output mode whose result fits through PCIe: 2 * n floats whatever the voice count)
+    hmix = torch.empty(2 * n_total, dtype=torch.float32).pin_memory()
+
+    def step_host():
+        sess.reset()
+        sess.render_into_host(hmix.data_ptr(), n_total, capi.OUT_MIX)
+
+    step_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(k):
+        step_host()
+    barrier()
+    dt = torch.tensor([time.perf_counter() - t0], device="cuda")
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
     units = (len(i2) * p2.num_units + len(i3) * p3.num_units) * world
+    e2e_mix = {"value": units * n_total * k / float(dt.item()), "unit": "unit-samples/s", "d2h_bytes_per_step": 2 * n_total * 4,
+               "note": "every rank renders its shard's stereo mix into its own pinned host buffer (no cross-rank sum: "
+                       "the host-side sum of N [2][n] arrays is not part of the timed region)"}
     out = {"workload": "W5 (BASELINE configs[4] shape): %d voices/GPU (W2-live on even, W3 on odd global indices) x %g s, "
                        "stereo mixdown only" % (nv, secs),
            "value": units * n_total / (ms_step / 1e3), "unit": "unit-samples/s", "voices_total": nv * world,
@@ -207,9 +264,71 @@ def measure_mixdown(args, rank, world, local_rank, barrier):
                           "(system-scope float reductions + arrival counters, csrc/mixpush.cu); no rendezvous kernel" % blk
                           if r.collective == "p2p" else
                           "ncclReduce(sum) of the [2][%d] f32 mix per block onto rank 0, async (overlaps the next block)" % blk),
-           "mix_peak": peak[0]}
-    r.close()
+           "mix_peak": peak[0], "mix_check": mix_check, "e2e_mix": e2e_mix}
     sess.close()
+    return out
+
+
+# ------------------------------------------- the other BASELINE configs (N = 1): W1, W2, W4
+def measure_workloads(args):
+    """BASELINE configs[0], [1] and [3] as short device-timed legs beside the headline (one GPU): per-voice output
+    into a recycled device block buffer, state resident, CUDA events, best of 3 passes after one warm-up pass."""
+    import numpy as np
+    import torch
+    from dusp_b200 import capi, workloads as W
+    from dusp_b200.render import circuit_blob
+
+    st = torch.cuda.current_stream()
+
+    def timed(sess, total, rows, blk=88064):
+        blk = min(blk, (total + 255) // 256 * 256)
+        buf = torch.empty(rows * blk, dtype=torch.float32, device="cuda")
+        best = 1e30
+        for rep in range(4):
+            sess.reset()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            for t in range(0, total, blk):
+                sess.render_device(min(blk, total - t), buf.data_ptr(), capi.OUT_VOICES, st.cuda_stream)
+            e1.record(st)
+            torch.cuda.synchronize()
+            if rep:
+                best = min(best, e0.elapsed_time(e1))
+        return best / 1e3
+
+    out = []
+    total = 10 * SR
+    # W1: `[Osc 440]`, 10 s mono, one circuit (a latency test on a GPU)
+    blob, _ = circuit_blob(W.w1_circuit())
+    p = capi.Program(blob)
+    s = capi.Session([p], [1], 0)
+    g = timed(s, total, 1, blk=441088)
+    out.append({"workload": "W1 (BASELINE configs[0]): [Osc 440], 10 s mono, one circuit", "voices": 1, "units_per_voice": 1,
+                "value": total / g, "unit": "unit-samples/s", "ms": g * 1e3, "kernel": s.launch_info()})
+    s.close()
+    # W2: FM ring-mod patch, 1 000 voices x 10 s, every voice its own live Ramp
+    blob, _ = circuit_blob(W.w2_live_circuit())
+    p = capi.Program(blob)
+    s = capi.Session([p], [1000], 0)
+    ov = W.w2_overrides(blob, W.w2_params(0, 1000))
+    s.set_params(0, list(ov), np.stack([ov[k] for k in ov], axis=1))
+    g = timed(s, total, 1000)
+    out.append({"workload": "W2 (BASELINE configs[1]): [Multiply A:[Osc #o f:<live Ramp>] B:#o], 1 000 voices x 10 s",
+                "voices": 1000, "units_per_voice": p.num_units, "value": 1000 * p.num_units * total / g, "unit": "unit-samples/s",
+                "ms": g * 1e3, "bytes_per_voice_sample": p.bytes_per_voice_sample(capi.OUT_VOICES), "kernel": s.launch_info()})
+    s.close()
+    # W4: 10 000 random Dusp circuits (depth 4-8), 10 s mono, one multi-program launch per block
+    nc = args.w4_circuits
+    t0 = time.perf_counter()
+    progs = [capi.Program(circuit_blob(W.w4_circuit(i))[0]) for i in range(nc)]
+    s = capi.Session(progs, [1] * nc, 0)
+    build_s = time.perf_counter() - t0
+    g = timed(s, total, nc)
+    out.append({"workload": "W4 (BASELINE configs[3]): %d random Dusp circuits (depth 4-8), 10 s mono" % nc, "voices": nc,
+                "units_per_voice": s.unit_count / nc, "value": s.unit_count * total / g, "unit": "unit-samples/s", "ms": g * 1e3,
+                "host_build_s": build_s, "kernel": s.launch_info()})
+    s.close()
     return out
 
 
@@ -299,23 +418,27 @@ def run_b200(args, rank, world, local_rank):
     full = [m for m, (t, n) in zip(launch_ms, blocks * args.steps) if n == blk] or launch_ms
     avg_launch_ms = sum(full) / len(full)
     achieved = bpvs * nv * blk / (avg_launch_ms / 1e3) / 1e9
-    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum of one such launch, from the committed ncu capture
+    # dram__bytes_read.sum + dram__bytes_write.sum of one such launch, from the committed `ncu --set full` capture
+    # (profiles/ncu_traffic.json names the build it was taken from; ncu cannot run inside the timed bench)
+    traffic, traffic_build = None, None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
         if tj["voices"] == nv and tj["samples"] == blk:
             traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+            traffic_build = tj.get("build")
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": traffic, "algorithmic_bytes_per_launch": bpvs * nv * blk, "peak_source": peak_src, "kernel": "dusp_piped" if sess.launch_info().get("block") == 160 else "dusp_fused",
+                "traffic": traffic, "traffic_capture": traffic_build, "algorithmic_bytes_per_launch": bpvs * nv * blk, "peak_source": peak_src, "kernel": "dusp_piped" if sess.launch_info().get("block") == 160 else "dusp_fused",
                 "bytes_per_voice_sample": bpvs, "avg_launch_ms": avg_launch_ms,
                 "kernel_share_of_step": sum(launch_ms) / total_ms}
 
     # e2e: the C-ABI call a host shim makes, HOST output buffers (pinned), D2H inside the timed region
     e2e = None
     if not args.no_e2e:
-        # 10k voices x 10 s stereo = 35 GB of pinned host memory per rank at N <= 2, less per rank beyond
-        e2e_secs = min(args.seconds, 10.0, 20.0 / world)  # <= 70 GB pinned per box (the GPU box has 196 GB of RAM)
+        # the SAME workload at every N (so the four scaling figures compare): 10k voices x 2.5 s stereo per rank
+        # = 8.8 GB of pinned host memory per rank, 70 GB per box at N = 8
+        e2e_secs = min(args.seconds, args.e2e_seconds)
         n_e2e = int(e2e_secs * SR)
         hbuf = torch.empty(nv * nch * n_e2e, dtype=torch.float32).pin_memory()
         dwords = np.stack([ov[k] for k in ov], axis=1)
@@ -338,12 +461,18 @@ def run_b200(args, rank, world, local_rank):
         e2e_val = nv * n_e2e * world * units * k / float(dt.item())
         e2e = {"value": e2e_val, "unit": "unit-samples/s", "h2d_bytes_per_step": int(dwords.size * 8),
                "d2h_bytes_per_step": int(nv * nch * n_e2e * 4), "seconds_rendered": e2e_secs,
-               "note": "per-voice stereo channel data copied to pinned host memory (PCIe-bound)"}
+               "GBps_d2h_per_rank": nv * nch * n_e2e * 4 * k / float(dt.item()) / 1e9,
+               "note": "per-voice stereo channel data copied to pinned host memory (PCIe-bound); the same per-rank "
+                       "workload at every N"}
         del hbuf
 
     mixdown = None
     if not args.no_mix:
         mixdown = measure_mixdown(args, rank, world, local_rank, barrier)
+
+    workloads = None
+    if world == 1 and not args.no_workloads:
+        workloads = measure_workloads(args)
 
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -361,7 +490,8 @@ def run_b200(args, rank, world, local_rank):
                        "l2": "working set (rings %.2f GB + block outputs %.1f GB) larger than L2"
                              % (nv * 44100 * 4 / 1e9, 2 * nv * nch * blk * 4 / 1e9)},
             "realtime_voices": value / units / SR, "voice_samples_per_sec": value / units,
-            "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "mixdown": mixdown, "gpu_launches": int(launches),
+            "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "mixdown": mixdown, "workloads": workloads,
+            "gpu_launches": int(launches),
             "launch": sess.launch_info(), "clocks": clocks,
         }
         print(json.dumps(line), flush=True)

@@ -96,7 +96,7 @@ int dusp_mix_acc_close(float *acc, int owner) {
 }
 
 int dusp_mix_acc_clear(float *acc, size_t n_floats, size_t n_counters, void *cuda_stream) {
-  const size_t bytes = (n_floats + 3) / 4 * 16 + n_counters * sizeof(unsigned);
+  const size_t bytes = (n_floats + 3) / 4 * 16 + (n_counters + 1) * sizeof(unsigned);  // + the timed-out word behind the counters
   cudaError_t e = cudaMemsetAsync(acc, 0, bytes, (cudaStream_t)cuda_stream);
   return e == cudaSuccess ? DUSP_OK : dusp::fail_public(DUSP_ECUDA, std::string("dusp_mix_acc_clear: ") + cudaGetErrorString(e));
 }

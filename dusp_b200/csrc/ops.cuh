@@ -657,10 +657,10 @@ DOPS_DEV void ring_store_shifted(const float (&y)[B], float *buf, int i0, int tl
     for (int j = 0; j < 3; j++) if (j < m) a[B + j] = y[B - m + j];
   }
 }
-// Measured on B200 (W3, 10 000 voices): 6.42 ms per launch against 5.87 ms for the element-wise path -- the P-warps are
-// bound by instruction issue / latency, not by L1 sectors, and the shuffles and selects cost more than the wider
-// accesses save.  Kept behind DOPS_SHIFT (DUSP_FUSED_DEFS) for circuits with many taps per voice.
-#ifdef DOPS_SHIFT
+// Measured on B200 (W3, 10 000 voices, per launch): 5.53 ms against 5.86 ms for the element-wise path.  (With the
+// round-1 splitmix64 noise the same change cost time, 6.42 against 5.87 ms: the P-warps' extra shuffles and selects
+// then competed with the lane-per-voice warp for issue slots.)  DOPS_NO_SHIFT (DUSP_FUSED_DEFS) restores the old path.
+#ifndef DOPS_NO_SHIFT
 DOPS_DEV bool ring_base_aligned(const float *buf) { return (reinterpret_cast<unsigned long long>(buf) & 15ull) == 0; }
 #else
 DOPS_DEV bool ring_base_aligned(const float *) { return false; }

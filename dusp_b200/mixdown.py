@@ -165,7 +165,7 @@ class MixdownRenderer:
         work, t0, n = self.pending[i]
         if work is not None:
             work.wait()  # orders the current stream after the collective
-        if on_block is not None:
+        if on_block is not None and self.rank == 0:  # the other ranks' buffers are undefined after a reduce onto rank 0
             on_block(t0, n, self.bufs[i][:2 * n].view(2, n))
         self.pending[i] = None
 
