@@ -46,26 +46,6 @@ constexpr double SRD = 44100.0;
 DOPS_DEV double js_or0(double x) { return fabs(x) > 0.0 ? x : 0.0; }  // `x || 0`: NaN, +0, -0 -> +0 (one compare: |x| > 0 is false for all three)
 DOPS_DEV float js_or0f(float x) { return fabsf(x) > 0.0f ? x : 0.0f; }
 
-// f32 -> f64 on the integer pipe (the conversion instruction runs on the XU pipe, 16 lanes per clock and SM: the lane-per-
-// voice warp of the pipelined kernel is bound by it).  A normal f32 widens exactly with a shift and an add: sign and
-// exponent move from bits 31..23 to 31..20 (the exponent bias grows by 896), the mantissa's low 3 bits start the low
-// word.  Zeros, denormals, Inf and NaN (exponent field 0 or 255) take the conversion instruction.
-DOPS_DEV double widen_f32(float x) {
-  const uint32_t u = __float_as_uint(x);
-  const uint32_t e = (u >> 23) & 0xffu;
-  double d = __hiloint2double((int)((u >> 3) + ((u >> 31) ? 0xA8000000u : 0x38000000u)), (int)(u << 29));
-  if (e == 0u || e == 0xffu) d = (double)x;
-  return d;
-}
-// (double)(x || 0) the same way: +-0 and NaN give +0
-DOPS_DEV double widen_or0_f32(float x) {
-  const uint32_t u = __float_as_uint(x);
-  const uint32_t a = u & 0x7fffffffu, e = a >> 23;
-  double d = __hiloint2double((int)((u >> 3) + ((u >> 31) ? 0xA8000000u : 0x38000000u)), (int)(u << 29));
-  if (e == 0u || e == 0xffu) d = (a == 0u || a > 0x7f800000u) ? 0.0 : (double)x;
-  return d;
-}
-
 // Stereo mixdown accumulation (DUSP_OUT_MIX): y[0..B) += into dst[0..B), `room` = samples left before the requested
 // length.  A lane owns B consecutive samples, so the adds go out as 16-byte vector reductions (REDG.ADD.F32x4: one L2
 // atomic per four samples) when the destination is aligned and the run is whole; scalar adds otherwise.
@@ -476,10 +456,58 @@ DOPS_DEV void c_filter(const Cx<B, T> &cx, float (&x)[B], const float (&f)[B], i
 
 // Filter.js:27-51 with host-derived coefficients (constant F).
 //   y[n] = ((a0 x + a1 x1) + a2 x2) - b1 y1 - b2 y2
-// The bracket depends only on inputs: all lanes at once.  The two subtractions and the f32
-// rounding are the recurrence: the T lanes of a voice run it in turn, handing (y1, y2) on by
+// The bracket depends only on inputs (filterc_ff: any number of samples at once).  The two subtractions and the f32
+// rounding are the recurrence (filterc_rec): strictly one sample after the other.
+// State convention: x1 raw previous input, x2 / y2 already `|| 0`-normalised, y1 previous output (f32-valued);
+// o1 / o2 / q1 / q2 are their normalised forms carried in registers.
+template <int B>
+DOPS_DEV void filterc_ff(const float (&x)[B], double (&c)[B], double a0, double a1, double a2, double &o1, double &o2) {
+#pragma unroll
+  for (int s = 0; s < B; s++) {
+    const double xin = x[s];
+    c[s] = a0 * xin + a1 * o1 + a2 * o2;
+    o2 = o1; o1 = (double)js_or0f(x[s]);
+  }
+}
+// MAGIC: the f32 rounding of y (the store into the outlet's Float32Array, Filter.js:43) without leaving the FP64 pipe.
+// For t with exponent E, (t + M) - M with M = 1.5 * 2^(E+29) rounds t to a multiple of 2^(E-23) -- its 24-bit
+// significand, ties to even like the conversion -- and the result is already the double the next sample needs, so
+// neither conversion (2 x ~18 cycles on the XU pipe) sits on the recurrence.  Exact whenever every output of the run
+// is a normal f32 (then `|| 0` changes nothing either); checked once per run from the min / max of the results'
+// exponent words; anything else (zeros, denormals, overflow, NaN) redoes the run in the literal form.  Measured: only
+// pays where the warp issues nothing but the recurrence (the pipelined kernel's S-warp after the feed-forward split).
+template <int B, bool MAGIC>
+DOPS_DEV void filterc_rec(const double (&c)[B], float (&y)[B], double b1, double b2, double &q1, double &q2) {
+  if (MAGIC) {
+    const double s1 = q1, s2 = q2;
+    uint32_t lo_ = 0xffffffffu, hi_ = 0u;
+    double b2q2 = b2 * q2;
+#pragma unroll
+    for (int s = 0; s < B; s++) {
+      const double t = c[s] - b1 * q1 - b2q2;
+      const double M = __hiloint2double((int)(((uint32_t)__double2hiint(t) & 0x7ff00000u) + 0x01D80000u), 0);
+      const double r = (t + M) - M;
+      const uint32_t rh = (uint32_t)__double2hiint(r) & 0x7fffffffu;
+      lo_ = min(lo_, rh); hi_ = max(hi_, rh);
+      b2q2 = b2 * q1;
+      q2 = q1; q1 = r;
+      y[s] = (float)r;  // exact
+    }
+    if (lo_ >= 0x38100000u && hi_ < 0x47F00000u) return;  // 2^-126 <= |y| < 2^128 throughout
+    q1 = s1; q2 = s2;
+  }
+  double b2q2 = b2 * q2;
+#pragma unroll
+  for (int s = 0; s < B; s++) {
+    const float yf = (float)(c[s] - b1 * q1 - b2q2);
+    y[s] = yf;
+    b2q2 = b2 * q1;  // next sample's b2*y2, ready before it is needed
+    q2 = q1; q1 = (double)js_or0f(yf);
+  }
+}
+
+// T > 1: the bracket on all lanes at once; the T lanes of a voice run the recurrence in turn, handing (y1, y2) on by
 // shuffle -- the same operations in the same order as the reference, so bit-exact.
-// State: x1 raw previous input, x2/y2 already `|| 0`-normalised, y1 previous output (f32-valued).
 template <int B, int T>
 DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1, double a2, double b1, double b2,
                         double &x1, double &x2, double &y1, double &y2) {
@@ -489,85 +517,14 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
     if (cx.tl > 0) { o1 = (double)js_or0f(pm1); o2 = (double)js_or0f(pm2); }
   }
   double c[B];
-#pragma unroll
-  for (int s = 0; s < B; s++) {
-#ifdef DOPS_WIDEN_FF
-    const double xin = widen_f32(x[s]);
-    c[s] = a0 * xin + a1 * o1 + a2 * o2;
-    o2 = o1; o1 = widen_or0_f32(x[s]);
-#else
-    const double xin = x[s];
-    c[s] = a0 * xin + a1 * o1 + a2 * o2;
-    o2 = o1; o1 = (double)js_or0f(x[s]);
-#endif
-  }
   const double xlast = x[B - 1];
-  auto recur = [&]() {
-#ifdef DOPS_SPEC_FILTER
-    // The `|| 0` on the fed-back output (Filter.js:45-48) only ever changes a NaN or a -0.  Run the
-    // recurrence without it on the dependency chain, note whether such a value occurred, and in that
-    // (rare) case redo the run from the saved state with the literal form below.
-    const double s1 = q1, s2 = q2;
-    bool odd = false;
-    {
-      double b2q2 = b2 * q2;
-#pragma unroll
-      for (int s = 0; s < B; s++) {
-        const float yf = (float)(c[s] - b1 * q1 - b2q2);
-        x[s] = yf;
-        b2q2 = b2 * q1;
-        q2 = q1; q1 = (double)yf;
-        odd |= (yf != yf) | (__float_as_uint(yf) == 0x80000000u);
-      }
-    }
-    if (!odd) return;
-    q1 = s1; q2 = s2;
-#endif
-#ifdef DOPS_MAGIC
-    // The f32 rounding of y (the store into the outlet's Float32Array, Filter.js:43) WITHOUT leaving the FP64 pipe: for
-    // t with exponent E, (t + M) - M with M = 1.5 * 2^(E+29) rounds t to a multiple of 2^(E-23) -- its 24-bit
-    // significand, ties to even like the conversion -- and the result is already the double the next sample needs, so
-    // neither conversion (2 x ~18 cycles on the XU pipe) sits on the recurrence.  Exact whenever every output of the
-    // run is a normal f32 (then `|| 0` changes nothing either); checked once per run from the min / max of the
-    // results' exponent words, anything else (zeros, denormals, overflow, NaN) redoes the run literally below.
-    {
-      const double s1 = q1, s2 = q2;
-      uint32_t lo_ = 0xffffffffu, hi_ = 0u;
-      double b2q2 = b2 * q2;
-#pragma unroll
-      for (int s = 0; s < B; s++) {
-        const double t = c[s] - b1 * q1 - b2q2;
-        const double M = __hiloint2double((int)(((uint32_t)__double2hiint(t) & 0x7ff00000u) + 0x01D80000u), 0);
-        const double r = (t + M) - M;
-        const uint32_t rh = (uint32_t)__double2hiint(r) & 0x7fffffffu;
-        lo_ = min(lo_, rh); hi_ = max(hi_, rh);
-        b2q2 = b2 * q1;
-        q2 = q1; q1 = r;
-        x[s] = (float)r;  // exact
-      }
-      if (lo_ >= 0x38100000u && hi_ < 0x47F00000u) return;  // 2^-126 <= |y| < 2^128 throughout
-      q1 = s1; q2 = s2;
-    }
-#endif
-    double b2q2 = b2 * q2;
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      const float yf = (float)(c[s] - b1 * q1 - b2q2);
-      x[s] = yf;
-      b2q2 = b2 * q1;  // next sample's b2*y2, ready before it is needed
-#ifdef DOPS_WIDEN_CHAIN
-      q2 = q1; q1 = widen_or0_f32(yf);
-#else
-      q2 = q1; q1 = (double)js_or0f(yf);
-#endif
-    }
-  };
+  filterc_ff<B>(x, c, a0, a1, a2, o1, o2);
   if (T == 1) {
-    recur();
+    filterc_rec<B, false>(c, x, b1, b2, q1, q2);
   } else {
 #pragma unroll 1
     for (int turn = 0; turn < T; turn++) {
-      if (cx.tl == turn) recur();
+      if (cx.tl == turn) filterc_rec<B, false>(c, x, b1, b2, q1, q2);
       const double n1 = cx.from(q1, turn), n2 = cx.from(q2, turn);
       if (cx.tl == turn + 1) { q1 = n1; q2 = n2; }
     }

@@ -190,6 +190,23 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   if (!make_plan(p, pl)) return "";
   const int n = (int)p.code.size();
   const int NB = pl.n_buffers;
+  // Feed-forward split (DUSP_PIPED_SPLIT=0 turns it off): when the ONE sequential op of the circuit is a biquad with
+  // host-derived coefficients, its time-parallel half (a0 x + a1 x1 + a2 x2, Filter.js:40-42) leaves the S-warp for a
+  // second lane-per-voice warp (the "F-warp"), which hands the f64 bracket on through a small shared-memory ring, one
+  // 8-sample group at a time, with named-barrier handshakes.  The S-warp then issues nothing but the recurrence -- its
+  // in-order instruction stream is the critical path of the launch (profiles/r1_v10_piped_barrier_attribution.txt).
+  // The exchange buffers rotate over TWO steps instead of three (a P-warp reads a voice's stage-1 results of step
+  // k-2 into registers before it writes the stage-0 values of step k into the same row), which pays for the ring.
+  int fc = -1;
+  {
+    int n1 = 0;
+    for (int i = 0; i < n; i++) if (pl.stage[i] == 1) { n1++; fc = i; }
+    const char *se = getenv("DUSP_PIPED_SPLIT");
+    if (n1 != 1 || p.code[fc].op != OP_FILTERC || (se && atoi(se) == 0) || STEP != 256) fc = -1;
+  }
+  const bool split = fc >= 0;
+  const int NROT = split ? 2 : 3;
+  const int RING_D = 4;  // groups of B samples in flight between the F-warp and the S-warp
 
   // ---- the three stage bodies
   Gen g0(p, PB, 32), g1(p, PB, 1), g2(p, PB, 32);
@@ -197,7 +214,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   std::ostringstream s_decl, s_load, s_store;  // S-warp: crossing loads first, stores last (in-place buffer reuse)
   // stage-2 loads that depend on nothing this step computes are issued before stage 0 of the next step,
   // so their HBM / L2 latency hides behind that work
-  std::ostringstream pre_decl, pre_code;
+  std::ostringstream pre_decl, pre_code, prex_code;
   if (!getenv("DUSP_PIPED_NOPREFETCH"))
     for (int i = 0; i < n; i++)
       if (pl.stage[i] == 2 && Gen::can_prefetch(p, p.code[i], STEP) && p.code[i].out[0] >= 0) {
@@ -230,6 +247,10 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
           if (st == 1) {
             s_load << "        float xi" << i << "_" << k << "[B]; LDX(xi" << i << "_" << k << ", " << c.buf << ")\n";
             g.o << "      CP(s" << c.slot << ", xi" << i << "_" << k << ")  // value of instruction " << i << " (stage " << c.from << ")\n";
+          } else if (split) {  // read before stage 0 of this iteration reuses the row (two-step rotation)
+            pre_decl << "        float prex" << i << "_" << k << "[B];\n";
+            prex_code << "          LDX(prex" << i << "_" << k << ", " << c.buf << ")  // value of instruction " << i << " (stage " << c.from << ")\n";
+            g.o << "      CP(s" << c.slot << ", prex" << i << "_" << k << ")\n";
           } else {
             g.o << "      LDX(s" << c.slot << ", " << c.buf << ")  // value of instruction " << i << " (stage " << c.from << ")\n";
           }
@@ -243,7 +264,8 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   std::map<int, int> pj;  // word -> row of the shared-memory word table
   for (int w : p_words) { int j = (int)pj.size(); pj[w] = j; }
   const int NPW = (int)pj.size();
-  const size_t xb_bytes = (size_t)3 * NB * VC * STEP * sizeof(float);
+  const size_t xb_bytes = (size_t)NROT * NB * VC * STEP * sizeof(float);
+  const size_t ring_bytes = split ? (size_t)RING_D * PB * 32 * sizeof(double) : 0;
   // optional dynamic voice queue for the P-warps (measured slightly slower than the static split: off)
   const bool dyn = getenv("DUSP_PIPED_DYN") != nullptr;
   int s_unroll = PB == 4 ? 2 : 1;  // S-warp groups per loop body; DUSP_PIPED_SUNROLL overrides (experiments)
@@ -253,10 +275,11 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   const int srot_fixed = srot && srot_env[0] >= '0' && srot_env[0] <= '9' ? std::min(atoi(srot_env), NP) : -1;
   const bool slot = getenv("DUSP_PIPED_SLOT") != nullptr && NP == 4;  // S-warp role by per-SM ticket (experiments)
   const bool slot_hw = slot && atoi(getenv("DUSP_PIPED_SLOT")) == 2;   // ... matched against the hardware warp slot
-  const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double) + 16;  // (+16: qctr[3] queue heads, qctr[3] = S-warp ticket)
+  const size_t smem = xb_bytes + (size_t)NPW * VC * sizeof(double) + 16 + ring_bytes;  // (+16: qctr[3] queue heads, qctr[3] = S-warp ticket)
+  const int NWARPS = NP + (split ? 2 : 1);
   if (smem > 200 * 1024) return "";
   if (info) {
-    info->voices_per_cta = VC; info->threads = (NP + 1) * 32; info->smem_bytes = (int)smem; info->n_buffers = NB;
+    info->voices_per_cta = VC; info->threads = NWARPS * 32; info->smem_bytes = (int)smem; info->n_buffers = NB;
     info->n_ops = n; info->n_ops_sequential_stage = 0;
     for (int i = 0; i < n; i++) info->n_ops_sequential_stage += pl.stage[i] == 1;
   }
@@ -289,12 +312,15 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "      UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) dst[i_] = a[i_]; } }\\\n"
     << "  else if ((CH) < 2 && active) { mix_add<B>(kp.out + (long long)(CH) * kp.out_len + tl0, a, kp.n_samples - tl0);\\\n"
     << "      if (kp.prog_nch == 1) mix_add<B>(kp.out + kp.out_len + tl0, a, kp.n_samples - tl0); } }\n"
-    << "extern \"C\" __global__ void __launch_bounds__(" << (NP + 1) * 32 << ", " << min_blocks << ") dusp_piped(const __grid_constant__ FusedParams kp) {\n"
-    << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", ROW = STEP / 4, NP = " << NP << ", VW = VC / NP;\n"
+    << "#define BAR_SYNC(id) asm volatile(\"bar.sync %0, 64;\" ::\"r\"(id) : \"memory\")\n"
+    << "#define BAR_ARRIVE(id) asm volatile(\"bar.arrive %0, 64;\" ::\"r\"(id) : \"memory\")\n"
+    << "extern \"C\" __global__ void __launch_bounds__(" << NWARPS * 32 << ", " << min_blocks << ") dusp_piped(const __grid_constant__ FusedParams kp) {\n"
+    << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", ROW = STEP / 4, NP = " << NP << ", VW = VC / NP, NROT = " << NROT << ", RING_D = " << RING_D << ";\n"
     << "  extern __shared__ float4 smem4[];\n"
-    << "  float4 *const xb = smem4;                                                    // [3][NB][VC][ROW] float4, swizzled\n"
-    << "  double *const pw = reinterpret_cast<double *>(smem4 + 3 * NB * VC * ROW);  // [" << NPW << "][VC] words of the P-warps' units\n"
+    << "  float4 *const xb = smem4;                                                    // [NROT][NB][VC][ROW] float4, swizzled\n"
+    << "  double *const pw = reinterpret_cast<double *>(smem4 + NROT * NB * VC * ROW);  // [" << NPW << "][VC] words of the P-warps' units\n"
     << "  int *const qctr = reinterpret_cast<int *>(pw + " << NPW << " * VC);                 // [3] per-step voice queue heads\n"
+    << "  double *const cring = reinterpret_cast<double *>(qctr + 4); (void)cring;            // [RING_D][B][32] brackets on their way to the S-warp\n"
     << "  if (threadIdx.x < 3) qctr[threadIdx.x] = 0;\n"
     << "  const int lane = threadIdx.x & 31, wraw = threadIdx.x >> 5;\n"
     // Which warp of the CTA is the lane-per-voice warp.  Warps go to the SM's four schedulers by warp index, and the
@@ -334,7 +360,8 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "    _Pragma(\"unroll 1\")\n"
     << "    for (int it = 0; it < n_steps + 2; it++) {\n"
     << "      const bool do0 = it < n_steps, do2 = it >= 2;\n"
-    << "      const int rot0 = it % 3, rot2 = (it + 1) % 3;  // (it - 2) mod 3\n"
+    << (split ? "      const int rot0 = it & 1, rot2 = it & 1;  // two-step rotation: stage 2 of step it-2 frees the row stage 0 of step it fills\n"
+              : "      const int rot0 = it % 3, rot2 = (it + 1) % 3;  // (it - 2) mod 3\n")
     << "      float macc[2][B]; UNROLL for (int i_ = 0; i_ < B; i_++) { macc[0][i_] = 0.0f; macc[1][i_] = 0.0f; }\n"
     << (dyn ? "      if (threadIdx.x == 0) qctr[(it + 1) % 3] = 0;  // next step's queue (last used two steps ago)\n" : "")
     << "      _Pragma(\"unroll 1\")\n"
@@ -352,11 +379,12 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "        float *const out_row = kp.out + (long long)(kp.voice0 + v) * kp.out_nch * kp.out_len;\n"
     << "        (void)rings; (void)stale; (void)out_row; (void)active;\n";
   for (auto &kv : pj) s << "        double w" << kv.first << " = pw[" << kv.second << " * VC + vl];\n";
-  if (!pre_code.str().empty())
+  if (!pre_code.str().empty() || !prex_code.str().empty())
     s << pre_decl.str()
       << "        if (do2) {  // ---- stage 2, early loads\n"
       << "          const int cpos = (int)(((long long)(it - 2) * STEP + lane * B) & (DUSP_CHUNK - 1)); (void)cpos;\n"
-      << pre_code.str() << "        }\n";
+      << "          float4 *const xs = xb + ((size_t)rot2 * NB * VC + vl) * ROW + (lane ^ (vl & 7)); (void)xs;\n"
+      << pre_code.str() << prex_code.str() << "        }\n";
   s << "#define OUT_CHANNEL OUT_CHANNEL_P\n";
   const char *rot[3] = {"rot0", "", "rot2"};
   const char *cond[3] = {"do0", "", "do2"};
@@ -384,8 +412,86 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "        else mix_add<B>(kp.out + kp.out_len + t2, macc[1], kp.n_samples - t2);\n"
     << "      }\n"
     << "      __syncthreads();\n"
-    << "    }\n"
-    << "  } else {\n"
+    << "    }\n";
+  if (split) {
+    // ---- S-warp: the recurrence only; F-warp: the bracket.  Both one voice per lane, state in registers for the launch.
+    const DuspInstr &F = p.code[fc];
+    const int P = F.p;  // words: a0 a1 a2 b1 b2 (derived), x1 x2 y1 y2
+    int in_buf = -1, out_buf = -1;
+    for (auto &c : pl.cross) {
+      if (c.to >= 1 && c.from == 0 && c.slot == F.in[0] && c.used_in[1]) in_buf = c.buf;
+      if (c.def == fc) out_buf = c.buf;
+    }
+    const char *magic = getenv("DUSP_PIPED_MAGIC");
+    const bool use_magic = !magic || atoi(magic) != 0;
+    auto W = [&](int k) { return "kp.words[" + std::to_string(P + k) + " * nv + v]"; };
+    s << "  } else if (wib == NP) {\n"
+      << "    // ---------------- S-warp: one voice per lane, nothing but the recurrence  y = c - b1 y1 - b2 y2  (Filter.js:40-48)\n"
+      << "    const int vl = lane < VC ? lane : VC - 1;\n"
+      << "    const long long v = v0 + vl;\n"
+      << "    const double b1 = " << W(3) << ", b2 = " << W(4) << ";\n"
+      << "    double q1 = js_or0(" << W(7) << "), q2 = js_or0(" << W(8) << ");\n"
+      << "    float ylast = (float)" << W(7) << ";\n"
+      << "    unsigned G = 0;  // groups consumed so far: ring slot G % RING_D\n"
+      << "    _Pragma(\"unroll 1\")\n"
+      << "    for (int it = 0; it < n_steps + 2; it++) {\n"
+      << "      if (it >= 1 && it <= n_steps) {\n"
+      << "        const int rot1 = (it - 1) & 1;\n"
+      << "        _Pragma(\"unroll 1\")\n"
+      << "        for (int g = 0; g < STEP / B; g++, G++) {\n"
+      << "          const int slot = (int)(G % RING_D);\n"
+      << "          BAR_SYNC(1 + slot);  // the F-warp has filled the slot\n"
+      << "          double c[B];\n"
+      << "          UNROLL for (int i_ = 0; i_ < B; i_++) c[i_] = cring[(slot * B + i_) * 32 + lane];\n"
+      << "          float y[B];\n"
+      << "          filterc_rec<B, " << (use_magic ? "true" : "false") << ">(c, y, b1, b2, q1, q2);\n"
+      << "          BAR_ARRIVE(1 + RING_D + slot);  // slot free again\n"
+      << "          ylast = y[B - 1];\n";
+    if (out_buf >= 0)
+      s << "          if (lane < VC) { float4 *const xs = xb + ((size_t)rot1 * NB * VC + vl) * ROW + (g ^ (vl & 7)); STX(" << out_buf << ", y) }\n";
+    s << "        }\n"
+      << "      }\n"
+      << "      __syncthreads();\n"
+      << "    }\n"
+      << "    if (lane < VC) { " << W(7) << " = (double)ylast; " << W(8) << " = q2; }\n"
+      << "  } else {\n"
+      << "    // ---------------- F-warp: one voice per lane, the bracket  c = a0 x + a1 x1 + a2 x2  (Filter.js:40-42)\n"
+      << "    const int vl = lane < VC ? lane : VC - 1;\n"
+      << "    const long long v = v0 + vl;\n"
+      << "    const double a0 = " << W(0) << ", a1 = " << W(1) << ", a2 = " << W(2) << ";\n"
+      << "    double o1 = js_or0(" << W(5) << "), o2 = js_or0(" << W(6) << ");\n"
+      << "    double xlast = " << W(5) << ";\n";
+    if (in_buf < 0 && F.in[0] != REF_NONE && F.in[0] < 0)
+      s << "    const float xconst = (float)kp.words[" << (REF_CONST_BASE - F.in[0]) << " * nv + v];\n";
+    s << "    unsigned G = 0;\n"
+      << "    _Pragma(\"unroll 1\")\n"
+      << "    for (int it = 0; it < n_steps + 2; it++) {\n"
+      << "      if (it >= 1 && it <= n_steps) {\n"
+      << "        const int rot1 = (it - 1) & 1; (void)rot1;\n"
+      << "        _Pragma(\"unroll 1\")\n"
+      << "        for (int g = 0; g < STEP / B; g++, G++) {\n"
+      << "          const int slot = (int)(G % RING_D);\n"
+      << "          float x[B];\n";
+    if (in_buf >= 0)
+      s << "          { float4 *const xs = xb + ((size_t)rot1 * NB * VC + vl) * ROW + (g ^ (vl & 7)); LDX(x, " << in_buf << ") }\n";
+    else if (F.in[0] == REF_NONE)
+      s << "          FILL(x, 0.0f)\n";
+    else
+      s << "          FILL(x, xconst)\n";
+    s << "          double c[B];\n"
+      << "          xlast = (double)x[B - 1];\n"
+      << "          filterc_ff<B>(x, c, a0, a1, a2, o1, o2);\n"
+      << "          if (G >= RING_D) BAR_SYNC(1 + RING_D + slot);  // the S-warp is done with what the slot held\n"
+      << "          UNROLL for (int i_ = 0; i_ < B; i_++) cring[(slot * B + i_) * 32 + lane] = c[i_];\n"
+      << "          BAR_ARRIVE(1 + slot);\n"
+      << "        }\n"
+      << "      }\n"
+      << "      __syncthreads();\n"
+      << "    }\n"
+      << "    if (lane < VC) { " << W(5) << " = xlast; " << W(6) << " = o2; }\n"
+      << "  }\n";
+  } else {
+  s << "  } else {\n"
     << "    // ---------------- S-warp: one voice per lane, the reference's sequential order\n"
     << "    constexpr int T = 1;\n"
     << "    Cx<B, T> cx; cx.tl = 0; cx.lane = lane;\n"
@@ -420,6 +526,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     s << "    }\n";
   }
   s << "  }\n";
+  }  // !split
   if (!p_mut.empty()) {
     s << "  __syncthreads();\n";
     for (int w : p_mut)
