@@ -170,6 +170,7 @@ typedef struct OEvent { long chunk; int unit; char prop[24]; double value; } OEv
  * retriggering unit's index instead of a time. */
 typedef struct Oracle {
   struct Oracle *next; long next_chunk; /* graph edit: the circuit as it stands from chunk next_chunk on */
+  int next_fin_unit;                    /* >= 0: ... made by this unit finishing by itself inside a tick, whenever that happens */
   int ntriggers; OEvent *triggers;
   int nevents; OEvent *events;
   int nunits;
@@ -516,7 +517,14 @@ Oracle *oracle_load(const char *blob, char *err, int errlen) {
    * the host mirror's snapshot of the circuit after the edit; units are matched by label (adopt_state) */
   while (!bad && (*p == '\n' || *p == ' ' || *p == '\r')) p++;
   if (!bad && !strncmp(p, "EPOCH ", 6)) {
-    o->next_chunk = atol(p + 6);
+    char *rest = NULL;
+    o->next_chunk = strtol(p + 6, &rest, 10);
+    /* "EPOCH <chunk> FIN <unit>": the edit is made by unit <unit> of THIS section when it finishes by itself inside a
+     * tick (Shape/index.js:40-42 -> UnitOrPatch.js:77-84); the chunk number is the host's prediction and is not used
+     * here: the switch happens when this oracle's own Shape runs out (oracle_render) */
+    o->next_fin_unit = -1;
+    while (rest && *rest == ' ') rest++;
+    if (rest && !strncmp(rest, "FIN ", 4)) o->next_fin_unit = atoi(rest + 4);
     const char *e = strchr(p, '\n');
     o->next = e ? oracle_load(e + 1, o->err, sizeof o->err) : NULL;
     if (!o->next) { if (!o->err[0]) fail(o, "EPOCH record without a graph"); bad = 1; }
@@ -1474,7 +1482,7 @@ int oracle_render(Oracle *first, double duration, float **out, int max_ch, int *
   for (double t0 = 0; t0 < length; t0 += (double)csize) { /* :29 */
     /* circuit.tickUntil(t1): Circuit.js:19-47 -- one tick per 256 samples; a unit ticks when clock % tickInterval == 0 */
     while (o->clock < t0 + (double)csize) {
-      while (o->next && (long)(o->clock / CHUNK) >= o->next_chunk) { /* the event that edits the graph runs first */
+      while (o->next && o->next_fin_unit < 0 && (long)(o->clock / CHUNK) >= o->next_chunk) { /* the event that edits the graph runs first */
         adopt_state(o->next, o);
         o = o->next;
         if (!o->has_order) oracle_schedule(o, NULL);
@@ -1485,7 +1493,20 @@ int oracle_render(Oracle *first, double duration, float **out, int max_ch, int *
       for (int i = 0; i < o->norder; i++) {
         Unit *w = &o->units[o->order[i]];
         if (fmod(o->clock, (double)w->tick_interval) != 0) continue; /* Circuit.js:35 */
+        const int was_finished = w->finished;
         if (unit_tick(o, w, o->clock)) return chain_fail(first, o);
+        if (o->next && o->next_fin_unit == o->order[i] && w->finished && !was_finished) {
+          /* finish() from inside this tick ran onFinish, which edited the graph: Inlet.connect re-aliased chunks and
+           * Circuit.add re-sorted `this.units` (Circuit.js:67-107) while Circuit.tick's `for i` loop is running
+           * (Circuit.js:34-37).  The loop simply goes on with index i + 1 over the NEW list. */
+          Oracle *nx = o->next;
+          adopt_state(nx, o);
+          if (!nx->has_order) oracle_schedule(nx, NULL);
+          for (int e = 0; e < nx->nevents; e++)    /* state onFinish assigned, at this moment */
+            if (nx->events[e].chunk == (long)(nx->clock / CHUNK) && apply_event(nx, &nx->events[e])) return chain_fail(first, nx);
+          o = nx;
+          root = o->units[o->root_unit].out[o->root_outlet].chunk;
+        }
       }
       o->clock += CHUNK;
     }

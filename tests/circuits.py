@@ -303,6 +303,19 @@ def then_with_delay():  # a feedback delay patch downstream: CircleBuffer conten
     return P.SimpleDelay(src, 0.11, 0.5, 0.4)
 
 
+def shape_then_osc():  # `a then b` where a ends BY ITSELF: Shape.finish() from inside its tick (Shape/index.js:40-42) hands the
+    return d.unDusp("D0.3 then O440")  # Repeater its new source in the middle of Circuit.tick; units after the Shape see it in that tick
+
+
+def attack_then_decay():  # two self-finishing envelopes in a row (the second one's own finish only raises its flag)
+    return d.unDusp("(A0.1 then D0.4) * O220")
+
+
+def shape_then_number_into_delay():  # the edit sets a constant; a feedback delay downstream keeps ringing across it
+    src = d.unDusp("(D0.2 then 0.25) * Z330")
+    return P.SimpleDelay(src, 0.07, 0.4, 0.5)
+
+
 def event_assigns_inlet():  # an event that assigns an inlet constant and later connects a unit (Unit.js:59-67)
     osc = C.Osc(200)
     out = C.Multiply(osc, 0.5)
@@ -570,6 +583,9 @@ CASES = {
     "then_into_filter": (then_into_filter, 0.7, True),
     "then_with_delay": (then_with_delay, 0.9, True),
     "event_assigns_inlet": (event_assigns_inlet, 0.8, True),
+    "shape_then_osc": (shape_then_osc, 0.6, True),
+    "attack_then_decay": (attack_then_decay, 0.7, True),
+    "shape_then_number_into_delay": (shape_then_number_into_delay, 0.6, True),
     "sample_rate_redux": (sample_rate_redux, 0.4, True),
     "sample_rate_redux_static": (sample_rate_redux_static, 0.2, True),
     "fm_synth": (fm_synth, 0.6, False),

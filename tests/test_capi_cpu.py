@@ -115,10 +115,24 @@ def test_unsupported_configurations_fail_loudly(lib):
     o.schedule(1.0, lambda unit: setattr(unit, "waveform", "saw"))
     with pytest.raises(capi.UnsupportedCircuit, match="event"):
         circuit_blob(o)
-    # a Shape finishes from inside its own tick (Shape/index.js:40-42): an onFinish that edits the graph there is refused,
-    # one that only raises finish flags (Boop.js:15-17) is not
+    # a Shape finishes from inside its own tick (Shape/index.js:40-42).  With a constant duration the sample is known: the
+    # edit its onFinish makes becomes an epoch at the chunk that holds it, marked FIN (the oracle switches when ITS Shape
+    # runs out) ...
+    blob, _ = circuit_blob(d.unDusp("D0.1 then 0.5"))
+    assert "EPOCH 17 FIN 0" in blob  # 0.1 s = 4410 samples: chunk 17
+    # ... a signal-rate duration makes the moment data-dependent: refused; so is an onFinish that reaches a unit which
+    # has already ticked in that tick; one that only raises finish flags (Boop.js:15-17) needs nothing
+    env = C.Shape("decay", C.Sum(C.Multiply(C.Osc(1), 0.05), 0.2)).trigger()
+    rep = C.Repeater(env)
+    env.onFinish = lambda: setattr(rep, "IN", C.Osc(440))
     with pytest.raises(capi.UnsupportedCircuit, match="inside a tick"):
-        circuit_blob(d.unDusp("D0.1 then 0.5"))
+        circuit_blob(rep)
+    osc = C.Osc(200)
+    env = C.Shape("decay", 0.05).trigger()
+    out = C.Multiply(osc, env)  # the oscillator ticks before the envelope
+    env.onFinish = lambda: setattr(osc, "F", 300)
+    with pytest.raises(capi.UnsupportedCircuit, match="already ticked"):
+        circuit_blob(out)
     from dusp_b200 import patches as patches_
     assert "EPOCH" not in circuit_blob(patches_.Boop(440, 0.2))[0]
 

@@ -262,3 +262,31 @@ def test_fft_rejects_sizes_fft_js_rejects(oracle):
     for n in (1, 3, 12, 100):
         with pytest.raises(OracleError):
             oracle.fft(np.zeros(n), "real")
+
+
+def test_shape_finishing_by_itself_switches_inside_that_tick(oracle):
+    """`D0.3 then O440`: the envelope's running sum t += 1/duration passes 44100 at sample 13230 (the same sequential
+    f64 additions as Shape/index.js:31-32); finish() -> onFinish hands the Repeater the oscillator in the middle of
+    Circuit.tick; Circuit.add sorts the oscillator between the Shape and the Repeater, and the loop goes on with it
+    (Circuit.js:34-37): the whole chunk that holds the finish sample (51) already is the oscillator's first chunk."""
+    import math
+    import dusp_b200 as d
+    from dusp_b200.render import circuit_blob
+    blob, _ = circuit_blob(d.unDusp("D0.3 then O440"))
+    out = oracle.render(blob, 0.5)[0]
+    inc, t, n = np.float64(1.0) / np.float64(np.float32(0.3)), np.float64(0), 0
+    while True:
+        t += inc
+        if t > 44100:
+            break
+        n += 1
+    assert n == 13230 and "EPOCH %d FIN 0" % (n // 256) in blob
+    k = n // 256
+    tab = np.array([math.sin(2 * math.pi * i / 44101) for i in range(44101)], dtype=np.float32)
+    j = np.arange(len(out) - k * 256, dtype=np.int64)
+    assert np.array_equal(out[k * 256:], tab[(440 * (j + 1)) % 44100])
+    dec = np.array([1 - i / 44100 for i in range(44101)], dtype=np.float32)  # shapeTables.js "decay"
+    tt = np.cumsum(np.full(k * 256, inc))
+    fr = tt % 1
+    env = (dec[np.ceil(tt).astype(int)].astype(np.float64) * fr + dec[np.floor(tt).astype(int)].astype(np.float64) * (1 - fr))
+    assert np.array_equal(out[:k * 256], env.astype(np.float32))
