@@ -190,7 +190,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   if (!make_plan(p, pl)) return "";
   const int n = (int)p.code.size();
   const int NB = pl.n_buffers;
-  // Feed-forward split (DUSP_PIPED_SPLIT=0 turns it off): when the ONE sequential op of the circuit is a biquad with
+  // Feed-forward split (DUSP_PIPED_SPLIT=1 turns it on): when the ONE sequential op of the circuit is a biquad with
   // host-derived coefficients, its time-parallel half (a0 x + a1 x1 + a2 x2, Filter.js:40-42) leaves the S-warp for a
   // second lane-per-voice warp (the "F-warp"), which hands the f64 bracket on through a small shared-memory ring, one
   // 8-sample group at a time, with named-barrier handshakes.  The S-warp then issues nothing but the recurrence -- its
@@ -202,7 +202,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     int n1 = 0;
     for (int i = 0; i < n; i++) if (pl.stage[i] == 1) { n1++; fc = i; }
     const char *se = getenv("DUSP_PIPED_SPLIT");
-    if (n1 != 1 || p.code[fc].op != OP_FILTERC || (se && atoi(se) == 0) || STEP != 256) fc = -1;
+    if (n1 != 1 || p.code[fc].op != OP_FILTERC || !se || atoi(se) == 0 || STEP != 256) fc = -1;  // opt-in: measured slower
   }
   const bool split = fc >= 0;
   const int NROT = split ? 2 : 3;
