@@ -37,7 +37,7 @@ const char *OP_NAMES[OP_COUNT] = {
     "timer", "noise", "filter", "fixdelay", "comb", "allpass", "delay", "monodelay", "readback", "cbwrite",
     "cbread", "ldstale", "ststale", "out", "filterc", "panc", "gainc", "noise1", "cbwritec", "cbreadc", "add0",
     "retrig", "sretrig", "pokeif", "srredux", "hopper", "window", "fft", "ifft", "unhop", "rechunk", "specpass",
-    "specgate", "binshift", "augment", "specsum", "ldframe", "stframe", "outring"};
+    "specgate", "binshift", "augment", "specsum", "ldframe", "stframe", "outring", "pick"};
 
 struct Opnd {
   int kind = 0;  // 0 none (reads 0), 1 value, 2 const word, 3 immediate (frame ops: ring ids / sizes travel in `in`)
@@ -414,19 +414,29 @@ Program compile(const Graph &g) {
       b.prog.chunk_tiles = true;
     } else if (k == "Noise") {
       need_in(1);
-      if (b.nch[ui][0] != 1) throw Unsupported("multi-channel Noise shares one phase across channels chunk by chunk (Noise.js:17-27)");
-      IR &r = b.emit(OP_NOISE, ui, 0); r.in[0] = b.in_ref(ui, 0, 0);
-      // constant F >= sampleRate with phase 0: `phase += f` crosses the threshold on every sample (Noise.js:21-24)
-      if (r.in[0].kind == 2 && (float)b.prog.words[r.in[0].id].dflt >= (float)DUSP_SR && u.num("phase", 0) == 0) {
-        r.op = OP_NOISE1;
-        b.prog.locked.push_back({r.in[0].id, (double)DUSP_SR, INFINITY});
+      // A multi-channel Noise fills one channel after the other with ONE phase / held value / random stream
+      // (Noise.js:17-27: `for c in out: for t: phase += f[0][t] ...`): one instruction per channel on the same state
+      // words, in whole-chunk tiles so that channel c's 256 samples come before channel c + 1's.
+      const int noise_nch = b.nch[ui][0];
+      if (noise_nch > 1) b.prog.chunk_tiles = true;
+      int pw = -1;
+      for (int c = 0; c < noise_nch; c++) {
+        IR &r = b.emit(OP_NOISE, ui, c); r.in[0] = b.in_ref(ui, 0, 0);
+        // constant F >= sampleRate with phase 0: `phase += f` crosses the threshold on every sample (Noise.js:21-24)
+        if (r.in[0].kind == 2 && (float)b.prog.words[r.in[0].id].dflt >= (float)DUSP_SR && u.num("phase", 0) == 0) {
+          r.op = OP_NOISE1;
+          if (c == 0) b.prog.locked.push_back({r.in[0].id, (double)DUSP_SR, INFINITY});
+        }
+        if (c == 0) {
+          pw = b.word(un + ".phase", u.num("phase", 0), false);
+          b.word(un + ".y", u.num("y", 0), false);
+          b.word(un + ".draw", u.num("draw", 1), false);
+          b.word(un + ".seed_lo", u.num("seed_lo", 0), false);
+          b.word(un + ".seed_hi", u.num("seed_hi", 0), false);
+        }
+        b.ir.back().p = pw;
+        b.def(b.ir.back(), 0, ui, 0, c);
       }
-      r.p = b.word(un + ".phase", u.num("phase", 0), false);
-      b.word(un + ".y", u.num("y", 0), false);
-      b.word(un + ".draw", u.num("draw", 1), false);
-      b.word(un + ".seed_lo", u.num("seed_lo", 0), false);
-      b.word(un + ".seed_hi", u.num("seed_hi", 0), false);
-      b.def(r, 0, ui, 0, 0);
     } else if (k == "Filter") {
       need_in(2);
       std::string kind = u.str("kind", "LP");
@@ -522,12 +532,20 @@ Program compile(const Graph &g) {
     } else if (k == "PickChannel") {
       need_in(2);
       const GPort &cp = u.in[1];
-      if (cp.connected) throw Unsupported("PickChannel with a signal-rate channel index");
-      double idx = std::fmod((double)(float)cp.consts[0], (double)inn(0));  // PickChannel.js:19
-      IR &r = b.emit(OP_COPY, ui, 0);
-      if (idx == std::floor(idx) && idx >= 0 && idx < inn(0)) r.in[0] = b.in_ref(ui, 0, (int)idx);
-      else throw Unsupported("PickChannel index selects no channel (the reference throws a TypeError)");
-      b.def(r, 0, ui, 0, 0);
+      if (cp.connected) {  // the index is a signal: a per-sample select over the input's channels (PickChannel.js:19)
+        if (inn(0) > 4) throw Unsupported("PickChannel with a signal-rate index over more than 4 channels");
+        IR &r = b.emit(OP_PICK, ui, 0);
+        r.in[0] = b.in_ref(ui, 1, 0);
+        for (int c = 0; c < inn(0); c++) r.in[1 + c] = b.in_ref(ui, 0, c);
+        r.aux[0] = inn(0);
+        b.def(r, 0, ui, 0, 0);
+      } else {
+        double idx = std::fmod((double)(float)cp.consts[0], (double)inn(0));  // PickChannel.js:19
+        IR &r = b.emit(OP_COPY, ui, 0);
+        if (idx == std::floor(idx) && idx >= 0 && idx < inn(0)) r.in[0] = b.in_ref(ui, 0, (int)idx);
+        else throw Unsupported("PickChannel index selects no channel (the reference throws a TypeError)");
+        b.def(r, 0, ui, 0, 0);
+      }
     } else if (k == "VectorMagnitude") {
       need_in(1);
       if (inn(0) > 5) throw Unsupported("VectorMagnitude over more than 5 channels");
@@ -710,11 +728,34 @@ Program compile(const Graph &g) {
   // Two different units touching one ring see the same samples in the same
   // order as the reference (unit after unit per 256-chunk) iff their constant
   // time shifts are equal or at least one chunk apart on the ring.
-  std::set<int> not_hoistable;
+  // Graphs outside that condition -- taps of different units closer than a chunk, a shared ring shorter than two
+  // chunks, a signal-rate OFFSET on a shared ring (MultiTapDelay.js:28-44 with short or modulated taps) -- need the
+  // reference's own order, unit after unit over a WHOLE chunk (CircleBufferWriter.js:12-25, CircleBufferReader.js:
+  // 12-25): the program is rendered in whole-chunk tiles (interpreter, B * T = 256: every op covers the chunk before
+  // the next one starts, signal-rate taps and rings shorter than the tile run their samples in turn).
+  auto tap_sign = [&](const Tap &t) { return g.units[t.unit].kind == "CircleBufferWriter" ? 1 : -1; };
   for (auto &kv : taps) {
     auto &tv = kv.second;
+    const long long len = b.prog.rings[kv.first].length;
+    if (len < 2 * DUSP_CHUNK && tv.size() > 1) b.prog.chunk_tiles = true;
+    for (size_t i = 0; i < tv.size(); i++)
+      for (size_t j = i + 1; j < tv.size(); j++) {
+        if (tv[i].unit == tv[j].unit || (!tv[i].writer && !tv[j].writer)) continue;
+        if (tv[i].off.kind != 2 || tv[j].off.kind != 2) { b.prog.chunk_tiles = true; continue; }
+        const double sa = tap_sign(tv[i]) * (double)DUSP_SR * (double)(float)b.prog.words[tv[i].off.id].dflt;
+        const double sb = tap_sign(tv[j]) * (double)DUSP_SR * (double)(float)b.prog.words[tv[j].off.id].dflt;
+        double d = std::fabs(sa - sb);
+        if (!(d == d) || std::isinf(d)) continue;
+        d = std::fmod(d, (double)len);
+        d = std::min(d, (double)len - d);
+        if (d != 0 && d < DUSP_CHUNK) b.prog.chunk_tiles = true;
+      }
+  }
+  std::set<int> not_hoistable;
+  for (auto &kv : taps) {
+    if (b.prog.chunk_tiles) break;  // whole-chunk tiles keep the reference's order whatever the offsets are
+    auto &tv = kv.second;
     long long len = b.prog.rings[kv.first].length;
-    if (len < 2 * DUSP_CHUNK && tv.size() > 1) throw Unsupported("shared CircleBuffer shorter than two chunks");
     for (size_t i = 0; i < tv.size(); i++)
       for (size_t j = i + 1; j < tv.size(); j++) {
         if (tv[i].unit == tv[j].unit) continue;

@@ -542,18 +542,28 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
 // elements that belong to a neighbour's run travel by shuffle; only the window's first and last partial float4 use
 // scalar accesses (lane 0 / lane 31).  Requires a 16-byte aligned ring base and i0 + 32*B <= n (no wrap inside the
 // window): the callers check both (warp-uniform) and otherwise keep the element-wise path.
+// Two phases, so that a kernel can ISSUE the loads early and only touch the data where the unit ticks (the shuffles
+// are the first consumers: doing them at once exposes the whole memory latency, profiles/r2_c5_piped_roles.txt).
 template <int B>
-DOPS_DEV void ring_load_shifted(float (&x)[B], const float *buf, int i0, int tl) {
+DOPS_DEV void ring_load_issue(float (&f)[B + 3], const float *buf, int i0, int tl) {
   const int m = i0 & 3;
   const float4 *b4 = reinterpret_cast<const float4 *>(buf + (i0 - m)) + tl * (B / 4);
-  float f[B + 3];
 #pragma unroll
   for (int q = 0; q < B / 4; q++) { const float4 t = b4[q]; f[4 * q] = t.x; f[4 * q + 1] = t.y; f[4 * q + 2] = t.z; f[4 * q + 3] = t.w; }
 #pragma unroll
-  for (int j = 0; j < 3; j++) f[B + j] = __shfl_down_sync(0xffffffffu, f[j], 1);  // the next lane's first elements
+  for (int j = 0; j < 3; j++) f[B + j] = 0.0f;
   if (tl == 31 && m > 0) {
 #pragma unroll
     for (int j = 0; j < 3; j++) if (j < m) f[B + j] = buf[i0 - m + 32 * B + j];     // (inside the window: index <= i0 + 32 B - 1)
+  }
+}
+template <int B>
+DOPS_DEV void ring_load_finish(float (&x)[B], float (&f)[B + 3], int i0, int tl) {
+  const int m = i0 & 3;
+#pragma unroll
+  for (int j = 0; j < 3; j++) {  // the next lane's first elements (lane 31 keeps the window's tail it loaded itself)
+    const float nx = __shfl_down_sync(0xffffffffu, f[j], 1);
+    if (tl != 31) f[B + j] = nx;
   }
   switch (m) {
     case 0:
@@ -572,6 +582,12 @@ DOPS_DEV void ring_load_shifted(float (&x)[B], const float *buf, int i0, int tl)
 #pragma unroll
       for (int s = 0; s < B; s++) x[s] = f[s + 3];
   }
+}
+template <int B>
+DOPS_DEV void ring_load_shifted(float (&x)[B], const float *buf, int i0, int tl) {
+  float f[B + 3];
+  ring_load_issue<B>(f, buf, i0, tl);
+  ring_load_finish<B>(x, f, i0, tl);
 }
 template <int B>
 DOPS_DEV void ring_store_shifted(const float (&y)[B], float *buf, int i0, int tl) {
@@ -852,25 +868,35 @@ DOPS_DEV void c_cbtapc(const Cx<B, T> &cx, float (&x)[B], float *buf, int n, dou
 
 // A plain CircleBufferReader with a constant OFFSET, split in two so that a kernel can issue the ring
 // loads early (before unrelated work of the same step) and consume them where the unit ticks:
-// c_cbpeek loads what c_cbtapc<reader> would read, c_cbadv advances the ring index like it does.
+// c_cbpeek_issue starts the loads of what c_cbtapc<reader> would read (raw aligned runs on the shifted path),
+// c_cbpeek_finish turns them into the lane's B samples, c_cbadv advances the ring index like the unit does.
 // Only valid when no other tap stores into those positions during the step (compile.cc: aux[2]).
 template <int B, int T>
-DOPS_DEV void c_cbpeek(const Cx<B, T> &cx, float (&x)[B], const float *buf, int n, double idx) {
+DOPS_DEV bool cbpeek_shifted(const float *buf, int n, double idx) { return T == 32 && (int)idx + T * B <= n && ring_base_aligned(buf); }
+template <int B, int T>
+DOPS_DEV void c_cbpeek_issue(const Cx<B, T> &cx, float (&f)[B + 3], const float *buf, int n, double idx) {
+  if (idx < 0.0) return;
+  if (cbpeek_shifted<B, T>(buf, n, idx)) { ring_load_issue<B>(f, buf, (int)idx, cx.tl); return; }
+  int i = (int)idx + cx.tl * B;
+  if (i >= n) i %= n;
+  if (i + B <= n) {
+#pragma unroll
+    for (int s = 0; s < B; s++) f[s] = buf[i + s];
+  } else {
+#pragma unroll
+    for (int s = 0; s < B; s++) { f[s] = buf[i]; if (++i == n) i = 0; }
+  }
+}
+template <int B, int T>
+DOPS_DEV void c_cbpeek_finish(const Cx<B, T> &cx, float (&x)[B], float (&f)[B + 3], const float *buf, int n, double idx) {
   if (idx < 0.0) {
 #pragma unroll
     for (int s = 0; s < B; s++) x[s] = NAN;
     return;
   }
-  if (T == 32 && (int)idx + T * B <= n && ring_base_aligned(buf)) { ring_load_shifted<B>(x, buf, (int)idx, cx.tl); return; }
-  int i = (int)idx + cx.tl * B;
-  if (i >= n) i %= n;
-  if (i + B <= n) {
+  if (cbpeek_shifted<B, T>(buf, n, idx)) { ring_load_finish<B>(x, f, (int)idx, cx.tl); return; }
 #pragma unroll
-    for (int s = 0; s < B; s++) x[s] = buf[i + s];
-  } else {
-#pragma unroll
-    for (int s = 0; s < B; s++) { x[s] = buf[i]; if (++i == n) i = 0; }
-  }
+  for (int s = 0; s < B; s++) x[s] = f[s];
 }
 // pulls the ring lines the NEXT step's c_cbpeek will read from HBM into L2 (no register cost)
 template <int B, int T>

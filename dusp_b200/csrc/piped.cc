@@ -218,7 +218,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   if (!getenv("DUSP_PIPED_NOPREFETCH"))
     for (int i = 0; i < n; i++)
       if (pl.stage[i] == 2 && Gen::can_prefetch(p, p.code[i], STEP) && p.code[i].out[0] >= 0) {
-        pre_decl << "        float pre" << i << "[B];\n";
+        pre_decl << "        float pre" << i << "[B" << (p.code[i].op == OP_CBREADC ? " + 3" : "") << "];\n";
         g2.prefetch(i, p.code[i], pre_code);
       }
   for (int st = 0; st < 3; st++) {

@@ -1154,6 +1154,23 @@ __global__ void __launch_bounds__(128, B <= 8 ? 4 : 2) dusp_render_tile(const __
           L.st(o, I.out[0]);
           break;
         }
+        case OP_PICK: {  // PickChannel.js:19 with a signal-rate index
+          float ci[B], o[B];
+          L.ld(ci, I.in[0]);
+#pragma unroll
+          for (int s = 0; s < B; s++) o[s] = NAN;
+#pragma unroll
+          for (int c = 0; c < 4; c++) {
+            if (c < I.aux0) {
+              float x[B];
+              L.ld(x, I.in[1 + c]);
+#pragma unroll
+              for (int s = 0; s < B; s++) if (fmod((double)ci[s], (double)I.aux0) == (double)c) o[s] = x[s];
+            }
+          }
+          L.st(o, I.out[0]);
+          break;
+        }
         case OP_OSC: op_osc<B, T>(L, I); break;
         case OP_MCOSC: op_mcosc<B, T>(L, I); break;
         case OP_RAMP: op_ramp<B, T>(L, I); break;

@@ -92,6 +92,7 @@ enum DuspOp : int32_t {
   OP_LDFRAME,   // slot <- first 256 samples of a frame ring (a standard unit reading a 256-sample frame outlet)
   OP_STFRAME,   // frame ring <- slot (a frame inlet fed by a standard outlet)
   OP_OUTRING,   // renderChannelData.js:25-45 with outlet.chunkSize = aux2 > 256: out[aux0][t] = ring aux1 [t % aux2] || 0
+  OP_PICK,      // PickChannel.js:16-21 with a signal-rate index: out = in[c % n], in0 = c, in1..in4 = the channels, aux0 = n (<= 4)
   OP_COUNT
 };
 

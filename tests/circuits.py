@@ -316,6 +316,41 @@ def shape_then_number_into_delay():  # the edit sets a constant; a feedback dela
     return P.SimpleDelay(src, 0.07, 0.4, 0.5)
 
 
+def tight_taps():  # a11: MultiTapDelay taps closer than one chunk to the writer (and to each other): whole-chunk tiles
+    src = C.Multiply(C.Osc(220, "saw"), C.Shape("decay", 0.2).trigger())
+    mt = P.MultiTapDelay(1, 0.5, src)
+    a = mt.addTap(0.003)
+    b = mt.addFeedback(0.0041, 0.5, 0)
+    return C.Sum(a, b)
+
+
+def short_shared_ring():  # a11: a 353-sample CircleBuffer shared by a writer and a reader (shorter than two chunks)
+    mt = P.MultiTapDelay(1, 0.008, C.Osc(330))
+    return mt.addTap(0.004)
+
+
+def modulated_tap():  # a11: signal-rate OFFSET on a shared ring (CircleBufferReader.js:12-25, sample after sample)
+    mt = P.MultiTapDelay(1, 0.5, C.Osc(440))
+    return mt.addTap(quick.add(quick.multiply(C.Osc(2), 0.002), 0.01))
+
+
+def noise_two_channels():  # Noise.js:17-27: one phase / held value / stream, channel after channel
+    n = C.Noise(seed=99)
+    n.OUT.chunk = [0.0, 0.0]
+    return n
+
+
+def noise_two_channels_held():  # ... with F below the sample rate: the hold carries over from channel 0 to channel 1
+    n = C.Noise(2500.5, seed=7)
+    n.OUT.chunk = [0.0, 0.0]
+    return n
+
+
+def pick_channel_signal():  # PickChannel.js:19 with a signal-rate index
+    st = quick.concat(C.Osc(300), C.Osc(301.5, "saw"))
+    return C.PickChannel(st, quick.add(quick.multiply(C.Osc(5, "square"), 0.5), 0.5))  # 1 / 0
+
+
 def event_assigns_inlet():  # an event that assigns an inlet constant and later connects a unit (Unit.js:59-67)
     osc = C.Osc(200)
     out = C.Multiply(osc, 0.5)
@@ -583,6 +618,12 @@ CASES = {
     "then_into_filter": (then_into_filter, 0.7, True),
     "then_with_delay": (then_with_delay, 0.9, True),
     "event_assigns_inlet": (event_assigns_inlet, 0.8, True),
+    "tight_taps": (tight_taps, 0.5, True),
+    "short_shared_ring": (short_shared_ring, 0.3, True),
+    "modulated_tap": (modulated_tap, 0.6, True),
+    "noise_two_channels": (noise_two_channels, 0.2, True),
+    "noise_two_channels_held": (noise_two_channels_held, 0.3, True),
+    "pick_channel_signal": (pick_channel_signal, 0.5, True),
     "shape_then_osc": (shape_then_osc, 0.6, True),
     "attack_then_decay": (attack_then_decay, 0.7, True),
     "shape_then_number_into_delay": (shape_then_number_into_delay, 0.6, True),

@@ -87,12 +87,12 @@ def test_bad_blob_is_rejected(lib):
 
 
 def test_unsupported_configurations_fail_loudly(lib):
-    # CircleBuffer taps closer than one chunk: sub-block order would differ from the reference
+    # CircleBuffer taps closer than one chunk: sub-block order would differ from the reference, so the program is
+    # marked for whole-chunk tiles instead (rendered, not refused: tests/circuits.py tight_taps)
     mt = P.MultiTapDelay(1, 1.0, C.Osc(100))
     tap = mt.addFeedback(0.001, 0.5, 0)
     blob, _ = circuit_blob(C.Sum(mt.writer.IN.outlet, tap))
-    with pytest.raises(capi.UnsupportedCircuit, match="closer than one"):
-        capi.Program(blob)
+    assert capi.Program(blob).num_instructions >= 5
     # a unit feeding itself
     m = C.Multiply(1, 0.5)
     m.A = m
