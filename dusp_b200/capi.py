@@ -31,6 +31,7 @@ SYMBOLS = [
     "dusp_session_tile_info", "dusp_session_warning", "dusp_program_specialise", "dusp_session_poke",
     "dusp_session_adopt", "dusp_program_warmup_ticks",
     "dusp_mix_acc_create", "dusp_mix_acc_open", "dusp_mix_acc_close", "dusp_mix_acc_clear", "dusp_mix_push", "dusp_mix_wait",
+    "dusp_mix_push_static",
     "dusp_session_clock", "dusp_run_create", "dusp_run_destroy", "dusp_run_num_voices", "dusp_run_num_channels",
     "dusp_run_channels_rendered", "dusp_run_position", "dusp_run_session", "dusp_run_program", "dusp_run_num_epochs",
     "dusp_run_epoch_program", "dusp_run_set_params", "dusp_run_render",
@@ -93,6 +94,7 @@ def load():
     L.dusp_mix_acc_clear.argtypes = [c.c_void_p, c.c_size_t, c.c_size_t, c.c_void_p]
     L.dusp_mix_push.argtypes = [c.c_void_p, c.c_void_p, c.c_size_t, c.c_void_p, c.c_void_p, c.c_void_p]
     L.dusp_mix_wait.argtypes = [c.c_void_p, c.c_uint, c.c_void_p, c.c_void_p]
+    L.dusp_mix_push_static.argtypes = [c.c_int, c.c_void_p, c.c_void_p, c.c_size_t, c.c_void_p, c.c_void_p]
     L.dusp_session_clock.argtypes = [c.c_void_p]
     L.dusp_session_clock.restype = c.c_longlong
     L.dusp_run_create.argtypes = [c.POINTER(c.c_char_p), c.POINTER(c.c_size_t), c.POINTER(c.c_int), c.c_int, c.c_int, c.POINTER(c.c_void_p)]

@@ -15,6 +15,7 @@
 // Nothing waits for a peer except the root's consumer, so a late rank delays only the block it is late for.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <string.h>
 
 #include <string>
@@ -111,6 +112,49 @@ int dusp_mix_push(const float *local, float *remote, size_t n_floats, unsigned *
   mix_push_kernel<<<grid, block, 0, (cudaStream_t)cuda_stream>>>(local, remote, n_floats, remote_counter, ticket);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? DUSP_OK : dusp::fail_public(DUSP_ECUDA, std::string("dusp_mix_push: ") + cudaGetErrorString(e));
+}
+
+// ---- the push without any allocation on the caller's side (no counterpart in the reference; operators' request) ----
+// dusp_mix_push needs one zeroed u32 of device scratch (the CTA-arrival ticket) that the caller has to allocate.
+// Callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc) use this variant:
+// the ticket lives in a file-scope device array that every GPU loading the library holds until exit (256 bytes).
+// In HOST code `g_mix_static_scratch` is only a stand-in for the symbol, not a device address: its address is looked up
+// once per device, with that device current, by cudaGetSymbolAddress and that pointer is what the kernel gets.
+#define DUSP_MIX_STATIC_WORDS 64
+static __device__ __align__(256) unsigned g_mix_static_scratch[DUSP_MIX_STATIC_WORDS];  // word 0: arrival ticket; rest reserved
+static unsigned *g_mix_static_ptr[64];  // per device ordinal: device address of the array (0 = not looked up yet)
+
+int dusp_mix_push_static(int device, const float *local, float *remote, size_t n_floats, unsigned *remote_counter,
+                         void *cuda_stream) {
+  if (!local || !remote || !remote_counter) return dusp::fail_public(DUSP_EINVAL, "dusp_mix_push_static: null argument");
+  if (device < 0 || device >= 64) return dusp::fail_public(DUSP_EINVAL, "dusp_mix_push_static: device ordinal out of range (0..63)");
+  if (n_floats > (size_t)DUSP_MIX_PUSH_STATIC_MAX_FLOATS) {
+    char m[200];
+    snprintf(m, sizeof m, "dusp_mix_push_static: %zu floats exceed the maximum of %d per call (DUSP_MIX_PUSH_STATIC_MAX_FLOATS); "
+             "split the block or use dusp_mix_push with caller-owned scratch", n_floats, DUSP_MIX_PUSH_STATIC_MAX_FLOATS);
+    return dusp::fail_public(DUSP_EINVAL, m);
+  }
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return dusp::fail_public(DUSP_ECUDA, std::string("dusp_mix_push_static: cudaSetDevice: ") + cudaGetErrorString(e));
+  if (!g_mix_static_ptr[device]) {  // set-up, once per device, with that device current
+    unsigned *p = nullptr;
+    e = cudaGetSymbolAddress((void **)&p, g_mix_static_scratch);
+    if (e != cudaSuccess || !p)
+      return dusp::fail_public(DUSP_ECUDA, std::string("dusp_mix_push_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    g_mix_static_ptr[device] = p;
+  }
+  unsigned *ticket = g_mix_static_ptr[device];
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  // every call shares the array and it keeps the last call's contents: the ticket must start at zero
+  e = cudaMemsetAsync(ticket, 0, sizeof(unsigned), st);
+  if (e != cudaSuccess) return dusp::fail_public(DUSP_ECUDA, std::string("dusp_mix_push_static: clearing the ticket: ") + cudaGetErrorString(e));
+  const int block = 256;
+  int grid = (int)((n_floats + block * 4 - 1) / (block * 4));
+  if (grid < 1) grid = 1;
+  if (grid > 148) grid = 148;
+  mix_push_kernel<<<grid, block, 0, st>>>(local, remote, n_floats, remote_counter, ticket);
+  e = cudaGetLastError();
+  return e == cudaSuccess ? DUSP_OK : dusp::fail_public(DUSP_ECUDA, std::string("dusp_mix_push_static: ") + cudaGetErrorString(e));
 }
 
 int dusp_mix_wait(const unsigned *counter, unsigned target, unsigned *timed_out, void *cuda_stream) {

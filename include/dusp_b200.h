@@ -227,6 +227,21 @@ int dusp_mix_push(const float *local, float *remote, size_t n_floats, unsigned *
                   void *cuda_stream);
 int dusp_mix_wait(const unsigned *counter, unsigned target, unsigned *timed_out, void *cuda_stream);
 
+/* dusp_mix_push for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same adds and the same arrival-counter increment as dusp_mix_push, but the one word of scratch that call takes from
+ * the caller (`ticket`) lives in a static device array inside the library: 256 bytes that every GPU loading the
+ * library holds until exit.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine): it
+ * selects `device`, looks the array's device address up once per device (cudaGetSymbolAddress; do the first call per
+ * device outside a capture), clears the ticket on `cuda_stream` and launches the kernel there.  `local`, `remote` and
+ * `remote_counter` are the caller's, as in dusp_mix_push.  Limits: n_floats <= DUSP_MIX_PUSH_STATIC_MAX_FLOATS per call
+ * (more: DUSP_EINVAL with a message; split the block or use dusp_mix_push), device ordinals 0..63.  Every call on a
+ * device shares the one ticket: calls that overlap on the GPU (different streams, no ordering between them) RACE --
+ * keep them on one stream or order them with events. */
+#define DUSP_MIX_PUSH_STATIC_MAX_FLOATS (1 << 24)
+int dusp_mix_push_static(int device, const float *local, float *remote, size_t n_floats, unsigned *remote_counter,
+                         void *cuda_stream);
+
 /* The injected PRNG (replaces Math.random inside a tick: Noise.js:10,23, SporadicRetrigger.js:13): draw k of stream
  * `seed`, uniform in [0,1) with 32 bits of resolution:
  *   x = low32(k) + low32(seed); x ^= x >> 16; x *= 0x7feb352d; x ^= x >> 15; x *= 0x846ca68b; x ^= x >> 16;
