@@ -466,7 +466,7 @@ DOPS_DEV void filterc_ff(const float (&x)[B], double (&c)[B], double a0, double 
   for (int s = 0; s < B; s++) {
     const double xin = x[s];
     c[s] = a0 * xin + a1 * o1 + a2 * o2;
-    o2 = o1; o1 = (double)js_or0f(x[s]);
+    o2 = o1; o1 = fabsf(x[s]) > 0.0f ? xin : 0.0;  // (double)(x || 0) from the one conversion: NaN, +0, -0 -> +0
   }
 }
 // MAGIC: the f32 rounding of y (the store into the outlet's Float32Array, Filter.js:43) without leaving the FP64 pipe.
@@ -502,7 +502,8 @@ DOPS_DEV void filterc_rec(const double (&c)[B], float (&y)[B], double b1, double
     const float yf = (float)(c[s] - b1 * q1 - b2q2);
     y[s] = yf;
     b2q2 = b2 * q1;  // next sample's b2*y2, ready before it is needed
-    q2 = q1; q1 = (double)js_or0f(yf);
+    const double yd = (double)yf;
+    q2 = q1; q1 = fabsf(yf) > 0.0f ? yd : 0.0;  // (double)(y || 0): the select runs beside the conversion, not ahead of it
   }
 }
 

@@ -206,7 +206,8 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   }
   const bool split = fc >= 0;
   const int NROT = split ? 2 : 3;
-  const int RING_D = 4;  // groups of B samples in flight between the F-warp and the S-warp
+  int RING_D = 4;  // groups of B samples in flight between the F-warp and the S-warp (DUSP_PIPED_RING overrides)
+  if (const char *e = getenv("DUSP_PIPED_RING")) RING_D = std::max(2, std::min(16, atoi(e)));
 
   // ---- the three stage bodies
   Gen g0(p, PB, 32), g1(p, PB, 1), g2(p, PB, 32);
@@ -265,7 +266,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   for (int w : p_words) { int j = (int)pj.size(); pj[w] = j; }
   const int NPW = (int)pj.size();
   const size_t xb_bytes = (size_t)NROT * NB * VC * STEP * sizeof(float);
-  const size_t ring_bytes = split ? (size_t)RING_D * PB * 32 * sizeof(double) : 0;
+  const size_t ring_bytes = split ? (size_t)RING_D * PB * 32 * sizeof(double) + 16 : 0;  // + the two hand-over counters
   // optional dynamic voice queue for the P-warps (measured slightly slower than the static split: off)
   const bool dyn = getenv("DUSP_PIPED_DYN") != nullptr;
   int s_unroll = PB == 4 ? 2 : 1;  // S-warp groups per loop body; DUSP_PIPED_SUNROLL overrides (experiments)
@@ -312,15 +313,24 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "      UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) dst[i_] = a[i_]; } }\\\n"
     << "  else if ((CH) < 2 && active) { mix_add<B>(kp.out + (long long)(CH) * kp.out_len + tl0, a, kp.n_samples - tl0);\\\n"
     << "      if (kp.prog_nch == 1) mix_add<B>(kp.out + kp.out_len + tl0, a, kp.n_samples - tl0); } }\n"
-    << "#define BAR_SYNC(id) asm volatile(\"bar.sync %0, 64;\" ::\"r\"(id) : \"memory\")\n"
-    << "#define BAR_ARRIVE(id) asm volatile(\"bar.arrive %0, 64;\" ::\"r\"(id) : \"memory\")\n"
-    << "extern \"C\" __global__ void __launch_bounds__(" << NWARPS * 32 << ", " << min_blocks << ") dusp_piped(const __grid_constant__ FusedParams kp) {\n"
+    // F-warp -> S-warp hand-over of 8-sample groups of brackets: a ring in shared memory with two monotonic counters
+    // (flags[0] groups produced, flags[1] groups taken).  Taking group k: wait until it is produced, load it into
+    // registers, then publish the slot as free -- BEFORE the recurrence runs on it.  (Named barriers here cost the
+    // S-warp ~210 cycles per group, profiles/r2_c5_split_roles.txt.)
+    << "#define RING_TAKE(d, k) { const unsigned k_ = (k); while (flags[0] < k_ + 1u) {} __threadfence_block();\\\n"
+    << "    UNROLL for (int i_ = 0; i_ < B; i_++) d[i_] = cring[((int)(k_ % RING_D) * B + i_) * 32 + lane];\\\n"
+    << "    __syncwarp(); if (lane == 0) flags[1] = k_ + 1u; }\n"
+    << "extern \"C\" __global__ void " << (getenv("DUSP_PIPED_MAXNREG") ? "__maxnreg__(" + std::string(getenv("DUSP_PIPED_MAXNREG")) + ")"
+                                             : "__launch_bounds__(" + std::to_string(NWARPS * 32) + ", " + std::to_string(min_blocks) + ")")
+    << " dusp_piped(const __grid_constant__ FusedParams kp) {\n"
     << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", ROW = STEP / 4, NP = " << NP << ", VW = VC / NP, NROT = " << NROT << ", RING_D = " << RING_D << ";\n"
     << "  extern __shared__ float4 smem4[];\n"
     << "  float4 *const xb = smem4;                                                    // [NROT][NB][VC][ROW] float4, swizzled\n"
     << "  double *const pw = reinterpret_cast<double *>(smem4 + NROT * NB * VC * ROW);  // [" << NPW << "][VC] words of the P-warps' units\n"
     << "  int *const qctr = reinterpret_cast<int *>(pw + " << NPW << " * VC);                 // [3] per-step voice queue heads\n"
     << "  double *const cring = reinterpret_cast<double *>(qctr + 4); (void)cring;            // [RING_D][B][32] brackets on their way to the S-warp\n"
+    << "  volatile unsigned *const flags = reinterpret_cast<volatile unsigned *>(cring + RING_D * B * 32 * " << (split ? 1 : 0) << "); (void)flags;\n"
+    << (split ? "  if (threadIdx.x < 2) flags[threadIdx.x] = 0u;\n" : "")
     << "  if (threadIdx.x < 3) qctr[threadIdx.x] = 0;\n"
     << "  const int lane = threadIdx.x & 31, wraw = threadIdx.x >> 5;\n"
     // Which warp of the CTA is the lane-per-voice warp.  Warps go to the SM's four schedulers by warp index, and the
@@ -437,15 +447,14 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
       << "    for (int it = 0; it < n_steps + 2; it++) {\n"
       << "      if (it >= 1 && it <= n_steps) {\n"
       << "        const int rot1 = (it - 1) & 1;\n"
-      << "        _Pragma(\"unroll 1\")\n"
+      << "        double c[B], cn[B];\n"
+      << "        RING_TAKE(c, G)  // the step's first group\n"
+      << "        _Pragma(\"unroll 2\")\n"
       << "        for (int g = 0; g < STEP / B; g++, G++) {\n"
-      << "          const int slot = (int)(G % RING_D);\n"
-      << "          BAR_SYNC(1 + slot);  // the F-warp has filled the slot\n"
-      << "          double c[B];\n"
-      << "          UNROLL for (int i_ = 0; i_ < B; i_++) c[i_] = cring[(slot * B + i_) * 32 + lane];\n"
+      << "          if (g + 1 < STEP / B) RING_TAKE(cn, G + 1)  // the next group's brackets: in flight while this group's chain runs\n"
       << "          float y[B];\n"
       << "          filterc_rec<B, " << (use_magic ? "true" : "false") << ">(c, y, b1, b2, q1, q2);\n"
-      << "          BAR_ARRIVE(1 + RING_D + slot);  // slot free again\n"
+      << "          UNROLL for (int i_ = 0; i_ < B; i_++) c[i_] = cn[i_];\n"
       << "          ylast = y[B - 1];\n";
     if (out_buf >= 0)
       s << "          if (lane < VC) { float4 *const xs = xb + ((size_t)rot1 * NB * VC + vl) * ROW + (g ^ (vl & 7)); STX(" << out_buf << ", y) }\n";
@@ -481,9 +490,10 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     s << "          double c[B];\n"
       << "          xlast = (double)x[B - 1];\n"
       << "          filterc_ff<B>(x, c, a0, a1, a2, o1, o2);\n"
-      << "          if (G >= RING_D) BAR_SYNC(1 + RING_D + slot);  // the S-warp is done with what the slot held\n"
+      << "          if (G >= RING_D) { while (flags[1] < G - RING_D + 1) {} }  // the S-warp has taken what the slot held\n"
       << "          UNROLL for (int i_ = 0; i_ < B; i_++) cring[(slot * B + i_) * 32 + lane] = c[i_];\n"
-      << "          BAR_ARRIVE(1 + slot);\n"
+      << "          __syncwarp();\n"
+      << "          if (lane == 0) { __threadfence_block(); flags[0] = G + 1; }\n"
       << "        }\n"
       << "      }\n"
       << "      __syncthreads();\n"
