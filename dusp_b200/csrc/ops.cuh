@@ -6,7 +6,7 @@
 //   * the specialised render kernel (fused.cc generates one straight-line kernel per circuit
 //     shape that calls the cores with every slot and every state word held in registers; it is
 //     compiled at session creation with NVRTC for sm_100a), and
-//   * (being migrated) the interpreter in render_sm100.cu.
+//   * the interpreter in render_sm100.cu (its ops load operands / state words, call the cores, store the state back).
 // The file must stay self-contained: NVRTC compiles it without any CUDA header.
 //
 // Tile model (see render_sm100.cu): a warp renders V voices x T time-lanes, lane (vi, tl) owns
@@ -521,7 +521,11 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
   const double xlast = x[B - 1];
   filterc_ff<B>(x, c, a0, a1, a2, o1, o2);
   if (T == 1) {
+#ifdef DOPS_MAGIC
+    filterc_rec<B, true>(c, x, b1, b2, q1, q2);
+#else
     filterc_rec<B, false>(c, x, b1, b2, q1, q2);
+#endif
   } else {
 #pragma unroll 1
     for (int turn = 0; turn < T; turn++) {
@@ -641,8 +645,10 @@ DOPS_DEV bool ring_base_aligned(const float *) { return false; }
 #endif
 
 // FixedDelay.js:14-20 (KIND 0), CombFilter.js:11-17 (1), AllPass.js:8-15 (2).  x: input in, output out.
-template <int B, int T, int KIND>
-DOPS_DEV void c_fixdelay(const Cx<B, T> &cx, float (&x)[B], const float (&g)[B], float *buf, int n, double &tb) {
+// (KIND and the flags of the ring cores below are ordinary arguments: the specialised kernels pass literals, which fold
+// away after inlining; the interpreter passes what its instruction says.)
+template <int B, int T>
+DOPS_DEV void c_fixdelay(const Cx<B, T> &cx, float (&x)[B], const float (&g)[B], float *buf, int n, double &tb, const int KIND) {
   const double len = (double)n;
   auto step = [&](int p, int s) {
     const float d = buf[p];
@@ -674,8 +680,8 @@ DOPS_DEV void c_fixdelay(const Cx<B, T> &cx, float (&x)[B], const float (&g)[B],
 
 // Delay.js:20-41 (MONO false) / MonoDelay.js:19-30 (MONO true).  Write-ahead scatter-add: later
 // samples read what earlier ones added -> strictly sequential.  t0 = absolute index of x[0].
-template <int B, int T, bool MONO>
-DOPS_DEV void c_delay(const Cx<B, T> &cx, float (&x)[B], const float (&dl)[B], float *buf, int n, long long t0) {
+template <int B, int T>
+DOPS_DEV void c_delay(const Cx<B, T> &cx, float (&x)[B], const float (&dl)[B], float *buf, int n, long long t0, const bool MONO) {
   const double len = (double)n;
   serial0<B, T>(cx, [&] {
     // Fast path: the delay is one value over the lane's B samples, at least B + 1 samples long, and neither the
@@ -755,8 +761,9 @@ DOPS_DEV void c_readback(const Cx<B, T> &cx, float (&x)[B], const float (&dl)[B]
 
 // CircleBufferWriter.js:12-25 / CircleBufferReader.js:12-25 with a signal-rate OFFSET (admitted only
 // for a ring with a single tap unit): sequential.  off: offsets in; for a reader, output out.
-template <int B, int T, bool WRITER, bool WIPE, bool HAS_IN>
-DOPS_DEV void c_cbtap(const Cx<B, T> &cx, float (&off)[B], const float (&x)[B], float *buf, int n, double tu, long long t0) {
+template <int B, int T>
+DOPS_DEV void c_cbtap(const Cx<B, T> &cx, float (&off)[B], const float (&x)[B], float *buf, int n, double tu, long long t0,
+                      const bool WRITER, const bool WIPE, const bool HAS_IN) {
   const double len = (double)n;
   serial0<B, T>(cx, [&] {
 #pragma unroll
@@ -783,8 +790,9 @@ DOPS_DEV void c_cbtap(const Cx<B, T> &cx, float (&off)[B], const float (&x)[B], 
 // Same units with a constant OFFSET: the ring index advances by one per sample; its start value is
 // derived on the host (CircleBuffer.js:17-20 applied to the first access).  idx < 0: never valid.
 // x: writer input in / reader output out.
-template <int B, int T, bool WRITER, bool WIPE, bool HAS_IN>
-DOPS_DEV void c_cbtapc(const Cx<B, T> &cx, float (&x)[B], float *buf, int n, double &idx) {
+template <int B, int T>
+DOPS_DEV void c_cbtapc(const Cx<B, T> &cx, float (&x)[B], float *buf, int n, double &idx, const bool WRITER, const bool WIPE,
+                       const bool HAS_IN) {
   auto run = [&](int i) {
     if (i + B <= n) {  // no wrap inside the run: plain pointer walk
       float *q = buf + i;

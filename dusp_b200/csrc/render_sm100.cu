@@ -34,64 +34,13 @@
 
 namespace {
 
-constexpr double SRD = 44100.0;
+using dops::SRD;
 
 // ---------------------------------------------------------------- helpers
-__device__ __forceinline__ double js_or0(double x) { return fabs(x) > 0.0 ? x : 0.0; }  // `x || 0`: NaN, +0, -0 -> +0 (one compare: |x| > 0 is false for all three)
-__device__ __forceinline__ float js_or0f(float x) { return fabsf(x) > 0.0f ? x : 0.0f; }
-// DUSP_OUT_MIX accumulation: 16-byte vector reductions where the run is whole and aligned (same as ops.cuh mix_add)
-template <int B>
-__device__ __forceinline__ void mix_add(float *dst, const float (&y)[B], long long room) {
-  if (room >= B && (reinterpret_cast<unsigned long long>(dst) & 15ull) == 0) {
-#pragma unroll
-    for (int q = 0; q < B / 4; q++)
-      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * q), "f"(y[4 * q]), "f"(y[4 * q + 1]),
-                   "f"(y[4 * q + 2]), "f"(y[4 * q + 3]) : "memory");
-  } else {
-#pragma unroll
-    for (int s = 0; s < B; s++) if (s < room) atomicAdd(dst + s, y[s]);
-  }
-}
-
-// JS `x % 44100` (= C fmod) with exact fast paths for the common range.
-__device__ __forceinline__ double fmod_sr(double x) {
-  if (x >= 0.0) {
-    if (x < SRD) return x;
-    if (x < 2 * SRD) return x - SRD;  // exact (Sterbenz)
-  } else if (x > -SRD) {
-    return x;
-  } else if (x > -2 * SRD) {
-    return x + SRD;
-  }
-  return fmod(x, SRD);
-}
-// x mod 44100 in [0, 44100) for |x| < 2^40: exact quotient correction with one fma
-__device__ __forceinline__ double posmod_sr(double x) {
-  if (!(fabs(x) < 1.0e12)) { x = fmod(x, SRD); return x < 0.0 ? x + SRD : x; }
-  const double q = floor(x / SRD);
-  double r = fma(-q, SRD, x);
-  if (r < 0.0) r += SRD;
-  if (r >= SRD) r -= SRD;
-  return r;
-}
-
-// typed-array read `table[i]` with a double index: out of range / NaN -> undefined -> NaN
-__device__ __forceinline__ double tab_read(const float *__restrict__ tab, double idx) {
-  return (idx >= 0.0 && idx <= 44100.0) ? (double)__ldg(tab + (int)idx) : (double)NAN;
-}
-__device__ __forceinline__ bool ring_valid(double idx, double len) { return idx == floor(idx) && idx >= 0.0 && idx < len; }
-__device__ __forceinline__ double ring_read(const float *r, double len, double idx) {
-  return ring_valid(idx, len) ? (double)r[(long long)idx] : (double)NAN;
-}
-// CircleBuffer.js:17-20 index normalisation
-__device__ __forceinline__ double cb_index(double t, double len) {
-  t = floor(fmod(t, len));
-  if (t < 0.0) t += len;  // `while(t < 0)`: fmod result is > -len, one step suffices
-  return t;
-}
-
-// injected PRNG (replaces Math.random inside a tick): dops::tick_rand / noise_bipolar in ops.cuh
-__device__ __forceinline__ double shfl_d(double x, int src) { return __shfl_sync(0xffffffffu, x, src); }
+// (`x || 0`, the mixdown reductions, 10^(dB/20) and every unit's arithmetic come from ops.cuh)
+using dops::js_or0f;
+using dops::mix_add;
+using dops::dB;
 
 template <int B, int T>
 struct Lane {
@@ -177,104 +126,33 @@ __device__ __forceinline__ void map2(const Lane<B, T> &L, const DuspDevInstr &I,
   L.st(a, I.out[0]);
 }
 
-__device__ __forceinline__ double dB(double db) { return pow(10.0, db / 20.0); }  // Gain.js:26-28
 
 // ------------------------------------------------------------- stateful ops
-// Osc.js:35-47.  negfix=false is MultiChannelOsc.js:21-38 (its truncated-modulo phase has no canonical
-// range, so it only runs in sequential order).
-template <int B, int T>
-__device__ __forceinline__ void osc_body(const Lane<B, T> &L, const DuspDevInstr &I, float (&f)[B], double &ph, bool negfix) {
-  const float *tab = L.tables + (size_t)I.aux0 * DUSP_TABLE_LEN;
-  if (negfix) {
-    // straight-line form while phase + f stays inside (-SR, 2 SR) (same as ops.cuh osc_run): `% SR` and the negative fix
-    // are one exact add or subtract chosen by two compares; validity is checked once per run, else the literal loop below
-    double p = ph, q[B];
-    bool ok = true;
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      const double x = p + (double)f[s];
-      ok = ok && x > -SRD && x < 2.0 * SRD;
-      p = x < 0.0 ? x + SRD : (x >= SRD ? x - SRD : x);
-      q[s] = p;
-    }
-    if (ok) {
-#pragma unroll
-      for (int s = 0; s < B; s++) ok = ok && q[s] < SRD;
-    }
-    if (ok) {
-#pragma unroll
-      for (int s = 0; s < B; s++) {
-        const int i = __double2int_rz(q[s]);
-        const double fr = q[s] - (double)i;
-        const double a = (double)__ldg(tab + i), b = (double)__ldg(tab + i + (fr != 0.0));
-        f[s] = (float)(a * (1.0 - fr) + b * fr);
-      }
-      ph = p;
-      return;
-    }
-  }
-#pragma unroll
-  for (int s = 0; s < B; s++) {
-    ph += (double)f[s];
-    ph = fmod_sr(ph);
-    if (negfix && ph < 0.0) ph += SRD;
-    if (ph >= 0.0 && ph < SRD) {  // the only reachable case for Osc unless f is NaN / Infinity
-      const int i = __double2int_rz(ph);
-      const double fr = ph - (double)i;  // phase % 1
-      const double a = (double)__ldg(tab + i), b = (double)__ldg(tab + i + (fr != 0.0));  // floor / ceil entries
-      f[s] = (float)(a * (1.0 - fr) + b * fr);
-    } else {
-      const double fl = floor(ph), ce = ceil(ph), fr = ph - trunc(ph);
-      f[s] = (float)(tab_read(tab, fl) * (1.0 - fr) + tab_read(tab, ce) * fr);
-    }
-  }
-}
+// One copy of the arithmetic: every op below loads its operands and state words, calls the unit's core in ops.cuh (the
+// same code the specialised kernels are generated from) and stores the state back.  A core returns with the END-of-tile
+// state on every lane of the voice; the last time-lane writes it.
+#define CX dops::Cx<B, T> cx; cx.tl = L.tl; cx.lane = L.lane;
+#define TABLE(id) (L.tables + (size_t)(id) * DUSP_TABLE_LEN)
 
 template <int B, int T>
-__device__ __forceinline__ void op_osc(const Lane<B, T> &L, const DuspDevInstr &I) {  // Osc.js:35-47: the core in ops.cuh
+__device__ __forceinline__ void op_osc(const Lane<B, T> &L, const DuspDevInstr &I, bool negfix) {  // Osc.js:35-47 / MultiChannelOsc.js:21-38
   float f[B];
   L.ld(f, I.in[0]);
   double ph = L.w(I.p);
-  dops::Cx<B, T> cx; cx.tl = L.tl; cx.lane = L.lane;
-  dops::c_osc<B, T>(cx, f, ph, L.tables + (size_t)I.aux0 * DUSP_TABLE_LEN);  // every lane returns with the end-of-tile phase
+  CX
+  if (negfix) dops::c_osc<B, T>(cx, f, ph, TABLE(I.aux0));
+  else dops::c_mcosc<B, T>(cx, f, ph, TABLE(I.aux0));
   L.sync();
   if (L.tl == T - 1) L.w(I.p) = ph;
   L.st(f, I.out[0]);
 }
 
 template <int B, int T>
-__device__ __forceinline__ void op_mcosc(const Lane<B, T> &L, const DuspDevInstr &I) {
-  float f[B];
-  L.ld(f, I.in[0]);
-  L.serial([&] { double ph = L.w(I.p); osc_body<B, T>(L, I, f, ph, false); L.w(I.p) = ph; });
-  L.st(f, I.out[0]);
-}
-
-template <int B, int T>
 __device__ __forceinline__ void op_ramp(const Lane<B, T> &L, const DuspDevInstr &I) {  // Ramp.js:25-40
   double t = L.w(I.p), playing = L.w(I.p + 1);
-  const double dur = L.w(I.p + 2), y0 = L.w(I.p + 3), y1 = L.w(I.p + 4);
-  if (T > 1 && L.tl > 0 && playing != 0.0) {
-    // the tl*B steps before this lane's first sample: one literal step, then the closed form of
-    // "count up by one until t passes duration" (after the first step 0 <= t <= duration holds)
-    t += 1.0;
-    if (t > dur) { playing = 0.0; t = dur; }
-    if (t < 0.0) { playing = 0.0; t = 0.0; }
-    if (playing != 0.0) {
-      const double rem = (double)(L.tl * B - 1);
-      if (t + rem > dur) { t = dur; playing = 0.0; } else t += rem;
-    }
-  }
   float o[B];
-#pragma unroll
-  for (int s = 0; s < B; s++) {
-    if (playing != 0.0) {
-      t += 1.0;
-      if (t > dur) { playing = 0.0; t = dur; }
-      if (t < 0.0) { playing = 0.0; t = 0.0; }
-    }
-    o[s] = (float)(y0 + (t / dur) * (y1 - y0));
-  }
+  CX
+  dops::c_ramp<B, T>(cx, o, t, playing, L.w(I.p + 2), L.w(I.p + 3), L.w(I.p + 4));
   L.sync();
   if (L.tl == T - 1) { L.w(I.p) = t; L.w(I.p + 1) = playing; }
   L.st(o, I.out[0]);
@@ -284,36 +162,14 @@ template <int B, int T>
 __device__ __forceinline__ void op_shape(const Lane<B, T> &L, const DuspDevInstr &I) {  // Shape/index.js:28-59
   float d[B], mn[B], mx[B];
   L.ld(d, I.in[0]); L.ld(mn, I.in[1]); L.ld(mx, I.in[2]);
-  const float *tab = L.tables + (size_t)I.aux0 * DUSP_TABLE_LEN;
-  const double playing = L.w(I.p + 1);
+  const float *tab = TABLE(I.aux0);
+  double t = L.w(I.p);
   const double le = (I.aux1 & 1) ? (double)__ldg(tab) : L.w(I.p + 2);
   const double re = (I.aux1 & 2) ? (double)__ldg(tab + DUSP_SR) : L.w(I.p + 3);
-  // only the f64 running sum t += 1/duration is order-dependent: the divisions before it and the table
-  // interpolation after it run on every time-lane at once
-  double tt[B];
-#pragma unroll
-  for (int s = 0; s < B; s++) tt[s] = 1.0 / (double)d[s];
-  L.serial([&] {
-    double t = L.w(I.p);
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      if (playing != 0.0) t += tt[s];
-      tt[s] = t;
-    }
-    L.w(I.p) = t;
-  });
-#pragma unroll
-  for (int s = 0; s < B; s++) {
-    const double ts = tt[s], lo = mn[s], hi = mx[s];
-    double y;
-    if (ts <= 0.0) y = le * (hi - lo) + lo;
-    else if (ts > SRD) y = re * (hi - lo) + lo;
-    else {
-      const double fr = ts - trunc(ts);  // t % 1
-      y = lo + (hi - lo) * (tab_read(tab, ceil(ts)) * fr + tab_read(tab, floor(ts)) * (1.0 - fr));
-    }
-    d[s] = (float)y;
-  }
+  CX
+  dops::c_shape<B, T>(cx, d, mn, mx, t, L.w(I.p + 1), le, re, tab);
+  L.sync();
+  if (L.tl == T - 1) L.w(I.p) = t;
   L.st(d, I.out[0]);
 }
 
@@ -321,41 +177,22 @@ template <int B, int T>
 __device__ __forceinline__ void op_ahd(const Lane<B, T> &L, const DuspDevInstr &I) {  // AHD.js:35-76
   float a[B], h[B], d[B];
   L.ld(a, I.in[0]); L.ld(h, I.in[1]); L.ld(d, I.in[2]);
-  L.serial([&] {
-    double t = L.w(I.p);
-    int state = (int)L.w(I.p + 1);
-    bool playing = L.w(I.p + 2) != 0.0;
-    const double sp = 1.0 / SRD;
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      float y = 0.0f;
-      if (state == 1) {
-        y = (float)t;
-        if (playing) { t += sp / (double)a[s]; if (t >= 1.0) { state++; t -= 1.0; } }
-      } else if (state == 2) {
-        y = 1.0f;
-        if (playing) { t += sp / (double)h[s]; if (t >= 1.0) { state++; t -= 1.0; } }
-      } else if (state == 3) {
-        y = (float)(1.0 - t);
-        if (playing) { t += sp / (double)d[s]; if (t >= 1.0) { state = 0; playing = false; } }
-      }
-      a[s] = y;
-    }
-    L.w(I.p) = t; L.w(I.p + 1) = (double)state; L.w(I.p + 2) = playing ? 1.0 : 0.0;
-  });
+  double t = L.w(I.p), state = L.w(I.p + 1), playing = L.w(I.p + 2);
+  CX
+  dops::c_ahd<B, T>(cx, a, h, d, t, state, playing);
+  L.sync();
+  if (L.tl == T - 1) { L.w(I.p) = t; L.w(I.p + 1) = state; L.w(I.p + 2) = playing; }
   L.st(a, I.out[0]);
 }
 
 template <int B, int T>
 __device__ __forceinline__ void op_timer(const Lane<B, T> &L, const DuspDevInstr &I) {  // Timer.js:37-42
   float o[B];
-  L.serial([&] {
-    double t = L.w(I.p);
-    const double sp = 1.0 / SRD;
-#pragma unroll
-    for (int s = 0; s < B; s++) { t += sp; o[s] = (float)t; }
-    L.w(I.p) = t;
-  });
+  double t = L.w(I.p);
+  CX
+  dops::c_timer<B, T>(cx, o, t);
+  L.sync();
+  if (L.tl == T - 1) L.w(I.p) = t;
   L.st(o, I.out[0]);
 }
 
@@ -363,38 +200,28 @@ template <int B, int T>
 __device__ __forceinline__ void op_srredux(const Lane<B, T> &L, const DuspDevInstr &I) {  // SampleRateRedux.js:20-37
   float x[B], m[B];
   L.ld(x, I.in[0]); L.ld(m, I.in[1]);
-  L.serial([&] {
-    double ts = L.w(I.p), val = L.w(I.p + 1);
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      ts += 1.0;
-      if (ts > (double)m[s]) { val = (double)x[s]; ts = 0.0; }
-      x[s] = (float)val;
-    }
-    L.w(I.p) = ts; L.w(I.p + 1) = val;
-  });
+  double ts = L.w(I.p), val = L.w(I.p + 1);
+  CX
+  dops::c_srredux<B, T>(cx, x, m, ts, val);
+  L.sync();
+  if (L.tl == T - 1) { L.w(I.p) = ts; L.w(I.p + 1) = val; }
   L.st(x, I.out[0]);
 }
 
 template <int B, int T>
-__device__ __forceinline__ void op_noise(const Lane<B, T> &L, const DuspDevInstr &I) {  // Noise.js:16-28
-  float f[B];
-  L.ld(f, I.in[0]);
+__device__ __forceinline__ void op_noise(const Lane<B, T> &L, const DuspDevInstr &I, bool every_sample) {  // Noise.js:16-28
+  double ph = L.w(I.p), y = L.w(I.p + 1), draw = L.w(I.p + 2);
   const uint64_t seed = (uint64_t)L.w(I.p + 3) | ((uint64_t)L.w(I.p + 4) << 32);
-  L.serial([&] {
-    double ph = L.w(I.p), y = L.w(I.p + 1), draw = L.w(I.p + 2);
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      ph += (double)f[s];
-      if (ph >= SRD) {
-        ph = 0.0;
-        y = dops::noise_bipolar(dops::tick_hash((uint32_t)(uint64_t)draw + (uint32_t)seed) ^ (uint32_t)(seed >> 32));
-        draw += 1.0;
-      }
-      f[s] = (float)y;
-    }
-    L.w(I.p) = ph; L.w(I.p + 1) = y; L.w(I.p + 2) = draw;
-  });
+  float f[B];
+  CX
+  if (every_sample) {  // constant F >= sampleRate: a draw per sample, the counter-based stream makes the lanes independent
+    dops::c_noise1<B, T>(cx, f, y, draw, seed);
+  } else {
+    L.ld(f, I.in[0]);
+    dops::c_noise<B, T>(cx, f, ph, y, draw, seed);
+  }
+  L.sync();
+  if (L.tl == T - 1) { L.w(I.p) = ph; L.w(I.p + 1) = y; L.w(I.p + 2) = draw; }
   L.st(f, I.out[0]);
 }
 
@@ -438,144 +265,48 @@ __device__ __forceinline__ void op_pokeif(const Lane<B, T> &L, const DuspDevInst
 }
 
 template <int B, int T>
-__device__ __forceinline__ void op_noise1(const Lane<B, T> &L, const DuspDevInstr &I) {  // Noise.js:16-28 with F >= sampleRate: the core in ops.cuh
-  double y = L.w(I.p + 1), draw = L.w(I.p + 2);
-  const uint64_t seed = (uint64_t)L.w(I.p + 3) | ((uint64_t)L.w(I.p + 4) << 32);
-  dops::Cx<B, T> cx; cx.tl = L.tl; cx.lane = L.lane;
-  float o[B];
-  dops::c_noise1<B, T>(cx, o, y, draw, seed);  // counter-based stream: the draws of the time-lanes are independent
-  L.sync();
-  if (L.tl == T - 1) { L.w(I.p + 1) = y; L.w(I.p + 2) = draw; }  // phase stays 0
-  L.st(o, I.out[0]);
-}
-
-// Filter.js:66-84
-__device__ __forceinline__ void filter_coeffs(int hp, double f, double &a0, double &a1, double &a2, double &b1, double &b2) {
-  const double PI = 3.141592653589793;
-  if (!hp) {
-    double lamda = 1.0 / tan(PI * f / SRD), l2 = lamda * lamda;
-    a0 = 1.0 / (1.0 + 2.0 * lamda + l2); a1 = 2.0 * a0; a2 = a0;
-    b1 = 2.0 * a0 * (1.0 - l2); b2 = a0 * (1.0 - 2.0 * lamda + l2);
-  } else {
-    double lamda = tan(PI * f / SRD), l2 = lamda * lamda;
-    a0 = 1.0 / (1.0 + 2.0 * lamda + l2); a1 = 0.0; a2 = -a0;
-    b1 = 2.0 * a0 * (l2 - 1.0); b2 = a0 * (1.0 - 2.0 * lamda + l2);
-  }
-}
-
-template <int B, int T>
-__device__ __forceinline__ void op_filter(const Lane<B, T> &L, const DuspDevInstr &I) {  // Filter.js:27-51
+__device__ __forceinline__ void op_filter(const Lane<B, T> &L, const DuspDevInstr &I) {  // Filter.js:27-51, signal-rate F
   float x[B], f[B];
   L.ld(x, I.in[0]); L.ld(f, I.in[1]);
   const int p = I.p;
-  L.serial([&] {
-    double a0 = L.w(p), a1 = L.w(p + 1), a2 = L.w(p + 2), b1 = L.w(p + 3), b2 = L.w(p + 4);
-    double lastf = L.w(p + 5);
-    bool lastdef = L.w(p + 6) != 0.0;
-    double x1 = L.w(p + 7), x2 = L.w(p + 8), y1 = L.w(p + 9), y2 = L.w(p + 10);
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      const double ft = f[s];
-      if (!lastdef || ft != lastf) { lastdef = true; lastf = ft; filter_coeffs(I.aux0, ft, a0, a1, a2, b1, b2); }
-      const double xin = x[s];
-      const double y = a0 * xin + a1 * js_or0(x1) + a2 * js_or0(x2) - b1 * js_or0(y1) - b2 * js_or0(y2);
-      const float yf = (float)y;
-      x[s] = yf;
-      y2 = js_or0(y1); y1 = (double)yf; x2 = js_or0(x1); x1 = xin;
-    }
-    L.w(p) = a0; L.w(p + 1) = a1; L.w(p + 2) = a2; L.w(p + 3) = b1; L.w(p + 4) = b2;
-    L.w(p + 5) = lastf; L.w(p + 6) = lastdef ? 1.0 : 0.0;
-    L.w(p + 7) = x1; L.w(p + 8) = x2; L.w(p + 9) = y1; L.w(p + 10) = y2;
-  });
+  dops::FilterState S = {L.w(p), L.w(p + 1), L.w(p + 2), L.w(p + 3), L.w(p + 4), L.w(p + 5), L.w(p + 6), L.w(p + 7), L.w(p + 8),
+                         L.w(p + 9), L.w(p + 10)};
+  CX
+  dops::c_filter<B, T>(cx, x, f, I.aux0, S);
+  L.sync();
+  if (L.tl == T - 1) {
+    L.w(p) = S.a0; L.w(p + 1) = S.a1; L.w(p + 2) = S.a2; L.w(p + 3) = S.b1; L.w(p + 4) = S.b2; L.w(p + 5) = S.lastf;
+    L.w(p + 6) = S.lastdef; L.w(p + 7) = S.x1; L.w(p + 8) = S.x2; L.w(p + 9) = S.y1; L.w(p + 10) = S.y2;
+  }
   L.st(x, I.out[0]);
 }
 
-// Filter.js:27-51 with host-derived coefficients.  y[n] = ((a0 x + a1 x1) + a2 x2) - b1 y1 - b2 y2:
-// the bracket depends only on inputs (all lanes at once); the two subtractions and the f32
-// rounding are the recurrence, run by the T lanes of a voice in turn.
 template <int B, int T>
-__device__ __forceinline__ void op_filterc(const Lane<B, T> &L, const DuspDevInstr &I) {
+__device__ __forceinline__ void op_filterc(const Lane<B, T> &L, const DuspDevInstr &I) {  // Filter.js:27-51, host-derived coefficients
   float x[B];
   L.ld(x, I.in[0]);
   const int p = I.p;
-  const double a0 = L.w(p), a1 = L.w(p + 1), a2 = L.w(p + 2), b1 = L.w(p + 3), b2 = L.w(p + 4);
-  // o1/o2: the previous two inputs after `|| 0` (the reference keeps x2, y2 already normalised and
-  // applies `|| 0` to x1, y1 on every read, Filter.js:38-47); q1/q2: same for the outputs.
-  double o1 = js_or0(L.w(p + 5)), o2 = js_or0(L.w(p + 6)), q1 = js_or0(L.w(p + 7)), q2 = js_or0(L.w(p + 8));
-  if (T > 1) {  // inputs preceding this lane's first sample come from the previous time-lane
-    const float pm1 = __shfl_up_sync(0xffffffffu, x[B - 1], 1, T), pm2 = __shfl_up_sync(0xffffffffu, x[B - 2], 1, T);
-    if (L.tl > 0) { o1 = (double)js_or0f(pm1); o2 = (double)js_or0f(pm2); }
-  }
-  double c[B];
-#pragma unroll
-  for (int s = 0; s < B; s++) {
-    const double xin = x[s];
-    c[s] = a0 * xin + a1 * o1 + a2 * o2;
-    o2 = o1; o1 = (double)js_or0f(x[s]);
-  }
-  const double xlast = x[B - 1];  // raw x1 for the state block
-  auto recur = [&]() {
-    double b2q2 = b2 * q2;
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      const float yf = (float)(c[s] - b1 * q1 - b2q2);
-      x[s] = yf;
-      b2q2 = b2 * q1;              // next sample's b2*y2, ready before it is needed
-      q2 = q1; q1 = (double)js_or0f(yf);
-    }
-  };
-  if (T == 1) {
-    recur();
-  } else {
-#pragma unroll 1
-    for (int turn = 0; turn < T; turn++) {
-      if (L.tl == turn) recur();
-      const double n1 = shfl_d(q1, L.peer(turn)), n2 = shfl_d(q2, L.peer(turn));
-      if (L.tl == turn + 1) { q1 = n1; q2 = n2; }
-    }
-  }
+  double x1 = L.w(p + 5), x2 = L.w(p + 6), y1 = L.w(p + 7), y2 = L.w(p + 8);
+  CX
+  dops::c_filterc<B, T>(cx, x, L.w(p), L.w(p + 1), L.w(p + 2), L.w(p + 3), L.w(p + 4), x1, x2, y1, y2);
   L.sync();
-  if (L.tl == T - 1) { L.w(p + 5) = xlast; L.w(p + 6) = o2; L.w(p + 7) = (double)x[B - 1]; L.w(p + 8) = q2; }
+  if (L.tl == T - 1) { L.w(p + 5) = x1; L.w(p + 6) = x2; L.w(p + 7) = y1; L.w(p + 8) = y2; }
   L.st(x, I.out[0]);
 }
 
 // ----------------------------------------------------------------- rings
-// FixedDelay.js:14-20, CombFilter.js:11-17, AllPass.js:8-15
 template <int B, int T>
-__device__ __forceinline__ void op_fixdelay(const Lane<B, T> &L, const DuspDevInstr &I) {
+__device__ __forceinline__ void op_fixdelay(const Lane<B, T> &L, const DuspDevInstr &I) {  // FixedDelay.js:14-20, CombFilter.js:11-17, AllPass.js:8-15
   float x[B], g[B];
   L.ld(x, I.in[0]);
-  if (I.op != OP_FIXDELAY) L.ld(g, I.in[1]);
+  L.ld(g, I.op != OP_FIXDELAY ? I.in[1] : REF_NONE);
   long long n;
   float *buf = L.ring(I.aux0, n);
-  const double len = (double)n;
-  auto step = [&](long long p, int s) {
-    const float d = buf[p];
-    if (I.op == OP_FIXDELAY) { buf[p] = x[s]; x[s] = d; }
-    else if (I.op == OP_COMB) { buf[p] = (float)((double)x[s] + (double)d * (double)g[s]); x[s] = d; }
-    else { buf[p] = (float)((double)x[s] + (double)d * (double)g[s]); x[s] = (float)((double)d - (double)x[s] * (double)g[s]); }
-  };
-  const double tb0 = L.w(I.p);
-  if (T > 1 && n >= T * B && tb0 == floor(tb0) && tb0 >= 0.0 && tb0 < len) {
-    // every sample of the tile touches its own ring position: no dependence between time-lanes
-    long long p = (long long)tb0 + 1 + L.tl * B;
-    if (p >= n) p -= n;
-#pragma unroll
-    for (int s = 0; s < B; s++) { step(p, s); if (++p == n) p = 0; }
-    L.sync();
-    if (L.tl == T - 1) L.w(I.p) = (double)(p == 0 ? n - 1 : p - 1);
-  } else {
-    L.serial([&] {
-      double tb = L.w(I.p);
-#pragma unroll
-      for (int s = 0; s < B; s++) {
-        tb += 1.0;
-        if (!(tb < len)) tb = fmod(tb, len);  // (tBuffer + 1) % length
-        step((long long)tb, s);
-      }
-      L.w(I.p) = tb;
-    });
-  }
+  double tb = L.w(I.p);
+  CX
+  dops::c_fixdelay<B, T>(cx, x, g, buf, (int)n, tb, I.op == OP_FIXDELAY ? 0 : I.op == OP_COMB ? 1 : 2);
+  L.sync();
+  if (L.tl == T - 1) L.w(I.p) = tb;
   L.st(x, I.out[0]);
 }
 
@@ -585,28 +316,8 @@ __device__ __forceinline__ void op_delay(const Lane<B, T> &L, const DuspDevInstr
   L.ld(x, I.in[0]); L.ld(dl, I.in[1]);
   long long n;
   float *buf = L.ring(I.aux0, n);
-  const double len = (double)n;
-  const bool mono = I.op == OP_MONODELAY;
-  L.serial([&] {  // write-ahead scatter-add: later samples read what earlier ones added
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      double tb = (double)(t0 + s);
-      if (!(tb < len)) tb = fmod(tb, len);  // (clock + t) % length
-      float y = 0.0f;
-      if (!mono) { y = (float)ring_read(buf, len, tb); if (ring_valid(tb, len)) buf[(long long)tb] = 0.0f; }
-      double tw = tb + (double)dl[s];  // (tBuffer + delay) % length, exact fast paths for the usual range
-      if (tw >= len) { tw = tw < 2.0 * len ? tw - len : fmod(tw, len); }
-      else if (!(tw > -len)) tw = fmod(tw, len);
-      const double fr = tw - trunc(tw);
-      const double fl = floor(tw);
-      double ce = ceil(tw);
-      if (mono && !(ce < len && ce > -len)) ce = fmod(ce, len);
-      if (ring_valid(fl, len)) buf[(long long)fl] = (float)((double)buf[(long long)fl] + (double)x[s] * (1.0 - fr));
-      if (ring_valid(ce, len)) buf[(long long)ce] = (float)((double)buf[(long long)ce] + (double)x[s] * fr);
-      if (mono) { y = (float)ring_read(buf, len, tb); if (ring_valid(tb, len)) buf[(long long)tb] = 0.0f; }
-      x[s] = y;
-    }
-  });
+  CX
+  dops::c_delay<B, T>(cx, x, dl, buf, (int)n, t0, I.op == OP_MONODELAY);
   L.st(x, I.out[0]);
 }
 
@@ -616,124 +327,43 @@ __device__ __forceinline__ void op_readback(const Lane<B, T> &L, const DuspDevIn
   L.ld(x, I.in[0]); L.ld(dl, I.in[1]);
   long long n;
   float *buf = L.ring(I.aux0, n);
-  const double len = (double)n;
-  L.serial([&] {
-    double t = L.w(I.p);
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      const double wi = fmod(t + len, len);
-      if (ring_valid(wi, len)) buf[(long long)wi] = x[s];
-      x[s] = (float)ring_read(buf, len, fmod(t - (double)dl[s] + len, len));
-      t += 1.0;
-    }
-    L.w(I.p) = t;
-  });
+  double t = L.w(I.p);
+  CX
+  dops::c_readback<B, T>(cx, x, dl, buf, (int)n, t);
+  L.sync();
+  if (L.tl == T - 1) L.w(I.p) = t;
   L.st(x, I.out[0]);
 }
 
-// CircleBufferWriter.js:12-25 / CircleBufferReader.js:12-25 with a signal-rate OFFSET.  The compiler
-// only admits this form for a ring with a single tap unit, so serial turns keep the exact order.
 template <int B, int T>
-__device__ __forceinline__ void op_cbtap(const Lane<B, T> &L, const DuspDevInstr &I, long long t0) {
+__device__ __forceinline__ void op_cbtap(const Lane<B, T> &L, const DuspDevInstr &I, long long t0) {  // CircleBufferWriter/Reader.js:12-25, signal-rate OFFSET
   float off[B], x[B];
   L.ld(off, I.in[0]);
-  const bool writer = I.op == OP_CBWRITE;
-  const bool has_in = writer && I.in[1] != REF_NONE;
-  if (has_in) L.ld(x, I.in[1]);
+  const bool writer = I.op == OP_CBWRITE, has_in = writer && I.in[1] != REF_NONE;
+  L.ld(x, has_in ? I.in[1] : REF_NONE);
   long long n;
   float *buf = L.ring(I.aux0, n);
-  const double len = (double)n;
-  const double tu = L.w(I.p);
-  L.serial([&] {
-#pragma unroll
-    for (int s = 0; s < B; s++) {
-      const double tt = writer ? tu + (double)(t0 + s) + SRD * (double)off[s] : tu + (double)(t0 + s) - SRD * (double)off[s];
-      const double i = cb_index(tt, len);
-      float y = NAN;
-      if (ring_valid(i, len)) {
-        if (writer) {
-          float v = buf[(long long)i];
-          if (I.aux1) v = 0.0f;                                   // preWipe: write(c, tWrite, 0)
-          if (has_in) v = (float)((double)v + (double)x[s]);      // mix: +=
-          buf[(long long)i] = v;
-        } else {
-          y = buf[(long long)i];
-          if (I.aux1) buf[(long long)i] = 0.0f;                   // postWipe
-        }
-      }
-      off[s] = y;
-    }
-  });
+  CX
+  dops::c_cbtap<B, T>(cx, off, x, buf, (int)n, L.w(I.p), t0, writer, I.aux1 != 0, has_in);
   if (!writer) L.st(off, I.out[0]);
 }
 
-// Constant OFFSET: the ring index advances by one per sample; its start value is derived on the host.
 template <int B, int T>
-__device__ __forceinline__ void op_cbtapc(const Lane<B, T> &L, const DuspDevInstr &I) {
-  long long n64;
-  float *buf = L.ring(I.aux0, n64);
-  const int n = (int)n64;
-  const int i0 = (int)L.w(I.p + 1);  // running index; -1 = the offset never yields a valid index
+__device__ __forceinline__ void op_cbtapc(const Lane<B, T> &L, const DuspDevInstr &I) {  // ... constant OFFSET: the ring index just advances
   float x[B];
-  const bool writer = I.op == OP_CBWRITEC;
-  const bool has_in = writer && I.in[1] != REF_NONE;
-  const bool wipe = I.aux1 != 0;
-  if (has_in) L.ld(x, I.in[1]);
-  // one lane's run of B consecutive ring positions starting at i (wraps at most once)
-  auto run = [&](int i) {
-    if (i + B <= n) {  // no wrap inside the run: plain pointer walk
-      float *q = buf + i;
-      if (!writer) {
-#pragma unroll
-        for (int s = 0; s < B; s++) x[s] = q[s];
-        if (wipe) {                                                // postWipe
-#pragma unroll
-          for (int s = 0; s < B; s++) q[s] = 0.0f;
-        }
-      } else if (wipe) {                                           // preWipe: write(0) then mix -> 0 + in
-#pragma unroll
-        for (int s = 0; s < B; s++) q[s] = has_in ? __fadd_rn(0.0f, x[s]) : 0.0f;
-      } else if (has_in) {                                         // mix: `+=` (one f32 add == f64 add + rounding)
-        float v[B];
-#pragma unroll
-        for (int s = 0; s < B; s++) v[s] = q[s];
-#pragma unroll
-        for (int s = 0; s < B; s++) q[s] = __fadd_rn(v[s], x[s]);
-      }
-      i += B;
-      return i == n ? 0 : i;
-    }
-#pragma unroll 1
-    for (int s = 0; s < B; s++) {
-      if (writer) {
-        float v = wipe ? 0.0f : buf[i];
-        if (has_in) v = __fadd_rn(v, x[s]);
-        if (has_in || wipe) buf[i] = v;
-      } else {
-        x[s] = buf[i];
-        if (wipe) buf[i] = 0.0f;
-      }
-      if (++i == n) i = 0;
-    }
-    return i;
-  };
-  if (i0 < 0) {
-    if (!writer) {
-#pragma unroll
-      for (int s = 0; s < B; s++) x[s] = NAN;
-    }
-  } else if (T == 1 || n >= T * B) {  // distinct positions within the tile: time-lanes are independent
-    int i = i0 + L.tl * B;
-    if (i >= n) i %= n;
-    i = run(i);
-    L.sync();
-    if (L.tl == T - 1) L.w(I.p + 1) = (double)i;
-  } else {
-    L.serial([&] { L.w(I.p + 1) = (double)run((int)L.w(I.p + 1)); });
-  }
+  const bool writer = I.op == OP_CBWRITEC, has_in = writer && I.in[1] != REF_NONE;
+  L.ld(x, has_in ? I.in[1] : REF_NONE);
+  long long n;
+  float *buf = L.ring(I.aux0, n);
+  double idx = L.w(I.p + 1);
+  CX
+  dops::c_cbtapc<B, T>(cx, x, buf, (int)n, idx, writer, I.aux1 != 0, has_in);
+  L.sync();
+  if (L.tl == T - 1) L.w(I.p + 1) = idx;
   if (!writer) L.st(x, I.out[0]);
 }
-
+#undef CX
+#undef TABLE
 
 // ------------------------------------------------- frame-rate units (components/spectral)
 // Whole-chunk tiles only (B = 8, T = 32: one voice per warp, one 256-sample chunk per tile).  Frames are per-voice
@@ -1171,15 +801,15 @@ __global__ void __launch_bounds__(128, B <= 8 ? 4 : 2) dusp_render_tile(const __
           L.st(o, I.out[0]);
           break;
         }
-        case OP_OSC: op_osc<B, T>(L, I); break;
-        case OP_MCOSC: op_mcosc<B, T>(L, I); break;
+        case OP_OSC: op_osc<B, T>(L, I, true); break;
+        case OP_MCOSC: op_osc<B, T>(L, I, false); break;
         case OP_RAMP: op_ramp<B, T>(L, I); break;
         case OP_SHAPE: op_shape<B, T>(L, I); break;
         case OP_AHD: op_ahd<B, T>(L, I); break;
         case OP_TIMER: op_timer<B, T>(L, I); break;
         case OP_SRREDUX: op_srredux<B, T>(L, I); break;
-        case OP_NOISE: op_noise<B, T>(L, I); break;
-        case OP_NOISE1: op_noise1<B, T>(L, I); break;
+        case OP_NOISE: op_noise<B, T>(L, I, false); break;
+        case OP_NOISE1: op_noise<B, T>(L, I, true); break;
         case OP_RETRIG: if (B * T == DUSP_CHUNK) op_retrig<B, T>(L, I); break;
         case OP_SRETRIG: if (B * T == DUSP_CHUNK) op_sretrig<B, T>(L, I); break;
         case OP_POKEIF: if (B * T == DUSP_CHUNK) op_pokeif<B, T>(L, I); break;
