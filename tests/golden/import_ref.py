@@ -6,6 +6,10 @@ import numpy as np
 
 src = sys.argv[1]
 index = json.load(open(os.path.join(src, "index.json")))
+if "cases" in index:  # ref_dump.js of round 2: {"cases": {...}, "failed": {...}}
+    for name, why in index.get("failed", {}).items():
+        print("reference render FAILED for", name, "--", why.splitlines()[0])
+    index = {k: v for k, v in index["cases"].items() if "skipped" not in v}
 out = {}
 for name, meta in index.items():
     a = np.fromfile(os.path.join(src, name + ".f32"), dtype="<f4").reshape(meta["channels"], meta["samples"])

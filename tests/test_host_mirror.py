@@ -170,3 +170,17 @@ def test_incremental_circuit_growth_keeps_order_valid():
     circ = d.Circuit(a)
     m = C.Multiply(a, 0.5)  # Inlet.connect adds the new unit to a's circuit (Inlet.js:60-73)
     assert m.circuit is circ and circ.units.index(a) < circ.units.index(m)
+
+
+def test_cases_json_is_current():
+    """bindings/node/cases.json (what a Node host renders on the untouched reference, ref_dump.js) covers every case of
+    tests/circuits.py and says how each one is rebuilt."""
+    import json, os
+    import circuits
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "bindings", "node", "cases.json")
+    cases = json.load(open(path))
+    assert set(cases) == set(circuits.CASES)
+    for name, c in cases.items():
+        assert c["seconds"] == circuits.CASES[name][1] and c["exact"] == bool(circuits.CASES[name][2])
+        assert sum(k in c for k in ("dusp", "blob", "skip")) == 1, name
+    assert sum("skip" in c for c in cases.values()) <= 6
