@@ -240,13 +240,16 @@ DOPS_DEV void c_osc(const Cx<B, T> &cx, float (&f)[B], double &ph, const float *
   if (T > 1) {
     bool ok = ph >= 0.0 && ph < SRD && (ph + 65536.0) - 65536.0 == ph;  // multiple of 2^-36 (ulp of [2^16, 2^17))
     double part = 0.0;  // this lane's increments, reduced to [0, 44100)
+    uint32_t umax = 0u, umin = 0x7fffffffu;  // largest |f| and smallest nonzero |f| of the lane, as bit patterns
 #pragma unroll
     for (int s = 0; s < B; s++) {
       const uint32_t u = __float_as_uint(f[s]) & 0x7fffffffu;
-      ok = ok && (u == 0u || (u >= 0x39000000u && u < 0x472C4400u));  // 0, or 2^-13 <= |f| < 44100
+      umax = max(umax, u);
+      umin = min(umin, u - 1u);  // (0 wraps to 0xffffffff and drops out)
       const double x = part + (double)f[s];
       part = x < 0.0 ? x + SRD : (x >= SRD ? x - SRD : x);
     }
+    ok = ok && umax < 0x472C4400u && umin >= 0x38FFFFFFu;  // every f is 0, or 2^-13 <= |f| < 44100 (NaN / Inf fail the first test)
     if (!__all_sync(0xffffffffu, ok)) {
       serial1<B, T>(cx, ph, [&] { osc_run<B>(f, ph, tab, true); });
       return;

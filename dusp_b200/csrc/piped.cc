@@ -159,7 +159,7 @@ bool make_plan(const Program &p, Plan &pl) {
 }  // namespace
 
 namespace {
-std::string generate(const Program &p, int VC, int STEP, PipedInfo *info);
+std::string generate(const Program &p, int VC, int STEP, PipedInfo *info, bool want_ffp = false);
 }
 
 bool program_has_sequential(const Program &p) {
@@ -170,6 +170,9 @@ bool program_has_sequential(const Program &p) {
 std::string generate_piped_source(const Program &p, int VC, PipedInfo *info, int out_mode) {
   if (VC < 8 || VC > 32 || VC % 8) return "";
   std::string src;
+  const char *fe = getenv("DUSP_PIPED_FFP");
+  if (fe && atoi(fe) != 0) src = generate(p, VC, 128, info, true);  // "" when the circuit has no such form: the usual kernel then
+  if (!src.empty()) return fused_mode_prefix(out_mode) + src;
   if (const char *se = getenv("DUSP_PIPED_STEP")) src = generate(p, VC, atoi(se) == 128 ? 128 : 256, info);
   else {
     PipedInfo pi;
@@ -182,7 +185,7 @@ std::string generate_piped_source(const Program &p, int VC, PipedInfo *info, int
 
 namespace {
 
-std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
+std::string generate(const Program &p, int VC, int STEP, PipedInfo *info, bool want_ffp) {
   const int PB = STEP / 32;  // samples per lane in the P-warps and per S-warp group
   int NP = 4;                // P-warps per CTA (VC / NP voices each); DUSP_PIPED_PWARPS overrides (experiments)
   if (const char *e = getenv("DUSP_PIPED_PWARPS")) { int v = atoi(e); if (v >= 1 && v <= 8 && VC % v == 0) NP = v; }
@@ -205,7 +208,28 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     if (n1 != 1 || p.code[fc].op != OP_FILTERC || !se || atoi(se) == 0 || STEP != 256) fc = -1;  // opt-in: measured slower
   }
   const bool split = fc >= 0;
-  const int NROT = split ? 2 : 3;
+  // Feed-forward half in the P-warps (DUSP_PIPED_FFP=1): same circuits, no extra warp.  Stage 0 of the P-warps, lanes
+  // along time, turns the filter's input straight into the f64 brackets c = a0 x + a1 x1 + a2 x2 (the two preceding
+  // inputs of a lane's first samples come from its neighbour by shuffle, the voice's x1 / x2 words feed lane 0) and
+  // stores THOSE in the exchange row; the S-warp reads eight brackets, runs nothing but the recurrence, and overwrites
+  // the row in place with its f32 results (y of samples [8g, 8g+8) lands on the bytes of brackets that are already in
+  // registers).  Rows of doubles: 128-sample steps, two-step rotation, so three CTAs per SM still fit.
+  int ffc = -1, ff_in = -1;
+  if (want_ffp) {
+    int n1 = 0;
+    for (int i = 0; i < n; i++) if (pl.stage[i] == 1) { n1++; ffc = i; }
+    if (n1 != 1 || p.code[ffc].op != OP_FILTERC || STEP != 128 || NB != 1 || split) return "";
+    const DuspInstr &F = p.code[ffc];
+    bool in_ok = false, out_ok = false;
+    for (auto &c : pl.cross) {
+      if (c.from == 0 && c.slot == F.in[0] && c.used_in[1] && !c.used_in[2]) { in_ok = true; ff_in = c.def; }
+      if (c.def == ffc && c.to == 2) out_ok = true;
+    }
+    if (!in_ok || !out_ok || pl.cross.size() != 2) return "";
+  }
+  const bool ffp = ffc >= 0;
+  const bool tworot = split || ffp;
+  const int NROT = tworot ? 2 : 3;
   int RING_D = 4;  // groups of B samples in flight between the F-warp and the S-warp (DUSP_PIPED_RING overrides)
   if (const char *e = getenv("DUSP_PIPED_RING")) RING_D = std::max(2, std::min(16, atoi(e)));
 
@@ -236,6 +260,19 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
             s_decl << "        float xo" << i << "_" << k << "[B];\n";
             g.o << "      CP(xo" << i << "_" << k << ", s" << c.slot << ")\n";
             s_store << "        STX(" << c.buf << ", xo" << i << "_" << k << ")\n";
+          } else if (ffp && st == 0 && i == ff_in) {
+            const int P = p.code[ffc].p;  // words: a0 a1 a2 b1 b2 (derived), x1 x2 y1 y2
+            g.o << "      {  // feed-forward half of instruction " << ffc << " (Filter.js:40-42), lanes along time\n"
+                << "        const float xp1_ = __shfl_up_sync(0xffffffffu, s" << c.slot << "[B - 1], 1), xp2_ = __shfl_up_sync(0xffffffffu, s" << c.slot << "[B - 2], 1);\n"
+                << "        double o1_ = lane ? (double)js_or0f(xp1_) : js_or0(" << g.w(P + 5) << "), o2_ = lane ? (double)js_or0f(xp2_) : js_or0(" << g.w(P + 6) << ");\n"
+                << "        double c_[B];\n"
+                << "        filterc_ff<B>(s" << c.slot << ", c_, " << g.w(P) << ", " << g.w(P + 1) << ", " << g.w(P + 2) << ", o1_, o2_);\n"
+                << "        " << g.w(P + 5) << " = __shfl_sync(0xffffffffu, (double)s" << c.slot << "[B - 1], 31);  // x1: the raw last input\n"
+                << "        " << g.w(P + 6) << " = __shfl_sync(0xffffffffu, o2_, 31);                       // x2: normalised\n"
+                << "        double2 *const row_ = reinterpret_cast<double2 *>(xb + ((size_t)rot0 * VC + vl) * ROW);\n"
+                << "        UNROLL for (int q_ = 0; q_ < B / 2; q_++) row_[((B / 2) * lane + q_) ^ (vl & 7)] = make_double2(c_[2 * q_], c_[2 * q_ + 1]);\n"
+                << "      }\n";
+            g.mut(P + 5); g.mut(P + 6);
           } else {
             g.o << "      STX(" << c.buf << ", s" << c.slot << ")\n";
           }
@@ -248,7 +285,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
           if (st == 1) {
             s_load << "        float xi" << i << "_" << k << "[B]; LDX(xi" << i << "_" << k << ", " << c.buf << ")\n";
             g.o << "      CP(s" << c.slot << ", xi" << i << "_" << k << ")  // value of instruction " << i << " (stage " << c.from << ")\n";
-          } else if (split) {  // read before stage 0 of this iteration reuses the row (two-step rotation)
+          } else if (tworot) {  // read before stage 0 of this iteration reuses the row (two-step rotation)
             pre_decl << "        float prex" << i << "_" << k << "[B];\n";
             prex_code << "          LDX(prex" << i << "_" << k << ", " << c.buf << ")  // value of instruction " << i << " (stage " << c.from << ")\n";
             g.o << "      CP(s" << c.slot << ", prex" << i << "_" << k << ")\n";
@@ -265,7 +302,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
   std::map<int, int> pj;  // word -> row of the shared-memory word table
   for (int w : p_words) { int j = (int)pj.size(); pj[w] = j; }
   const int NPW = (int)pj.size();
-  const size_t xb_bytes = (size_t)NROT * NB * VC * STEP * sizeof(float);
+  const size_t xb_bytes = (size_t)NROT * NB * VC * STEP * (ffp ? sizeof(double) : sizeof(float));
   const size_t ring_bytes = split ? (size_t)RING_D * PB * 32 * sizeof(double) + 16 : 0;  // + the two hand-over counters
   // optional dynamic voice queue for the P-warps (measured slightly slower than the static split: off)
   const bool dyn = getenv("DUSP_PIPED_DYN") != nullptr;
@@ -323,7 +360,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "extern \"C\" __global__ void " << (getenv("DUSP_PIPED_MAXNREG") ? "__maxnreg__(" + std::string(getenv("DUSP_PIPED_MAXNREG")) + ")"
                                              : "__launch_bounds__(" + std::to_string(NWARPS * 32) + ", " + std::to_string(min_blocks) + ")")
     << " dusp_piped(const __grid_constant__ FusedParams kp) {\n"
-    << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", ROW = STEP / 4, NP = " << NP << ", VW = VC / NP, NROT = " << NROT << ", RING_D = " << RING_D << ";\n"
+    << "  constexpr int B = " << PB << ", VC = " << VC << ", NB = " << NB << ", STEP = " << STEP << ", ROW = STEP / " << (ffp ? 2 : 4) << ", NP = " << NP << ", VW = VC / NP, NROT = " << NROT << ", RING_D = " << RING_D << ";\n"
     << "  extern __shared__ float4 smem4[];\n"
     << "  float4 *const xb = smem4;                                                    // [NROT][NB][VC][ROW] float4, swizzled\n"
     << "  double *const pw = reinterpret_cast<double *>(smem4 + NROT * NB * VC * ROW);  // [" << NPW << "][VC] words of the P-warps' units\n"
@@ -370,7 +407,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "    _Pragma(\"unroll 1\")\n"
     << "    for (int it = 0; it < n_steps + 2; it++) {\n"
     << "      const bool do0 = it < n_steps, do2 = it >= 2;\n"
-    << (split ? "      const int rot0 = it & 1, rot2 = it & 1;  // two-step rotation: stage 2 of step it-2 frees the row stage 0 of step it fills\n"
+    << (tworot ? "      const int rot0 = it & 1, rot2 = it & 1;  // two-step rotation: stage 2 of step it-2 frees the row stage 0 of step it fills\n"
               : "      const int rot0 = it % 3, rot2 = (it + 1) % 3;  // (it - 2) mod 3\n")
     << "      float macc[2][B]; UNROLL for (int i_ = 0; i_ < B; i_++) { macc[0][i_] = 0.0f; macc[1][i_] = 0.0f; }\n"
     << (dyn ? "      if (threadIdx.x == 0) qctr[(it + 1) % 3] = 0;  // next step's queue (last used two steps ago)\n" : "")
@@ -423,7 +460,40 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info) {
     << "      }\n"
     << "      __syncthreads();\n"
     << "    }\n";
-  if (split) {
+  if (ffp) {
+    const int P = p.code[ffc].p;
+    auto W = [&](int k) { return "kp.words[" + std::to_string(P + k) + " * nv + v]"; };
+    const char *magic = getenv("DUSP_PIPED_MAGIC");
+    const bool use_magic = magic && atoi(magic) != 0;
+    s << "  } else {\n"
+      << "    // ---------------- S-warp: one voice per lane, nothing but the recurrence  y = c - b1 y1 - b2 y2  (Filter.js:40-48)\n"
+      << "    const int vl = lane < VC ? lane : VC - 1;\n"
+      << "    const long long v = v0 + vl;\n"
+      << "    const double b1 = " << W(3) << ", b2 = " << W(4) << ";\n"
+      << "    double q1 = js_or0(" << W(7) << "), q2 = js_or0(" << W(8) << ");\n"
+      << "    float ylast = (float)" << W(7) << ";\n"
+      << "    _Pragma(\"unroll 1\")\n"
+      << "    for (int it = 0; it < n_steps + 2; it++) {\n"
+      << "      if (it >= 1 && it <= n_steps && lane < VC) {\n"
+      << "        float4 *const row = xb + ((size_t)((it - 1) & 1) * VC + vl) * ROW;\n"
+      << "        const double2 *const rowd = reinterpret_cast<const double2 *>(row);\n"
+      << "        const int k_ = vl & 7;\n"
+      << "        _Pragma(\"unroll 1\")\n"
+      << "        for (int g = 0; g < STEP / 8; g++) {\n"
+      << "          double c[8];\n"
+      << "          UNROLL for (int q_ = 0; q_ < 4; q_++) { const double2 t_ = rowd[(4 * g + q_) ^ k_]; c[2 * q_] = t_.x; c[2 * q_ + 1] = t_.y; }\n"
+      << "          float y[8];\n"
+      << "          filterc_rec<8, " << (use_magic ? "true" : "false") << ">(c, y, b1, b2, q1, q2);\n"
+      << "          ylast = y[7];\n"
+      << "          row[(2 * g) ^ k_] = make_float4(y[0], y[1], y[2], y[3]);\n"
+      << "          row[(2 * g + 1) ^ k_] = make_float4(y[4], y[5], y[6], y[7]);\n"
+      << "        }\n"
+      << "      }\n"
+      << "      __syncthreads();\n"
+      << "    }\n"
+      << "    if (lane < VC) { " << W(7) << " = (double)ylast; " << W(8) << " = q2; }\n"
+      << "  }\n";
+  } else if (split) {
     // ---- S-warp: the recurrence only; F-warp: the bracket.  Both one voice per lane, state in registers for the launch.
     const DuspInstr &F = p.code[fc];
     const int P = F.p;  // words: a0 a1 a2 b1 b2 (derived), x1 x2 y1 y2
