@@ -18,7 +18,8 @@
 //   dusp.renderChannelData = require('dusp-b200')     // this file
 //   const cd = await dusp.renderChannelData(dusp.unDusp('(O440 for 0.5) then O220'), 10)
 'use strict'
-const addon = require('./build/Release/dusp_b200_addon.node')
+let addon_ = null
+function addon() { return addon_ || (addon_ = require('./build/Release/dusp_b200_addon.node')) }  // on first render: the blob writer works without it
 let refDir = 'dusp'
 let Circuit = null
 function reference(mod) { return require(refDir + '/src/' + mod) }
@@ -29,7 +30,8 @@ const EVENT_HORIZON_S = 600      // self-rescheduling events are expanded up to 
 
 // ---------------------------------------------------------------- the injected random generator
 // Math.random inside Noise (Noise.js:10,23) and SporadicRetriggerer (SporadicRetrigger.js:13) is replaced on BOTH
-// sides by a counter-based generator, draw k of stream `seed` = dusp_rand53(seed, k) (include/dusp_b200.h).
+// sides by a counter-based generator, draw k of stream `seed` = dusp_rand(seed, k) (include/dusp_b200.h): 32 bits,
+// lowbias32(low32(k) + low32(seed)) ^ high32(seed), as a fraction of 2^32.  The splitmix below only hands out seeds.
 const M64 = (1n << 64n) - 1n
 function mix64(z) {
   z &= M64
@@ -37,7 +39,14 @@ function mix64(z) {
   z = ((z ^ (z >> 27n)) * 0x94D049BB133111EBn) & M64
   return z ^ (z >> 31n)
 }
-function rand53(seed, k) { return Number(mix64(BigInt(seed) + (BigInt(k) + 1n) * 0x9E3779B97F4A7C15n) >> 11n) / 9007199254740992 }
+function tickRand(seed, k) {
+  seed = BigInt(seed)
+  let x = Number((BigInt(k) + (seed & 0xffffffffn)) & 0xffffffffn)
+  x ^= x >>> 16; x = Math.imul(x, 0x7feb352d) >>> 0
+  x ^= x >>> 15; x = Math.imul(x, 0x846ca68b) >>> 0
+  x ^= x >>> 16
+  return ((x ^ Number((seed >> 32n) & 0xffffffffn)) >>> 0) / 4294967296
+}
 let hostSeed = 12345n, noiseOrdinal = 0n
 function seed(s) { hostSeed = BigInt(s); noiseOrdinal = 0n }                      // dusp_b200/config.py: seed()
 function nextNoiseSeed() { return mix64((hostSeed ^ 0xD1B54A32D192ED03n) + (noiseOrdinal++) * 0x9E3779B97F4A7C15n) }
@@ -50,7 +59,7 @@ function assignStreams(units) {
     if ((k === 'Noise' || k === 'SporadicRetriggerer') && u.dusp_b200_seed === undefined) {
       Object.defineProperty(u, 'dusp_b200_seed', { value: nextNoiseSeed(), enumerable: false, writable: true })
       Object.defineProperty(u, 'dusp_b200_draw', { value: k === 'Noise' ? 1 : 0, enumerable: false, writable: true })
-      if (k === 'Noise') u.y = 2 * rand53(u.dusp_b200_seed, 0) - 1
+      if (k === 'Noise') u.y = 2 * tickRand(u.dusp_b200_seed, 0) - 1
     }
   }
 }
@@ -59,7 +68,7 @@ function assignStreams(units) {
 function installSeededRandom() {
   const real = Math.random
   let current = null
-  Math.random = () => current ? rand53(current.dusp_b200_seed, current.dusp_b200_draw++) : real()
+  Math.random = () => current ? tickRand(current.dusp_b200_seed, current.dusp_b200_draw++) : real()
   for (const mod of ['components/Noise', 'components/SporadicRetrigger']) {
     const proto = reference(mod).prototype
     if (proto._tick.dusp_b200_wrapped) continue
@@ -321,7 +330,7 @@ async function renderChannelData(outlet, duration = 1, { TypedArray = Float32Arr
   const { blob, circuit, outlet: out } = circuitBlob(outlet)
   const length = duration * out.sampleRate                                       // renderChannelData.js:24
   const n = Number.isFinite(length) ? Math.max(0, Math.trunc(length)) : 0
-  const { data, channels } = await addon.renderRun([blob], [1], [], [], n, 0, device)
+  const { data, channels } = await addon().renderRun([blob], [1], [], [], n, 0, device)
   circuit.dusp_b200_rendered = true
   const channelData = []
   for (let c = 0; c < channels; c++) channelData.push(TypedArray.from(data.subarray(c * n, (c + 1) * n)))
@@ -341,7 +350,7 @@ async function renderBatch(outlet, nVoices, duration = 1, { overrides = {}, outM
     for (let v = 0; v < nVoices; v++) values[v * names.length + k] = overrides[nm][v]
   })
   const n = Math.max(0, Math.trunc(duration * out.sampleRate))
-  const res = await addon.renderRun([blob], [nVoices], [names], [values], n, outMode, device)
+  const res = await addon().renderRun([blob], [nVoices], [names], [values], n, outMode, device)
   circuit.dusp_b200_rendered = true
   return res
 }
@@ -349,6 +358,6 @@ async function renderBatch(outlet, nVoices, duration = 1, { overrides = {}, outM
 module.exports = renderChannelData
 Object.assign(module.exports, {
   renderChannelData, renderBatch, circuitBlob, circuitToBlob, collectTimeline, collectTriggers, assignStreams,
-  installSeededRandom, seed, rand53,
+  installSeededRandom, seed, tickRand,
   useReference(dir) { refDir = dir; Circuit = null },
 })
