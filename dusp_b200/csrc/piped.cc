@@ -323,6 +323,7 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info, bool w
   }
   int min_blocks = (int)std::min<size_t>(4, (227 * 1024) / (smem + 1024));
   if (min_blocks < 1) min_blocks = 1;
+  if (const char *e = getenv("DUSP_PIPED_MINB")) min_blocks = std::max(1, std::min(min_blocks, atoi(e)));  // experiments
 
   bool stage_has[3] = {false, false, false};
   for (int i = 0; i < n; i++) stage_has[pl.stage[i]] = true;
