@@ -318,13 +318,13 @@ def measure_workloads(args):
                 "voices": 1000, "units_per_voice": p.num_units, "value": 1000 * p.num_units * total / g, "unit": "unit-samples/s",
                 "ms": g * 1e3, "bytes_per_voice_sample": p.bytes_per_voice_sample(capi.OUT_VOICES), "kernel": s.launch_info()})
     s.close()
-    # W4: 10 000 random Dusp circuits (depth 4-8), 10 s mono, one multi-program launch per block
+    # W4: 10 000 random Dusp circuits (depth 4-8), 10 s mono, one multi-program launch
     nc = args.w4_circuits
     t0 = time.perf_counter()
     progs = [capi.Program(circuit_blob(W.w4_circuit(i))[0]) for i in range(nc)]
     s = capi.Session(progs, [1] * nc, 0)
     build_s = time.perf_counter() - t0
-    g = timed(s, total, nc)
+    g = timed(s, total, nc, blk=441088)  # 17.6 GB of channel data: one launch per pass, so the longest circuit is the tail once
     out.append({"workload": "W4 (BASELINE configs[3]): %d random Dusp circuits (depth 4-8), 10 s mono" % nc, "voices": nc,
                 "units_per_voice": s.unit_count / nc, "value": s.unit_count * total / g, "unit": "unit-samples/s", "ms": g * 1e3,
                 "host_build_s": build_s, "kernel": s.launch_info()})

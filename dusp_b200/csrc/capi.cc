@@ -10,6 +10,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -370,6 +371,24 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
           descs.push_back(d);
         }
       }
+    // longest circuits first: the launch is one CTA per circuit handed out in index order, so its tail is the circuit
+    // that starts last; the estimate weighs the ops that run as 32 serial turns of the warp
+    if (descs.size() > 1 && !getenv("DUSP_MULTI_UNSORTED")) {
+      std::vector<std::pair<long long, size_t>> key(descs.size());
+      size_t k = 0;
+      for (auto &g : s->groups) {
+        if (!g.in_multi) continue;
+        long long cost = 0;
+        for (auto &I : g.dev_code)
+          cost += (I.op == OP_FILTER || I.op == OP_FILTERC || I.op == OP_SHAPE || I.op == OP_AHD || I.op == OP_COMB || I.op == OP_ALLPASS) ? 12
+                  : (I.op == OP_OSC || I.op == OP_MCOSC || I.op == OP_NOISE || I.op == OP_RAMP) ? 3 : 1;
+        for (int v = 0; v < g.n_voices; v++, k++) key[k] = {-cost, k};
+      }
+      std::stable_sort(key.begin(), key.end());
+      std::vector<DuspWarpDesc> sorted(descs.size());
+      for (size_t i = 0; i < key.size(); i++) sorted[i] = descs[key[i].second];
+      descs.swap(sorted);
+    }
     s->n_multi = (int)descs.size();
     if (s->n_multi) {
       CUDA_TRY(cudaMalloc(&s->d_multi, descs.size() * sizeof(DuspWarpDesc)));
@@ -609,6 +628,8 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     int wpc = 1;
     if (const char *e = getenv("DUSP_MULTI_WPC")) wpc = std::max(1, std::min(4, atoi(e)));
     while (wpc > 1 && (size_t)s->multi_slots * mb * 128 * wpc > 100 * 1024) wpc >>= 1;
+    kp.density = 6;  // 80 registers per thread: up to 25 circuits per SM now that the slots no longer bound it
+    if (const char *e = getenv("DUSP_MULTI_DENSITY")) kp.density = atoi(e);
     int grid = 0, smem = 0;
     int e = dusp_launch_render(&kp, mb, 32, wpc, st, &grid, &smem);
     if (e != 0) return fail(DUSP_ECUDA, std::string("render launch: ") + cudaGetErrorString((cudaError_t)e));

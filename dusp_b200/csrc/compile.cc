@@ -935,6 +935,73 @@ Program compile(const Graph &g) {
   }
   recompute_defs();
 
+  // ---- evaluation order ----
+  // The reference ticks a feed-forward circuit level by level (Circuit.js:67-107: every leaf first), so all of a
+  // tree's leaves are live at once: 28 slots for a 64-unit W4 circuit, 15 KB of shared memory per warp and 14
+  // circuits per SM in a heterogeneous batch.  Where the order of two ops cannot be observed -- no value is read one
+  // chunk late, every op owns its state words and its ring, nothing pokes another unit's state -- the ops are
+  // re-sequenced depth first from the sinks, deeper operand first (Sethi-Ullman): same values, a handful of slots.
+  {
+    auto own_state_only = [](int op) {
+      switch (op) {
+        case OP_COPY: case OP_NEG: case OP_ABS: case OP_S2S: case OP_SEMI: case OP_DB2S: case OP_MIDI2F: case OP_FIXMUL:
+        case OP_MUL: case OP_DIV: case OP_POW: case OP_ADD: case OP_SUB: case OP_GAIN: case OP_CLIP: case OP_HCA: case OP_HCB:
+        case OP_RESCALE: case OP_XFADE: case OP_PAN: case OP_VECMAG: case OP_OSC: case OP_MCOSC: case OP_RAMP: case OP_SHAPE:
+        case OP_AHD: case OP_TIMER: case OP_NOISE: case OP_FILTER: case OP_FIXDELAY: case OP_COMB: case OP_ALLPASS:
+        case OP_OUT: case OP_FILTERC: case OP_PANC: case OP_GAINC: case OP_NOISE1: case OP_ADD0: case OP_PICK:
+          return true;
+        default:
+          return false;
+      }
+    };
+    auto has_ring = [](int op) { return op == OP_FIXDELAY || op == OP_COMB || op == OP_ALLPASS; };
+    bool ok = b.prog.n_stale == 0 && !g.keep_all && !b.prog.chunk_tiles && !getenv("DUSP_KEEP_TICK_ORDER");
+    std::set<int> words_seen, rings_seen;
+    const int n = (int)seq.size();
+    for (int i = 0; i < n && ok; i++) {
+      const IR &r = seq[i];
+      if (!own_state_only(r.op)) ok = false;
+      if (r.p >= 0 && !words_seen.insert(r.p).second) ok = false;
+      if (has_ring(r.op) && !rings_seen.insert(r.aux[0]).second) ok = false;
+      for (auto &o : r.in) if (o.kind == 1 && !(b.vals[o.id].def >= 0 && b.vals[o.id].def < i)) ok = false;
+    }
+    if (ok && n > 2) {
+      std::vector<std::vector<int>> kids(n);
+      std::vector<char> is_read(n, 0);
+      std::vector<int> need(n, 1);
+      for (int i = 0; i < n; i++) {
+        for (auto &o : seq[i].in)
+          if (o.kind == 1) {
+            const int d = b.vals[o.id].def;
+            is_read[d] = 1;
+            if (std::find(kids[i].begin(), kids[i].end(), d) == kids[i].end()) kids[i].push_back(d);
+          }
+        std::stable_sort(kids[i].begin(), kids[i].end(), [&](int a, int c) { return need[a] > need[c]; });
+        for (size_t k = 0; k < kids[i].size(); k++) need[i] = std::max(need[i], need[kids[i][k]] + (int)k);
+      }
+      std::vector<char> done(n, 0);
+      std::vector<IR> res;
+      res.reserve(n);
+      std::vector<std::pair<int, size_t>> stack;
+      for (int root = 0; root < n; root++) {
+        if (is_read[root] || done[root]) continue;
+        stack.push_back({root, 0});
+        done[root] = 1;
+        while (!stack.empty()) {
+          auto &top = stack.back();
+          if (top.second < kids[top.first].size()) {
+            const int c = kids[top.first][top.second++];
+            if (!done[c]) { done[c] = 1; stack.push_back({c, 0}); }
+          } else {
+            res.push_back(seq[top.first]);
+            stack.pop_back();
+          }
+        }
+      }
+      if ((int)res.size() == n) { seq.swap(res); recompute_defs(); }
+    }
+  }
+
   // ---- slot allocation: linear scan, in-place reuse allowed (ops load all inputs before storing) ----
   std::vector<int> last_use(b.vals.size(), -1);
   for (size_t i = 0; i < seq.size(); i++) for (auto &o : seq[i].in) if (o.kind == 1) last_use[o.id] = (int)i;

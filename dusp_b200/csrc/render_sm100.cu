@@ -648,10 +648,17 @@ __device__ __noinline__ void frame_op(const FrameCtx &F, const DuspDevInstr &I, 
   __syncwarp();
 }
 
+__device__ __forceinline__ void fetch_instr(DuspDevInstr &I, const DuspDevInstr *p) {
+  const int4 *src = reinterpret_cast<const int4 *>(p);
+  int4 *dst = reinterpret_cast<int4 *>(&I);
+  dst[0] = __ldg(src); dst[1] = __ldg(src + 1); dst[2] = __ldg(src + 2);
+}
+
 // --------------------------------------------------------------- the kernel
 // registers are capped so that at least 16 (B=8) / 8 (B=16) warps are resident per SM
-template <int B, int T>
-__global__ void __launch_bounds__(128, B <= 8 ? 4 : 2) dusp_render_tile(const __grid_constant__ DuspKernelParams kp) {
+// D > 0 (heterogeneous batches, one circuit per warp: latency-bound, so residency is what counts): D CTAs of 128 threads
+template <int B, int T, int D = 0>
+__global__ void __launch_bounds__(128, D > 0 ? D : (B <= 8 ? 4 : 2)) dusp_render_tile(const __grid_constant__ DuspKernelParams kp) {
   static_assert(B % 4 == 0 && (DUSP_CHUNK % (B * T)) == 0 && 32 % T == 0, "tile must divide the chunk");
   extern __shared__ float4 smem[];
   constexpr int V = 32 / T;
@@ -690,15 +697,18 @@ __global__ void __launch_bounds__(128, B <= 8 ? 4 : 2) dusp_render_tile(const __
   for (long long tile = 0; tile < n_proc; tile += T * B) {
     const long long tl0 = tile + tl * B;   // this lane's first sample within the launch
     const int cpos = (int)(tl0 & (DUSP_CHUNK - 1));
+    // programs in global memory: the next instruction's 48 bytes are requested before the current one executes (with
+    // a circuit per warp the fetch is an L2 hit more often than an L1 hit: 11 % of the W4 launch's stall samples sat
+    // on the switch below, waiting for I.op)
+    DuspDevInstr I, Inext;
+    if (!use_inline) fetch_instr(Inext, code);
 #pragma unroll 1
     for (int pc = 0; pc < n_instr; pc++) {
-      DuspDevInstr I;
       if (use_inline) {
         I = kp.prog_inline[pc];
       } else {
-        const int4 *src = reinterpret_cast<const int4 *>(code + pc);
-        int4 *dst = reinterpret_cast<int4 *>(&I);
-        dst[0] = __ldg(src); dst[1] = __ldg(src + 1); dst[2] = __ldg(src + 2);
+        I = Inext;
+        fetch_instr(Inext, code + (pc + 1 < n_instr ? pc + 1 : 0));
       }
       switch (I.op) {
         case OP_COPY: map1<B, T>(L, I, [](float a) { return a; }); break;
@@ -917,7 +927,7 @@ if (!kp.out_raw) {
   }
 }
 
-template <int B, int T>
+template <int B, int T, int D = 0>
 int launch(const DuspKernelParams *kp, int warps_per_cta, cudaStream_t st, int *grid_out, int *smem_out) {
   constexpr int V = 32 / T;
   const int n_warps = (kp->n_voices + V - 1) / V;
@@ -926,9 +936,9 @@ int launch(const DuspKernelParams *kp, int warps_per_cta, cudaStream_t st, int *
   const size_t smem = (size_t)warps_per_cta * kp->n_slots * B * 32 * sizeof(float);
   if (grid_out) *grid_out = grid;
   if (smem_out) *smem_out = (int)smem;
-  cudaError_t e = cudaFuncSetAttribute(dusp_render_tile<B, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(dusp_render_tile<B, T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  dusp_render_tile<B, T><<<grid, block, smem, st>>>(*kp);
+  dusp_render_tile<B, T, D><<<grid, block, smem, st>>>(*kp);
   return (int)cudaGetLastError();
 }
 
@@ -946,6 +956,12 @@ extern "C" int dusp_launch_supported(int sub_block, int time_lanes) {
 
 extern "C" int dusp_launch_render(const DuspKernelParams *kp, int sub_block, int time_lanes, int warps_per_cta,
                                   void *stream, int *grid_out, int *smem_out) {
+  if (kp->multi && time_lanes == 32 && kp->density > 0) {  // heterogeneous batch: the register-capped instantiations
+    if (sub_block == 4 && kp->density >= 8) return launch<4, 32, 8>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
+    if (sub_block == 4) return launch<4, 32, 6>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
+    if (sub_block == 8 && kp->density >= 8) return launch<8, 32, 8>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
+    if (sub_block == 8) return launch<8, 32, 6>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
+  }
 #define X(BV, TV) if (sub_block == BV && time_lanes == TV) return launch<BV, TV>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
   DUSP_CONFIGS(X)
 #undef X

@@ -1,5 +1,5 @@
 """W4 probe (BASELINE configs[3]): N random circuits in one session, multi-program interpreter launch.
-usage: perf_w4.py [n_circuits=10000] [seconds=10]"""
+usage: perf_w4.py [n_circuits=10000] [seconds=10] [block_samples=88064]"""
 import sys, os, time, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -15,7 +15,7 @@ t1 = time.perf_counter()
 s = capi.Session(progs, [1] * n, 0)
 t2 = time.perf_counter()
 units = s.unit_count
-blk = 88064
+blk = int(sys.argv[3]) if len(sys.argv) > 3 else 88064
 total = int(secs * 44100)
 buf = torch.empty(n * blk, dtype=torch.float32, device="cuda")
 st = torch.cuda.current_stream()
