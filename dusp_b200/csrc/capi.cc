@@ -628,7 +628,8 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     int wpc = 1;
     if (const char *e = getenv("DUSP_MULTI_WPC")) wpc = std::max(1, std::min(4, atoi(e)));
     while (wpc > 1 && (size_t)s->multi_slots * mb * 128 * wpc > 100 * 1024) wpc >>= 1;
-    kp.density = 6;  // 80 registers per thread: up to 25 circuits per SM now that the slots no longer bound it
+    kp.density = 8;  // 64 registers per thread, 32 circuits per SM now that the slots no longer bound it (W4: 1134 ms against
+                     // 1200 at 80 registers and 1302 uncapped); DUSP_MULTI_DENSITY=0 selects the uncapped kernel
     if (const char *e = getenv("DUSP_MULTI_DENSITY")) kp.density = atoi(e);
     int grid = 0, smem = 0;
     int e = dusp_launch_render(&kp, mb, 32, wpc, st, &grid, &smem);

@@ -657,6 +657,7 @@ __device__ __forceinline__ void fetch_instr(DuspDevInstr &I, const DuspDevInstr 
 // --------------------------------------------------------------- the kernel
 // registers are capped so that at least 16 (B=8) / 8 (B=16) warps are resident per SM
 // D > 0 (heterogeneous batches, one circuit per warp: latency-bound, so residency is what counts): D CTAs of 128 threads
+// per SM, i.e. 64 registers per thread at D = 8 (a few hundred bytes of spills, measured faster: DESIGN.md section 5)
 template <int B, int T, int D = 0>
 __global__ void __launch_bounds__(128, D > 0 ? D : (B <= 8 ? 4 : 2)) dusp_render_tile(const __grid_constant__ DuspKernelParams kp) {
   static_assert(B % 4 == 0 && (DUSP_CHUNK % (B * T)) == 0 && 32 % T == 0, "tile must divide the chunk");
@@ -956,12 +957,8 @@ extern "C" int dusp_launch_supported(int sub_block, int time_lanes) {
 
 extern "C" int dusp_launch_render(const DuspKernelParams *kp, int sub_block, int time_lanes, int warps_per_cta,
                                   void *stream, int *grid_out, int *smem_out) {
-  if (kp->multi && time_lanes == 32 && kp->density > 0) {  // heterogeneous batch: the register-capped instantiations
-    if (sub_block == 4 && kp->density >= 8) return launch<4, 32, 8>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
-    if (sub_block == 4) return launch<4, 32, 6>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
-    if (sub_block == 8 && kp->density >= 8) return launch<8, 32, 8>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
-    if (sub_block == 8) return launch<8, 32, 6>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
-  }
+  if (kp->multi && time_lanes == 32 && sub_block == 4 && kp->density > 0)  // heterogeneous batch: the register-capped instantiation
+    return launch<4, 32, 8>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
 #define X(BV, TV) if (sub_block == BV && time_lanes == TV) return launch<BV, TV>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
   DUSP_CONFIGS(X)
 #undef X

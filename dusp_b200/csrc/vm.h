@@ -175,6 +175,6 @@ struct DuspKernelParams {
   const double *ctab;    // program constants built on the host with libm: FFT twiddles, window envelopes (f64)
   const DuspDevInstr *prog_global;
   const DuspWarpDesc *multi;  // non-null: n_voices descriptors, one per warp (requires T = 32)
-  int64_t density;       // multi only: > 0 selects the register-capped instantiation (CTAs of 128 threads per SM: 6 or 8)
+  int64_t density;       // multi only: > 0 selects the register-capped instantiation (64 registers per thread, 32 circuits per SM)
   DuspDevInstr prog_inline[DUSP_INLINE_INSTR];
 };
