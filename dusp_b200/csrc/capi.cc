@@ -113,6 +113,7 @@ struct dusp_session {
   DuspRing *d_ringtab_pool = nullptr; DuspDevInstr *d_code_pool = nullptr;
   size_t words_total = 0, rings_total = 0, stale_total = 0;
   std::vector<double> h_all;  // staging image of the words pool
+  long long *d_dbg = nullptr;   // DUSP_MULTI_DEBUG_FILE: per-warp tick counts of the last multi-program launch
   DuspWarpDesc *d_multi = nullptr;  // one descriptor per voice of the interpreter groups (multi-program launch)
   int n_multi = 0, multi_slots = 1;
   float *d_staging[2] = {nullptr, nullptr};  // host-output path: double-buffered device blocks
@@ -181,7 +182,7 @@ void dusp_session_destroy(dusp_session *s) {
   if (!s) return;
   cudaSetDevice(s->device);
   cudaFree(s->d_words_pool); cudaFree(s->d_rings_pool); cudaFree(s->d_stale_pool); cudaFree(s->d_ringtab_pool);
-  cudaFree(s->d_code_pool); cudaFree(s->d_multi);
+  cudaFree(s->d_code_pool); cudaFree(s->d_multi); cudaFree(s->d_dbg);
   cudaFree(s->d_tables); cudaFree(s->d_sm_slots);
   for (auto &g : s->groups) cudaFree(g.d_ctab);
   for (int i = 0; i < 2; i++) {
@@ -631,9 +632,24 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     kp.density = 8;  // 64 registers per thread, 32 circuits per SM now that the slots no longer bound it (W4: 1134 ms against
                      // 1200 at 80 registers and 1302 uncapped); DUSP_MULTI_DENSITY=0 selects the uncapped kernel
     if (const char *e = getenv("DUSP_MULTI_DENSITY")) kp.density = atoi(e);
+    // diagnostics: DUSP_MULTI_DEBUG_FILE=<path> appends "launch warp output_row instructions ticks" for every circuit
+    const char *dbg_file = getenv("DUSP_MULTI_DEBUG_FILE");
+    if (dbg_file && !s->d_dbg) CUDA_TRY(cudaMalloc(&s->d_dbg, (size_t)s->n_multi * sizeof(long long)));
+    kp.dbg_cycles = dbg_file ? s->d_dbg : nullptr;
     int grid = 0, smem = 0;
     int e = dusp_launch_render(&kp, mb, 32, wpc, st, &grid, &smem);
     if (e != 0) return fail(DUSP_ECUDA, std::string("render launch: ") + cudaGetErrorString((cudaError_t)e));
+    if (dbg_file) {
+      std::vector<long long> t(s->n_multi);
+      std::vector<DuspWarpDesc> d(s->n_multi);
+      CUDA_TRY(cudaStreamSynchronize(st));
+      CUDA_TRY(cudaMemcpy(t.data(), s->d_dbg, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+      CUDA_TRY(cudaMemcpy(d.data(), s->d_multi, d.size() * sizeof(DuspWarpDesc), cudaMemcpyDeviceToHost));
+      if (FILE *f = fopen(dbg_file, "a")) {
+        for (int i = 0; i < s->n_multi; i++) fprintf(f, "%d %d %lld %d %lld\n", s->launches, i, (long long)d[i].out_row, d[i].n_instr, t[i]);
+        fclose(f);
+      }
+    }
     s->launches++;
     s->last_grid = grid; s->last_block = wpc * 32; s->last_smem = smem; s->last_fused = false;
     for (auto &g : s->groups) if (g.in_multi) g.sub_block = mb;

@@ -669,6 +669,20 @@ DOPS_DEV void c_fixdelay(const Cx<B, T> &cx, float (&x)[B], const float (&g)[B],
     cx.last(e);
     tb = e;
     __syncwarp();
+  } else if (T > 1 && n >= 32 && tb == floor(tb) && tb >= 0.0 && tb < len) {
+    // a ring shorter than the tile (e.g. a 2.4 ms AllPass, 106 samples, under 128-sample tiles): sample j of the tile meets
+    // what sample j - n left, nothing else -- so the tile runs in ceil(T*B / n) <= 4 rounds of n independent samples
+    // instead of T serial turns (which made such circuits the tail of the W4 launch: 20 % of their instructions)
+    const int base = (int)tb + 1, j0 = cx.tl * B;
+    for (int r0 = 0; r0 < T * B; r0 += n) {
+#pragma unroll
+      for (int s = 0; s < B; s++) {
+        const int j = j0 + s;
+        if (j >= r0 && j < r0 + n) step((base + j) % n, s);
+      }
+      __syncwarp();
+    }
+    tb = (double)((base + T * B - 1) % n);
   } else {
     serial1<B, T>(cx, tb, [&] {
 #pragma unroll

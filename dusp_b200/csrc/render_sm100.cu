@@ -692,6 +692,7 @@ __global__ void __launch_bounds__(128, D > 0 ? D : (B <= 8 ? 4 : 2)) dusp_render
   }
 
   const long long n_proc = (kp.n_samples + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;  // whole chunks, like Circuit.tick
+  const long long dbg_t0 = kp.dbg_cycles ? clock64() : 0;
   float *const out_row = kp.out + row * kp.out_nch * kp.out_len;
 
 #pragma unroll 1
@@ -926,6 +927,7 @@ if (!kp.out_raw) {
       }
     }
   }
+  if (kp.dbg_cycles && lane == 0) kp.dbg_cycles[warp] = clock64() - dbg_t0;
 }
 
 template <int B, int T, int D = 0>

@@ -175,6 +175,7 @@ struct DuspKernelParams {
   const double *ctab;    // program constants built on the host with libm: FFT twiddles, window envelopes (f64)
   const DuspDevInstr *prog_global;
   const DuspWarpDesc *multi;  // non-null: n_voices descriptors, one per warp (requires T = 32)
+  long long *dbg_cycles; // diagnostics (DUSP_MULTI_DEBUG_FILE): clock64() ticks every warp of a multi launch spent, else null
   int64_t density;       // multi only: > 0 selects the register-capped instantiation (64 registers per thread, 32 circuits per SM)
   DuspDevInstr prog_inline[DUSP_INLINE_INSTR];
 };

@@ -144,6 +144,19 @@ def fixed_delays():
     return ap2
 
 
+def short_rings():
+    """Rings shorter than a 128- / 256-sample tile but not tiny (100, 40 and 106 samples): the tile runs in rounds of n
+    independent samples (ops.cuh c_fixdelay), W4's shortest AllPass / FixedDelay times."""
+    src = C.Multiply(C.Noise(), C.Shape("decay", 0.2).trigger())
+    fd = C.FixedDelay(100 / 44100)
+    fd.IN = src
+    cf = C.CombFilter(40 / 44100, 0.55)
+    cf.IN = fd
+    ap = C.AllPass(0.0024, 0.151)
+    ap.IN = cf
+    return ap
+
+
 def delay_interp():
     src = C.Multiply(C.Noise(), C.Shape("decay", 0.02).trigger())
     return C.Delay(src, quick.add(quick.multiply(C.Osc(3), 40.5), 300.25))
@@ -587,6 +600,7 @@ CASES = {
     "shape_variants": (shape_variants, 0.5, True),
     "ahd_timer": (ahd_timer, 0.2, True),
     "fixed_delays": (fixed_delays, 0.3, True),
+    "short_rings": (short_rings, 0.3, True),
     "delay_interp": (delay_interp, 0.3, True),
     "delay_short_and_mono": (delay_short_and_mono, 0.2, True),
     "readback_delay": (readback_delay, 0.2, True),

@@ -200,3 +200,48 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cc", ".cu", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "liboracle" not in text and "import oracle" not in text and "from oracle" not in text, f
+
+
+def _listing(prog):
+    """[(op, unit label, [input refs], [output refs])] of a program's disassembly."""
+    rows = []
+    for l in prog.disassemble().splitlines()[1:]:
+        t = l.split()
+        if len(t) < 3:
+            continue
+        arrow = t.index("->")
+        end = next(i for i, x in enumerate(t) if x.startswith("[p="))
+        rows.append((t[1], t[2], t[3:arrow], t[arrow + 1:end]))
+    return rows
+
+
+def test_evaluation_order_of_feed_forward_circuits(lib, monkeypatch):
+    """compile.cc re-sequences a program depth first where the tick order cannot be observed: the
+    same instructions (one per unit and channel), every slot written before it is read, far fewer slots; circuits with
+    CircleBuffers / feedback keep the reference's tick order."""
+    from dusp_b200 import workloads as W
+    for i in (0, 3, 7, 11, 19):
+        blob = circuit_blob(W.w4_circuit(i))[0]
+        new = capi.Program(blob)
+        monkeypatch.setenv("DUSP_KEEP_TICK_ORDER", "1")
+        old = capi.Program(blob)
+        monkeypatch.delenv("DUSP_KEEP_TICK_ORDER")
+        a, b = _listing(new), _listing(old)
+        assert sorted((op, u) for op, u, _, _ in a) == sorted((op, u) for op, u, _, _ in b)  # a permutation of the same ops
+        assert a[-1][0] == "out"
+        live = set()
+        for op, u, ins, outs in a:  # every slot read holds a value written earlier in the new order
+            for r in ins:
+                if r.startswith("s") and r[1:].isdigit():
+                    assert r in live, (i, op, u, r)
+            live.update(o for o in outs if o.startswith("s"))
+        n_new = int(new.disassemble().split(" slots")[0].split()[-1])
+        n_old = int(old.disassemble().split(" slots")[0].split()[-1])
+        assert n_new <= n_old and n_new <= 6, (i, n_new, n_old)
+    for fac in (W.w3_circuit, W.w3b_circuit):  # rings shared between units / a cycle edge: order kept
+        blob = circuit_blob(fac())[0]
+        new = capi.Program(blob)
+        monkeypatch.setenv("DUSP_KEEP_TICK_ORDER", "1")
+        old = capi.Program(blob)
+        monkeypatch.delenv("DUSP_KEEP_TICK_ORDER")
+        assert new.disassemble() == old.disassemble()
