@@ -160,6 +160,7 @@ bool make_plan(const Program &p, Plan &pl) {
 
 namespace {
 std::string generate(const Program &p, int VC, int STEP, PipedInfo *info, bool want_ffp = false);
+std::string generate_ffq(const Program &p, int VC, PipedInfo *info);
 }
 
 bool program_has_sequential(const Program &p) {
@@ -171,7 +172,8 @@ std::string generate_piped_source(const Program &p, int VC, PipedInfo *info, int
   if (VC < 8 || VC > 32 || VC % 8) return "";
   std::string src;
   const char *fe = getenv("DUSP_PIPED_FFP");
-  if (fe && atoi(fe) != 0) src = generate(p, VC, 128, info, true);  // "" when the circuit has no such form: the usual kernel then
+  if (fe && atoi(fe) == 2) src = generate_ffq(p, VC, info);
+  else if (fe && atoi(fe) != 0) src = generate(p, VC, 128, info, true);  // "" when the circuit has no such form: the usual kernel then
   if (!src.empty()) return fused_mode_prefix(out_mode) + src;
   if (const char *se = getenv("DUSP_PIPED_STEP")) src = generate(p, VC, atoi(se) == 128 ? 128 : 256, info);
   else {
@@ -611,6 +613,238 @@ std::string generate(const Program &p, int VC, int STEP, PipedInfo *info, bool w
   if (!p_mut.empty()) {
     s << "  __syncthreads();\n";
     for (int w : p_mut)
+      s << "  if (wib == " << pj[w] % (NP + 1) << " && lane < VC) kp.words[" << w << " * nv + v0 + lane] = pw[" << pj[w] << " * VC + lane];\n";
+  }
+  s << "}\n";
+  return s.str();
+}
+
+
+// Quarter-step form (DUSP_PIPED_FFP=2; same circuits as the ffp form above).  The feed-forward half of the biquad runs in
+// the P-warps and the S-warp issues nothing but the recurrence, as in ffp -- but only stage 0 pays for the f64 brackets'
+// size: it runs on 64-sample quarters (two voices per pass, 16 lanes along time each, 4 samples per lane) into two
+// quarter rows of brackets per voice, the S-warp follows one quarter behind and writes its f32 results into the y rows
+// of the step (the layout stage 2 reads), and stage 2 keeps whole 256-sample steps with 8 samples per lane -- where the
+// P-warps' per-step costs are (ring index arithmetic, shifted ring access, stale buffers, output).  Stage 2 of a step
+// is spread over the four quarters after its last recurrence, one of a warp's four voices per quarter (VW = 4, so
+// VC = 24 means six P-warps).  Shared memory: y rows [2 steps][VC][1 KB] + bracket rows [2 quarters][VC][512 B] + words:
+// 76.6 KB at VC = 24, three CTAs per SM like the default kernel.
+std::string generate_ffq(const Program &p, int VC, PipedInfo *info) {
+  Plan pl;
+  if (!make_plan(p, pl)) return "";
+  const int n = (int)p.code.size();
+  if (pl.n_buffers != 1 || VC % 4 != 0 || VC / 4 > 7) return "";
+  const int NP = VC / 4;
+  int ffc = -1, ff_in = -1, n1 = 0;
+  for (int i = 0; i < n; i++) if (pl.stage[i] == 1) { n1++; ffc = i; }
+  if (n1 != 1 || p.code[ffc].op != OP_FILTERC) return "";
+  {
+    const DuspInstr &F = p.code[ffc];
+    bool in_ok = false, out_ok = false;
+    for (auto &c : pl.cross) {
+      if (c.from == 0 && c.slot == F.in[0] && c.used_in[1] && !c.used_in[2]) { in_ok = true; ff_in = c.def; }
+      if (c.def == ffc && c.to == 2) out_ok = true;
+    }
+    if (!in_ok || !out_ok || pl.cross.size() != 2) return "";
+  }
+  const int P = p.code[ffc].p;  // words: a0 a1 a2 b1 b2 (derived), x1 x2 y1 y2
+  Gen g0(p, 4, 16), g2(p, 8, 32);
+  std::ostringstream pre_decl, pre_code;
+  if (!getenv("DUSP_PIPED_NOPREFETCH"))
+    for (int i = 0; i < n; i++)
+      if (pl.stage[i] == 2 && Gen::can_prefetch(p, p.code[i], 256) && p.code[i].out[0] >= 0) {
+        pre_decl << "        float pre" << i << "[B" << (p.code[i].op == OP_CBREADC ? " + 3" : "") << "];\n";
+        g2.prefetch(i, p.code[i], pre_code);
+      }
+  for (int i = 0; i < n; i++) {
+    const DuspInstr &I = p.code[i];
+    if (pl.stage[i] == 0) {
+      g0.instr(i, I);
+      if (i == ff_in) {
+        int slot = -1;
+        for (int k = 0; k < 2; k++) { auto it = pl.cross_of.find({i, k}); if (it != pl.cross_of.end()) slot = pl.cross[it->second].slot; }
+        g0.o << "      {  // feed-forward half of instruction " << ffc << " (Filter.js:40-42), 16 lanes along time per voice\n"
+             << "        const float xp1_ = __shfl_up_sync(0xffffffffu, s" << slot << "[B - 1], 1, 16), xp2_ = __shfl_up_sync(0xffffffffu, s" << slot << "[B - 2], 1, 16);\n"
+             << "        double o1_ = cx.tl ? (double)js_or0f(xp1_) : js_or0(" << g0.w(P + 5) << "), o2_ = cx.tl ? (double)js_or0f(xp2_) : js_or0(" << g0.w(P + 6) << ");\n"
+             << "        double c_[B];\n"
+             << "        filterc_ff<B>(s" << slot << ", c_, " << g0.w(P) << ", " << g0.w(P + 1) << ", " << g0.w(P + 2) << ", o1_, o2_);\n"
+             << "        " << g0.w(P + 5) << " = __shfl_sync(0xffffffffu, (double)s" << slot << "[B - 1], (lane & 16) | 15);  // x1: the raw last input\n"
+             << "        " << g0.w(P + 6) << " = __shfl_sync(0xffffffffu, o2_, (lane & 16) | 15);                         // x2: normalised\n"
+             << "        double2 *const row_ = reinterpret_cast<double2 *>(bk + ((size_t)(Q & 1) * VC + vl) * 32);\n"
+             << "        UNROLL for (int q_ = 0; q_ < B / 2; q_++) row_[((B / 2) * cx.tl + q_) ^ (vl & 7)] = make_double2(c_[2 * q_], c_[2 * q_ + 1]);\n"
+             << "      }\n";
+        g0.mut(P + 5); g0.mut(P + 6);
+      }
+    } else if (pl.stage[i] == 2) {
+      g2.instr(i, I);
+    }
+    if (pl.stage[i] == 1) {  // its value reaches stage 2 through the y rows
+      for (int k = 0; k < 2; k++) {
+        auto it = pl.cross_of.find({i, k});
+        if (it == pl.cross_of.end()) continue;
+        const Cross &c = pl.cross[it->second];
+        g2.o << "      LDX(s" << c.slot << ", " << c.buf << ")  // value of instruction " << i << " (stage 1)\n";
+      }
+    }
+  }
+  // (stage-2 code must see the crossing load BEFORE its consumers: instructions are emitted in program order and the
+  //  stage-1 op precedes every stage-2 consumer of its value, so the LDX above lands in front of them)
+  std::set<int> words0 = g0.used_words, words2 = g2.used_words, mut0 = g0.mutable_words, mut2 = g2.mutable_words, all_words, all_mut;
+  for (int w : words0) if (words2.count(w)) return "";  // a unit on both sides of the recurrence: not this form
+  all_words.insert(words0.begin(), words0.end()); all_words.insert(words2.begin(), words2.end());
+  all_mut.insert(mut0.begin(), mut0.end()); all_mut.insert(mut2.begin(), mut2.end());
+  std::map<int, int> pj;
+  for (int w : all_words) { int j = (int)pj.size(); pj[w] = j; }
+  const int NPW = (int)pj.size();
+  const size_t smem = (size_t)2 * VC * 1024 + (size_t)2 * VC * 512 + (size_t)NPW * VC * sizeof(double);
+  if (smem > 200 * 1024) return "";
+  const int NWARPS = NP + 1;
+  if (info) {
+    info->voices_per_cta = VC; info->threads = NWARPS * 32; info->smem_bytes = (int)smem; info->n_buffers = 1;
+    info->n_ops = n; info->n_ops_sequential_stage = 1;
+  }
+  int min_blocks = (int)std::min<size_t>(4, (228 * 1024) / (smem + 1024));
+  if (min_blocks < 1) min_blocks = 1;
+  if (const char *e = getenv("DUSP_PIPED_MINB")) min_blocks = std::max(1, std::min(min_blocks, atoi(e)));
+  auto W = [&](int k) { return "kp.words[" + std::to_string(P + k) + " * nv + v]"; };
+
+  std::ostringstream s;
+  s << "// generated by libdusp_b200 (piped.cc, quarter-step form) -- pipelined render kernel for one circuit shape\n// stages:";
+  for (int i = 0; i < n; i++) s << " " << i << ":" << op_name(p.code[i].op) << "=" << pl.stage[i];
+  s << "\n" << fused_prelude()
+    << "#define LDX(d, b) { UNROLL for (int q_ = 0; q_ < B / 4; q_++) { const float4 t_ = xs[q_ * 32];\\\n"
+    << "    d[4*q_] = t_.x; d[4*q_+1] = t_.y; d[4*q_+2] = t_.z; d[4*q_+3] = t_.w; } }\n"
+    << "#define OUT_CHANNEL(a, CH) { if (!KP_OUT_RAW) { UNROLL for (int i_ = 0; i_ < B; i_++) a[i_] = js_or0f(a[i_]); }\\\n"
+    << "  if (KP_OUT_MODE == 0) { if (active) { float *dst = out_row + (long long)(CH) * kp.out_len + tl0;\\\n"
+    << "      if (tl0 + B <= kp.n_samples && ((kp.out_len & 3) | (reinterpret_cast<unsigned long long>(kp.out) & 15ull)) == 0) { UNROLL for (int q_ = 0; q_ < B / 4; q_++)\\\n"
+    << "        __stcs(reinterpret_cast<float4 *>(dst) + q_, make_float4(a[4*q_], a[4*q_+1], a[4*q_+2], a[4*q_+3])); }\\\n"
+    << "      else { UNROLL for (int i_ = 0; i_ < B; i_++) if (tl0 + i_ < kp.n_samples) dst[i_] = a[i_]; } } }\\\n"
+    << "  else if ((CH) < 2 && active) { UNROLL for (int i_ = 0; i_ < B; i_++) macc[CH][i_] += a[i_]; } }\n"
+    << "extern \"C\" __global__ void __launch_bounds__(" << NWARPS * 32 << ", " << min_blocks << ") dusp_piped(const __grid_constant__ FusedParams kp) {\n"
+    << "  constexpr int VC = " << VC << ", NP = " << NP << ", VW = 4, STEP = 256, ROW = 64;\n"
+    << "  extern __shared__ float4 smem4[];\n"
+    << "  float4 *const yb = smem4;                    // [2 steps][VC][64] float4: the recurrences' results, stage 2's layout (swizzled)\n"
+    << "  float4 *const bk = yb + 2 * VC * ROW;        // [2 quarters][VC][32] float4: f64 brackets of 64 samples (swizzled)\n"
+    << "  double *const pw = reinterpret_cast<double *>(bk + 2 * VC * 32);  // [" << NPW << "][VC] words of the P-warps' units\n"
+    << "  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;\n"
+    << "  const long long v0 = (long long)blockIdx.x * VC;  // allocations are padded to a multiple of 96 voices\n"
+    << "  const size_t nv = (size_t)kp.nv_stride;\n"
+    << "  const float *const tables = kp.tables; (void)tables;\n"
+    << "  const long long n_proc = (kp.n_samples + DUSP_CHUNK - 1) / DUSP_CHUNK * DUSP_CHUNK;  // whole chunks, like Circuit.tick\n"
+    << "  const int NQ = (int)(n_proc / 64);  // quarters; the loop runs 5 more: recurrence one behind, stage 2 five behind\n";
+  for (auto &kv : pj)
+    s << "  if (wib == " << kv.second % (NP + 1) << " && lane < VC) pw[" << kv.second << " * VC + lane] = kp.words[" << kv.first << " * nv + v0 + lane];  // "
+      << p.words[kv.first].name << "\n";
+  s << "  __syncthreads();\n"
+    << "  if (wib < NP) {\n"
+    << "    // ---------------- P-warps\n"
+    << "    float macc[2][8]; UNROLL for (int i_ = 0; i_ < 8; i_++) { macc[0][i_] = 0.0f; macc[1][i_] = 0.0f; }\n"
+    << "    constexpr int B = 8, T = 32;\n"
+    << pre_decl.str()   // stage 2's early loads are issued ONE QUARTER AHEAD (end of the previous pass) and live across the barrier
+    << "    _Pragma(\"unroll 1\")\n"
+    << "    for (int Q = 0; Q < NQ + 5; Q++) {\n"
+    << "      const bool do0 = Q < NQ, do2 = Q >= 5;\n"
+    << "      const int stp2_ = (Q - 5) >> 2;  // the step stage 2 works on, one voice of this warp per quarter\n"
+    << "      {\n"
+    << "        Cx<B, T> cx; cx.tl = lane; cx.lane = lane;\n"
+    << "        const int vl = wib * VW + ((Q - 5) & 3);\n"
+    << "        const long long v = v0 + vl;\n"
+    << "        const bool active = v < kp.n_voices;\n"
+    << "        float *const rings = kp.rings + v * kp.ring_stride;\n"
+    << "        float *const stale = kp.stale + v * (long long)kp.n_stale * DUSP_CHUNK;\n"
+    << "        float *const out_row = kp.out + (long long)(kp.voice0 + v) * kp.out_nch * kp.out_len;\n"
+    << "        (void)rings; (void)stale; (void)out_row; (void)active; (void)cx;\n"
+    << "        const long long tl0 = (long long)stp2_ * STEP + lane * B;\n"
+    << "        const int cpos = (int)(tl0 & (DUSP_CHUNK - 1)); (void)cpos;\n"
+    << "        float4 *const xs = yb + ((size_t)(stp2_ & 1) * VC + vl) * ROW + (lane ^ (vl & 7)); (void)xs;\n";
+  for (int w : words2) s << "        double w" << w << " = pw[" << pj[w] << " * VC + vl];\n";
+  s << "        if (do2) {  // ---- stage 2 of step stp2_, voice vl (its early loads were issued in the previous pass)\n";
+  for (int k = 0; k < p.n_slots; k++) s << "          float s" << k << "[B];\n";
+  s << g2.o.str();
+  if (!mut2.empty()) {
+    s << "          __syncwarp();\n          if (lane == 0) {\n";
+    for (int w : mut2) s << "            pw[" << pj[w] << " * VC + vl] = w" << w << ";\n";
+    s << "          }\n          __syncwarp();\n";
+  }
+  s << "          if (KP_OUT_MODE != 0 && ((Q - 5) & 3) == 3) {  // stereo mixdown of this warp's four voices of step stp2_\n"
+    << "            const long long t2 = (long long)stp2_ * STEP + lane * B;\n"
+    << "            mix_add<B>(kp.out + t2, macc[0], kp.n_samples - t2);\n"
+    << "            if (kp.prog_nch == 1) mix_add<B>(kp.out + kp.out_len + t2, macc[0], kp.n_samples - t2);\n"
+    << "            else mix_add<B>(kp.out + kp.out_len + t2, macc[1], kp.n_samples - t2);\n"
+    << "            UNROLL for (int i_ = 0; i_ < B; i_++) { macc[0][i_] = 0.0f; macc[1][i_] = 0.0f; }\n"
+    << "          }\n"
+    << "        }\n"
+    << "        if (Q >= 4 && Q < NQ + 4) {  // ---- early loads of the NEXT pass's stage 2 (voice (Q - 4) & 3, step (Q - 4) >> 2):\n"
+    << "          // its stale buffers and ring positions were last written four passes ago\n"
+    << "          const int vl = wib * VW + ((Q - 4) & 3);\n"
+    << "          const long long v = v0 + vl;\n"
+    << "          float *const rings = kp.rings + v * kp.ring_stride;\n"
+    << "          float *const stale = kp.stale + v * (long long)kp.n_stale * DUSP_CHUNK;\n"
+    << "          const int cpos = (int)(((long long)((Q - 4) >> 2) * STEP + lane * B) & (DUSP_CHUNK - 1));\n"
+    << "          (void)rings; (void)stale; (void)cpos;\n";
+  for (int w : words2) s << "          const double w" << w << " = pw[" << pj[w] << " * VC + vl]; (void)w" << w << ";\n";
+  s << pre_code.str()
+    << "        }\n"
+    << "        if (do0) {  // ---- stage 0 of quarter Q: this warp's four voices, two per pass\n"
+    << "          _Pragma(\"unroll 1\")\n"
+    << "          for (int ps_ = 0; ps_ < 2; ps_++) {\n"
+    << "            constexpr int B = 4, T = 16;\n"
+    << "            Cx<B, T> cx; cx.tl = lane & 15; cx.lane = lane;\n"
+    << "            const int vl = wib * VW + ps_ * 2 + (lane >> 4);\n"
+    << "            const long long v = v0 + vl;\n"
+    << "            const bool active = v < kp.n_voices;\n"
+    << "            float *const rings = kp.rings + v * kp.ring_stride;\n"
+    << "            float *const stale = kp.stale + v * (long long)kp.n_stale * DUSP_CHUNK;\n"
+    << "            (void)rings; (void)stale; (void)active;\n"
+    << "            const long long tl0 = (long long)Q * 64 + cx.tl * B;\n"
+    << "            const int cpos = (int)(tl0 & (DUSP_CHUNK - 1)); (void)cpos;\n";
+  for (int w : words0) s << "            double w" << w << " = pw[" << pj[w] << " * VC + vl];\n";
+  for (int k = 0; k < p.n_slots; k++) s << "            float s" << k << "[B];\n";
+  s << g0.o.str();
+  if (!mut0.empty()) {
+    s << "            __syncwarp();\n            if (cx.tl == 0) {\n";
+    for (int w : mut0) s << "              pw[" << pj[w] << " * VC + vl] = w" << w << ";\n";
+    s << "            }\n            __syncwarp();\n";
+  }
+  s << "          }\n"
+    << "        }\n"
+;
+  s     << "      }\n"
+    << "      __syncthreads();\n"
+    << "    }\n"
+    << "  } else {\n"
+    << "    // ---------------- S-warp: one voice per lane, nothing but the recurrence  y = c - b1 y1 - b2 y2  (Filter.js:40-48)\n"
+    << "    const int vl = lane < VC ? lane : VC - 1;\n"
+    << "    const long long v = v0 + vl;\n"
+    << "    const double b1 = " << W(3) << ", b2 = " << W(4) << ";\n"
+    << "    double q1 = js_or0(" << W(7) << "), q2 = js_or0(" << W(8) << ");\n"
+    << "    float ylast = (float)" << W(7) << ";\n"
+    << "    const int k_ = vl & 7;\n"
+    << "    _Pragma(\"unroll 1\")\n"
+    << "    for (int Q = 0; Q < NQ + 5; Q++) {\n"
+    << "      if (Q >= 1 && Q <= NQ && lane < VC) {\n"
+    << "        const int qs = Q - 1;  // the quarter the P-warps filled in the previous pass\n"
+    << "        const double2 *const rowd = reinterpret_cast<const double2 *>(bk + ((size_t)(qs & 1) * VC + vl) * 32);\n"
+    << "        float4 *const yrow = yb + ((size_t)((qs >> 2) & 1) * VC + vl) * ROW;\n"
+    << "        _Pragma(\"unroll 1\")\n"
+    << "        for (int g = 0; g < 8; g++) {\n"
+    << "          double c[8];\n"
+    << "          UNROLL for (int q_ = 0; q_ < 4; q_++) { const double2 t_ = rowd[(4 * g + q_) ^ k_]; c[2 * q_] = t_.x; c[2 * q_ + 1] = t_.y; }\n"
+    << "          float y[8];\n"
+    << "          filterc_rec<8, false>(c, y, b1, b2, q1, q2);\n"
+    << "          ylast = y[7];\n"
+    << "          const int l_ = (qs & 3) * 8 + g;  // the stage-2 lane that owns these eight samples\n"
+    << "          yrow[l_ ^ k_] = make_float4(y[0], y[1], y[2], y[3]);\n"
+    << "          yrow[32 + (l_ ^ k_)] = make_float4(y[4], y[5], y[6], y[7]);\n"
+    << "        }\n"
+    << "      }\n"
+    << "      __syncthreads();\n"
+    << "    }\n"
+    << "    if (lane < VC) { " << W(7) << " = (double)ylast; " << W(8) << " = q2; }\n"
+    << "  }\n";
+  if (!all_mut.empty()) {
+    s << "  __syncthreads();\n";
+    for (int w : all_mut)
       s << "  if (wib == " << pj[w] % (NP + 1) << " && lane < VC) kp.words[" << w << " * nv + v0 + lane] = pw[" << pj[w] << " * VC + lane];\n";
   }
   s << "}\n";

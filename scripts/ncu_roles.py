@@ -13,6 +13,7 @@ for i, l in enumerate(src, 1):
     if "P-warps: lanes along time" in l: marks["P"] = i
     if "S-warp: one voice per lane" in l: marks["S"] = i
     if "F-warp: one voice per lane" in l: marks["F"] = i
+    if "---------------- P-warps" in l and "P" not in marks: marks["P"] = i
 order = sorted(marks.items(), key=lambda kv: kv[1])
 
 
