@@ -32,7 +32,7 @@ SYMBOLS = [
     "dusp_session_adopt", "dusp_program_warmup_ticks",
     "dusp_mix_acc_create", "dusp_mix_acc_open", "dusp_mix_acc_close", "dusp_mix_acc_clear", "dusp_mix_push", "dusp_mix_wait",
     "dusp_mix_push_static",
-    "dusp_session_clock", "dusp_run_create", "dusp_run_destroy", "dusp_run_num_voices", "dusp_run_num_channels",
+    "dusp_session_clock", "dusp_session_state_size", "dusp_session_state_export", "dusp_session_state_import", "dusp_run_create", "dusp_run_destroy", "dusp_run_num_voices", "dusp_run_num_channels",
     "dusp_run_channels_rendered", "dusp_run_position", "dusp_run_session", "dusp_run_program", "dusp_run_num_epochs",
     "dusp_run_epoch_program", "dusp_run_set_params", "dusp_run_render",
 ]
@@ -97,6 +97,9 @@ def load():
     L.dusp_mix_push_static.argtypes = [c.c_int, c.c_void_p, c.c_void_p, c.c_size_t, c.c_void_p, c.c_void_p]
     L.dusp_session_clock.argtypes = [c.c_void_p]
     L.dusp_session_clock.restype = c.c_longlong
+    L.dusp_session_state_size.argtypes = [c.c_void_p, c.POINTER(c.c_size_t)]
+    L.dusp_session_state_export.argtypes = [c.c_void_p, c.c_void_p, c.c_size_t, c.c_void_p]
+    L.dusp_session_state_import.argtypes = [c.c_void_p, c.c_void_p, c.c_size_t, c.c_void_p]
     L.dusp_run_create.argtypes = [c.POINTER(c.c_char_p), c.POINTER(c.c_size_t), c.POINTER(c.c_int), c.c_int, c.c_int, c.POINTER(c.c_void_p)]
     L.dusp_run_destroy.argtypes = [c.c_void_p]
     L.dusp_run_destroy.restype = None
@@ -227,6 +230,22 @@ class Session:
         vals = np.ascontiguousarray(values, dtype=np.float64)
         check(L.dusp_session_set_params(self._h, program_index, ids, len(names),
                                         vals.ctypes.data_as(ctypes.POINTER(ctypes.c_double))))
+
+    def export_state(self, stream=None):
+        """The session's state block (clock, words, rings, stale chunks) as a numpy uint8 array: checkpoint."""
+        import numpy as np
+        L = load()
+        n = ctypes.c_size_t(0)
+        check(L.dusp_session_state_size(self._h, ctypes.byref(n)))
+        buf = np.empty(n.value, dtype=np.uint8)
+        check(L.dusp_session_state_export(self._h, buf.ctypes.data_as(ctypes.c_void_p), n.value, stream))
+        return buf
+
+    def import_state(self, block, stream=None):
+        """Resume from a block exported by a session of the same programs and voice counts."""
+        import numpy as np
+        block = np.ascontiguousarray(block, dtype=np.uint8)
+        check(load().dusp_session_state_import(self._h, block.ctypes.data_as(ctypes.c_void_p), block.size, stream))
 
     def reset(self):
         check(load().dusp_session_reset(self._h))

@@ -583,6 +583,101 @@ int dusp_session_reset(dusp_session *s) {
   return DUSP_OK;
 }
 
+// Groups that were (re)created, reset or re-parameterised since their last render: initial words up, rings and stale
+// chunks cleared -- on the stream, right before the first kernel that needs them.
+static int upload_initial_state(dusp_session *s, cudaStream_t st) {
+  bool all_dirty = true, any_dirty = false;
+  for (auto &g : s->groups) { all_dirty = all_dirty && g.dirty; any_dirty = any_dirty || g.dirty; }
+  if (all_dirty && s->groups.size() > 1) {  // one upload + two memsets for the whole session
+    s->h_all.resize(s->words_total);
+    for (auto &g : s->groups) { std::copy(g.h_words.begin(), g.h_words.end(), s->h_all.begin() + g.off_words); g.dirty = false; }
+    CUDA_TRY(cudaMemcpyAsync(s->d_words_pool, s->h_all.data(), s->words_total * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemsetAsync(s->d_rings_pool, 0, s->rings_total * sizeof(float), st));
+    CUDA_TRY(cudaMemsetAsync(s->d_stale_pool, 0, s->stale_total * sizeof(float), st));
+  } else if (any_dirty) {
+    for (auto &g : s->groups) {
+      if (!g.dirty) continue;
+      CUDA_TRY(cudaMemcpyAsync(g.d_words, g.h_words.data(), g.h_words.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+      CUDA_TRY(cudaMemsetAsync(g.d_rings, 0, (size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad * sizeof(float), st));
+      CUDA_TRY(cudaMemsetAsync(g.d_stale, 0, (size_t)std::max(g.prog.n_stale, 1) * DUSP_CHUNK * g.nv_pad * sizeof(float), st));
+      g.dirty = false;
+    }
+  }
+  return DUSP_OK;
+}
+
+// ---- state block (include/dusp_b200.h): header, then per group words | rings | stale
+namespace {
+struct StateHeader { char magic[8]; long long clock, n_groups; };
+struct StateShape { long long words, rings, stale, voices; };  // element counts of one group (padded) and its voices
+StateShape state_shape(const Group &g) {
+  return {(long long)g.h_words.size(), std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad,
+          (long long)std::max(g.prog.n_stale, 1) * DUSP_CHUNK * g.nv_pad, (long long)g.n_voices};
+}
+size_t state_bytes(const dusp_session *s) {
+  size_t n = sizeof(StateHeader) + s->groups.size() * sizeof(StateShape);
+  for (auto &g : s->groups) { const StateShape h = state_shape(g); n += (size_t)h.words * sizeof(double) + (size_t)(h.rings + h.stale) * sizeof(float); }
+  return n;
+}
+}  // namespace
+
+int dusp_session_state_size(const dusp_session *s, size_t *bytes) {
+  if (!s || !bytes) return fail(DUSP_EINVAL, "dusp_session_state_size: null argument");
+  *bytes = state_bytes(s);
+  return DUSP_OK;
+}
+
+int dusp_session_state_export(dusp_session *s, void *host_block, size_t bytes, void *cuda_stream) {
+  if (!s || !host_block) return fail(DUSP_EINVAL, "dusp_session_state_export: null argument");
+  if (bytes < state_bytes(s)) return fail(DUSP_EINVAL, "dusp_session_state_export: the buffer is smaller than dusp_session_state_size says");
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  CUDA_TRY(cudaSetDevice(s->device));
+  if (int e = upload_initial_state(s, st)) return e;  // a session that has not rendered yet exports its initial state
+  char *p = static_cast<char *>(host_block);
+  StateHeader h;
+  memcpy(h.magic, "DUSPST01", 8);
+  h.clock = s->clock; h.n_groups = (long long)s->groups.size();
+  memcpy(p, &h, sizeof h); p += sizeof h;
+  for (auto &g : s->groups) { const StateShape sh = state_shape(g); memcpy(p, &sh, sizeof sh); p += sizeof sh; }
+  for (auto &g : s->groups) {
+    const StateShape sh = state_shape(g);
+    CUDA_TRY(cudaMemcpyAsync(p, g.d_words, (size_t)sh.words * sizeof(double), cudaMemcpyDeviceToHost, st)); p += (size_t)sh.words * sizeof(double);
+    CUDA_TRY(cudaMemcpyAsync(p, g.d_rings, (size_t)sh.rings * sizeof(float), cudaMemcpyDeviceToHost, st)); p += (size_t)sh.rings * sizeof(float);
+    CUDA_TRY(cudaMemcpyAsync(p, g.d_stale, (size_t)sh.stale * sizeof(float), cudaMemcpyDeviceToHost, st)); p += (size_t)sh.stale * sizeof(float);
+  }
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return DUSP_OK;
+}
+
+int dusp_session_state_import(dusp_session *s, const void *host_block, size_t bytes, void *cuda_stream) {
+  if (!s || !host_block) return fail(DUSP_EINVAL, "dusp_session_state_import: null argument");
+  if (bytes < state_bytes(s)) return fail(DUSP_EINVAL, "dusp_session_state_import: the block is smaller than this session's state");
+  const char *p = static_cast<const char *>(host_block);
+  StateHeader h;
+  memcpy(&h, p, sizeof h); p += sizeof h;
+  if (memcmp(h.magic, "DUSPST01", 8) != 0) return fail(DUSP_EINVAL, "dusp_session_state_import: not a state block");
+  if (h.n_groups != (long long)s->groups.size() || h.clock < 0 || h.clock % DUSP_CHUNK != 0)
+    return fail(DUSP_EINVAL, "dusp_session_state_import: the block comes from a session of another shape");
+  for (auto &g : s->groups) {
+    StateShape sh, want = state_shape(g);
+    memcpy(&sh, p, sizeof sh); p += sizeof sh;
+    if (sh.words != want.words || sh.rings != want.rings || sh.stale != want.stale || sh.voices != want.voices)
+      return fail(DUSP_EINVAL, "dusp_session_state_import: the block comes from a session of another shape (programs or voice counts differ)");
+  }
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  CUDA_TRY(cudaSetDevice(s->device));
+  for (auto &g : s->groups) {
+    const StateShape sh = state_shape(g);
+    CUDA_TRY(cudaMemcpyAsync(g.d_words, p, (size_t)sh.words * sizeof(double), cudaMemcpyHostToDevice, st)); p += (size_t)sh.words * sizeof(double);
+    CUDA_TRY(cudaMemcpyAsync(g.d_rings, p, (size_t)sh.rings * sizeof(float), cudaMemcpyHostToDevice, st)); p += (size_t)sh.rings * sizeof(float);
+    CUDA_TRY(cudaMemcpyAsync(g.d_stale, p, (size_t)sh.stale * sizeof(float), cudaMemcpyHostToDevice, st)); p += (size_t)sh.stale * sizeof(float);
+    g.dirty = false;
+  }
+  CUDA_TRY(cudaStreamSynchronize(st));  // the caller's buffer is pageable in general: done with it on return
+  s->clock = h.clock;
+  return DUSP_OK;
+}
+
 // Enqueue the kernels that render the next `n` samples of every group into d_out on stream `st`.  Rows of d_out
 // are `pitch` floats apart (>= n); per-voice output has `nch` channel rows per voice (>= the session's own count:
 // a run whose later epochs have more channels, run.cc).
@@ -597,25 +692,7 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
     if (pitch == n) CUDA_TRY(cudaMemsetAsync(d_out, 0, out_rows * (size_t)n * sizeof(float), st));
     else CUDA_TRY(cudaMemset2DAsync(d_out, (size_t)pitch * sizeof(float), 0, (size_t)n * sizeof(float), out_rows, st));
   }
-  {
-    bool all_dirty = true, any_dirty = false;
-    for (auto &g : s->groups) { all_dirty = all_dirty && g.dirty; any_dirty = any_dirty || g.dirty; }
-    if (all_dirty && s->groups.size() > 1) {  // one upload + two memsets for the whole session
-      s->h_all.resize(s->words_total);
-      for (auto &g : s->groups) { std::copy(g.h_words.begin(), g.h_words.end(), s->h_all.begin() + g.off_words); g.dirty = false; }
-      CUDA_TRY(cudaMemcpyAsync(s->d_words_pool, s->h_all.data(), s->words_total * sizeof(double), cudaMemcpyHostToDevice, st));
-      CUDA_TRY(cudaMemsetAsync(s->d_rings_pool, 0, s->rings_total * sizeof(float), st));
-      CUDA_TRY(cudaMemsetAsync(s->d_stale_pool, 0, s->stale_total * sizeof(float), st));
-    } else if (any_dirty) {
-      for (auto &g : s->groups) {
-        if (!g.dirty) continue;
-        CUDA_TRY(cudaMemcpyAsync(g.d_words, g.h_words.data(), g.h_words.size() * sizeof(double), cudaMemcpyHostToDevice, st));
-        CUDA_TRY(cudaMemsetAsync(g.d_rings, 0, (size_t)std::max<long long>(g.prog.ring_floats, 4) * g.nv_pad * sizeof(float), st));
-        CUDA_TRY(cudaMemsetAsync(g.d_stale, 0, (size_t)std::max(g.prog.n_stale, 1) * DUSP_CHUNK * g.nv_pad * sizeof(float), st));
-        g.dirty = false;
-      }
-    }
-  }
+  if (int e = upload_initial_state(s, st)) return e;
   if (s->n_multi) {  // every one-voice-per-warp interpreter group in one launch
     DuspKernelParams kp;
     memset(&kp, 0, sizeof kp);

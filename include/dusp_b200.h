@@ -154,6 +154,21 @@ int dusp_session_render(dusp_session *s, long long n_samples, int out_mode, floa
 
 long long dusp_session_clock(const dusp_session *s); /* samples ticked so far (whole chunks, like Circuit.clock) */
 
+/* ---- state block: checkpoint / resume ----------------------------------------
+ * Replaces: nothing the reference offers as a feature -- its state is the live objects themselves: `circuit.clock`
+ * (Circuit.js:8,39) and every unit's own fields (Osc.phase, Filter.x1..y2, the CircleBuffers' channelData, ...), which
+ * is why a render can be continued only on the same objects ("checkpoint / resume").  Here that
+ * state is device arrays, so it can be taken out and put back: the clock, every voice's words (parameters + unit
+ * state), rings and stale chunks of every program group.  A block can be imported into any session created from the
+ * same programs with the same voice counts (the header carries the shapes and the call checks them); the render then
+ * continues bit for bit.  Runs (dusp_run_*) keep their timeline position themselves and are not covered.
+ *   dusp_session_state_size    -- bytes a block of this session takes
+ *   dusp_session_state_export  -- block -> caller's HOST buffer of at least that size (synchronises `cuda_stream`)
+ *   dusp_session_state_import  -- HOST buffer -> session (enqueued on `cuda_stream`, the buffer may be reused on return) */
+int dusp_session_state_size(const dusp_session *s, size_t *bytes);
+int dusp_session_state_export(dusp_session *s, void *host_block, size_t bytes, void *cuda_stream);
+int dusp_session_state_import(dusp_session *s, const void *host_block, size_t bytes, void *cuda_stream);
+
 /* ---- runs: a render driven through the circuits' timelines -----------------
  * Replaces: the whole `for t0 ... await circuit.tickUntil(t1)` loop of renderChannelData.js:29-45 INCLUDING what
  * Circuit.tick does before each chunk -- runEvents (Circuit.js:23,57-65; Event.js:18-30): triggers / state

@@ -239,6 +239,41 @@ def test_set_params_after_a_render_needs_a_reset(lib):
     assert np.array_equal(a[:2], b[:2]) and np.array_equal(b[:2], b[2:])
 
 
+def test_state_block_checkpoint_and_resume(lib, kernel_mode):
+    """dusp_session_state_export / _import (include/dusp_b200.h): a render continued in a NEW session from an exported
+    block is bit for bit the render that never stopped -- words (phases, biquad memory, ring heads, noise draw
+    counters), rings and stale chunks all travel.  Two program groups (feedback delay voices and FM voices); a block
+    from a session of another shape is refused."""
+    blob3, _ = circuit_blob(circuits.w3_voice())
+    blob2, _ = circuit_blob(circuits.w2_live())
+    progs = [capi.Program(blob3), capi.Program(blob2)]
+    n = 3 * 256 * 7 + 100  # not chunk-aligned at the end: the clock runs in whole chunks (Circuit.js:38)
+    whole = capi.Session(progs, [3, 2], 0)
+    a1 = whole.render_host(256 * 9)
+    a2 = whole.render_host(n)
+    first = capi.Session(progs, [3, 2], 0)
+    b1 = first.render_host(256 * 9)
+    block = first.export_state()
+    clock = first.clock
+    first.close()
+    second = capi.Session(progs, [3, 2], 0)
+    second.import_state(block)
+    assert second.clock == clock == whole.clock - (n + 255) // 256 * 256
+    b2 = second.render_host(n)
+    assert np.array_equal(a1, b1) and np.array_equal(a2, b2)
+    fresh = capi.Session(progs, [3, 2], 0)   # a session that never rendered exports its initial state
+    third = capi.Session(progs, [3, 2], 0)
+    third.import_state(fresh.export_state())
+    assert np.array_equal(third.render_host(256 * 9), a1)
+    other = capi.Session(progs, [2, 2], 0)
+    with pytest.raises(d.DuspError, match="another shape"):
+        other.import_state(block)
+    with pytest.raises(d.DuspError, match="not a state block"):
+        other.import_state(np.zeros(other.export_state().size, dtype=np.uint8))
+    for x in (whole, second, fresh, third, other):
+        x.close()
+
+
 def test_multi_program_session(lib, oracle, kernel_mode):
     cases = ["w2_live", "w3_voice", "fixed_delays", "stereo_concat"]
     blobs = [circuit_blob(circuits.CASES[c][0]())[0] for c in cases]
