@@ -95,6 +95,13 @@ struct Group {
   bool dirty = true;  // device words/rings need (re)initialisation
   size_t off_words = 0, off_rings = 0, off_stale = 0;  // this group's segments of the session pools (elements)
   bool in_multi = false;  // rendered by the session's one multi-program interpreter launch
+  // segmented rendering (ops.cuh "segments of one voice's timeline on different warps"): small batches of circuits whose
+  // stateful units can all be put at an arbitrary sample -- a launch's timeline is cut into up to seg_max pieces per voice
+  int seg_max = 0, seg_nosc = 0, seg_wps = 0;
+  FusedKernel *seg_scan = nullptr;
+  FusedKernel *seg_render[3] = {nullptr, nullptr, nullptr};  // per output mode, built on first use
+  double *d_seg_totals = nullptr;  // [n_voices][seg_max][max(seg_nosc, 1)]
+  int *d_seg_flags = nullptr;      // [n_voices]
 };
 
 }  // namespace
@@ -184,7 +191,7 @@ void dusp_session_destroy(dusp_session *s) {
   cudaFree(s->d_words_pool); cudaFree(s->d_rings_pool); cudaFree(s->d_stale_pool); cudaFree(s->d_ringtab_pool);
   cudaFree(s->d_code_pool); cudaFree(s->d_multi); cudaFree(s->d_dbg);
   cudaFree(s->d_tables); cudaFree(s->d_sm_slots);
-  for (auto &g : s->groups) cudaFree(g.d_ctab);
+  for (auto &g : s->groups) { cudaFree(g.d_ctab); cudaFree(g.d_seg_totals); cudaFree(g.d_seg_flags); }
   for (int i = 0; i < 2; i++) {
     cudaFree(s->d_staging[i]);
     if (s->ev_rendered[i]) cudaEventDestroy(s->ev_rendered[i]);
@@ -296,6 +303,23 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
         if (!g.fused && fe) return fail(DUSP_ECUDA, "circuit specialisation failed: " + err);
         if (!g.fused) s->warning = "circuit specialisation unavailable, using the interpreter: " + err;
         if (g.fused) { g.fused_wps = wps; g.sub_block = B; g.time_lanes = T; g.warps_per_cta = 1; }
+        // a batch too small to fill the GPU with one warp per voice: several warps per voice, along time
+        if (g.fused && B == 8 && T == 32 && !getenv("DUSP_NO_SEGMENTS")) {
+          // about 48 warps per SM in total: two waves of the 24 resident ones (measured on W2, 1 000 voices x 10 s: 2.85 ms at
+          // 8 segments, 3.09 at 3, 3.32 in one piece; 100 voices: 0.33 ms at 35 segments against 2.93)
+          int smax = (int)std::min<long long>(64, (148 * 48) / std::max<long long>(n_warps, 1));
+          if (const char *se = getenv("DUSP_SEGMENTS")) smax = std::max(1, std::min(64, atoi(se)));
+          std::string scan_src, render_src;
+          if (smax >= 2 && generate_segmented_sources(g.prog, 1, 0, scan_src, render_src, &g.seg_nosc)) {
+            g.seg_wps = (int)std::min<long long>(24, std::max<long long>(8, (n_warps * smax + 147) / 148));
+            generate_segmented_sources(g.prog, g.seg_wps, 0, scan_src, render_src, &g.seg_nosc);
+            std::string e2;
+            g.seg_scan = fused_build(scan_src, "dusp_fused_scan", e2);
+            if (g.seg_scan) g.seg_render[0] = fused_build(render_src, "dusp_fused", e2);
+            if (g.seg_scan && g.seg_render[0]) g.seg_max = smax;
+            else s->warning = "segmented kernels unavailable: " + e2;
+          }
+        }
       }
       if (!g.fused) {
         if ((size_t)g.prog.n_slots * B * 128 > 200 * 1024 && T == 1 && !chunky) B = 8;
@@ -343,6 +367,11 @@ int dusp_session_create(const dusp_program *const *programs, const int *voices, 
       std::copy(g.prog.rings.begin(), g.prog.rings.end(), h_rt.begin() + off_rt[i]);
       std::copy(g.dev_code.begin(), g.dev_code.end(), h_code.begin() + off_code[i]);
     }
+    for (auto &g : s->groups)
+      if (g.seg_max >= 2) {
+        CUDA_TRY(cudaMalloc(&g.d_seg_totals, (size_t)g.n_voices * g.seg_max * std::max(g.seg_nosc, 1) * sizeof(double)));
+        CUDA_TRY(cudaMalloc(&g.d_seg_flags, (size_t)g.n_voices * sizeof(int)));
+      }
     for (auto &g : s->groups)
       if (!g.prog.ctab.empty()) {
         CUDA_TRY(cudaMalloc(&g.d_ctab, g.prog.ctab.size() * sizeof(double)));
@@ -795,8 +824,27 @@ static int enqueue_block(dusp_session *s, long long n, int out_mode, float *d_ou
       } else {
         const int V = 32 / g.time_lanes;
         const int n_warps = (g.n_voices + V - 1) / V;
-        grid = (n_warps + wpc - 1) / wpc;
-        if (fused_launch(kernel, fp, grid, wpc * 32, 0, st, err) != 0) return fail(DUSP_ECUDA, err);
+        const long long n_tiles = (n + DUSP_CHUNK - 1) / DUSP_CHUNK;
+        long long seg_tiles = g.seg_max >= 2 ? (n_tiles + g.seg_max - 1) / g.seg_max : n_tiles;
+        const int seg_n = (int)((n_tiles + seg_tiles - 1) / std::max<long long>(seg_tiles, 1));
+        if (g.seg_max >= 2 && seg_n >= 2) {  // a voice's timeline of this launch on seg_n warps
+          const int m = raw ? 2 : out_mode == DUSP_OUT_MIX ? 1 : 0;
+          if (!g.seg_render[m]) {
+            std::string scan_src, render_src;
+            generate_segmented_sources(g.prog, g.seg_wps, m, scan_src, render_src, &g.seg_nosc);
+            g.seg_render[m] = fused_build(render_src, "dusp_fused", err);
+            if (!g.seg_render[m]) return fail(DUSP_ECUDA, "segmented kernel for this output mode failed: " + err);
+          }
+          fp.seg_totals = g.d_seg_totals; fp.seg_flags = g.d_seg_flags; fp.seg_tiles = seg_tiles; fp.seg_n = seg_n;
+          CUDA_TRY(cudaMemsetAsync(g.d_seg_flags, 0, (size_t)g.n_voices * sizeof(int), st));
+          grid = g.n_voices * seg_n;
+          if (fused_launch(g.seg_scan, fp, grid, 32, 0, st, err) != 0) return fail(DUSP_ECUDA, err);
+          if (fused_launch(g.seg_render[m], fp, grid, 32, 0, st, err) != 0) return fail(DUSP_ECUDA, err);
+          s->launches++;  // (the scan; the render is counted below)
+        } else {
+          grid = (n_warps + wpc - 1) / wpc;
+          if (fused_launch(kernel, fp, grid, wpc * 32, 0, st, err) != 0) return fail(DUSP_ECUDA, err);
+        }
       }
     } else {
       int e = dusp_launch_render(&kp, g.sub_block, g.time_lanes, wpc, st, &grid, &smem);
@@ -895,6 +943,13 @@ size_t dusp_program_specialise(const dusp_program *p, int sub_block, int time_la
   if (pe && atoi(pe) != 0) {  // the pipelined kernel instead (time_lanes is then the voices per CTA)
     PipedInfo info;
     n = piped_compile_only(p->prog, time_lanes, &info, err, &src);
+  } else if (getenv("DUSP_SPECIALISE_SEGMENTED")) {  // the two segmented kernels (build checks): scan, then render
+    std::string scan_src, render_src;
+    int nosc = 0;
+    if (!generate_segmented_sources(p->prog, wps, 0, scan_src, render_src, &nosc)) { fail(DUSP_EUNSUPPORTED, "the circuit has no segmented form"); return 0; }
+    n = fused_build_cubin(scan_src, err);
+    if (n) n = fused_build_cubin(render_src, err);
+    src = scan_src + "\n// ======== render ========\n" + render_src;
   } else {
     n = fused_compile_only(p->prog, sub_block, time_lanes, wps, err, &src);
   }

@@ -21,7 +21,20 @@ struct FusedParams {
   int out_raw, pad_;
   long long out_len, clock0, n_samples;
   unsigned *sm_slots;  // [256] per-SM arrival counters (pipelined kernel: which warp of a CTA takes the lane-per-voice role)
+  // segmented kernels (a voice's timeline of this launch on `seg_n` warps): wrapped totals of every oscillator's
+  // increments per segment [voice][seg_n][n_osc], one flag per voice (non-zero: render it in one piece)
+  double *seg_totals;
+  int *seg_flags;
+  long long seg_tiles;  // 256-sample tiles per segment
+  int seg_n, seg_pad_;
 };
+
+// Segmented rendering (see ops.cuh "segments of one voice's timeline"): "" when the program does not qualify.
+// `scan`: the kernel `dusp_fused_scan` that leaves the totals and flags; `render`: `dusp_fused` with the segment logic.
+bool generate_segmented_sources(const Program &p, int min_blocks, int out_mode, std::string &scan, std::string &render, int *n_osc);
+struct FusedKernel;
+FusedKernel *fused_build(const std::string &src, const char *entry, std::string &err);
+size_t fused_build_cubin(const std::string &src, std::string &err);  // NVRTC only (no device needed)
 
 // CUDA C++ source of the specialised kernel `dusp_fused` for tile shape (B, T).
 std::string generate_fused_source(const Program &p, int B, int T, int min_blocks, int out_mode = 0);

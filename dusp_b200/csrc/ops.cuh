@@ -541,6 +541,47 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
   cx.last(x1); cx.last(x2); cx.last(y1); cx.last(y2);
 }
 
+// ------------------------------------------------------------------ segments of one voice's timeline on different warps
+// A batch too small to fill the GPU (W2: 1 000 voices = 1 000 warps) is bound by each warp's own latency.  Where every
+// stateful unit of a circuit can be put at an arbitrary sample without running the samples before it, the timeline of a
+// launch is cut into segments rendered by different warps (fused.cc, "segmented" kernels).  That holds for Ramp (a
+// counter: ramp_jump), Noise at F >= sampleRate (counter-based draws) and Osc -- whose phase at a segment's start is the
+// start phase plus the wrapped sum of all earlier increments, exact under c_osc's own conditions: a first kernel
+// evaluates only what feeds the oscillators' F inlets and leaves each segment's wrapped total (c_osc_total) and
+// whether the conditions held; voices where they did not are rendered in one piece, in the reference's order.
+//
+// Exact total of a tile's increments, wrapped to [0, 44100) -- the first half of c_osc; ok: c_osc's conditions on f.
+template <int B, int T>
+DOPS_DEV double c_osc_total(const Cx<B, T> &cx, const float (&f)[B], bool &ok) {
+  double part = 0.0;
+  uint32_t umax = 0u, umin = 0x7fffffffu;
+#pragma unroll
+  for (int s = 0; s < B; s++) {
+    const uint32_t u = __float_as_uint(f[s]) & 0x7fffffffu;
+    umax = max(umax, u);
+    umin = min(umin, u - 1u);
+    const double x = part + (double)f[s];
+    part = x < 0.0 ? x + SRD : (x >= SRD ? x - SRD : x);
+  }
+  ok = __all_sync(0xffffffffu, umax < 0x472C4400u && umin >= 0x38FFFFFFu);
+#pragma unroll
+  for (int o = 1; o < T; o <<= 1) part = wrap_add_sr(part, __shfl_xor_sync(0xffffffffu, part, o));
+  return part;
+}
+DOPS_DEV bool osc_phase_exact(double ph) { return ph >= 0.0 && ph < SRD && (ph + 65536.0) - 65536.0 == ph; }
+// Ramp.js:25-33 advanced by n samples without output: one literal step, then the closed form of "count up by one
+// until t passes duration" (the same two steps c_ramp takes for a lane's earlier samples).
+DOPS_DEV void ramp_jump(double &t, double &playing, double dur, long long n) {
+  if (n <= 0 || playing == 0.0) return;
+  t += 1.0;
+  if (t > dur) { playing = 0.0; t = dur; }
+  if (t < 0.0) { playing = 0.0; t = 0.0; }
+  if (playing != 0.0) {
+    const double rem = (double)(n - 1);
+    if (t + rem > dur) { t = dur; playing = 0.0; } else t += rem;
+  }
+}
+
 // ------------------------------------------------------------------ rings
 // A warp whose 32 lanes walk ONE ring along time (T = 32): lane tl owns the B consecutive ring positions
 // [i0 + tl*B, +B).  The tap offset is arbitrary, so i0 is in general not a multiple of 4 and a lane's run is not

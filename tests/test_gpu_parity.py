@@ -176,6 +176,43 @@ def test_w3_batch_with_per_voice_parameters(lib, oracle, kernel_mode):
     assert np.max(np.abs(mix - got.astype(np.float64).sum(axis=0))) <= 1e-5 * max(1.0, np.max(np.abs(ref_mix)))
 
 
+def test_small_batch_renders_a_voice_on_several_warps(lib, oracle, monkeypatch):
+    """Segmented rendering (ops.cuh "segments of one voice's timeline"): 70 FM voices with their own Ramp, rendered in
+    three launches -- every launch cuts a voice's timeline into segments on different warps (a first kernel leaves each
+    segment's wrapped sum of the oscillator's increments).  Bit for bit the render in one piece and the oracle; a voice
+    whose increments are too small for exact partial sums (f = 1e-6) is rendered whole, in the same launches."""
+    blob, _ = circuit_blob(circuits.w2_live())
+    ramp = unit_index(blob, "Ramp")
+    n = 70
+    f0 = np.linspace(110.0, 790.0, n)
+    f0[5] = 1e-6   # below 2^-13: this voice's sums are not exact -> one piece
+    vals = np.stack([f0, f0 / 2], axis=1)
+    lens = [256 * 40 + 3, 256 * 7, 256 * 61 + 200]
+
+    def render():
+        s = capi.Session([capi.Program(blob)], [n], 0)
+        s.set_params(0, ["u%d.y0" % ramp, "u%d.y1" % ramp], vals)
+        l0 = s.launch_count
+        out = [s.render_host(k) for k in lens]
+        launches = s.launch_count - l0
+        info = s.launch_info()
+        s.close()
+        return out, launches, info
+    seg, seg_launches, info = render()
+    monkeypatch.setenv("DUSP_NO_SEGMENTS", "1")
+    whole, whole_launches, _ = render()
+    monkeypatch.delenv("DUSP_NO_SEGMENTS")
+    assert info["specialised"] and seg_launches == 2 * whole_launches == 6
+    for a, b in zip(seg, whole):
+        assert np.array_equal(a, b)
+    for v in (0, 5, 33, 69):  # the first launch of a few voices against the oracle
+        osc = C.Osc(C.Ramp(88200, float(f0[v]), float(f0[v]) / 2).trigger())
+        vb, _ = circuit_blob(C.Multiply(osc, osc))
+        want = oracle.render(vb, 0.25)
+        m = min(lens[0], len(want[0]))
+        compare(seg[0][v][:, :m], [w[:m] for w in want], True, "voice %d" % v)
+
+
 def test_w3_three_voices_at_the_benchmarked_sixty_seconds(lib, oracle, kernel_mode):
     """BASELINE config 2 renders 60 s: three voices of bench.py's generator at that length, bit for bit (the
     44 100-sample CircleBuffer wraps 60 times, the noise stream runs 2.6 M draws, the session renders it in the
