@@ -275,8 +275,26 @@ DOPS_DEV void c_mcosc(const Cx<B, T> &cx, float (&f)[B], double &ph, const float
 
 // -------------------------------------------------------------- envelopes
 // Ramp.js:25-40
+// IEEE a / b for many a and one b (Ramp.js:37: t / duration, B times per lane by the same duration).  With the
+// correctly rounded reciprocal y = RN(1 / b):  q = RN(a y),  r = a - b q (one FMA: exact),  RN(q + r y) = RN(a / b)
+// (Markstein's theorem; tests/kat_div.c checks 4e8 cases against the hardware's division, among them the significands
+// the proof is tight for).  Three FP64 operations instead of the ~25 of a division.  Outside the guarded range (zero,
+// subnormal or huge operands, NaN) the literal division runs: signs of zero and overflow behave as IEEE says there.
+struct SharedDiv {
+  double b, y;
+  bool fast;
+  DOPS_DEV explicit SharedDiv(double b_) : b(b_), y(1.0 / b_) { const double ab = fabs(b_); fast = ab >= 3.0549363634996047e-151 && ab <= 3.273390607896142e150; }
+  DOPS_DEV double operator()(double a) const {
+    const double aa = fabs(a);
+    if (!(fast && aa >= 3.0549363634996047e-151 && aa <= 3.273390607896142e150)) return a / b;
+    const double q = a * y, r = __fma_rn(-q, b, a);
+    return __fma_rn(r, y, q);
+  }
+};
+
 template <int B, int T>
 DOPS_DEV void c_ramp(const Cx<B, T> &cx, float (&o)[B], double &t, double &playing, double dur, double y0, double y1) {
+  const SharedDiv over_dur(dur);
   if (T > 1 && cx.tl > 0 && playing != 0.0) {
     // the tl*B steps before this lane's first sample: one literal step, then the closed form of
     // "count up by one until t passes duration" (after the first step 0 <= t <= duration holds)
@@ -295,7 +313,7 @@ DOPS_DEV void c_ramp(const Cx<B, T> &cx, float (&o)[B], double &t, double &playi
       if (t > dur) { playing = 0.0; t = dur; }
       if (t < 0.0) { playing = 0.0; t = 0.0; }
     }
-    o[s] = (float)(y0 + (t / dur) * (y1 - y0));
+    o[s] = (float)(y0 + over_dur(t) * (y1 - y0));
   }
   cx.last(t); cx.last(playing);
 }

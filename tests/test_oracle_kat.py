@@ -290,3 +290,15 @@ def test_shape_finishing_by_itself_switches_inside_that_tick(oracle):
     fr = tt % 1
     env = (dec[np.ceil(tt).astype(int)].astype(np.float64) * fr + dec[np.floor(tt).astype(int)].astype(np.float64) * (1 - fr))
     assert np.array_equal(out[:k * 256], env.astype(np.float32))
+
+
+def test_shared_reciprocal_division_is_ieee_division(tmp_path):
+    """ops.cuh SharedDiv (the Ramp's t / duration as q + (t - duration q) / duration with one correctly rounded
+    reciprocal per call) must equal the hardware's division bit for bit: tests/kat_div.c, 2.6e7 random and hard cases
+    here (4.2e8 when run by hand)."""
+    import os, subprocess
+    here = os.path.dirname(os.path.abspath(__file__))
+    exe = str(tmp_path / "kat_div")
+    subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-o", exe, os.path.join(here, "kat_div.c"), "-lm"])
+    r = subprocess.run([exe, "10"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and " 0 mismatches" in r.stdout, r.stdout[-500:]
