@@ -548,11 +548,18 @@ DOPS_DEV void c_filterc(const Cx<B, T> &cx, float (&x)[B], double a0, double a1,
     filterc_rec<B, false>(c, x, b1, b2, q1, q2);
 #endif
   } else {
-#pragma unroll 1
+    // T turns.  Every lane runs the recurrence in every turn on its own brackets with the state broadcast from the lane
+    // whose turn it was (a warp instruction costs the same with one lane active or all): only the lane whose turn it is
+    // keeps the results -- selects instead of a divergent branch, and the state needs no second hand-over.
+#pragma unroll 2
     for (int turn = 0; turn < T; turn++) {
-      if (cx.tl == turn) filterc_rec<B, false>(c, x, b1, b2, q1, q2);
-      const double n1 = cx.from(q1, turn), n2 = cx.from(q2, turn);
-      if (cx.tl == turn + 1) { q1 = n1; q2 = n2; }
+      float yt[B];
+      double a1 = q1, a2 = q2;
+      filterc_rec<B, false>(c, yt, b1, b2, a1, a2);
+      const bool mine = cx.tl == turn;
+#pragma unroll
+      for (int s = 0; s < B; s++) x[s] = mine ? yt[s] : x[s];
+      q1 = cx.from(a1, turn); q2 = cx.from(a2, turn);
     }
   }
   x1 = xlast; x2 = o2; y1 = (double)x[B - 1]; y2 = q2;
