@@ -948,21 +948,50 @@ int launch(const DuspKernelParams *kp, int warps_per_cta, cudaStream_t st, int *
 }  // namespace
 
 // --------------------------------------------------------------- launcher
-#define DUSP_CONFIGS(X) X(16, 1) X(8, 1) X(8, 4) X(16, 4) X(8, 8) X(16, 8) X(16, 16) X(8, 32) X(4, 32)
+// The tile shapes are instantiated in three translation units (the same file compiled with DUSP_INST_GROUP = 0 / 1 / 2,
+// see the Makefile) so that a clean build runs them side by side: the switch above is ~4 minutes of ptxas per shape set.
+#ifndef DUSP_INST_GROUP
+#define DUSP_INST_GROUP 0
+#endif
+#if DUSP_INST_GROUP == 0
+#define DUSP_CONFIGS(X) X(16, 1) X(8, 1) X(8, 4) X(16, 4)
+#define DUSP_GROUP_FN dusp_launch_render_g0
+#elif DUSP_INST_GROUP == 1
+#define DUSP_CONFIGS(X) X(8, 8) X(16, 8) X(16, 16)
+#define DUSP_GROUP_FN dusp_launch_render_g1
+#else
+#define DUSP_CONFIGS(X) X(8, 32) X(4, 32)
+#define DUSP_GROUP_FN dusp_launch_render_g2
+#endif
+
+// cudaErrorInvalidValue when the shape belongs to another group
+extern "C" int DUSP_GROUP_FN(const DuspKernelParams *kp, int sub_block, int time_lanes, int warps_per_cta,
+                             void *stream, int *grid_out, int *smem_out) {
+#if DUSP_INST_GROUP == 2
+  if (kp->multi && time_lanes == 32 && sub_block == 4 && kp->density > 0)  // heterogeneous batch: the register-capped instantiation
+    return launch<4, 32, 8>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
+#endif
+#define X(BV, TV) if (sub_block == BV && time_lanes == TV) return launch<BV, TV>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
+  DUSP_CONFIGS(X)
+#undef X
+  return (int)cudaErrorInvalidValue;
+}
+
+#if DUSP_INST_GROUP == 0
+extern "C" int dusp_launch_render_g1(const DuspKernelParams *, int, int, int, void *, int *, int *);
+extern "C" int dusp_launch_render_g2(const DuspKernelParams *, int, int, int, void *, int *, int *);
 
 extern "C" int dusp_launch_supported(int sub_block, int time_lanes) {
 #define X(BV, TV) if (sub_block == BV && time_lanes == TV) return 1;
-  DUSP_CONFIGS(X)
+  X(16, 1) X(8, 1) X(8, 4) X(16, 4) X(8, 8) X(16, 8) X(16, 16) X(8, 32) X(4, 32)
 #undef X
   return 0;
 }
 
 extern "C" int dusp_launch_render(const DuspKernelParams *kp, int sub_block, int time_lanes, int warps_per_cta,
                                   void *stream, int *grid_out, int *smem_out) {
-  if (kp->multi && time_lanes == 32 && sub_block == 4 && kp->density > 0)  // heterogeneous batch: the register-capped instantiation
-    return launch<4, 32, 8>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
-#define X(BV, TV) if (sub_block == BV && time_lanes == TV) return launch<BV, TV>(kp, warps_per_cta, (cudaStream_t)stream, grid_out, smem_out);
-  DUSP_CONFIGS(X)
-#undef X
-  return (int)cudaErrorInvalidValue;
+  if (time_lanes == 32) return dusp_launch_render_g2(kp, sub_block, time_lanes, warps_per_cta, stream, grid_out, smem_out);
+  if (time_lanes >= 8) return dusp_launch_render_g1(kp, sub_block, time_lanes, warps_per_cta, stream, grid_out, smem_out);
+  return dusp_launch_render_g0(kp, sub_block, time_lanes, warps_per_cta, stream, grid_out, smem_out);
 }
+#endif

@@ -6,7 +6,8 @@ rep, so, tag = sys.argv[1], sys.argv[2], sys.argv[3]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 tmp = tempfile.mkdtemp()
 subprocess.check_call(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, stdout=subprocess.DEVNULL)
-cubin = [f for f in os.listdir(tmp) if f.startswith("render_sm100") and f.endswith(".cubin")][0]
+cubins = [f for f in os.listdir(tmp) if f.endswith(".cubin")]
+cubin = [f for f in cubins if tag in subprocess.run(["cuobjdump", "-elf", os.path.join(tmp, f)], capture_output=True, text=True).stdout][0] if len(cubins) > 1 else cubins[0]
 sass = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout.split("\n")
 starts = [i for i, l in enumerate(sass) if l.startswith(".text.")]
 s0 = [i for i in starts if tag in sass[i]][0]
