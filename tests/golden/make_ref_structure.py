@@ -1,0 +1,74 @@
+"""Extracts, from the REFERENCE'S OWN SOURCE TEXT (/root/reference/src, present only in the build container), the
+structural facts the host mirror must share with it: per unit class the constructor's parameter names, the inlets in
+declaration order with their `mono` flag, the outlets with their channel count where it is a literal, the defaults
+of the form `this.NAME = param || <number>`, and the state fields the constructor sets to a literal (`this.phase = 0`).  Writes tests/golden/ref_structure.json (committed);
+tests/test_host_mirror.py compares the Python mirror against it, so a wrong port name, port order or default in the
+mirror -- which the oracle, fed by the same mirror, could not see -- fails a test.
+
+usage: python tests/golden/make_ref_structure.py [/root/reference]"""
+import json, os, re, sys
+
+ref = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
+src = os.path.join(ref, "src")
+out = {}
+
+
+def parse_opts(text):
+    o = {}
+    if text is None:
+        return o
+    m = re.search(r"mono\s*:\s*(true|false)", text)
+    if m:
+        o["mono"] = m.group(1) == "true"
+    m = re.search(r"numberOfChannels\s*:\s*(\d+)", text)
+    if m:
+        o["numberOfChannels"] = int(m.group(1))
+    return o
+
+
+def scan(path, rel):
+    text = open(path).read()
+    m = re.search(r"^function\s+([A-Z]\w*)\s*\(([^)]*)\)\s*\{", text, re.M)
+    cls_style = False
+    if not m:
+        mc = re.search(r"^class\s+([A-Z]\w*)\s+extends\s+(\w+)", text, re.M)
+        m2 = re.search(r"constructor\s*\(([^)]*)\)\s*\{", text)
+        if not mc:
+            return
+        name, base, params = mc.group(1), mc.group(2), (m2.group(1) if m2 else "")
+        cls_style = True
+    else:
+        name, params = m.group(1), m.group(2)
+        mb = re.search(r"^\s*(\w+)\.call\(this", text, re.M)
+        base = mb.group(1) if mb else None
+    # constructor body: up to the first prototype assignment / the first method of the class
+    start = (m2.end() if cls_style and m2 else m.end() if m else 0)
+    if cls_style:
+        depth, i = 1, start
+        while i < len(text) and depth:
+            depth += text[i] == "{"
+            depth -= text[i] == "}"
+            i += 1
+        body = text[start:i]
+    else:
+        end = re.search(r"^\}", text[start:], re.M)
+        body = text[start:start + end.start()] if end else text[start:]
+    inlets = [{"name": a, **parse_opts(b)} for a, b in re.findall(r"this\.add(?:Spectral)?Inlet\(\s*[\"'](\w+)[\"']\s*(?:,\s*\{([^}]*)\})?", body)]
+    outlets = [{"name": a, **parse_opts(b)} for a, b in re.findall(r"this\.add(?:Spectral)?Outlet\(\s*[\"'](\w+)[\"']\s*(?:,\s*\{([^}]*)\})?", body)]
+    defaults = {}
+    for port, param, dflt in re.findall(r"this\.([A-Z][A-Z0-9_]*)\s*=\s*(\w+)\s*\|\|\s*(-?[0-9.]+(?:e-?\d+)?)\s*$", body, re.M):
+        defaults[port] = {"param": param, "default": float(dflt)}
+    fields = {}
+    for fld, val in re.findall(r"^\s*this\.([a-z]\w*)\s*=\s*(-?[0-9.]+(?:e-?\d+)?|true|false)\s*;?\s*(?://.*)?$", body, re.M):
+        fields[fld] = {"true": 1.0, "false": 0.0}.get(val, None) if val in ("true", "false") else float(val)
+    out[name] = {"fields": fields, "file": rel, "base": base, "params": [p.strip().split("=")[0].strip() for p in params.split(",") if p.strip()],
+                 "inlets": inlets, "outlets": outlets, "defaults": defaults}
+
+
+for root, _, files in os.walk(os.path.join(src, "components")):
+    for f in sorted(files):
+        if f.endswith(".js") and f != "index.js":
+            scan(os.path.join(root, f), os.path.relpath(os.path.join(root, f), ref))
+dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_structure.json")
+json.dump(out, open(dst, "w"), indent=1, sort_keys=True)
+print("wrote %d classes to %s" % (len(out), dst))

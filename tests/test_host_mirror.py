@@ -184,3 +184,73 @@ def test_cases_json_is_current():
         assert c["seconds"] == circuits.CASES[name][1] and c["exact"] == bool(circuits.CASES[name][2])
         assert sum(k in c for k in ("dusp", "blob", "skip")) == 1, name
     assert sum("skip" in c for c in cases.values()) <= 6
+
+
+# ---- structure of every unit class against the reference's own source text (tests/golden/ref_structure.json, written by
+#      tests/golden/make_ref_structure.py in the build container, where /root/reference exists)
+_CTOR_ARGS = {  # classes whose constructor refuses to run without arguments (as the reference's does)
+    "AllPass": (0.01, 0.5), "CombFilter": (0.01, 0.5), "FixedDelay": (0.01,), "Clip": (0.5,), "Pow": (1, 2), "Monitor": (0,),
+    "FFT": (4096, 1024), "IFFT": (4096, 1024), "Hopper": (1024, 4096), "UnHopper": (1024, 4096), "Windower": (4096, "hamming", 1024),
+    "ReChunk": (256, 4096),
+    "HardLowPass": (1000,), "HardHighPass": (1000,), "SpectralSum": (0, 0),
+}
+
+
+def _ref_structure():
+    import json, os
+    return json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_structure.json")))
+
+
+def _chain(ref, name, key):
+    r = ref.get(name)
+    if r is None:
+        return []
+    return _chain(ref, r["base"], key) + r[key]
+
+
+def test_unit_classes_have_the_references_ports_and_defaults():
+    """Port names, their order, `mono` flags, literal channel counts, constructor parameter order and `param || number`
+    defaults of every component class, against what the reference's source declares.  (The oracle and the device are
+    fed by this mirror: a wrong port or default here would be identically wrong on both sides of every parity test.)"""
+    import inspect
+    from dusp_b200 import components as C
+    ref = _ref_structure()
+    checked = fields_checked = 0
+    for name, r in sorted(ref.items()):
+        cls = getattr(C, name, None)
+        if cls is None:
+            assert name in ("CircularMotion", "LinearMotion", "GreaterThan", "LessThan", "SpectralUnit", "SignalCombiner"), name
+            continue
+        if name in ("CircleBufferReader", "CircleBufferWriter", "CircleBufferNode"):
+            u = cls(C.CircleBuffer(1, 1.0))
+        else:
+            u = cls(*_CTOR_ARGS.get(name, ()))
+        want_in = [(i["name"], bool(i.get("mono", False))) for i in _chain(ref, name, "inlets")]
+        got_in = [(i.name, i.exposeAsMono) for i in u.inletsOrdered if not i.noData]
+        assert got_in == want_in, (name, got_in, want_in)
+        want_out = _chain(ref, name, "outlets")
+        got_out = [o for o in u.outletsOrdered if not o.noData]
+        assert [o.name for o in got_out] == [o["name"] for o in want_out], (name, [o.name for o in got_out], want_out)
+        for o, w in zip(got_out, want_out):
+            if "numberOfChannels" in w:
+                assert o.numberOfChannels == w["numberOfChannels"], (name, o.name)
+            if w.get("mono"):
+                assert o.numberOfChannels == 1, (name, o.name)
+        params = [p for p in inspect.signature(cls.__init__).parameters if p != "self"]
+        assert len(params) >= len(r["params"]), (name, params, r["params"])
+        if name not in _CTOR_ARGS:
+            defaults = {}
+            k = name
+            while k in ref:  # a subclass inherits its base's `this.A = a || 0`
+                for port, dv in ref[k]["defaults"].items():
+                    defaults.setdefault(port, dv)
+                k = ref[k]["base"]
+            for port, dv in defaults.items():
+                inlet = next(i for i in u.inletsOrdered if i.name.upper() == port)
+                assert not inlet.connected and float(inlet.constant) == dv["default"], (name, port, inlet.constant, dv)
+        for fld, val in r["fields"].items():  # state the constructor sets to a literal: this.phase = 0, this.compensationDB = 1.5 ...
+            if hasattr(u, fld) and isinstance(getattr(u, fld), (int, float, bool)) and name not in _CTOR_ARGS:
+                assert float(getattr(u, fld)) == val, (name, fld, getattr(u, fld), val)
+                fields_checked += 1
+        checked += 1
+    assert checked >= 50 and fields_checked >= 12
