@@ -69,6 +69,23 @@ for root, _, files in os.walk(os.path.join(src, "components")):
     for f in sorted(files):
         if f.endswith(".js") and f != "index.js":
             scan(os.path.join(root, f), os.path.relpath(os.path.join(root, f), ref))
+# patches: the aliases a patch's constructor declares, in order (Patch.js:24-60: the name defaults to the aliased port's)
+patches = {}
+for f in sorted(os.listdir(os.path.join(src, "patches"))):
+    if not f.endswith(".js") or f == "index.js":
+        continue
+    text = open(os.path.join(src, "patches", f)).read()
+    m = re.search(r"^function\s+([A-Z]\w*)\s*\(([^)]*)\)", text, re.M) or re.search(r"^class\s+([A-Z]\w*)\s+extends", text, re.M)
+    if not m:
+        continue
+    mc = re.search(r"constructor\s*\(([^)]*)\)", text)
+    params = m.group(2) if m.lastindex and m.lastindex >= 2 else (mc.group(1) if mc else "")
+    al = []
+    for kind, port, nm in re.findall(r"this\.alias(Inlet|Outlet)\(\s*[\w.\[\]\-+ ]*?\.([A-Z][A-Z0-9]*)\s*(?:,\s*[\"'](\w+)[\"'])?\s*\)", text):
+        al.append({"kind": kind.lower(), "name": nm or port.lower(), "explicit": bool(nm)})
+    patches[m.group(1)] = {"file": "src/patches/" + f, "aliases": al,
+                           "params": [q.strip().split("=")[0].strip() for q in params.split(",") if q.strip()]}
+out = {"components": out, "patches": patches}
 dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_structure.json")
 json.dump(out, open(dst, "w"), indent=1, sort_keys=True)
-print("wrote %d classes to %s" % (len(out), dst))
+print("wrote %d unit classes and %d patches to %s" % (len(out["components"]), len(out["patches"]), dst))

@@ -214,7 +214,7 @@ def test_unit_classes_have_the_references_ports_and_defaults():
     fed by this mirror: a wrong port or default here would be identically wrong on both sides of every parity test.)"""
     import inspect
     from dusp_b200 import components as C
-    ref = _ref_structure()
+    ref = _ref_structure()["components"]
     checked = fields_checked = 0
     for name, r in sorted(ref.items()):
         cls = getattr(C, name, None)
@@ -254,3 +254,30 @@ def test_unit_classes_have_the_references_ports_and_defaults():
                 fields_checked += 1
         checked += 1
     assert checked >= 50 and fields_checked >= 12
+
+
+def test_patches_declare_the_references_aliases():
+    """Every patch of the mirror exposes the inlets / outlets the reference's constructor aliases, under the same names
+    in the same order (src/patches/*.js, Patch.js:24-60)."""
+    import inspect
+    from dusp_b200 import patches as P
+    ref = _ref_structure()["patches"]
+    args = {"MultiTapDelay": (1, 1.0), "DelayMixer": (1, 1.0), "APStack": (2,), "Mixer": (), "HardBandPass": (), "SpaceChannel": ()}
+    checked = 0
+    for name, r in sorted(ref.items()):
+        cls = getattr(P, name, None)
+        if cls is None or not r["aliases"]:
+            continue
+        try:
+            u = cls(*args.get(name, ()))
+        except Exception:
+            continue  # needs constructor arguments this table does not have
+        want_in = [a["name"] for a in r["aliases"] if a["kind"] == "inlet"]
+        want_out = [a["name"] for a in r["aliases"] if a["kind"] == "outlet"]
+        got_in, got_out = list(u.inlets), list(u.outlets)
+        assert [x.lower() for x in got_in][:len(want_in)] == [x.lower() for x in want_in] or set(x.lower() for x in want_in) <= set(x.lower() for x in got_in), (name, got_in, want_in)
+        assert set(x.lower() for x in want_out) <= set(x.lower() for x in got_out), (name, got_out, want_out)
+        params = [p for p in inspect.signature(cls.__init__).parameters if p != "self"]
+        assert len(params) >= len(r["params"]), (name, params, r["params"])
+        checked += 1
+    assert checked >= 12, checked
