@@ -85,7 +85,17 @@ for f in sorted(os.listdir(os.path.join(src, "patches"))):
         al.append({"kind": kind.lower(), "name": nm or port.lower(), "explicit": bool(nm)})
     patches[m.group(1)] = {"file": "src/patches/" + f, "aliases": al,
                            "params": [q.strip().split("=")[0].strip() for q in params.split(",") if q.strip()]}
-out = {"components": out, "patches": patches}
+# the Dusp front door: shorthand constructors, binary operators, the names `[Name ...]` can construct
+text = open(os.path.join(src, "construct", "shorthandConstructors.js")).read()
+shorthands = re.findall(r"^\s{2}(\w+)\s*:\s*function\s*\(([^)]*)\)", text, re.M)
+text = open(os.path.join(src, "construct", "constructOperation.js")).read()
+operators = re.findall(r"case\s+\"([^\"]+)\"\s*:", text)
+exported = {}
+for pkg in ("components", "patches"):
+    text = open(os.path.join(src, pkg, "index.js")).read()
+    exported[pkg] = re.findall(r"^\s*(\w+)\s*:\s*require\(", text, re.M)
+front = {"shorthands": {k: [q.strip() for q in v.split(",") if q.strip()] for k, v in shorthands}, "operators": operators, "exported": exported}
+out = {"components": out, "patches": patches, "front_door": front}
 dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_structure.json")
 json.dump(out, open(dst, "w"), indent=1, sort_keys=True)
 print("wrote %d unit classes and %d patches to %s" % (len(out["components"]), len(out["patches"]), dst))

@@ -281,3 +281,22 @@ def test_patches_declare_the_references_aliases():
         assert len(params) >= len(r["params"]), (name, params, r["params"])
         checked += 1
     assert checked >= 12, checked
+
+
+def test_front_door_tables_match_the_reference():
+    """Shorthand constructors (shorthandConstructors.js), binary operators (constructOperation.js) and the names an
+    object expression `[Name ...]` can construct (components/index.js, patches/index.js), from the reference's text."""
+    import inspect
+    from dusp_b200 import construct, components as C, patches as P
+    fd = _ref_structure()["front_door"]
+    assert set(fd["shorthands"]) == set(construct.SHORTHAND_CONSTRUCTORS)
+    for k, params in fd["shorthands"].items():
+        assert len(inspect.signature(construct.SHORTHAND_CONSTRUCTORS[k]).parameters) == len(params), k
+    src = inspect.getsource(construct)
+    for op in fd["operators"]:
+        assert 'op == "%s"' % op in src, op
+    not_mirrored = {"GreaterThan", "LessThan", "CircularMotion", "LinearMotion"}  # vector units / units that throw at construction (DESIGN.md section 9)
+    missing_c = [n for n in fd["exported"]["components"] if not hasattr(C, n) and n not in not_mirrored]
+    assert missing_c in ([], ["vector", "spectral"]) or all(n in ("vector", "spectral") for n in missing_c), missing_c
+    missing_p = [n for n in fd["exported"]["patches"] if not hasattr(P, n)]
+    assert set(missing_p) <= {"ComplexOrbit", "OrbittySine", "SineCloud"}, missing_p  # patches built on the vector units
