@@ -95,7 +95,12 @@ for pkg in ("components", "patches"):
     text = open(os.path.join(src, pkg, "index.js")).read()
     exported[pkg] = re.findall(r"^\s*(\w+)\s*:\s*require\(", text, re.M)
 front = {"shorthands": {k: [q.strip() for q in v.split(",") if q.strip()] for k, v in shorthands}, "operators": operators, "exported": exported}
-out = {"components": out, "patches": patches, "front_door": front}
+text = open(os.path.join(src, "config.js")).read()
+cfg = {k: float(v) for k, v in re.findall(r"^\s*(standardChunkSize|sampleRate|windowSize)\s*:\s*([0-9.]+)", text, re.M)}
+cfg["hopSize_expr"] = re.search(r"hopSize\s*:\s*([^,\n]+)", text).group(1).strip()
+cfg["channelFormat"] = re.search(r"channelFormat\s*:\s*\"(\w+)\"", text).group(1)
+cfg["windowKind"] = re.search(r"windowKind\s*:\s*\"(\w+)\"", text).group(1)
+out = {"components": out, "patches": patches, "front_door": front, "config": cfg}
 dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_structure.json")
 json.dump(out, open(dst, "w"), indent=1, sort_keys=True)
 print("wrote %d unit classes and %d patches to %s" % (len(out["components"]), len(out["patches"]), dst))

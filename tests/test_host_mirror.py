@@ -300,3 +300,12 @@ def test_front_door_tables_match_the_reference():
     assert missing_c in ([], ["vector", "spectral"]) or all(n in ("vector", "spectral") for n in missing_c), missing_c
     missing_p = [n for n in fd["exported"]["patches"] if not hasattr(P, n)]
     assert set(missing_p) <= {"ComplexOrbit", "OrbittySine", "SineCloud"}, missing_p  # patches built on the vector units
+
+
+def test_config_constants_match_the_reference():
+    """src/config.js:5-16 against dusp_b200/config.py and the constants compiled into the library."""
+    from dusp_b200 import config
+    c = _ref_structure()["config"]
+    assert config.standardChunkSize == c["standardChunkSize"] == 256 and config.sampleRate == c["sampleRate"] == 44100
+    assert config.fft["windowSize"] == c["windowSize"] and c["hopSize_expr"] == "4096/4" and config.fft["hopSize"] == 1024
+    assert config.channelFormat == c["channelFormat"] and config.fft["windowKind"] == c["windowKind"]
