@@ -100,7 +100,28 @@ cfg = {k: float(v) for k, v in re.findall(r"^\s*(standardChunkSize|sampleRate|wi
 cfg["hopSize_expr"] = re.search(r"hopSize\s*:\s*([^,\n]+)", text).group(1).strip()
 cfg["channelFormat"] = re.search(r"channelFormat\s*:\s*\"(\w+)\"", text).group(1)
 cfg["windowKind"] = re.search(r"windowKind\s*:\s*\"(\w+)\"", text).group(1)
-out = {"components": out, "patches": patches, "front_door": front, "config": cfg}
+# the per-sample statement of the stateless units' _tick, verbatim, with the local names that alias a port's channel:
+# tests/test_oracle_kat.py translates these statements (JavaScript arithmetic is Python arithmetic) and runs them
+# against the oracle on known inputs
+tick_expr = {}
+for u in ["Multiply", "Divide", "Subtract", "Sum", "Gain", "Clip", "HardClipAbove", "HardClipBelow", "Pow", "Rescale", "CrossFader",
+          "PolarityInvert", "Abs", "DecibelToScaler", "SemitoneToRatio", "MidiToFrequency", "SecondsToSamples", "FixedMultiply", "Pan"]:
+    text = open(os.path.join(src, "components", u + ".js")).read()
+    m = re.search(r"_tick\s*(?:=\s*function)?\s*\([^)]*\)\s*\{", text)
+    body = text[m.end():]
+    depth, i = 1, 0
+    while i < len(body) and depth:
+        depth += body[i] == "{"
+        depth -= body[i] == "}"
+        i += 1
+    body = body[:i - 1]
+    aliases = dict(re.findall(r"var\s+(\w+)\s*=\s*this\.(\w+)\[", body))
+    inner = body[body.rfind("for(var t"):]
+    hdr = re.match(r"for\(var t[^)]*\)\s*\{?", inner)
+    stmt = inner[hdr.end():].strip().rstrip("}").strip()
+    helpers = re.findall(r"^function\s+(\w+)\s*\(([^)]*)\)\s*\{[^\n]*\n\s*return\s+([^\n;]+)", text, re.M)
+    tick_expr[u] = {"aliases": aliases, "stmt": stmt, "helpers": {h: {"params": p, "expr": e.strip()} for h, p, e in helpers}}
+out = {"components": out, "patches": patches, "front_door": front, "config": cfg, "tick_expr": tick_expr}
 dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_structure.json")
 json.dump(out, open(dst, "w"), indent=1, sort_keys=True)
 print("wrote %d unit classes and %d patches to %s" % (len(out["components"]), len(out["patches"]), dst))

@@ -302,3 +302,111 @@ def test_shared_reciprocal_division_is_ieee_division(tmp_path):
     subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-o", exe, os.path.join(here, "kat_div.c"), "-lm"])
     r = subprocess.run([exe, "10"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and " 0 mismatches" in r.stdout, r.stdout[-500:]
+
+
+# ---- the reference's own per-sample statements, executed ----------------------------------------------------------
+def _js_statement_to_python(stmt, aliases, helpers):
+    """The innermost statement of a stateless unit's _tick (verbatim JavaScript from tests/golden/ref_structure.json)
+    as the source of a Python function of the unit's inlets.  JavaScript's arithmetic operators on Numbers ARE IEEE
+    double operations, as Python's on floats; only the surface differs."""
+    import re
+    s = stmt
+    s = re.sub(r"//[^\n]*", "", s)
+    s = re.sub(r"[{}]", "", s)
+    for local, port in aliases.items():
+        s = re.sub(r"\b%s\[t\]" % re.escape(local), "P_" + port, s)
+    s = re.sub(r"this\.(\w+)\[(\d)\]\[t\]", r"P_\1\2", s)          # this.out[0][t]
+    s = re.sub(r"this\.(\w+)\[c\]\[t\]", r"P_\1", s)
+    s = re.sub(r"this\.(\w+)\[t\]", r"P_\1", s)
+    s = re.sub(r"\b(out\w*|fOut)\[t\]", r"P_out", s)                 # local names of the output channel
+    s = s.replace("config.sampleRate", "44100").replace("Math.abs", "abs").replace("Math.pow", "jspow")
+    s = re.sub(r"this\.(\w+)", r"F_\1", s)                           # plain fields: this.sf, this.compensationDB
+    s = re.sub(r"\bvar\s+", "", s)
+    lines = []
+    text = " ".join(l.strip() for l in s.splitlines())
+    m = re.match(r"if\((.*?)\)\s*(P_\w+\s*=.*?)\s*else\s*(P_\w+\s*=.*)$", text)   # if(..) a = x else a = y
+    if m:
+        lines = ["if %s:" % m.group(1), "    " + m.group(2), "else:", "    " + m.group(3)]
+    else:
+        for part in re.split(r"\s+(?=(?:P_\w+|\w+)\s*=[^=])", text):   # one assignment per line
+            part = part.strip()
+            if not part:
+                continue
+            t = re.match(r"(\w+)\s*=\s*(.*?)\s*\?\s*(.*?)\s*:\s*(.*)$", part)   # a = cond ? x : y
+            if t:
+                part = "%s = (%s) if (%s) else (%s)" % (t.group(1), t.group(3), t.group(2), t.group(4))
+            lines.append(part)
+    src = "def f(I, F):\n"
+    names = sorted(set(re.findall(r"\bP_(\w+)", "\n".join(lines))))
+    assigned = set(re.findall(r"(?:^|\s)P_(\w+)\s*=[^=]", "\n".join(lines), re.M))
+    for n in names:
+        if n not in assigned:
+            src += "    P_%s = I[%r]\n" % (n, n)
+    for n in sorted(set(re.findall(r"\bF_(\w+)", "\n".join(lines)))):
+        src += "    F_%s = F[%r]\n" % (n, n)
+    src += "".join("    " + l + "\n" for l in lines)
+    outs = [n for n in names if n in assigned]
+    src += "    return [%s]\n" % ", ".join("P_" + n for n in outs)
+    for h, d in helpers.items():
+        src = "def %s(%s):\n    return %s\n" % (h, d["params"], d["expr"].replace("Math.pow", "jspow").replace("Math.abs", "abs")) + src
+    return src
+
+
+def _jspow(a, b):
+    import math
+    try:
+        return math.pow(a, b)
+    except (ValueError, OverflowError):  # Math.pow: NaN for a negative base with a fractional exponent, Infinity on overflow
+        if a < 0 and b != int(b):
+            return float("nan")
+        return float("inf") if abs(a) > 1 else 0.0
+    except ZeroDivisionError:
+        return float("inf")
+
+
+def test_oracle_matches_the_references_own_tick_statements(oracle):
+    """The strongest pin available without a JavaScript engine: the per-sample statements of the stateless units'
+    `_tick`s, taken VERBATIM from the reference's source in the build container (tests/golden/make_ref_structure.py ->
+    ref_structure.json "tick_expr"), are translated token for token into Python (IEEE double arithmetic on both sides),
+    run on known inputs -- seeded Noise units, whose samples the test computes itself from the injected generator --
+    and compared with the oracle's render of the same unit: bit for bit, or within an ulp of f32 where Math.pow runs."""
+    import json, math, os
+    import numpy as np
+    import dusp_b200 as d
+    from dusp_b200 import components as C, config
+    from dusp_b200.render import circuit_blob
+    ref = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_structure.json")))["tick_expr"]
+    n = 512
+    checked = 0
+
+    def noise_samples(seed):  # Noise.js:16-28 at the default F = sampleRate: a new draw every sample; draw 0 was the constructor's
+        return [float(np.float32(2 * config.rand_tick(seed, k + 1) - 1)) for k in range(n)]
+    for name, r in sorted(ref.items()):
+        src = _js_statement_to_python(r["stmt"], r["aliases"], r["helpers"])
+        env = {"jspow": _jspow, "abs": abs}
+        exec(src, env)
+        f = env["f"]
+        u = getattr(C, name)(*{"FixedMultiply": (0.37,), "Clip": (0.5,), "Pow": (1, 2)}.get(name, ()))
+        inputs, seed = {}, 1000
+        for inlet in u.inletsOrdered:
+            if inlet.noData:
+                continue
+            seed += 1
+            setattr(u, inlet.name.upper(), C.Noise(seed=seed))
+            inputs[inlet.name] = noise_samples(seed)
+        fields = {k: float(v) for k, v in vars(u).items() if isinstance(v, (int, float)) and not k.startswith("_")}
+        blob, _ = circuit_blob(u)
+        got = oracle.render(blob, n / 44100)
+        want = [f({k: v[t] for k, v in inputs.items()}, fields) for t in range(n)]
+        for ch in range(len(want[0])):
+            w = np.array([x[ch] for x in want], dtype=np.float64)
+            w32 = w.astype(np.float32)
+            w32 = np.where(np.isnan(w32) | (w32 == 0), np.float32(0), w32)  # renderChannelData.js:44: x || 0
+            g = got[ch][:n]
+            if "pow" in src:
+                ok = np.isclose(g, w32, rtol=2e-7, atol=0) | (np.isinf(w32) & np.isinf(g)) | (g == w32)
+                assert ok.all(), (name, ch, int(np.flatnonzero(~ok)[0]))
+            else:
+                assert np.array_equal(g, w32), (name, ch, int(np.flatnonzero(g != w32)[0]), src)
+        checked += 1
+    assert checked == len(ref) >= 19
