@@ -121,7 +121,33 @@ for u in ["Multiply", "Divide", "Subtract", "Sum", "Gain", "Clip", "HardClipAbov
     stmt = inner[hdr.end():].strip().rstrip("}").strip()
     helpers = re.findall(r"^function\s+(\w+)\s*\(([^)]*)\)\s*\{[^\n]*\n\s*return\s+([^\n;]+)", text, re.M)
     tick_expr[u] = {"aliases": aliases, "stmt": stmt, "helpers": {h: {"params": p, "expr": e.strip()} for h, p, e in helpers}}
-out = {"components": out, "patches": patches, "front_door": front, "config": cfg, "tick_expr": tick_expr}
+# whole _tick bodies of the stateful hot-path units, verbatim: tests/js2py.py
+# translates them line by line and tests/test_oracle_kat.py runs them against the oracle
+def body_after(text, pattern):
+    m = re.search(pattern, text)
+    b = text[m.end():]
+    depth, i = 1, 0
+    while depth:
+        depth += b[i] == "{"
+        depth -= b[i] == "}"
+        i += 1
+    return b[:i - 1]
+
+
+comp = os.path.join(src, "components")
+tick_body = {}
+for u, f, pat in (("Osc", "Osc/Osc.js", r"_tick = function\(clock\) \{"), ("Ramp", "Ramp.js", r"_tick = function\(\) \{"),
+                  ("Filter", "Filter.js", r"_tick = function\(\) \{"), ("Noise", "Noise.js", r"_tick = function\(\) \{"),
+                  ("FixedDelay", "FixedDelay.js", r"_tick\(\) \{"), ("CombFilter", "CombFilter.js", r"_tick\(\) \{"),
+                  ("AllPass", "AllPass.js", r"_tick\(\) \{"), ("Timer", "Timer.js", r"_tick = function\(\) \{"),
+                  ("Shape", "Shape/index.js", r"_tick = function\(\) \{")):
+    tick_body[u] = body_after(open(os.path.join(comp, f)).read(), pat)
+text = open(os.path.join(comp, "Filter.js")).read()
+tick_body["Filter.LP"] = body_after(text, r"LP: function\(f\) \{")
+tick_body["Filter.HP"] = body_after(text, r"HP: function\(f\) \{")
+text = open(os.path.join(comp, "Osc", "waveTables.js")).read()
+tick_body["sineTable"] = text[text.index("const PHI"):text.index("var sawTable")]
+out = {"components": out, "patches": patches, "front_door": front, "config": cfg, "tick_expr": tick_expr, "tick_body": tick_body}
 dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_structure.json")
 json.dump(out, open(dst, "w"), indent=1, sort_keys=True)
 print("wrote %d unit classes and %d patches to %s" % (len(out["components"]), len(out["patches"]), dst))

@@ -1,0 +1,206 @@
+"""Test infrastructure: a line-oriented translator for the small JavaScript function bodies of the reference's `_tick`s
+(verbatim text in tests/golden/ref_structure.json, extracted from the reference's source in the build container) into
+Python, so that the reference's OWN statements can be executed against the oracle without a JavaScript engine.
+
+What makes that sound: JavaScript's Number arithmetic is IEEE binary64, as Python's float arithmetic; `%` on Numbers is
+C's fmod; a store into a Float32Array rounds to binary32 (F32 below does), a read widens.  The translator only changes
+the surface: `this.` -> `S.`, braces -> indentation, `x++`, `a % b`, `(x || 0)`, `Math.*`, `for(var ...)`.  It covers
+the constructs these bodies use and raises on anything else."""
+import math
+import re
+
+import numpy as np
+
+
+class F32:
+    """A Float32Array: stores round to binary32, reads return Python floats, out-of-range reads are `undefined` (None)."""
+
+    def __init__(self, n_or_values):
+        self.a = np.zeros(n_or_values, dtype=np.float32) if isinstance(n_or_values, int) else np.array(n_or_values, dtype=np.float32)
+
+    def __len__(self):
+        return len(self.a)
+
+    def __getitem__(self, i):
+        i = int(i)
+        return float(self.a[i]) if 0 <= i < len(self.a) else None
+
+    def __setitem__(self, i, v):
+        with np.errstate(over="ignore", invalid="ignore"):
+            self.a[int(i)] = np.float32(float("nan") if v is None else v)
+
+
+class JSArray(list):
+    """A plain JavaScript array of Numbers: reading past the end gives `undefined`, writing extends."""
+
+    def __getitem__(self, i):
+        return list.__getitem__(self, i) if 0 <= i < len(self) else None
+
+    def __setitem__(self, i, v):
+        while len(self) <= i:
+            self.append(None)
+        list.__setitem__(self, i, v)
+
+
+class Bag:
+    """`this`: attribute bag; `in` is spelled `in_`."""
+
+    def __init__(self, **kw):
+        self.__dict__.update(kw)
+
+
+def js_or(a, b):  # a || b on Numbers / undefined
+    return b if (a is None or a == 0 or a != a) else a
+
+
+def js_mod(a, b):
+    if b == 0 or a != a or b != b or math.isinf(a):
+        return float("nan")
+    return math.fmod(a, b)
+
+
+ENV = {"js_or": js_or, "js_mod": js_mod, "M_floor": math.floor, "M_ceil": math.ceil, "M_tan": math.tan, "M_cos": math.cos,
+       "M_sin": math.sin, "M_PI": math.pi, "M_abs": abs, "M_round": lambda x: math.floor(x + 0.5), "F32": F32, "len": len,
+       "range": range, "True": True, "False": False, "isinstance": isinstance, "int": int, "float": float}
+
+
+def _expr(e):
+    e = e.strip().rstrip(";")
+    e = re.sub(r"\bthis\.in\b", "S.in_", e)
+    e = re.sub(r"\bthis\.", "S.", e)
+    e = re.sub(r"\b(?:Unit|config)\.sampleRate\b", "44100", e)
+    e = re.sub(r"\bS\.sampleRate\b", "44100", e)
+    e = re.sub(r"\bS\.(?:IN|OUT)\.chunkSize\b", "256", e)
+    e = re.sub(r"\bMath\.(\w+)", r"M_\1", e)
+    e = re.sub(r"new Float32Array\(([^()]*)\)", r"F32(\1)", e)
+    e = re.sub(r"\.push\(", ".append(", e)
+    e = re.sub(r"([\w.]+(?:\[[^\]]*\])*)\.length\b", r"len(\1)", e)
+    e = re.sub(r"([\w.]+)\.constructor\s*==\s*Number", r"isinstance(\1, (int, float))", e)
+    e = re.sub(r"\btrue\b", "True", e)
+    e = re.sub(r"\bfalse\b", "False", e)
+    e = re.sub(r"&&", " and ", e)
+    e = re.sub(r"!(?!=)", " not ", e)
+    # (x || 0) and x || 0 with a simple left operand
+    e = re.sub(r"([\w.]+(?:\[[^\]]*\])*)\s*\|\|\s*0\b", r"js_or(\1, 0)", e)
+    if "||" in e:
+        raise ValueError("unsupported ||: " + e)
+    # a % b with simple operands (an identifier / member / index chain, a parenthesised sum, or a number)
+    opnd = r"(\((?:[^()]|\([^()]*\))*\)|[\w.]+(?:\[[^\]]*\]|\([^()]*\))*)"
+    for _ in range(4):
+        e2 = re.sub(opnd + r"\s*%\s*(?!=)" + opnd, r"js_mod(\1, \2)", e)
+        if e2 == e:
+            break
+        e = e2
+    return e
+
+
+def _stmt(s):
+    s = s.strip().rstrip(";")
+    if not s:
+        return []
+    s = re.sub(r"^(?:var|const|let)\s+", "", s)
+    m = re.match(r"^([\w.\[\]]+)\+\+$", s)
+    if m:
+        return [_expr(m.group(1)) + " += 1"]
+    m = re.match(r"^([\w.\[\]]+)--$", s)
+    if m:
+        return [_expr(m.group(1)) + " -= 1"]
+    m = re.match(r"^(.+?)\s*%=\s*(.+)$", s)
+    if m:
+        return ["%s = js_mod(%s, %s)" % (_expr(m.group(1)), _expr(m.group(1)), _expr(m.group(2)))]
+    if re.match(r"^\w+$", s):  # `var fraction`
+        return [s + " = None"]
+    # chained assignment a = b = expr (outData[c] = outData[c] || new ...): not needed by the covered bodies
+    return [_expr(s)]
+
+
+def translate(body, name="f", args="S"):
+    body = re.sub(r"//[^\n]*", "", body)   # (a line comment hides a `/*` inside it: Filter.js:38 relies on that)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    raw = [l.rstrip() for l in body.splitlines() if l.strip()]
+    lines = []
+    for l in raw:  # continuation lines: the previous one ends, or this one starts, with a binary operator
+        t = l.strip()
+        if lines and (re.search(r"[+\-*/=(,]$", lines[-1].strip()) and not lines[-1].strip().endswith("++") and not lines[-1].strip().endswith("--")
+                      or re.match(r"^[+\-*/)]", t)):
+            lines[-1] = lines[-1] + " " + t
+        else:
+            lines.append(t)
+    out = ["def %s(%s):" % (name, args)]
+    indent = 1
+    once = []  # indentation levels opened by a brace-less header: closed after one statement
+
+    def emit(text):
+        nonlocal indent
+        out.append("    " * indent + text)
+
+    def close_once():
+        nonlocal indent
+        while once and once[-1] == indent:
+            once.pop()
+            indent -= 1
+
+    for l in lines:
+        while l.startswith("}"):
+            indent -= 1
+            l = l[1:].strip()
+            if not (l.startswith("else")):
+                close_once()
+        if not l:
+            continue
+        m = re.match(r"^else\s+if\s*\((.*)\)\s*(\{)?\s*$", l)
+        if m:
+            emit("elif %s:" % _expr(m.group(1)))
+            indent += 1
+            if not m.group(2):
+                once.append(indent)
+            continue
+        m = re.match(r"^else\s*(\{)?\s*(.*)$", l)
+        if m and l.startswith("else"):
+            emit("else:")
+            indent += 1
+            rest = m.group(2).strip()
+            if not m.group(1):
+                if rest:
+                    for s in _stmt(rest):
+                        emit(s)
+                    indent -= 1
+                    close_once()
+                else:
+                    once.append(indent)
+            continue
+        m = re.match(r"^for\s*\(\s*var\s+(\w+)\s*=\s*(.+?);\s*\1\s*<\s*(.+?);\s*\1\+\+\s*\)\s*(\{)?\s*$", l)
+        if m:
+            emit("for %s in range(%s, %s):" % (m.group(1), _expr(m.group(2)), _expr(m.group(3))))
+            indent += 1
+            if not m.group(4):
+                once.append(indent)
+            continue
+        m = re.match(r"^for\s*\(\s*var\s+(\w+)\s+in\s+(.+?)\)\s*(\{)?\s*$", l)
+        if m:
+            emit("for %s in range(len(%s)):" % (m.group(1), _expr(m.group(2))))
+            indent += 1
+            if not m.group(3):
+                once.append(indent)
+            continue
+        m = re.match(r"^(if|while)\s*\((.*)\)\s*(\{)?\s*$", l)
+        if m:
+            emit("%s %s:" % (m.group(1), _expr(m.group(2))))
+            indent += 1
+            if not m.group(3):
+                once.append(indent)
+            continue
+        m = re.match(r"^(if|while)\s*\((.*?)\)\s+(\S.*)$", l)  # header and statement on one line
+        if m and not m.group(3).startswith("{"):
+            emit("%s %s:" % (m.group(1), _expr(m.group(2))))
+            indent += 1
+            for s in _stmt(m.group(3)):
+                emit(s)
+            indent -= 1
+            continue
+        for s in _stmt(l):
+            emit(s)
+        close_once()
+    src = "\n".join(out) + "\n"
+    compile(src, "<js2py>", "exec")
+    return src

@@ -410,3 +410,121 @@ def test_oracle_matches_the_references_own_tick_statements(oracle):
                 assert np.array_equal(g, w32), (name, ch, int(np.flatnonzero(g != w32)[0]), src)
         checked += 1
     assert checked == len(ref) >= 19
+
+
+def test_oracle_matches_the_references_stateful_tick_bodies(oracle):
+    """The same for the hot-path units that carry state: the WHOLE `_tick` bodies
+    of Osc, Ramp, Shape, Filter (with its LP coefficient function), Noise, FixedDelay, CombFilter, AllPass and Timer,
+    verbatim from the reference's source (ref_structure.json "tick_body"), translated line by line (tests/js2py.py) and
+    run chunk after chunk on known inputs; the oracle's render of the same circuit must equal the result bit for bit --
+    phase wrap, the biquad's f32-rounded feedback, `x || 0` on undefined history, the delay lines' index arithmetic and
+    the sample-and-hold of Noise included.  The sine table is built by the reference's own loop (waveTables.js:3-9)."""
+    import json, os, sys
+    import numpy as np
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import js2py
+    from js2py import F32, Bag, JSArray
+    from dusp_b200 import components as C, config
+    from dusp_b200.render import circuit_blob
+    bodies = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_structure.json")))["tick_body"]
+    SR, CH = 44100, 256
+
+    def fn(name, args="S", tail=""):
+        env = dict(js2py.ENV)
+        exec(js2py.translate(bodies[name] + tail, "f", args), env)
+        return env["f"], env
+
+    def noise(seed, n):  # a Noise unit at the default F: draw k + 1 at sample k, stored as f32
+        return np.array([2 * config.rand_tick(seed, k + 1) - 1 for k in range(n)], dtype=np.float64).astype(np.float32)
+
+    def js_out(x):  # renderChannelData.js:44
+        x = np.asarray(x, dtype=np.float32)
+        return np.where(np.isnan(x) | (x == 0), np.float32(0), x)
+
+    def check(name, unit, run_chunk, n_chunks, channel=0):
+        blob, _ = circuit_blob(unit)
+        got = oracle.render(blob, n_chunks * CH / SR)[channel][:n_chunks * CH]
+        want = np.concatenate([js_out(run_chunk(k)) for k in range(n_chunks)])
+        assert np.array_equal(got, want), (name, int(np.flatnonzero(got != want)[0]))
+
+    # ---- Osc (Osc.js:35-47), F driven by noise * 1000: negative phases, wraps, both table neighbours
+    sine = fn("sineTable", "S", "\nreturn sineTable")[0](None)
+    n_ch = 12
+    fsig = (noise(7, n_ch * CH).astype(np.float64) * 1000.0).astype(np.float32)
+    tick, _ = fn("Osc")
+    S = Bag(out=F32(CH), f=None, phase=0, waveTable=sine)
+
+    def osc_chunk(k):
+        S.f = F32(fsig[k * CH:(k + 1) * CH])
+        tick(S)
+        return S.out.a.copy()
+    check("Osc", C.Osc(C.Multiply(C.Noise(seed=7), 1000)), osc_chunk, n_ch)
+
+    # ---- Ramp (Ramp.js:25-40) past its end
+    tick, _ = fn("Ramp")
+    R = Bag(out=F32(CH), t=0, playing=True, duration=5000, y0=200, y1=100)
+    check("Ramp", C.Ramp(5000, 200, 100).trigger(), lambda k: (tick(R), R.out.a.copy())[1], 24)
+
+    # ---- Timer (Timer.js:37-42)
+    tick, _ = fn("Timer")
+    T = Bag(out=F32(CH), t=0, samplePeriod=1 / SR)
+    check("Timer", C.Timer(), lambda k: (tick(T), T.out.a.copy())[1], 8)
+
+    # ---- Shape (Shape/index.js:28-59), decay over 0.05 s: the playing sum, the lerp, the right edge after the finish
+    tick, _ = fn("Shape")
+    decay = F32([1 - x / SR for x in range(SR + 1)])  # shapeTables.js:3-25: table[x] = func(x / sampleRate), func = 1 - x
+    H = Bag(out=F32(CH), t=0, playing=True, duration=F32([0.05] * CH), min=F32([0] * CH), max=F32([1] * CH), leftEdge=0,
+            rightEdge="shape", shapeTableData=decay, finished=False)
+    H.finish = lambda: setattr(H, "finished", True)
+    check("Shape", C.Shape("decay", 0.05).trigger(), lambda k: (tick(H), H.out.a.copy())[1], 12)
+
+    # ---- Filter (Filter.js:27-51 + the LP coefficients :66-75): constant F, then F as a signal (recomputed per sample)
+    lp, _ = fn("Filter.LP", "S, f")
+    tick, _ = fn("Filter")
+    for variant in ("constant", "signal"):
+        n_ch = 6
+        x = noise(9, n_ch * CH)
+        if variant == "constant":
+            fs = np.full(n_ch * CH, 1000.0, dtype=np.float32)
+            unit = C.Filter(C.Noise(seed=9), 1000, "LP")
+        else:
+            fs = ((noise(11, n_ch * CH).astype(np.float64) * 300.0).astype(np.float32).astype(np.float64) + 900.0).astype(np.float32)
+            unit = C.Filter(C.Noise(seed=9), C.Sum(C.Multiply(C.Noise(seed=11), 300), 900), "LP")
+        nan = float("nan")
+        Fl = Bag(in_=None, f=None, out=[], lastF=None, x1=JSArray(), x2=JSArray(), y1=JSArray(), y2=JSArray(),
+                 a0=nan, a1=nan, a2=nan, b1=nan, b2=nan)   # `this.kind = ...` ran calculateCoefficients(undefined): NaN
+        Fl.calculateCoefficients = lambda f, Fl=Fl: lp(Fl, f)
+
+        def filt_chunk(k, Fl=Fl, x=x, fs=fs):
+            Fl.in_ = [F32(x[k * CH:(k + 1) * CH])]
+            Fl.f = F32(fs[k * CH:(k + 1) * CH])
+            tick(Fl)
+            return Fl.out[0].a.copy()
+        check("Filter " + variant, unit, filt_chunk, n_ch)
+
+    # ---- Noise (Noise.js:16-28): a draw per sample at the default F, sample-and-hold at F = 10 kHz
+    for f_hz, seed in ((SR, 21), (10000.0, 22)):
+        tick, env = fn("Noise")
+        k_draw = [0]
+
+        def rnd(seed=seed, k_draw=k_draw):
+            k_draw[0] += 1
+            return config.rand_tick(seed, k_draw[0])
+        env["M_random"] = rnd
+        N = Bag(out=[F32(CH)], f=[F32([f_hz] * CH)], phase=0, y=2 * config.rand_tick(seed, 0) - 1)
+        check("Noise %g" % f_hz, C.Noise(f_hz, seed=seed), lambda k, N=N, tick=tick: (tick(N), N.out[0].a.copy())[1], 5)
+
+    # ---- FixedDelay / CombFilter / AllPass (FixedDelay.js:14-20, CombFilter.js:11-17, AllPass.js:8-15)
+    for name, cls in (("FixedDelay", C.FixedDelay), ("CombFilter", C.CombFilter), ("AllPass", C.AllPass)):
+        n_ch = 8
+        x = noise(31, n_ch * CH)
+        tick, _ = fn(name)
+        D = Bag(in_=None, out=F32(CH), buffer=F32(441), tBuffer=0, feedbackGain=F32([0.6] * CH))
+        unit = cls(0.01) if name == "FixedDelay" else cls(0.01, 0.6)
+        unit.IN = C.Noise(seed=31)
+
+        def dly_chunk(k, D=D, x=x, tick=tick):
+            D.in_ = F32(x[k * CH:(k + 1) * CH])
+            tick(D)
+            return D.out.a.copy()
+        check(name, unit, dly_chunk, n_ch)
