@@ -147,6 +147,12 @@ tick_body["Filter.LP"] = body_after(text, r"LP: function\(f\) \{")
 tick_body["Filter.HP"] = body_after(text, r"HP: function\(f\) \{")
 text = open(os.path.join(comp, "Osc", "waveTables.js")).read()
 tick_body["sineTable"] = text[text.index("const PHI"):text.index("var sawTable")]
+tick_body["CircleBufferWriter"] = body_after(open(os.path.join(comp, "CircleBufferWriter.js")).read(), r"_tick\(\) \{")
+tick_body["CircleBufferReader"] = body_after(open(os.path.join(comp, "CircleBufferReader.js")).read(), r"_tick\(\) \{")
+text = open(os.path.join(src, "CircleBuffer.js")).read()
+tick_body["CircleBuffer.read"] = body_after(text, r"read\(c, t\) \{")
+tick_body["CircleBuffer.write"] = body_after(text, r"write\(c, t, y\) \{")
+tick_body["CircleBuffer.mix"] = body_after(text, r"mix\(c, t, y\) \{")
 out = {"components": out, "patches": patches, "front_door": front, "config": cfg, "tick_expr": tick_expr, "tick_body": tick_body}
 dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_structure.json")
 json.dump(out, open(dst, "w"), indent=1, sort_keys=True)

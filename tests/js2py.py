@@ -34,9 +34,11 @@ class JSArray(list):
     """A plain JavaScript array of Numbers: reading past the end gives `undefined`, writing extends."""
 
     def __getitem__(self, i):
+        i = int(i)
         return list.__getitem__(self, i) if 0 <= i < len(self) else None
 
     def __setitem__(self, i, v):
+        i = int(i)
         while len(self) <= i:
             self.append(None)
         list.__setitem__(self, i, v)

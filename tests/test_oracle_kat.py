@@ -528,3 +528,115 @@ def test_oracle_matches_the_references_stateful_tick_bodies(oracle):
             tick(D)
             return D.out.a.copy()
         check(name, unit, dly_chunk, n_ch)
+
+
+def test_oracle_matches_the_reference_bodies_on_the_benchmark_voice(oracle):
+    """BASELINE config 2's voice -- Noise -> LP Filter -> CircleBuffer feedback delay -> Pan, the circuit `bench.py`
+    times -- run by the reference's OWN code: every unit's `_tick` (Noise, Filter + LP coefficients, the two
+    CircleBufferWriters, the CircleBufferReader with CircleBuffer.read / write / mix, Multiply, Sum, Pan) translated from
+    the verbatim JavaScript (tests/js2py.py), wired as the reference wires them (a connected inlet reads the producing
+    outlet's chunk itself, Inlet.js:53; `mono` ports expose channel 0, Piglet.js:13-17), ticked in the circuit's order
+    chunk after chunk.  The oracle's render of the same blob must be bit-identical on both channels."""
+    import json, os, sys
+    import numpy as np
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import js2py
+    from js2py import F32, Bag, JSArray
+    import dusp_b200 as d
+    from dusp_b200 import components as C, patches as P, config
+    from dusp_b200.render import circuit_blob
+    ref = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_structure.json")))
+    bodies, exprs = ref["tick_body"], ref["tick_expr"]
+    CH, SR = 256, 44100
+
+    def fn(name, args="S"):
+        env = dict(js2py.ENV)
+        exec(js2py.translate(bodies[name], "f", args), env)
+        return env["f"], env
+
+    # the circuit (tests/circuits.w3_voice): seeded noise -> LP -> feedback delay (pre-wiping writer, tap, gain, mixing writer) -> pan
+    filt = C.Filter(C.Noise(seed=77), 1234.5, "LP")
+    mt = P.MultiTapDelay(1, 1.0, filt)
+    tap = mt.addFeedback(0.137, 0.55, 0)
+    root = C.Pan(C.Sum(filt, tap), -0.3)
+    blob, _ = circuit_blob(root)
+    units = list(root.circuit.units)
+
+    cb_read, cb_write, cb_mix = (fn("CircleBuffer." + k, a)[0] for k, a in (("read", "S, c, t"), ("write", "S, c, t, y"), ("mix", "S, c, t, y")))
+
+    class CB:  # CircleBuffer.js:3-35
+        def __init__(self, b):
+            self.lengthInSamples = b.lengthInSamples
+            self.channelData = JSArray(F32(b.lengthInSamples) for _ in range(b.numberOfChannels))
+        read = lambda self, c, t: cb_read(self, c, t)
+        write = lambda self, c, t, y: cb_write(self, c, t, y)
+        mix = lambda self, c, t, y: cb_mix(self, c, t, y)
+    buffers = {}
+    chunk_of = {}   # outlet -> its SignalChunk's channelData (a list of F32)
+    bags, ticks = [], []
+    for u in units:
+        for o in u.outletsOrdered:
+            chunk_of[id(o)] = JSArray(F32(CH) for _ in range(o.numberOfChannels))
+    lp = fn("Filter.LP", "S, f")[0]
+    for u in units:
+        S = Bag()
+        for o in u.outletsOrdered:
+            setattr(S, o.name, chunk_of[id(o)][0] if o.exposeAsMono else chunk_of[id(o)])
+        for i in u.inletsOrdered:
+            if i.noData:
+                continue
+            data = chunk_of[id(i.outlet)] if i.connected else JSArray(F32([v] * CH) for v in i.chunk)
+            setattr(S, "in_" if i.name == "in" else i.name, data[0] if i.exposeAsMono else data)
+        kind = type(u).__name__
+        if kind == "Noise":
+            tick, env = fn("Noise")
+            k_draw = [0]
+
+            def rnd(seed=u.seed, k_draw=k_draw):
+                k_draw[0] += 1
+                return config.rand_tick(seed, k_draw[0])
+            env["M_random"] = rnd
+            S.phase, S.y = u.phase, u.y
+        elif kind == "Filter":
+            tick = fn("Filter")[0]
+            nan = float("nan")
+            S.__dict__.update(lastF=None, x1=JSArray(), x2=JSArray(), y1=JSArray(), y2=JSArray(), a0=nan, a1=nan, a2=nan, b1=nan, b2=nan)
+            S.calculateCoefficients = lambda f, S=S: lp(S, f)
+        elif kind in ("CircleBufferWriter", "CircleBufferReader"):
+            tick = fn(kind)[0]
+            S._buffer = buffers.setdefault(id(u.buffer), CB(u.buffer))
+            S.__dict__.update(t=u.t, numberOfChannels=u.buffer.numberOfChannels, tickInterval=CH,
+                              preWipe=bool(getattr(u, "preWipe", False)), postWipe=bool(getattr(u, "postWipe", False)))
+        elif kind in ("Multiply", "Sum", "Pan"):
+            src = _js_statement_to_python(exprs[kind]["stmt"], exprs[kind]["aliases"], exprs[kind]["helpers"])
+            env = {"jspow": _jspow, "abs": abs}
+            exec(src, env)
+            per_sample = env["f"]
+            fields = {"compensationDB": getattr(u, "compensationDB", None)}
+
+            def tick(S, per_sample=per_sample, fields=fields, kind=kind):
+                for t in range(CH):
+                    if kind == "Pan":   # Pan.js:18-24: mono in / pan, two output channels
+                        l, r = per_sample({"in": S.in_[t], "pan": S.pan[t]}, fields)
+                        S.out[0][t], S.out[1][t] = l, r
+                    else:               # SignalCombiner: channel c of a and b (one channel each here)
+                        S.out[0][t] = per_sample({"a": S.a[0][t], "b": S.b[0][t]}, fields)[0]
+        else:
+            raise AssertionError("unit kind without a translated body: " + kind)
+        bags.append(S)
+        ticks.append(tick)
+    n_chunks = 70   # 0.406 s: the 0.137 s feedback tap comes round twice
+    out = [[], []]
+    root_chunk = chunk_of[id(root.outletsOrdered[0])]
+    for k in range(n_chunks):
+        for S, tick in zip(bags, ticks):
+            tick(S)
+        for c in range(2):
+            out[c].append(root_chunk[c].a.copy())
+    got = oracle.render(blob, n_chunks * CH / SR)
+    for c in range(2):
+        w = np.concatenate(out[c])
+        w = np.where(np.isnan(w) | (w == 0), np.float32(0), w)
+        g = got[c][:n_chunks * CH]
+        assert np.array_equal(g, w), (c, int(np.flatnonzero(g != w)[0]))
+        assert float(np.max(np.abs(w))) > 0.05
