@@ -142,6 +142,19 @@ for u, f, pat in (("Osc", "Osc/Osc.js", r"_tick = function\(clock\) \{"), ("Ramp
                   ("AllPass", "AllPass.js", r"_tick\(\) \{"), ("Timer", "Timer.js", r"_tick = function\(\) \{"),
                   ("Shape", "Shape/index.js", r"_tick = function\(\) \{")):
     tick_body[u] = body_after(open(os.path.join(comp, f)).read(), pat)
+# ... and every other non-spectral component's whole _tick, keyed by class name (the first nine above win)
+for f in sorted(os.listdir(comp)):
+    if not f.endswith(".js") or f == "index.js":
+        continue
+    text = open(os.path.join(comp, f)).read()
+    mname = re.search(r"^function\s+([A-Z]\w*)\s*\(|^class\s+([A-Z]\w*)\s+extends", text, re.M)
+    mt = re.search(r"_tick\s*(?:=\s*function)?\s*\(([^)]*)\)\s*\{", text)
+    if mname and mt:
+        nm = mname.group(1) or mname.group(2)
+        tick_body.setdefault(nm, body_after(text, r"_tick\s*(?:=\s*function)?\s*\([^)]*\)\s*\{"))
+        tick_body[nm + ".args"] = mt.group(1).strip()
+text = open(os.path.join(comp, "Osc", "MultiChannelOsc.js")).read()
+tick_body["MultiChannelOsc"] = body_after(text, r"_tick\s*(?:=\s*function)?\s*\([^)]*\)\s*\{")
 text = open(os.path.join(comp, "Filter.js")).read()
 tick_body["Filter.LP"] = body_after(text, r"LP: function\(f\) \{")
 tick_body["Filter.HP"] = body_after(text, r"HP: function\(f\) \{")
@@ -149,6 +162,9 @@ text = open(os.path.join(comp, "Osc", "waveTables.js")).read()
 tick_body["sineTable"] = text[text.index("const PHI"):text.index("var sawTable")]
 tick_body["CircleBufferWriter"] = body_after(open(os.path.join(comp, "CircleBufferWriter.js")).read(), r"_tick\(\) \{")
 tick_body["CircleBufferReader"] = body_after(open(os.path.join(comp, "CircleBufferReader.js")).read(), r"_tick\(\) \{")
+tick_body["MonoDelay"] = body_after(open(os.path.join(comp, "MonoDelay.js")).read(), r"_tick = function\(clock\) \{")
+tick_body["Delay"] = body_after(open(os.path.join(comp, "Delay.js")).read(), r"_tick\(clock\) \{")
+tick_body["ReadBackDelay"] = body_after(open(os.path.join(comp, "ReadBackDelay.js")).read(), r"_tick = function\(\) \{")
 text = open(os.path.join(src, "CircleBuffer.js")).read()
 tick_body["CircleBuffer.read"] = body_after(text, r"read\(c, t\) \{")
 tick_body["CircleBuffer.write"] = body_after(text, r"write\(c, t, y\) \{")

@@ -640,3 +640,41 @@ def test_oracle_matches_the_reference_bodies_on_the_benchmark_voice(oracle):
         g = got[c][:n_chunks * CH]
         assert np.array_equal(g, w), (c, int(np.flatnonzero(g != w)[0]))
         assert float(np.max(np.abs(w))) > 0.05
+
+
+def _ref_runtime_cases():
+    import circuits
+    return sorted(circuits.CASES)
+
+
+@pytest.mark.parametrize("name", _ref_runtime_cases())
+def test_parity_cases_run_by_the_references_own_code(oracle, name):
+    """Every parity case of tests/circuits.py whose units all have a translated body (tests/ref_runtime.py: the
+    reference's verbatim `_tick`s run by tests/js2py.py) is rendered by that code and compared with the oracle, bit for
+    bit (cases with a libm transcendental on the device keep their 1e-5 class only on the GPU side: here both sides call
+    the host's libm).  Cases with events, multi-rate units or kinds without a translated body are skipped."""
+    import os, sys
+    import numpy as np
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import circuits, ref_runtime
+    import dusp_b200 as d
+    from dusp_b200.render import circuit_blob
+    d.config.seed(12345)
+    fac, seconds, _ = circuits.CASES[name]
+    unit = fac()
+    blob, _ = circuit_blob(unit)
+    if "\nEV " in blob or "\nEPOCH" in blob or "\nTG " in blob or "WARMUP" in blob:
+        pytest.skip("events / graph edits")
+    outlet = unit if getattr(unit, "isOutlet", False) else unit.defaultOutlet
+    try:
+        rt = ref_runtime.RefRuntime(outlet.unit)
+    except ref_runtime.Unsupported as e:
+        pytest.skip("no translated body: %s" % e)
+    n_chunks = min(int(seconds * 44100) // 256 + 1, 40)
+    want = rt.render(outlet, n_chunks)
+    got = oracle.render(blob, n_chunks * 256 / 44100)
+    if len(got) != len(want):
+        pytest.skip("channel counts grow at run time")
+    for c in range(len(want)):
+        g = got[c][:n_chunks * 256]
+        assert np.array_equal(g, want[c]), (name, c, int(np.flatnonzero(g != want[c])[0]))
