@@ -124,7 +124,7 @@ for u in ["Multiply", "Divide", "Subtract", "Sum", "Gain", "Clip", "HardClipAbov
 # whole _tick bodies of the stateful hot-path units, verbatim: tests/js2py.py
 # translates them line by line and tests/test_oracle_kat.py runs them against the oracle
 def body_after(text, pattern):
-    m = re.search(pattern, text)
+    m = re.search(pattern, text, re.M)
     b = text[m.end():]
     depth, i = 1, 0
     while depth:
@@ -153,6 +153,15 @@ for f in sorted(os.listdir(comp)):
         nm = mname.group(1) or mname.group(2)
         tick_body.setdefault(nm, body_after(text, r"_tick\s*(?:=\s*function)?\s*\([^)]*\)\s*\{"))
         tick_body[nm + ".args"] = mt.group(1).strip()
+# trigger() / stop() of the units a Retriggerer can target
+for u, f in (("Ramp", "Ramp.js"), ("Shape", "Shape/index.js"), ("AHD", "AHD.js"), ("Timer", "Timer.js")):
+    text = open(os.path.join(comp, f)).read()
+    for meth in ("trigger", "stop"):
+        m = re.search(r"(?:\.prototype\.%s\s*=\s*function\s*\(\)|^\s*%s\(\))\s*\{" % (meth, meth), text, re.M)
+        if m:
+            tick_body[u + "." + meth] = body_after(text, r"(?:\.prototype\.%s\s*=\s*function\s*\(\)|^\s*%s\(\))\s*\{" % (meth, meth))
+text = open(os.path.join(comp, "SporadicRetrigger.js")).read()
+tick_body["SporadicRetriggerer"] = body_after(text, r"_tick\(\) \{")
 text = open(os.path.join(comp, "Osc", "MultiChannelOsc.js")).read()
 tick_body["MultiChannelOsc"] = body_after(text, r"_tick\s*(?:=\s*function)?\s*\([^)]*\)\s*\{")
 text = open(os.path.join(comp, "Filter.js")).read()

@@ -97,6 +97,7 @@ def _expr(e):
     e = e.strip().rstrip(";")
     e = re.sub(r"\bthis\.in\b", "S.in_", e)
     e = re.sub(r"\bthis\.", "S.", e)
+    e = re.sub(r"\bthis\b", "S", e)
     e = re.sub(r"\b(?:Unit|config)\.sampleRate\b", "44100", e)
     e = re.sub(r"\bS\.sampleRate\b", "44100", e)
     e = re.sub(r"\bS\.(?:IN|OUT)\.chunkSize\b", "256", e)

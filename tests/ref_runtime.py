@@ -119,8 +119,19 @@ class RefRuntime:
             write = lambda self, c, t, y: cb[1](self, c, t, y)
             mix = lambda self, c, t, y: cb[2](self, c, t, y)
         self.steps = []
+        bag_of = {}
+
+        class Target:  # what a Retriggerer holds: the target unit with its own trigger() (the translated method body)
+            def __init__(self, unit):
+                self.unit = unit
+                kind = type(unit).__name__
+                if kind + ".trigger" not in BODIES:
+                    raise Unsupported("retrigger target " + kind)
+                self.f = fn(kind + ".trigger")[0]
+            trigger = property(lambda self: (lambda: self.f(bag_of[id(self.unit)])))
         for u in self.units:
             S = Bag()
+            bag_of[id(u)] = S
             S.label = u.label
             for o in u.outletsOrdered:
                 setattr(S, o.name, chunk_of[id(o)][0] if o.exposeAsMono else chunk_of[id(o)])
@@ -193,11 +204,23 @@ class RefRuntime:
                     S.state = 0
                     S.playing = False
                 S.stop = stop
+            elif kind in ("Retriggerer", "SporadicRetriggerer"):
+                tick, env = _fn(kind)
+                S.__dict__.update(_target=Target(u.target) if u.target is not None else None, tickInterval=CH)
+                if kind == "Retriggerer":
+                    S.t = u.t
+                else:
+                    k_draw = [u.draw - 1]
+
+                    def rnd(seed=u.seed, k_draw=k_draw):  # the injected generator: one draw per tick from draw 0 on
+                        k_draw[0] += 1
+                        return config.rand_tick(seed, k_draw[0])
+                    env["M_random"] = rnd
             elif kind == "SampleRateRedux":
                 tick = fn("SampleRateRedux")[0]
                 S.val = JSArray([np.float64(0)])
                 S.timeSinceLastUpdate = float("inf")
-            elif kind in BODIES and kind not in ("Retriggerer", "SporadicRetriggerer", "Monitor", "GreaterThan", "LessThan", "MultiChannelOsc"):
+            elif kind in BODIES and kind not in ("Monitor", "GreaterThan", "LessThan", "MultiChannelOsc"):
                 # stateless units and the rest: the whole _tick, the unit's plain fields as they are in the mirror
                 args = BODIES.get(kind + ".args", "")
                 takes_clock = bool(args)
