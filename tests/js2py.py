@@ -16,7 +16,7 @@ class F32:
     """A Float32Array: stores round to binary32, reads return Python floats, out-of-range reads are `undefined` (None)."""
 
     def __init__(self, n_or_values):
-        self.a = np.zeros(n_or_values, dtype=np.float32) if isinstance(n_or_values, int) else np.array(n_or_values, dtype=np.float32)
+        self.a = np.zeros(int(n_or_values), dtype=np.float32) if np.isscalar(n_or_values) else np.array(n_or_values, dtype=np.float32)
 
     def __len__(self):
         return len(self.a)

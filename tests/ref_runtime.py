@@ -97,8 +97,6 @@ class RefRuntime:
     def __init__(self, root_unit, stmt_translator=None):
         from dusp_b200 import config
         circuit = root_unit.circuit
-        if getattr(circuit, "events", None):
-            raise Unsupported("events")
         self.units = list(circuit.units)
         self.clock = 0
         chunk_of = {}
@@ -156,6 +154,9 @@ class RefRuntime:
             elif kind == "Osc":
                 tick = fn("Osc")[0]
                 S.phase, S.waveTable = u.phase, _wave_table(u.waveform)
+            elif kind == "MultiChannelOsc":
+                tick, takes_clock = fn("MultiChannelOsc", "S, clock")[0], True
+                S.phase, S.waveTable = JSArray(np.float64(x) for x in u.phase), _wave_table(u.waveform)
             elif kind == "Ramp":
                 tick = fn("Ramp")[0]
                 S.__dict__.update(t=u.t, playing=bool(u.playing), duration=u.duration, y0=u.y0, y1=u.y1)
@@ -232,10 +233,31 @@ class RefRuntime:
                 raise Unsupported(kind)
             self.steps.append((S, tick, takes_clock))
 
-    def render(self, root_outlet, n_chunks):
+    def apply_initial_props(self, blob):
+        """State at the first tick as the blob has it (`P` records): events due at t = 0 have run by then (Circuit.js:23)."""
+        ui = -1
+        for t in (l.split() for l in blob.splitlines()):
+            if not t:
+                continue
+            if t[0] == "U":
+                ui += 1
+            elif t[0] == "P" and 0 <= ui < len(self.steps):
+                S = self.steps[ui][0]
+                if hasattr(S, t[1]) and isinstance(getattr(S, t[1]), (bool, int, float, np.floating)):
+                    setattr(S, t[1], bool(float(t[2])) if isinstance(getattr(S, t[1]), bool) else float(t[2]))
+            elif t[0] == "END":
+                break
+
+    def render(self, root_outlet, n_chunks, events=()):
+        """events: (chunk, unit index, field, value) -- the `EV` records of the blob: what the circuit's event queue
+        assigns before that chunk's tick (Circuit.js:23,57-65), as found by the host mirror."""
         chunk = self.chunk_of[id(root_outlet)]
         out = []
         for k in range(n_chunks):
+            for ck, ui, field, value in events:
+                if ck == k:
+                    S = self.steps[ui][0]
+                    setattr(S, field, bool(value) if isinstance(getattr(S, field, None), bool) else value)
             for S, tick, takes_clock in self.steps:
                 with np.errstate(all="ignore"):
                     tick(S, self.clock) if takes_clock else tick(S)

@@ -663,8 +663,9 @@ def test_parity_cases_run_by_the_references_own_code(oracle, name):
     fac, seconds, _ = circuits.CASES[name]
     unit = fac()
     blob, _ = circuit_blob(unit)
-    if "\nEV " in blob or "\nEPOCH" in blob or "WARMUP" in blob:
-        pytest.skip("events / graph edits")
+    if "\nEPOCH" in blob or "WARMUP" in blob:
+        pytest.skip("graph edits")
+    events = [(int(t[1]), int(t[2]), t[3], float(t[4])) for t in (l.split() for l in blob.splitlines()) if t and t[0] == "EV"]
     # a second, untouched instance for the reference's code (writing the blob runs target.trigger() on the live objects to
     # record what it assigns)
     d.config.seed(12345)
@@ -677,7 +678,8 @@ def test_parity_cases_run_by_the_references_own_code(oracle, name):
     except ref_runtime.Unsupported as e:
         pytest.skip("no translated body: %s" % e)
     n_chunks = min(int(seconds * 44100) // 256 + 1, 40)
-    want = rt.render(outlet, n_chunks)
+    rt.apply_initial_props(blob)
+    want = rt.render(outlet, n_chunks, events)
     got = oracle.render(blob, n_chunks * 256 / 44100)
     if len(got) != len(want):
         pytest.skip("channel counts grow at run time")
