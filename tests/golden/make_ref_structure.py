@@ -5,7 +5,11 @@ of the form `this.NAME = param || <number>`, and the state fields the constructo
 tests/test_host_mirror.py compares the Python mirror against it, so a wrong port name, port order or default in the
 mirror -- which the oracle, fed by the same mirror, could not see -- fails a test.
 
-usage: python tests/golden/make_ref_structure.py [/root/reference]"""
+The same pass also pulls the verbatim per-sample statements / `_tick` bodies out of the source; those are NOT committed:
+with a second argument the script writes everything to that scratch path, which is how tests/ref_text.py hands the
+reference's own text to the tests that execute it (only where /root/reference exists).
+
+usage: python tests/golden/make_ref_structure.py [/root/reference [scratch.json]]"""
 import json, os, re, sys
 
 ref = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
@@ -179,6 +183,12 @@ tick_body["CircleBuffer.read"] = body_after(text, r"read\(c, t\) \{")
 tick_body["CircleBuffer.write"] = body_after(text, r"write\(c, t, y\) \{")
 tick_body["CircleBuffer.mix"] = body_after(text, r"mix\(c, t, y\) \{")
 out = {"components": out, "patches": patches, "front_door": front, "config": cfg, "tick_expr": tick_expr, "tick_body": tick_body}
-dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_structure.json")
-json.dump(out, open(dst, "w"), indent=1, sort_keys=True)
-print("wrote %d unit classes and %d patches to %s" % (len(out["components"]), len(out["patches"]), dst))
+if len(sys.argv) > 2:
+    # everything, the verbatim statements included: a scratch file for the tests that execute the reference's text
+    # (tests/ref_text.py runs this script against /root/reference at test time; that text is never committed)
+    json.dump(out, open(sys.argv[2], "w"))
+else:
+    # the committed fixture: structural FACTS only (names, orders, flags, numbers) -- no source text
+    dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_structure.json")
+    json.dump({k: v for k, v in out.items() if k not in ("tick_expr", "tick_body")}, open(dst, "w"), indent=1, sort_keys=True)
+    print("wrote %d unit classes and %d patches to %s" % (len(out["components"]), len(out["patches"]), dst))

@@ -1,5 +1,5 @@
 """Test infrastructure: a line-oriented translator for the small JavaScript function bodies of the reference's `_tick`s
-(verbatim text in tests/golden/ref_structure.json, extracted from the reference's source in the build container) into
+(verbatim text read from the reference's source at test time by tests/ref_text.py -- never committed) into
 Python, so that the reference's OWN statements can be executed against the oracle without a JavaScript engine.
 
 What makes that sound: JavaScript's Number arithmetic is IEEE binary64, as Python's float arithmetic; `%` on Numbers is

@@ -1,5 +1,5 @@
 """Test infrastructure: a circuit of the host mirror run by the REFERENCE'S OWN `_tick` code -- the verbatim JavaScript
-bodies in tests/golden/ref_structure.json (extracted from the reference's source in the build container), translated by
+bodies read from the reference's source at test time (tests/ref_text.py; never committed), translated by
 tests/js2py.py -- wired as the reference wires units (a connected inlet reads the producing outlet's SignalChunk itself,
 Inlet.js:53; `mono` ports expose channel 0, Piglet.js:13-17; constants fill their chunk, Inlet.js:76-93), ticked in the
 circuit's order with the circuit's clock (Circuit.js:34-39), copied out as renderChannelData.js:42-44 does.
@@ -13,9 +13,38 @@ import numpy as np
 import js2py
 from js2py import F32, Bag, JSArray
 
+import ref_text
+
 CH, SR = 256, 44100
-_REF = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_structure.json")))
-BODIES, EXPRS = _REF["tick_body"], _REF["tick_expr"]
+
+
+class _Lazy(dict):
+    """The reference's verbatim `_tick` bodies, pulled from its source on first use (tests/ref_text.py; skips the test when
+    the reference is not on this machine)."""
+
+    def __init__(self, key):
+        super().__init__()
+        self.key, self.loaded = key, False
+
+    def _load(self):
+        if not self.loaded:
+            self.update(ref_text.reference_text()[self.key])
+            self.loaded = True
+
+    def __getitem__(self, k):
+        self._load()
+        return dict.__getitem__(self, k)
+
+    def __contains__(self, k):
+        self._load()
+        return dict.__contains__(self, k)
+
+    def get(self, k, default=None):
+        self._load()
+        return dict.get(self, k, default)
+
+
+BODIES, EXPRS = _Lazy("tick_body"), _Lazy("tick_expr")
 
 
 class Unsupported(Exception):

@@ -306,7 +306,7 @@ def test_shared_reciprocal_division_is_ieee_division(tmp_path):
 
 # ---- the reference's own per-sample statements, executed ----------------------------------------------------------
 def _js_statement_to_python(stmt, aliases, helpers):
-    """The innermost statement of a stateless unit's _tick (verbatim JavaScript from tests/golden/ref_structure.json)
+    """The innermost statement of a stateless unit's _tick (verbatim JavaScript, read from the reference's source at test time: tests/ref_text.py)
     as the source of a Python function of the unit's inlets.  JavaScript's arithmetic operators on Numbers ARE IEEE
     double operations, as Python's on floats; only the surface differs."""
     import re
@@ -366,8 +366,8 @@ def _jspow(a, b):
 
 def test_oracle_matches_the_references_own_tick_statements(oracle):
     """The strongest pin available without a JavaScript engine: the per-sample statements of the stateless units'
-    `_tick`s, taken VERBATIM from the reference's source in the build container (tests/golden/make_ref_structure.py ->
-    ref_structure.json "tick_expr"), are translated token for token into Python (IEEE double arithmetic on both sides),
+    `_tick`s, taken VERBATIM from the reference's source at test time (tests/ref_text.py runs
+    tests/golden/make_ref_structure.py on /root/reference; nothing of it is committed; skipped where the reference is absent), are translated token for token into Python (IEEE double arithmetic on both sides),
     run on known inputs -- seeded Noise units, whose samples the test computes itself from the injected generator --
     and compared with the oracle's render of the same unit: bit for bit, or within an ulp of f32 where Math.pow runs."""
     import json, math, os
@@ -375,7 +375,8 @@ def test_oracle_matches_the_references_own_tick_statements(oracle):
     import dusp_b200 as d
     from dusp_b200 import components as C, config
     from dusp_b200.render import circuit_blob
-    ref = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_structure.json")))["tick_expr"]
+    import ref_text
+    ref = ref_text.reference_text()["tick_expr"]
     n = 512
     checked = 0
 
@@ -415,7 +416,7 @@ def test_oracle_matches_the_references_own_tick_statements(oracle):
 def test_oracle_matches_the_references_stateful_tick_bodies(oracle):
     """The same for the hot-path units that carry state: the WHOLE `_tick` bodies
     of Osc, Ramp, Shape, Filter (with its LP coefficient function), Noise, FixedDelay, CombFilter, AllPass and Timer,
-    verbatim from the reference's source (ref_structure.json "tick_body"), translated line by line (tests/js2py.py) and
+    verbatim from the reference's source (tests/ref_text.py, read at test time), translated line by line (tests/js2py.py) and
     run chunk after chunk on known inputs; the oracle's render of the same circuit must equal the result bit for bit --
     phase wrap, the biquad's f32-rounded feedback, `x || 0` on undefined history, the delay lines' index arithmetic and
     the sample-and-hold of Noise included.  The sine table is built by the reference's own loop (waveTables.js:3-9)."""
@@ -426,7 +427,8 @@ def test_oracle_matches_the_references_stateful_tick_bodies(oracle):
     from js2py import F32, Bag, JSArray
     from dusp_b200 import components as C, config
     from dusp_b200.render import circuit_blob
-    bodies = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_structure.json")))["tick_body"]
+    import ref_text
+    bodies = ref_text.reference_text()["tick_body"]
     SR, CH = 44100, 256
 
     def fn(name, args="S", tail=""):
@@ -545,7 +547,8 @@ def test_oracle_matches_the_reference_bodies_on_the_benchmark_voice(oracle):
     import dusp_b200 as d
     from dusp_b200 import components as C, patches as P, config
     from dusp_b200.render import circuit_blob
-    ref = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_structure.json")))
+    import ref_text
+    ref = ref_text.reference_text()
     bodies, exprs = ref["tick_body"], ref["tick_expr"]
     CH, SR = 256, 44100
 
